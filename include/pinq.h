@@ -1,0 +1,223 @@
+/*
+ * pinq.h -- C-ABI of libpinq: the B200 (sm_100a) neural-point SDF query path of PIN-SLAM.
+ *
+ * The reference (kelly7707/PIN_SLAM) is pure Python/PyTorch and has no FFI layer; the seam it
+ * offers is its Python class API.  Every entry point below names the reference function
+ * (path:line relative to the reference root) whose arithmetic it replaces.  The Python mirror
+ * in pin_slam_b200/{model,utils} binds these with ctypes.
+ *
+ * Conventions
+ *   - all pointers are DEVICE pointers unless the parameter name starts with h_;
+ *   - every call is asynchronous on `stream` (a cudaStream_t passed as void*), never
+ *     synchronises the device and never allocates (callers own all buffers);
+ *   - return value: 0 = success, negative = PINQ_ERR_*; pinq_last_error() gives the text;
+ *   - index type on the device is int32 (the reference uses int64: model/neural_points.py:47);
+ *     -1 means "empty / invalid" exactly as in the reference.
+ */
+#ifndef PINQ_H_
+#define PINQ_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PINQ_OK 0
+#define PINQ_ERR_BAD_ARG (-1)
+#define PINQ_ERR_CUDA (-2)
+#define PINQ_ERR_UNSUPPORTED (-3)
+
+#define PINQ_MAX_STENCIL 343 /* (2*3+1)^3: num_nei_cells <= 3 */
+
+/* flags for pinq_query_args.flags */
+#define PINQ_F_LOCAL 1u        /* query_locally=True: candidate filter + local index from cand[].w    */
+#define PINQ_F_TRAINING 2u     /* training_mode=True: certainty scatter-add (+ ts amax when query_ts)  */
+#define PINQ_F_ROTATE 4u       /* after_pgo=True: rotate x-p_k into the point frame (tools.py:316)     */
+#define PINQ_F_RECIP_DIV 8u    /* floor(x*(1/res)) instead of floor(x/res): CUDA-eager oracle (H1)     */
+#define PINQ_F_SKIP_EMPTY 16u  /* mesher: sdf = 0 where nn_count == 0 (utils/mesher.py:96-103)         */
+
+const char* pinq_last_error(void);
+int pinq_version(void);
+
+/* ---- voxel-hash index -------------------------------------------------------------------
+ * The table is the reference's direct-mapped `buffer_pt_index` (model/neural_points.py:73)
+ * held as dense int32[buffer_size]; slot(cell) = (cell . primes) mod buffer_size with the
+ * reference's signed-fmod + negative-index wrap (neural_points.py:216, 472). */
+
+/* model/neural_points.py:73, 377 -- table[:] = -1 */
+int pinq_table_clear(int32_t* table, uint32_t buffer_size, void* stream);
+
+/* model/neural_points.py:214-216 -- slots[i] = slot(floor(xyz[i]/res)) */
+int pinq_hash_points(const float* xyz, int64_t n, float res, uint32_t buffer_size, uint32_t flags,
+                     int32_t* slots, void* stream);
+
+/* model/neural_points.py:218, 242 -- out[i] = table[slots[i]] */
+int pinq_table_gather(const int32_t* table, const int32_t* slots, int64_t n, int32_t* out, void* stream);
+
+/* model/neural_points.py:247, 400, 422 -- table[slots[i]] = values[i] with the CPU reference's
+ * sequential semantics: among duplicate slots the highest i wins.  `scratch` = int32[n]. */
+int pinq_table_scatter_last_wins(int32_t* table, const int32_t* slots, const int32_t* values, int64_t n,
+                                 void* stream);
+
+/* model/neural_points.py:221-231 -- update_mask[i] = empty | moved-away | stale (uint8 0/1).
+ * hash_idx = table[slots]; map arrays may be empty (m == 0 -> all ones). */
+int pinq_update_mask(const float* sample_xyz, const int32_t* hash_idx, int64_t n, const float* map_xyz,
+                     const int64_t* map_ts_update, int64_t m, const float* travel_dist, int64_t cur_ts,
+                     float res, float diff_travel_dist_local, uint8_t* update_mask, void* stream);
+
+/* Order-preserving stream compaction helper: out_index[j] = i for the j-th set flag; *d_count = #set.
+ * `scratch` must hold pinq_compact_scratch_bytes(n) bytes.  (replaces boolean-mask indexing,
+ * model/neural_points.py:239, 293-296, 302) */
+int64_t pinq_compact_scratch_bytes(int64_t n);
+int pinq_compact_flags(const uint8_t* flags, int64_t n, int32_t* out_index, int32_t* d_count, void* scratch,
+                       void* stream);
+
+/* utils/tools.py:409-442 (mode 0, closest to voxel centre) and :444-477 (mode 1, min `value`).
+ * Three steps so that the caller owns all memory:
+ *   1. pinq_vds_prepare : per-point quirky linear key (scalar V, hazard H5) + quantised score;
+ *                         needs the two global reductions -> d_minmax float[8] scratch.
+ *   2. caller sorts nothing: pinq_vds_select groups by key with an open-addressing scratch table
+ *      (uint64 keys[cap], uint64 best[cap], cap = power of two >= 2n) and atomically keeps the
+ *      minimal packed (score, index) per key;
+ *   3. pinq_vds_emit compacts the winners; the caller orders them by key (ascending) -- the
+ *      reference's output order is the sorted unique key order. */
+int pinq_vds_prepare(const float* xyz, int64_t n, float voxel, const float* value /*nullable*/, int mode,
+                     float* d_scratch8, int64_t* keys, int32_t* qscore, void* stream);
+int pinq_vds_select(const int64_t* keys, const int32_t* qscore, int64_t n, uint64_t* tab_keys,
+                    uint64_t* tab_best, uint64_t cap, void* stream);
+int pinq_vds_emit(const uint64_t* tab_keys, const uint64_t* tab_best, uint64_t cap, int64_t n,
+                  int64_t* out_keys, int32_t* out_index, int32_t* d_count, void* stream);
+
+/* model/neural_points.py:272-305 -- local-map window: flags[i] = ||p_i - sensor||^2 < r^2 and
+ * |travel_dist[cur_ts] - travel_dist[ts_used[i]]| < diff (uint8). */
+int pinq_local_mask(const float* map_xyz, const int64_t* ts_create, const int64_t* ts_update, int64_t m,
+                    const float* sensor_xyz3, const float* travel_dist, int64_t cur_ts, float radius2,
+                    float diff_travel_dist_local, int use_mid_ts, uint8_t* flags, void* stream);
+
+/* Packed candidate record used by the fused kernels: cand[i] = {x, y, z, bits(int32 local)} where
+ * local = global2local[i] if the point also passes the travel-distance filter of
+ * model/neural_points.py:480-488, else -1.  global2local may be NULL (global queries: w = i). */
+int pinq_pack_candidates(const float* map_xyz, const int64_t* ts_create, int64_t m, const int64_t* global2local,
+                         const float* travel_dist, int64_t cur_ts, float diff_travel_dist_local,
+                         float* cand4, void* stream);
+
+/* ---- neighbour search -------------------------------------------------------------------- */
+typedef struct pinq_map_view {
+    const int32_t* table;       /* [buffer_size]                                              */
+    uint32_t buffer_size;
+    float resolution;           /* voxel_size_m                                               */
+    float max_valid_dist2;      /* model/neural_points.py:457                                 */
+    int32_t kn;                 /* stencil size (81 for run_kitti)                            */
+    const int32_t* stencil_dx;  /* [kn,3] int32 neighbour cell offsets (neural_points.py:439) */
+    const float* cand4;         /* [M] packed candidates (pinq_pack_candidates)               */
+    int64_t m;                  /* number of neural points (global)                           */
+} pinq_map_view;
+
+/* model/neural_points.py:459-509 -- standalone API form: writes dist2[n,kn] f32 and idx[n,kn] i64
+ * (global indices).  time_filtering reads ts_create / travel_dist exactly as the reference does. */
+int pinq_neighbor_search(const pinq_map_view* map, const float* xyz, int64_t n, uint32_t flags,
+                         const float* map_xyz, const int64_t* ts_create, const float* travel_dist,
+                         int64_t cur_ts, float diff_travel_dist_local, int time_filtering, float* out_dist2,
+                         int64_t* out_idx, void* stream);
+
+/* model/neural_points.py:511-525 -- max certainty over the stencil (global certainties). */
+int pinq_query_certainty(const pinq_map_view* map, const float* xyz, int64_t n, uint32_t flags,
+                         const float* map_xyz, const float* certainties, float* out, void* stream);
+
+/* ---- fused query -------------------------------------------------------------------------- */
+typedef struct pinq_decoder_view {
+    const float* W1; /* layers.0.weight [H, F+3] row-major (model/decoder.py:45) */
+    const float* b1; /* layers.0.bias   [H]                                      */
+    const float* W2; /* lout.weight     [1, H]                                   */
+    const float* b2; /* lout.bias       [1]                                      */
+    int32_t hidden;  /* H = 64                                                   */
+    int32_t in_dim;  /* F + 3 = 11                                               */
+    float sdf_scale; /* model/decoder.py:51-52, hazard H12                       */
+} pinq_decoder_view;
+
+typedef struct pinq_query_args {
+    pinq_map_view map;
+    pinq_decoder_view dec;
+    const float* xyz;          /* [n,3] query points                                              */
+    int64_t n;
+    uint32_t flags;            /* PINQ_F_*                                                        */
+    int32_t k;                 /* query_nn_k = 6                                                  */
+    int32_t feature_dim;       /* 8                                                               */
+    const float* features;     /* [Mx+1, F]: local_geo_features (LOCAL) or geo_features           */
+    float* certainties;        /* [Mx]: read for queried certainty; += w in TRAINING mode         */
+    const float* quats;        /* [Mx,4] or NULL (needed with PINQ_F_ROTATE)                      */
+    int64_t* ts_update;        /* [Mx] or NULL: amax with query_ts in TRAINING mode               */
+    const int64_t* query_ts;   /* [n] or NULL                                                     */
+    /* outputs (any may be NULL) */
+    float* sdf;                /* [n]   sum_k w_k s_k                 (tracker.py:245, mapper.py:468) */
+    float* grad_x;             /* [n,3] d sdf / d x                   (tools.py:174-184)              */
+    float* sdf_std;            /* [n]                                 (tracker.py:246-247)            */
+    int32_t* nn_count;         /* [n]   valid candidates over the whole stencil (neural_points.py:557) */
+    float* certainty;          /* [n]   sum_k w_k c_k                 (neural_points.py:651-656)      */
+    int32_t* knn_idx;          /* [n,k] top-k index (local or global), -1 invalid                    */
+    float* knn_w;              /* [n,k] normalised IDW weights                                       */
+    float* knn_d2;             /* [n,k] squared distances (9e3 invalid)                              */
+} pinq_query_args;
+
+/* neural_points.py:528-674 + decoder.py:66-88 + the weighted combine, in one pass.
+ * Supported specialisation: k=6, feature_dim=8, hidden=64, one hidden level, weighted_first=False. */
+int pinq_query_fused_fwd(const pinq_query_args* args, void* stream);
+
+/* Un-fused API form of query_feature (neural_points.py:574-632): geo_features_vector [n,k,F+3],
+ * weight [n,k], nn_count, certainty; same side effects as the fused form. */
+int pinq_query_feature(const pinq_query_args* args, float* feat_out, void* stream);
+
+typedef struct pinq_bwd_args {
+    pinq_decoder_view dec;
+    const float* xyz;          /* [n,3]                                                    */
+    int64_t n;
+    uint32_t flags;            /* PINQ_F_ROTATE only                                       */
+    int32_t k, feature_dim;
+    const float* point_xyz;    /* [Mx,3] positions indexed by knn_idx (local or global)    */
+    const float* quats;        /* [Mx,4] or NULL                                           */
+    const float* features;     /* [Mx+1,F]                                                 */
+    const int32_t* knn_idx;    /* [n,k] saved by the forward                               */
+    const float* knn_w;        /* [n,k]                                                    */
+    const float* grad_sdf;     /* [n] dL/dsdf                                              */
+    float* grad_features;      /* [Mx+1,F] accumulated (+=), may be NULL                   */
+    float* grad_W1;            /* [H,F+3] accumulated, NULL when the decoder is frozen (H11) */
+    float* grad_b1;            /* [H]                                                      */
+    float* grad_W2;            /* [1,H]                                                    */
+    float* grad_b2;            /* [1]                                                      */
+} pinq_bwd_args;
+
+/* hand-derived backward of the fused query w.r.t. features and decoder (replaces autograd through
+ * neural_points.py:562-632 and decoder.py:66-88 as triggered at utils/mapper.py:572). */
+int pinq_query_fused_bwd(const pinq_bwd_args* args, void* stream);
+
+/* ---- Gauss-Newton accumulation (utils/tracker.py:293-394, 468-491) ------------------------
+ * One pass over the source points: validity mask (nn >= min_nn, min_g < |g| < max_g, std < max_std),
+ * Geman-McClure weights (un-normalised), and the reduction of
+ *   out[0..20]  upper triangle of sum w J^T J (row-major, J = [p x g, g])
+ *   out[21..26] sum w r J          out[27] sum w      out[28] sum |r|      out[29] valid count
+ * in fp64.  `out` (double[32]) must be zeroed by the caller.  valid_out (uint8[n]) optional. */
+int pinq_gn_accumulate(const float* xyz, const float* sdf, const float* grad, const float* sdf_std,
+                       const int32_t* nn_count, const float* sdf_label /*nullable = 0*/, int64_t n,
+                       int32_t min_nn, float min_grad_norm, float max_grad_norm, float max_sdf_std,
+                       float gm_dist, float gm_grad, double* out32, uint8_t* valid_out, void* stream);
+
+/* utils/tools.py:386-399 -- out = (T[:3,:3] x + T[:3,3]) with T given as 12 floats (row-major 3x4). */
+int pinq_transform_points(const float* xyz, int64_t n, const float* T12, float* out, void* stream);
+
+/* ---- mesher dense grid (utils/mesher.py:41-180) -------------------------------------------
+ * Grid coordinates are generated in-kernel: p = float(i)*voxel + origin, z fastest
+ * (mesher.py:168-178); linear range [first, first+count) of the nx*ny*nz grid.
+ * sdf_out [count] f32, mask_out [count] u8 = nn_count >= min_nn. */
+int pinq_mesher_grid_query(const pinq_query_args* args, const float* origin3_host, const int32_t* dims3_host,
+                           float voxel, int64_t first, int64_t count, int32_t min_nn, float* sdf_out,
+                           uint8_t* mask_out, void* stream);
+
+/* ---- fused Adam (utils/tools.py:89-116; torch.optim.Adam single-tensor semantics) -------- */
+int pinq_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, float lr,
+                   float beta1, float beta2, float eps, int32_t step, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PINQ_H_ */

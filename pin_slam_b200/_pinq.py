@@ -1,0 +1,118 @@
+"""ctypes binding of libpinq.so (include/pinq.h).  No CPU fallback: a missing library or a non-CUDA
+tensor raises immediately."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB_PATH = os.path.join(_HERE, "libpinq.so")
+
+F_LOCAL, F_TRAINING, F_ROTATE, F_RECIP_DIV, F_SKIP_EMPTY = 1, 2, 4, 8, 16
+
+_vp, _i64, _i32, _u32, _u64, _f32 = C.c_void_p, C.c_int64, C.c_int32, C.c_uint32, C.c_uint64, C.c_float
+
+
+class MapView(C.Structure):
+    _fields_ = [("table", _vp), ("buffer_size", _u32), ("resolution", _f32), ("max_valid_dist2", _f32),
+                ("kn", _i32), ("stencil_dx", _vp), ("cand4", _vp), ("m", _i64)]
+
+
+class DecoderView(C.Structure):
+    _fields_ = [("W1", _vp), ("b1", _vp), ("W2", _vp), ("b2", _vp), ("hidden", _i32), ("in_dim", _i32),
+                ("sdf_scale", _f32)]
+
+
+class QueryArgs(C.Structure):
+    _fields_ = [("map", MapView), ("dec", DecoderView), ("xyz", _vp), ("n", _i64), ("flags", _u32), ("k", _i32),
+                ("feature_dim", _i32), ("features", _vp), ("certainties", _vp), ("quats", _vp), ("ts_update", _vp),
+                ("query_ts", _vp), ("sdf", _vp), ("grad_x", _vp), ("sdf_std", _vp), ("nn_count", _vp),
+                ("certainty", _vp), ("knn_idx", _vp), ("knn_w", _vp), ("knn_d2", _vp)]
+
+
+class BwdArgs(C.Structure):
+    _fields_ = [("dec", DecoderView), ("xyz", _vp), ("n", _i64), ("flags", _u32), ("k", _i32), ("feature_dim", _i32),
+                ("point_xyz", _vp), ("quats", _vp), ("features", _vp), ("knn_idx", _vp), ("knn_w", _vp),
+                ("grad_sdf", _vp), ("grad_features", _vp), ("grad_W1", _vp), ("grad_b1", _vp), ("grad_W2", _vp),
+                ("grad_b2", _vp)]
+
+
+# name -> (restype, argtypes); mirrors include/pinq.h one to one
+SIGNATURES = {
+    "pinq_last_error": (C.c_char_p, []),
+    "pinq_version": (C.c_int, []),
+    "pinq_table_clear": (C.c_int, [_vp, _u32, _vp]),
+    "pinq_hash_points": (C.c_int, [_vp, _i64, _f32, _u32, _u32, _vp, _vp]),
+    "pinq_table_gather": (C.c_int, [_vp, _vp, _i64, _vp, _vp]),
+    "pinq_table_scatter_last_wins": (C.c_int, [_vp, _vp, _vp, _i64, _vp]),
+    "pinq_update_mask": (C.c_int, [_vp, _vp, _i64, _vp, _vp, _i64, _vp, _i64, _f32, _f32, _vp, _vp]),
+    "pinq_compact_scratch_bytes": (_i64, [_i64]),
+    "pinq_compact_flags": (C.c_int, [_vp, _i64, _vp, _vp, _vp, _vp]),
+    "pinq_vds_prepare": (C.c_int, [_vp, _i64, _f32, _vp, C.c_int, _vp, _vp, _vp, _vp]),
+    "pinq_vds_select": (C.c_int, [_vp, _vp, _i64, _vp, _vp, _u64, _vp]),
+    "pinq_vds_emit": (C.c_int, [_vp, _vp, _u64, _i64, _vp, _vp, _vp, _vp]),
+    "pinq_local_mask": (C.c_int, [_vp, _vp, _vp, _i64, _vp, _vp, _i64, _f32, _f32, C.c_int, _vp, _vp]),
+    "pinq_pack_candidates": (C.c_int, [_vp, _vp, _i64, _vp, _vp, _i64, _f32, _vp, _vp]),
+    "pinq_neighbor_search": (C.c_int, [C.POINTER(MapView), _vp, _i64, _u32, _vp, _vp, _vp, _i64, _f32, C.c_int, _vp,
+                                       _vp, _vp]),
+    "pinq_query_certainty": (C.c_int, [C.POINTER(MapView), _vp, _i64, _u32, _vp, _vp, _vp, _vp]),
+    "pinq_query_fused_fwd": (C.c_int, [C.POINTER(QueryArgs), _vp]),
+    "pinq_query_feature": (C.c_int, [C.POINTER(QueryArgs), _vp, _vp]),
+    "pinq_query_fused_bwd": (C.c_int, [C.POINTER(BwdArgs), _vp]),
+    "pinq_gn_accumulate": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i32, _f32, _f32, _f32, _f32, _f32, _vp,
+                                     _vp, _vp]),
+    "pinq_transform_points": (C.c_int, [_vp, _i64, _vp, _vp, _vp]),
+    "pinq_mesher_grid_query": (C.c_int, [C.POINTER(QueryArgs), C.POINTER(_f32), C.POINTER(_i32), _f32, _i64, _i64,
+                                         _i32, _vp, _vp, _vp]),
+    "pinq_adam_step": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _f32, _f32, _f32, _f32, _i32, _vp]),
+}
+
+_lib = None
+
+
+def lib_path() -> str:
+    return _LIB_PATH
+
+
+def load():
+    """dlopen libpinq.so and declare every prototype.  Raises if the library is absent."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(_LIB_PATH):
+        raise RuntimeError(
+            "libpinq.so is missing (%s): build it with `python -m pin_slam_b200.build` "
+            "(there is no CPU or PyTorch fallback for the neural-point query path)" % _LIB_PATH)
+    lib = C.CDLL(_LIB_PATH, mode=C.RTLD_GLOBAL)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+class PinqError(RuntimeError):
+    pass
+
+
+def check(rc: int):
+    if rc != 0:
+        raise PinqError("libpinq error %d: %s" % (rc, load().pinq_last_error().decode()))
+
+
+def ptr(t):
+    """Device pointer of a CUDA tensor (None -> NULL).  Refuses CPU tensors: no host path exists."""
+    if t is None:
+        return None
+    if not t.is_cuda:
+        raise PinqError("libpinq needs CUDA tensors (got a %s tensor); there is no CPU fallback" % t.device)
+    if not t.is_contiguous():
+        raise PinqError("libpinq needs contiguous tensors")
+    return t.data_ptr()
+
+
+def stream():
+    return torch.cuda.current_stream().cuda_stream
