@@ -1,0 +1,89 @@
+"""Shared builders for the parity tests: the same seeded inputs go to the CUDA path and to the oracle."""
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+from oracle import pin_oracle as O  # noqa: E402  (tests may import the oracle)
+
+
+def frames_of_points(n_frames=3, n_per_frame=40000, seed=0, side=60.0):
+    """A few overlapping 'frames' of surface points (CPU float32 tensors) + sensor positions."""
+    from pin_slam_b200 import synth
+
+    out = []
+    for f in range(n_frames):
+        p = synth.surface_points(n_per_frame, side, seed=seed + f)
+        p[:, 0] += 4.0 * f
+        out.append((torch.from_numpy(p), torch.tensor([4.0 * f, 0.0, 0.0])))
+    return out
+
+
+def build_oracle_map(frames, params=None, travel=None):
+    s = O.new_map(params or O.MapParams())
+    n = len(frames)
+    s.travel_dist = travel if travel is not None else torch.arange(n + 1, dtype=torch.float32) * 4.0
+    for ts, (pts, sensor) in enumerate(frames):
+        O.map_update(s, pts, sensor, ts)
+    return s
+
+
+def build_cuda_map(frames, travel=None, cfg=None):
+    from pin_slam_b200.model.neural_points import NeuralPoints
+    from pin_slam_b200.utils.config import kitti_config
+
+    cfg = cfg or kitti_config("cuda")
+    m = NeuralPoints(cfg)
+    n = len(frames)
+    m.travel_dist = travel if travel is not None else torch.arange(n + 1, dtype=torch.float32) * 4.0
+    eye = torch.eye(3, device="cuda")
+    for ts, (pts, sensor) in enumerate(frames):
+        m.update(pts.cuda(), sensor.cuda(), eye, ts)
+    return m, cfg
+
+
+def randomize_features(oracle_map, cuda_map=None, seed=3, std=0.1):
+    """Features start exactly at 0 (feature_std = 0); give both sides the same non-trivial values."""
+    g = torch.Generator().manual_seed(seed)
+    f = torch.randn(oracle_map.feats.shape, generator=g) * std
+    f[-1] = 0
+    oracle_map.feats = f.clone()
+    oracle_map.l_feats = f[oracle_map.local_mask].clone()
+    c = torch.rand(oracle_map.certainty.shape, generator=g) * 50
+    oracle_map.certainty = c.clone()
+    oracle_map.l_certainty = c[oracle_map.local_mask[:-1]].clone()
+    if cuda_map is not None:
+        cuda_map.geo_features = f.cuda()
+        cuda_map.point_certainties = c.cuda()
+        with torch.no_grad():
+            cuda_map.local_geo_features.data = f.cuda()[cuda_map._local_idx]
+        cuda_map.local_point_certainties = c.cuda()[cuda_map._local_idx[:-1]]
+
+
+def make_queries(points_cpu, n, seed=1):
+    from pin_slam_b200 import synth
+
+    return torch.from_numpy(synth.microbench_queries(points_cpu.numpy(), n, seed=seed))
+
+
+def decoder_pair(cfg, seed=42):
+    """(CUDA Decoder module, oracle DecoderParams) with identical weights."""
+    from pin_slam_b200.model.decoder import Decoder
+
+    torch.manual_seed(seed)
+    dec = Decoder(cfg, cfg.geo_mlp_hidden_dim, cfg.geo_mlp_level, 1)
+    d = O.DecoderParams(dec.layers[0].weight.detach().cpu().clone(), dec.layers[0].bias.detach().cpu().clone(),
+                        dec.lout.weight.detach().cpu().clone(), dec.lout.bias.detach().cpu().clone(),
+                        sdf_scale=dec.sdf_scale)
+    return dec, d
+
+
+def rel_err(a, b, floor=1e-6):
+    a = a.double().cpu()
+    b = b.double().cpu()
+    return float((a - b).norm() / max(float(b.norm()), floor))
