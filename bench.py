@@ -1,0 +1,386 @@
+#!/usr/bin/env python3
+"""bench.py -- SDF queries/s (fwd+bwd) of the neural-point query path on B200 (BASELINE.json metric).
+
+Workload (BASELINE.json configs[2]): isolated query microbench,
+M ~ 1 M neural points (0.4 m voxels over a ~350 m synthetic street scene), N = 4 Mi unsorted queries per
+GPU (90 % near-surface, 10 % free space), run_kitti parameters (Kn = 81, K = 6, F = 8), local query with
+travel-distance filtering, training mode (certainty scatter + ts amax), forward + hand-derived backward
+(feature-table and decoder gradients), upstream gradient = ones.
+
+One "step" = one fused forward launch + one backward launch over the N queries of this rank
+(+ NCCL all-reduce of the feature / decoder gradients when N_gpus > 1).
+
+  python bench.py --gpus 1 --steps 10 --warmup 3
+  python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N ...
+  python bench.py --impl reference      # the CPU restatement of the reference path on the host cores
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import time
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "sdf_queries_per_sec_fwd_bwd"
+UNIT = "queries/s"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="pinq", choices=["pinq", "reference"])
+    ap.add_argument("--queries", type=int, default=4 * 1024 * 1024, help="queries per GPU per step")
+    ap.add_argument("--surface-points", type=int, default=9_000_000, help="raw surface samples -> ~1 M neural points")
+    ap.add_argument("--side", type=float, default=350.0)
+    ap.add_argument("--cpu-sample", type=int, default=200_000, help="queries per CPU-baseline step")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured"
+    return 6650.0, "fallback"
+
+
+# ------------------------------------------------------------------------------------------------
+def build_map(args, device):
+    from pin_slam_b200 import synth
+    from pin_slam_b200.model.decoder import Decoder
+    from pin_slam_b200.model.neural_points import NeuralPoints
+    from pin_slam_b200.utils.config import kitti_config
+
+    cfg = kitti_config(device)
+    cfg.local_map_radius = 1.0e4  # microbench: the whole synthetic map is the local map (config 3)
+    npts = NeuralPoints(cfg)
+    npts.travel_dist = torch.zeros(2)
+    raw = torch.from_numpy(synth.surface_points(args.surface_points, args.side, seed=0)).to(device)
+    npts.update(raw, torch.zeros(3, device=device), torch.eye(3, device=device), 0)
+    del raw
+    g = torch.Generator(device="cpu").manual_seed(0)
+    m = npts.count()
+    feats = torch.randn((m + 1, cfg.feature_dim), generator=g) * 0.1
+    feats[-1] = 0
+    cert = torch.rand(m, generator=g) * 50
+    npts.geo_features = feats.to(device)
+    npts.point_certainties = cert.to(device)
+    with torch.no_grad():
+        npts.local_geo_features.data = npts.geo_features[npts._local_idx].clone()
+    npts.local_point_certainties = npts.point_certainties[npts._local_idx[:-1]].clone()
+    torch.manual_seed(42)
+    dec = Decoder(cfg, cfg.geo_mlp_hidden_dim, cfg.geo_mlp_level, 1)
+    return cfg, npts, dec
+
+
+def mean_nonempty_slots(npts, q, sample=100_000):
+    """V-bar of SURVEY.md section 8(d): mean number of non-empty probed slots per query."""
+    x = q[:sample]
+    cells = torch.floor(x / npts.resolution).to(torch.int64)[:, None, :] + npts.neighbor_dx[None]
+    h = torch.fmod((cells * npts.primes).sum(-1), npts.buffer_size)
+    h = torch.where(h < 0, h + npts.buffer_size, h)
+    return float((npts._table[h] >= 0).sum(1).float().mean())
+
+
+class ClockSampler:
+    QUERY = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+             "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+             "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.proc = None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(gpu_index), "--query-gpu=" + self.QUERY,
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        if self.proc is None:
+            return None
+        self.proc.terminate()
+        try:
+            out, _ = self.proc.communicate(timeout=5)
+        except Exception:
+            self.proc.kill()
+            return None
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in out.strip().splitlines():
+            f = [t.strip() for t in line.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1]))
+                mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, v in zip(names, f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        if not sm:
+            return None
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------
+def oracle_state_from(npts, dec):
+    """CPU oracle state holding the same map as the CUDA path (only the cpu_baseline / reference legs use it)."""
+    from oracle import pin_oracle as O
+
+    p = O.MapParams(local_map_radius=float(npts.local_map_radius))
+    s = O.MapState(p=p)
+    s.table = npts.buffer_pt_index.cpu()
+    s.points = npts.neural_points.cpu()
+    s.quats = npts.point_orientations.cpu()
+    s.feats = npts.geo_features.cpu()
+    s.ts_create = npts.point_ts_create.cpu()
+    s.ts_update = npts.point_ts_update.cpu()
+    s.certainty = npts.point_certainties.cpu()
+    s.travel_dist = npts.travel_dist.cpu()
+    O.set_search_neighborhood(s, p.num_nei_cells, p.search_alpha)
+    O.reset_local_map(s, torch.zeros(3), 0)
+    d = O.DecoderParams(*[t.detach().cpu().clone() for t in dec.fused_params()], sdf_scale=dec.sdf_scale)
+    return O, s, d
+
+
+def cpu_step(O, s, d, x, ts):
+    """fwd + bwd of the reference's PyTorch path (restated) on the host cores."""
+    s.l_feats = s.l_feats.detach().requires_grad_(True)
+    dp = O.DecoderParams(*[t.detach().requires_grad_(True) for t in d.tensors()], sdf_scale=d.sdf_scale)
+    out = O.query_sdf(s, dp, x, ts, True, True)
+    out["sdf"].backward(torch.ones_like(out["sdf"]))
+    return out["sdf"]
+
+
+def time_cpu(O, s, d, q_cpu, ts_cpu, sample, steps, warmup):
+    torch.set_num_threads(os.cpu_count() or 1)
+    x, ts = q_cpu[:sample].contiguous(), ts_cpu[:sample].contiguous()
+    for _ in range(warmup):
+        cpu_step(O, s, d, x, ts)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        cpu_step(O, s, d, x, ts)
+    dt = (time.perf_counter() - t0) / max(steps, 1)
+    return sample / dt, dt
+
+
+def run_reference(args):
+    """--impl reference: the reference's own CPU implementation of the path (oracle restatement; the Python
+    reference tree does not travel to the GPU box) on all host threads, bounded sample of the same workload."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    dev = "cuda" if torch.cuda.is_available() else None
+    if dev is None:
+        print(json.dumps({"impl": "reference", "unavailable": "map construction needs the CUDA path (no GPU visible)"}))
+        return
+    from pin_slam_b200 import synth
+
+    cfg, npts, dec = build_map(args, dev)
+    q = torch.from_numpy(synth.microbench_queries(npts.neural_points.cpu().numpy(), max(args.cpu_sample, 1), seed=1))
+    ts = torch.zeros(q.shape[0], dtype=torch.int64)
+    O, s, d = oracle_state_from(npts, dec)
+    qps, dt = time_cpu(O, s, d, q, ts, args.cpu_sample, args.steps, args.warmup)
+    cores = torch.get_num_threads()
+    line = {
+        "impl": "reference", "metric": METRIC, "value": qps, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args, npts, None),
+        "cpu_baseline": {"value": qps, "unit": UNIT, "cores": cores, "kind": "port",
+                         "sample": "%d queries/step of the same query set, fwd+bwd, torch CPU fp32" % args.cpu_sample},
+        "e2e": {"value": qps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line))
+
+
+def workload_config(args, npts, vbar):
+    c = {"workload": "isolated SDF query microbench (BASELINE configs[2]): fwd+bwd, K=6, Kn=81, F=8, local+time filter, "
+                     "training mode, feature+decoder grads",
+         "neural_points": int(npts.count()), "queries_per_gpu": int(args.queries), "voxel_size_m": 0.4,
+         "buffer_size": int(npts.buffer_size), "l2_policy": "inputs larger than L2 (200 MB slot table + 48 MB queries "
+                                                           "+ 32 MB features per step)"}
+    if vbar is not None:
+        c["mean_nonempty_slots"] = round(vbar, 2)
+    return c
+
+
+# ------------------------------------------------------------------------------------------------
+def main():
+    args = parse()
+    if args.impl == "reference":
+        return run_reference(args)
+
+    import torch.distributed as dist
+    from pin_slam_b200 import _pinq as P
+    from pin_slam_b200 import synth
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the neural-point query path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = "cuda:%d" % local_rank
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device(dev))
+    P.load()
+    lib = P.load()
+
+    cfg, npts, dec = build_map(args, dev)
+    # every rank holds a replica of the map; its queries are its own shard (seeded by rank) -> weak scaling
+    q_host = torch.from_numpy(synth.microbench_queries(npts.neural_points.cpu().numpy(), args.queries, seed=1 + rank))
+    ts_host = torch.zeros(args.queries, dtype=torch.int64)
+    q = q_host.to(dev)
+    ts = ts_host.to(dev)
+    vbar = mean_nonempty_slots(npts, q)
+    n = args.queries
+    ones = torch.ones(n, device=dev)
+    params = [npts.local_geo_features] + list(dec.parameters())
+
+    def zero_grads():
+        for p in params:
+            p.grad = None
+
+    def step(x, t):
+        zero_grads()
+        out = npts.query_sdf(x, dec, t, True, True)
+        out["sdf"].backward(ones)
+        if world > 1:  # data-parallel exchange step: feature-table + decoder gradients
+            flat = torch.cat([p.grad.reshape(-1) for p in params[1:]])
+            dist.all_reduce(npts.local_geo_features.grad)
+            dist.all_reduce(flat)
+        return out["sdf"]
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        step(q, ts)
+    barrier()
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for _ in range(args.steps):
+        step(q, ts)
+    ev1.record()
+    barrier()
+    ms_total = ev0.elapsed_time(ev1)
+    clocks = sampler.stop() if sampler else None
+    t = torch.tensor([ms_total], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_step = float(t.item()) / args.steps
+    value = world * n / (ms_step * 1e-3)
+
+    # ---- per-kernel timing (CUDA events on the launching stream) for the roofline ----------------------
+    K = 6
+    a = npts._query_args(q, dec.view(), ts, True, True)
+    sdf = torch.empty(n, device=dev)
+    nnc = torch.empty(n, dtype=torch.int32, device=dev)
+    knn_idx = torch.empty((n, K), dtype=torch.int32, device=dev)
+    knn_w = torch.empty((n, K), device=dev)
+    a.sdf, a.nn_count, a.knn_idx, a.knn_w = P.ptr(sdf), P.ptr(nnc), P.ptr(knn_idx), P.ptr(knn_w)
+    b = P.BwdArgs()
+    b.dec = dec.view()
+    b.xyz, b.n, b.flags, b.k, b.feature_dim = P.ptr(q), n, 0, K, 8
+    b.point_xyz = P.ptr(npts.local_neural_points.contiguous())
+    b.features = P.ptr(npts.local_geo_features.detach())
+    b.knn_idx, b.knn_w, b.grad_sdf = P.ptr(knn_idx), P.ptr(knn_w), P.ptr(ones)
+    gf = torch.zeros_like(npts.local_geo_features)
+    gd = [torch.zeros_like(p) for p in dec.fused_params()]
+    b.grad_features = P.ptr(gf)
+    b.grad_W1, b.grad_b1, b.grad_W2, b.grad_b2 = (P.ptr(g) for g in gd)
+    st = P.stream()
+    reps = max(3, min(args.steps, 10))
+    t_f, t_b = [], []
+    for i in range(reps + 2):
+        e = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+        e[0].record()
+        P.check(lib.pinq_query_fused_fwd(a, st))
+        e[1].record()
+        P.check(lib.pinq_query_fused_bwd(b, st))
+        e[2].record()
+        torch.cuda.synchronize()
+        if i >= 2:
+            t_f.append(e[0].elapsed_time(e[1]))
+            t_b.append(e[1].elapsed_time(e[2]))
+    ms_f, ms_b = float(np.mean(t_f)), float(np.mean(t_b))
+    hbm, peak_kind = peaks()
+    bytes_f = 556 + 20 * vbar + 4 * K   # fwd incl. the certainty scatter
+    bytes_b = 4 + K * 4 * 8             # dL/dsdf + feature-gradient accumulate
+    dom = "fwd" if ms_f >= ms_b else "bwd"
+    ach = (n * (bytes_f if dom == "fwd" else bytes_b)) / ((ms_f if dom == "fwd" else ms_b) * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "kernel": "k_query_fwd" if dom == "fwd" else "k_query_bwd", "achieved": ach,
+                "peak": hbm, "peak_kind": peak_kind + " (burst copy)", "unit": "GB/s", "frac": ach / hbm,
+                "traffic": None, "bytes_per_query": bytes_f if dom == "fwd" else bytes_b,
+                "ms_fwd_kernel": ms_f, "ms_bwd_kernel": ms_b,
+                "step_frac_of_hbm": (n * (bytes_f + bytes_b)) / ((ms_f + ms_b) * 1e-3) / 1e9 / hbm}
+
+    # ---- end to end through the public API with HOST buffers ---------------------------------------------
+    e2e = None
+    if not args.no_e2e:
+        qh, th = q_host.pin_memory(), ts_host.pin_memory()
+        out_h = torch.empty(n, dtype=torch.float32).pin_memory()
+
+        def e2e_step():
+            x = qh.to(dev, non_blocking=True)
+            tt = th.to(dev, non_blocking=True)
+            s_ = step(x, tt)
+            out_h.copy_(s_.detach(), non_blocking=True)
+
+        for _ in range(3):
+            e2e_step()
+        barrier()
+        ev0.record()
+        for _ in range(args.steps):
+            e2e_step()
+        ev1.record()
+        barrier()
+        te = torch.tensor([ev0.elapsed_time(ev1)], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(te, op=dist.ReduceOp.MAX)
+        e2e = {"value": world * n / (float(te.item()) / args.steps * 1e-3), "unit": UNIT,
+               "h2d_bytes_per_step": n * 12 + n * 8, "d2h_bytes_per_step": n * 4}
+
+    cpu_baseline = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        O, s, d = oracle_state_from(npts, dec)
+        qps, dt = time_cpu(O, s, d, q_host, ts_host, min(args.cpu_sample, n), 3, 1)
+        cpu_baseline = {"value": qps, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
+                        "sample": "%d queries of the same set, fwd+bwd, 3 steps after 1 warm-up, torch CPU fp32 "
+                                  "restatement of the reference path" % min(args.cpu_sample, n)}
+
+    if rank == 0:
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+                "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(args, npts, vbar),
+                "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e,
+                "gpu_launches": 2 * args.steps, "clocks": clocks}
+        line["config"]["parallelism"] = "replicated map, queries sharded x%d%s" % (
+            world, ", NCCL all-reduce of feature+decoder grads" if world > 1 else "")
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
