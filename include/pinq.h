@@ -95,22 +95,31 @@ int pinq_local_mask(const float* map_xyz, const int64_t* ts_create, const int64_
                     const float* sensor_xyz3, const float* travel_dist, int64_t cur_ts, float radius2,
                     float diff_travel_dist_local, int use_mid_ts, uint8_t* flags, void* stream);
 
-/* Packed candidate record used by the fused kernels: cand[i] = {x, y, z, bits(int32 local)} where
- * local = global2local[i] if the point also passes the travel-distance filter of
- * model/neural_points.py:480-488, else -1.  global2local may be NULL (global queries: w = i). */
-int pinq_pack_candidates(const float* map_xyz, const int64_t* ts_create, int64_t m, const int64_t* global2local,
-                         const float* travel_dist, int64_t cur_ts, float diff_travel_dist_local,
-                         float* cand4, void* stream);
+/* ---- occupancy index: the L2-resident, bit-identical read view of the slot table ----------
+ * occ[w]  = { bits: occupancy of slots 32w..32w+31, prefix: #occupied slots below 32w }  (uint32[nwords][2])
+ * rec[r]  = { x, y, z, bits(index) } of the r-th occupied slot; lookup(slot) == table[slot] by construction.
+ * Built from the dense table by two streaming passes whenever the map changes (csrc/index.cu). */
+int64_t pinq_index_words(uint32_t buffer_size);
+int64_t pinq_index_scratch_bytes(uint32_t buffer_size);
+int pinq_index_build(const int32_t* table, uint32_t buffer_size, uint32_t* occ2, int32_t* d_count, void* scratch,
+                     void* stream);
+/* rec_global.w = table value (global point index); rec_local.w = global2local[] of it after the
+ * travel-distance filter of model/neural_points.py:480-488 (-1 = rejected).  Either may be NULL. */
+int pinq_index_pack(const int32_t* table, uint32_t buffer_size, const uint32_t* occ2, const float* map_xyz,
+                    const int64_t* ts_create, const int64_t* global2local, const float* travel_dist,
+                    int64_t cur_ts, float diff_travel_dist_local, float* rec_global4, float* rec_local4,
+                    void* stream);
 
 /* ---- neighbour search -------------------------------------------------------------------- */
 typedef struct pinq_map_view {
-    const int32_t* table;       /* [buffer_size]                                              */
+    const uint32_t* occ;        /* [nwords][2] occupancy index (pinq_index_build)             */
+    const float* rec4;          /* [n_occupied][4] rank-ordered records: local flavour for
+                                   PINQ_F_LOCAL queries, global flavour otherwise             */
     uint32_t buffer_size;
     float resolution;           /* voxel_size_m                                               */
     float max_valid_dist2;      /* model/neural_points.py:457                                 */
     int32_t kn;                 /* stencil size (81 for run_kitti)                            */
     const int32_t* stencil_dx;  /* [kn,3] int32 neighbour cell offsets (neural_points.py:439) */
-    const float* cand4;         /* [M] packed candidates (pinq_pack_candidates)               */
     int64_t m;                  /* number of neural points (global)                           */
 } pinq_map_view;
 
@@ -158,7 +167,10 @@ typedef struct pinq_query_args {
     int32_t* knn_idx;          /* [n,k] top-k index (local or global), -1 invalid                    */
     float* knn_w;              /* [n,k] normalised IDW weights                                       */
     float* knn_d2;             /* [n,k] squared distances (9e3 invalid)                              */
+    void* workspace;           /* pinq_query_workspace_bytes(n) bytes: search -> decode hand-off      */
 } pinq_query_args;
+
+int64_t pinq_query_workspace_bytes(int64_t n);
 
 /* neural_points.py:528-674 + decoder.py:66-88 + the weighted combine, in one pass.
  * Supported specialisation: k=6, feature_dim=8, hidden=64, one hidden level, weighted_first=False. */

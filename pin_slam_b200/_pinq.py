@@ -16,8 +16,8 @@ _vp, _i64, _i32, _u32, _u64, _f32 = C.c_void_p, C.c_int64, C.c_int32, C.c_uint32
 
 
 class MapView(C.Structure):
-    _fields_ = [("table", _vp), ("buffer_size", _u32), ("resolution", _f32), ("max_valid_dist2", _f32),
-                ("kn", _i32), ("stencil_dx", _vp), ("cand4", _vp), ("m", _i64)]
+    _fields_ = [("occ", _vp), ("rec4", _vp), ("buffer_size", _u32), ("resolution", _f32), ("max_valid_dist2", _f32),
+                ("kn", _i32), ("stencil_dx", _vp), ("m", _i64)]
 
 
 class DecoderView(C.Structure):
@@ -29,7 +29,7 @@ class QueryArgs(C.Structure):
     _fields_ = [("map", MapView), ("dec", DecoderView), ("xyz", _vp), ("n", _i64), ("flags", _u32), ("k", _i32),
                 ("feature_dim", _i32), ("features", _vp), ("certainties", _vp), ("quats", _vp), ("ts_update", _vp),
                 ("query_ts", _vp), ("sdf", _vp), ("grad_x", _vp), ("sdf_std", _vp), ("nn_count", _vp),
-                ("certainty", _vp), ("knn_idx", _vp), ("knn_w", _vp), ("knn_d2", _vp)]
+                ("certainty", _vp), ("knn_idx", _vp), ("knn_w", _vp), ("knn_d2", _vp), ("workspace", _vp)]
 
 
 class BwdArgs(C.Structure):
@@ -54,7 +54,11 @@ SIGNATURES = {
     "pinq_vds_select": (C.c_int, [_vp, _vp, _i64, _vp, _vp, _u64, _vp]),
     "pinq_vds_emit": (C.c_int, [_vp, _vp, _u64, _i64, _vp, _vp, _vp, _vp]),
     "pinq_local_mask": (C.c_int, [_vp, _vp, _vp, _i64, _vp, _vp, _i64, _f32, _f32, C.c_int, _vp, _vp]),
-    "pinq_pack_candidates": (C.c_int, [_vp, _vp, _i64, _vp, _vp, _i64, _f32, _vp, _vp]),
+    "pinq_index_words": (_i64, [_u32]),
+    "pinq_index_scratch_bytes": (_i64, [_u32]),
+    "pinq_index_build": (C.c_int, [_vp, _u32, _vp, _vp, _vp, _vp]),
+    "pinq_index_pack": (C.c_int, [_vp, _u32, _vp, _vp, _vp, _vp, _vp, _i64, _f32, _vp, _vp, _vp]),
+    "pinq_query_workspace_bytes": (_i64, [_i64]),
     "pinq_neighbor_search": (C.c_int, [C.POINTER(MapView), _vp, _i64, _u32, _vp, _vp, _vp, _i64, _f32, C.c_int, _vp,
                                        _vp, _vp]),
     "pinq_query_certainty": (C.c_int, [C.POINTER(MapView), _vp, _i64, _u32, _vp, _vp, _vp, _vp]),

@@ -15,6 +15,7 @@ constexpr long long kP3 = 83492791LL;
 
 void set_error(const char* fmt, ...);
 int check_launch(const char* what);
+void launch_tile_scan(int32_t* tile_sums, int64_t ntiles, int32_t* d_count, cudaStream_t st);
 
 #define PINQ_REQUIRE(cond, msg)                              \
     do {                                                     \

@@ -1,5 +1,11 @@
-// query.cu -- neighbour search (API form), fused neural-point SDF query forward (+ d sdf/dx, std),
-// un-fused query_feature, mesher dense-grid query.
+// query.cu -- neighbour search (API form), neural-point SDF query forward (+ d sdf/dx, std), un-fused
+// query_feature, mesher dense-grid query.
+//
+// The forward is two launches that share 28 B/query of workspace:
+//   k_search : 81 probes of the occupancy index + candidate records, top-K in registers.  Few registers
+//              -> high occupancy, which is what hides the L2 latency of the random probes.
+//   k_decode : feature gather + IDW + 11->64->1 MLP + weighted combine (+ d sdf/dx, std, side effects).
+//              FP32-FMA bound; the decoder lives in shared memory, activations in registers.
 // Reference: model/neural_points.py:459-674, model/decoder.py:66-88, utils/tracker.py:245-253,
 //            utils/mapper.py:466-468, utils/mesher.py:93-180.
 #include "query_common.cuh"
@@ -9,9 +15,9 @@ namespace pinq {
 // ---------------------------------------------------------------------------------------------
 // Standalone API form: dist2[n,kn], idx[n,kn] (global int64).  One thread per (query, cell).
 __global__ void k_neighbor_search(MapDev map, const float* __restrict__ xyz, int64_t n, bool recip,
-                                  const float* __restrict__ map_xyz, const int64_t* __restrict__ ts_create,
-                                  const float* __restrict__ travel_dist, int64_t cur_ts, float diff_td,
-                                  bool time_filtering, float* __restrict__ out_d2, int64_t* __restrict__ out_idx) {
+                                  const int64_t* __restrict__ ts_create, const float* __restrict__ travel_dist,
+                                  int64_t cur_ts, float diff_td, bool time_filtering, float* __restrict__ out_d2,
+                                  int64_t* __restrict__ out_idx) {
     extern __shared__ uint32_t s_off_ns[];
     load_stencil(map, s_off_ns);
     __syncthreads();
@@ -20,8 +26,14 @@ __global__ void k_neighbor_search(MapDev map, const float* __restrict__ xyz, int
         const int64_t q = t / map.kn;
         const int c = (int)(t - q * map.kn);
         const float x = xyz[3 * q], y = xyz[3 * q + 1], z = xyz[3 * q + 2];
-        const uint32_t base = base_slot(map, x, y, z, recip);
-        int32_t idx = map.table[probe_slot(base, s_off_ns[c], map.B)];
+        const uint32_t slot = probe_slot(base_slot(map, x, y, z, recip), s_off_ns[c], map.B);
+        const int32_t r = rank_of(map.occ[slot >> 5], slot);
+        int32_t idx = -1;
+        float4 rc = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (r >= 0) {
+            rc = map.rec[r];
+            idx = __float_as_int(rc.w);
+        }
         if (time_filtering && map.m > 0) {
             const int64_t j = idx < 0 ? map.m - 1 : idx;  // -1 is a live wrapping index (hazard H8)
             const float dt = fabsf(__fsub_rn(travel_dist[cur_ts], travel_dist[ts_create[j]]));
@@ -29,8 +41,7 @@ __global__ void k_neighbor_search(MapDev map, const float* __restrict__ xyz, int
         }
         float d2 = map.max_d2;
         if (idx >= 0) {
-            const int64_t j = idx;
-            d2 = dist2_rn(map_xyz[3 * j], map_xyz[3 * j + 1], map_xyz[3 * j + 2], x, y, z);
+            d2 = dist2_rn(rc.x, rc.y, rc.z, x, y, z);
             if (d2 > map.max_d2) idx = -1;  // the distance itself is kept (neural_points.py:495-499)
         }
         out_d2[t] = d2;
@@ -39,8 +50,7 @@ __global__ void k_neighbor_search(MapDev map, const float* __restrict__ xyz, int
 }
 
 __global__ void k_query_certainty(MapDev map, const float* __restrict__ xyz, int64_t n, bool recip,
-                                  const float* __restrict__ map_xyz, const float* __restrict__ cert,
-                                  float* __restrict__ out) {
+                                  const float* __restrict__ cert, float* __restrict__ out) {
     extern __shared__ uint32_t s_off_qc[];
     load_stencil(map, s_off_qc);
     __syncthreads();
@@ -51,12 +61,13 @@ __global__ void k_query_certainty(MapDev map, const float* __restrict__ xyz, int
     // torch.max over the row of certainties with invalid entries set to 0 (neural_points.py:518-521)
     float best = -INFINITY;
     for (int c = 0; c < map.kn; ++c) {
-        const int32_t idx = __ldg(&map.table[probe_slot(base, s_off_qc[c], map.B)]);
+        const uint32_t slot = probe_slot(base, s_off_qc[c], map.B);
+        const int32_t r = rank_of(__ldg(&map.occ[slot >> 5]), slot);
         float v = 0.f;
-        if (idx >= 0) {
-            const int64_t j = idx;
-            const float d2 = dist2_rn(map_xyz[3 * j], map_xyz[3 * j + 1], map_xyz[3 * j + 2], x, y, z);
-            if (!(d2 > map.max_d2)) v = cert[j];
+        if (r >= 0) {
+            const float4 rc = __ldg(&map.rec[r]);
+            const float d2 = dist2_rn(rc.x, rc.y, rc.z, x, y, z);
+            if (!(d2 > map.max_d2)) v = cert[__float_as_int(rc.w)];
         }
         best = fmaxf(best, v);
     }
@@ -64,12 +75,36 @@ __global__ void k_query_certainty(MapDev map, const float* __restrict__ xyz, int
 }
 
 // ---------------------------------------------------------------------------------------------
-struct FwdParams {
-    MapDev map;
+// workspace layout: int32 ws[n][K+1] = K record ranks (ascending d2, -1 = none) + nn_count
+constexpr int kWs = K + 1;
+
+__global__ void __launch_bounds__(kBlock) k_search(MapDev map, PointSrc src, int64_t n, bool recip,
+                                                   int32_t* __restrict__ ws) {
+    extern __shared__ uint32_t s_off_s[];
+    load_stencil(map, s_off_s);
+    __syncthreads();
+    const int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= n) return;
+    float x, y, z;
+    load_point(src, q, x, y, z);
+    float kd2[K];
+    int32_t kr[K];
+    int nn;
+    search_topk(map, s_off_s, x, y, z, recip, kd2, kr, nn);
+    int32_t* o = ws + q * kWs;
+#pragma unroll
+    for (int k = 0; k < K; ++k) o[k] = kr[k];
+    o[K] = nn;
+}
+
+struct DecodeParams {
+    const float4* rec;
+    float max_d2;
     pinq_decoder_view dec;
-    const float* xyz;
+    PointSrc src;
     int64_t n;
-    uint32_t flags;
+    bool rotate, scatter_in_kernel;
+    const int32_t* ws;
     const float* features;
     float* certainties;
     const float4* quats;
@@ -81,73 +116,49 @@ struct FwdParams {
     int32_t* knn_idx;
     float *knn_w, *knn_d2;
     float* feat_out;  // MODE 1: [n,K,IN]
-    bool scatter_in_kernel;
-    // MODE 2 (mesher grid)
-    float ox, oy, oz, voxel;
-    int ny, nz;
-    int64_t first;
-    int min_nn;
+    int min_nn;       // MODE 2
     uint8_t* mask_out;
 };
 
-// MODE 0: fused forward   MODE 1: un-fused query_feature (no MLP)   MODE 2: mesher grid (forward only)
-template <bool LOCAL, bool GRAD, int MODE>
-__global__ void __launch_bounds__(kBlock) k_query_fwd(const FwdParams p) {
-    extern __shared__ __align__(16) unsigned char smem[];
-    float4* s_w = reinterpret_cast<float4*>(smem);                     // H*16 floats
-    uint32_t* s_off = reinterpret_cast<uint32_t*>(smem + H * 16 * 4);  // kn, padded to a multiple of 4
-    int32_t* s_list = reinterpret_cast<int32_t*>(s_off + ((p.map.kn + 3) & ~3));
-    load_stencil(p.map, s_off);
-    if (MODE != 1) load_decoder(p.dec, s_w);
-    __syncthreads();
-
+// MODE 0: fused decode   MODE 1: un-fused query_feature (no MLP)   MODE 2: mesher grid (forward only)
+template <bool GRAD, int MODE>
+__global__ void __launch_bounds__(kBlock) k_decode(const DecodeParams p) {
+    __shared__ __align__(16) float4 s_w[MODE == 1 ? 1 : H * 4];
+    if (MODE != 1) {
+        load_decoder(p.dec, s_w);
+        __syncthreads();
+    }
     const int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (q >= p.n) return;
-    const bool recip = (p.flags & PINQ_F_RECIP_DIV) != 0;
-    const bool rotate = (p.flags & PINQ_F_ROTATE) != 0;
     float x, y, z;
-    if (MODE == 2) {
-        // utils/mesher.py:168-178: int16 meshgrid -> float -> *= voxel -> += origin; z fastest
-        const int64_t g = p.first + q;
-        const int iz = (int)(g % p.nz);
-        const int64_t r = g / p.nz;
-        const int iy = (int)(r % p.ny);
-        const int ix = (int)(r / p.ny);
-        x = __fadd_rn(__fmul_rn((float)ix, p.voxel), p.ox);
-        y = __fadd_rn(__fmul_rn((float)iy, p.voxel), p.oy);
-        z = __fadd_rn(__fmul_rn((float)iz, p.voxel), p.oz);
-    } else {
-        x = p.xyz[3 * q];
-        y = p.xyz[3 * q + 1];
-        z = p.xyz[3 * q + 2];
-    }
+    load_point(p.src, q, x, y, z);
 
-    float kd2[K];
-    int32_t kg[K];
-    int nn;
-    search_topk<LOCAL>(p.map, s_off, s_list, x, y, z, recip, kd2, kg, nn);
-
-    // resolve the K winners: position (for x - p_k) and the index space of the feature arrays
+    const int32_t* wsq = p.ws + q * kWs;
+    const int nn = wsq[K];
     int32_t kidx[K];
+    float kd2[K];
     float in[K][IN];
     float ux[K], uy[K], uz[K];  // un-rotated x - p_k, needed by the IDW gradient
 #pragma unroll
     for (int k = 0; k < K; ++k) {
         kidx[k] = -1;
+        kd2[k] = kInvalidD2;
         ux[k] = uy[k] = uz[k] = 0.f;
 #pragma unroll
         for (int i = 0; i < IN; ++i) in[k][i] = 0.f;
-        if (kg[k] >= 0) {
-            const float4 r = __ldg(&p.map.cand[kg[k]]);
-            const int32_t li = LOCAL ? __float_as_int(r.w) : kg[k];
+        const int32_t r = wsq[k];
+        if (r >= 0) {
+            const float4 rc = __ldg(&p.rec[r]);
+            const int32_t li = __float_as_int(rc.w);
             kidx[k] = li;
+            kd2[k] = dist2_rn(rc.x, rc.y, rc.z, x, y, z);  // same ops as the search -> same bits
             const float4* fr = reinterpret_cast<const float4*>(p.features + (int64_t)li * F);
             const float4 a = __ldg(fr), b = __ldg(fr + 1);
             in[k][0] = a.x; in[k][1] = a.y; in[k][2] = a.z; in[k][3] = a.w;
             in[k][4] = b.x; in[k][5] = b.y; in[k][6] = b.z; in[k][7] = b.w;
-            float vx = __fsub_rn(x, r.x), vy = __fsub_rn(y, r.y), vz = __fsub_rn(z, r.z);
+            float vx = __fsub_rn(x, rc.x), vy = __fsub_rn(y, rc.y), vz = __fsub_rn(z, rc.z);
             ux[k] = vx; uy[k] = vy; uz[k] = vz;
-            if (rotate) quat_rotate(__ldg(&p.quats[li]), false, vx, vy, vz);
+            if (p.rotate) quat_rotate(__ldg(&p.quats[li]), false, vx, vy, vz);
             in[k][8] = vx; in[k][9] = vy; in[k][10] = vz;
         }
     }
@@ -202,7 +213,7 @@ __global__ void __launch_bounds__(kBlock) k_query_fwd(const FwdParams p) {
         }
     }
 
-    // phase D: MLP.  acc[k] = sum_j W2[j] relu(pre_kj);  gv[k] = sum_j W2[j] 1[pre>0] W1[j][8..10]
+    // MLP.  acc[k] = sum_j W2[j] relu(pre_kj);  gv[k] = sum_j W2[j] 1[pre>0] W1[j][8..10]
     float acc[K];
     float gvx[K], gvy[K], gvz[K];
 #pragma unroll
@@ -247,7 +258,7 @@ __global__ void __launch_bounds__(kBlock) k_query_fwd(const FwdParams p) {
         for (int k = 0; k < K; ++k) {
             if (kidx[k] >= 0) {
                 float ax = gvx[k] * scale, ay = gvy[k] * scale, az = gvz[k] * scale;
-                if (rotate) quat_rotate(__ldg(&p.quats[kidx[k]]), true, ax, ay, az);
+                if (p.rotate) quat_rotate(__ldg(&p.quats[kidx[k]]), true, ax, ay, az);
                 const float c = (s[k] - sdf) * (-2.f * wt[k] * wt[k]) * inv_s;
                 gx += w[k] * ax + c * ux[k];
                 gy += w[k] * ay + c * uy[k];
@@ -272,71 +283,68 @@ __global__ void k_certainty_scatter(const int32_t* __restrict__ knn_idx, const f
     if (query_ts && ts_update) atomicMax(&ts_update[i], (long long)query_ts[t / K]);
 }
 
-static size_t fwd_smem_bytes(int kn) { return (size_t)H * 16 * 4 + (size_t)((kn + 3) & ~3) * 4 + (size_t)kn * kBlock * 4; }
-
-template <bool LOCAL, bool GRAD, int MODE>
-static int launch_fwd(const FwdParams& p, cudaStream_t st) {
-    const size_t smem = fwd_smem_bytes(p.map.kn);
-    auto kern = k_query_fwd<LOCAL, GRAD, MODE>;
-    static size_t configured = 0;  // per instantiation
-    if (smem > 48 * 1024 && smem > configured) {
-        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) {
-            set_error("cudaFuncSetAttribute(%zu B smem): %s", smem, cudaGetErrorString(e));
-            return PINQ_ERR_CUDA;
-        }
-        configured = smem;
-    }
-    kern<<<grid_for(p.n, kBlock), kBlock, smem, st>>>(p);
-    return check_launch("k_query_fwd");
-}
-
-static int fill_params(const pinq_query_args* a, FwdParams& p, bool need_decoder) {
+static int run_query(const pinq_query_args* a, int mode, float* feat_out, const PointSrc* grid_src, int min_nn,
+                     uint8_t* mask_out, cudaStream_t st) {
     int rc = check_map(a->map);
     if (rc) return rc;
-    if (need_decoder) {
+    if (mode != 1) {
         rc = check_decoder(a->dec, a->k, a->feature_dim);
         if (rc) return rc;
     } else if (a->k != K || a->feature_dim != F) {
         set_error("unsupported specialisation: need query_nn_k=6, feature_dim=8");
         return PINQ_ERR_UNSUPPORTED;
     }
-    if (!a->map.cand4 || !a->features) {
-        set_error("null cand4/features");
+    if (!a->features || !a->workspace) {
+        set_error("null features/workspace");
         return PINQ_ERR_BAD_ARG;
     }
     if ((a->flags & PINQ_F_ROTATE) && !a->quats) {
         set_error("PINQ_F_ROTATE needs quats");
         return PINQ_ERR_BAD_ARG;
     }
-    if (((a->flags & PINQ_F_TRAINING) || a->certainty) && !a->certainties) {
+    const bool training = (a->flags & PINQ_F_TRAINING) != 0;
+    if ((training || a->certainty) && !a->certainties) {
         set_error("certainties pointer required");
         return PINQ_ERR_BAD_ARG;
     }
-    p.map = to_dev(a->map);
-    p.dec = a->dec;
-    p.xyz = a->xyz; p.n = a->n; p.flags = a->flags;
-    p.features = a->features; p.certainties = a->certainties;
-    p.quats = reinterpret_cast<const float4*>(a->quats);
-    p.ts_update = reinterpret_cast<long long*>(a->ts_update);
-    p.query_ts = a->query_ts;
-    p.sdf = a->sdf; p.grad_x = a->grad_x; p.sdf_std = a->sdf_std; p.nn_count = a->nn_count;
-    p.certainty = a->certainty; p.knn_idx = a->knn_idx; p.knn_w = a->knn_w; p.knn_d2 = a->knn_d2;
-    p.feat_out = nullptr;
+    const int64_t n = grid_src ? a->n : a->n;
+    if (n == 0) return PINQ_OK;
+    const MapDev map = to_dev(a->map);
+    PointSrc src;
+    if (grid_src) src = *grid_src;
+    else {
+        src.xyz = a->xyz; src.grid = false;
+        src.ox = src.oy = src.oz = src.voxel = 0.f; src.ny = src.nz = 1; src.first = 0;
+    }
+    const bool recip = (a->flags & PINQ_F_RECIP_DIV) != 0;
+    int32_t* ws = reinterpret_cast<int32_t*>(a->workspace);
+    k_search<<<grid_for(n, kBlock), kBlock, map.kn * sizeof(uint32_t), st>>>(map, src, n, recip, ws);
+    rc = check_launch("k_search");
+    if (rc) return rc;
+
+    DecodeParams p;
+    p.rec = map.rec; p.max_d2 = map.max_d2; p.dec = a->dec; p.src = src; p.n = n;
+    p.rotate = (a->flags & PINQ_F_ROTATE) != 0;
     // Exactness of the queried certainty in training mode needs all reads before any scatter: if the
     // caller wants it (and gave knn buffers), scatter in a second kernel; otherwise fuse the atomics.
-    const bool training = (a->flags & PINQ_F_TRAINING) != 0;
-    p.scatter_in_kernel = training && !(a->certainty && a->knn_idx && a->knn_w);
-    p.ox = p.oy = p.oz = p.voxel = 0.f; p.ny = p.nz = 1; p.first = 0; p.min_nn = 0; p.mask_out = nullptr;
-    return PINQ_OK;
-}
-
-static int post_scatter(const pinq_query_args* a, const FwdParams& p, cudaStream_t st) {
-    const bool training = (a->flags & PINQ_F_TRAINING) != 0;
-    if (training && !p.scatter_in_kernel && a->n > 0) {
-        k_certainty_scatter<<<grid_for(a->n * K, 256), 256, 0, st>>>(a->knn_idx, a->knn_w, a->query_ts, a->n,
-                                                                      a->certainties,
-                                                                      reinterpret_cast<long long*>(a->ts_update));
+    const bool two_pass = training && a->certainty && a->knn_idx && a->knn_w;
+    p.scatter_in_kernel = training && !two_pass;
+    p.ws = ws; p.features = a->features; p.certainties = a->certainties;
+    p.quats = reinterpret_cast<const float4*>(a->quats);
+    p.ts_update = reinterpret_cast<long long*>(a->ts_update); p.query_ts = a->query_ts;
+    p.sdf = a->sdf; p.grad_x = a->grad_x; p.sdf_std = a->sdf_std; p.nn_count = a->nn_count;
+    p.certainty = a->certainty; p.knn_idx = a->knn_idx; p.knn_w = a->knn_w; p.knn_d2 = a->knn_d2;
+    p.feat_out = feat_out; p.min_nn = min_nn; p.mask_out = mask_out;
+    const unsigned g = grid_for(n, kBlock);
+    if (mode == 1) k_decode<false, 1><<<g, kBlock, 0, st>>>(p);
+    else if (mode == 2) k_decode<false, 2><<<g, kBlock, 0, st>>>(p);
+    else if (a->grad_x) k_decode<true, 0><<<g, kBlock, 0, st>>>(p);
+    else k_decode<false, 0><<<g, kBlock, 0, st>>>(p);
+    rc = check_launch("k_decode");
+    if (rc) return rc;
+    if (two_pass) {
+        k_certainty_scatter<<<grid_for(n * K, 256), 256, 0, st>>>(a->knn_idx, a->knn_w, a->query_ts, n, a->certainties,
+                                                                  reinterpret_cast<long long*>(a->ts_update));
         return check_launch("k_certainty_scatter");
     }
     return PINQ_OK;
@@ -348,10 +356,13 @@ using namespace pinq;
 
 extern "C" {
 
+int64_t pinq_query_workspace_bytes(int64_t n) { return (n > 0 ? n : 1) * (int64_t)kWs * (int64_t)sizeof(int32_t); }
+
 int pinq_neighbor_search(const pinq_map_view* map, const float* xyz, int64_t n, uint32_t flags, const float* map_xyz,
                          const int64_t* ts_create, const float* travel_dist, int64_t cur_ts,
                          float diff_travel_dist_local, int time_filtering, float* out_dist2, int64_t* out_idx,
                          void* stream) {
+    (void)map_xyz;
     PINQ_REQUIRE(map && out_dist2 && out_idx, "null pointer");
     int rc = check_map(*map);
     if (rc) return rc;
@@ -362,69 +373,48 @@ int pinq_neighbor_search(const pinq_map_view* map, const float* xyz, int64_t n, 
     unsigned g = grid_for(total, 256);
     if (g > 148u * 64u) g = 148u * 64u;
     k_neighbor_search<<<g, 256, d.kn * sizeof(uint32_t), as_stream(stream)>>>(
-        d, xyz, n, (flags & PINQ_F_RECIP_DIV) != 0, map_xyz, ts_create, travel_dist, cur_ts, diff_travel_dist_local,
+        d, xyz, n, (flags & PINQ_F_RECIP_DIV) != 0, ts_create, travel_dist, cur_ts, diff_travel_dist_local,
         time_filtering != 0, out_dist2, out_idx);
     return check_launch("pinq_neighbor_search");
 }
 
 int pinq_query_certainty(const pinq_map_view* map, const float* xyz, int64_t n, uint32_t flags, const float* map_xyz,
                          const float* certainties, float* out, void* stream) {
-    PINQ_REQUIRE(map && out, "null pointer");
+    (void)map_xyz;
+    PINQ_REQUIRE(map && out && certainties, "null pointer");
     int rc = check_map(*map);
     if (rc) return rc;
     if (n == 0) return PINQ_OK;
     MapDev d = to_dev(*map);
     k_query_certainty<<<grid_for(n, 128), 128, d.kn * sizeof(uint32_t), as_stream(stream)>>>(
-        d, xyz, n, (flags & PINQ_F_RECIP_DIV) != 0, map_xyz, certainties, out);
+        d, xyz, n, (flags & PINQ_F_RECIP_DIV) != 0, certainties, out);
     return check_launch("pinq_query_certainty");
 }
 
 int pinq_query_fused_fwd(const pinq_query_args* a, void* stream) {
     PINQ_REQUIRE(a != nullptr, "null args");
-    FwdParams p;
-    int rc = fill_params(a, p, true);
-    if (rc) return rc;
-    if (a->n == 0) return PINQ_OK;
-    cudaStream_t st = as_stream(stream);
-    const bool local = (a->flags & PINQ_F_LOCAL) != 0;
-    const bool grad = a->grad_x != nullptr;
-    if (local) rc = grad ? launch_fwd<true, true, 0>(p, st) : launch_fwd<true, false, 0>(p, st);
-    else rc = grad ? launch_fwd<false, true, 0>(p, st) : launch_fwd<false, false, 0>(p, st);
-    if (rc) return rc;
-    return post_scatter(a, p, st);
+    return run_query(a, 0, nullptr, nullptr, 0, nullptr, as_stream(stream));
 }
 
 int pinq_query_feature(const pinq_query_args* a, float* feat_out, void* stream) {
     PINQ_REQUIRE(a != nullptr && feat_out != nullptr, "null args");
-    FwdParams p;
-    int rc = fill_params(a, p, false);
-    if (rc) return rc;
-    if (a->n == 0) return PINQ_OK;
-    p.feat_out = feat_out;
-    cudaStream_t st = as_stream(stream);
-    rc = (a->flags & PINQ_F_LOCAL) ? launch_fwd<true, false, 1>(p, st) : launch_fwd<false, false, 1>(p, st);
-    if (rc) return rc;
-    return post_scatter(a, p, st);
+    return run_query(a, 1, feat_out, nullptr, 0, nullptr, as_stream(stream));
 }
 
 int pinq_mesher_grid_query(const pinq_query_args* a, const float* origin3_host, const int32_t* dims3_host, float voxel,
                            int64_t first, int64_t count, int32_t min_nn, float* sdf_out, uint8_t* mask_out,
                            void* stream) {
     PINQ_REQUIRE(a && origin3_host && dims3_host && sdf_out, "null pointer");
-    FwdParams p;
-    int rc = fill_params(a, p, true);
-    if (rc) return rc;
     PINQ_REQUIRE(!(a->flags & PINQ_F_TRAINING), "mesher query is inference only");
     const int64_t total = (int64_t)dims3_host[0] * dims3_host[1] * dims3_host[2];
     PINQ_REQUIRE(first >= 0 && count >= 0 && first + count <= total, "grid range out of bounds");
-    if (count == 0) return PINQ_OK;
-    p.n = count; p.xyz = nullptr;
-    p.ox = origin3_host[0]; p.oy = origin3_host[1]; p.oz = origin3_host[2]; p.voxel = voxel;
-    p.ny = dims3_host[1]; p.nz = dims3_host[2]; p.first = first; p.min_nn = min_nn;
-    p.sdf = sdf_out; p.mask_out = mask_out; p.grad_x = nullptr; p.sdf_std = nullptr;
-    p.scatter_in_kernel = false;
-    cudaStream_t st = as_stream(stream);
-    return (a->flags & PINQ_F_LOCAL) ? launch_fwd<true, false, 2>(p, st) : launch_fwd<false, false, 2>(p, st);
+    pinq_query_args b = *a;
+    b.n = count; b.xyz = nullptr; b.sdf = sdf_out; b.grad_x = nullptr; b.sdf_std = nullptr;
+    PointSrc src;
+    src.xyz = nullptr; src.grid = true;
+    src.ox = origin3_host[0]; src.oy = origin3_host[1]; src.oz = origin3_host[2]; src.voxel = voxel;
+    src.ny = dims3_host[1]; src.nz = dims3_host[2]; src.first = first;
+    return run_query(&b, 2, nullptr, &src, min_nn, mask_out, as_stream(stream));
 }
 
 }  // extern "C"

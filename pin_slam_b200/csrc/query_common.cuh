@@ -1,12 +1,11 @@
 // query_common.cuh -- device building blocks shared by the forward, backward and mesher kernels.
 // One thread owns one query point end to end:
-//   phase A  kn (81) independent 4-byte probes of the dense slot table; non-empty hits are compacted
-//            into a per-thread shared-memory list (bank == lane -> conflict free);
-//   phase B  one 16-byte candidate record per hit (xyz + filtered local index), exact fp32 d^2,
-//            running top-K kept sorted in registers (replaces torch.sort over [N,kn]);
-//   phase C  gather K feature rows (2 x 16 B each), IDW weights;
-//   phase D  11 -> 64 -> 1 MLP, decoder staged once per CTA in shared memory (broadcast LDS.128),
-//            hidden activations never leave registers.
+//   search   kn (81) probes of the L2-resident occupancy index (8 B each), one 16-byte candidate record
+//            per occupied slot, exact fp32 d^2, running top-K kept sorted in registers (replaces
+//            torch.sort over [N,kn]); hands K record ranks + nn_count to the decode kernel;
+//   decode   gather K feature rows (2 x 16 B each), IDW weights, 11 -> 64 -> 1 MLP with the decoder
+//            staged once per CTA in shared memory (broadcast LDS.128); hidden activations never leave
+//            registers; d sdf/dx in the same pass.
 // Reference: model/neural_points.py:459-674, model/decoder.py:66-88.
 #pragma once
 #include "common.cuh"
@@ -22,33 +21,33 @@ constexpr float kInvalidD2 = 9e3f;  // model/neural_points.py:561
 constexpr float kEps = 1e-15f;      // model/neural_points.py:618
 
 struct MapDev {
-    const int32_t* table;
+    const uint2* occ;    // occupancy index: {bits, prefix} per 32 slots
+    const float4* rec;   // rank-ordered candidate records {x, y, z, bits(index)}
     uint32_t B;
     float res, inv_res, max_d2;
     int kn;
     const int32_t* stencil_dx;
-    const float4* cand;
     int64_t m;
 };
 
 static inline MapDev to_dev(const pinq_map_view& v) {
     MapDev d;
-    d.table = v.table;
+    d.occ = reinterpret_cast<const uint2*>(v.occ);
+    d.rec = reinterpret_cast<const float4*>(v.rec4);
     d.B = v.buffer_size;
     d.res = v.resolution;
     d.inv_res = 1.0f / v.resolution;
     d.max_d2 = v.max_valid_dist2;
     d.kn = v.kn;
     d.stencil_dx = v.stencil_dx;
-    d.cand = reinterpret_cast<const float4*>(v.cand4);
     d.m = v.m;
     return d;
 }
 
 static inline int check_map(const pinq_map_view& v) {
-    if (!v.table || !v.stencil_dx || v.kn <= 0 || v.kn > PINQ_MAX_STENCIL || v.buffer_size == 0 ||
+    if (!v.occ || !v.rec4 || !v.stencil_dx || v.kn <= 0 || v.kn > PINQ_MAX_STENCIL || v.buffer_size == 0 ||
         v.buffer_size >= 0x7fffffffu || !(v.resolution > 0.f)) {
-        set_error("bad pinq_map_view (table/stencil null, kn out of range or bad buffer_size/resolution)");
+        set_error("bad pinq_map_view (occ/rec/stencil null, kn out of range or bad buffer_size/resolution)");
         return PINQ_ERR_BAD_ARG;
     }
     return PINQ_OK;
@@ -70,51 +69,84 @@ __device__ __forceinline__ uint32_t base_slot(const MapDev& map, float x, float 
                         cell_of(z, map.res, map.inv_res, recip), map.B);
 }
 
-// phase A + B.  kg[k] = GLOBAL index of the k-th nearest valid candidate (-1 = none), kd2 ascending.
-// Validity (neural_points.py:480-499, 555-561): local filter (cand.w >= 0) and d2 <= max_valid_dist2.
-template <bool LOCAL>
-__device__ __forceinline__ void search_topk(const MapDev& map, const uint32_t* s_off, int32_t* s_list, float x, float y,
-                                            float z, bool recip, float (&kd2)[K], int32_t (&kg)[K], int& nn) {
+// table[slot] through the occupancy index: rank of the slot's record, or -1 when the slot is empty
+__device__ __forceinline__ int32_t rank_of(const uint2 w, uint32_t slot) {
+    const uint32_t bit = slot & 31u;
+    return ((w.x >> bit) & 1u) ? (int32_t)(w.y + __popc(w.x & ((1u << bit) - 1u))) : -1;
+}
+
+// where the query point comes from: an [n,3] array, or generated in-kernel for the mesher grid
+// (utils/mesher.py:168-178: int16 meshgrid -> float -> *= voxel -> += origin; z fastest)
+struct PointSrc {
+    const float* xyz;
+    float ox, oy, oz, voxel;
+    int ny, nz;
+    int64_t first;
+    bool grid;
+};
+
+__device__ __forceinline__ void load_point(const PointSrc& s, int64_t q, float& x, float& y, float& z) {
+    if (s.grid) {
+        const int64_t g = s.first + q;
+        const int iz = (int)(g % s.nz);
+        const int64_t r = g / s.nz;
+        const int iy = (int)(r % s.ny);
+        const int ix = (int)(r / s.ny);
+        x = __fadd_rn(__fmul_rn((float)ix, s.voxel), s.ox);
+        y = __fadd_rn(__fmul_rn((float)iy, s.voxel), s.oy);
+        z = __fadd_rn(__fmul_rn((float)iz, s.voxel), s.oz);
+    } else {
+        x = s.xyz[3 * q];
+        y = s.xyz[3 * q + 1];
+        z = s.xyz[3 * q + 2];
+    }
+}
+
+// Neighbour search of one query: kr[k] = record rank of the k-th nearest valid candidate (-1 = none),
+// kd2 ascending, nn = valid candidates over the whole stencil.  Probes go out in batches of U independent
+// 8-byte index loads followed by U predicated 16-byte record loads (memory-level parallelism without a
+// shared-memory hit list, so occupancy is bounded by registers only).
+// Validity (neural_points.py:480-499, 555-561): index >= 0 (local filter baked into rec.w) and d2 <= max.
+__device__ __forceinline__ void search_topk(const MapDev& map, const uint32_t* s_off, float x, float y, float z,
+                                            bool recip, float (&kd2)[K], int32_t (&kr)[K], int& nn) {
     const uint32_t base = base_slot(map, x, y, z, recip);
     const int kn = map.kn;
-    int cnt = 0;
-    constexpr int U = 9;  // 81 = 9 * 9: nine independent probes in flight per thread
-    for (int c0 = 0; c0 < kn; c0 += U) {
-        int32_t v[U];
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-            int c = c0 + u;
-            v[u] = (c < kn) ? __ldg(&map.table[probe_slot(base, s_off[c], map.B)]) : -1;
-        }
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-            if (v[u] >= 0) {
-                s_list[cnt * blockDim.x + threadIdx.x] = v[u];
-                ++cnt;
-            }
-        }
-    }
 #pragma unroll
     for (int k = 0; k < K; ++k) {
         kd2[k] = kInvalidD2;
-        kg[k] = -1;
+        kr[k] = -1;
     }
     nn = 0;
-    for (int j = 0; j < cnt; ++j) {
-        const int32_t gi = s_list[j * blockDim.x + threadIdx.x];
-        const float4 r = __ldg(&map.cand[gi]);
-        const float d2 = dist2_rn(r.x, r.y, r.z, x, y, z);
-        const bool ok = (!LOCAL || __float_as_int(r.w) >= 0) && !(d2 > map.max_d2);
-        if (ok) {
+    constexpr int U = 9;  // 81 = 9 * 9
+    for (int c0 = 0; c0 < kn; c0 += U) {
+        int32_t r[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int c = c0 + u;
+            r[u] = -1;
+            if (c < kn) {
+                const uint32_t slot = probe_slot(base, s_off[c], map.B);
+                r[u] = rank_of(__ldg(&map.occ[slot >> 5]), slot);
+            }
+        }
+        float4 rc[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+            if (r[u] >= 0) rc[u] = __ldg(&map.rec[r[u]]);
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            if (r[u] < 0) continue;
+            const float d2 = dist2_rn(rc[u].x, rc[u].y, rc[u].z, x, y, z);
+            if (__float_as_int(rc[u].w) < 0 || d2 > map.max_d2) continue;
             ++nn;
             if (d2 < kd2[K - 1]) {  // strict <: equal distances keep stencil order (stable)
                 kd2[K - 1] = d2;
-                kg[K - 1] = gi;
+                kr[K - 1] = r[u];
 #pragma unroll
                 for (int k = K - 1; k > 0; --k) {
                     if (kd2[k] < kd2[k - 1]) {
-                        float td = kd2[k]; kd2[k] = kd2[k - 1]; kd2[k - 1] = td;
-                        int32_t ti = kg[k]; kg[k] = kg[k - 1]; kg[k - 1] = ti;
+                        const float td = kd2[k]; kd2[k] = kd2[k - 1]; kd2[k - 1] = td;
+                        const int32_t ti = kr[k]; kr[k] = kr[k - 1]; kr[k - 1] = ti;
                     }
                 }
             }

@@ -141,6 +141,11 @@ __global__ void k_tile_scan(int32_t* tile_sums, int64_t ntiles, int32_t* d_count
     if (threadIdx.x == 0) *d_count = carry;
 }
 
+// host launcher shared with index.cu: in-place exclusive scan of `ntiles` int32 sums, total -> *d_count
+void launch_tile_scan(int32_t* tile_sums, int64_t ntiles, int32_t* d_count, cudaStream_t st) {
+    k_tile_scan<<<1, 1024, 0, st>>>(tile_sums, ntiles, d_count);
+}
+
 __global__ void k_tile_emit(const uint8_t* __restrict__ flags, int64_t n, const int32_t* __restrict__ tile_offs,
                             int32_t* __restrict__ out_index) {
     __shared__ int wsum[32];
@@ -276,7 +281,7 @@ __global__ void k_vds_emit(const unsigned long long* __restrict__ tab_keys,
     }
 }
 
-// ---- local-map window + packed candidates -----------------------------------------------------
+// ---- local-map window -----------------------------------------------------
 __global__ void k_local_mask(const float* __restrict__ xyz, const int64_t* __restrict__ ts_c,
                              const int64_t* __restrict__ ts_u, int64_t m, const float* __restrict__ sensor3,
                              const float* __restrict__ td, int64_t cur_ts, float r2, float diff_td, int use_mid,
@@ -290,20 +295,6 @@ __global__ void k_local_mask(const float* __restrict__ xyz, const int64_t* __res
     if (use_mid) t = (int64_t)((float)(ts_c[i] + ts_u[i]) / 2.0f);  // ((a+b)/2).long(): fp32 true-div then trunc
     float dt = fabsf(__fsub_rn(td[cur_ts], td[t]));
     flags[i] = (d2 < r2) & (dt < diff_td);
-}
-
-__global__ void k_pack_cand(const float* __restrict__ xyz, const int64_t* __restrict__ ts_c, int64_t m,
-                            const int64_t* __restrict__ g2l, const float* __restrict__ td, int64_t cur_ts,
-                            float diff_td, float4* __restrict__ cand) {
-    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= m) return;
-    int32_t li = (int32_t)i;
-    if (g2l) {
-        li = (int32_t)g2l[i];
-        float dt = fabsf(__fsub_rn(td[cur_ts], td[ts_c[i]]));
-        if (!(dt < diff_td)) li = -1;  // neural_points.py:482-488
-    }
-    cand[i] = make_float4(xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2], __int_as_float(li));
 }
 
 }  // namespace pinq
@@ -420,16 +411,6 @@ int pinq_local_mask(const float* map_xyz, const int64_t* ts_create, const int64_
                                                                       travel_dist, cur_ts, radius2,
                                                                       diff_travel_dist_local, use_mid_ts, flags);
     return check_launch("pinq_local_mask");
-}
-
-int pinq_pack_candidates(const float* map_xyz, const int64_t* ts_create, int64_t m, const int64_t* global2local,
-                         const float* travel_dist, int64_t cur_ts, float diff_travel_dist_local, float* cand4,
-                         void* stream) {
-    if (m == 0) return PINQ_OK;
-    k_pack_cand<<<grid_for(m, 256), 256, 0, as_stream(stream)>>>(map_xyz, ts_create, m, global2local, travel_dist,
-                                                                 cur_ts, diff_travel_dist_local,
-                                                                 reinterpret_cast<float4*>(cand4));
-    return check_launch("pinq_pack_candidates");
 }
 
 }  // extern "C"

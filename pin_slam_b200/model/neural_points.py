@@ -7,8 +7,9 @@ sequences the launches.  There is no CPU path: a non-CUDA config.device raises.
 
 Differences in representation (results identical):
   * the slot table is dense int32 (`_table`); `buffer_pt_index` is a lazily materialised int64 view;
-  * a packed 16-byte candidate record per neural point (`_cand` = xyz + filtered local index) is
-    rebuilt whenever the local map or `travel_dist` changes and is what the fused kernels read;
+  * the query kernels read an L2-resident view of that table (`_occ` occupancy words + rank-ordered
+    16-byte candidate records `_cand_*` = xyz + global / filtered local index, csrc/index.cu), rebuilt
+    whenever the table, the local map or `travel_dist` change;
   * `query_sdf()` is the fused entry used by Tracker / Mapper / Mesher (one autograd.Function).
 """
 from __future__ import annotations
@@ -92,6 +93,9 @@ class NeuralPoints(nn.Module):
         self._cand_local = None
         self._cand_global = None
         self._cand_dirty = True
+        self._index_dirty = True
+        self._occ = None
+        self._ws = None
         self.set_search_neighborhood(num_nei_cells=config.num_nei_cells, search_alpha=config.search_alpha)
         self.memory_footprint = []
         self.to(self.device)
@@ -123,6 +127,8 @@ class NeuralPoints(nn.Module):
             self._table = None
         else:
             self._table = value.to(device=self.device, dtype=torch.int32).contiguous()
+        self._cand_dirty = True
+        self._index_dirty = True
 
     def is_empty(self):
         return self.neural_points.shape[0] == 0
@@ -164,6 +170,8 @@ class NeuralPoints(nn.Module):
         if self._table is None:
             self._table = torch.empty(self.buffer_size, dtype=torch.int32, device=self.device)
             P.check(P.load().pinq_table_clear(P.ptr(self._table), self.buffer_size, P.stream()))
+            self._index_dirty = True
+            self._cand_dirty = True
 
     # ---- map maintenance -----------------------------------------------------------------------
     def update(self, points: torch.Tensor, sensor_position: torch.Tensor, sensor_orientation: torch.Tensor, cur_ts):
@@ -190,6 +198,7 @@ class NeuralPoints(nn.Module):
         values = hash_idx  # cur_pt_idx (neural_points.py:242-245)
         values[sel64] = torch.arange(new_point_count, dtype=torch.int32, device=self.device) + m0
         P.check(lib.pinq_table_scatter_last_wins(P.ptr(self._table), P.ptr(slots), P.ptr(values), n, st))
+        self._index_dirty = True
 
         self.neural_points = torch.cat((self.neural_points, added_pt), 0)
         ident = torch.zeros((new_point_count, 4), dtype=self.dtype, device=self.device)
@@ -308,6 +317,7 @@ class NeuralPoints(nn.Module):
             values = torch.arange(self.neural_points.shape[0], dtype=torch.int32, device=self.device)
         P.check(lib.pinq_table_scatter_last_wins(P.ptr(self._table), P.ptr(slots), P.ptr(values), slots.shape[0], st))
         self._cand_dirty = True
+        self._index_dirty = True
         if sensor_position is not None:
             self.reset_local_map(sensor_position, sensor_orientation, cur_ts)
         if not kept_points:
@@ -326,32 +336,53 @@ class NeuralPoints(nn.Module):
 
     # ---- packed views for the kernels ---------------------------------------------------------
     def _refresh_candidates(self):
-        """(Re)build the 16-byte candidate records: xyz + local index after the travel-distance filter
-        (reference: model/neural_points.py:480-488 fused with the global2local remap :555)."""
+        """(Re)build the L2-resident read view of the slot table (csrc/index.cu): occupancy words +
+        rank-ordered 16-byte candidate records (xyz + global index | local index after the
+        travel-distance filter of model/neural_points.py:480-488 and the global2local remap :555)."""
         if not self._cand_dirty:
             return
         lib = P.load()
+        st = P.stream()
+        self._ensure_table()
         m = self.neural_points.shape[0]
         self.neural_points = self.neural_points.contiguous()
+        if self._index_dirty or self._occ is None:
+            nwords = int(lib.pinq_index_words(self.buffer_size))
+            if self._occ is None:
+                self._occ = torch.empty((nwords, 2), dtype=torch.int32, device=self.device)
+                self._occ_scratch = torch.empty(int(lib.pinq_index_scratch_bytes(self.buffer_size)), dtype=torch.uint8,
+                                                device=self.device)
+                self._occ_count = torch.empty(1, dtype=torch.int32, device=self.device)
+            P.check(lib.pinq_index_build(P.ptr(self._table), self.buffer_size, P.ptr(self._occ), P.ptr(self._occ_count),
+                                         P.ptr(self._occ_scratch), st))
+            self._index_dirty = False
+        # occupied slots <= number of points ever inserted, so m rows always suffice (no host sync)
         self._cand_global = torch.empty((max(m, 1), 4), dtype=torch.float32, device=self.device)
-        P.check(lib.pinq_pack_candidates(P.ptr(self.neural_points), P.ptr(self.point_ts_create), m, None, None, 0, 0.0,
-                                         P.ptr(self._cand_global), P.stream()))
-        if self.global2local is not None and self.global2local.shape[0] == m + 1 and self._travel_dist is not None:
-            self._cand_local = torch.empty((max(m, 1), 4), dtype=torch.float32, device=self.device)
-            P.check(lib.pinq_pack_candidates(P.ptr(self.neural_points), P.ptr(self.point_ts_create), m,
-                                             P.ptr(self.global2local), P.ptr(self._travel_dist), int(self.cur_ts),
-                                             float(self.diff_travel_dist_local), P.ptr(self._cand_local), P.stream()))
-        else:
-            self._cand_local = None
+        have_local = (self.global2local is not None and self.global2local.shape[0] == m + 1
+                      and self._travel_dist is not None)
+        self._cand_local = torch.empty((max(m, 1), 4), dtype=torch.float32, device=self.device) if have_local else None
+        if m > 0:
+            P.check(lib.pinq_index_pack(P.ptr(self._table), self.buffer_size, P.ptr(self._occ), P.ptr(self.neural_points),
+                                        P.ptr(self.point_ts_create), P.ptr(self.global2local) if have_local else None,
+                                        P.ptr(self._travel_dist) if have_local else None, int(self.cur_ts),
+                                        float(self.diff_travel_dist_local), P.ptr(self._cand_global),
+                                        P.ptr(self._cand_local) if have_local else None, st))
         self._cand_dirty = False
 
     def _map_view(self, local: bool) -> P.MapView:
         self._refresh_candidates()
-        cand = self._cand_local if local else self._cand_global
-        if local and cand is None:
+        rec = self._cand_local if local else self._cand_global
+        if local and rec is None:
             raise P.PinqError("local query before reset_local_map()/travel_dist were set")
-        return P.MapView(P.ptr(self._table), self.buffer_size, float(self.resolution), float(self.max_valid_dist2),
-                         int(self.neighbor_K), P.ptr(self._stencil_i32), P.ptr(cand), int(self.neural_points.shape[0]))
+        return P.MapView(P.ptr(self._occ), P.ptr(rec), self.buffer_size, float(self.resolution),
+                         float(self.max_valid_dist2), int(self.neighbor_K), P.ptr(self._stencil_i32),
+                         int(self.neural_points.shape[0]))
+
+    def _workspace(self, n: int):
+        nbytes = int(P.load().pinq_query_workspace_bytes(n))
+        if self._ws is None or self._ws.numel() < nbytes:
+            self._ws = torch.empty(nbytes, dtype=torch.uint8, device=self.device)
+        return self._ws
 
     @staticmethod
     def _as_query(points):
@@ -410,7 +441,9 @@ class NeuralPoints(nn.Module):
         a.quats = P.ptr(quats.contiguous()) if self.after_pgo else None
         if training_mode and query_ts is not None and ts_upd is not None:
             a.ts_update = P.ptr(ts_upd)
-            a.query_ts = P.ptr(query_ts.to(torch.int64).contiguous())
+            self._ts_keepalive = query_ts.to(torch.int64).contiguous()
+            a.query_ts = P.ptr(self._ts_keepalive)
+        a.workspace = P.ptr(self._workspace(x.shape[0]))
         return a
 
     def query_feature(self, query_points: torch.Tensor, query_ts: torch.Tensor = None, training_mode: bool = True,
@@ -453,6 +486,12 @@ class NeuralPoints(nn.Module):
         self._cand_local = None
         self._cand_global = None
         self._cand_dirty = True
+        self._index_dirty = True
+        self._occ = None
+        self._occ_scratch = None
+        self._occ_count = None
+        self._ws = None
+        self._ts_keepalive = None
         self._local_idx = None
         self.local_neural_points = None
         self.local_point_orientations = None
