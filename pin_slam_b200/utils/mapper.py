@@ -1,0 +1,258 @@
+"""Mapper -- online training of the neural-point map (reference: utils/mapper.py:27-733).
+
+Same constructor, attributes (`lose_track`, `static_mask`, `used_poses`, the `*_pool` tensors,
+`train_less`, `new_idx`) and method names as the reference.  `mapping()` runs, per iteration, the fused
+query kernels for the 16 384 pool samples and for the 6 x ceil(bs/10) numerical-gradient samples
+(training mode, hazard H9), the BCE + eikonal loss on [N] tensors in PyTorch, the hand-derived backward
+kernel (feature scatter-add + decoder gradients, skipped per flag when the decoder is frozen, H11) and
+the Adam step.  `process_frame()` keeps the replay pool with torch ops ("next" row) and
+uses the libpinq kernels for the map update and the new-sample certainty query.
+Bundle adjustment (pypose), semantics, colour and the Open3D helpers are out of scope.
+"""
+from __future__ import annotations
+
+import math
+
+import torch
+
+from .. import _pinq as P
+from .data_sampler import DataSampler
+from .loss import sdf_bce_loss
+from .tools import get_time, setup_optimizer, transform_torch
+
+
+class Mapper:
+    def __init__(self, config, dataset, neural_points, geo_mlp, sem_mlp=None, color_mlp=None):
+        self.config = config
+        self.silence = config.silence
+        self.dataset = dataset
+        self.neural_points = neural_points
+        self.geo_mlp = geo_mlp
+        self.sem_mlp = sem_mlp
+        self.color_mlp = color_mlp
+        self.device = config.device
+        self.dtype = config.dtype
+        self.used_poses = None
+        self.lose_track = False
+        self.require_gradient = False
+        if config.ekional_loss_on or config.proj_correction_on or config.consistency_loss_on:
+            self.require_gradient = True
+        if config.numerical_grad and not config.proj_correction_on and not config.consistency_loss_on:
+            self.require_gradient = False
+        if self.require_gradient or config.proj_correction_on or config.consistency_loss_on:
+            raise NotImplementedError("analytic-gradient / projection-correction / consistency losses are unused by "
+                                      "the reference configs and out of scope")
+        self.total_iter = 0
+        self.sdf_scale = config.logistic_gaussian_ratio * config.sigma_sigmoid_m
+        self.sampler = DataSampler(config)
+        self.ray_sample_count = 1 + config.surface_sample_n + config.free_behind_n + config.free_front_n
+        self.new_idx = None
+        self.ba_done_flag = False
+        self.train_less = False
+        self.static_mask = None
+        self.generator = None  # optional torch.Generator for reproducible sampling / batches
+        dev, dt = self.device, self.dtype
+        self.coord_pool = torch.empty((0, 3), device=dev, dtype=dt)
+        self.global_coord_pool = torch.empty((0, 3), device=dev, dtype=dt)
+        self.sdf_label_pool = torch.empty((0), device=dev, dtype=dt)
+        self.color_pool = None
+        self.sem_label_pool = None
+        self.normal_label_pool = None
+        self.weight_pool = torch.empty((0), device=dev, dtype=dt)
+        self.time_pool = torch.empty((0), device=dev, dtype=torch.long)
+        self.cur_sample_count = 0
+        self.pool_sample_count = 0
+        self.timing = {}
+
+    # ------------------------------------------------------------------------------------------
+    def dynamic_filter(self, points_torch, type_2_on: bool = False):
+        """reference: utils/mapper.py:79-108."""
+        with torch.no_grad():
+            out = self.neural_points.query_sdf(points_torch, self.geo_mlp, None, False, True, want_grad=type_2_on,
+                                               want_certainty=True)
+        cfg = self.config
+        static_mask = (out["certainty"] < cfg.dynamic_certainty_thre) | (out["sdf"] < cfg.dynamic_sdf_ratio_thre * cfg.voxel_size_m)
+        if type_2_on:
+            grad_norm = out["grad"].norm(dim=-1)
+            static_mask = static_mask & ((grad_norm > 0.3) | (out["certainty"] < 0.5))
+        return static_mask
+
+    def _randint(self, high, size):
+        if self.generator is not None:
+            return torch.randint(0, high, size, device=self.generator.device, generator=self.generator).to(self.device)
+        return torch.randint(0, high, size, device=self.device)
+
+    def process_frame(self, point_cloud_torch, frame_label_torch, cur_pose_torch, frame_id: int,
+                      filter_dynamic: bool = False, samples=None):
+        """reference: utils/mapper.py:110-321.  `samples` = (coord, sdf_label, weight) overrides the sampler
+        (used to feed the CUDA path and the oracle identical draws)."""
+        cfg = self.config
+        T0 = get_time()
+        frame_origin_torch = cur_pose_torch[:3, 3]
+        frame_orientation_torch = cur_pose_torch[:3, :3]
+        frame_point_torch = point_cloud_torch[:, :3]
+        self.static_mask = torch.ones(frame_point_torch.shape[0], dtype=torch.bool, device=self.device)
+        if filter_dynamic:
+            self.static_mask = self.dynamic_filter(transform_torch(frame_point_torch, cur_pose_torch))
+            frame_point_torch = frame_point_torch[self.static_mask]
+        T1 = get_time()
+        if samples is None:
+            coord, sdf_label, _, _, _, weight = self.sampler.sample(frame_point_torch, None, None, None,
+                                                                    generator=self.generator)
+        else:
+            coord, sdf_label, weight = samples
+        time_repeat = torch.full((coord.shape[0],), int(frame_id), dtype=torch.long, device=self.device)
+        self.cur_sample_count = sdf_label.shape[0]
+        self.pool_sample_count = self.sdf_label_pool.shape[0]
+        T2 = get_time()
+        if cfg.from_sample_points:
+            if cfg.from_all_samples:
+                update_points = coord
+            else:
+                update_points = coord[torch.abs(sdf_label) < cfg.surface_sample_range_m * cfg.map_surface_ratio, :]
+                update_points = transform_torch(update_points.contiguous(), cur_pose_torch)
+        else:
+            update_points = transform_torch(frame_point_torch.contiguous(), cur_pose_torch)
+        if cfg.prune_map_on and self.neural_points.prune_map(cfg.max_prune_certainty):
+            self.neural_points.recreate_hash(None, None, True, True, frame_id)
+        self.neural_points.update(update_points, frame_origin_torch, frame_orientation_torch, frame_id)
+        T3 = get_time()
+        self.coord_pool = torch.cat((self.coord_pool, coord), 0)
+        self.weight_pool = torch.cat((self.weight_pool, weight), 0)
+        self.sdf_label_pool = torch.cat((self.sdf_label_pool, sdf_label), 0)
+        self.time_pool = torch.cat((self.time_pool, time_repeat), 0)
+        if cfg.track_on and getattr(self.dataset, "odom_poses", None):
+            import numpy as np
+            self.used_poses = torch.tensor(np.array(self.dataset.odom_poses), device=self.device, dtype=torch.float64)
+        elif getattr(self.dataset, "gt_pose_provided", False):
+            import numpy as np
+            self.used_poses = torch.tensor(np.array(self.dataset.gt_poses), device=self.device, dtype=torch.float64)
+        global_coord = transform_torch(coord.contiguous(), cur_pose_torch)
+        self.global_coord_pool = torch.cat((self.global_coord_pool, global_coord), 0)
+        T3_1 = get_time()
+        if (frame_id + 1) % cfg.pool_filter_freq == 0:  # mapper.py:229-263
+            rel = self.global_coord_pool - frame_origin_torch.to(self.global_coord_pool)
+            filter_mask = torch.sum(rel ** 2, dim=-1) < cfg.window_radius ** 2
+            true_indices = torch.nonzero(filter_mask).squeeze()
+            pool_sample_count = true_indices.shape[0]
+            if pool_sample_count > cfg.pool_capacity:
+                discard_count = pool_sample_count - cfg.pool_capacity
+                discarded = self._randint(pool_sample_count, (discard_count,))
+                filter_mask[true_indices[discarded]] = False
+            self.coord_pool = self.coord_pool[filter_mask]
+            self.global_coord_pool = self.global_coord_pool[filter_mask]
+            self.sdf_label_pool = self.sdf_label_pool[filter_mask]
+            self.weight_pool = self.weight_pool[filter_mask]
+            self.time_pool = self.time_pool[filter_mask]
+            self.cur_sample_count = int(filter_mask[-self.cur_sample_count:].sum().item())
+            self.pool_sample_count = int(filter_mask.sum().item())
+        else:
+            self.cur_sample_count = coord.shape[0]
+            self.pool_sample_count = self.coord_pool.shape[0]
+        T3_2 = get_time()
+        if cfg.bs_new_sample > 0:  # mapper.py:274-307: learn more where the map is new
+            cur = self.global_coord_pool[-self.cur_sample_count:]
+            n_cur = cur.shape[0]
+            cert = torch.zeros(n_cur, device=self.device)
+            cur_label = self.sdf_label_pool[-self.cur_sample_count:]
+            self.neural_points.set_search_neighborhood(num_nei_cells=1, search_alpha=0.0)
+            bs = cfg.infer_bs
+            for head in range(0, n_cur, bs):
+                tail = min(head + bs, n_cur)
+                cert[head:tail] = self.neural_points.query_certainty(cur[head:tail].contiguous())
+            self.neural_points.set_search_neighborhood(num_nei_cells=cfg.num_nei_cells, search_alpha=cfg.search_alpha)
+            self.new_idx = torch.where((cert < cfg.new_certainty_thre) &
+                                       (torch.abs(cur_label) < cfg.surface_sample_range_m * 3.0))[0]
+            self.new_idx += (self.pool_sample_count - self.cur_sample_count)
+            new_sample_count = self.new_idx.shape[0]
+            self.train_less = bool(cfg.adaptive_mode and new_sample_count / self.cur_sample_count < cfg.new_sample_ratio_thre)
+        T4 = get_time()
+        self.timing = {"dynamic_filter_ms": (T1 - T0) * 1e3, "sampling_ms": (T2 - T1) * 1e3,
+                       "map_update_ms": (T3 - T2) * 1e3, "pool_ms": (T4 - T3) * 1e3,
+                       "pool_transform_ms": (T3_1 - T3) * 1e3, "pool_filter_ms": (T3_2 - T3_1) * 1e3}
+
+    def get_batch(self, global_coord=False):
+        """reference: utils/mapper.py:323-361."""
+        cfg = self.config
+        stop_status = getattr(self.dataset, "stop_status", False)
+        if cfg.bs_new_sample > 0 and self.new_idx is not None and not self.lose_track and not stop_status:
+            new_idx_count = self.new_idx.shape[0]
+            if new_idx_count > 0:
+                bs_new = min(new_idx_count, cfg.bs_new_sample)
+                index_history = self._randint(self.pool_sample_count, (cfg.bs - bs_new,))
+                index_new = self.new_idx[self._randint(new_idx_count, (bs_new,))]
+                index = torch.cat((index_history, index_new), dim=0)
+            else:
+                index = self._randint(self.pool_sample_count, (cfg.bs,))
+        else:
+            index = self._randint(self.pool_sample_count, (cfg.bs,))
+        coord = self.global_coord_pool[index, :] if global_coord else self.coord_pool[index, :]
+        return coord, self.sdf_label_pool[index], self.time_pool[index], None, None, None, self.weight_pool[index]
+
+    def free_pool(self):
+        self.coord_pool = self.weight_pool = self.sdf_label_pool = self.time_pool = None
+        self.sem_label_pool = self.color_pool = self.normal_label_pool = None
+
+    # ------------------------------------------------------------------------------------------
+    def mapping(self, iter_count):
+        """reference: utils/mapper.py:425-593."""
+        cfg = self.config
+        if self.train_less:
+            iter_count = max(1, iter_count - 5)
+        neural_point_feat = list(self.neural_points.parameters())
+        geo_mlp_param = list(self.geo_mlp.parameters())
+        opt = setup_optimizer(cfg, neural_point_feat, geo_mlp_param, None, None)
+        for _ in range(iter_count):
+            coord, sdf_label, ts, _, _, _, weight = self.get_batch(global_coord=not self.ba_done_flag)
+            cur_loss, _ = self.mapping_loss(coord, sdf_label, ts, weight)
+            opt.zero_grad(set_to_none=True)
+            cur_loss.backward(retain_graph=False)
+            opt.step()
+            self.total_iter += 1
+        self.neural_points.assign_local_to_global()
+
+    def mapping_loss(self, coord, sdf_label, ts, weight):
+        """One iteration's loss (reference: utils/mapper.py:461-547): BCE on the fused SDF prediction plus the
+        eikonal term on numerical gradients of every `gradient_decimation`-th sample."""
+        cfg = self.config
+        sdf_pred = self.neural_points.query_sdf(coord, self.geo_mlp, ts, True, True)["sdf"]
+        weight = torch.abs(weight).detach()
+        if cfg.main_loss_type != "bce":
+            raise NotImplementedError("only the bce main loss is in scope (reference: mapper.py:515-524 '[used]')")
+        cur_loss = sdf_bce_loss(sdf_pred, sdf_label, self.sdf_scale, weight, cfg.loss_weight_on)
+        if cfg.ekional_loss_on and cfg.weight_e > 0:
+            if not cfg.numerical_grad:
+                raise NotImplementedError("analytic eikonal gradient in mapping is unused by the reference configs")
+            g = self.get_numerical_gradient(coord[::cfg.gradient_decimation], sdf_pred[::cfg.gradient_decimation],
+                                            cfg.voxel_size_m * cfg.num_grad_step_ratio)
+            if cfg.ekional_add_to != "all":
+                surface_mask = (torch.abs(sdf_label) < cfg.surface_sample_range_m)[::cfg.gradient_decimation]
+                g = g[surface_mask] if cfg.ekional_add_to == "surface" else g[~surface_mask]
+            eikonal_loss = ((g.norm(2, dim=-1) - 1.0) ** 2).mean()
+            cur_loss = cur_loss + cfg.weight_e * eikonal_loss
+        return cur_loss, sdf_pred
+
+    def sdf(self, x, get_std=False):
+        """reference: utils/mapper.py:671-681 (default training_mode=True, no timestamps: hazard H9)."""
+        out = self.neural_points.query_sdf(x, self.geo_mlp, None, True, True, want_std=get_std)
+        return out["sdf"], out["std"]
+
+    def get_numerical_gradient(self, x, sdf_x=None, eps=0.02, two_side=True):
+        """reference: utils/mapper.py:683-733."""
+        N = x.shape[0]
+        e = torch.eye(3, dtype=x.dtype, device=x.device) * eps
+        if two_side:
+            x_posneg = torch.cat((x + e[0], x - e[0], x + e[1], x - e[1], x + e[2], x - e[2]), dim=0)
+            s = self.sdf(x_posneg)[0].unsqueeze(-1)
+            gx = (s[:N] - s[N:2 * N]) / (2 * eps)
+            gy = (s[2 * N:3 * N] - s[3 * N:4 * N]) / (2 * eps)
+            gz = (s[4 * N:5 * N] - s[5 * N:]) / (2 * eps)
+        else:
+            x_all = torch.cat((x + e[0], x + e[1], x + e[2]), dim=0)
+            s = self.sdf(x_all)[0].unsqueeze(-1)
+            sx = sdf_x.unsqueeze(-1)
+            gx, gy, gz = (s[:N] - sx) / eps, (s[N:2 * N] - sx) / eps, (s[2 * N:] - sx) / eps
+        return torch.cat([gx, gy, gz], dim=1)
+
+    def bundle_adjustment(self, iter_count, window_size: int = 50, use_lie_group: bool = False):
+        raise NotImplementedError("bundle adjustment needs pypose and is off by default (reference: config.py:236)")

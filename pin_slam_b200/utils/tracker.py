@@ -1,0 +1,197 @@
+"""Tracker -- point-to-implicit-model registration (reference: utils/tracker.py:19-520).
+
+Same constructor, `tracking()` signature, return tuple and validity control flow as the reference.
+Per Gauss-Newton iteration the device runs four launches -- transform (pinq_transform_points),
+search + decode (pinq_query_fused_fwd: sdf, d sdf/dx, std, nn_count in one pass, replacing
+query_feature -> Decoder.sdf -> get_gradient) and the fused mask/weights/normal-equation reduction
+(pinq_gn_accumulate) -- followed by ONE 256-byte device->host read; the 6x6 solve runs on the host in
+fp64 exactly as the reference does (tracker.py:491).  Colour / normal / semantic inputs are out of scope.
+"""
+from __future__ import annotations
+
+import math
+
+import numpy as np
+import torch
+
+from .. import _pinq as P
+
+
+class Tracker:
+    def __init__(self, config, neural_points, geo_decoder, sem_decoder=None, color_decoder=None):
+        self.config = config
+        self.silence = config.silence
+        self.neural_points = neural_points
+        self.geo_decoder = geo_decoder
+        self.sem_decoder = sem_decoder
+        self.color_decoder = color_decoder
+        self.device = config.device
+        self.dtype = config.dtype
+        self.sdf_scale = config.logistic_gaussian_ratio * config.sigma_sigmoid_m
+        self._gn_out = torch.zeros(32, dtype=torch.float64, device=self.device)
+        self._gn_host = torch.zeros(32, dtype=torch.float64).pin_memory()
+        self.last_iterations = 0
+
+    # ------------------------------------------------------------------------------------------
+    def tracking(self, source_points, init_pose=None, source_colors=None, source_normals=None, source_semantics=None,
+                 source_sdf=None, cur_ts=None, loop_reg: bool = False, vis_result: bool = False):
+        """reference: utils/tracker.py:39-174 -> (T [4,4] f64, cov_mat | None, weight_pc | None, valid_flag)."""
+        if source_colors is not None or source_normals is not None:
+            raise NotImplementedError("photometric / normal-weighted registration is out of scope")
+        cfg = self.config
+        if init_pose is None:
+            init_pose = torch.eye(4, dtype=torch.float64, device=self.device)
+        T = init_pose.detach().to("cpu", torch.float64).numpy().copy()
+        cov_mat = None
+        min_grad_norm, max_grad_norm = cfg.reg_min_grad_norm, cfg.reg_max_grad_norm
+        GM_dist = cfg.reg_GM_dist_m if cfg.reg_GM_dist_m > 0 else None
+        GM_grad = cfg.reg_GM_grad if cfg.reg_GM_grad > 0 else None
+        iter_n = cfg.reg_iter_n
+        max_valid_final_sdf_residual_cm = cfg.surface_sample_range_m * 0.5 * 100.0
+        min_valid_ratio = 0.2
+        if loop_reg:
+            max_valid_final_sdf_residual_cm = cfg.surface_sample_range_m * 0.6 * 100.0
+            min_valid_ratio = 0.15
+        max_increment_sdf_residual_ratio = 1.1
+        eigenvalue_ratio_thre = 0.01
+        min_valid_points = 30
+        converged = False
+        valid_flag = True
+        last_sdf_residual_cm = 1e5
+        src = source_points.detach().to(self.dtype).contiguous()
+        source_point_count = src.shape[0]
+        sdf_residual_cm = 0.0
+        valid_point_count = 0
+        eigenvalues = None
+        cur_points = torch.empty_like(src)
+        lib = P.load()
+        it = 0
+        for i in range(iter_n):
+            it = i + 1
+            T12 = torch.from_numpy(T[:3, :].astype(np.float32)).to(self.device, non_blocking=True)
+            P.check(lib.pinq_transform_points(P.ptr(src), source_point_count, P.ptr(T12), P.ptr(cur_points), P.stream()))
+            reg = self.registration_step(cur_points, None, source_sdf, None, cur_ts, min_grad_norm, max_grad_norm,
+                                         GM_dist, GM_grad, cfg.reg_lm_lambda, (vis_result and converged))
+            delta_T, cov_mat, eigenvalues, _, valid_point_count, sdf_residual_cm, _ = reg
+            T = delta_T @ T
+            if (sdf_residual_cm - last_sdf_residual_cm) / last_sdf_residual_cm > max_increment_sdf_residual_ratio:
+                if not self.silence:
+                    print("(Warning) registration failed: wrong optimization")
+                valid_flag = False
+            else:
+                last_sdf_residual_cm = sdf_residual_cm
+            if (valid_point_count < min_valid_points) or (1.0 * valid_point_count / source_point_count < min_valid_ratio):
+                if not self.silence:
+                    print("(Warning) registration failed: not enough valid points")
+                valid_flag = False
+            if not valid_flag or converged:
+                break
+            with np.errstate(invalid="ignore"):
+                rot_angle_deg = math.degrees(np.arccos((np.trace(delta_T[:3, :3]) - 1) / 2))
+            tran_m = float(np.linalg.norm(delta_T[:3, 3]))
+            # NOTE `and` binds tighter than `or` (tracker.py:135); NaN angles compare False as in torch
+            if abs(rot_angle_deg) < cfg.reg_term_thre_deg and tran_m < cfg.reg_term_thre_m or i == iter_n - 2:
+                converged = True
+        self.last_iterations = it
+        if sdf_residual_cm > max_valid_final_sdf_residual_cm:
+            if not self.silence:
+                print("(Warning) registration failed: too large final residual")
+            valid_flag = False
+        if eigenvalues is not None:
+            min_eigenvalue = float(np.min(eigenvalues))
+            if cfg.eigenvalue_check and min_eigenvalue < valid_point_count * eigenvalue_ratio_thre:
+                valid_flag = False
+        T_out = torch.tensor(T, dtype=torch.float64, device=self.device)
+        if not valid_flag:  # NOTE: if not valid, just take the initial guess (tracker.py:170-172)
+            T_out = init_pose
+            cov_mat = None
+        return T_out, cov_mat, None, valid_flag
+
+    # ------------------------------------------------------------------------------------------
+    def query_source_points(self, coord, ts, bs, query_sdf=True, query_sdf_grad=True, query_color=False,
+                            query_color_grad=False, query_sem=False, query_mask=True, query_certainty=True,
+                            query_locally=True, mask_min_nn_count: int = 4):
+        """reference: utils/tracker.py:176-275 -> (sdf, sdf_grad, None, None, None, mc_mask, certainty, sdf_std)."""
+        if query_color or query_sem or query_color_grad:
+            raise NotImplementedError("colour / semantic queries are out of scope")
+        n = coord.shape[0]
+        dev = coord.device
+        sdf_pred = torch.zeros(n, device=dev)
+        sdf_std = torch.zeros(n, device=dev)
+        sdf_grad = torch.zeros((n, 3), device=dev) if query_sdf_grad else None
+        mc_mask = torch.zeros(n, device=dev, dtype=torch.bool) if query_mask else None
+        certainty = torch.zeros(n, device=dev) if query_certainty else None
+        with torch.no_grad():
+            for head in range(0, n, bs):
+                tail = min(head + bs, n)
+                out = self.neural_points.query_sdf(coord[head:tail], self.geo_decoder, None, False, query_locally,
+                                                   want_grad=query_sdf_grad, want_std=True,
+                                                   want_certainty=query_certainty)
+                sdf_pred[head:tail] = out["sdf"]
+                sdf_std[head:tail] = out["std"]
+                if query_sdf_grad:
+                    sdf_grad[head:tail] = out["grad"]
+                if query_mask:
+                    mc_mask[head:tail] = out["nn_count"] >= mask_min_nn_count
+                if query_certainty:
+                    certainty[head:tail] = out["certainty"]
+        return sdf_pred, sdf_grad, None, None, None, mc_mask, certainty, sdf_std
+
+    def registration_step(self, points, normals, sdf_labels, colors, cur_ts, min_grad_norm, max_grad_norm, GM_dist=None,
+                          GM_grad=None, lm_lambda=0.0, vis_weight_pc=False):
+        """reference: utils/tracker.py:277-452 + implicit_reg :468-520.
+        -> (delta_T ndarray[4,4] f64, cov_mat, eigenvalues, None, valid_point_count, residual_cm, None)"""
+        cfg = self.config
+        lib = P.load()
+        n = points.shape[0]
+        with torch.no_grad():
+            out = self.neural_points.query_sdf(points, self.geo_decoder, None, False, True, want_grad=True, want_std=True)
+        max_sdf_std = cfg.surface_sample_range_m * cfg.max_sdf_std_ratio
+        self._gn_out.zero_()
+        P.check(lib.pinq_gn_accumulate(P.ptr(points), P.ptr(out["sdf"]), P.ptr(out["grad"]), P.ptr(out["std"]),
+                                       P.ptr(out["nn_count"]), P.ptr(sdf_labels) if sdf_labels is not None else None, n,
+                                       int(cfg.query_nn_k), float(min_grad_norm), float(max_grad_norm), float(max_sdf_std),
+                                       float(GM_dist or 0.0), float(GM_grad or 0.0), P.ptr(self._gn_out), None, P.stream()))
+        self._gn_host.copy_(self._gn_out, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        g = self._gn_host.numpy()
+        valid_point_count = int(round(g[29]))
+        if valid_point_count < 10:  # tracker.py:310-312
+            return np.eye(4), None, None, None, valid_point_count, 0.0, 0.0
+        residual_cm = g[28] / valid_point_count * 100.0
+        T, cov_mat, eig = solve_normal_equations(g, valid_point_count, lm_lambda, vis_weight_pc, vis_weight_pc)
+        return T, cov_mat, eig, None, valid_point_count, residual_cm, None
+
+
+def solve_normal_equations(g: np.ndarray, count: int, lm_lambda: float, require_cov=False, require_eigen=False):
+    """Host side of implicit_reg (utils/tracker.py:468-520) from the fused reduction of pinq_gn_accumulate:
+    g[0:21] = upper triangle of sum w J^T J, g[21:27] = sum w r J, g[27] = sum w  (w un-normalised)."""
+    norm = 2.0 * g[27] / count  # w /= 2 mean(w), tracker.py:394
+    H = np.zeros((6, 6))
+    iu = np.triu_indices(6)
+    H[iu] = g[:21]
+    H = H + H.T - np.diag(np.diag(H))
+    H /= norm
+    b = -g[21:27] / norm
+    H0 = H.copy()
+    H = H + lm_lambda * np.diag(np.diag(H))
+    t = np.linalg.inv(H) @ b
+    T = np.eye(4)
+    T[:3, :3] = expmap(t[:3])
+    T[:3, 3] = t[3:]
+    eig = np.linalg.eigvals(H0[3:, 3:]).real if require_eigen else None
+    cov = None  # needs sum w r^2 (visualisation only, tracker.py:507-510): not accumulated
+    return T, cov, eig
+
+
+def skew(v):
+    """reference: utils/tracker.py:573-578."""
+    return np.array([[0.0, -v[2], v[1]], [v[2], 0.0, -v[0]], [-v[1], v[0], 0.0]])
+
+
+def expmap(axis_angle: np.ndarray):
+    """Rodrigues (reference: utils/tracker.py:580-589); a zero rotation yields NaNs there as here."""
+    angle = np.linalg.norm(axis_angle)
+    with np.errstate(invalid="ignore", divide="ignore"):
+        S = skew(axis_angle / angle)
+    return np.eye(3) + S * np.sin(angle) + (S @ S) * (1.0 - np.cos(angle))
