@@ -104,9 +104,14 @@ int64_t pinq_index_scratch_bytes(uint32_t buffer_size);
 int pinq_index_build(const int32_t* table, uint32_t buffer_size, uint32_t* occ2, int32_t* d_count, void* scratch,
                      void* stream);
 /* rec_global.w = table value (global point index); rec_local.w = global2local[] of it after the
- * travel-distance filter of model/neural_points.py:480-488 (-1 = rejected).  Either may be NULL. */
+ * travel-distance filter of model/neural_points.py:480-488 (-1 = rejected).  Either may be NULL.
+ * Hazard H13: the reference remaps points OUTSIDE the local map to local index 1, not -1
+ * (neural_points.py:301, full_like on a bool mask); such candidates are stored as -2 and the decode
+ * kernel resolves them to index 1 with the position of local point 1, exactly as the reference does.
+ * local_mask = uint8[m+1] flags of reset_local_map. */
 int pinq_index_pack(const int32_t* table, uint32_t buffer_size, const uint32_t* occ2, const float* map_xyz,
-                    const int64_t* ts_create, const int64_t* global2local, const float* travel_dist,
+                    const int64_t* ts_create, const int64_t* global2local, const uint8_t* local_mask,
+                    const float* travel_dist,
                     int64_t cur_ts, float diff_travel_dist_local, float* rec_global4, float* rec_local4,
                     void* stream);
 
@@ -154,6 +159,7 @@ typedef struct pinq_query_args {
     int32_t k;                 /* query_nn_k = 6                                                  */
     int32_t feature_dim;       /* 8                                                               */
     const float* features;     /* [Mx+1, F]: local_geo_features (LOCAL) or geo_features           */
+    const float* point_xyz;    /* [Mx,3] positions indexed like `features` (hazard H13 only)      */
     float* certainties;        /* [Mx]: read for queried certainty; += w in TRAINING mode         */
     const float* quats;        /* [Mx,4] or NULL (needed with PINQ_F_ROTATE)                      */
     int64_t* ts_update;        /* [Mx] or NULL: amax with query_ts in TRAINING mode               */

@@ -208,7 +208,10 @@ def reset_local_map(s: MapState, sensor_position: torch.Tensor, cur_ts: int) -> 
     s.l_ts_update = s.ts_update[m]
     m = torch.cat((m, torch.tensor([True])))
     s.local_mask = m
-    g2l = torch.full((m.shape[0],), -1, dtype=I64)
+    # QUIRK (hazard H13, found by the golden vectors): the reference writes torch.full_like(local_mask, -1).long()
+    # with a BOOL local_mask, i.e. True -> 1: points outside the local map remap to local index 1, not -1
+    # (model/neural_points.py:301); only the padding entry is -1 (:305).
+    g2l = torch.full_like(m, -1).long()
     nz = torch.nonzero(m).flatten()
     g2l[nz] = torch.arange(nz.shape[0], dtype=I64)
     g2l[-1] = -1

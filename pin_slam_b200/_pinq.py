@@ -27,7 +27,7 @@ class DecoderView(C.Structure):
 
 class QueryArgs(C.Structure):
     _fields_ = [("map", MapView), ("dec", DecoderView), ("xyz", _vp), ("n", _i64), ("flags", _u32), ("k", _i32),
-                ("feature_dim", _i32), ("features", _vp), ("certainties", _vp), ("quats", _vp), ("ts_update", _vp),
+                ("feature_dim", _i32), ("features", _vp), ("point_xyz", _vp), ("certainties", _vp), ("quats", _vp), ("ts_update", _vp),
                 ("query_ts", _vp), ("sdf", _vp), ("grad_x", _vp), ("sdf_std", _vp), ("nn_count", _vp),
                 ("certainty", _vp), ("knn_idx", _vp), ("knn_w", _vp), ("knn_d2", _vp), ("workspace", _vp)]
 
@@ -57,7 +57,7 @@ SIGNATURES = {
     "pinq_index_words": (_i64, [_u32]),
     "pinq_index_scratch_bytes": (_i64, [_u32]),
     "pinq_index_build": (C.c_int, [_vp, _u32, _vp, _vp, _vp, _vp]),
-    "pinq_index_pack": (C.c_int, [_vp, _u32, _vp, _vp, _vp, _vp, _vp, _i64, _f32, _vp, _vp, _vp]),
+    "pinq_index_pack": (C.c_int, [_vp, _u32, _vp, _vp, _vp, _vp, _vp, _vp, _i64, _f32, _vp, _vp, _vp]),
     "pinq_query_workspace_bytes": (_i64, [_i64]),
     "pinq_neighbor_search": (C.c_int, [C.POINTER(MapView), _vp, _i64, _u32, _vp, _vp, _vp, _i64, _f32, C.c_int, _vp,
                                        _vp, _vp]),

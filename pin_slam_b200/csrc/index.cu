@@ -88,7 +88,7 @@ __global__ void k_occ_prefix(uint2* __restrict__ occ, uint32_t nwords, const int
 // model/neural_points.py:480-488 (-1 = not a candidate for local queries).
 __global__ void k_occ_pack(const int32_t* __restrict__ table, uint32_t B, uint32_t nwords, const uint2* __restrict__ occ,
                            const float* __restrict__ xyz, const int64_t* __restrict__ ts_c, const int64_t* __restrict__ g2l,
-                           const float* __restrict__ td, int64_t cur_ts, float diff_td, float4* __restrict__ rec_global,
+                           const uint8_t* __restrict__ lmask, const float* __restrict__ td, int64_t cur_ts, float diff_td, float4* __restrict__ rec_global,
                            float4* __restrict__ rec_local) {
     const int lane = threadIdx.x & 31;
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -110,7 +110,7 @@ __global__ void k_occ_pack(const int32_t* __restrict__ table, uint32_t B, uint32
             const float x = xyz[3 * (int64_t)v], y = xyz[3 * (int64_t)v + 1], z = xyz[3 * (int64_t)v + 2];
             if (rec_global) rec_global[r] = make_float4(x, y, z, __int_as_float(v));
             if (rec_local) {
-                int32_t li = (int32_t)g2l[v];
+                int32_t li = lmask[v] ? (int32_t)g2l[v] : -2;  // -2: outside the local map -> index 1 (hazard H13)
                 const float dt = fabsf(__fsub_rn(td[cur_ts], td[ts_c[v]]));
                 if (!(dt < diff_td)) li = -1;
                 rec_local[r] = make_float4(x, y, z, __int_as_float(li));
@@ -148,14 +148,14 @@ int pinq_index_build(const int32_t* table, uint32_t buffer_size, uint32_t* occ2,
 }
 
 int pinq_index_pack(const int32_t* table, uint32_t buffer_size, const uint32_t* occ2, const float* map_xyz,
-                    const int64_t* ts_create, const int64_t* global2local, const float* travel_dist, int64_t cur_ts,
-                    float diff_travel_dist_local, float* rec_global4, float* rec_local4, void* stream) {
+                    const int64_t* ts_create, const int64_t* global2local, const uint8_t* local_mask,
+                    const float* travel_dist, int64_t cur_ts, float diff_travel_dist_local, float* rec_global4, float* rec_local4, void* stream) {
     PINQ_REQUIRE(table && occ2 && map_xyz, "null pointer");
-    PINQ_REQUIRE(!rec_local4 || (ts_create && global2local && travel_dist), "local records need ts_create, global2local, travel_dist");
+    PINQ_REQUIRE(!rec_local4 || (ts_create && global2local && travel_dist && local_mask), "local records need ts_create, global2local, travel_dist");
     if (!rec_global4 && !rec_local4) return PINQ_OK;
     const uint32_t nwords = (uint32_t)pinq_index_words(buffer_size);
     k_occ_pack<<<148 * 8, 256, 0, as_stream(stream)>>>(table, buffer_size, nwords, reinterpret_cast<const uint2*>(occ2),
-                                                       map_xyz, ts_create, global2local, travel_dist, cur_ts,
+                                                       map_xyz, ts_create, global2local, local_mask, travel_dist, cur_ts,
                                                        diff_travel_dist_local, reinterpret_cast<float4*>(rec_global4),
                                                        reinterpret_cast<float4*>(rec_local4));
     return check_launch("pinq_index_pack");

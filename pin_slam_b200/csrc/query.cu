@@ -106,6 +106,7 @@ struct DecodeParams {
     bool rotate, scatter_in_kernel;
     const int32_t* ws;
     const float* features;
+    const float* point_xyz;
     float* certainties;
     const float4* quats;
     long long* ts_update;
@@ -149,15 +150,21 @@ __global__ void __launch_bounds__(kBlock) k_decode(const DecodeParams p) {
         const int32_t r = wsq[k];
         if (r >= 0) {
             const float4 rc = __ldg(&p.rec[r]);
-            const int32_t li = __float_as_int(rc.w);
-            kidx[k] = li;
+            int32_t li = __float_as_int(rc.w);
+            float px = rc.x, py = rc.y, pz = rc.z;
             kd2[k] = dist2_rn(rc.x, rc.y, rc.z, x, y, z);  // same ops as the search -> same bits
+            if (li == -2) {  // hazard H13: candidate outside the local map -> the reference gathers local row 1
+                li = 1;
+                px = p.point_xyz[3]; py = p.point_xyz[4]; pz = p.point_xyz[5];
+            }
+            kidx[k] = li;
             const float4* fr = reinterpret_cast<const float4*>(p.features + (int64_t)li * F);
             const float4 a = __ldg(fr), b = __ldg(fr + 1);
             in[k][0] = a.x; in[k][1] = a.y; in[k][2] = a.z; in[k][3] = a.w;
             in[k][4] = b.x; in[k][5] = b.y; in[k][6] = b.z; in[k][7] = b.w;
-            float vx = __fsub_rn(x, rc.x), vy = __fsub_rn(y, rc.y), vz = __fsub_rn(z, rc.z);
-            ux[k] = vx; uy[k] = vy; uz[k] = vz;
+            float vx = __fsub_rn(x, px), vy = __fsub_rn(y, py), vz = __fsub_rn(z, pz);
+            // the IDW weights (and their x-gradient) come from the TRUE candidate position
+            ux[k] = __fsub_rn(x, rc.x); uy[k] = __fsub_rn(y, rc.y); uz[k] = __fsub_rn(z, rc.z);
             if (p.rotate) quat_rotate(__ldg(&p.quats[li]), false, vx, vy, vz);
             in[k][8] = vx; in[k][9] = vy; in[k][10] = vz;
         }
@@ -294,8 +301,8 @@ static int run_query(const pinq_query_args* a, int mode, float* feat_out, const 
         set_error("unsupported specialisation: need query_nn_k=6, feature_dim=8");
         return PINQ_ERR_UNSUPPORTED;
     }
-    if (!a->features || !a->workspace) {
-        set_error("null features/workspace");
+    if (!a->features || !a->workspace || ((a->flags & PINQ_F_LOCAL) && !a->point_xyz)) {
+        set_error("null features/workspace (or point_xyz for a local query)");
         return PINQ_ERR_BAD_ARG;
     }
     if ((a->flags & PINQ_F_ROTATE) && !a->quats) {
@@ -329,7 +336,7 @@ static int run_query(const pinq_query_args* a, int mode, float* feat_out, const 
     // caller wants it (and gave knn buffers), scatter in a second kernel; otherwise fuse the atomics.
     const bool two_pass = training && a->certainty && a->knn_idx && a->knn_w;
     p.scatter_in_kernel = training && !two_pass;
-    p.ws = ws; p.features = a->features; p.certainties = a->certainties;
+    p.ws = ws; p.features = a->features; p.point_xyz = a->point_xyz; p.certainties = a->certainties;
     p.quats = reinterpret_cast<const float4*>(a->quats);
     p.ts_update = reinterpret_cast<long long*>(a->ts_update); p.query_ts = a->query_ts;
     p.sdf = a->sdf; p.grad_x = a->grad_x; p.sdf_std = a->sdf_std; p.nn_count = a->nn_count;

@@ -106,7 +106,7 @@ __device__ __forceinline__ void load_point(const PointSrc& s, int64_t q, float& 
 // kd2 ascending, nn = valid candidates over the whole stencil.  Probes go out in batches of U independent
 // 8-byte index loads followed by U predicated 16-byte record loads (memory-level parallelism without a
 // shared-memory hit list, so occupancy is bounded by registers only).
-// Validity (neural_points.py:480-499, 555-561): index >= 0 (local filter baked into rec.w) and d2 <= max.
+// Validity (neural_points.py:480-499, 555-561): index != -1 (local filter baked into rec.w) and d2 <= max.
 __device__ __forceinline__ void search_topk(const MapDev& map, const uint32_t* s_off, float x, float y, float z,
                                             bool recip, float (&kd2)[K], int32_t (&kr)[K], int& nn) {
     const uint32_t base = base_slot(map, x, y, z, recip);
@@ -137,7 +137,7 @@ __device__ __forceinline__ void search_topk(const MapDev& map, const uint32_t* s
         for (int u = 0; u < U; ++u) {
             if (r[u] < 0) continue;
             const float d2 = dist2_rn(rc[u].x, rc[u].y, rc[u].z, x, y, z);
-            if (__float_as_int(rc[u].w) < 0 || d2 > map.max_d2) continue;
+            if (__float_as_int(rc[u].w) == -1 || d2 > map.max_d2) continue;  // -2 = hazard H13, still a candidate
             ++nn;
             if (d2 < kd2[K - 1]) {  // strict <: equal distances keep stencil order (stable)
                 kd2[K - 1] = d2;

@@ -237,8 +237,13 @@ class NeuralPoints(nn.Module):
         self.local_point_certainties = self.point_certainties[idx]
         self.local_point_ts_update = self.point_ts_update[idx]
         self.local_mask = flags.to(torch.bool)
-        g2l = torch.full((m + 1,), -1, dtype=torch.int64, device=self.device)
+        self._local_flags = flags
+        # QUIRK kept for parity (hazard H13): the reference builds this with full_like(<bool mask>, -1).long(),
+        # so points outside the local map remap to local index 1 (not -1); only the padding entry is -1
+        # (reference: model/neural_points.py:301-305).
+        g2l = torch.full((m + 1,), 1, dtype=torch.int64, device=self.device)
         g2l[idx] = torch.arange(idx.shape[0], dtype=torch.int64, device=self.device)
+        g2l[m] = -1
         self.global2local = g2l
         self._local_idx = idx_pad
         self.local_geo_features = nn.Parameter(self.geo_features[idx_pad])
@@ -364,6 +369,7 @@ class NeuralPoints(nn.Module):
         if m > 0:
             P.check(lib.pinq_index_pack(P.ptr(self._table), self.buffer_size, P.ptr(self._occ), P.ptr(self.neural_points),
                                         P.ptr(self.point_ts_create), P.ptr(self.global2local) if have_local else None,
+                                        P.ptr(self._local_flags) if have_local else None,
                                         P.ptr(self._travel_dist) if have_local else None, int(self.cur_ts),
                                         float(self.diff_travel_dist_local), P.ptr(self._cand_global),
                                         P.ptr(self._cand_local) if have_local else None, st))
@@ -439,6 +445,8 @@ class NeuralPoints(nn.Module):
         a.features = P.ptr(feats.detach())
         a.certainties = P.ptr(cert)
         a.quats = P.ptr(quats.contiguous()) if self.after_pgo else None
+        pts = self.local_neural_points if query_locally else self.neural_points
+        a.point_xyz = P.ptr(pts.contiguous())
         if training_mode and query_ts is not None and ts_upd is not None:
             a.ts_update = P.ptr(ts_upd)
             self._ts_keepalive = query_ts.to(torch.int64).contiguous()

@@ -84,6 +84,53 @@ def decoder_pair(cfg, seed=42):
 
 
 def rel_err(a, b, floor=1e-6):
-    a = a.double().cpu()
-    b = b.double().cpu()
-    return float((a - b).norm() / max(float(b.norm()), floor))
+    a = a.detach().double().cpu()
+    b = b.detach().double().cpu()
+    return float((a - b).norm()) / max(float(b.norm()), floor)
+
+
+# ---- golden fixture (generated from the unmodified reference by oracle/make_golden.py) -------------------
+GOLDEN = os.path.join(ROOT, "tests", "golden", "ref_kitti_small.npz")
+
+
+def load_golden():
+    return {k: v for k, v in np.load(GOLDEN).items()}
+
+
+def golden_oracle_world(G):
+    """Replay the fixture's inputs through the oracle: (state, decoder)."""
+    p = O.MapParams(buffer_size=int(G["buffer_size"]))
+    s = O.new_map(p)
+    s.travel_dist = torch.from_numpy(G["travel_dist"])
+    for ts in range(3):
+        O.map_update(s, torch.from_numpy(G["frames%d" % ts]), torch.tensor([3.0 * ts, 0.0, 0.0]), ts)
+    s.feats = torch.from_numpy(G["features"]).clone()
+    s.certainty = torch.from_numpy(G["certainties"]).clone()
+    O.reset_local_map(s, torch.tensor([6.0, 0.0, 0.0]), 2)
+    d = O.DecoderParams(*[torch.from_numpy(G[k]).clone() for k in ("W1", "b1", "W2", "b2")], sdf_scale=float(G["sdf_scale"]))
+    return s, d
+
+
+def golden_cuda_world(G):
+    """Replay the fixture's inputs through the CUDA path: (NeuralPoints, Decoder, cfg)."""
+    from pin_slam_b200.model.decoder import Decoder
+    from pin_slam_b200.model.neural_points import NeuralPoints
+    from pin_slam_b200.utils.config import kitti_config
+
+    cfg = kitti_config("cuda")
+    cfg.buffer_size = int(G["buffer_size"])
+    m = NeuralPoints(cfg)
+    m.travel_dist = torch.from_numpy(G["travel_dist"])
+    eye = torch.eye(3, device="cuda")
+    for ts in range(3):
+        m.update(torch.from_numpy(G["frames%d" % ts]).cuda(), torch.tensor([3.0 * ts, 0.0, 0.0]).cuda(), eye, ts)
+    m.geo_features = torch.from_numpy(G["features"]).cuda()
+    m.point_certainties = torch.from_numpy(G["certainties"]).cuda()
+    m.reset_local_map(torch.tensor([6.0, 0.0, 0.0]).cuda(), eye, 2)
+    dec = Decoder(cfg, 64, 1, 1)
+    with torch.no_grad():
+        dec.layers[0].weight.copy_(torch.from_numpy(G["W1"]))
+        dec.layers[0].bias.copy_(torch.from_numpy(G["b1"]))
+        dec.lout.weight.copy_(torch.from_numpy(G["W2"]))
+        dec.lout.bias.copy_(torch.from_numpy(G["b2"]))
+    return m, dec, cfg

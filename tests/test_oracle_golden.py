@@ -1,0 +1,131 @@
+"""CPU: the oracle restatement vs golden vectors produced by the UNMODIFIED reference (oracle/make_golden.py).
+Bit-exact for slots / indices / counts and for everything that is pure gather + exact fp32 arithmetic;
+1e-6 for values that go through BLAS / reductions."""
+import numpy as np
+import pytest
+import torch
+
+from helpers import O, golden_oracle_world, load_golden, rel_err
+
+
+@pytest.fixture(scope="module")
+def world():
+    G = load_golden()
+    s, d = golden_oracle_world(G)
+    return G, s, d
+
+
+def T(a):
+    return torch.from_numpy(np.asarray(a))
+
+
+def test_map_state_bit_exact(world):
+    G, s, _ = world
+    assert torch.equal(s.table.int(), T(G["table"]))
+    assert torch.equal(s.points, T(G["neural_points"]))
+    assert torch.equal(s.ts_create, T(G["ts_create"]))
+    assert torch.equal(s.global2local.int(), T(G["global2local"]))
+    assert torch.equal(s.local_mask, T(G["local_mask"]))
+    # the travel-distance window must have excluded something, otherwise the fixture tests nothing
+    assert 0 < int(s.local_mask.sum()) - 1 < s.points.shape[0]
+
+
+def test_voxel_downsample_bit_exact(world):
+    G, _, _ = world
+    assert torch.equal(O.voxel_down_sample(T(G["frames0"]), 0.4).int(), T(G["vds_04"]))
+    assert torch.equal(O.voxel_down_sample(T(G["frames0"]), 0.08).int(), T(G["vds_008"]))
+    got = O.voxel_down_sample_min_value(T(G["frames1"]), 0.4, T(G["vds_min_value_in"]))
+    assert torch.equal(got.int(), T(G["vds_min_value"]))
+
+
+@pytest.mark.parametrize("tf", [0, 1])
+def test_radius_search_bit_exact(world, tf):
+    G, s, _ = world
+    d2, idx = O.radius_search(s, T(G["queries"]), bool(tf))
+    assert torch.equal(idx.int(), T(G["rs_idx_%d" % tf]))
+    assert torch.equal(d2, T(G["rs_d2_%d" % tf]))
+
+
+def test_query_certainty(world):
+    G, s, _ = world
+    O.set_search_neighborhood(s, 1, 0.0)
+    try:
+        got = O.query_certainty(s, T(G["queries"]))
+    finally:
+        O.set_search_neighborhood(s, 2, 0.5)
+    assert torch.equal(got, T(G["query_certainty"]))
+
+
+@pytest.mark.parametrize("tag,local", [("L", True), ("G", False)])
+def test_query_sdf_grad(world, tag, local):
+    G, s, d = world
+    q = T(G["queries"])
+    fv, w, nn, qc, _ = O.query_feature(s, q, None, False, local)
+    assert torch.equal(nn.int(), T(G["nn_" + tag]))
+    assert torch.equal(fv, T(G["fv_" + tag]))
+    assert torch.equal(w, T(G["w_" + tag]))
+    assert torch.equal(qc, T(G["qc_" + tag]))
+    out = O.query_sdf(s, d, q, None, False, local, want_grad=True, want_std=True)
+    assert rel_err(out["sdf"], T(G["sdf_" + tag])) < 1e-6
+    assert rel_err(out["grad"], T(G["grad_" + tag])) < 1e-6
+    assert rel_err(out["std"], T(G["std_" + tag])) < 1e-5
+
+
+def test_gauss_newton_system(world):
+    G, _, _ = world
+    H, b, _ = O.gauss_newton_system(T(G["gn_points"]), T(G["gn_grad"]), T(G["gn_res"]), T(G["gn_w"]), 1e-4)
+    t = torch.linalg.inv(H.double()) @ b.double()
+    Tm = torch.eye(4, dtype=torch.float64)
+    Tm[:3, :3] = O.expmap(t[:3])
+    Tm[:3, 3] = t[3:]
+    assert np.allclose(Tm.numpy(), G["gn_T"], rtol=1e-9, atol=1e-12)
+
+
+def test_registration_step(world):
+    G, s, d = world
+    Tm, n_valid, res_cm, _ = O.registration_step(s, d, T(G["reg_src"]), min_grad_norm=0.0, max_grad_norm=1e3,
+                                                GM_dist=0.2, GM_grad=0.1, lm_lambda=1e-4, max_sdf_std=0.25)
+    assert n_valid == int(G["reg_valid"])
+    assert abs(res_cm - float(G["reg_res_cm"])) < 1e-6 * max(1.0, float(G["reg_res_cm"]))
+    assert np.allclose(Tm.numpy(), G["reg_T"], rtol=1e-6, atol=1e-9)
+
+
+def test_mapping_loss_and_gradients(world):
+    G, s, d = world
+    import copy
+    s2 = copy.copy(s)
+    s2.l_feats = s.l_feats.clone().requires_grad_(True)
+    s2.l_certainty = T(G["map_cert_before"]).clone()
+    s2.l_ts_update = s.l_ts_update.clone()
+    dp = O.DecoderParams(*[t.clone().requires_grad_(True) for t in d.tensors()], sdf_scale=d.sdf_scale)
+    loss, pred, _ = O.mapping_loss(s2, dp, T(G["map_coord"]), T(G["map_label"]), T(G["map_ts"]), T(G["map_weight"]))
+    loss.backward()
+    assert rel_err(pred, T(G["map_pred"])) < 1e-6
+    assert abs(float(loss) - float(G["map_loss"])) < 1e-6 * abs(float(G["map_loss"]))
+    assert rel_err(s2.l_feats.grad, T(G["map_gfeat"])) < 1e-5
+    assert rel_err(dp.W1.grad, T(G["map_gW1"])) < 1e-5
+    assert rel_err(dp.b1.grad, T(G["map_gb1"])) < 1e-5
+    assert rel_err(dp.W2.grad, T(G["map_gW2"])) < 1e-5
+    assert rel_err(dp.b2.grad, T(G["map_gb2"])) < 1e-5
+    assert rel_err(s2.l_certainty, T(G["map_cert_after"])) < 1e-6
+    assert torch.equal(s2.l_ts_update, T(G["map_ts_update_after"]))
+
+
+def test_h13_out_of_radius_candidates_map_to_local_row_1(world):
+    """Reference quirk: global2local is built with full_like(<bool>, -1).long() == 1 (neural_points.py:301)."""
+    G, s, d = world
+    import copy
+    s2 = copy.copy(s)
+    s2.p = copy.copy(s.p)
+    s2.p.local_map_radius = float(G["h13_radius"])
+    O.reset_local_map(s2, torch.tensor([6.0, 0.0, 0.0]), 2)
+    assert s2.l_points.shape[0] == int(G["h13_local_count"])
+    q = T(G["queries"])
+    fv, w, nn, qc, knn = O.query_feature(s2, q, None, False, True)
+    assert torch.equal(nn.int(), T(G["h13_nn"]))
+    assert torch.equal(fv, T(G["h13_fv"])) and torch.equal(w, T(G["h13_w"])) and torch.equal(qc, T(G["h13_qc"]))
+    # the quirk must actually fire in this fixture: some neighbour vector is far longer than the search radius
+    assert float(fv[..., 8:].norm(dim=-1).max()) > 3.0
+    out = O.query_sdf(s2, d, q, None, False, True, want_grad=True)
+    assert rel_err(out["sdf"], T(G["h13_sdf"])) < 1e-6
+    assert rel_err(out["grad"], T(G["h13_grad"])) < 1e-6
