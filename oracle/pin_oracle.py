@@ -160,6 +160,20 @@ def _argmin_per_key(key: torch.Tensor, q: torch.Tensor) -> torch.Tensor:
     return best % pack_base
 
 
+def put_last_wins(table: torch.Tensor, index: torch.Tensor, values: torch.Tensor) -> None:
+    """``table[index] = values`` with the semantics of a SEQUENTIAL index_put_: among duplicate indices the
+    highest batch position wins (hazard H4).  The reference relies on ATen's CPU index_put_, which is only
+    sequential on one thread -- with several threads (and on CUDA) duplicate slots race and the reference's
+    own result varies from run to run (observed: 2-12 differing slots out of 17 k on an 8-thread run of the
+    golden scenario).  The oracle, the golden vectors (generated with one thread) and the CUDA kernels all
+    implement the deterministic single-thread outcome."""
+    index = torch.where(index < 0, index + table.shape[0], index)
+    uniq, inv = torch.unique(index, return_inverse=True)
+    pos = torch.arange(index.shape[0], dtype=I64)
+    last = torch.full(uniq.shape, -1, dtype=I64).scatter_reduce_(0, inv, pos, reduce="amax", include_self=True)
+    table[uniq] = values[last]
+
+
 # --------------------------------------------------------------------------------------
 # map maintenance
 # --------------------------------------------------------------------------------------
@@ -181,7 +195,7 @@ def map_update(s: MapState, points: torch.Tensor, sensor_position: torch.Tensor,
     m0 = s.points.shape[0]
     val = s.table[h]
     val[upd] = torch.arange(n_new, dtype=I64) + m0
-    s.table[h] = val                                                     # sequential: last writer wins (H4)
+    put_last_wins(s.table, h, val)                                       # sequential: last writer wins (H4)
     s.points = torch.cat((s.points, added), 0)
     ident = torch.zeros((n_new, 4))
     ident[:, 0] = 1.0
@@ -240,7 +254,7 @@ def recreate_hash(s: MapState, sensor_position, kept_points: bool = True, with_t
         keep = voxel_down_sample_min_value(s.points, res, -s.certainty)
     if kept_points:
         h = signed_hash(cells_of(s.points[keep], res), s.p.buffer_size)
-        s.table[h] = keep
+        put_last_wins(s.table, h, keep)
     else:
         s.points = s.points[keep]
         s.quats = s.quats[keep]
@@ -249,7 +263,7 @@ def recreate_hash(s: MapState, sensor_position, kept_points: bool = True, with_t
         s.certainty = s.certainty[keep]
         s.feats = s.feats[torch.cat((keep, torch.tensor([-1])))]
         h = signed_hash(cells_of(s.points, res), s.p.buffer_size)
-        s.table[h] = torch.arange(s.points.shape[0], dtype=I64)
+        put_last_wins(s.table, h, torch.arange(s.points.shape[0], dtype=I64))
     if sensor_position is not None:
         reset_local_map(s, sensor_position, cur_ts)
 
