@@ -22,7 +22,7 @@ from .tools import get_time, setup_optimizer, transform_torch
 
 
 class Mapper:
-    def __init__(self, config, dataset, neural_points, geo_mlp, sem_mlp=None, color_mlp=None):
+    def __init__(self, config, dataset, neural_points, geo_mlp, sem_mlp, color_mlp):
         self.config = config
         self.silence = config.silence
         self.dataset = dataset

@@ -18,7 +18,7 @@ from .. import _pinq as P
 
 
 class Tracker:
-    def __init__(self, config, neural_points, geo_decoder, sem_decoder=None, color_decoder=None):
+    def __init__(self, config, neural_points, geo_decoder, sem_decoder, color_decoder):
         self.config = config
         self.silence = config.silence
         self.neural_points = neural_points
