@@ -298,13 +298,16 @@ def main():
     nnc = torch.empty(n, dtype=torch.int32, device=dev)
     knn_idx = torch.empty((n, K), dtype=torch.int32, device=dev)
     knn_w = torch.empty((n, K), device=dev)
+    relu_mask = torch.empty(int(lib.pinq_relu_mask_words(n)), dtype=torch.int32, device=dev)
     a.sdf, a.nn_count, a.knn_idx, a.knn_w = P.ptr(sdf), P.ptr(nnc), P.ptr(knn_idx), P.ptr(knn_w)
+    a.relu_mask = P.ptr(relu_mask)
     b = P.BwdArgs()
     b.dec = dec.view()
     b.xyz, b.n, b.flags, b.k, b.feature_dim = P.ptr(q), n, 0, K, 8
     b.point_xyz = P.ptr(npts.local_neural_points.contiguous())
     b.features = P.ptr(npts.local_geo_features.detach())
     b.knn_idx, b.knn_w, b.grad_sdf = P.ptr(knn_idx), P.ptr(knn_w), P.ptr(ones)
+    b.relu_mask = P.ptr(relu_mask)
     gf = torch.zeros_like(npts.local_geo_features)
     gd = [torch.zeros_like(p) for p in dec.fused_params()]
     b.grad_features = P.ptr(gf)

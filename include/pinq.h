@@ -173,10 +173,14 @@ typedef struct pinq_query_args {
     int32_t* knn_idx;          /* [n,k] top-k index (local or global), -1 invalid                    */
     float* knn_w;              /* [n,k] normalised IDW weights                                       */
     float* knn_d2;             /* [n,k] squared distances (9e3 invalid)                              */
+    uint32_t* relu_mask;       /* pinq_relu_mask_words(n) words or NULL: relu'(pre) of the hidden layer,
+                                  one bit per (query, neighbour, hidden unit) in tensor-core fragment
+                                  order; saved for pinq_query_fused_bwd (48 B/query, opaque)          */
     void* workspace;           /* pinq_query_workspace_bytes(n) bytes: search -> decode hand-off      */
 } pinq_query_args;
 
 int64_t pinq_query_workspace_bytes(int64_t n);
+int64_t pinq_relu_mask_words(int64_t n);
 
 /* neural_points.py:528-674 + decoder.py:66-88 + the weighted combine, in one pass.
  * Supported specialisation: k=6, feature_dim=8, hidden=64, one hidden level, weighted_first=False. */
@@ -197,6 +201,7 @@ typedef struct pinq_bwd_args {
     const float* features;     /* [Mx+1,F]                                                 */
     const int32_t* knn_idx;    /* [n,k] saved by the forward                               */
     const float* knn_w;        /* [n,k]                                                    */
+    const uint32_t* relu_mask; /* pinq_relu_mask_words(n), saved by the forward            */
     const float* grad_sdf;     /* [n] dL/dsdf                                              */
     float* grad_features;      /* [Mx+1,F] accumulated (+=), may be NULL                   */
     float* grad_W1;            /* [H,F+3] accumulated, NULL when the decoder is frozen (H11) */

@@ -1,0 +1,136 @@
+// mma.cuh -- warp-level tensor-core building blocks of the decoder kernels.
+//
+// The 11 -> 64 -> 1 decoder (model/decoder.py:66-88) evaluated for 6 neighbours of 32 queries is a
+// [192 x 12] x [12 x 64] product per warp; ncu showed the FP32-FMA formulation pipe-bound (profiles/r1c_*),
+// so the three contractions of the path run on the tensor cores with fp32-equivalent accuracy:
+//   layer 1      pre  = [f_k, v_k, 1] W1b^T          3xTF32 (hi*hi + hi*lo + lo*hi), m16n8k8
+//   mask x V     d s_k / d in_k = relu'(pre) (W2 . W1)   the mask is exact in bf16, V split in 3 bf16, m16n8k16
+//   mask^T x X   decoder gradients (reduction over rows)  mask exact, X = a_k in_k split in 3 bf16, m16n8k16
+// Everything stays in registers: the layer-1 accumulator fragment IS the A fragment of the mask products
+// (same trick as the P.V product of fused attention), so the hidden layer never touches memory.
+//
+// Fragment coordinates (PTX ISA, mma.m16n8k8 / m16n8k16): g = lane >> 2, t = lane & 3.
+//   C (16x8 f32)      c0 (g, 2t)  c1 (g, 2t+1)  c2 (g+8, 2t)  c3 (g+8, 2t+1)
+//   A tf32 (16x8)     a0 (g, t)   a1 (g+8, t)   a2 (g, t+4)   a3 (g+8, t+4)
+//   B tf32 (8x8)      b0 (k=t, n=g)   b1 (k=t+4, n=g)
+//   A bf16 (16x16)    a0 (g, 2t..2t+1)  a1 (g+8, 2t..)  a2 (g, 2t+8..)  a3 (g+8, 2t+8..)   (low half = lower k)
+//   B bf16 (16x8)     b0 (k=2t..2t+1, n=g)   b1 (k=2t+8..2t+9, n=g)
+#pragma once
+#include <cuda_bf16.h>
+
+#include "query_common.cuh"
+
+namespace pinq {
+
+__device__ __forceinline__ uint32_t tf32_rna(float x) {
+    uint32_t r;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+    return r;
+}
+// x = hi + lo + O(2^-22 |x|), both exactly representable in tf32
+__device__ __forceinline__ void tf32_split(float x, uint32_t& hi, uint32_t& lo) {
+    hi = tf32_rna(x);
+    lo = tf32_rna(x - __uint_as_float(hi));
+}
+
+// x = b1 + b2 + b3 + O(2^-24 |x|)
+__device__ __forceinline__ void bf16_split3(float x, __nv_bfloat16& b1, __nv_bfloat16& b2, __nv_bfloat16& b3) {
+    b1 = __float2bfloat16_rn(x);
+    const float r1 = x - __bfloat162float(b1);
+    b2 = __float2bfloat16_rn(r1);
+    const float r2 = r1 - __bfloat162float(b2);
+    b3 = __float2bfloat16_rn(r2);
+}
+__device__ __forceinline__ uint32_t pack_bf16(__nv_bfloat16 lo, __nv_bfloat16 hi) {
+    return (uint32_t)__bfloat16_as_ushort(lo) | ((uint32_t)__bfloat16_as_ushort(hi) << 16);
+}
+
+__device__ __forceinline__ void mma_tf32(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0,
+                                         uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+                 : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ void mma_bf16(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0,
+                                         uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+                 : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+// transpose of an 8x8 b16 matrix held one 32-bit register per lane (row g, columns 2t..2t+1)
+__device__ __forceinline__ uint32_t movmatrix_trans(uint32_t a) {
+    uint32_t d;
+    asm volatile("movmatrix.sync.aligned.m8n8.trans.b16 %0, %1;" : "=r"(d) : "r"(a));
+    return d;
+}
+
+constexpr int kRowsPerWarp = 32 * K;  // 192 rows = 12 m-tiles of 16
+constexpr int kMTiles = kRowsPerWarp / 16;
+constexpr uint32_t kBf16One = 0x3F80u;
+
+// Decoder operands in fragment order, built once per CTA in shared memory.
+struct DecFrags {
+    float4 w1a[8][32];    // layer 1, k-step 0 (inputs 0..7):  {hi B[t][j], hi B[t+4][j], lo B[t][j], lo B[t+4][j]}, j = 8 nt + g
+    float2 w1b[8][32];    // layer 1, k-step 1 (inputs 8..11): {hi B[8+t][j], lo B[8+t][j]}   (B[11][j] = b1[j], B[12..15] = 0)
+    float2 w2[32];        // {W2[2i], W2[2i+1]}
+    uint2 vf[4][3][32];   // mask x V, columns = feature inputs 0..7:   split s of {V[16p+2t..][g], V[16p+2t+8..][g]}
+    uint2 vv[4][3][32];   // mask x V, columns = inputs 8..10 (x - p_k), zero-padded to 8
+};
+
+// B[i][j] of layer 1: W1[j][i] for i < 11, b1[j] for i = 11
+__device__ __forceinline__ float l1_operand(const pinq_decoder_view& d, int i, int j) {
+    return i < IN ? d.W1[j * IN + i] : (i == IN ? d.b1[j] : 0.f);
+}
+
+__device__ __forceinline__ void build_dec_frags(const pinq_decoder_view& d, DecFrags* s, bool want_l1, bool want_vf,
+                                                bool want_vv) {
+    for (int e = threadIdx.x; e < 8 * 32; e += blockDim.x) {
+        const int nt = e >> 5, lane = e & 31, g = lane >> 2, t = lane & 3, j = 8 * nt + g;
+        if (want_l1) {
+            uint32_t h0, l0, h1, l1, h2, l2;
+            tf32_split(l1_operand(d, t, j), h0, l0);
+            tf32_split(l1_operand(d, t + 4, j), h1, l1);
+            tf32_split(l1_operand(d, t + 8, j), h2, l2);
+            s->w1a[nt][lane] = make_float4(__uint_as_float(h0), __uint_as_float(h1), __uint_as_float(l0), __uint_as_float(l1));
+            s->w1b[nt][lane] = make_float2(__uint_as_float(h2), __uint_as_float(l2));
+        }
+    }
+    for (int e = threadIdx.x; e < 32; e += blockDim.x) s->w2[e] = make_float2(d.W2[2 * e], d.W2[2 * e + 1]);
+    for (int e = threadIdx.x; e < 4 * 32; e += blockDim.x) {
+        const int p = e >> 5, lane = e & 31, g = lane >> 2, t = lane & 3;
+#pragma unroll
+        for (int which = 0; which < 2; ++which) {
+            if (which == 0 ? !want_vf : !want_vv) continue;
+            const int col = which == 0 ? g : 8 + g;  // decoder input column this lane's n index maps to
+            __nv_bfloat16 sp[4][3];
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+                const int j = 16 * p + 2 * t + (r & 1) + 8 * (r >> 1);
+                const float v = col < IN ? d.W2[j] * d.W1[j * IN + col] : 0.f;
+                bf16_split3(v, sp[r][0], sp[r][1], sp[r][2]);
+            }
+#pragma unroll
+            for (int sidx = 0; sidx < 3; ++sidx) {
+                const uint2 v = make_uint2(pack_bf16(sp[0][sidx], sp[1][sidx]), pack_bf16(sp[2][sidx], sp[3][sidx]));
+                if (which == 0) s->vf[p][sidx][lane] = v;
+                else s->vv[p][sidx][lane] = v;
+            }
+        }
+    }
+}
+
+// relu'(pre) of one 16-row m-tile as bf16 A fragments (4 k-steps of 16 hidden units), from the bit mask
+// bit (4 nt + c) <-> accumulator acc[nt][c]
+__device__ __forceinline__ void mask_frags(uint32_t bits, uint32_t (&a)[4][4]) {
+#pragma unroll
+    for (int p = 0; p < 4; ++p) {
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+            const int nt = 2 * p + (r >> 1), c = 2 * (r & 1);  // r: 0 (g, lo n-tile) 1 (g+8, lo) 2 (g, hi) 3 (g+8, hi)
+            const uint32_t lo = (bits >> (4 * nt + c)) & 1u, hi = (bits >> (4 * nt + c + 1)) & 1u;
+            a[p][r] = (lo ? kBf16One : 0u) | (hi ? (kBf16One << 16) : 0u);
+        }
+    }
+}
+
+}  // namespace pinq

@@ -8,7 +8,7 @@
 //              FP32-FMA bound; the decoder lives in shared memory, activations in registers.
 // Reference: model/neural_points.py:459-674, model/decoder.py:66-88, utils/tracker.py:245-253,
 //            utils/mapper.py:466-468, utils/mesher.py:93-180.
-#include "query_common.cuh"
+#include "mma.cuh"
 
 namespace pinq {
 
@@ -116,165 +116,291 @@ struct DecodeParams {
     float* certainty;
     int32_t* knn_idx;
     float *knn_w, *knn_d2;
-    float* feat_out;  // MODE 1: [n,K,IN]
-    int min_nn;       // MODE 2
+    uint32_t* relu_mask;  // [ceil(n/32)][12][32] bit masks of relu'(pre), fragment order (consumed by the backward)
+    float* feat_out;      // un-fused query_feature: [n,K,IN]
+    int min_nn;           // mesher
     uint8_t* mask_out;
 };
 
-// MODE 0: fused decode   MODE 1: un-fused query_feature (no MLP)   MODE 2: mesher grid (forward only)
-template <bool GRAD, int MODE>
-__global__ void __launch_bounds__(kBlock) k_decode(const DecodeParams p) {
-    __shared__ __align__(16) float4 s_w[MODE == 1 ? 1 : H * 4];
-    if (MODE != 1) {
-        load_decoder(p.dec, s_w);
-        __syncthreads();
-    }
-    const int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (q >= p.n) return;
-    float x, y, z;
-    load_point(p.src, q, x, y, z);
-
-    const int32_t* wsq = p.ws + q * kWs;
-    const int nn = wsq[K];
+// Per-query part shared by the fused decode and the un-fused query_feature: resolve the K record ranks
+// to (index, d^2, x - p_k), IDW weights, API outputs and the training-mode side effects.
+struct QueryLane {
     int32_t kidx[K];
-    float kd2[K];
-    float in[K][IN];
-    float ux[K], uy[K], uz[K];  // un-rotated x - p_k, needed by the IDW gradient
+    float kd2[K], w[K], wt[K], wsum;
+    float vx[K], vy[K], vz[K];  // decoder inputs 8..10 (rotated into the point frame when after_pgo)
+    float ux[K], uy[K], uz[K];  // un-rotated x - p_k of the TRUE candidate position (IDW gradient)
+    int nn;
+};
+
+template <bool WANT_U>
+__device__ __forceinline__ void resolve_query(const DecodeParams& p, int64_t q, bool live, float x, float y, float z,
+                                              QueryLane& L) {
+    L.nn = 0;
 #pragma unroll
     for (int k = 0; k < K; ++k) {
-        kidx[k] = -1;
-        kd2[k] = kInvalidD2;
-        ux[k] = uy[k] = uz[k] = 0.f;
+        L.kidx[k] = -1;
+        L.kd2[k] = kInvalidD2;
+        L.vx[k] = L.vy[k] = L.vz[k] = 0.f;
+        if (WANT_U) L.ux[k] = L.uy[k] = L.uz[k] = 0.f;
+    }
+    if (live) {
+        const int32_t* wsq = p.ws + q * kWs;
+        L.nn = wsq[K];
+        int32_t r[K];
 #pragma unroll
-        for (int i = 0; i < IN; ++i) in[k][i] = 0.f;
-        const int32_t r = wsq[k];
-        if (r >= 0) {
-            const float4 rc = __ldg(&p.rec[r]);
-            int32_t li = __float_as_int(rc.w);
-            float px = rc.x, py = rc.y, pz = rc.z;
-            kd2[k] = dist2_rn(rc.x, rc.y, rc.z, x, y, z);  // same ops as the search -> same bits
+        for (int k = 0; k < K; ++k) r[k] = wsq[k];
+        float4 rc[K];
+#pragma unroll
+        for (int k = 0; k < K; ++k)
+            if (r[k] >= 0) rc[k] = __ldg(&p.rec[r[k]]);
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+            if (r[k] < 0) continue;
+            int32_t li = __float_as_int(rc[k].w);
+            float px = rc[k].x, py = rc[k].y, pz = rc[k].z;
+            L.kd2[k] = dist2_rn(rc[k].x, rc[k].y, rc[k].z, x, y, z);  // same ops as the search -> same bits
             if (li == -2) {  // hazard H13: candidate outside the local map -> the reference gathers local row 1
                 li = 1;
                 px = p.point_xyz[3]; py = p.point_xyz[4]; pz = p.point_xyz[5];
             }
-            kidx[k] = li;
-            const float4* fr = reinterpret_cast<const float4*>(p.features + (int64_t)li * F);
-            const float4 a = __ldg(fr), b = __ldg(fr + 1);
-            in[k][0] = a.x; in[k][1] = a.y; in[k][2] = a.z; in[k][3] = a.w;
-            in[k][4] = b.x; in[k][5] = b.y; in[k][6] = b.z; in[k][7] = b.w;
+            L.kidx[k] = li;
             float vx = __fsub_rn(x, px), vy = __fsub_rn(y, py), vz = __fsub_rn(z, pz);
-            // the IDW weights (and their x-gradient) come from the TRUE candidate position
-            ux[k] = __fsub_rn(x, rc.x); uy[k] = __fsub_rn(y, rc.y); uz[k] = __fsub_rn(z, rc.z);
+            if (WANT_U) {  // the IDW weights (and their x-gradient) come from the TRUE candidate position
+                L.ux[k] = __fsub_rn(x, rc[k].x); L.uy[k] = __fsub_rn(y, rc[k].y); L.uz[k] = __fsub_rn(z, rc[k].z);
+            }
             if (p.rotate) quat_rotate(__ldg(&p.quats[li]), false, vx, vy, vz);
-            in[k][8] = vx; in[k][9] = vy; in[k][10] = vz;
+            L.vx[k] = vx; L.vy[k] = vy; L.vz[k] = vz;
         }
     }
-
-    float wt[K], w[K], wsum;
-    idw_weights(kd2, kidx, nn, wt, w, wsum);
-
-    if (p.nn_count) p.nn_count[q] = nn;
+    idw_weights(L.kd2, L.kidx, L.nn, L.wt, L.w, L.wsum);
+    if (!live) return;
+    if (p.nn_count) p.nn_count[q] = L.nn;
     if (p.knn_idx) {
 #pragma unroll
-        for (int k = 0; k < K; ++k) p.knn_idx[q * K + k] = kidx[k];
+        for (int k = 0; k < K; ++k) p.knn_idx[q * K + k] = L.kidx[k];
     }
     if (p.knn_w) {
 #pragma unroll
-        for (int k = 0; k < K; ++k) p.knn_w[q * K + k] = w[k];
+        for (int k = 0; k < K; ++k) p.knn_w[q * K + k] = L.w[k];
     }
     if (p.knn_d2) {
 #pragma unroll
-        for (int k = 0; k < K; ++k) p.knn_d2[q * K + k] = kd2[k];
+        for (int k = 0; k < K; ++k) p.knn_d2[q * K + k] = L.kd2[k];
     }
     if (p.certainty) {  // sum_k w_k c_k, neural_points.py:651-656
         float c = 0.f;
 #pragma unroll
         for (int k = 0; k < K; ++k)
-            if (kidx[k] >= 0) c += p.certainties[kidx[k]] * w[k];
+            if (L.kidx[k] >= 0) c += p.certainties[L.kidx[k]] * L.w[k];
         p.certainty[q] = c;
     }
     if (p.scatter_in_kernel) {  // training side effects, neural_points.py:637-648 (hazard H9)
         const long long ts = p.query_ts ? (long long)p.query_ts[q] : 0;
 #pragma unroll
         for (int k = 0; k < K; ++k) {
-            if (kidx[k] >= 0) {
-                atomicAdd(&p.certainties[kidx[k]], w[k]);
-                if (p.query_ts && p.ts_update) atomicMax(&p.ts_update[kidx[k]], ts);
+            if (L.kidx[k] >= 0) {
+                atomicAdd(&p.certainties[L.kidx[k]], L.w[k]);
+                if (p.query_ts && p.ts_update) atomicMax(&p.ts_update[L.kidx[k]], ts);
             }
         }
     }
+}
 
-    if (MODE == 1) {
-        float* o = p.feat_out + q * (K * IN);
-#pragma unroll
-        for (int k = 0; k < K; ++k)
-#pragma unroll
-            for (int i = 0; i < IN; ++i) o[k * IN + i] = in[k][i];
-        return;
-    }
-    if (MODE == 2) {
-        if (p.mask_out) p.mask_out[q] = (uint8_t)(nn >= p.min_nn);
-        if (nn == 0) {  // MLP skipped where nothing is near (mesher.py:96-103)
-            p.sdf[q] = 0.f;
-            return;
-        }
-    }
-
-    // MLP.  acc[k] = sum_j W2[j] relu(pre_kj);  gv[k] = sum_j W2[j] 1[pre>0] W1[j][8..10]
-    float acc[K];
-    float gvx[K], gvy[K], gvz[K];
-#pragma unroll
-    for (int k = 0; k < K; ++k) acc[k] = gvx[k] = gvy[k] = gvz[k] = 0.f;
-#pragma unroll 2
-    for (int j = 0; j < H; ++j) {
-        const float4 wa = s_w[4 * j], wb = s_w[4 * j + 1], wc = s_w[4 * j + 2], wd = s_w[4 * j + 3];
-#pragma unroll
-        for (int k = 0; k < K; ++k) {
-            const float pre = mlp_pre(in[k], wa, wb, wc);
-            acc[k] = fmaf(fmaxf(pre, 0.f), wd.x, acc[k]);
-            if (GRAD) {
-                const float m = pre > 0.f ? wd.x : 0.f;
-                gvx[k] = fmaf(m, wc.x, gvx[k]);
-                gvy[k] = fmaf(m, wc.y, gvy[k]);
-                gvz[k] = fmaf(m, wc.z, gvz[k]);
-            }
-        }
-    }
-    const float b2 = __ldg(p.dec.b2), scale = p.dec.sdf_scale;
-    float s[K], sdf = 0.f;
+// Un-fused API form (model/neural_points.py:574-632): writes the [n,K,F+3] feature tensor, no MLP.
+__global__ void __launch_bounds__(kBlock) k_query_feature(const DecodeParams p) {
+    const int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= p.n) return;
+    float x, y, z;
+    load_point(p.src, q, x, y, z);
+    QueryLane L;
+    resolve_query<false>(p, q, true, x, y, z, L);
+    float* o = p.feat_out + q * (K * IN);
 #pragma unroll
     for (int k = 0; k < K; ++k) {
-        s[k] = (acc[k] + b2) * scale;  // decoder.py:80-81
-        sdf = fmaf(s[k], w[k], sdf);
-    }
-    if (p.sdf) p.sdf[q] = sdf;
-    if (p.sdf_std) {  // tracker.py:246-247
-        float var = 0.f;
-#pragma unroll
-        for (int k = 0; k < K; ++k) {
-            const float d = s[k] - sdf;
-            var = fmaf(w[k], d * d, var);
+        float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
+        if (L.kidx[k] >= 0) {
+            const float4* fr = reinterpret_cast<const float4*>(p.features + (int64_t)L.kidx[k] * F);
+            a = __ldg(fr);
+            b = __ldg(fr + 1);
         }
-        p.sdf_std[q] = sqrtf(var);
+        float* ok = o + k * IN;
+        ok[0] = a.x; ok[1] = a.y; ok[2] = a.z; ok[3] = a.w;
+        ok[4] = b.x; ok[5] = b.y; ok[6] = b.z; ok[7] = b.w;
+        ok[8] = L.vx[k]; ok[9] = L.vy[k]; ok[10] = L.vz[k];
     }
-    if (GRAD && p.grad_x) {
-        // d sdf/dx = sum_k w_k R_k^T (ds_k/dv_k) + (1/S) sum_k (s_k - sdf) d wt_k/dx,  d wt_k/dx = -2 wt_k^2 (x - p_k)
-        float gx = 0.f, gy = 0.f, gz = 0.f;
-        const float inv_s = 1.0f / wsum;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Fused decode on the tensor cores.  One warp owns 32 queries = 192 (query, neighbour) rows = 12 m-tiles:
+// m-tile mt = 2 k + half holds neighbour k of queries 16 half + {g, g + 8}.
+//   phase A  lane = query : resolve ranks, IDW weights, side effects; stage (index, x - p_k) per row
+//   phase B  lane = (g,t) : A fragments straight from the feature table (each quad reads one 32-byte row),
+//                           3xTF32 layer 1, relu . W2 in the accumulator layout, relu' mask -> saved bits
+//                           (+ mask x V product for d s_k / d v_k when the gradient is wanted)
+//   phase C  lane = query : weighted combine, std, d sdf/dx, outputs
+template <bool GRAD>
+struct WarpStage {
+    float4 vb[K][32];  // {vx, vy, vz, 1}: decoder inputs 8..11 of row (k, query)
+    int32_t li[K][32];
+    float sk[K][32];   // sum_j W2[j] relu(pre_j) of row (k, query)
+    float4 gv[GRAD ? K : 1][32];
+};
+
+template <bool GRAD, bool MESH>
+__global__ void __launch_bounds__(kBlock, GRAD ? 3 : 4) k_decode_mma(const DecodeParams p) {
+    extern __shared__ __align__(16) unsigned char s_raw[];
+    DecFrags* fr = reinterpret_cast<DecFrags*>(s_raw);
+    WarpStage<GRAD>* stages = reinterpret_cast<WarpStage<GRAD>*>(s_raw + sizeof(DecFrags));
+    build_dec_frags(p.dec, fr, true, false, GRAD);
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane >> 2, t = lane & 3;
+    WarpStage<GRAD>& st = stages[warp];
+    const float b2 = __ldg(p.dec.b2), scale = p.dec.sdf_scale;
+    const int64_t nblocks = (p.n + kBlock - 1) / kBlock;
+
+    for (int64_t blk = blockIdx.x; blk < nblocks; blk += gridDim.x) {
+        const int64_t q0 = blk * kBlock + warp * 32;  // first query of this warp
+        if (q0 >= p.n) continue;                      // warp-uniform
+        const int64_t q = q0 + lane;
+        const bool live = q < p.n;
+        float x = 0.f, y = 0.f, z = 0.f;
+        if (live) load_point(p.src, q, x, y, z);
+        QueryLane L;
+        resolve_query<GRAD>(p, q, live, x, y, z, L);
+        __syncwarp();  // the previous iteration's phase C reads are done
 #pragma unroll
         for (int k = 0; k < K; ++k) {
-            if (kidx[k] >= 0) {
-                float ax = gvx[k] * scale, ay = gvy[k] * scale, az = gvz[k] * scale;
-                if (p.rotate) quat_rotate(__ldg(&p.quats[kidx[k]]), true, ax, ay, az);
-                const float c = (s[k] - sdf) * (-2.f * wt[k] * wt[k]) * inv_s;
-                gx += w[k] * ax + c * ux[k];
-                gy += w[k] * ay + c * uy[k];
-                gz += w[k] * az + c * uz[k];
+            st.vb[k][lane] = make_float4(L.vx[k], L.vy[k], L.vz[k], 1.f);
+            st.li[k][lane] = L.kidx[k];
+        }
+        __syncwarp();
+
+        // ---- phase B ----
+#pragma unroll 1
+        for (int mt = 0; mt < kMTiles; ++mt) {
+            const int k = mt >> 1, half = mt & 1;
+            const int qa = 16 * half + g, qb = qa + 8;
+            const int la = st.li[k][qa], lb = st.li[k][qb];
+            const bool any = __any_sync(0xffffffffu, (la >= 0) | (lb >= 0));
+            uint32_t bits = 0;
+            float sA = 0.f, sB = 0.f, c2[4] = {0.f, 0.f, 0.f, 0.f};
+            if (any) {  // warp-uniform: tiles without a single valid neighbour carry weight 0 everywhere
+                float raw[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+                if (la >= 0) {
+                    const float* f = p.features + (int64_t)la * F;
+                    raw[0] = __ldg(f + t); raw[2] = __ldg(f + t + 4);
+                }
+                if (lb >= 0) {
+                    const float* f = p.features + (int64_t)lb * F;
+                    raw[1] = __ldg(f + t); raw[3] = __ldg(f + t + 4);
+                }
+                raw[4] = reinterpret_cast<const float*>(&st.vb[k][qa])[t];
+                raw[5] = reinterpret_cast<const float*>(&st.vb[k][qb])[t];
+                uint32_t ah[6], al[6];
+#pragma unroll
+                for (int i = 0; i < 6; ++i) tf32_split(raw[i], ah[i], al[i]);
+                float acc[8][4];
+#pragma unroll
+                for (int nt = 0; nt < 8; ++nt) {
+                    acc[nt][0] = acc[nt][1] = acc[nt][2] = acc[nt][3] = 0.f;
+                    const float4 wa = fr->w1a[nt][lane];
+                    const float2 wb = fr->w1b[nt][lane];
+                    const uint32_t bh0 = __float_as_uint(wa.x), bh1 = __float_as_uint(wa.y);
+                    const uint32_t bl0 = __float_as_uint(wa.z), bl1 = __float_as_uint(wa.w);
+                    const uint32_t ch = __float_as_uint(wb.x), cl = __float_as_uint(wb.y);
+                    // small terms first: lo*hi, hi*lo, then hi*hi
+                    mma_tf32(acc[nt], al[0], al[1], al[2], al[3], bh0, bh1);
+                    mma_tf32(acc[nt], al[4], al[5], 0u, 0u, ch, 0u);
+                    mma_tf32(acc[nt], ah[0], ah[1], ah[2], ah[3], bl0, bl1);
+                    mma_tf32(acc[nt], ah[4], ah[5], 0u, 0u, cl, 0u);
+                    mma_tf32(acc[nt], ah[0], ah[1], ah[2], ah[3], bh0, bh1);
+                    mma_tf32(acc[nt], ah[4], ah[5], 0u, 0u, ch, 0u);
+                }
+#pragma unroll
+                for (int nt = 0; nt < 8; ++nt) {
+                    const float2 w2 = fr->w2[4 * nt + t];
+                    sA = fmaf(fmaxf(acc[nt][0], 0.f), w2.x, sA);
+                    sA = fmaf(fmaxf(acc[nt][1], 0.f), w2.y, sA);
+                    sB = fmaf(fmaxf(acc[nt][2], 0.f), w2.x, sB);
+                    sB = fmaf(fmaxf(acc[nt][3], 0.f), w2.y, sB);
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) bits |= (acc[nt][c] > 0.f ? 1u : 0u) << (4 * nt + c);
+                }
+                sA += __shfl_xor_sync(0xffffffffu, sA, 1);
+                sB += __shfl_xor_sync(0xffffffffu, sB, 1);
+                sA += __shfl_xor_sync(0xffffffffu, sA, 2);
+                sB += __shfl_xor_sync(0xffffffffu, sB, 2);
+                if (GRAD) {  // d s_k / d v_k = sum_j relu'(pre_j) W2[j] W1[j][8..10]
+                    uint32_t am[4][4];
+                    mask_frags(bits, am);
+#pragma unroll
+                    for (int s = 2; s >= 0; --s)
+#pragma unroll
+                        for (int pp = 0; pp < 4; ++pp) {
+                            const uint2 bv = fr->vv[pp][s][lane];
+                            mma_bf16(c2, am[pp][0], am[pp][1], am[pp][2], am[pp][3], bv.x, bv.y);
+                        }
+                }
+            }
+            if (t == 0) {
+                st.sk[k][qa] = sA;
+                st.sk[k][qb] = sB;
+            }
+            if (GRAD) {
+                float* ga = reinterpret_cast<float*>(&st.gv[k][qa]);
+                float* gb = reinterpret_cast<float*>(&st.gv[k][qb]);
+                if (t == 0) { ga[0] = c2[0]; ga[1] = c2[1]; gb[0] = c2[2]; gb[1] = c2[3]; }
+                if (t == 1) { ga[2] = c2[0]; gb[2] = c2[2]; }
+            }
+            if (p.relu_mask) p.relu_mask[((q0 >> 5) * kMTiles + mt) * 32 + lane] = bits;
+        }
+        __syncwarp();
+
+        // ---- phase C ----
+        if (!live) continue;
+        if (MESH) {
+            if (p.mask_out) p.mask_out[q] = (uint8_t)(L.nn >= p.min_nn);
+            if (L.nn == 0) {  // MLP result unused where nothing is near (mesher.py:96-103)
+                p.sdf[q] = 0.f;
+                continue;
             }
         }
-        p.grad_x[3 * q] = gx;
-        p.grad_x[3 * q + 1] = gy;
-        p.grad_x[3 * q + 2] = gz;
+        float s[K], sdf = 0.f;
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+            s[k] = (st.sk[k][lane] + b2) * scale;  // decoder.py:80-81
+            sdf = fmaf(s[k], L.w[k], sdf);
+        }
+        if (p.sdf) p.sdf[q] = sdf;
+        if (p.sdf_std) {  // tracker.py:246-247
+            float var = 0.f;
+#pragma unroll
+            for (int k = 0; k < K; ++k) {
+                const float d = s[k] - sdf;
+                var = fmaf(L.w[k], d * d, var);
+            }
+            p.sdf_std[q] = sqrtf(var);
+        }
+        if (GRAD && p.grad_x) {
+            // d sdf/dx = sum_k w_k R_k^T (ds_k/dv_k) + (1/S) sum_k (s_k - sdf) d wt_k/dx,  d wt_k/dx = -2 wt_k^2 (x - p_k)
+            float gx = 0.f, gy = 0.f, gz = 0.f;
+            const float inv_s = 1.0f / L.wsum;
+#pragma unroll
+            for (int k = 0; k < K; ++k) {
+                if (L.kidx[k] >= 0) {
+                    const float4 gvk = st.gv[k][lane];
+                    float ax = gvk.x * scale, ay = gvk.y * scale, az = gvk.z * scale;
+                    if (p.rotate) quat_rotate(__ldg(&p.quats[L.kidx[k]]), true, ax, ay, az);
+                    const float c = (s[k] - sdf) * (-2.f * L.wt[k] * L.wt[k]) * inv_s;
+                    gx += L.w[k] * ax + c * L.ux[k];
+                    gy += L.w[k] * ay + c * L.uy[k];
+                    gz += L.w[k] * az + c * L.uz[k];
+                }
+            }
+            p.grad_x[3 * q] = gx;
+            p.grad_x[3 * q + 1] = gy;
+            p.grad_x[3 * q + 2] = gz;
+        }
     }
 }
 
@@ -342,11 +468,19 @@ static int run_query(const pinq_query_args* a, int mode, float* feat_out, const 
     p.sdf = a->sdf; p.grad_x = a->grad_x; p.sdf_std = a->sdf_std; p.nn_count = a->nn_count;
     p.certainty = a->certainty; p.knn_idx = a->knn_idx; p.knn_w = a->knn_w; p.knn_d2 = a->knn_d2;
     p.feat_out = feat_out; p.min_nn = min_nn; p.mask_out = mask_out;
-    const unsigned g = grid_for(n, kBlock);
-    if (mode == 1) k_decode<false, 1><<<g, kBlock, 0, st>>>(p);
-    else if (mode == 2) k_decode<false, 2><<<g, kBlock, 0, st>>>(p);
-    else if (a->grad_x) k_decode<true, 0><<<g, kBlock, 0, st>>>(p);
-    else k_decode<false, 0><<<g, kBlock, 0, st>>>(p);
+    p.relu_mask = reinterpret_cast<uint32_t*>(a->relu_mask);
+    if (mode == 1) {
+        k_query_feature<<<grid_for(n, kBlock), kBlock, 0, st>>>(p);
+    } else {
+        // persistent-ish grid: the decoder fragments are built once per CTA and amortised over its blocks
+        const unsigned nb = grid_for(n, kBlock);
+        const unsigned g = nb < 148u * 8u ? nb : 148u * 8u;
+        const size_t sm_plain = sizeof(DecFrags) + (kBlock / 32) * sizeof(WarpStage<false>);
+        const size_t sm_grad = sizeof(DecFrags) + (kBlock / 32) * sizeof(WarpStage<true>);
+        if (mode == 2) k_decode_mma<false, true><<<g, kBlock, sm_plain, st>>>(p);
+        else if (a->grad_x) k_decode_mma<true, false><<<g, kBlock, sm_grad, st>>>(p);
+        else k_decode_mma<false, false><<<g, kBlock, sm_plain, st>>>(p);
+    }
     rc = check_launch("k_decode");
     if (rc) return rc;
     if (two_pass) {
@@ -364,6 +498,8 @@ using namespace pinq;
 extern "C" {
 
 int64_t pinq_query_workspace_bytes(int64_t n) { return (n > 0 ? n : 1) * (int64_t)kWs * (int64_t)sizeof(int32_t); }
+
+int64_t pinq_relu_mask_words(int64_t n) { return ((n > 0 ? n : 1) + 31) / 32 * (int64_t)kMTiles * 32; }
 
 int pinq_neighbor_search(const pinq_map_view* map, const float* xyz, int64_t n, uint32_t flags, const float* map_xyz,
                          const int64_t* ts_create, const float* travel_dist, int64_t cur_ts,

@@ -2,14 +2,17 @@
 // parameters.  Replaces torch.autograd through
 // model/neural_points.py:562-632 + model/decoder.py:66-88 as triggered at utils/mapper.py:572.
 //
-//   a_k        = g * w_k                    (g = dL/dsdf; the IDW weights carry no parameter gradient)
-//   delta_kj   = scale * W2[j] * 1[pre_kj > 0]
-//   dL/df_k    = a_k * sum_j delta_kj W1[j][0:8]        -> red.global.add.v4.f32 into grad_features[idx_k]
-//   dL/dW1[j]  += a_k delta_kj in_k ; dL/db1[j] += a_k delta_kj
-//   dL/dW2[j]  += a_k scale relu(pre_kj) ; dL/db2 += a_k scale
-// The hidden layer is recomputed from the saved (knn_idx, knn_w): 48 B/query of saved state instead of
-// 1.5 KB/query of activations.
-#include "query_common.cuh"
+//   a_k        = g * w_k * scale            (g = dL/dsdf; the IDW weights carry no parameter gradient)
+//   m_kj       = relu'(pre_kj)              saved by the forward as one bit per (row, hidden unit)
+//   dL/df_k    = a_k * (m_k . V)[0:8],  V[j][i] = W2[j] W1[j][i]      -> red.global.add.v2.f32 into grad_features[idx_k]
+//   G[j][i]    = sum_rows m_kj a_k in_k[i]  (in_k = [f_k, v_k, 1])    -> reduction over rows on the tensor cores
+//   dL/dW1[j][i] = W2[j] G[j][i]   dL/db1[j] = W2[j] G[j][11]
+//   dL/dW2[j]  = sum_rows a_k relu(pre_kj) = sum_i W1b[j][i] G[j][i]  (relu(pre) = m * pre, pre = W1b . in)
+//   dL/db2     = sum_rows a_k
+// Nothing of the hidden layer is recomputed: the backward needs the mask (48 B/query), the K indices and
+// weights, and -- only while the decoder is trainable -- the gathered inputs.  Both products have one EXACT
+// operand (the 0/1 mask), so a 3-way bf16 split of the other one keeps fp32 accuracy (csrc/mma.cuh).
+#include "mma.cuh"
 
 namespace pinq {
 
@@ -23,129 +26,183 @@ struct BwdParams {
     const float* features;
     const int32_t* knn_idx;
     const float* knn_w;
+    const uint32_t* relu_mask;
     const float* grad_sdf;
     float* grad_features;
     float *grad_W1, *grad_b1, *grad_W2, *grad_b2;
 };
 
-__device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
-    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+__device__ __forceinline__ void red_add_v2(float* addr, float a, float b) {
+    asm volatile("red.global.add.v2.f32 [%0], {%1, %2};" ::"l"(addr), "f"(a), "f"(b) : "memory");
 }
 
-// per-CTA decoder-gradient accumulator layout: [j*13 + 0..10] dW1[j][:], [j*13+11] db1[j], [j*13+12] dW2[j], [H*13] db2
-constexpr int kAccN = H * 13 + 1;
-
 template <bool DEC>
-__global__ void __launch_bounds__(kBlock) k_query_bwd(const BwdParams p) {
-    __shared__ __align__(16) float4 s_w[H * 4];
-    __shared__ float s_acc[DEC ? kAccN : 1];
-    load_decoder(p.dec, s_w);
-    if (DEC)
-        for (int t = threadIdx.x; t < kAccN; t += blockDim.x) s_acc[t] = 0.f;
+struct BwdStage {
+    int32_t li[K][32];
+    float ab[K][32];             // a_k of row (k, query)
+    float4 vb[DEC ? K : 1][32];  // {vx, vy, vz, 1}: decoder inputs 8..11 of row (k, query)
+};
+
+constexpr int kGCols = IN + 1;  // 11 inputs + the bias column
+
+// Same warp <-> row mapping as k_decode_mma: one warp = 32 queries = 12 m-tiles, m-tile mt = 2 k + half
+// holds neighbour k of queries 16 half + {g, g + 8}.
+template <bool DEC, bool FEAT>
+__global__ void __launch_bounds__(kBlock, 4) k_bwd_mma(const BwdParams p) {
+    extern __shared__ __align__(16) unsigned char s_raw[];
+    DecFrags* fr = reinterpret_cast<DecFrags*>(s_raw);
+    BwdStage<DEC>* stages = reinterpret_cast<BwdStage<DEC>*>(s_raw + sizeof(DecFrags));
+    __shared__ float s_G[DEC ? H * kGCols : 1];
+    __shared__ float s_db2;
+    build_dec_frags(p.dec, fr, false, FEAT, false);
+    if (DEC) {
+        for (int e = threadIdx.x; e < H * kGCols; e += blockDim.x) s_G[e] = 0.f;
+        if (threadIdx.x == 0) s_db2 = 0.f;
+    }
     __syncthreads();
-
-    const int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    const bool live = q < p.n;
-    const int lane = threadIdx.x & 31;
-
-    float in[K][IN];
-    float a[K];
-    int32_t kidx[K];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane >> 2, t = lane & 3;
+    BwdStage<DEC>& st = stages[warp];
     const float scale = p.dec.sdf_scale;
-#pragma unroll
-    for (int k = 0; k < K; ++k) {
-        kidx[k] = -1;
-        a[k] = 0.f;
-#pragma unroll
-        for (int i = 0; i < IN; ++i) in[k][i] = 0.f;
-    }
-    if (live) {
-        const float g = p.grad_sdf[q];
-        const float x = p.xyz[3 * q], y = p.xyz[3 * q + 1], z = p.xyz[3 * q + 2];
-#pragma unroll
-        for (int k = 0; k < K; ++k) {
-            const int32_t li = p.knn_idx[q * K + k];
-            kidx[k] = li;
-            a[k] = g * p.knn_w[q * K + k];
-            if (li >= 0) {
-                const float4* fr = reinterpret_cast<const float4*>(p.features + (int64_t)li * F);
-                const float4 fa = __ldg(fr), fb = __ldg(fr + 1);
-                in[k][0] = fa.x; in[k][1] = fa.y; in[k][2] = fa.z; in[k][3] = fa.w;
-                in[k][4] = fb.x; in[k][5] = fb.y; in[k][6] = fb.z; in[k][7] = fb.w;
-                const float* pp = p.point_xyz + 3 * (int64_t)li;
-                float vx = __fsub_rn(x, pp[0]), vy = __fsub_rn(y, pp[1]), vz = __fsub_rn(z, pp[2]);
-                if (p.rotate) quat_rotate(__ldg(&p.quats[li]), false, vx, vy, vz);
-                in[k][8] = vx; in[k][9] = vy; in[k][10] = vz;
-            }
-        }
-    }
+    const int64_t nblocks = (p.n + kBlock - 1) / kBlock;
 
-    float gf[K][F];
+    float G[4][2][4];  // G[16 jt + g (+8)][8 nt + 2t (+1)], C-fragment layout
 #pragma unroll
-    for (int k = 0; k < K; ++k)
+    for (int jt = 0; jt < 4; ++jt)
 #pragma unroll
-        for (int i = 0; i < F; ++i) gf[k][i] = 0.f;
+        for (int nt = 0; nt < 2; ++nt) G[jt][nt][0] = G[jt][nt][1] = G[jt][nt][2] = G[jt][nt][3] = 0.f;
     float db2 = 0.f;
 
-    for (int j = 0; j < H; ++j) {
-        const float4 wa = s_w[4 * j], wb = s_w[4 * j + 1], wc = s_w[4 * j + 2], wd = s_w[4 * j + 3];
-        float dw[13];
+    for (int64_t blk = blockIdx.x; blk < nblocks; blk += gridDim.x) {
+        const int64_t q0 = blk * kBlock + warp * 32;
+        if (q0 >= p.n) continue;  // warp-uniform
+        const int64_t q = q0 + lane;
+        const bool live = q < p.n;
+        // ---- phase A: lane = query ----
+        __syncwarp();
+        {
+            const float gq = live ? p.grad_sdf[q] : 0.f;
+            float x = 0.f, y = 0.f, z = 0.f;
+            if (DEC && live) {
+                x = p.xyz[3 * q]; y = p.xyz[3 * q + 1]; z = p.xyz[3 * q + 2];
+            }
 #pragma unroll
-        for (int i = 0; i < 13; ++i) dw[i] = 0.f;
+            for (int k = 0; k < K; ++k) {
+                const int32_t li = live ? p.knn_idx[q * K + k] : -1;
+                const float a = live ? gq * p.knn_w[q * K + k] * scale : 0.f;
+                st.li[k][lane] = li;
+                st.ab[k][lane] = li >= 0 ? a : 0.f;
+                if (DEC) {
+                    float vx = 0.f, vy = 0.f, vz = 0.f;
+                    if (li >= 0) {
+                        const float* pp = p.point_xyz + 3 * (int64_t)li;
+                        vx = __fsub_rn(x, pp[0]); vy = __fsub_rn(y, pp[1]); vz = __fsub_rn(z, pp[2]);
+                        if (p.rotate) quat_rotate(__ldg(&p.quats[li]), false, vx, vy, vz);
+                        db2 += a;
+                    }
+                    st.vb[k][lane] = make_float4(vx, vy, vz, 1.f);
+                }
+            }
+        }
+        __syncwarp();
+
+        // ---- phase B: lane = (g, t) ----
+#pragma unroll 1
+        for (int mt = 0; mt < kMTiles; ++mt) {
+            const int k = mt >> 1, half = mt & 1;
+            const int qa = 16 * half + g, qb = qa + 8;
+            const int la = st.li[k][qa], lb = st.li[k][qb];
+            if (!__any_sync(0xffffffffu, (la >= 0) | (lb >= 0))) continue;  // warp-uniform
+            const uint32_t bits = __ldg(&p.relu_mask[((q0 >> 5) * kMTiles + mt) * 32 + lane]);
+            uint32_t am[4][4];
+            mask_frags(bits, am);
+            if (FEAT) {
+                float c2[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-        for (int k = 0; k < K; ++k) {
-            const float pre = mlp_pre(in[k], wa, wb, wc);
-            const float t = pre > 0.f ? a[k] * scale * wd.x : 0.f;  // a_k * delta_kj
-            gf[k][0] = fmaf(t, wa.x, gf[k][0]); gf[k][1] = fmaf(t, wa.y, gf[k][1]);
-            gf[k][2] = fmaf(t, wa.z, gf[k][2]); gf[k][3] = fmaf(t, wa.w, gf[k][3]);
-            gf[k][4] = fmaf(t, wb.x, gf[k][4]); gf[k][5] = fmaf(t, wb.y, gf[k][5]);
-            gf[k][6] = fmaf(t, wb.z, gf[k][6]); gf[k][7] = fmaf(t, wb.w, gf[k][7]);
+                for (int s = 2; s >= 0; --s)
+#pragma unroll
+                    for (int pp = 0; pp < 4; ++pp) {
+                        const uint2 bv = fr->vf[pp][s][lane];
+                        mma_bf16(c2, am[pp][0], am[pp][1], am[pp][2], am[pp][3], bv.x, bv.y);
+                    }
+                // c2 = (m . V)[row g | g+8][2t, 2t+1]: the quad covers one 32-byte gradient row
+                if (la >= 0) {
+                    const float aa = st.ab[k][qa];
+                    red_add_v2(p.grad_features + (int64_t)la * F + 2 * t, c2[0] * aa, c2[1] * aa);
+                }
+                if (lb >= 0) {
+                    const float aa = st.ab[k][qb];
+                    red_add_v2(p.grad_features + (int64_t)lb * F + 2 * t, c2[2] * aa, c2[3] * aa);
+                }
+            }
             if (DEC) {
+                // A = mask^T (hidden unit x row): transpose the 8x8 blocks of the mask fragments
+                uint32_t at[4][4];
 #pragma unroll
-                for (int i = 0; i < IN; ++i) dw[i] = fmaf(t, in[k][i], dw[i]);
-                dw[11] += t;
-                dw[12] = fmaf(a[k] * scale, fmaxf(pre, 0.f), dw[12]);
-            }
-        }
-        if (DEC) {
+                for (int pp = 0; pp < 4; ++pp) {
+                    at[pp][0] = movmatrix_trans(am[pp][0]);  // (j = 16p + g     ; rows 2t, 2t+1)
+                    at[pp][2] = movmatrix_trans(am[pp][1]);  // (j = 16p + g     ; rows 2t+8, 2t+9)
+                    at[pp][1] = movmatrix_trans(am[pp][2]);  // (j = 16p + 8 + g ; rows 2t, 2t+1)
+                    at[pp][3] = movmatrix_trans(am[pp][3]);  // (j = 16p + 8 + g ; rows 2t+8, 2t+9)
+                }
+                // B = X (row x input column): rows 2t, 2t+1, 2t+8, 2t+9 of this m-tile, column g (and 8 + g)
+                __nv_bfloat16 xf[4][3], xv[4][3];
 #pragma unroll
-            for (int i = 0; i < 13; ++i) {
-                const float v = warp_sum(dw[i]);
-                if (lane == 0) atomicAdd(&s_acc[j * 13 + i], v);
+                for (int r4 = 0; r4 < 4; ++r4) {
+                    const int qr = 16 * half + 2 * t + (r4 & 1) + 8 * (r4 >> 1);
+                    const int lr = st.li[k][qr];
+                    const float ar = st.ab[k][qr];
+                    const float f = lr >= 0 ? ar * __ldg(p.features + (int64_t)lr * F + g) : 0.f;
+                    const float v = g < 4 ? ar * reinterpret_cast<const float*>(&st.vb[k][qr])[g] : 0.f;
+                    bf16_split3(f, xf[r4][0], xf[r4][1], xf[r4][2]);
+                    bf16_split3(v, xv[r4][0], xv[r4][1], xv[r4][2]);
+                }
+#pragma unroll
+                for (int jt = 0; jt < 4; ++jt) {
+                    float tf[4] = {0.f, 0.f, 0.f, 0.f}, tv[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+                    for (int s = 2; s >= 0; --s) {
+                        mma_bf16(tf, at[jt][0], at[jt][1], at[jt][2], at[jt][3], pack_bf16(xf[0][s], xf[1][s]),
+                                 pack_bf16(xf[2][s], xf[3][s]));
+                        mma_bf16(tv, at[jt][0], at[jt][1], at[jt][2], at[jt][3], pack_bf16(xv[0][s], xv[1][s]),
+                                 pack_bf16(xv[2][s], xv[3][s]));
+                    }
+                    // accumulate outside the tensor core (round-to-nearest fp32 adds over the long row reduction)
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) {
+                        G[jt][0][c] += tf[c];
+                        G[jt][1][c] += tv[c];
+                    }
+                }
             }
         }
     }
+
     if (DEC) {
 #pragma unroll
-        for (int k = 0; k < K; ++k) db2 += a[k] * scale;
+        for (int jt = 0; jt < 4; ++jt)
+#pragma unroll
+            for (int nt = 0; nt < 2; ++nt)
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    const int j = 16 * jt + g + 8 * (c >> 1), i = 8 * nt + 2 * t + (c & 1);
+                    if (i < kGCols) atomicAdd(&s_G[j * kGCols + i], G[jt][nt][c]);
+                }
         db2 = warp_sum(db2);
-        if (lane == 0) atomicAdd(&s_acc[H * 13], db2);
-    }
-
-    if (live && p.grad_features) {
-#pragma unroll
-        for (int k = 0; k < K; ++k) {
-            if (kidx[k] >= 0) {
-                float* dst = p.grad_features + (int64_t)kidx[k] * F;
-                red_add_v4(dst, gf[k][0], gf[k][1], gf[k][2], gf[k][3]);
-                red_add_v4(dst + 4, gf[k][4], gf[k][5], gf[k][6], gf[k][7]);
-            }
-        }
-    }
-
-    if (DEC) {
+        if (lane == 0) atomicAdd(&s_db2, db2);
         __syncthreads();
-        for (int t = threadIdx.x; t < kAccN; t += blockDim.x) {
-            const float v = s_acc[t];
-            if (t == H * 13) {
-                atomicAdd(p.grad_b2, v);
-            } else {
-                const int j = t / 13, i = t - j * 13;
-                if (i < IN) atomicAdd(&p.grad_W1[j * IN + i], v);
-                else if (i == 11) atomicAdd(&p.grad_b1[j], v);
-                else atomicAdd(&p.grad_W2[j], v);
-            }
+        for (int e = threadIdx.x; e < H * kGCols; e += blockDim.x) {
+            const int j = e / kGCols, i = e - j * kGCols;
+            const float v = __ldg(&p.dec.W2[j]) * s_G[e];
+            if (i < IN) atomicAdd(&p.grad_W1[j * IN + i], v);
+            else atomicAdd(&p.grad_b1[j], v);
         }
+        for (int j = threadIdx.x; j < H; j += blockDim.x) {
+            float acc = __ldg(&p.dec.b1[j]) * s_G[j * kGCols + IN];
+#pragma unroll
+            for (int i = 0; i < IN; ++i) acc = fmaf(__ldg(&p.dec.W1[j * IN + i]), s_G[j * kGCols + i], acc);
+            atomicAdd(&p.grad_W2[j], acc);
+        }
+        if (threadIdx.x == 0) atomicAdd(p.grad_b2, s_db2);
     }
 }
 
@@ -157,19 +214,27 @@ extern "C" int pinq_query_fused_bwd(const pinq_bwd_args* a, void* stream) {
     PINQ_REQUIRE(a != nullptr, "null args");
     int rc = check_decoder(a->dec, a->k, a->feature_dim);
     if (rc) return rc;
-    PINQ_REQUIRE(a->xyz && a->point_xyz && a->features && a->knn_idx && a->knn_w && a->grad_sdf, "null input");
+    PINQ_REQUIRE(a->xyz && a->point_xyz && a->features && a->knn_idx && a->knn_w && a->grad_sdf && a->relu_mask,
+                 "null input (the backward needs the relu mask saved by pinq_query_fused_fwd)");
     PINQ_REQUIRE(!(a->flags & PINQ_F_ROTATE) || a->quats, "PINQ_F_ROTATE needs quats");
     const bool dec = a->grad_W1 != nullptr;
     PINQ_REQUIRE(!dec || (a->grad_b1 && a->grad_W2 && a->grad_b2), "decoder gradients: all four or none");
-    if (a->n == 0 || (!dec && !a->grad_features)) return PINQ_OK;
+    const bool feat = a->grad_features != nullptr;
+    if (a->n == 0 || (!dec && !feat)) return PINQ_OK;
     BwdParams p;
     p.dec = a->dec; p.xyz = a->xyz; p.n = a->n; p.rotate = (a->flags & PINQ_F_ROTATE) != 0;
     p.point_xyz = a->point_xyz; p.quats = reinterpret_cast<const float4*>(a->quats);
-    p.features = a->features; p.knn_idx = a->knn_idx; p.knn_w = a->knn_w; p.grad_sdf = a->grad_sdf;
-    p.grad_features = a->grad_features;
+    p.features = a->features; p.knn_idx = a->knn_idx; p.knn_w = a->knn_w; p.relu_mask = a->relu_mask;
+    p.grad_sdf = a->grad_sdf; p.grad_features = a->grad_features;
     p.grad_W1 = a->grad_W1; p.grad_b1 = a->grad_b1; p.grad_W2 = a->grad_W2; p.grad_b2 = a->grad_b2;
     cudaStream_t st = as_stream(stream);
-    if (dec) k_query_bwd<true><<<grid_for(a->n, kBlock), kBlock, 0, st>>>(p);
-    else k_query_bwd<false><<<grid_for(a->n, kBlock), kBlock, 0, st>>>(p);
+    const unsigned nb = grid_for(a->n, kBlock);
+    const unsigned cap = 148u * (dec ? 4u : 8u);  // fewer, longer-lived CTAs while every CTA ends in 833 global atomics
+    const unsigned g = nb < cap ? nb : cap;
+    const size_t sm_dec = sizeof(DecFrags) + (kBlock / 32) * sizeof(BwdStage<true>);
+    const size_t sm_plain = sizeof(DecFrags) + (kBlock / 32) * sizeof(BwdStage<false>);
+    if (dec && feat) k_bwd_mma<true, true><<<g, kBlock, sm_dec, st>>>(p);
+    else if (dec) k_bwd_mma<true, false><<<g, kBlock, sm_dec, st>>>(p);
+    else k_bwd_mma<false, true><<<g, kBlock, sm_plain, st>>>(p);
     return check_launch("pinq_query_fused_bwd");
 }

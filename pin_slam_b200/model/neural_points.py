@@ -533,7 +533,7 @@ class _FusedSDFFn(torch.autograd.Function):
         nn_count = torch.empty(n, dtype=torch.int32, device=dev)
         a.sdf = P.ptr(sdf)
         a.nn_count = P.ptr(nn_count)
-        grad = std = cert = knn_idx = knn_w = None
+        grad = std = cert = knn_idx = knn_w = relu_mask = None
         if need_dx:
             grad = torch.empty((n, 3), dtype=torch.float32, device=dev)
             a.grad_x = P.ptr(grad)
@@ -545,6 +545,9 @@ class _FusedSDFFn(torch.autograd.Function):
             knn_w = torch.empty((n, K), dtype=torch.float32, device=dev)
             a.knn_idx = P.ptr(knn_idx)
             a.knn_w = P.ptr(knn_w)
+        if need_bwd:  # relu'(pre) bits of the hidden layer: 48 B/query instead of re-evaluating layer 1
+            relu_mask = torch.empty(int(lib.pinq_relu_mask_words(n)), dtype=torch.int32, device=dev)
+            a.relu_mask = P.ptr(relu_mask)
         if want_certainty:
             cert = torch.empty(n, dtype=torch.float32, device=dev)
             a.certainty = P.ptr(cert)
@@ -552,7 +555,7 @@ class _FusedSDFFn(torch.autograd.Function):
         ctx.npts, ctx.decoder, ctx.query_locally = npts, decoder, query_locally
         ctx.after_pgo = npts.after_pgo
         if need_bwd:
-            ctx.save_for_backward(x, feats, knn_idx, knn_w, grad if ctx.needs_input_grad[2] else None)
+            ctx.save_for_backward(x, feats, knn_idx, knn_w, relu_mask, grad if ctx.needs_input_grad[2] else None)
         empty = torch.empty(0, device=dev)
         outs = (sdf, nn_count, grad if grad is not None else empty, std if std is not None else empty,
                 cert if cert is not None else empty)
@@ -563,7 +566,7 @@ class _FusedSDFFn(torch.autograd.Function):
     def backward(ctx, g_sdf, *unused):
         lib = P.load()
         npts, decoder = ctx.npts, ctx.decoder
-        x, feats, knn_idx, knn_w, dx = ctx.saved_tensors
+        x, feats, knn_idx, knn_w, relu_mask, dx = ctx.saved_tensors
         g = g_sdf.contiguous().float()
         b = P.BwdArgs()
         b.dec = decoder.view()
@@ -579,6 +582,7 @@ class _FusedSDFFn(torch.autograd.Function):
         b.features = P.ptr(feats.detach())
         b.knn_idx = P.ptr(knn_idx)
         b.knn_w = P.ptr(knn_w)
+        b.relu_mask = P.ptr(relu_mask)
         b.grad_sdf = P.ptr(g)
         g_feats = gW1 = gb1 = gW2 = gb2 = None
         if ctx.needs_input_grad[3]:
