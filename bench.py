@@ -301,6 +301,8 @@ def main():
     relu_mask = torch.empty(int(lib.pinq_relu_mask_words(n)), dtype=torch.int32, device=dev)
     a.sdf, a.nn_count, a.knn_idx, a.knn_w = P.ptr(sdf), P.ptr(nnc), P.ptr(knn_idx), P.ptr(knn_w)
     a.relu_mask = P.ptr(relu_mask)
+    perm = torch.empty(n, dtype=torch.int32, device=dev)
+    a.perm = P.ptr(perm)
     b = P.BwdArgs()
     b.dec = dec.view()
     b.xyz, b.n, b.flags, b.k, b.feature_dim = P.ptr(q), n, 0, K, 8
@@ -308,6 +310,7 @@ def main():
     b.features = P.ptr(npts.local_geo_features.detach())
     b.knn_idx, b.knn_w, b.grad_sdf = P.ptr(knn_idx), P.ptr(knn_w), P.ptr(ones)
     b.relu_mask = P.ptr(relu_mask)
+    b.perm = P.ptr(perm)
     gf = torch.zeros_like(npts.local_geo_features)
     gd = [torch.zeros_like(p) for p in dec.fused_params()]
     b.grad_features = P.ptr(gf)
@@ -377,7 +380,7 @@ def main():
                 "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(args, npts, vbar),
                 "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e,
-                "gpu_launches": 2 * args.steps, "clocks": clocks}
+                "gpu_launches": 6 * args.steps, "clocks": clocks}
         line["config"]["parallelism"] = "replicated map, queries sharded x%d%s" % (
             world, ", NCCL all-reduce of feature+decoder grads" if world > 1 else "")
         print(json.dumps(line))

@@ -176,6 +176,11 @@ typedef struct pinq_query_args {
     uint32_t* relu_mask;       /* pinq_relu_mask_words(n) words or NULL: relu'(pre) of the hidden layer,
                                   one bit per (query, neighbour, hidden unit) in tensor-core fragment
                                   order; saved for pinq_query_fused_bwd (48 B/query, opaque)          */
+    int32_t* perm;             /* [n] or NULL.  When given, the fused forward bins the queries by 4x4x4-voxel
+                                  brick and processes them in that order (perm[i] = query at position i):
+                                  gathers become cache hits, results are unchanged.  knn_idx / knn_w /
+                                  knn_d2 / relu_mask are then stored in PROCESSING order; pass the same
+                                  perm to pinq_query_fused_bwd.  Ignored by pinq_query_feature and the mesher. */
     void* workspace;           /* pinq_query_workspace_bytes(n) bytes: search -> decode hand-off      */
 } pinq_query_args;
 
@@ -202,6 +207,7 @@ typedef struct pinq_bwd_args {
     const int32_t* knn_idx;    /* [n,k] saved by the forward                               */
     const float* knn_w;        /* [n,k]                                                    */
     const uint32_t* relu_mask; /* pinq_relu_mask_words(n), saved by the forward            */
+    const int32_t* perm;       /* [n] processing order of the forward, or NULL             */
     const float* grad_sdf;     /* [n] dL/dsdf                                              */
     float* grad_features;      /* [Mx+1,F] accumulated (+=), may be NULL                   */
     float* grad_W1;            /* [H,F+3] accumulated, NULL when the decoder is frozen (H11) */

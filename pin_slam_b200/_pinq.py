@@ -29,13 +29,13 @@ class QueryArgs(C.Structure):
     _fields_ = [("map", MapView), ("dec", DecoderView), ("xyz", _vp), ("n", _i64), ("flags", _u32), ("k", _i32),
                 ("feature_dim", _i32), ("features", _vp), ("point_xyz", _vp), ("certainties", _vp), ("quats", _vp), ("ts_update", _vp),
                 ("query_ts", _vp), ("sdf", _vp), ("grad_x", _vp), ("sdf_std", _vp), ("nn_count", _vp),
-                ("certainty", _vp), ("knn_idx", _vp), ("knn_w", _vp), ("knn_d2", _vp), ("relu_mask", _vp), ("workspace", _vp)]
+                ("certainty", _vp), ("knn_idx", _vp), ("knn_w", _vp), ("knn_d2", _vp), ("relu_mask", _vp), ("perm", _vp), ("workspace", _vp)]
 
 
 class BwdArgs(C.Structure):
     _fields_ = [("dec", DecoderView), ("xyz", _vp), ("n", _i64), ("flags", _u32), ("k", _i32), ("feature_dim", _i32),
                 ("point_xyz", _vp), ("quats", _vp), ("features", _vp), ("knn_idx", _vp), ("knn_w", _vp),
-                ("relu_mask", _vp), ("grad_sdf", _vp), ("grad_features", _vp), ("grad_W1", _vp), ("grad_b1", _vp), ("grad_W2", _vp),
+                ("relu_mask", _vp), ("perm", _vp), ("grad_sdf", _vp), ("grad_features", _vp), ("grad_W1", _vp), ("grad_b1", _vp), ("grad_W2", _vp),
                 ("grad_b2", _vp)]
 
 

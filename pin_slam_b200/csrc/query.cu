@@ -79,19 +79,19 @@ __global__ void k_query_certainty(MapDev map, const float* __restrict__ xyz, int
 constexpr int kWs = K + 1;
 
 __global__ void __launch_bounds__(kBlock) k_search(MapDev map, PointSrc src, int64_t n, bool recip,
-                                                   int32_t* __restrict__ ws) {
+                                                   const int32_t* __restrict__ perm, int32_t* __restrict__ ws) {
     extern __shared__ uint32_t s_off_s[];
     load_stencil(map, s_off_s);
     __syncthreads();
-    const int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (q >= n) return;
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;  // position in processing order
+    if (i >= n) return;
     float x, y, z;
-    load_point(src, q, x, y, z);
+    load_point(src, perm ? perm[i] : i, x, y, z);
     float kd2[K];
     int32_t kr[K];
     int nn;
     search_topk(map, s_off_s, x, y, z, recip, kd2, kr, nn);
-    int32_t* o = ws + q * kWs;
+    int32_t* o = ws + i * kWs;
 #pragma unroll
     for (int k = 0; k < K; ++k) o[k] = kr[k];
     o[K] = nn;
@@ -105,6 +105,8 @@ struct DecodeParams {
     int64_t n;
     bool rotate, scatter_in_kernel;
     const int32_t* ws;
+    const int32_t* perm;  // processing order -> query index (spatial binning, csrc/sort.cu); NULL = identity.
+                          // ws / knn_* / relu_mask are indexed by processing position, everything else by query.
     const float* features;
     const float* point_xyz;
     float* certainties;
@@ -133,8 +135,8 @@ struct QueryLane {
 };
 
 template <bool WANT_U>
-__device__ __forceinline__ void resolve_query(const DecodeParams& p, int64_t q, bool live, float x, float y, float z,
-                                              QueryLane& L) {
+__device__ __forceinline__ void resolve_query(const DecodeParams& p, int64_t i, int64_t q, bool live, float x, float y,
+                                              float z, QueryLane& L) {
     L.nn = 0;
 #pragma unroll
     for (int k = 0; k < K; ++k) {
@@ -144,7 +146,7 @@ __device__ __forceinline__ void resolve_query(const DecodeParams& p, int64_t q, 
         if (WANT_U) L.ux[k] = L.uy[k] = L.uz[k] = 0.f;
     }
     if (live) {
-        const int32_t* wsq = p.ws + q * kWs;
+        const int32_t* wsq = p.ws + i * kWs;
         L.nn = wsq[K];
         int32_t r[K];
 #pragma unroll
@@ -177,15 +179,15 @@ __device__ __forceinline__ void resolve_query(const DecodeParams& p, int64_t q, 
     if (p.nn_count) p.nn_count[q] = L.nn;
     if (p.knn_idx) {
 #pragma unroll
-        for (int k = 0; k < K; ++k) p.knn_idx[q * K + k] = L.kidx[k];
+        for (int k = 0; k < K; ++k) p.knn_idx[i * K + k] = L.kidx[k];
     }
     if (p.knn_w) {
 #pragma unroll
-        for (int k = 0; k < K; ++k) p.knn_w[q * K + k] = L.w[k];
+        for (int k = 0; k < K; ++k) p.knn_w[i * K + k] = L.w[k];
     }
     if (p.knn_d2) {
 #pragma unroll
-        for (int k = 0; k < K; ++k) p.knn_d2[q * K + k] = L.kd2[k];
+        for (int k = 0; k < K; ++k) p.knn_d2[i * K + k] = L.kd2[k];
     }
     if (p.certainty) {  // sum_k w_k c_k, neural_points.py:651-656
         float c = 0.f;
@@ -213,7 +215,7 @@ __global__ void __launch_bounds__(kBlock) k_query_feature(const DecodeParams p) 
     float x, y, z;
     load_point(p.src, q, x, y, z);
     QueryLane L;
-    resolve_query<false>(p, q, true, x, y, z, L);
+    resolve_query<false>(p, q, q, true, x, y, z, L);
     float* o = p.feat_out + q * (K * IN);
 #pragma unroll
     for (int k = 0; k < K; ++k) {
@@ -261,12 +263,13 @@ __global__ void __launch_bounds__(kBlock, GRAD ? 3 : 4) k_decode_mma(const Decod
     for (int64_t blk = blockIdx.x; blk < nblocks; blk += gridDim.x) {
         const int64_t q0 = blk * kBlock + warp * 32;  // first query of this warp
         if (q0 >= p.n) continue;                      // warp-uniform
-        const int64_t q = q0 + lane;
-        const bool live = q < p.n;
+        const int64_t i = q0 + lane;  // processing position; q = the query it holds
+        const bool live = i < p.n;
+        const int64_t q = (live && p.perm) ? (int64_t)p.perm[i] : i;
         float x = 0.f, y = 0.f, z = 0.f;
         if (live) load_point(p.src, q, x, y, z);
         QueryLane L;
-        resolve_query<GRAD>(p, q, live, x, y, z, L);
+        resolve_query<GRAD>(p, i, q, live, x, y, z, L);
         __syncwarp();  // the previous iteration's phase C reads are done
 #pragma unroll
         for (int k = 0; k < K; ++k) {
@@ -406,15 +409,17 @@ __global__ void __launch_bounds__(kBlock, GRAD ? 3 : 4) k_decode_mma(const Decod
 
 // second pass of the exact training path: scatter after every query has read its certainties
 __global__ void k_certainty_scatter(const int32_t* __restrict__ knn_idx, const float* __restrict__ knn_w,
-                                    const int64_t* __restrict__ query_ts, int64_t n, float* certainties,
-                                    long long* ts_update) {
+                                    const int64_t* __restrict__ query_ts, const int32_t* __restrict__ perm, int64_t n,
+                                    float* certainties, long long* ts_update) {
     const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= n * K) return;
     const int32_t i = knn_idx[t];
     if (i < 0) return;
     atomicAdd(&certainties[i], knn_w[t]);
-    if (query_ts && ts_update) atomicMax(&ts_update[i], (long long)query_ts[t / K]);
+    if (query_ts && ts_update) atomicMax(&ts_update[i], (long long)query_ts[perm ? perm[t / K] : t / K]);
 }
+
+static inline int64_t ws_bytes(int64_t n) { return (((n > 0 ? n : 1) * (int64_t)kWs * 4 + 255) / 256) * 256; }
 
 static int run_query(const pinq_query_args* a, int mode, float* feat_out, const PointSrc* grid_src, int min_nn,
                      uint8_t* mask_out, cudaStream_t st) {
@@ -451,7 +456,14 @@ static int run_query(const pinq_query_args* a, int mode, float* feat_out, const 
     }
     const bool recip = (a->flags & PINQ_F_RECIP_DIV) != 0;
     int32_t* ws = reinterpret_cast<int32_t*>(a->workspace);
-    k_search<<<grid_for(n, kBlock), kBlock, map.kn * sizeof(uint32_t), st>>>(map, src, n, recip, ws);
+    const int32_t* perm = nullptr;
+    if (a->perm && !grid_src && mode != 1) {  // spatial binning: processing order only, results unchanged
+        rc = launch_spatial_bin(a->xyz, n, map.res, recip, reinterpret_cast<unsigned char*>(a->workspace) + ws_bytes(n),
+                                a->perm, st);
+        if (rc) return rc;
+        perm = a->perm;
+    }
+    k_search<<<grid_for(n, kBlock), kBlock, map.kn * sizeof(uint32_t), st>>>(map, src, n, recip, perm, ws);
     rc = check_launch("k_search");
     if (rc) return rc;
 
@@ -462,7 +474,7 @@ static int run_query(const pinq_query_args* a, int mode, float* feat_out, const 
     // caller wants it (and gave knn buffers), scatter in a second kernel; otherwise fuse the atomics.
     const bool two_pass = training && a->certainty && a->knn_idx && a->knn_w;
     p.scatter_in_kernel = training && !two_pass;
-    p.ws = ws; p.features = a->features; p.point_xyz = a->point_xyz; p.certainties = a->certainties;
+    p.ws = ws; p.perm = perm; p.features = a->features; p.point_xyz = a->point_xyz; p.certainties = a->certainties;
     p.quats = reinterpret_cast<const float4*>(a->quats);
     p.ts_update = reinterpret_cast<long long*>(a->ts_update); p.query_ts = a->query_ts;
     p.sdf = a->sdf; p.grad_x = a->grad_x; p.sdf_std = a->sdf_std; p.nn_count = a->nn_count;
@@ -484,7 +496,7 @@ static int run_query(const pinq_query_args* a, int mode, float* feat_out, const 
     rc = check_launch("k_decode");
     if (rc) return rc;
     if (two_pass) {
-        k_certainty_scatter<<<grid_for(n * K, 256), 256, 0, st>>>(a->knn_idx, a->knn_w, a->query_ts, n, a->certainties,
+        k_certainty_scatter<<<grid_for(n * K, 256), 256, 0, st>>>(a->knn_idx, a->knn_w, a->query_ts, perm, n, a->certainties,
                                                                   reinterpret_cast<long long*>(a->ts_update));
         return check_launch("k_certainty_scatter");
     }
@@ -497,7 +509,7 @@ using namespace pinq;
 
 extern "C" {
 
-int64_t pinq_query_workspace_bytes(int64_t n) { return (n > 0 ? n : 1) * (int64_t)kWs * (int64_t)sizeof(int32_t); }
+int64_t pinq_query_workspace_bytes(int64_t n) { return ws_bytes(n) + bin_scratch_bytes(n > 0 ? n : 1); }
 
 int64_t pinq_relu_mask_words(int64_t n) { return ((n > 0 ? n : 1) + 31) / 32 * (int64_t)kMTiles * 32; }
 

@@ -27,6 +27,7 @@ struct BwdParams {
     const int32_t* knn_idx;
     const float* knn_w;
     const uint32_t* relu_mask;
+    const int32_t* perm;
     const float* grad_sdf;
     float* grad_features;
     float *grad_W1, *grad_b1, *grad_W2, *grad_b2;
@@ -75,8 +76,9 @@ __global__ void __launch_bounds__(kBlock, 4) k_bwd_mma(const BwdParams p) {
     for (int64_t blk = blockIdx.x; blk < nblocks; blk += gridDim.x) {
         const int64_t q0 = blk * kBlock + warp * 32;
         if (q0 >= p.n) continue;  // warp-uniform
-        const int64_t q = q0 + lane;
-        const bool live = q < p.n;
+        const int64_t i = q0 + lane;  // processing position; q = the query it holds
+        const bool live = i < p.n;
+        const int64_t q = (live && p.perm) ? (int64_t)p.perm[i] : i;
         // ---- phase A: lane = query ----
         __syncwarp();
         {
@@ -87,8 +89,8 @@ __global__ void __launch_bounds__(kBlock, 4) k_bwd_mma(const BwdParams p) {
             }
 #pragma unroll
             for (int k = 0; k < K; ++k) {
-                const int32_t li = live ? p.knn_idx[q * K + k] : -1;
-                const float a = live ? gq * p.knn_w[q * K + k] * scale : 0.f;
+                const int32_t li = live ? p.knn_idx[i * K + k] : -1;
+                const float a = live ? gq * p.knn_w[i * K + k] * scale : 0.f;
                 st.li[k][lane] = li;
                 st.ab[k][lane] = li >= 0 ? a : 0.f;
                 if (DEC) {
@@ -224,7 +226,7 @@ extern "C" int pinq_query_fused_bwd(const pinq_bwd_args* a, void* stream) {
     BwdParams p;
     p.dec = a->dec; p.xyz = a->xyz; p.n = a->n; p.rotate = (a->flags & PINQ_F_ROTATE) != 0;
     p.point_xyz = a->point_xyz; p.quats = reinterpret_cast<const float4*>(a->quats);
-    p.features = a->features; p.knn_idx = a->knn_idx; p.knn_w = a->knn_w; p.relu_mask = a->relu_mask;
+    p.features = a->features; p.knn_idx = a->knn_idx; p.knn_w = a->knn_w; p.relu_mask = a->relu_mask; p.perm = a->perm;
     p.grad_sdf = a->grad_sdf; p.grad_features = a->grad_features;
     p.grad_W1 = a->grad_W1; p.grad_b1 = a->grad_b1; p.grad_W2 = a->grad_W2; p.grad_b2 = a->grad_b2;
     cudaStream_t st = as_stream(stream);

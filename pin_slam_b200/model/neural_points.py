@@ -96,6 +96,7 @@ class NeuralPoints(nn.Module):
         self._index_dirty = True
         self._occ = None
         self._ws = None
+        self.bin_queries_min = 32768  # fused queries of at least this many points are binned by brick first
         self.set_search_neighborhood(num_nei_cells=config.num_nei_cells, search_alpha=config.search_alpha)
         self.memory_footprint = []
         self.to(self.device)
@@ -533,7 +534,10 @@ class _FusedSDFFn(torch.autograd.Function):
         nn_count = torch.empty(n, dtype=torch.int32, device=dev)
         a.sdf = P.ptr(sdf)
         a.nn_count = P.ptr(nn_count)
-        grad = std = cert = knn_idx = knn_w = relu_mask = None
+        grad = std = cert = knn_idx = knn_w = relu_mask = perm = None
+        if n >= npts.bin_queries_min:  # large batches are processed brick by brick (csrc/sort.cu)
+            perm = torch.empty(n, dtype=torch.int32, device=dev)
+            a.perm = P.ptr(perm)
         if need_dx:
             grad = torch.empty((n, 3), dtype=torch.float32, device=dev)
             a.grad_x = P.ptr(grad)
@@ -555,7 +559,7 @@ class _FusedSDFFn(torch.autograd.Function):
         ctx.npts, ctx.decoder, ctx.query_locally = npts, decoder, query_locally
         ctx.after_pgo = npts.after_pgo
         if need_bwd:
-            ctx.save_for_backward(x, feats, knn_idx, knn_w, relu_mask, grad if ctx.needs_input_grad[2] else None)
+            ctx.save_for_backward(x, feats, knn_idx, knn_w, relu_mask, perm, grad if ctx.needs_input_grad[2] else None)
         empty = torch.empty(0, device=dev)
         outs = (sdf, nn_count, grad if grad is not None else empty, std if std is not None else empty,
                 cert if cert is not None else empty)
@@ -566,7 +570,7 @@ class _FusedSDFFn(torch.autograd.Function):
     def backward(ctx, g_sdf, *unused):
         lib = P.load()
         npts, decoder = ctx.npts, ctx.decoder
-        x, feats, knn_idx, knn_w, relu_mask, dx = ctx.saved_tensors
+        x, feats, knn_idx, knn_w, relu_mask, perm, dx = ctx.saved_tensors
         g = g_sdf.contiguous().float()
         b = P.BwdArgs()
         b.dec = decoder.view()
@@ -583,6 +587,7 @@ class _FusedSDFFn(torch.autograd.Function):
         b.knn_idx = P.ptr(knn_idx)
         b.knn_w = P.ptr(knn_w)
         b.relu_mask = P.ptr(relu_mask)
+        b.perm = P.ptr(perm)
         b.grad_sdf = P.ptr(g)
         g_feats = gW1 = gb1 = gW2 = gb2 = None
         if ctx.needs_input_grad[3]:

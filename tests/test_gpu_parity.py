@@ -173,3 +173,35 @@ def test_cpu_tensor_is_refused(maps):
     from pin_slam_b200 import _pinq as P
     with pytest.raises(P.PinqError):
         m.query_sdf(q, dec, None, False, True)
+
+
+def test_binned_processing_order_changes_nothing(maps):
+    """Spatial binning (csrc/sort.cu) only permutes the processing order: per-query outputs are bit-identical
+    to the unbinned run, the training side effects and all gradients agree to atomics-order tolerance."""
+    s, m, cfg, dec, d, _ = maps
+    q = make_queries(s.points, 50000, seed=11).cuda()  # ragged: not a multiple of 32
+    ts = torch.full((q.shape[0],), 2, dtype=torch.int64, device="cuda")
+    res = {}
+    cert0 = m.local_point_certainties.clone()
+    tsu0 = m.local_point_ts_update.clone()
+    for name, thr in (("plain", 1 << 60), ("binned", 0)):
+        m.bin_queries_min = thr
+        m.local_point_certainties = cert0.clone()
+        m.local_point_ts_update = tsu0.clone()
+        m.local_geo_features.grad = None
+        for p_ in dec.parameters():
+            p_.grad = None
+        out = m.query_sdf(q, dec, ts, True, True, want_grad=True, want_std=True, want_certainty=True)
+        (out["sdf"] * torch.linspace(0.5, 1.5, q.shape[0], device="cuda")).sum().backward()
+        res[name] = dict(out=out, gf=m.local_geo_features.grad.clone(), gd=[p_.grad.clone() for p_ in dec.parameters()],
+                         cert=m.local_point_certainties.clone(), tsu=m.local_point_ts_update.clone())
+    m.bin_queries_min = 32768
+    m.local_point_certainties, m.local_point_ts_update = cert0, tsu0
+    a, b = res["plain"], res["binned"]
+    for key in ("sdf", "nn_count", "grad", "std", "certainty"):
+        assert torch.equal(a["out"][key], b["out"][key]), key
+    assert torch.equal(a["tsu"], b["tsu"])
+    assert rel_err(b["cert"], a["cert"]) < 1e-6
+    assert rel_err(b["gf"], a["gf"]) < 1e-6
+    for x, y in zip(a["gd"], b["gd"]):
+        assert rel_err(y, x) < 1e-5
