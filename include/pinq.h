@@ -115,6 +115,19 @@ int pinq_index_pack(const int32_t* table, uint32_t buffer_size, const uint32_t* 
                     int64_t cur_ts, float diff_travel_dist_local, float* rec_global4, float* rec_local4,
                     void* stream);
 
+/* ---- brick index: spatially coherent read view (csrc/brick.cuh) ---------------------------------
+ * A brick = 4x4x4 voxels; open-addressing table keyed by brick coordinates -> {64-bit voxel occupancy,
+ * rank of the brick's first record}; records of a brick are contiguous.  Holds exactly the points that
+ * are findable through the slot table (table[slot(cell(p))] == p), so a lookup by voxel returns what
+ * the reference's probe of that voxel returns, minus far-collision aliases that the reference rejects
+ * by distance anyway (caller checks the no-near-collision property of buffer_size first).
+ * rec_*4 = slot-rank-ordered records of pinq_index_pack, d_count = *pinq_index_build count,
+ * tab = pinq_brick_capacity(m) * 32 bytes, d_counters2 = int32[2] {records placed, invariant violations}. */
+int64_t pinq_brick_capacity(int64_t m);
+int pinq_brick_build(const float* rec_global4, const float* rec_local4, const int32_t* d_count, int64_t m, float res,
+                     uint32_t flags, void* tab, uint32_t cap, int32_t* d_counters2, float* brick_rec_global4,
+                     float* brick_rec_local4, void* stream);
+
 /* ---- neighbour search -------------------------------------------------------------------- */
 typedef struct pinq_map_view {
     const uint32_t* occ;        /* [nwords][2] occupancy index (pinq_index_build)             */
@@ -126,6 +139,12 @@ typedef struct pinq_map_view {
     int32_t kn;                 /* stencil size (81 for run_kitti)                            */
     const int32_t* stencil_dx;  /* [kn,3] int32 neighbour cell offsets (neural_points.py:439) */
     int64_t m;                  /* number of neural points (global)                           */
+    /* optional brick index (pinq_brick_build); NULL = probe the slot view.  Used by the fused query
+       and the mesher; the API-form search / query_certainty always read the slot view. */
+    const void* brick_tab;      /* [brick_cap] 32-byte entries                                */
+    const float* brick_rec4;    /* [n_occupied][4] records in brick order (same flavour as rec4) */
+    uint32_t brick_cap;         /* power of two                                               */
+    int32_t stencil_radius;     /* max |dx| over the stencil (<= 2 for the brick path)        */
 } pinq_map_view;
 
 /* model/neural_points.py:459-509 -- standalone API form: writes dist2[n,kn] f32 and idx[n,kn] i64

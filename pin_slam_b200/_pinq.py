@@ -17,7 +17,8 @@ _vp, _i64, _i32, _u32, _u64, _f32 = C.c_void_p, C.c_int64, C.c_int32, C.c_uint32
 
 class MapView(C.Structure):
     _fields_ = [("occ", _vp), ("rec4", _vp), ("buffer_size", _u32), ("resolution", _f32), ("max_valid_dist2", _f32),
-                ("kn", _i32), ("stencil_dx", _vp), ("m", _i64)]
+                ("kn", _i32), ("stencil_dx", _vp), ("m", _i64), ("brick_tab", _vp), ("brick_rec4", _vp), ("brick_cap", _u32),
+                ("stencil_radius", _i32)]
 
 
 class DecoderView(C.Structure):
@@ -58,6 +59,8 @@ SIGNATURES = {
     "pinq_index_scratch_bytes": (_i64, [_u32]),
     "pinq_index_build": (C.c_int, [_vp, _u32, _vp, _vp, _vp, _vp]),
     "pinq_index_pack": (C.c_int, [_vp, _u32, _vp, _vp, _vp, _vp, _vp, _vp, _i64, _f32, _vp, _vp, _vp]),
+    "pinq_brick_capacity": (_i64, [_i64]),
+    "pinq_brick_build": (C.c_int, [_vp, _vp, _vp, _i64, _f32, _u32, _vp, _u32, _vp, _vp, _vp, _vp]),
     "pinq_query_workspace_bytes": (_i64, [_i64]),
     "pinq_relu_mask_words": (_i64, [_i64]),
     "pinq_neighbor_search": (C.c_int, [C.POINTER(MapView), _vp, _i64, _u32, _vp, _vp, _vp, _i64, _f32, C.c_int, _vp,

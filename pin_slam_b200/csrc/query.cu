@@ -8,6 +8,7 @@
 //              FP32-FMA bound; the decoder lives in shared memory, activations in registers.
 // Reference: model/neural_points.py:459-674, model/decoder.py:66-88, utils/tracker.py:245-253,
 //            utils/mapper.py:466-468, utils/mesher.py:93-180.
+#include "brick.cuh"
 #include "mma.cuh"
 
 namespace pinq {
@@ -94,6 +95,113 @@ __global__ void __launch_bounds__(kBlock) k_search(MapDev map, PointSrc src, int
     int32_t* o = ws + i * kWs;
 #pragma unroll
     for (int k = 0; k < K; ++k) o[k] = kr[k];
+    o[K] = nn;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Neighbour search through the brick index (csrc/brick.cuh): the stencil of a query touches 2 x 2 x 2 bricks;
+// per brick one probe, then only the OCCUPIED voxels inside the stencil box are visited (bit scan of the
+// 64-bit occupancy mask).  Same candidates, same exact d^2, same (d^2, stencil position) order as k_search.
+__device__ __forceinline__ void topk_insert(float d2, uint32_t key2, float (&kd2)[K], uint32_t (&kk)[K]) {
+    if (d2 < kd2[K - 1] || (d2 == kd2[K - 1] && key2 < kk[K - 1])) {
+        kd2[K - 1] = d2;
+        kk[K - 1] = key2;
+#pragma unroll
+        for (int k = K - 1; k > 0; --k) {
+            if (kd2[k] < kd2[k - 1] || (kd2[k] == kd2[k - 1] && kk[k] < kk[k - 1])) {
+                const float td = kd2[k]; kd2[k] = kd2[k - 1]; kd2[k - 1] = td;
+                const uint32_t tk = kk[k]; kk[k] = kk[k - 1]; kk[k - 1] = tk;
+            }
+        }
+    }
+}
+
+// per-axis part of the stencil box that falls into brick b (voxels o .. o+3): local range [lo, hi]
+__device__ __forceinline__ void axis_range(int c, int R, int b, int& lo, int& hi) {
+    const int o = b * 4;
+    lo = max(c - R - o, 0);
+    hi = min(c + R - o, 3);
+}
+
+constexpr uint32_t kRankBits = 24;  // key2 = stencil position << 24 | record rank (host guards m < 2^24)
+
+__global__ void __launch_bounds__(kBlock) k_search_brick(MapDev map, BrickDev bd, PointSrc src, int64_t n, bool recip,
+                                                         const int32_t* __restrict__ perm, int32_t* __restrict__ ws) {
+    __shared__ uint8_t s_sid[128];  // stencil position of offset (dx,dy,dz), 0xFF = not in the stencil
+    const int R = bd.radius, W = 2 * R + 1;
+    for (int c = threadIdx.x; c < 128; c += blockDim.x) s_sid[c] = 0xFF;
+    __syncthreads();
+    for (int c = threadIdx.x; c < map.kn; c += blockDim.x) {
+        const int dx = map.stencil_dx[3 * c], dy = map.stencil_dx[3 * c + 1], dz = map.stencil_dx[3 * c + 2];
+        s_sid[((dx + R) * W + (dy + R)) * W + (dz + R)] = (uint8_t)c;
+    }
+    __syncthreads();
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float x, y, z;
+    load_point(src, perm ? perm[i] : i, x, y, z);
+    const int cx = cell_of(x, map.res, map.inv_res, recip), cy = cell_of(y, map.res, map.inv_res, recip),
+              cz = cell_of(z, map.res, map.inv_res, recip);
+    const int b0x = (cx - R) >> 2, b0y = (cy - R) >> 2, b0z = (cz - R) >> 2;
+
+    float kd2[K];
+    uint32_t kk[K];
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+        kd2[k] = kInvalidD2;
+        kk[k] = 0xFFFFFFFFu;
+    }
+    int nn = 0;
+
+#pragma unroll 1
+    for (int ix = 0; ix < 2; ++ix) {
+        int lox, hix;
+        axis_range(cx, R, b0x + ix, lox, hix);
+        if (lox > hix) continue;
+        const unsigned long long xm = (hix == 3 ? ~0ull : ((1ull << (16 * (hix + 1))) - 1ull)) & ~((1ull << (16 * lox)) - 1ull);
+        // the four bricks of this x-slab: probe first, then walk
+        unsigned long long msk[4], sel[4];
+        uint32_t bas[4];
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+            const int iy = b >> 1, iz = b & 1;
+            msk[b] = sel[b] = 0ull;
+            bas[b] = 0u;
+            int loy, hiy, loz, hiz;
+            axis_range(cy, R, b0y + iy, loy, hiy);
+            axis_range(cz, R, b0z + iz, loz, hiz);
+            if (loy > hiy || loz > hiz) continue;
+            const int e = brick_find(bd.tab, bd.cap_mask, brick_key(b0x + ix, b0y + iy, b0z + iz));
+            if (e < 0) continue;
+            const uint4 v = __ldg(reinterpret_cast<const uint4*>(&bd.tab[e]));
+            msk[b] = ((unsigned long long)v.y << 32) | v.x;
+            bas[b] = v.z;
+            const uint32_t y16 = ((1u << (4 * (hiy + 1))) - 1u) & ~((1u << (4 * loy)) - 1u);
+            const uint32_t zn = (((1u << (hiz - loz + 1)) - 1u) << loz);
+            sel[b] = msk[b] & xm & (y16 * 0x0001000100010001ull) & (zn * 0x1111111111111111ull);
+        }
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+            const int ox = (b0x + ix) * 4 - cx + R, oy = (b0y + (b >> 1)) * 4 - cy + R, oz = (b0z + (b & 1)) * 4 - cz + R;
+            unsigned long long m = sel[b];
+            while (m) {
+                const int bit = __ffsll((long long)m) - 1;
+                m &= m - 1ull;
+                const int lin = ((ox + (bit >> 4)) * W + (oy + ((bit >> 2) & 3))) * W + (oz + (bit & 3));
+                const uint32_t sid = s_sid[lin];
+                if (sid == 0xFFu) continue;
+                const uint32_t rank = bas[b] + (uint32_t)__popcll(msk[b] & ((1ull << bit) - 1ull));
+                const float4 rc = __ldg(&bd.rec[rank]);
+                const float d2 = dist2_rn(rc.x, rc.y, rc.z, x, y, z);
+                if (__float_as_int(rc.w) == -1 || d2 > map.max_d2) continue;  // -2 = hazard H13, still a candidate
+                ++nn;
+                topk_insert(d2, (sid << kRankBits) | rank, kd2, kk);
+            }
+        }
+    }
+    int32_t* o = ws + i * kWs;
+#pragma unroll
+    for (int k = 0; k < K; ++k) o[k] = kk[k] == 0xFFFFFFFFu ? -1 : (int32_t)(kk[k] & ((1u << kRankBits) - 1u));
     o[K] = nn;
 }
 
@@ -311,11 +419,11 @@ __global__ void __launch_bounds__(kBlock, GRAD ? 3 : 4) k_decode_mma(const Decod
                     const uint32_t bh0 = __float_as_uint(wa.x), bh1 = __float_as_uint(wa.y);
                     const uint32_t bl0 = __float_as_uint(wa.z), bl1 = __float_as_uint(wa.w);
                     const uint32_t ch = __float_as_uint(wb.x), cl = __float_as_uint(wb.y);
-                    // small terms first: lo*hi, hi*lo, then hi*hi
+                    // the three products of 3xTF32 concatenated along K: [lo | hi | hi] x [hi ; lo ; hi] = 36 real
+                    // columns in 5 k-steps (small terms first)
                     mma_tf32(acc[nt], al[0], al[1], al[2], al[3], bh0, bh1);
-                    mma_tf32(acc[nt], al[4], al[5], 0u, 0u, ch, 0u);
-                    mma_tf32(acc[nt], ah[0], ah[1], ah[2], ah[3], bl0, bl1);
-                    mma_tf32(acc[nt], ah[4], ah[5], 0u, 0u, cl, 0u);
+                    mma_tf32(acc[nt], al[4], al[5], ah[0], ah[1], ch, bl0);
+                    mma_tf32(acc[nt], ah[2], ah[3], ah[4], ah[5], bl1, cl);
                     mma_tf32(acc[nt], ah[0], ah[1], ah[2], ah[3], bh0, bh1);
                     mma_tf32(acc[nt], ah[4], ah[5], 0u, 0u, ch, 0u);
                 }
@@ -463,12 +571,27 @@ static int run_query(const pinq_query_args* a, int mode, float* feat_out, const 
         if (rc) return rc;
         perm = a->perm;
     }
-    k_search<<<grid_for(n, kBlock), kBlock, map.kn * sizeof(uint32_t), st>>>(map, src, n, recip, perm, ws);
+    const bool brick = a->map.brick_tab != nullptr;
+    BrickDev bd;
+    if (brick) {
+        if (!a->map.brick_rec4 || a->map.brick_cap < 1024 || (a->map.brick_cap & (a->map.brick_cap - 1)) ||
+            a->map.stencil_radius < 0 || a->map.stencil_radius > 2 || map.kn > 125 || a->map.m >= (1ll << kRankBits)) {
+            set_error("bad brick view (needs records, power-of-two capacity, stencil radius <= 2, m < 2^24)");
+            return PINQ_ERR_BAD_ARG;
+        }
+        bd.tab = reinterpret_cast<const BrickEntry*>(a->map.brick_tab);
+        bd.cap_mask = a->map.brick_cap - 1;
+        bd.rec = reinterpret_cast<const float4*>(a->map.brick_rec4);
+        bd.radius = a->map.stencil_radius;
+        k_search_brick<<<grid_for(n, kBlock), kBlock, 0, st>>>(map, bd, src, n, recip, perm, ws);
+    } else {
+        k_search<<<grid_for(n, kBlock), kBlock, map.kn * sizeof(uint32_t), st>>>(map, src, n, recip, perm, ws);
+    }
     rc = check_launch("k_search");
     if (rc) return rc;
 
     DecodeParams p;
-    p.rec = map.rec; p.max_d2 = map.max_d2; p.dec = a->dec; p.src = src; p.n = n;
+    p.rec = brick ? bd.rec : map.rec; p.max_d2 = map.max_d2; p.dec = a->dec; p.src = src; p.n = n;
     p.rotate = (a->flags & PINQ_F_ROTATE) != 0;
     // Exactness of the queried certainty in training mode needs all reads before any scatter: if the
     // caller wants it (and gave knn buffers), scatter in a second kernel; otherwise fuse the atomics.

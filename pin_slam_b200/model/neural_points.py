@@ -14,6 +14,7 @@ Differences in representation (results identical):
 """
 from __future__ import annotations
 
+import os
 import sys
 
 import torch
@@ -97,6 +98,13 @@ class NeuralPoints(nn.Module):
         self._occ = None
         self._ws = None
         self.bin_queries_min = 32768  # fused queries of at least this many points are binned by brick first
+        # fused search through the brick index when it is provably equivalent (PINQ_BRICK=0: slot probing only)
+        self.use_brick_index = os.environ.get("PINQ_BRICK", "1") != "0"
+        self._brick_tab = self._brick_global = self._brick_local = self._brick_buf = self._brick_counters = None
+        self._brick_host = self._brick_event = None
+        self._brick_cap = 0
+        self._brick_pending = False
+        self._brick_safe_cache, self._stencil_radius = {}, 0
         self.set_search_neighborhood(num_nei_cells=config.num_nei_cells, search_alpha=config.search_alpha)
         self.memory_footprint = []
         self.to(self.device)
@@ -337,6 +345,7 @@ class NeuralPoints(nn.Module):
         dx2 = torch.sum(dx ** 2, dim=-1)
         self.neighbor_dx = dx[dx2 < (num_nei_cells + search_alpha) ** 2]
         self.neighbor_K = self.neighbor_dx.shape[0]
+        self._stencil_radius = int(num_nei_cells)
         self.max_valid_dist2 = 3 * ((num_nei_cells + 1) * self.resolution) ** 2
         self._stencil_i32 = self.neighbor_dx.to(torch.int32).contiguous()
 
@@ -374,16 +383,80 @@ class NeuralPoints(nn.Module):
                                         P.ptr(self._travel_dist) if have_local else None, int(self.cur_ts),
                                         float(self.diff_travel_dist_local), P.ptr(self._cand_global),
                                         P.ptr(self._cand_local) if have_local else None, st))
+        self._build_bricks(m, have_local, st)
         self._cand_dirty = False
+
+    # ---- brick index (csrc/brick.cuh) --------------------------------------------------------------
+    def _brick_safe(self) -> bool:
+        """The brick view equals the slot view iff every far-collision alias is rejected by the distance test,
+        i.e. no two voxels closer than radius + ceil(sqrt(max_valid_dist2)/res) + 1 share a slot.  A property
+        of (primes, buffer_size) only; checked once per (buffer_size, stencil) on the host, no device sync."""
+        radius = int(self._stencil_radius)
+        key = (int(self.buffer_size), radius, int(self.neighbor_K), float(self.max_valid_dist2), float(self.resolution))
+        ok = self._brick_safe_cache.get(key)
+        if ok is None:
+            ok = radius <= 2 and self.neighbor_K <= 125
+            if ok:
+                import math
+                rc = radius + int(math.ceil(math.sqrt(float(self.max_valid_dist2)) / float(self.resolution))) + 1
+                d = torch.arange(-rc, rc + 1, dtype=torch.int64)
+                off = torch.stack(torch.meshgrid(d, d, d, indexing="ij"), dim=-1).reshape(-1, 3)
+                primes = torch.tensor([73856093, 19349669, 83492791], dtype=torch.int64)
+                h = torch.remainder((off * primes).sum(-1), int(self.buffer_size))
+                ok = int((h == 0).sum()) == 1  # only the zero offset maps to slot difference 0
+            self._brick_safe_cache[key] = bool(ok)
+        return bool(ok)
+
+    def _build_bricks(self, m: int, have_local: bool, st):
+        self._brick_tab = self._brick_global = self._brick_local = None
+        if not self.use_brick_index or m == 0 or m >= (1 << 24) or not self._brick_safe():
+            return
+        lib = P.load()
+        self.check_index_invariants(block=False)
+        cap = int(lib.pinq_brick_capacity(m))
+        if self._brick_buf is None or self._brick_buf.numel() != cap * 32:
+            self._brick_buf = torch.empty(cap * 32, dtype=torch.uint8, device=self.device)
+            self._brick_counters = torch.zeros(2, dtype=torch.int32, device=self.device)
+        self._brick_global = torch.empty((m, 4), dtype=torch.float32, device=self.device)
+        self._brick_local = torch.empty((m, 4), dtype=torch.float32, device=self.device) if have_local else None
+        P.check(lib.pinq_brick_build(P.ptr(self._cand_global), P.ptr(self._cand_local) if have_local else None,
+                                     P.ptr(self._occ_count), m, float(self.resolution), 0, P.ptr(self._brick_buf), cap,
+                                     P.ptr(self._brick_counters), P.ptr(self._brick_global),
+                                     P.ptr(self._brick_local) if have_local else None, st))
+        self._brick_tab, self._brick_cap = self._brick_buf, cap
+        self._brick_pending = True
+
+    def check_index_invariants(self, block: bool = True):
+        """Raises if the last brick build saw two findable points in one voxel (the slot table and the point
+        positions disagree, e.g. points were moved without recreate_hash).  Non-blocking callers check the
+        counters of the PREVIOUS build, so the hot path never waits for the device."""
+        if not getattr(self, "_brick_pending", False) or self._brick_counters is None:
+            return
+        if not block:
+            if self._brick_host is None:
+                self._brick_host = torch.zeros(2, dtype=torch.int32).pin_memory()
+                self._brick_event = torch.cuda.Event()
+            elif self._brick_event.query() and int(self._brick_host[1]) != 0:
+                raise P.PinqError("brick index: %d voxels hold two findable points" % int(self._brick_host[1]))
+            self._brick_host.copy_(self._brick_counters, non_blocking=True)
+            self._brick_event.record()
+            return
+        bad = int(self._brick_counters[1].item())
+        if bad:
+            raise P.PinqError("brick index: %d voxels hold two findable points" % bad)
 
     def _map_view(self, local: bool) -> P.MapView:
         self._refresh_candidates()
         rec = self._cand_local if local else self._cand_global
         if local and rec is None:
             raise P.PinqError("local query before reset_local_map()/travel_dist were set")
+        brec = self._brick_local if local else self._brick_global
+        use_brick = self._brick_tab is not None and brec is not None and self._brick_safe()
         return P.MapView(P.ptr(self._occ), P.ptr(rec), self.buffer_size, float(self.resolution),
                          float(self.max_valid_dist2), int(self.neighbor_K), P.ptr(self._stencil_i32),
-                         int(self.neural_points.shape[0]))
+                         int(self.neural_points.shape[0]), P.ptr(self._brick_tab) if use_brick else None,
+                         P.ptr(brec) if use_brick else None, int(self._brick_cap) if use_brick else 0,
+                         int(self._stencil_radius) if use_brick else 0)
 
     def _workspace(self, n: int):
         nbytes = int(P.load().pinq_query_workspace_bytes(n))
@@ -499,6 +572,9 @@ class NeuralPoints(nn.Module):
         self._occ = None
         self._occ_scratch = None
         self._occ_count = None
+        self._brick_tab = self._brick_global = self._brick_local = self._brick_buf = self._brick_counters = None
+        self._brick_host = self._brick_event = None
+        self._brick_pending = False
         self._ws = None
         self._ts_keepalive = None
         self._local_idx = None

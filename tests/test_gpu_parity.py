@@ -205,3 +205,31 @@ def test_binned_processing_order_changes_nothing(maps):
     assert rel_err(b["gf"], a["gf"]) < 1e-6
     for x, y in zip(a["gd"], b["gd"]):
         assert rel_err(y, x) < 1e-5
+
+
+def test_brick_index_equals_slot_probing(maps):
+    """The brick index (csrc/brick.cuh) is a read view of the same table: the fused query through it returns
+    bit-identical per-query results to the 81-probe slot path, for local and global queries."""
+    s, m, cfg, dec, d, _ = maps
+    q = make_queries(s.points, 40000, seed=5).cuda()
+    assert m._brick_safe(), "run_kitti buffer_size has no near collisions"
+    res = {}
+    for use in (False, True):
+        m.use_brick_index = use
+        m._cand_dirty = True
+        for local in (True, False):
+            with torch.no_grad():
+                out = m.query_sdf(q, dec, None, False, local, want_grad=True, want_std=True, want_certainty=True)
+            view = m._map_view(local)
+            assert bool(view.brick_tab) == use
+            res[(use, local)] = out
+    m.check_index_invariants()
+    for local in (True, False):
+        a, b = res[(False, local)], res[(True, local)]
+        for key in ("sdf", "nn_count", "grad", "std", "certainty"):
+            assert torch.equal(a[key], b[key]), (local, key)
+    # every local slot record is present exactly once in brick order
+    n_occ = int(m._occ_count.item())
+    assert int(m._brick_counters[0].item()) == n_occ
+    assert torch.equal(torch.sort(m._cand_global[:n_occ, 3].view(torch.int32)).values,
+                       torch.sort(m._brick_global[:n_occ, 3].view(torch.int32)).values)
