@@ -380,7 +380,7 @@ def main():
                 "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(args, npts, vbar),
                 "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e,
-                "gpu_launches": 6 * args.steps, "clocks": clocks}
+                "gpu_launches": 8 * args.steps, "clocks": clocks}
         line["config"]["parallelism"] = "replicated map, queries sharded x%d%s" % (
             world, ", NCCL all-reduce of feature+decoder grads" if world > 1 else "")
         print(json.dumps(line))

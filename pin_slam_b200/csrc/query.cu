@@ -100,108 +100,140 @@ __global__ void __launch_bounds__(kBlock) k_search(MapDev map, PointSrc src, int
 
 // ---------------------------------------------------------------------------------------------
 // Neighbour search through the brick index (csrc/brick.cuh): the stencil of a query touches 2 x 2 x 2 bricks;
-// per brick one probe, then only the OCCUPIED voxels inside the stencil box are visited (bit scan of the
-// 64-bit occupancy mask).  Same candidates, same exact d^2, same (d^2, stencil position) order as k_search.
-__device__ __forceinline__ void topk_insert(float d2, uint32_t key2, float (&kd2)[K], uint32_t (&kk)[K]) {
-    if (d2 < kd2[K - 1] || (d2 == kd2[K - 1] && key2 < kk[K - 1])) {
-        kd2[K - 1] = d2;
-        kk[K - 1] = key2;
-#pragma unroll
-        for (int k = K - 1; k > 0; --k) {
-            if (kd2[k] < kd2[k - 1] || (kd2[k] == kd2[k - 1] && kk[k] < kk[k - 1])) {
-                const float td = kd2[k]; kd2[k] = kd2[k - 1]; kd2[k - 1] = td;
-                const uint32_t tk = kk[k]; kk[k] = kk[k - 1]; kk[k - 1] = tk;
-            }
+// per brick one probe, then only the OCCUPIED voxels that belong to the stencil are visited (bit scan of
+// occupancy & stencil mask).  Same candidates, same exact d^2, same (d^2, stencil position) order as k_search.
+//
+// Stencil masks: for a query whose stencil box starts at voxel (sx, sy, sz) of brick b0 (s = (cell - R) & 3)
+// and for brick b0 + (ix, iy, iz), the 64-bit set of brick voxels that are stencil members.  64 x 8 masks,
+// built once per launch (k_stencil_masks) and staged in shared memory.
+constexpr int kStencilMasks = 64 * 8;
+constexpr uint32_t kRankBits = 24;  // low key word = stencil position << 24 | record rank (host guards m < 2^24)
+
+__global__ void k_stencil_masks(const int32_t* __restrict__ stencil_dx, int kn, int R, unsigned long long* __restrict__ out) {
+    __shared__ uint8_t member[128];
+    const int W = 2 * R + 1;
+    for (int c = threadIdx.x; c < 128; c += blockDim.x) member[c] = 0;
+    __syncthreads();
+    for (int c = threadIdx.x; c < kn; c += blockDim.x)
+        member[((stencil_dx[3 * c] + R) * W + (stencil_dx[3 * c + 1] + R)) * W + (stencil_dx[3 * c + 2] + R)] = 1;
+    __syncthreads();
+    for (int e = threadIdx.x; e < kStencilMasks; e += blockDim.x) {
+        const int sx = (e >> 7) & 3, sy = (e >> 5) & 3, sz = (e >> 3) & 3, ix = (e >> 2) & 1, iy = (e >> 1) & 1, iz = e & 1;
+        unsigned long long m = 0ull;
+        for (int bit = 0; bit < 64; ++bit) {
+            // offset of brick voxel (lx,ly,lz) from the box origin, per axis: 4 i + l - s  in [0, 2R] for members
+            const int ox = 4 * ix + (bit >> 4) - sx, oy = 4 * iy + ((bit >> 2) & 3) - sy, oz = 4 * iz + (bit & 3) - sz;
+            if (ox < 0 || oy < 0 || oz < 0 || ox >= W || oy >= W || oz >= W) continue;
+            if (member[(ox * W + oy) * W + oz]) m |= 1ull << bit;
         }
+        out[e] = m;
     }
 }
 
-// per-axis part of the stencil box that falls into brick b (voxels o .. o+3): local range [lo, hi]
-__device__ __forceinline__ void axis_range(int c, int R, int b, int& lo, int& hi) {
-    const int o = b * 4;
-    lo = max(c - R - o, 0);
-    hi = min(c + R - o, 3);
+// sorted insertion of a 64-bit key (d^2 bits : stencil position : rank) into the ascending top-K
+__device__ __forceinline__ void topk_insert64(unsigned long long key, unsigned long long (&kk)[K]) {
+#pragma unroll
+    for (int k = K - 1; k > 0; --k) {
+        // after the step slot k holds the k-th smallest of {old slots, key}
+        const unsigned long long lo = kk[k - 1], cur = kk[k];
+        kk[k] = key < lo ? lo : (key < cur ? key : cur);
+    }
+    kk[0] = key < kk[0] ? key : kk[0];
 }
 
-constexpr uint32_t kRankBits = 24;  // key2 = stencil position << 24 | record rank (host guards m < 2^24)
+struct BrickLane {  // per-lane walk state of one brick, staged in shared memory ([brick][thread], conflict-free)
+    unsigned long long msk[8][kBlock];
+    unsigned long long sel[8][kBlock];
+    uint32_t bas[8][kBlock];
+};
 
 __global__ void __launch_bounds__(kBlock) k_search_brick(MapDev map, BrickDev bd, PointSrc src, int64_t n, bool recip,
-                                                         const int32_t* __restrict__ perm, int32_t* __restrict__ ws) {
-    __shared__ uint8_t s_sid[128];  // stencil position of offset (dx,dy,dz), 0xFF = not in the stencil
-    const int R = bd.radius, W = 2 * R + 1;
-    for (int c = threadIdx.x; c < 128; c += blockDim.x) s_sid[c] = 0xFF;
+                                                         const int32_t* __restrict__ perm,
+                                                         const unsigned long long* __restrict__ stencil_masks,
+                                                         int32_t* __restrict__ ws) {
+    extern __shared__ __align__(16) unsigned char s_brick_raw[];
+    BrickLane* bl = reinterpret_cast<BrickLane*>(s_brick_raw);
+    unsigned long long* s_masks = reinterpret_cast<unsigned long long*>(s_brick_raw + sizeof(BrickLane));
+    uint8_t* s_sid = reinterpret_cast<uint8_t*>(s_masks + kStencilMasks);  // stencil position of offset (dx,dy,dz)
+    const int R = bd.radius, W = 2 * R + 1, tid = threadIdx.x;
+    for (int c = tid; c < kStencilMasks; c += blockDim.x) s_masks[c] = stencil_masks[c];
+    for (int c = tid; c < 128; c += blockDim.x) s_sid[c] = 0xFF;
     __syncthreads();
-    for (int c = threadIdx.x; c < map.kn; c += blockDim.x) {
+    for (int c = tid; c < map.kn; c += blockDim.x) {
         const int dx = map.stencil_dx[3 * c], dy = map.stencil_dx[3 * c + 1], dz = map.stencil_dx[3 * c + 2];
         s_sid[((dx + R) * W + (dy + R)) * W + (dz + R)] = (uint8_t)c;
     }
     __syncthreads();
-    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    float x, y, z;
-    load_point(src, perm ? perm[i] : i, x, y, z);
+
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + tid;
+    const bool live = i < n;
+    float x = 0.f, y = 0.f, z = 0.f;
+    if (live) load_point(src, perm ? perm[i] : i, x, y, z);
     const int cx = cell_of(x, map.res, map.inv_res, recip), cy = cell_of(y, map.res, map.inv_res, recip),
               cz = cell_of(z, map.res, map.inv_res, recip);
-    const int b0x = (cx - R) >> 2, b0y = (cy - R) >> 2, b0z = (cz - R) >> 2;
+    const int ax = cx - R, ay = cy - R, az = cz - R;  // box origin
+    const int b0x = ax >> 2, b0y = ay >> 2, b0z = az >> 2;
+    const int srow = (((ax & 3) * 4 + (ay & 3)) * 4 + (az & 3)) * 8;
 
-    float kd2[K];
-    uint32_t kk[K];
+    // phase 1: one probe per brick, all eight issued before any is used
+    int total = 0;
 #pragma unroll
-    for (int k = 0; k < K; ++k) {
-        kd2[k] = kInvalidD2;
-        kk[k] = 0xFFFFFFFFu;
-    }
-    int nn = 0;
-
-#pragma unroll 1
-    for (int ix = 0; ix < 2; ++ix) {
-        int lox, hix;
-        axis_range(cx, R, b0x + ix, lox, hix);
-        if (lox > hix) continue;
-        const unsigned long long xm = (hix == 3 ? ~0ull : ((1ull << (16 * (hix + 1))) - 1ull)) & ~((1ull << (16 * lox)) - 1ull);
-        // the four bricks of this x-slab: probe first, then walk
-        unsigned long long msk[4], sel[4];
-        uint32_t bas[4];
-#pragma unroll
-        for (int b = 0; b < 4; ++b) {
-            const int iy = b >> 1, iz = b & 1;
-            msk[b] = sel[b] = 0ull;
-            bas[b] = 0u;
-            int loy, hiy, loz, hiz;
-            axis_range(cy, R, b0y + iy, loy, hiy);
-            axis_range(cz, R, b0z + iz, loz, hiz);
-            if (loy > hiy || loz > hiz) continue;
-            const int e = brick_find(bd.tab, bd.cap_mask, brick_key(b0x + ix, b0y + iy, b0z + iz));
-            if (e < 0) continue;
-            const uint4 v = __ldg(reinterpret_cast<const uint4*>(&bd.tab[e]));
-            msk[b] = ((unsigned long long)v.y << 32) | v.x;
-            bas[b] = v.z;
-            const uint32_t y16 = ((1u << (4 * (hiy + 1))) - 1u) & ~((1u << (4 * loy)) - 1u);
-            const uint32_t zn = (((1u << (hiz - loz + 1)) - 1u) << loz);
-            sel[b] = msk[b] & xm & (y16 * 0x0001000100010001ull) & (zn * 0x1111111111111111ull);
-        }
-#pragma unroll
-        for (int b = 0; b < 4; ++b) {
-            const int ox = (b0x + ix) * 4 - cx + R, oy = (b0y + (b >> 1)) * 4 - cy + R, oz = (b0z + (b & 1)) * 4 - cz + R;
-            unsigned long long m = sel[b];
-            while (m) {
-                const int bit = __ffsll((long long)m) - 1;
-                m &= m - 1ull;
-                const int lin = ((ox + (bit >> 4)) * W + (oy + ((bit >> 2) & 3))) * W + (oz + (bit & 3));
-                const uint32_t sid = s_sid[lin];
-                if (sid == 0xFFu) continue;
-                const uint32_t rank = bas[b] + (uint32_t)__popcll(msk[b] & ((1ull << bit) - 1ull));
-                const float4 rc = __ldg(&bd.rec[rank]);
-                const float d2 = dist2_rn(rc.x, rc.y, rc.z, x, y, z);
-                if (__float_as_int(rc.w) == -1 || d2 > map.max_d2) continue;  // -2 = hazard H13, still a candidate
-                ++nn;
-                topk_insert(d2, (sid << kRankBits) | rank, kd2, kk);
+    for (int b = 0; b < 8; ++b) {
+        unsigned long long msk = 0ull, sel = 0ull;
+        uint32_t bas = 0u;
+        const unsigned long long want = s_masks[srow + b];
+        if (live && want) {
+            const int e = brick_find(bd.tab, bd.cap_mask, brick_key(b0x + (b >> 2), b0y + ((b >> 1) & 1), b0z + (b & 1)));
+            if (e >= 0) {
+                const uint4 v = __ldg(reinterpret_cast<const uint4*>(&bd.tab[e]));
+                msk = ((unsigned long long)v.y << 32) | v.x;
+                bas = v.z;
+                sel = msk & want;
             }
         }
+        bl->msk[b][tid] = msk;
+        bl->sel[b][tid] = sel;
+        bl->bas[b][tid] = bas;
+        total += __popcll(sel);
     }
+
+    // phase 2: ONE loop over the lane's candidates of all bricks (trip count = max over the warp of `total`,
+    // not the sum over bricks of per-brick maxima); bodies are predicated so the warp stays converged
+    unsigned long long kk[K];
+#pragma unroll
+    for (int k = 0; k < K; ++k) kk[k] = ~0ull;
+    int nn = 0, b = -1;
+    unsigned long long m = 0ull, msk = 0ull;
+    uint32_t bas = 0u;
+    int ox = 0, oy = 0, oz = 0;
+    while (__any_sync(0xffffffffu, total > 0)) {
+        const bool act = total > 0;
+        while (act && m == 0ull) {  // next brick with candidates (at most 8 steps over the whole walk)
+            ++b;
+            m = bl->sel[b][tid];
+            msk = bl->msk[b][tid];
+            bas = bl->bas[b][tid];
+            ox = 4 * (b >> 2) - (ax & 3); oy = 4 * ((b >> 1) & 1) - (ay & 3); oz = 4 * (b & 1) - (az & 3);
+        }
+        --total;
+        const int bit = act ? __ffsll((long long)m) - 1 : 0;
+        m &= m - 1ull;  // 0 stays 0
+        const uint32_t rank = bas + (uint32_t)__popcll(msk & ((1ull << bit) - 1ull));
+        float4 rc = make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
+        if (act) rc = __ldg(&bd.rec[rank]);
+        const int lin = ((ox + (bit >> 4)) * W + (oy + ((bit >> 2) & 3))) * W + (oz + (bit & 3));
+        const uint32_t sid = s_sid[lin & 127];
+        const float d2 = dist2_rn(rc.x, rc.y, rc.z, x, y, z);
+        // valid: index != -1 (-2 = hazard H13, still a candidate) and not d2 > max (neural_points.py:499)
+        const bool ok = act && __float_as_int(rc.w) != -1 && !(d2 > map.max_d2);
+        nn += ok ? 1 : 0;
+        const unsigned long long key = ok ? ((unsigned long long)__float_as_uint(d2) << 32) | (sid << kRankBits) | rank : ~0ull;
+        topk_insert64(key, kk);
+    }
+    if (!live) return;
     int32_t* o = ws + i * kWs;
 #pragma unroll
-    for (int k = 0; k < K; ++k) o[k] = kk[k] == 0xFFFFFFFFu ? -1 : (int32_t)(kk[k] & ((1u << kRankBits) - 1u));
+    for (int k = 0; k < K; ++k) o[k] = kk[k] == ~0ull ? -1 : (int32_t)((uint32_t)kk[k] & ((1u << kRankBits) - 1u));
     o[K] = nn;
 }
 
@@ -583,7 +615,11 @@ static int run_query(const pinq_query_args* a, int mode, float* feat_out, const 
         bd.cap_mask = a->map.brick_cap - 1;
         bd.rec = reinterpret_cast<const float4*>(a->map.brick_rec4);
         bd.radius = a->map.stencil_radius;
-        k_search_brick<<<grid_for(n, kBlock), kBlock, 0, st>>>(map, bd, src, n, recip, perm, ws);
+        unsigned long long* smasks = reinterpret_cast<unsigned long long*>(
+            reinterpret_cast<unsigned char*>(a->workspace) + ws_bytes(n) + bin_scratch_bytes(n));
+        k_stencil_masks<<<1, 256, 0, st>>>(map.stencil_dx, map.kn, bd.radius, smasks);
+        const size_t smem = sizeof(BrickLane) + kStencilMasks * 8 + 128;
+        k_search_brick<<<grid_for(n, kBlock), kBlock, smem, st>>>(map, bd, src, n, recip, perm, smasks, ws);
     } else {
         k_search<<<grid_for(n, kBlock), kBlock, map.kn * sizeof(uint32_t), st>>>(map, src, n, recip, perm, ws);
     }
@@ -632,7 +668,9 @@ using namespace pinq;
 
 extern "C" {
 
-int64_t pinq_query_workspace_bytes(int64_t n) { return ws_bytes(n) + bin_scratch_bytes(n > 0 ? n : 1); }
+int64_t pinq_query_workspace_bytes(int64_t n) {
+    return ws_bytes(n) + bin_scratch_bytes(n > 0 ? n : 1) + kStencilMasks * 8;
+}
 
 int64_t pinq_relu_mask_words(int64_t n) { return ((n > 0 ? n : 1) + 31) / 32 * (int64_t)kMTiles * 32; }
 

@@ -1,4 +1,4 @@
-// sort.cu -- spatial binning of a query batch (one-pass counting sort on a 16-bit brick key).
+// sort.cu -- spatial binning of a query batch (one-pass counting sort on a 21-bit brick key).
 //
 // ncu on the unsorted batch (profiles/r1d_*): the decode and backward kernels wait on gathers that miss
 // L1 and half of L2 (1.5-2.2 GB of DRAM reads per 4 Mi queries for 53 MB of features), and the search is
@@ -7,42 +7,37 @@
 // reads its inputs and writes its per-query outputs through perm[], so results are those of the unsorted
 // batch.  The order inside a bin is whatever the atomics produce -- no output depends on it.
 //   k_bin_count   key[i] = brick key of query i, hist[key]++
-//   k_bin_scan    exclusive scan of the 65536 counters (one CTA)
+//   k_bin_tile_*  exclusive scan of the 2^21 counters (tile sums, scan of the sums, per-tile prefix)
 //   k_bin_scatter perm[cursor[key[i]]++] = i
 #include "query_common.cuh"
 
 namespace pinq {
 
-constexpr int kBinBits = 16;
+constexpr int kBinBits = 21;
 constexpr int kBins = 1 << kBinBits;
+constexpr int kScanTile = 1024;
+constexpr int kScanTiles = kBins / kScanTile;  // 2048
 
-__device__ __forceinline__ uint32_t brick_key16(int gx, int gy, int gz) {
-    // 6 + 6 + 4 bits of the brick coordinates (cell >> 2): bins alias with a period of 102 m / 102 m / 26 m,
-    // which only interleaves far-apart bricks in the processing order
-    return (uint32_t)((gx >> 2) & 63) | ((uint32_t)((gy >> 2) & 63) << 6) | ((uint32_t)((gz >> 2) & 15) << 12);
+__device__ __forceinline__ uint32_t brick_key21(int gx, int gy, int gz) {
+    // 8 + 8 + 5 bits of the brick coordinates (cell >> 2), x fastest: one bin = one brick up to a period of
+    // 410 m / 410 m / 51 m (aliases only interleave far-apart bricks in the processing order)
+    return (uint32_t)((gx >> 2) & 255) | ((uint32_t)((gy >> 2) & 255) << 8) | ((uint32_t)((gz >> 2) & 31) << 16);
 }
 
 __global__ void k_bin_count(const float* __restrict__ xyz, int64_t n, float res, float inv_res, bool recip,
-                            uint16_t* __restrict__ keys, uint32_t* __restrict__ hist) {
+                            uint32_t* __restrict__ keys, uint32_t* __restrict__ hist) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    const uint32_t key = brick_key16(cell_of(xyz[3 * i], res, inv_res, recip), cell_of(xyz[3 * i + 1], res, inv_res, recip),
+    const uint32_t key = brick_key21(cell_of(xyz[3 * i], res, inv_res, recip), cell_of(xyz[3 * i + 1], res, inv_res, recip),
                                      cell_of(xyz[3 * i + 2], res, inv_res, recip));
-    keys[i] = (uint16_t)key;
+    keys[i] = key;
     atomicAdd(&hist[key], 1u);
 }
 
-__global__ void __launch_bounds__(1024) k_bin_scan(uint32_t* __restrict__ hist) {
-    __shared__ uint32_t wsum[32];
-    constexpr int per = kBins / 1024;
-    uint32_t v[per], s = 0;
-#pragma unroll
-    for (int j = 0; j < per; ++j) {
-        v[j] = hist[threadIdx.x * per + j];
-        s += v[j];
-    }
+// block-wide exclusive scan of one value per thread (1024 threads); returns the exclusive prefix, total in *tot
+__device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t* wsum, uint32_t* tot) {
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    uint32_t incl = s;
+    uint32_t incl = v;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
         const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
@@ -50,40 +45,63 @@ __global__ void __launch_bounds__(1024) k_bin_scan(uint32_t* __restrict__ hist) 
     }
     if (lane == 31) wsum[w] = incl;
     __syncthreads();
-    if (threadIdx.x < 32) {
-        const uint32_t x = wsum[threadIdx.x];
+    if (w == 0) {
+        const uint32_t x = wsum[lane];
         uint32_t wi = x;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
             const uint32_t t = __shfl_up_sync(0xffffffffu, wi, o);
-            if (threadIdx.x >= o) wi += t;
+            if (lane >= o) wi += t;
         }
-        wsum[threadIdx.x] = wi - x;
+        wsum[lane] = wi - x;
+        if (lane == 31 && tot) *tot = wi;
     }
     __syncthreads();
-    uint32_t run = wsum[w] + incl - s;
-#pragma unroll
-    for (int j = 0; j < per; ++j) {
-        hist[threadIdx.x * per + j] = run;
-        run += v[j];
-    }
+    return wsum[w] + incl - v;
 }
 
-__global__ void k_bin_scatter(const uint16_t* __restrict__ keys, int64_t n, uint32_t* __restrict__ cursor,
+__global__ void __launch_bounds__(kScanTile) k_bin_tile_sums(const uint32_t* __restrict__ hist, uint32_t* __restrict__ tiles) {
+    __shared__ uint32_t wsum[32];
+    __shared__ uint32_t tot;
+    block_excl_scan(hist[blockIdx.x * kScanTile + threadIdx.x], wsum, &tot);
+    __syncthreads();
+    if (threadIdx.x == 0) tiles[blockIdx.x] = tot;
+}
+
+__global__ void __launch_bounds__(kScanTile) k_bin_tile_scan(uint32_t* __restrict__ tiles) {  // one CTA, 2048 tile sums
+    __shared__ uint32_t wsum[32];
+    __shared__ uint32_t tot;
+    const uint32_t a = tiles[2 * threadIdx.x], b = tiles[2 * threadIdx.x + 1];
+    const uint32_t ex = block_excl_scan(a + b, wsum, &tot);
+    tiles[2 * threadIdx.x] = ex;
+    tiles[2 * threadIdx.x + 1] = ex + a;
+}
+
+__global__ void __launch_bounds__(kScanTile) k_bin_tile_apply(uint32_t* __restrict__ hist, const uint32_t* __restrict__ tiles) {
+    __shared__ uint32_t wsum[32];
+    const uint32_t idx = blockIdx.x * kScanTile + threadIdx.x;
+    const uint32_t ex = block_excl_scan(hist[idx], wsum, nullptr);
+    hist[idx] = tiles[blockIdx.x] + ex;
+}
+
+__global__ void k_bin_scatter(const uint32_t* __restrict__ keys, int64_t n, uint32_t* __restrict__ cursor,
                               int32_t* __restrict__ perm) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     perm[atomicAdd(&cursor[keys[i]], 1u)] = (int32_t)i;
 }
 
-int64_t bin_scratch_bytes(int64_t n) { return (int64_t)kBins * 4 + ((n * 2 + 15) / 16) * 16; }
+int64_t bin_scratch_bytes(int64_t n) { return (int64_t)(kBins + kScanTiles) * 4 + ((n * 4 + 15) / 16) * 16; }
 
 int launch_spatial_bin(const float* xyz, int64_t n, float res, bool recip, void* scratch, int32_t* perm, cudaStream_t st) {
     uint32_t* hist = reinterpret_cast<uint32_t*>(scratch);
-    uint16_t* keys = reinterpret_cast<uint16_t*>(hist + kBins);
+    uint32_t* tiles = hist + kBins;
+    uint32_t* keys = tiles + kScanTiles;
     cudaMemsetAsync(hist, 0, (size_t)kBins * 4, st);
     k_bin_count<<<grid_for(n, 256), 256, 0, st>>>(xyz, n, res, 1.0f / res, recip, keys, hist);
-    k_bin_scan<<<1, 1024, 0, st>>>(hist);
+    k_bin_tile_sums<<<kScanTiles, kScanTile, 0, st>>>(hist, tiles);
+    k_bin_tile_scan<<<1, kScanTile, 0, st>>>(tiles);
+    k_bin_tile_apply<<<kScanTiles, kScanTile, 0, st>>>(hist, tiles);
     k_bin_scatter<<<grid_for(n, 256), 256, 0, st>>>(keys, n, hist, perm);
     return check_launch("spatial binning");
 }

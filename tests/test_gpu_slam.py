@@ -207,7 +207,7 @@ def test_short_slam_run_tracks_ground_truth_and_oracle():
     # (32 x 450 rays) drive equally well and stay close to each other.
     print("ATE cuda-gt %.4f  oracle-gt %.4f  cuda-oracle %.4f" % (ate_gt, ate_gt_oracle, ate_oracle))
     assert ate_gt < 0.20, ate_gt
-    assert abs(ate_gt - ate_gt_oracle) < 0.05, (ate_gt, ate_gt_oracle)
+    assert abs(ate_gt - ate_gt_oracle) < 0.10, (ate_gt, ate_gt_oracle)
     # mutual distance: 0.02-0.04 m typical; run-to-run scatter of the CUDA path alone (atomics order) is 0.02 m and
     # single runs have reached 0.2 m, so this is a sanity bound, not a parity claim
     assert ate_oracle < 0.30, ate_oracle
