@@ -30,7 +30,7 @@ def _digest() -> str:
     for p in [os.path.join(CSRC, s) for s in SOURCES] + HEADERS + [__file__]:
         with open(p, "rb") as f:
             h.update(f.read())
-    h.update(" ".join(NVCC_FLAGS).encode())
+    h.update((" ".join(NVCC_FLAGS) + os.environ.get("PINQ_NVCC_EXTRA", "")).encode())
     return h.hexdigest()
 
 
@@ -48,6 +48,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
             if f.read().strip() == digest:
                 return LIB
     cmd = [nvcc_path()] + NVCC_FLAGS + ["-I" + os.path.join(ROOT, "include"), "-I" + CSRC]
+    cmd += os.environ.get("PINQ_NVCC_EXTRA", "").split()  # timing experiments only (e.g. -DPINQ_EXP=1)
     if verbose:
         cmd += ["-Xptxas", "-v"]
     cmd += [os.path.join(CSRC, s) for s in SOURCES] + ["-o", LIB]

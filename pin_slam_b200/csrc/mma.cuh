@@ -33,6 +33,14 @@ __device__ __forceinline__ void tf32_split(float x, uint32_t& hi, uint32_t& lo) 
     lo = tf32_rna(x - __uint_as_float(hi));
 }
 
+// Hot-loop variant: the tensor core ignores the low 13 mantissa bits of a tf32 operand, so x itself serves as
+// `hi` (= x truncated) and lo = x - trunc(x) is exact; lo is truncated again by the hardware, leaving
+// O(2^-21 |x|).  Two instructions (LOP3 + FADD) instead of the ~9 the emulated cvt.rna pair costs (SASS).
+__device__ __forceinline__ void tf32_split_trunc(float x, uint32_t& hi, uint32_t& lo) {
+    hi = __float_as_uint(x);
+    lo = __float_as_uint(x - __uint_as_float(hi & 0xffffe000u));
+}
+
 // x = b1 + b2 + b3 + O(2^-24 |x|)
 __device__ __forceinline__ void bf16_split3(float x, __nv_bfloat16& b1, __nv_bfloat16& b2, __nv_bfloat16& b3) {
     b1 = __float2bfloat16_rn(x);
@@ -70,8 +78,11 @@ constexpr uint32_t kBf16One = 0x3F80u;
 
 // Decoder operands in fragment order, built once per CTA in shared memory.
 struct DecFrags {
-    float4 w1a[8][32];    // layer 1, k-step 0 (inputs 0..7):  {hi B[t][j], hi B[t+4][j], lo B[t][j], lo B[t+4][j]}, j = 8 nt + g
-    float2 w1b[8][32];    // layer 1, k-step 1 (inputs 8..11): {hi B[8+t][j], lo B[8+t][j]}   (B[11][j] = b1[j], B[12..15] = 0)
+    // layer 1 B operands of n-tile nt (j = 8 nt + g) as the register PAIRS the five concatenated k-steps consume:
+    //   w1a = {hi B[t][j], hi B[t+4][j] | hi B[8+t][j], lo B[t][j]}      k-steps 0/3 and 1
+    //   w1b = {lo B[t+4][j], lo B[8+t][j] | hi B[8+t][j], 0}             k-steps 2 and 4     (B[11][j] = b1[j])
+    float4 w1a[8][32];
+    float4 w1b[8][32];
     float2 w2[32];        // {W2[2i], W2[2i+1]}
     uint2 vf[4][3][32];   // mask x V, columns = feature inputs 0..7:   split s of {V[16p+2t..][g], V[16p+2t+8..][g]}
     uint2 vv[4][3][32];   // mask x V, columns = inputs 8..10 (x - p_k), zero-padded to 8
@@ -91,8 +102,8 @@ __device__ __forceinline__ void build_dec_frags(const pinq_decoder_view& d, DecF
             tf32_split(l1_operand(d, t, j), h0, l0);
             tf32_split(l1_operand(d, t + 4, j), h1, l1);
             tf32_split(l1_operand(d, t + 8, j), h2, l2);
-            s->w1a[nt][lane] = make_float4(__uint_as_float(h0), __uint_as_float(h1), __uint_as_float(l0), __uint_as_float(l1));
-            s->w1b[nt][lane] = make_float2(__uint_as_float(h2), __uint_as_float(l2));
+            s->w1a[nt][lane] = make_float4(__uint_as_float(h0), __uint_as_float(h1), __uint_as_float(h2), __uint_as_float(l0));
+            s->w1b[nt][lane] = make_float4(__uint_as_float(l1), __uint_as_float(l2), __uint_as_float(h2), 0.f);
         }
     }
     for (int e = threadIdx.x; e < 32; e += blockDim.x) s->w2[e] = make_float2(d.W2[2 * e], d.W2[2 * e + 1]);

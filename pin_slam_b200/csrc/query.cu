@@ -8,6 +8,9 @@
 //              FP32-FMA bound; the decoder lives in shared memory, activations in registers.
 // Reference: model/neural_points.py:459-674, model/decoder.py:66-88, utils/tracker.py:245-253,
 //            utils/mapper.py:466-468, utils/mesher.py:93-180.
+#ifndef PINQ_EXP
+#define PINQ_EXP 0  // timing experiments (scripts/gpu_exp.sh); 0 = the product
+#endif
 #include "brick.cuh"
 #include "mma.cuh"
 
@@ -274,9 +277,9 @@ struct QueryLane {
     int nn;
 };
 
-template <bool WANT_U>
-__device__ __forceinline__ void resolve_query(const DecodeParams& p, int64_t i, int64_t q, bool live, float x, float y,
-                                              float z, QueryLane& L) {
+template <bool WANT_U, bool STORE_KNN>
+__device__ __forceinline__ void resolve_query(const DecodeParams& p, const int32_t* wsq, int64_t i, int64_t q, bool live,
+                                              float x, float y, float z, QueryLane& L) {
     L.nn = 0;
 #pragma unroll
     for (int k = 0; k < K; ++k) {
@@ -286,7 +289,6 @@ __device__ __forceinline__ void resolve_query(const DecodeParams& p, int64_t i, 
         if (WANT_U) L.ux[k] = L.uy[k] = L.uz[k] = 0.f;
     }
     if (live) {
-        const int32_t* wsq = p.ws + i * kWs;
         L.nn = wsq[K];
         int32_t r[K];
 #pragma unroll
@@ -317,11 +319,11 @@ __device__ __forceinline__ void resolve_query(const DecodeParams& p, int64_t i, 
     idw_weights(L.kd2, L.kidx, L.nn, L.wt, L.w, L.wsum);
     if (!live) return;
     if (p.nn_count) p.nn_count[q] = L.nn;
-    if (p.knn_idx) {
+    if (STORE_KNN && p.knn_idx) {
 #pragma unroll
         for (int k = 0; k < K; ++k) p.knn_idx[i * K + k] = L.kidx[k];
     }
-    if (p.knn_w) {
+    if (STORE_KNN && p.knn_w) {
 #pragma unroll
         for (int k = 0; k < K; ++k) p.knn_w[i * K + k] = L.w[k];
     }
@@ -341,8 +343,12 @@ __device__ __forceinline__ void resolve_query(const DecodeParams& p, int64_t i, 
 #pragma unroll
         for (int k = 0; k < K; ++k) {
             if (L.kidx[k] >= 0) {
+#if PINQ_EXP != 4
                 atomicAdd(&p.certainties[L.kidx[k]], L.w[k]);
+#endif
+#if PINQ_EXP != 4 && PINQ_EXP != 5
                 if (p.query_ts && p.ts_update) atomicMax(&p.ts_update[L.kidx[k]], ts);
+#endif
             }
         }
     }
@@ -355,7 +361,7 @@ __global__ void __launch_bounds__(kBlock) k_query_feature(const DecodeParams p) 
     float x, y, z;
     load_point(p.src, q, x, y, z);
     QueryLane L;
-    resolve_query<false>(p, q, q, true, x, y, z, L);
+    resolve_query<false, true>(p, p.ws + q * kWs, q, q, true, x, y, z, L);
     float* o = p.feat_out + q * (K * IN);
 #pragma unroll
     for (int k = 0; k < K; ++k) {
@@ -380,25 +386,47 @@ __global__ void __launch_bounds__(kBlock) k_query_feature(const DecodeParams p) 
 //                           3xTF32 layer 1, relu . W2 in the accumulator layout, relu' mask -> saved bits
 //                           (+ mask x V product for d s_k / d v_k when the gradient is wanted)
 //   phase C  lane = query : weighted combine, std, d sdf/dx, outputs
+// shared-memory bytes of the decoder fragments a decode variant needs (vf / vv only for the mask products)
+__host__ __device__ constexpr size_t dec_frag_bytes(bool grad) { return grad ? sizeof(DecFrags) : offsetof(DecFrags, vf); }
+constexpr int kRowPad = K + 1;  // [query][k] staging rows of 7 words: conflict-free for lane = query AND lane = (g,t)
 template <bool GRAD>
 struct WarpStage {
-    float4 vb[K][32];  // {vx, vy, vz, 1}: decoder inputs 8..11 of row (k, query)
-    int32_t li[K][32];
-    float sk[K][32];   // sum_j W2[j] relu(pre_j) of row (k, query)
+    float4 vb[K][32];          // {vx, vy, vz, 1}: decoder inputs 8..11 of row (k, query); first holds the staged ws block
+    int32_t li[32][kRowPad];   // neighbour index of row (query, k); slot K = nn_count
+    float w[32][kRowPad];      // IDW weight of row (query, k)
+    float sk[K][32];           // sum_j W2[j] relu(pre_j) of row (k, query)
     float4 gv[GRAD ? K : 1][32];
 };
+static_assert(sizeof(float4) * K * 32 >= sizeof(int32_t) * 32 * kWs, "ws block is staged in vb");
+
+// min(bits(h), 1) as opaque PTX: nvcc otherwise expands the float-class reasoning of fmaxf + bit cast into ~10 instructions
+__device__ __forceinline__ uint32_t umin1(float h) {
+    uint32_t m;
+    asm("min.u32 %0, %1, 1;" : "=r"(m) : "r"(__float_as_uint(h)));
+    return m;
+}
 
 template <bool GRAD, bool MESH>
 __global__ void __launch_bounds__(kBlock, GRAD ? 3 : 4) k_decode_mma(const DecodeParams p) {
     extern __shared__ __align__(16) unsigned char s_raw[];
     DecFrags* fr = reinterpret_cast<DecFrags*>(s_raw);
-    WarpStage<GRAD>* stages = reinterpret_cast<WarpStage<GRAD>*>(s_raw + sizeof(DecFrags));
+    WarpStage<GRAD>* stages = reinterpret_cast<WarpStage<GRAD>*>(s_raw + dec_frag_bytes(GRAD));
     build_dec_frags(p.dec, fr, true, false, GRAD);
     __syncthreads();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane >> 2, t = lane & 3;
     WarpStage<GRAD>& st = stages[warp];
     const float b2 = __ldg(p.dec.b2), scale = p.dec.sdf_scale;
     const int64_t nblocks = (p.n + kBlock - 1) / kBlock;
+    // layer-1 B fragments live in registers for the CTA's lifetime: re-reading them from shared memory for every
+    // m-tile (16 x LDS.128) made the shared-memory pipe the busiest unit of the kernel
+    uint32_t breg[8][6];
+#pragma unroll
+    for (int nt = 0; nt < 8; ++nt) {
+        const float4 wa = fr->w1a[nt][lane];
+        const float4 wb = fr->w1b[nt][lane];
+        breg[nt][0] = __float_as_uint(wa.x); breg[nt][1] = __float_as_uint(wa.y); breg[nt][2] = __float_as_uint(wa.z);
+        breg[nt][3] = __float_as_uint(wa.w); breg[nt][4] = __float_as_uint(wb.x); breg[nt][5] = __float_as_uint(wb.y);
+    }
 
     for (int64_t blk = blockIdx.x; blk < nblocks; blk += gridDim.x) {
         const int64_t q0 = blk * kBlock + warp * 32;  // first query of this warp
@@ -408,67 +436,116 @@ __global__ void __launch_bounds__(kBlock, GRAD ? 3 : 4) k_decode_mma(const Decod
         const int64_t q = (live && p.perm) ? (int64_t)p.perm[i] : i;
         float x = 0.f, y = 0.f, z = 0.f;
         if (live) load_point(p.src, q, x, y, z);
-        QueryLane L;
-        resolve_query<GRAD>(p, i, q, live, x, y, z, L);
         __syncwarp();  // the previous iteration's phase C reads are done
+        {   // the warp's 32 x 7 workspace words are contiguous: coalesced loads, then one conflict-free row per lane
+            int32_t* wsb = reinterpret_cast<int32_t*>(&st.vb[0][0]);
+            const int32_t* src = p.ws + q0 * kWs;
+            const int64_t lim = (p.n - q0) * kWs;
+#pragma unroll
+            for (int c = 0; c < kWs; ++c) {
+                const int e = c * 32 + lane;
+                wsb[e] = e < lim ? __ldg(src + e) : -1;
+            }
+        }
+        __syncwarp();
+        QueryLane L;
+        resolve_query<GRAD, false>(p, reinterpret_cast<const int32_t*>(&st.vb[0][0]) + lane * kWs, i, q, live, x, y, z, L);
+        __syncwarp();  // every lane has read its workspace row: vb may be overwritten
 #pragma unroll
         for (int k = 0; k < K; ++k) {
             st.vb[k][lane] = make_float4(L.vx[k], L.vy[k], L.vz[k], 1.f);
-            st.li[k][lane] = L.kidx[k];
+            st.li[lane][k] = L.kidx[k];
+            st.w[lane][k] = L.w[k];
         }
+        st.li[lane][K] = L.nn;
         __syncwarp();
+        if (p.knn_idx || p.knn_w) {  // [32 x 6] block of the warp is contiguous: coalesced stores
+            const int64_t lim = (p.n - q0) * K;
+#pragma unroll
+            for (int c = 0; c < K; ++c) {
+                const int e = c * 32 + lane, qi = e / K, k = e - qi * K;
+                if (e < lim) {
+                    if (p.knn_idx) p.knn_idx[q0 * K + e] = st.li[qi][k];
+                    if (p.knn_w) p.knn_w[q0 * K + e] = st.w[qi][k];
+                }
+            }
+        }
 
-        // ---- phase B ----
+        // ---- phase B ---- (software-pipelined: the gathers of m-tile mt + 1 are in flight while mt is multiplied)
+        float nraw[6];
+        bool nany;
+        auto fetch = [&](int mt) {
+            const int k = mt >> 1, half = mt & 1;
+            const int qa = 16 * half + g, qb = qa + 8;
+            const int la = st.li[qa][k], lb = st.li[qb][k];
+#pragma unroll
+            for (int i = 0; i < 6; ++i) nraw[i] = 0.f;
+            nany = __any_sync(0xffffffffu, (la >= 0) | (lb >= 0));
+            if (la >= 0) {
+                const float* f = p.features + (int64_t)la * F;
+                nraw[0] = __ldg(f + t); nraw[2] = __ldg(f + t + 4);
+            }
+            if (lb >= 0) {
+                const float* f = p.features + (int64_t)lb * F;
+                nraw[1] = __ldg(f + t); nraw[3] = __ldg(f + t + 4);
+            }
+            nraw[4] = reinterpret_cast<const float*>(&st.vb[k][qa])[t];
+            nraw[5] = reinterpret_cast<const float*>(&st.vb[k][qb])[t];
+        };
+        fetch(0);
 #pragma unroll 1
         for (int mt = 0; mt < kMTiles; ++mt) {
             const int k = mt >> 1, half = mt & 1;
             const int qa = 16 * half + g, qb = qa + 8;
-            const int la = st.li[k][qa], lb = st.li[k][qb];
-            const bool any = __any_sync(0xffffffffu, (la >= 0) | (lb >= 0));
+            float raw[6];
+#pragma unroll
+            for (int i = 0; i < 6; ++i) raw[i] = nraw[i];
+#if PINQ_EXP == 6
+            const bool any = false;
+#else
+            const bool any = nany;
+#endif
+            if (mt + 1 < kMTiles) fetch(mt + 1);
             uint32_t bits = 0;
             float sA = 0.f, sB = 0.f, c2[4] = {0.f, 0.f, 0.f, 0.f};
             if (any) {  // warp-uniform: tiles without a single valid neighbour carry weight 0 everywhere
-                float raw[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-                if (la >= 0) {
-                    const float* f = p.features + (int64_t)la * F;
-                    raw[0] = __ldg(f + t); raw[2] = __ldg(f + t + 4);
-                }
-                if (lb >= 0) {
-                    const float* f = p.features + (int64_t)lb * F;
-                    raw[1] = __ldg(f + t); raw[3] = __ldg(f + t + 4);
-                }
-                raw[4] = reinterpret_cast<const float*>(&st.vb[k][qa])[t];
-                raw[5] = reinterpret_cast<const float*>(&st.vb[k][qb])[t];
                 uint32_t ah[6], al[6];
 #pragma unroll
-                for (int i = 0; i < 6; ++i) tf32_split(raw[i], ah[i], al[i]);
+                for (int i = 0; i < 6; ++i) tf32_split_trunc(raw[i], ah[i], al[i]);
                 float acc[8][4];
 #pragma unroll
                 for (int nt = 0; nt < 8; ++nt) {
                     acc[nt][0] = acc[nt][1] = acc[nt][2] = acc[nt][3] = 0.f;
-                    const float4 wa = fr->w1a[nt][lane];
-                    const float2 wb = fr->w1b[nt][lane];
-                    const uint32_t bh0 = __float_as_uint(wa.x), bh1 = __float_as_uint(wa.y);
-                    const uint32_t bl0 = __float_as_uint(wa.z), bl1 = __float_as_uint(wa.w);
-                    const uint32_t ch = __float_as_uint(wb.x), cl = __float_as_uint(wb.y);
+                    const uint32_t bh0 = breg[nt][0], bh1 = breg[nt][1], ch = breg[nt][2], bl0 = breg[nt][3];
+                    const uint32_t bl1 = breg[nt][4], cl = breg[nt][5], ch2 = ch, zz = 0u;
                     // the three products of 3xTF32 concatenated along K: [lo | hi | hi] x [hi ; lo ; hi] = 36 real
                     // columns in 5 k-steps (small terms first)
+#if PINQ_EXP != 2
                     mma_tf32(acc[nt], al[0], al[1], al[2], al[3], bh0, bh1);
                     mma_tf32(acc[nt], al[4], al[5], ah[0], ah[1], ch, bl0);
                     mma_tf32(acc[nt], ah[2], ah[3], ah[4], ah[5], bl1, cl);
                     mma_tf32(acc[nt], ah[0], ah[1], ah[2], ah[3], bh0, bh1);
-                    mma_tf32(acc[nt], ah[4], ah[5], 0u, 0u, ch, 0u);
+#endif
+                    mma_tf32(acc[nt], ah[4], ah[5], 0u, 0u, ch2, zz);
                 }
+                uint32_t bitsA = 0u, bitsB = 0u;  // two chains: rows g and g + 8
 #pragma unroll
                 for (int nt = 0; nt < 8; ++nt) {
                     const float2 w2 = fr->w2[4 * nt + t];
-                    sA = fmaf(fmaxf(acc[nt][0], 0.f), w2.x, sA);
-                    sA = fmaf(fmaxf(acc[nt][1], 0.f), w2.y, sA);
-                    sB = fmaf(fmaxf(acc[nt][2], 0.f), w2.x, sB);
-                    sB = fmaf(fmaxf(acc[nt][3], 0.f), w2.y, sB);
-#pragma unroll
-                    for (int c = 0; c < 4; ++c) bits |= (acc[nt][c] > 0.f ? 1u : 0u) << (4 * nt + c);
+                    const float h0 = fmaxf(acc[nt][0], 0.f), h1 = fmaxf(acc[nt][1], 0.f);
+                    const float h2 = fmaxf(acc[nt][2], 0.f), h3 = fmaxf(acc[nt][3], 0.f);
+                    sA = fmaf(h0, w2.x, sA);
+                    sA = fmaf(h1, w2.y, sA);
+                    sB = fmaf(h2, w2.x, sB);
+                    sB = fmaf(h3, w2.y, sB);
+                    // relu'(pre) = [h > 0] = min(bits(h), 1) for h >= 0: one IMNMX + one IMAD per element,
+                    // bit (4 nt + c) <-> acc[nt][c]
+                    bitsA = umin1(h0) * (1u << (4 * nt + 0)) + bitsA;
+                    bitsA = umin1(h1) * (1u << (4 * nt + 1)) + bitsA;
+                    bitsB = umin1(h2) * (1u << (4 * nt + 2)) + bitsB;
+                    bitsB = umin1(h3) * (1u << (4 * nt + 3)) + bitsB;
                 }
+                bits = bitsA | bitsB;
                 sA += __shfl_xor_sync(0xffffffffu, sA, 1);
                 sB += __shfl_xor_sync(0xffffffffu, sB, 1);
                 sA += __shfl_xor_sync(0xffffffffu, sA, 2);
@@ -499,20 +576,22 @@ __global__ void __launch_bounds__(kBlock, GRAD ? 3 : 4) k_decode_mma(const Decod
         }
         __syncwarp();
 
-        // ---- phase C ----
+        // ---- phase C ---- (weights and count come back from shared memory: nothing of phase A stays in registers)
         if (!live) continue;
+        const int nnq = st.li[lane][K];
         if (MESH) {
-            if (p.mask_out) p.mask_out[q] = (uint8_t)(L.nn >= p.min_nn);
-            if (L.nn == 0) {  // MLP result unused where nothing is near (mesher.py:96-103)
+            if (p.mask_out) p.mask_out[q] = (uint8_t)(nnq >= p.min_nn);
+            if (nnq == 0) {  // MLP result unused where nothing is near (mesher.py:96-103)
                 p.sdf[q] = 0.f;
                 continue;
             }
         }
-        float s[K], sdf = 0.f;
+        float s[K], wq[K], sdf = 0.f;
 #pragma unroll
         for (int k = 0; k < K; ++k) {
+            wq[k] = st.w[lane][k];
             s[k] = (st.sk[k][lane] + b2) * scale;  // decoder.py:80-81
-            sdf = fmaf(s[k], L.w[k], sdf);
+            sdf = fmaf(s[k], wq[k], sdf);
         }
         if (p.sdf) p.sdf[q] = sdf;
         if (p.sdf_std) {  // tracker.py:246-247
@@ -520,7 +599,7 @@ __global__ void __launch_bounds__(kBlock, GRAD ? 3 : 4) k_decode_mma(const Decod
 #pragma unroll
             for (int k = 0; k < K; ++k) {
                 const float d = s[k] - sdf;
-                var = fmaf(L.w[k], d * d, var);
+                var = fmaf(wq[k], d * d, var);
             }
             p.sdf_std[q] = sqrtf(var);
         }
@@ -535,9 +614,9 @@ __global__ void __launch_bounds__(kBlock, GRAD ? 3 : 4) k_decode_mma(const Decod
                     float ax = gvk.x * scale, ay = gvk.y * scale, az = gvk.z * scale;
                     if (p.rotate) quat_rotate(__ldg(&p.quats[L.kidx[k]]), true, ax, ay, az);
                     const float c = (s[k] - sdf) * (-2.f * L.wt[k] * L.wt[k]) * inv_s;
-                    gx += L.w[k] * ax + c * L.ux[k];
-                    gy += L.w[k] * ay + c * L.uy[k];
-                    gz += L.w[k] * az + c * L.uz[k];
+                    gx += wq[k] * ax + c * L.ux[k];
+                    gy += wq[k] * ay + c * L.uy[k];
+                    gz += wq[k] * az + c * L.uz[k];
                 }
             }
             p.grad_x[3 * q] = gx;
@@ -645,9 +724,28 @@ static int run_query(const pinq_query_args* a, int mode, float* feat_out, const 
     } else {
         // persistent-ish grid: the decoder fragments are built once per CTA and amortised over its blocks
         const unsigned nb = grid_for(n, kBlock);
-        const unsigned g = nb < 148u * 8u ? nb : 148u * 8u;
-        const size_t sm_plain = sizeof(DecFrags) + (kBlock / 32) * sizeof(WarpStage<false>);
-        const size_t sm_grad = sizeof(DecFrags) + (kBlock / 32) * sizeof(WarpStage<true>);
+        const size_t sm_plain = dec_frag_bytes(false) + (kBlock / 32) * sizeof(WarpStage<false>);
+        const size_t sm_grad = dec_frag_bytes(true) + (kBlock / 32) * sizeof(WarpStage<true>);
+        static bool carve = false;
+        if (!carve) {  // let 6 CTAs of ~31 KB share an SM
+            cudaFuncSetAttribute(k_decode_mma<false, false>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+            cudaFuncSetAttribute(k_decode_mma<false, true>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+            cudaFuncSetAttribute(k_decode_mma<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_grad);
+            carve = true;
+        }
+        // one wave of resident CTAs, each striding over the blocks (a partial second wave would idle SMs)
+        static int occ_plain = 0, occ_mesh = 0, occ_grad = 0, sms = 0;
+        if (!sms) {
+            int dev = 0;
+            cudaGetDevice(&dev);
+            cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_plain, k_decode_mma<false, false>, kBlock, sm_plain);
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_mesh, k_decode_mma<false, true>, kBlock, sm_plain);
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_grad, k_decode_mma<true, false>, kBlock, sm_grad);
+        }
+        const int occ = mode == 2 ? occ_mesh : (a->grad_x ? occ_grad : occ_plain);
+        const unsigned cap = (unsigned)(sms * (occ > 0 ? occ : 1));
+        const unsigned g = nb < cap ? nb : cap;
         if (mode == 2) k_decode_mma<false, true><<<g, kBlock, sm_plain, st>>>(p);
         else if (a->grad_x) k_decode_mma<true, false><<<g, kBlock, sm_grad, st>>>(p);
         else k_decode_mma<false, false><<<g, kBlock, sm_plain, st>>>(p);

@@ -231,10 +231,21 @@ extern "C" int pinq_query_fused_bwd(const pinq_bwd_args* a, void* stream) {
     p.grad_W1 = a->grad_W1; p.grad_b1 = a->grad_b1; p.grad_W2 = a->grad_W2; p.grad_b2 = a->grad_b2;
     cudaStream_t st = as_stream(stream);
     const unsigned nb = grid_for(a->n, kBlock);
-    const unsigned cap = 148u * (dec ? 4u : 8u);  // fewer, longer-lived CTAs while every CTA ends in 833 global atomics
-    const unsigned g = nb < cap ? nb : cap;
     const size_t sm_dec = sizeof(DecFrags) + (kBlock / 32) * sizeof(BwdStage<true>);
     const size_t sm_plain = sizeof(DecFrags) + (kBlock / 32) * sizeof(BwdStage<false>);
+    // one wave of resident CTAs striding over the blocks (every CTA ends in 833 global atomics when dec)
+    static int occ_a = 0, occ_b = 0, occ_c = 0, sms = 0;
+    if (!sms) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_a, k_bwd_mma<true, true>, kBlock, sm_dec);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_b, k_bwd_mma<true, false>, kBlock, sm_dec);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_c, k_bwd_mma<false, true>, kBlock, sm_plain);
+    }
+    const int occ = dec ? (feat ? occ_a : occ_b) : occ_c;
+    const unsigned cap = (unsigned)(sms * (occ > 0 ? occ : 1));
+    const unsigned g = nb < cap ? nb : cap;
     if (dec && feat) k_bwd_mma<true, true><<<g, kBlock, sm_dec, st>>>(p);
     else if (dec) k_bwd_mma<true, false><<<g, kBlock, sm_dec, st>>>(p);
     else k_bwd_mma<false, true><<<g, kBlock, sm_plain, st>>>(p);
