@@ -17,6 +17,7 @@ One "step" = one fused forward launch + one backward launch over the N queries o
 from __future__ import annotations
 
 import argparse
+import ctypes
 import json
 import os
 import subprocess
@@ -32,6 +33,25 @@ if ROOT not in sys.path:
 
 METRIC = "sdf_queries_per_sec_fwd_bwd"
 UNIT = "queries/s"
+
+
+# kernels of libpinq launched by one step (fused forward + backward of a binned training-mode batch):
+# k_bin_count, k_bin_tile_sums, k_bin_tile_scan, k_bin_tile_apply, k_bin_scatter, k_stencil_masks, k_search_brick,
+# k_resolve, k_decode_mma, k_bwd_mma (the certainty scatter is fused into k_resolve unless the caller asks for the
+# queried certainty).  profiles/*_launches.csv is the ncu list of the same command.
+LAUNCHES_PER_STEP = 10
+KERNEL_NAMES = {"bin": "k_bin_* (5 kernels)", "search": "k_search_brick", "resolve": "k_resolve",
+                "decode": "k_decode_mma", "scatter": "k_certainty_scatter", "bwd": "k_bwd_mma"}
+
+
+def ncu_traffic():
+    """dram bytes (read + write) per launch of each kernel from the committed `ncu --set full` capture of this
+    command (profiles/ncu_traffic.json, written by profiles/summarize.py); {} when no capture is committed."""
+    p = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return json.load(f)
+    return {}
 
 
 def parse():
@@ -291,55 +311,62 @@ def main():
     ms_step = float(t.item()) / args.steps
     value = world * n / (ms_step * 1e-3)
 
-    # ---- per-kernel timing (CUDA events on the launching stream) for the roofline ----------------------
+    # ---- per-kernel timing (CUDA events on the launching stream, recorded by the library between its kernels)
     K = 6
     a = npts._query_args(q, dec.view(), ts, True, True)
     sdf = torch.empty(n, device=dev)
     nnc = torch.empty(n, dtype=torch.int32, device=dev)
-    knn_idx = torch.empty((n, K), dtype=torch.int32, device=dev)
-    knn_w = torch.empty((n, K), device=dev)
+    stage = torch.empty(int(lib.pinq_stage_bytes(n)), dtype=torch.uint8, device=dev)
     relu_mask = torch.empty(int(lib.pinq_relu_mask_words(n)), dtype=torch.int32, device=dev)
-    a.sdf, a.nn_count, a.knn_idx, a.knn_w = P.ptr(sdf), P.ptr(nnc), P.ptr(knn_idx), P.ptr(knn_w)
-    a.relu_mask = P.ptr(relu_mask)
     perm = torch.empty(n, dtype=torch.int32, device=dev)
-    a.perm = P.ptr(perm)
+    a.sdf, a.nn_count, a.stage, a.relu_mask, a.perm = P.ptr(sdf), P.ptr(nnc), P.ptr(stage), P.ptr(relu_mask), P.ptr(perm)
     b = P.BwdArgs()
     b.dec = dec.view()
-    b.xyz, b.n, b.flags, b.k, b.feature_dim = P.ptr(q), n, 0, K, 8
-    b.point_xyz = P.ptr(npts.local_neural_points.contiguous())
+    b.n, b.flags, b.k, b.feature_dim = n, 0, K, 8
     b.features = P.ptr(npts.local_geo_features.detach())
-    b.knn_idx, b.knn_w, b.grad_sdf = P.ptr(knn_idx), P.ptr(knn_w), P.ptr(ones)
-    b.relu_mask = P.ptr(relu_mask)
-    b.perm = P.ptr(perm)
+    b.stage, b.relu_mask, b.perm, b.grad_sdf = P.ptr(stage), P.ptr(relu_mask), P.ptr(perm), P.ptr(ones)
     gf = torch.zeros_like(npts.local_geo_features)
     gd = [torch.zeros_like(p) for p in dec.fused_params()]
     b.grad_features = P.ptr(gf)
     b.grad_W1, b.grad_b1, b.grad_W2, b.grad_b2 = (P.ptr(g) for g in gd)
     st = P.stream()
     reps = max(3, min(args.steps, 10))
-    t_f, t_b = [], []
+    phases = ["bin", "search", "resolve", "decode", "scatter", None, "bwd"]
+    acc = {k: [] for k in phases if k}
+    buf = (ctypes.c_float * 8)()
+    lib.pinq_kernel_timing(1)
     for i in range(reps + 2):
-        e = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
-        e[0].record()
         P.check(lib.pinq_query_fused_fwd(a, st))
-        e[1].record()
         P.check(lib.pinq_query_fused_bwd(b, st))
-        e[2].record()
         torch.cuda.synchronize()
+        lib.pinq_kernel_times(buf, 8)
         if i >= 2:
-            t_f.append(e[0].elapsed_time(e[1]))
-            t_b.append(e[1].elapsed_time(e[2]))
-    ms_f, ms_b = float(np.mean(t_f)), float(np.mean(t_b))
+            for j, k in enumerate(phases):
+                if k and buf[j] >= 0:
+                    acc[k].append(float(buf[j]))
+    lib.pinq_kernel_timing(0)
+    kms = {k: float(np.mean(v)) for k, v in acc.items() if v}
+    ms_f = sum(v for k, v in kms.items() if k != "bwd")
+    ms_b = kms.get("bwd", 0.0)
     hbm, peak_kind = peaks()
-    bytes_f = 556 + 20 * vbar + 4 * K   # fwd incl. the certainty scatter
-    bytes_b = 4 + K * 4 * 8             # dL/dsdf + feature-gradient accumulate
-    dom = "fwd" if ms_f >= ms_b else "bwd"
-    ach = (n * (bytes_f if dom == "fwd" else bytes_b)) / ((ms_f if dom == "fwd" else ms_b) * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "kernel": "k_query_fwd" if dom == "fwd" else "k_query_bwd", "achieved": ach,
-                "peak": hbm, "peak_kind": peak_kind + " (burst copy)", "unit": "GB/s", "frac": ach / hbm,
-                "traffic": None, "bytes_per_query": bytes_f if dom == "fwd" else bytes_b,
-                "ms_fwd_kernel": ms_f, "ms_bwd_kernel": ms_b,
-                "step_frac_of_hbm": (n * (bytes_f + bytes_b)) / ((ms_f + ms_b) * 1e-3) / 1e9 / hbm}
+    # algorithmic bytes per query of each kernel (DESIGN.md "kernels"; SURVEY.md 8(d) for the whole path)
+    kbytes = {
+        "bin": 12 + 4 + 4 + 4,                 # xyz in, key out; key in, perm out (histogram stays in L2)
+        "search": 4 + 12 + 20 * vbar + 28,     # perm, xyz, 16 B record + 4 B brick share per occupied stencil voxel, K ranks + count
+        "resolve": 4 + 12 + 28 + K * 16 + 124 + 4,   # perm, xyz, ranks, K records, stage block out, nn_count out
+        "decode": 124 + K * 32 + 48 + 4 + 4,   # stage in, K feature rows, relu bits out, perm, sdf out
+        "scatter": K * (4 + 4 + 4 + 8),        # idx, w in; certainty and ts atomics
+        "bwd": 4 + 4 + 124 + 48 + K * 32 + K * 32,  # perm, dL/dsdf, stage, relu bits, K feature rows (decoder grads), K gradient rows
+    }
+    dom = max(kms, key=kms.get)
+    ach = n * kbytes[dom] / (kms[dom] * 1e-3) / 1e9
+    bytes_step = sum(kbytes[k] for k in kms)
+    roofline = {"bound": "hbm", "kernel": KERNEL_NAMES[dom], "achieved": ach, "peak": hbm,
+                "peak_kind": peak_kind + " (burst copy)", "unit": "GB/s", "frac": ach / hbm,
+                "traffic": ncu_traffic().get(dom), "bytes_per_query": kbytes[dom],
+                "kernel_ms": kms, "kernel_bytes_per_query": {k: kbytes[k] for k in kms},
+                "ms_fwd_kernels": ms_f, "ms_bwd_kernel": ms_b,
+                "step_frac_of_hbm": n * bytes_step / ((ms_f + ms_b) * 1e-3) / 1e9 / hbm}
 
     # ---- end to end through the public API with HOST buffers ---------------------------------------------
     e2e = None
@@ -380,7 +407,7 @@ def main():
                 "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(args, npts, vbar),
                 "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e,
-                "gpu_launches": 8 * args.steps, "clocks": clocks}
+                "gpu_launches": LAUNCHES_PER_STEP * args.steps, "clocks": clocks}
         line["config"]["parallelism"] = "replicated map, queries sharded x%d%s" % (
             world, ", NCCL all-reduce of feature+decoder grads" if world > 1 else "")
         print(json.dumps(line))

@@ -40,6 +40,22 @@ extern "C" {
 const char* pinq_last_error(void);
 int pinq_version(void);
 
+/* Measurement aid (no reference counterpart; the role of the reference's tic()/toc() in utils/tools.py around the
+ * query calls): when enabled, the query entry points record CUDA events on the launching stream between their
+ * kernels.  pinq_kernel_times() waits for them and returns, per phase i, the milliseconds between mark i and the
+ * next recorded mark (-1 where a phase did not run).  Phases of one fused forward + backward: */
+#define PINQ_KT_BIN 0      /* spatial binning (memset + 5 kernels)          */
+#define PINQ_KT_SEARCH 1   /* stencil masks + K-nearest search              */
+#define PINQ_KT_RESOLVE 2  /* k_resolve                                     */
+#define PINQ_KT_DECODE 3   /* k_decode_mma                                  */
+#define PINQ_KT_SCATTER 4  /* second-pass certainty scatter (training)      */
+#define PINQ_KT_FWD_END 5
+#define PINQ_KT_BWD 6      /* k_bwd_mma                                     */
+#define PINQ_KT_BWD_END 7
+#define PINQ_KT_MARKS 8
+void pinq_kernel_timing(int enable);
+int pinq_kernel_times(float* ms_out, int cap);
+
 /* ---- voxel-hash index -------------------------------------------------------------------
  * The table is the reference's direct-mapped `buffer_pt_index` (model/neural_points.py:73)
  * held as dense int32[buffer_size]; slot(cell) = (cell . primes) mod buffer_size with the
@@ -189,9 +205,13 @@ typedef struct pinq_query_args {
     float* sdf_std;            /* [n]                                 (tracker.py:246-247)            */
     int32_t* nn_count;         /* [n]   valid candidates over the whole stencil (neural_points.py:557) */
     float* certainty;          /* [n]   sum_k w_k c_k                 (neural_points.py:651-656)      */
-    int32_t* knn_idx;          /* [n,k] top-k index (local or global), -1 invalid                    */
-    float* knn_w;              /* [n,k] normalised IDW weights                                       */
+    int32_t* knn_idx;          /* [n,k] top-k index (local or global), -1 invalid   } written by              */
+    float* knn_w;              /* [n,k] normalised IDW weights                       } pinq_query_feature only */
     float* knn_d2;             /* [n,k] squared distances (9e3 invalid)                              */
+    void* stage;               /* pinq_stage_bytes(n) or NULL: the search -> decode hand-off of the fused query
+                                  (top-k index, IDW weight, x - p_k per neighbour; 124 B/query, opaque,
+                                  processing order).  Give a buffer and keep it to call pinq_query_fused_bwd;
+                                  NULL = scratch inside `workspace`.                                  */
     uint32_t* relu_mask;       /* pinq_relu_mask_words(n) words or NULL: relu'(pre) of the hidden layer,
                                   one bit per (query, neighbour, hidden unit) in tensor-core fragment
                                   order; saved for pinq_query_fused_bwd (48 B/query, opaque)          */
@@ -205,6 +225,7 @@ typedef struct pinq_query_args {
 
 int64_t pinq_query_workspace_bytes(int64_t n);
 int64_t pinq_relu_mask_words(int64_t n);
+int64_t pinq_stage_bytes(int64_t n);
 
 /* neural_points.py:528-674 + decoder.py:66-88 + the weighted combine, in one pass.
  * Supported specialisation: k=6, feature_dim=8, hidden=64, one hidden level, weighted_first=False. */
@@ -216,15 +237,11 @@ int pinq_query_feature(const pinq_query_args* args, float* feat_out, void* strea
 
 typedef struct pinq_bwd_args {
     pinq_decoder_view dec;
-    const float* xyz;          /* [n,3]                                                    */
     int64_t n;
-    uint32_t flags;            /* PINQ_F_ROTATE only                                       */
+    uint32_t flags;            /* unused (the rotated x - p_k comes from the stage)        */
     int32_t k, feature_dim;
-    const float* point_xyz;    /* [Mx,3] positions indexed by knn_idx (local or global)    */
-    const float* quats;        /* [Mx,4] or NULL                                           */
     const float* features;     /* [Mx+1,F]                                                 */
-    const int32_t* knn_idx;    /* [n,k] saved by the forward                               */
-    const float* knn_w;        /* [n,k]                                                    */
+    const void* stage;         /* pinq_stage_bytes(n), saved by the forward                 */
     const uint32_t* relu_mask; /* pinq_relu_mask_words(n), saved by the forward            */
     const int32_t* perm;       /* [n] processing order of the forward, or NULL             */
     const float* grad_sdf;     /* [n] dL/dsdf                                              */

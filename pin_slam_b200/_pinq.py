@@ -30,13 +30,12 @@ class QueryArgs(C.Structure):
     _fields_ = [("map", MapView), ("dec", DecoderView), ("xyz", _vp), ("n", _i64), ("flags", _u32), ("k", _i32),
                 ("feature_dim", _i32), ("features", _vp), ("point_xyz", _vp), ("certainties", _vp), ("quats", _vp), ("ts_update", _vp),
                 ("query_ts", _vp), ("sdf", _vp), ("grad_x", _vp), ("sdf_std", _vp), ("nn_count", _vp),
-                ("certainty", _vp), ("knn_idx", _vp), ("knn_w", _vp), ("knn_d2", _vp), ("relu_mask", _vp), ("perm", _vp), ("workspace", _vp)]
+                ("certainty", _vp), ("knn_idx", _vp), ("knn_w", _vp), ("knn_d2", _vp), ("stage", _vp), ("relu_mask", _vp), ("perm", _vp), ("workspace", _vp)]
 
 
 class BwdArgs(C.Structure):
-    _fields_ = [("dec", DecoderView), ("xyz", _vp), ("n", _i64), ("flags", _u32), ("k", _i32), ("feature_dim", _i32),
-                ("point_xyz", _vp), ("quats", _vp), ("features", _vp), ("knn_idx", _vp), ("knn_w", _vp),
-                ("relu_mask", _vp), ("perm", _vp), ("grad_sdf", _vp), ("grad_features", _vp), ("grad_W1", _vp), ("grad_b1", _vp), ("grad_W2", _vp),
+    _fields_ = [("dec", DecoderView), ("n", _i64), ("flags", _u32), ("k", _i32), ("feature_dim", _i32),
+                ("features", _vp), ("stage", _vp), ("relu_mask", _vp), ("perm", _vp), ("grad_sdf", _vp), ("grad_features", _vp), ("grad_W1", _vp), ("grad_b1", _vp), ("grad_W2", _vp),
                 ("grad_b2", _vp)]
 
 
@@ -61,8 +60,11 @@ SIGNATURES = {
     "pinq_index_pack": (C.c_int, [_vp, _u32, _vp, _vp, _vp, _vp, _vp, _vp, _i64, _f32, _vp, _vp, _vp]),
     "pinq_brick_capacity": (_i64, [_i64]),
     "pinq_brick_build": (C.c_int, [_vp, _vp, _vp, _i64, _f32, _u32, _vp, _u32, _vp, _vp, _vp, _vp]),
+    "pinq_kernel_timing": (None, [C.c_int]),
+    "pinq_kernel_times": (C.c_int, [C.POINTER(C.c_float), C.c_int]),
     "pinq_query_workspace_bytes": (_i64, [_i64]),
     "pinq_relu_mask_words": (_i64, [_i64]),
+    "pinq_stage_bytes": (_i64, [_i64]),
     "pinq_neighbor_search": (C.c_int, [C.POINTER(MapView), _vp, _i64, _u32, _vp, _vp, _vp, _i64, _f32, C.c_int, _vp,
                                        _vp, _vp]),
     "pinq_query_certainty": (C.c_int, [C.POINTER(MapView), _vp, _i64, _u32, _vp, _vp, _vp, _vp]),

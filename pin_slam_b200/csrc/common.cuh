@@ -15,6 +15,7 @@ constexpr long long kP3 = 83492791LL;
 
 void set_error(const char* fmt, ...);
 int check_launch(const char* what);
+void ktime_mark(int mark, cudaStream_t st);  // per-kernel timing marks (PINQ_KT_*), no-op unless enabled
 void launch_tile_scan(int32_t* tile_sums, int64_t ntiles, int32_t* d_count, cudaStream_t st);
 // csrc/sort.cu: perm[] = queries binned by 4x4x4-voxel brick (processing order -> query index)
 int64_t bin_scratch_bytes(int64_t n);

@@ -249,7 +249,7 @@ struct DecodeParams {
     bool rotate, scatter_in_kernel;
     const int32_t* ws;
     const int32_t* perm;  // processing order -> query index (spatial binning, csrc/sort.cu); NULL = identity.
-                          // ws / knn_* / relu_mask are indexed by processing position, everything else by query.
+                          // ws / stage / relu_mask are indexed by processing position, everything else by query.
     const float* features;
     const float* point_xyz;
     float* certainties;
@@ -261,6 +261,7 @@ struct DecodeParams {
     float* certainty;
     int32_t* knn_idx;
     float *knn_w, *knn_d2;
+    StageBlock* stage;    // [ceil(n/32)] search -> decode -> backward hand-off (processing order)
     uint32_t* relu_mask;  // [ceil(n/32)][12][32] bit masks of relu'(pre), fragment order (consumed by the backward)
     float* feat_out;      // un-fused query_feature: [n,K,IN]
     int min_nn;           // mesher
@@ -277,7 +278,9 @@ struct QueryLane {
     int nn;
 };
 
-template <bool WANT_U, bool STORE_KNN>
+// EFFECTS: write the per-query API outputs and apply the training-mode side effects (done exactly once per query:
+// by k_resolve / k_query_feature; the gradient flavour of the decode re-derives the lane state with EFFECTS = false)
+template <bool WANT_U, bool EFFECTS, bool STORE_KNN>
 __device__ __forceinline__ void resolve_query(const DecodeParams& p, const int32_t* wsq, int64_t i, int64_t q, bool live,
                                               float x, float y, float z, QueryLane& L) {
     L.nn = 0;
@@ -317,19 +320,19 @@ __device__ __forceinline__ void resolve_query(const DecodeParams& p, const int32
         }
     }
     idw_weights(L.kd2, L.kidx, L.nn, L.wt, L.w, L.wsum);
-    if (!live) return;
+    if (!live || !EFFECTS) return;
     if (p.nn_count) p.nn_count[q] = L.nn;
     if (STORE_KNN && p.knn_idx) {
 #pragma unroll
-        for (int k = 0; k < K; ++k) p.knn_idx[i * K + k] = L.kidx[k];
+        for (int k = 0; k < K; ++k) p.knn_idx[q * K + k] = L.kidx[k];
     }
     if (STORE_KNN && p.knn_w) {
 #pragma unroll
-        for (int k = 0; k < K; ++k) p.knn_w[i * K + k] = L.w[k];
+        for (int k = 0; k < K; ++k) p.knn_w[q * K + k] = L.w[k];
     }
     if (p.knn_d2) {
 #pragma unroll
-        for (int k = 0; k < K; ++k) p.knn_d2[i * K + k] = L.kd2[k];
+        for (int k = 0; k < K; ++k) p.knn_d2[q * K + k] = L.kd2[k];
     }
     if (p.certainty) {  // sum_k w_k c_k, neural_points.py:651-656
         float c = 0.f;
@@ -361,7 +364,7 @@ __global__ void __launch_bounds__(kBlock) k_query_feature(const DecodeParams p) 
     float x, y, z;
     load_point(p.src, q, x, y, z);
     QueryLane L;
-    resolve_query<false, true>(p, p.ws + q * kWs, q, q, true, x, y, z, L);
+    resolve_query<false, true, true>(p, p.ws + q * kWs, q, q, true, x, y, z, L);
     float* o = p.feat_out + q * (K * IN);
 #pragma unroll
     for (int k = 0; k < K; ++k) {
@@ -379,25 +382,48 @@ __global__ void __launch_bounds__(kBlock) k_query_feature(const DecodeParams p) 
 }
 
 // ---------------------------------------------------------------------------------------------
+// k_resolve: lane = query.  Turns the K record ranks of the search into the stage block (index, IDW weight,
+// x - p_k), writes the per-query API outputs and applies the training-mode side effects.  A light kernel
+// (few registers, many resident warps) so that its dependent gathers are hidden by occupancy instead of
+// stalling the tensor-core kernel (ncu r1l: that part ran at IPC 0.2 inside the decode).
+__global__ void __launch_bounds__(kBlock) k_resolve(const DecodeParams p) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;  // processing position
+    const int lane = threadIdx.x & 31;
+    const bool live = i < p.n;
+    const int64_t q = (live && p.perm) ? (int64_t)p.perm[i] : i;
+    float x = 0.f, y = 0.f, z = 0.f;
+    if (live) load_point(p.src, q, x, y, z);
+    QueryLane L;
+    resolve_query<false, true, true>(p, p.ws + i * kWs, i, q, live, x, y, z, L);
+    if (i - lane >= p.n) return;  // whole warp past the end
+    StageBlock& sb = p.stage[i >> 5];
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+        sb.idx[k][lane] = L.kidx[k];
+        sb.w[k][lane] = L.w[k];
+        sb.v[k][0][lane] = L.vx[k];
+        sb.v[k][1][lane] = L.vy[k];
+        sb.v[k][2][lane] = L.vz[k];
+    }
+    sb.nn[lane] = L.nn;
+}
+
+// ---------------------------------------------------------------------------------------------
 // Fused decode on the tensor cores.  One warp owns 32 queries = 192 (query, neighbour) rows = 12 m-tiles:
 // m-tile mt = 2 k + half holds neighbour k of queries 16 half + {g, g + 8}.
-//   phase A  lane = query : resolve ranks, IDW weights, side effects; stage (index, x - p_k) per row
-//   phase B  lane = (g,t) : A fragments straight from the feature table (each quad reads one 32-byte row),
-//                           3xTF32 layer 1, relu . W2 in the accumulator layout, relu' mask -> saved bits
-//                           (+ mask x V product for d s_k / d v_k when the gradient is wanted)
-//   phase C  lane = query : weighted combine, std, d sdf/dx, outputs
-// shared-memory bytes of the decoder fragments a decode variant needs (vf / vv only for the mask products)
-__host__ __device__ constexpr size_t dec_frag_bytes(bool grad) { return grad ? sizeof(DecFrags) : offsetof(DecFrags, vf); }
-constexpr int kRowPad = K + 1;  // [query][k] staging rows of 7 words: conflict-free for lane = query AND lane = (g,t)
+//   lane = (g,t) : A fragments straight from the stage block and the feature table (each quad reads one
+//                  32-byte row), software-pipelined one m-tile ahead; 3xTF32 layer 1 with the B fragments
+//                  resident in registers; relu . W2 in the accumulator layout; relu' mask -> saved bits
+//                  (+ mask x V product for d s_k / d v_k when the gradient is wanted)
+//   lane = query : weighted combine, std, d sdf/dx, outputs
 template <bool GRAD>
 struct WarpStage {
-    float4 vb[K][32];          // {vx, vy, vz, 1}: decoder inputs 8..11 of row (k, query); first holds the staged ws block
-    int32_t li[32][kRowPad];   // neighbour index of row (query, k); slot K = nn_count
-    float w[32][kRowPad];      // IDW weight of row (query, k)
-    float sk[K][32];           // sum_j W2[j] relu(pre_j) of row (k, query)
+    float sk[K][32];  // sum_j W2[j] relu(pre_j) of row (k, query)
     float4 gv[GRAD ? K : 1][32];
 };
-static_assert(sizeof(float4) * K * 32 >= sizeof(int32_t) * 32 * kWs, "ws block is staged in vb");
+
+// shared-memory bytes of the decoder fragments a decode variant needs (vf / vv only for the mask products)
+__host__ __device__ constexpr size_t dec_frag_bytes(bool grad) { return grad ? sizeof(DecFrags) : offsetof(DecFrags, vf); }
 
 // min(bits(h), 1) as opaque PTX: nvcc otherwise expands the float-class reasoning of fmaxf + bit cast into ~10 instructions
 __device__ __forceinline__ uint32_t umin1(float h) {
@@ -429,55 +455,28 @@ __global__ void __launch_bounds__(kBlock, GRAD ? 3 : 4) k_decode_mma(const Decod
     }
 
     for (int64_t blk = blockIdx.x; blk < nblocks; blk += gridDim.x) {
-        const int64_t q0 = blk * kBlock + warp * 32;  // first query of this warp
+        const int64_t q0 = blk * kBlock + warp * 32;  // first processing position of this warp
         if (q0 >= p.n) continue;                      // warp-uniform
-        const int64_t i = q0 + lane;  // processing position; q = the query it holds
-        const bool live = i < p.n;
-        const int64_t q = (live && p.perm) ? (int64_t)p.perm[i] : i;
-        float x = 0.f, y = 0.f, z = 0.f;
-        if (live) load_point(p.src, q, x, y, z);
-        __syncwarp();  // the previous iteration's phase C reads are done
-        {   // the warp's 32 x 7 workspace words are contiguous: coalesced loads, then one conflict-free row per lane
-            int32_t* wsb = reinterpret_cast<int32_t*>(&st.vb[0][0]);
-            const int32_t* src = p.ws + q0 * kWs;
-            const int64_t lim = (p.n - q0) * kWs;
-#pragma unroll
-            for (int c = 0; c < kWs; ++c) {
-                const int e = c * 32 + lane;
-                wsb[e] = e < lim ? __ldg(src + e) : -1;
-            }
+        const StageBlock& sb = p.stage[q0 >> 5];
+        QueryLane L;  // gradient flavour only: lane = query state for the IDW gradient
+        int64_t qg = 0;
+        if (GRAD) {
+            const int64_t i = q0 + lane;
+            const bool live = i < p.n;
+            qg = (live && p.perm) ? (int64_t)p.perm[i] : i;
+            float x = 0.f, y = 0.f, z = 0.f;
+            if (live) load_point(p.src, qg, x, y, z);
+            resolve_query<true, false, false>(p, p.ws + i * kWs, i, qg, live, x, y, z, L);
         }
-        __syncwarp();
-        QueryLane L;
-        resolve_query<GRAD, false>(p, reinterpret_cast<const int32_t*>(&st.vb[0][0]) + lane * kWs, i, q, live, x, y, z, L);
-        __syncwarp();  // every lane has read its workspace row: vb may be overwritten
-#pragma unroll
-        for (int k = 0; k < K; ++k) {
-            st.vb[k][lane] = make_float4(L.vx[k], L.vy[k], L.vz[k], 1.f);
-            st.li[lane][k] = L.kidx[k];
-            st.w[lane][k] = L.w[k];
-        }
-        st.li[lane][K] = L.nn;
-        __syncwarp();
-        if (p.knn_idx || p.knn_w) {  // [32 x 6] block of the warp is contiguous: coalesced stores
-            const int64_t lim = (p.n - q0) * K;
-#pragma unroll
-            for (int c = 0; c < K; ++c) {
-                const int e = c * 32 + lane, qi = e / K, k = e - qi * K;
-                if (e < lim) {
-                    if (p.knn_idx) p.knn_idx[q0 * K + e] = st.li[qi][k];
-                    if (p.knn_w) p.knn_w[q0 * K + e] = st.w[qi][k];
-                }
-            }
-        }
+        __syncwarp();  // the previous iteration's epilogue reads of st are done
 
-        // ---- phase B ---- (software-pipelined: the gathers of m-tile mt + 1 are in flight while mt is multiplied)
+        // ---- lane = (g,t): software-pipelined over the 12 m-tiles ----
         float nraw[6];
         bool nany;
         auto fetch = [&](int mt) {
             const int k = mt >> 1, half = mt & 1;
             const int qa = 16 * half + g, qb = qa + 8;
-            const int la = st.li[qa][k], lb = st.li[qb][k];
+            const int la = __ldg(&sb.idx[k][qa]), lb = __ldg(&sb.idx[k][qb]);
 #pragma unroll
             for (int i = 0; i < 6; ++i) nraw[i] = 0.f;
             nany = __any_sync(0xffffffffu, (la >= 0) | (lb >= 0));
@@ -489,8 +488,9 @@ __global__ void __launch_bounds__(kBlock, GRAD ? 3 : 4) k_decode_mma(const Decod
                 const float* f = p.features + (int64_t)lb * F;
                 nraw[1] = __ldg(f + t); nraw[3] = __ldg(f + t + 4);
             }
-            nraw[4] = reinterpret_cast<const float*>(&st.vb[k][qa])[t];
-            nraw[5] = reinterpret_cast<const float*>(&st.vb[k][qb])[t];
+            // inputs 8..11: x - p_k and the constant 1 of the bias column
+            nraw[4] = t < 3 ? __ldg(&sb.v[k][t < 3 ? t : 0][qa]) : 1.f;
+            nraw[5] = t < 3 ? __ldg(&sb.v[k][t < 3 ? t : 0][qb]) : 1.f;
         };
         fetch(0);
 #pragma unroll 1
@@ -517,16 +517,14 @@ __global__ void __launch_bounds__(kBlock, GRAD ? 3 : 4) k_decode_mma(const Decod
                 for (int nt = 0; nt < 8; ++nt) {
                     acc[nt][0] = acc[nt][1] = acc[nt][2] = acc[nt][3] = 0.f;
                     const uint32_t bh0 = breg[nt][0], bh1 = breg[nt][1], ch = breg[nt][2], bl0 = breg[nt][3];
-                    const uint32_t bl1 = breg[nt][4], cl = breg[nt][5], ch2 = ch, zz = 0u;
+                    const uint32_t bl1 = breg[nt][4], cl = breg[nt][5];
                     // the three products of 3xTF32 concatenated along K: [lo | hi | hi] x [hi ; lo ; hi] = 36 real
                     // columns in 5 k-steps (small terms first)
-#if PINQ_EXP != 2
                     mma_tf32(acc[nt], al[0], al[1], al[2], al[3], bh0, bh1);
                     mma_tf32(acc[nt], al[4], al[5], ah[0], ah[1], ch, bl0);
                     mma_tf32(acc[nt], ah[2], ah[3], ah[4], ah[5], bl1, cl);
                     mma_tf32(acc[nt], ah[0], ah[1], ah[2], ah[3], bh0, bh1);
-#endif
-                    mma_tf32(acc[nt], ah[4], ah[5], 0u, 0u, ch2, zz);
+                    mma_tf32(acc[nt], ah[4], ah[5], 0u, 0u, ch, 0u);
                 }
                 uint32_t bitsA = 0u, bitsB = 0u;  // two chains: rows g and g + 8
 #pragma unroll
@@ -576,10 +574,12 @@ __global__ void __launch_bounds__(kBlock, GRAD ? 3 : 4) k_decode_mma(const Decod
         }
         __syncwarp();
 
-        // ---- phase C ---- (weights and count come back from shared memory: nothing of phase A stays in registers)
-        if (!live) continue;
-        const int nnq = st.li[lane][K];
+        // ---- lane = query: weighted combine and outputs ----
+        const int64_t i = q0 + lane;
+        if (i >= p.n) continue;
+        const int64_t q = GRAD ? qg : (p.perm ? (int64_t)p.perm[i] : i);
         if (MESH) {
+            const int nnq = __ldg(&sb.nn[lane]);
             if (p.mask_out) p.mask_out[q] = (uint8_t)(nnq >= p.min_nn);
             if (nnq == 0) {  // MLP result unused where nothing is near (mesher.py:96-103)
                 p.sdf[q] = 0.f;
@@ -589,7 +589,7 @@ __global__ void __launch_bounds__(kBlock, GRAD ? 3 : 4) k_decode_mma(const Decod
         float s[K], wq[K], sdf = 0.f;
 #pragma unroll
         for (int k = 0; k < K; ++k) {
-            wq[k] = st.w[lane][k];
+            wq[k] = __ldg(&sb.w[k][lane]);
             s[k] = (st.sk[k][lane] + b2) * scale;  // decoder.py:80-81
             sdf = fmaf(s[k], wq[k], sdf);
         }
@@ -627,18 +627,37 @@ __global__ void __launch_bounds__(kBlock, GRAD ? 3 : 4) k_decode_mma(const Decod
 }
 
 // second pass of the exact training path: scatter after every query has read its certainties
-__global__ void k_certainty_scatter(const int32_t* __restrict__ knn_idx, const float* __restrict__ knn_w,
-                                    const int64_t* __restrict__ query_ts, const int32_t* __restrict__ perm, int64_t n,
-                                    float* certainties, long long* ts_update) {
+__global__ void k_certainty_scatter(const StageBlock* __restrict__ stage, const int64_t* __restrict__ query_ts,
+                                    const int32_t* __restrict__ perm, int64_t n, float* certainties,
+                                    long long* ts_update) {
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;  // (k, position) pairs, position fastest
+    const int64_t i = t % (((n + 31) / 32) * 32);
+    const int k = (int)(t / (((n + 31) / 32) * 32));
+    if (k >= K || i >= n) return;
+    const StageBlock& sb = stage[i >> 5];
+    const int32_t idx = sb.idx[k][i & 31];
+    if (idx < 0) return;
+    atomicAdd(&certainties[idx], sb.w[k][i & 31]);
+    if (query_ts && ts_update) atomicMax(&ts_update[idx], (long long)query_ts[perm ? perm[i] : i]);
+}
+
+// the same second pass for the un-fused form, from its [n,K] outputs
+__global__ void k_certainty_scatter_knn(const int32_t* __restrict__ knn_idx, const float* __restrict__ knn_w,
+                                        const int64_t* __restrict__ query_ts, int64_t n, float* certainties,
+                                        long long* ts_update) {
     const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= n * K) return;
     const int32_t i = knn_idx[t];
     if (i < 0) return;
     atomicAdd(&certainties[i], knn_w[t]);
-    if (query_ts && ts_update) atomicMax(&ts_update[i], (long long)query_ts[perm ? perm[t / K] : t / K]);
+    if (query_ts && ts_update) atomicMax(&ts_update[i], (long long)query_ts[t / K]);
 }
 
 static inline int64_t ws_bytes(int64_t n) { return (((n > 0 ? n : 1) * (int64_t)kWs * 4 + 255) / 256) * 256; }
+static inline int64_t stage_bytes(int64_t n) { return (((n > 0 ? n : 1) + 31) / 32) * (int64_t)sizeof(StageBlock); }
+// workspace layout: [search ranks | binning scratch | stencil masks | stage (when the caller keeps none)]
+static inline int64_t ws_off_masks(int64_t n) { return ws_bytes(n) + bin_scratch_bytes(n); }
+static inline int64_t ws_off_stage(int64_t n) { return ((ws_off_masks(n) + kStencilMasks * 8 + 255) / 256) * 256; }
 
 static int run_query(const pinq_query_args* a, int mode, float* feat_out, const PointSrc* grid_src, int min_nn,
                      uint8_t* mask_out, cudaStream_t st) {
@@ -677,11 +696,13 @@ static int run_query(const pinq_query_args* a, int mode, float* feat_out, const 
     int32_t* ws = reinterpret_cast<int32_t*>(a->workspace);
     const int32_t* perm = nullptr;
     if (a->perm && !grid_src && mode != 1) {  // spatial binning: processing order only, results unchanged
+        ktime_mark(PINQ_KT_BIN, st);
         rc = launch_spatial_bin(a->xyz, n, map.res, recip, reinterpret_cast<unsigned char*>(a->workspace) + ws_bytes(n),
                                 a->perm, st);
         if (rc) return rc;
         perm = a->perm;
     }
+    ktime_mark(PINQ_KT_SEARCH, st);
     const bool brick = a->map.brick_tab != nullptr;
     BrickDev bd;
     if (brick) {
@@ -695,7 +716,7 @@ static int run_query(const pinq_query_args* a, int mode, float* feat_out, const 
         bd.rec = reinterpret_cast<const float4*>(a->map.brick_rec4);
         bd.radius = a->map.stencil_radius;
         unsigned long long* smasks = reinterpret_cast<unsigned long long*>(
-            reinterpret_cast<unsigned char*>(a->workspace) + ws_bytes(n) + bin_scratch_bytes(n));
+            reinterpret_cast<unsigned char*>(a->workspace) + ws_off_masks(n));
         k_stencil_masks<<<1, 256, 0, st>>>(map.stencil_dx, map.kn, bd.radius, smasks);
         const size_t smem = sizeof(BrickLane) + kStencilMasks * 8 + 128;
         k_search_brick<<<grid_for(n, kBlock), kBlock, smem, st>>>(map, bd, src, n, recip, perm, smasks, ws);
@@ -710,7 +731,7 @@ static int run_query(const pinq_query_args* a, int mode, float* feat_out, const 
     p.rotate = (a->flags & PINQ_F_ROTATE) != 0;
     // Exactness of the queried certainty in training mode needs all reads before any scatter: if the
     // caller wants it (and gave knn buffers), scatter in a second kernel; otherwise fuse the atomics.
-    const bool two_pass = training && a->certainty && a->knn_idx && a->knn_w;
+    const bool two_pass = training && a->certainty && (mode != 1 || (a->knn_idx && a->knn_w));
     p.scatter_in_kernel = training && !two_pass;
     p.ws = ws; p.perm = perm; p.features = a->features; p.point_xyz = a->point_xyz; p.certainties = a->certainties;
     p.quats = reinterpret_cast<const float4*>(a->quats);
@@ -719,9 +740,16 @@ static int run_query(const pinq_query_args* a, int mode, float* feat_out, const 
     p.certainty = a->certainty; p.knn_idx = a->knn_idx; p.knn_w = a->knn_w; p.knn_d2 = a->knn_d2;
     p.feat_out = feat_out; p.min_nn = min_nn; p.mask_out = mask_out;
     p.relu_mask = reinterpret_cast<uint32_t*>(a->relu_mask);
+    p.stage = reinterpret_cast<StageBlock*>(a->stage ? a->stage
+                                                     : reinterpret_cast<unsigned char*>(a->workspace) + ws_off_stage(n));
+    ktime_mark(PINQ_KT_RESOLVE, st);
     if (mode == 1) {
         k_query_feature<<<grid_for(n, kBlock), kBlock, 0, st>>>(p);
     } else {
+        k_resolve<<<grid_for(n, kBlock), kBlock, 0, st>>>(p);
+        rc = check_launch("k_resolve");
+        if (rc) return rc;
+        ktime_mark(PINQ_KT_DECODE, st);
         // persistent-ish grid: the decoder fragments are built once per CTA and amortised over its blocks
         const unsigned nb = grid_for(n, kBlock);
         const size_t sm_plain = dec_frag_bytes(false) + (kBlock / 32) * sizeof(WarpStage<false>);
@@ -752,9 +780,17 @@ static int run_query(const pinq_query_args* a, int mode, float* feat_out, const 
     }
     rc = check_launch("k_decode");
     if (rc) return rc;
+    ktime_mark(two_pass ? PINQ_KT_SCATTER : PINQ_KT_FWD_END, st);
+    if (two_pass && mode == 1) {
+        k_certainty_scatter_knn<<<grid_for(n * K, 256), 256, 0, st>>>(a->knn_idx, a->knn_w, a->query_ts, n, a->certainties,
+                                                                      reinterpret_cast<long long*>(a->ts_update));
+        return check_launch("k_certainty_scatter");
+    }
     if (two_pass) {
-        k_certainty_scatter<<<grid_for(n * K, 256), 256, 0, st>>>(a->knn_idx, a->knn_w, a->query_ts, perm, n, a->certainties,
-                                                                  reinterpret_cast<long long*>(a->ts_update));
+        const int64_t padded = ((n + 31) / 32) * 32;
+        k_certainty_scatter<<<grid_for(padded * K, 256), 256, 0, st>>>(p.stage, a->query_ts, perm, n, a->certainties,
+                                                                       reinterpret_cast<long long*>(a->ts_update));
+        ktime_mark(PINQ_KT_FWD_END, st);
         return check_launch("k_certainty_scatter");
     }
     return PINQ_OK;
@@ -766,9 +802,8 @@ using namespace pinq;
 
 extern "C" {
 
-int64_t pinq_query_workspace_bytes(int64_t n) {
-    return ws_bytes(n) + bin_scratch_bytes(n > 0 ? n : 1) + kStencilMasks * 8;
-}
+int64_t pinq_query_workspace_bytes(int64_t n) { return ws_off_stage(n > 0 ? n : 1) + stage_bytes(n); }
+int64_t pinq_stage_bytes(int64_t n) { return stage_bytes(n); }
 
 int64_t pinq_relu_mask_words(int64_t n) { return ((n > 0 ? n : 1) + 31) / 32 * (int64_t)kMTiles * 32; }
 

@@ -18,14 +18,9 @@ namespace pinq {
 
 struct BwdParams {
     pinq_decoder_view dec;
-    const float* xyz;
     int64_t n;
-    bool rotate;
-    const float* point_xyz;
-    const float4* quats;
     const float* features;
-    const int32_t* knn_idx;
-    const float* knn_w;
+    const StageBlock* stage;
     const uint32_t* relu_mask;
     const int32_t* perm;
     const float* grad_sdf;
@@ -37,11 +32,8 @@ __device__ __forceinline__ void red_add_v2(float* addr, float a, float b) {
     asm volatile("red.global.add.v2.f32 [%0], {%1, %2};" ::"l"(addr), "f"(a), "f"(b) : "memory");
 }
 
-template <bool DEC>
 struct BwdStage {
-    int32_t li[K][32];
-    float ab[K][32];             // a_k of row (k, query)
-    float4 vb[DEC ? K : 1][32];  // {vx, vy, vz, 1}: decoder inputs 8..11 of row (k, query)
+    float ab[K][32];  // a_k = g w_k scale of row (k, query); 0 for invalid rows
 };
 
 constexpr int kGCols = IN + 1;  // 11 inputs + the bias column
@@ -52,7 +44,7 @@ template <bool DEC, bool FEAT>
 __global__ void __launch_bounds__(kBlock, 4) k_bwd_mma(const BwdParams p) {
     extern __shared__ __align__(16) unsigned char s_raw[];
     DecFrags* fr = reinterpret_cast<DecFrags*>(s_raw);
-    BwdStage<DEC>* stages = reinterpret_cast<BwdStage<DEC>*>(s_raw + sizeof(DecFrags));
+    BwdStage* stages = reinterpret_cast<BwdStage*>(s_raw + sizeof(DecFrags));
     __shared__ float s_G[DEC ? H * kGCols : 1];
     __shared__ float s_db2;
     build_dec_frags(p.dec, fr, false, FEAT, false);
@@ -62,7 +54,7 @@ __global__ void __launch_bounds__(kBlock, 4) k_bwd_mma(const BwdParams p) {
     }
     __syncthreads();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane >> 2, t = lane & 3;
-    BwdStage<DEC>& st = stages[warp];
+    BwdStage& st = stages[warp];
     const float scale = p.dec.sdf_scale;
     const int64_t nblocks = (p.n + kBlock - 1) / kBlock;
 
@@ -79,30 +71,17 @@ __global__ void __launch_bounds__(kBlock, 4) k_bwd_mma(const BwdParams p) {
         const int64_t i = q0 + lane;  // processing position; q = the query it holds
         const bool live = i < p.n;
         const int64_t q = (live && p.perm) ? (int64_t)p.perm[i] : i;
+        const StageBlock& sb = p.stage[q0 >> 5];
         // ---- phase A: lane = query ----
         __syncwarp();
         {
             const float gq = live ? p.grad_sdf[q] : 0.f;
-            float x = 0.f, y = 0.f, z = 0.f;
-            if (DEC && live) {
-                x = p.xyz[3 * q]; y = p.xyz[3 * q + 1]; z = p.xyz[3 * q + 2];
-            }
 #pragma unroll
             for (int k = 0; k < K; ++k) {
-                const int32_t li = live ? p.knn_idx[i * K + k] : -1;
-                const float a = live ? gq * p.knn_w[i * K + k] * scale : 0.f;
-                st.li[k][lane] = li;
-                st.ab[k][lane] = li >= 0 ? a : 0.f;
-                if (DEC) {
-                    float vx = 0.f, vy = 0.f, vz = 0.f;
-                    if (li >= 0) {
-                        const float* pp = p.point_xyz + 3 * (int64_t)li;
-                        vx = __fsub_rn(x, pp[0]); vy = __fsub_rn(y, pp[1]); vz = __fsub_rn(z, pp[2]);
-                        if (p.rotate) quat_rotate(__ldg(&p.quats[li]), false, vx, vy, vz);
-                        db2 += a;
-                    }
-                    st.vb[k][lane] = make_float4(vx, vy, vz, 1.f);
-                }
+                const int32_t li = __ldg(&sb.idx[k][lane]);
+                const float a = (live && li >= 0) ? gq * __ldg(&sb.w[k][lane]) * scale : 0.f;
+                st.ab[k][lane] = a;
+                if (DEC) db2 += a;
             }
         }
         __syncwarp();
@@ -112,7 +91,7 @@ __global__ void __launch_bounds__(kBlock, 4) k_bwd_mma(const BwdParams p) {
         for (int mt = 0; mt < kMTiles; ++mt) {
             const int k = mt >> 1, half = mt & 1;
             const int qa = 16 * half + g, qb = qa + 8;
-            const int la = st.li[k][qa], lb = st.li[k][qb];
+            const int la = __ldg(&sb.idx[k][qa]), lb = __ldg(&sb.idx[k][qb]);
             if (!__any_sync(0xffffffffu, (la >= 0) | (lb >= 0))) continue;  // warp-uniform
             const uint32_t bits = __ldg(&p.relu_mask[((q0 >> 5) * kMTiles + mt) * 32 + lane]);
             uint32_t am[4][4];
@@ -151,10 +130,11 @@ __global__ void __launch_bounds__(kBlock, 4) k_bwd_mma(const BwdParams p) {
 #pragma unroll
                 for (int r4 = 0; r4 < 4; ++r4) {
                     const int qr = 16 * half + 2 * t + (r4 & 1) + 8 * (r4 >> 1);
-                    const int lr = st.li[k][qr];
+                    const int lr = __ldg(&sb.idx[k][qr]);
                     const float ar = st.ab[k][qr];
                     const float f = lr >= 0 ? ar * __ldg(p.features + (int64_t)lr * F + g) : 0.f;
-                    const float v = g < 4 ? ar * reinterpret_cast<const float*>(&st.vb[k][qr])[g] : 0.f;
+                    // columns 8..10 = x - p_k from the stage, column 11 = the bias input 1
+                    const float v = g < 3 ? ar * __ldg(&sb.v[k][g < 3 ? g : 0][qr]) : (g == 3 ? ar : 0.f);
                     bf16_split3(f, xf[r4][0], xf[r4][1], xf[r4][2]);
                     bf16_split3(v, xv[r4][0], xv[r4][1], xv[r4][2]);
                 }
@@ -216,38 +196,38 @@ extern "C" int pinq_query_fused_bwd(const pinq_bwd_args* a, void* stream) {
     PINQ_REQUIRE(a != nullptr, "null args");
     int rc = check_decoder(a->dec, a->k, a->feature_dim);
     if (rc) return rc;
-    PINQ_REQUIRE(a->xyz && a->point_xyz && a->features && a->knn_idx && a->knn_w && a->grad_sdf && a->relu_mask,
-                 "null input (the backward needs the relu mask saved by pinq_query_fused_fwd)");
-    PINQ_REQUIRE(!(a->flags & PINQ_F_ROTATE) || a->quats, "PINQ_F_ROTATE needs quats");
+    PINQ_REQUIRE(a->features && a->stage && a->grad_sdf && a->relu_mask,
+                 "null input (the backward needs the stage and the relu mask saved by pinq_query_fused_fwd)");
     const bool dec = a->grad_W1 != nullptr;
     PINQ_REQUIRE(!dec || (a->grad_b1 && a->grad_W2 && a->grad_b2), "decoder gradients: all four or none");
     const bool feat = a->grad_features != nullptr;
     if (a->n == 0 || (!dec && !feat)) return PINQ_OK;
     BwdParams p;
-    p.dec = a->dec; p.xyz = a->xyz; p.n = a->n; p.rotate = (a->flags & PINQ_F_ROTATE) != 0;
-    p.point_xyz = a->point_xyz; p.quats = reinterpret_cast<const float4*>(a->quats);
-    p.features = a->features; p.knn_idx = a->knn_idx; p.knn_w = a->knn_w; p.relu_mask = a->relu_mask; p.perm = a->perm;
+    p.dec = a->dec; p.n = a->n;
+    p.features = a->features; p.stage = reinterpret_cast<const StageBlock*>(a->stage);
+    p.relu_mask = a->relu_mask; p.perm = a->perm;
     p.grad_sdf = a->grad_sdf; p.grad_features = a->grad_features;
     p.grad_W1 = a->grad_W1; p.grad_b1 = a->grad_b1; p.grad_W2 = a->grad_W2; p.grad_b2 = a->grad_b2;
     cudaStream_t st = as_stream(stream);
     const unsigned nb = grid_for(a->n, kBlock);
-    const size_t sm_dec = sizeof(DecFrags) + (kBlock / 32) * sizeof(BwdStage<true>);
-    const size_t sm_plain = sizeof(DecFrags) + (kBlock / 32) * sizeof(BwdStage<false>);
+    const size_t sm = sizeof(DecFrags) + (kBlock / 32) * sizeof(BwdStage);
     // one wave of resident CTAs striding over the blocks (every CTA ends in 833 global atomics when dec)
     static int occ_a = 0, occ_b = 0, occ_c = 0, sms = 0;
     if (!sms) {
         int dev = 0;
         cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_a, k_bwd_mma<true, true>, kBlock, sm_dec);
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_b, k_bwd_mma<true, false>, kBlock, sm_dec);
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_c, k_bwd_mma<false, true>, kBlock, sm_plain);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_a, k_bwd_mma<true, true>, kBlock, sm);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_b, k_bwd_mma<true, false>, kBlock, sm);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_c, k_bwd_mma<false, true>, kBlock, sm);
     }
     const int occ = dec ? (feat ? occ_a : occ_b) : occ_c;
     const unsigned cap = (unsigned)(sms * (occ > 0 ? occ : 1));
     const unsigned g = nb < cap ? nb : cap;
-    if (dec && feat) k_bwd_mma<true, true><<<g, kBlock, sm_dec, st>>>(p);
-    else if (dec) k_bwd_mma<true, false><<<g, kBlock, sm_dec, st>>>(p);
-    else k_bwd_mma<false, true><<<g, kBlock, sm_plain, st>>>(p);
+    ktime_mark(PINQ_KT_BWD, st);
+    if (dec && feat) k_bwd_mma<true, true><<<g, kBlock, sm, st>>>(p);
+    else if (dec) k_bwd_mma<true, false><<<g, kBlock, sm, st>>>(p);
+    else k_bwd_mma<false, true><<<g, kBlock, sm, st>>>(p);
+    ktime_mark(PINQ_KT_BWD_END, st);
     return check_launch("pinq_query_fused_bwd");
 }

@@ -20,6 +20,17 @@ constexpr int kBlock = 128;
 constexpr float kInvalidD2 = 9e3f;  // model/neural_points.py:561
 constexpr float kEps = 1e-15f;      // model/neural_points.py:618
 
+// Search -> decode -> backward hand-off ("stage"): one block per 32 consecutive processing positions,
+// struct-of-arrays inside the block so that lane = query (resolve, epilogue) AND lane = (g,t) fragment
+// accesses are coalesced.  124 B/query; written once by k_resolve, read by the decode and backward kernels.
+struct StageBlock {
+    int32_t idx[K][32];   // neighbour index (local or global), -1 = invalid
+    float w[K][32];       // normalised IDW weight (0 for invalid)
+    float v[K][3][32];    // decoder inputs 8..10: x - p_k, rotated into the point frame when after_pgo
+    int32_t nn[32];       // valid candidates over the whole stencil
+};
+static_assert(sizeof(StageBlock) == 3968, "124 bytes per query");
+
 struct MapDev {
     const uint2* occ;    // occupancy index: {bits, prefix} per 32 slots
     const float4* rec;   // rank-ordered candidate records {x, y, z, bits(index)}

@@ -26,6 +26,19 @@ int check_launch(const char* what) {
     return PINQ_OK;
 }
 
+// Optional per-kernel timing of the query path (bench.py roofline): CUDA events on the launching stream between
+// the kernels of one pinq_query_fused_fwd / _bwd call.  Off by default; marks cost nothing when off.
+static bool g_ktime_on = false;
+static cudaEvent_t g_ktime_ev[PINQ_KT_MARKS];
+static bool g_ktime_set[PINQ_KT_MARKS];
+
+void ktime_mark(int mark, cudaStream_t st) {
+    if (!g_ktime_on || mark < 0 || mark >= PINQ_KT_MARKS) return;
+    if (!g_ktime_ev[mark]) cudaEventCreate(&g_ktime_ev[mark]);
+    cudaEventRecord(g_ktime_ev[mark], st);
+    g_ktime_set[mark] = true;
+}
+
 // ---------------------------------------------------------------------------------------------
 __global__ void k_fill_i32(int32_t* p, int64_t n, int32_t v) {
     // 16-byte stores: the table is 200 MB at buffer_size = 5e7, so this is a pure HBM-write kernel.
@@ -305,6 +318,27 @@ extern "C" {
 
 const char* pinq_last_error(void) { return g_err; }
 int pinq_version(void) { return 100; }
+
+void pinq_kernel_timing(int enable) {
+    g_ktime_on = enable != 0;
+    for (int i = 0; i < PINQ_KT_MARKS; ++i) g_ktime_set[i] = false;
+}
+
+int pinq_kernel_times(float* ms_out, int cap) {
+    // ms_out[i] = time between mark i and the next recorded mark (phase i of pinq.h's PINQ_KT_* list); -1 if absent
+    int nout = 0;
+    for (int i = 0; i + 1 < PINQ_KT_MARKS && nout < cap; ++i, ++nout) {
+        ms_out[i] = -1.f;
+        if (!g_ktime_set[i] || i == PINQ_KT_FWD_END) continue;
+        int j = i + 1;
+        while (j < PINQ_KT_MARKS && !g_ktime_set[j]) ++j;
+        if (j >= PINQ_KT_MARKS || (i < PINQ_KT_FWD_END && j > PINQ_KT_FWD_END)) continue;
+        if (cudaEventSynchronize(g_ktime_ev[j]) != cudaSuccess) continue;
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, g_ktime_ev[i], g_ktime_ev[j]) == cudaSuccess) ms_out[i] = ms;
+    }
+    return nout;
+}
 
 int pinq_table_clear(int32_t* table, uint32_t buffer_size, void* stream) {
     PINQ_REQUIRE(table != nullptr && buffer_size > 0, "null table");

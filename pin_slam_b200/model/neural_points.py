@@ -610,7 +610,7 @@ class _FusedSDFFn(torch.autograd.Function):
         nn_count = torch.empty(n, dtype=torch.int32, device=dev)
         a.sdf = P.ptr(sdf)
         a.nn_count = P.ptr(nn_count)
-        grad = std = cert = knn_idx = knn_w = relu_mask = perm = None
+        grad = std = cert = stage = relu_mask = perm = None
         if n >= npts.bin_queries_min:  # large batches are processed brick by brick (csrc/sort.cu)
             perm = torch.empty(n, dtype=torch.int32, device=dev)
             a.perm = P.ptr(perm)
@@ -620,12 +620,11 @@ class _FusedSDFFn(torch.autograd.Function):
         if want_std:
             std = torch.empty(n, dtype=torch.float32, device=dev)
             a.sdf_std = P.ptr(std)
-        if need_bwd or (want_certainty and training_mode):
-            knn_idx = torch.empty((n, K), dtype=torch.int32, device=dev)
-            knn_w = torch.empty((n, K), dtype=torch.float32, device=dev)
-            a.knn_idx = P.ptr(knn_idx)
-            a.knn_w = P.ptr(knn_w)
-        if need_bwd:  # relu'(pre) bits of the hidden layer: 48 B/query instead of re-evaluating layer 1
+        if need_bwd:
+            # what the backward re-reads: the stage blocks (K indices, IDW weights, x - p_k; 124 B/query) and the
+            # relu'(pre) bits of the hidden layer (48 B/query) -- nothing of the decoder is re-evaluated
+            stage = torch.empty(int(lib.pinq_stage_bytes(n)), dtype=torch.uint8, device=dev)
+            a.stage = P.ptr(stage)
             relu_mask = torch.empty(int(lib.pinq_relu_mask_words(n)), dtype=torch.int32, device=dev)
             a.relu_mask = P.ptr(relu_mask)
         if want_certainty:
@@ -635,7 +634,8 @@ class _FusedSDFFn(torch.autograd.Function):
         ctx.npts, ctx.decoder, ctx.query_locally = npts, decoder, query_locally
         ctx.after_pgo = npts.after_pgo
         if need_bwd:
-            ctx.save_for_backward(x, feats, knn_idx, knn_w, relu_mask, perm, grad if ctx.needs_input_grad[2] else None)
+            ctx.n = n
+            ctx.save_for_backward(feats, stage, relu_mask, perm, grad if ctx.needs_input_grad[2] else None)
         empty = torch.empty(0, device=dev)
         outs = (sdf, nn_count, grad if grad is not None else empty, std if std is not None else empty,
                 cert if cert is not None else empty)
@@ -646,22 +646,16 @@ class _FusedSDFFn(torch.autograd.Function):
     def backward(ctx, g_sdf, *unused):
         lib = P.load()
         npts, decoder = ctx.npts, ctx.decoder
-        x, feats, knn_idx, knn_w, relu_mask, perm, dx = ctx.saved_tensors
+        feats, stage, relu_mask, perm, dx = ctx.saved_tensors
         g = g_sdf.contiguous().float()
         b = P.BwdArgs()
         b.dec = decoder.view()
-        b.xyz = P.ptr(x)
-        b.n = x.shape[0]
-        b.flags = P.F_ROTATE if ctx.after_pgo else 0
+        b.n = ctx.n
+        b.flags = 0
         b.k = int(npts.config.query_nn_k)
         b.feature_dim = int(npts.geo_feature_dim)
-        pts = npts.local_neural_points if ctx.query_locally else npts.neural_points
-        quats = npts.local_point_orientations if ctx.query_locally else npts.point_orientations
-        b.point_xyz = P.ptr(pts.contiguous())
-        b.quats = P.ptr(quats.contiguous()) if ctx.after_pgo else None
         b.features = P.ptr(feats.detach())
-        b.knn_idx = P.ptr(knn_idx)
-        b.knn_w = P.ptr(knn_w)
+        b.stage = P.ptr(stage)
         b.relu_mask = P.ptr(relu_mask)
         b.perm = P.ptr(perm)
         b.grad_sdf = P.ptr(g)
