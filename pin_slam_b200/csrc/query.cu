@@ -101,145 +101,6 @@ __global__ void __launch_bounds__(kBlock) k_search(MapDev map, PointSrc src, int
     o[K] = nn;
 }
 
-// ---------------------------------------------------------------------------------------------
-// Neighbour search through the brick index (csrc/brick.cuh): the stencil of a query touches 2 x 2 x 2 bricks;
-// per brick one probe, then only the OCCUPIED voxels that belong to the stencil are visited (bit scan of
-// occupancy & stencil mask).  Same candidates, same exact d^2, same (d^2, stencil position) order as k_search.
-//
-// Stencil masks: for a query whose stencil box starts at voxel (sx, sy, sz) of brick b0 (s = (cell - R) & 3)
-// and for brick b0 + (ix, iy, iz), the 64-bit set of brick voxels that are stencil members.  64 x 8 masks,
-// built once per launch (k_stencil_masks) and staged in shared memory.
-constexpr int kStencilMasks = 64 * 8;
-constexpr uint32_t kRankBits = 24;  // low key word = stencil position << 24 | record rank (host guards m < 2^24)
-
-__global__ void k_stencil_masks(const int32_t* __restrict__ stencil_dx, int kn, int R, unsigned long long* __restrict__ out) {
-    __shared__ uint8_t member[128];
-    const int W = 2 * R + 1;
-    for (int c = threadIdx.x; c < 128; c += blockDim.x) member[c] = 0;
-    __syncthreads();
-    for (int c = threadIdx.x; c < kn; c += blockDim.x)
-        member[((stencil_dx[3 * c] + R) * W + (stencil_dx[3 * c + 1] + R)) * W + (stencil_dx[3 * c + 2] + R)] = 1;
-    __syncthreads();
-    for (int e = threadIdx.x; e < kStencilMasks; e += blockDim.x) {
-        const int sx = (e >> 7) & 3, sy = (e >> 5) & 3, sz = (e >> 3) & 3, ix = (e >> 2) & 1, iy = (e >> 1) & 1, iz = e & 1;
-        unsigned long long m = 0ull;
-        for (int bit = 0; bit < 64; ++bit) {
-            // offset of brick voxel (lx,ly,lz) from the box origin, per axis: 4 i + l - s  in [0, 2R] for members
-            const int ox = 4 * ix + (bit >> 4) - sx, oy = 4 * iy + ((bit >> 2) & 3) - sy, oz = 4 * iz + (bit & 3) - sz;
-            if (ox < 0 || oy < 0 || oz < 0 || ox >= W || oy >= W || oz >= W) continue;
-            if (member[(ox * W + oy) * W + oz]) m |= 1ull << bit;
-        }
-        out[e] = m;
-    }
-}
-
-// sorted insertion of a 64-bit key (d^2 bits : stencil position : rank) into the ascending top-K
-__device__ __forceinline__ void topk_insert64(unsigned long long key, unsigned long long (&kk)[K]) {
-#pragma unroll
-    for (int k = K - 1; k > 0; --k) {
-        // after the step slot k holds the k-th smallest of {old slots, key}
-        const unsigned long long lo = kk[k - 1], cur = kk[k];
-        kk[k] = key < lo ? lo : (key < cur ? key : cur);
-    }
-    kk[0] = key < kk[0] ? key : kk[0];
-}
-
-struct BrickLane {  // per-lane walk state of one brick, staged in shared memory ([brick][thread], conflict-free)
-    unsigned long long msk[8][kBlock];
-    unsigned long long sel[8][kBlock];
-    uint32_t bas[8][kBlock];
-};
-
-__global__ void __launch_bounds__(kBlock) k_search_brick(MapDev map, BrickDev bd, PointSrc src, int64_t n, bool recip,
-                                                         const int32_t* __restrict__ perm,
-                                                         const unsigned long long* __restrict__ stencil_masks,
-                                                         int32_t* __restrict__ ws) {
-    extern __shared__ __align__(16) unsigned char s_brick_raw[];
-    BrickLane* bl = reinterpret_cast<BrickLane*>(s_brick_raw);
-    unsigned long long* s_masks = reinterpret_cast<unsigned long long*>(s_brick_raw + sizeof(BrickLane));
-    uint8_t* s_sid = reinterpret_cast<uint8_t*>(s_masks + kStencilMasks);  // stencil position of offset (dx,dy,dz)
-    const int R = bd.radius, W = 2 * R + 1, tid = threadIdx.x;
-    for (int c = tid; c < kStencilMasks; c += blockDim.x) s_masks[c] = stencil_masks[c];
-    for (int c = tid; c < 128; c += blockDim.x) s_sid[c] = 0xFF;
-    __syncthreads();
-    for (int c = tid; c < map.kn; c += blockDim.x) {
-        const int dx = map.stencil_dx[3 * c], dy = map.stencil_dx[3 * c + 1], dz = map.stencil_dx[3 * c + 2];
-        s_sid[((dx + R) * W + (dy + R)) * W + (dz + R)] = (uint8_t)c;
-    }
-    __syncthreads();
-
-    const int64_t i = (int64_t)blockIdx.x * blockDim.x + tid;
-    const bool live = i < n;
-    float x = 0.f, y = 0.f, z = 0.f;
-    if (live) load_point(src, perm ? perm[i] : i, x, y, z);
-    const int cx = cell_of(x, map.res, map.inv_res, recip), cy = cell_of(y, map.res, map.inv_res, recip),
-              cz = cell_of(z, map.res, map.inv_res, recip);
-    const int ax = cx - R, ay = cy - R, az = cz - R;  // box origin
-    const int b0x = ax >> 2, b0y = ay >> 2, b0z = az >> 2;
-    const int srow = (((ax & 3) * 4 + (ay & 3)) * 4 + (az & 3)) * 8;
-
-    // phase 1: one probe per brick, all eight issued before any is used
-    int total = 0;
-#pragma unroll
-    for (int b = 0; b < 8; ++b) {
-        unsigned long long msk = 0ull, sel = 0ull;
-        uint32_t bas = 0u;
-        const unsigned long long want = s_masks[srow + b];
-        if (live && want) {
-            const int e = brick_find(bd.tab, bd.cap_mask, brick_key(b0x + (b >> 2), b0y + ((b >> 1) & 1), b0z + (b & 1)));
-            if (e >= 0) {
-                const uint4 v = __ldg(reinterpret_cast<const uint4*>(&bd.tab[e]));
-                msk = ((unsigned long long)v.y << 32) | v.x;
-                bas = v.z;
-                sel = msk & want;
-            }
-        }
-        bl->msk[b][tid] = msk;
-        bl->sel[b][tid] = sel;
-        bl->bas[b][tid] = bas;
-        total += __popcll(sel);
-    }
-
-    // phase 2: ONE loop over the lane's candidates of all bricks (trip count = max over the warp of `total`,
-    // not the sum over bricks of per-brick maxima); bodies are predicated so the warp stays converged
-    unsigned long long kk[K];
-#pragma unroll
-    for (int k = 0; k < K; ++k) kk[k] = ~0ull;
-    int nn = 0, b = -1;
-    unsigned long long m = 0ull, msk = 0ull;
-    uint32_t bas = 0u;
-    int ox = 0, oy = 0, oz = 0;
-    while (__any_sync(0xffffffffu, total > 0)) {
-        const bool act = total > 0;
-        while (act && m == 0ull) {  // next brick with candidates (at most 8 steps over the whole walk)
-            ++b;
-            m = bl->sel[b][tid];
-            msk = bl->msk[b][tid];
-            bas = bl->bas[b][tid];
-            ox = 4 * (b >> 2) - (ax & 3); oy = 4 * ((b >> 1) & 1) - (ay & 3); oz = 4 * (b & 1) - (az & 3);
-        }
-        --total;
-        const int bit = act ? __ffsll((long long)m) - 1 : 0;
-        m &= m - 1ull;  // 0 stays 0
-        const uint32_t rank = bas + (uint32_t)__popcll(msk & ((1ull << bit) - 1ull));
-        float4 rc = make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
-        if (act) rc = __ldg(&bd.rec[rank]);
-        const int lin = ((ox + (bit >> 4)) * W + (oy + ((bit >> 2) & 3))) * W + (oz + (bit & 3));
-        const uint32_t sid = s_sid[lin & 127];
-        const float d2 = dist2_rn(rc.x, rc.y, rc.z, x, y, z);
-        // valid: index != -1 (-2 = hazard H13, still a candidate) and not d2 > max (neural_points.py:499)
-        const bool ok = act && __float_as_int(rc.w) != -1 && !(d2 > map.max_d2);
-        nn += ok ? 1 : 0;
-        const unsigned long long key = ok ? ((unsigned long long)__float_as_uint(d2) << 32) | (sid << kRankBits) | rank : ~0ull;
-        topk_insert64(key, kk);
-    }
-    if (!live) return;
-    int32_t* o = ws + i * kWs;
-#pragma unroll
-    for (int k = 0; k < K; ++k) o[k] = kk[k] == ~0ull ? -1 : (int32_t)((uint32_t)kk[k] & ((1u << kRankBits) - 1u));
-    o[K] = nn;
-}
-
 struct DecodeParams {
     const float4* rec;
     float max_d2;
@@ -281,7 +142,7 @@ struct QueryLane {
 // EFFECTS: write the per-query API outputs and apply the training-mode side effects (done exactly once per query:
 // by k_resolve / k_query_feature; the gradient flavour of the decode re-derives the lane state with EFFECTS = false)
 template <bool WANT_U, bool EFFECTS, bool STORE_KNN>
-__device__ __forceinline__ void resolve_query(const DecodeParams& p, const int32_t* wsq, int64_t i, int64_t q, bool live,
+__device__ __forceinline__ void resolve_ranks(const DecodeParams& p, const int32_t (&r)[K], int nn, int64_t q, bool live,
                                               float x, float y, float z, QueryLane& L) {
     L.nn = 0;
 #pragma unroll
@@ -292,10 +153,7 @@ __device__ __forceinline__ void resolve_query(const DecodeParams& p, const int32
         if (WANT_U) L.ux[k] = L.uy[k] = L.uz[k] = 0.f;
     }
     if (live) {
-        L.nn = wsq[K];
-        int32_t r[K];
-#pragma unroll
-        for (int k = 0; k < K; ++k) r[k] = wsq[k];
+        L.nn = nn;
         float4 rc[K];
 #pragma unroll
         for (int k = 0; k < K; ++k)
@@ -357,6 +215,186 @@ __device__ __forceinline__ void resolve_query(const DecodeParams& p, const int32
     }
 }
 
+// the same from the search workspace (K record ranks + count of query position i)
+template <bool WANT_U, bool EFFECTS, bool STORE_KNN>
+__device__ __forceinline__ void resolve_query(const DecodeParams& p, const int32_t* wsq, int64_t i, int64_t q, bool live,
+                                              float x, float y, float z, QueryLane& L) {
+    (void)i;
+    int32_t r[K];
+    int nn = 0;
+#pragma unroll
+    for (int k = 0; k < K; ++k) r[k] = live ? wsq[k] : -1;
+    if (live) nn = wsq[K];
+    resolve_ranks<WANT_U, EFFECTS, STORE_KNN>(p, r, nn, q, live, x, y, z, L);
+}
+
+// lane = query: the lane's column of its warp's stage block (the hand-off to the decode and the backward)
+__device__ __forceinline__ void stage_store(const DecodeParams& p, int64_t i, int lane, const QueryLane& L) {
+    StageBlock& sb = p.stage[i >> 5];
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+        sb.idx[k][lane] = L.kidx[k];
+        sb.w[k][lane] = L.w[k];
+        sb.v[k][0][lane] = L.vx[k];
+        sb.v[k][1][lane] = L.vy[k];
+        sb.v[k][2][lane] = L.vz[k];
+    }
+    sb.nn[lane] = L.nn;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Neighbour search through the brick index (csrc/brick.cuh): the stencil of a query touches 2 x 2 x 2 bricks;
+// per brick one probe, then only the OCCUPIED voxels that belong to the stencil are visited (bit scan of
+// occupancy & stencil mask).  Same candidates, same exact d^2, same (d^2, stencil position) order as k_search.
+//
+// Stencil masks: for a query whose stencil box starts at voxel (sx, sy, sz) of brick b0 (s = (cell - R) & 3)
+// and for brick b0 + (ix, iy, iz), the 64-bit set of brick voxels that are stencil members.  64 x 8 masks,
+// built once per launch (k_stencil_masks) and staged in shared memory.
+constexpr int kStencilMasks = 64 * 8;
+constexpr uint32_t kRankBits = 24;  // low key word = stencil position << 24 | record rank (host guards m < 2^24)
+
+__global__ void k_stencil_masks(const int32_t* __restrict__ stencil_dx, int kn, int R, unsigned long long* __restrict__ out) {
+    __shared__ uint8_t member[128];
+    const int W = 2 * R + 1;
+    for (int c = threadIdx.x; c < 128; c += blockDim.x) member[c] = 0;
+    __syncthreads();
+    for (int c = threadIdx.x; c < kn; c += blockDim.x)
+        member[((stencil_dx[3 * c] + R) * W + (stencil_dx[3 * c + 1] + R)) * W + (stencil_dx[3 * c + 2] + R)] = 1;
+    __syncthreads();
+    for (int e = threadIdx.x; e < kStencilMasks; e += blockDim.x) {
+        const int sx = (e >> 7) & 3, sy = (e >> 5) & 3, sz = (e >> 3) & 3, ix = (e >> 2) & 1, iy = (e >> 1) & 1, iz = e & 1;
+        unsigned long long m = 0ull;
+        for (int bit = 0; bit < 64; ++bit) {
+            // offset of brick voxel (lx,ly,lz) from the box origin, per axis: 4 i + l - s  in [0, 2R] for members
+            const int ox = 4 * ix + (bit >> 4) - sx, oy = 4 * iy + ((bit >> 2) & 3) - sy, oz = 4 * iz + (bit & 3) - sz;
+            if (ox < 0 || oy < 0 || oz < 0 || ox >= W || oy >= W || oz >= W) continue;
+            if (member[(ox * W + oy) * W + oz]) m |= 1ull << bit;
+        }
+        out[e] = m;
+    }
+}
+
+// sorted insertion of a 64-bit key (d^2 bits : stencil position : rank) into the ascending top-K
+__device__ __forceinline__ void topk_insert64(unsigned long long key, unsigned long long (&kk)[K]) {
+#pragma unroll
+    for (int k = K - 1; k > 0; --k) {
+        // after the step slot k holds the k-th smallest of {old slots, key}
+        const unsigned long long lo = kk[k - 1], cur = kk[k];
+        kk[k] = key < lo ? lo : (key < cur ? key : cur);
+    }
+    kk[0] = key < kk[0] ? key : kk[0];
+}
+
+struct BrickLane {  // per-lane walk state of one brick, staged in shared memory ([brick][thread], conflict-free)
+    unsigned long long msk[8][kBlock];
+    unsigned long long sel[8][kBlock];
+    uint32_t bas[8][kBlock];
+};
+
+// RESOLVE: the walk ends with the lane's K winners in registers and their records hot in L1, so the resolve step
+// (stage block, per-query outputs, training side effects -- what k_resolve does after the slot-probing search)
+// runs in the tail of this kernel; the rank workspace is then only written for the gradient flavour of the decode.
+template <bool RESOLVE>
+__global__ void __launch_bounds__(kBlock) k_search_brick(MapDev map, BrickDev bd, PointSrc src, int64_t n, bool recip,
+                                                         const int32_t* __restrict__ perm,
+                                                         const unsigned long long* __restrict__ stencil_masks,
+                                                         int32_t* __restrict__ ws, const DecodeParams p) {
+    extern __shared__ __align__(16) unsigned char s_brick_raw[];
+    BrickLane* bl = reinterpret_cast<BrickLane*>(s_brick_raw);
+    unsigned long long* s_masks = reinterpret_cast<unsigned long long*>(s_brick_raw + sizeof(BrickLane));
+    uint8_t* s_sid = reinterpret_cast<uint8_t*>(s_masks + kStencilMasks);  // stencil position of offset (dx,dy,dz)
+    const int R = bd.radius, W = 2 * R + 1, tid = threadIdx.x;
+    for (int c = tid; c < kStencilMasks; c += blockDim.x) s_masks[c] = stencil_masks[c];
+    for (int c = tid; c < 128; c += blockDim.x) s_sid[c] = 0xFF;
+    __syncthreads();
+    for (int c = tid; c < map.kn; c += blockDim.x) {
+        const int dx = map.stencil_dx[3 * c], dy = map.stencil_dx[3 * c + 1], dz = map.stencil_dx[3 * c + 2];
+        s_sid[((dx + R) * W + (dy + R)) * W + (dz + R)] = (uint8_t)c;
+    }
+    __syncthreads();
+
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + tid;
+    const bool live = i < n;
+    const int64_t q = (live && perm) ? (int64_t)perm[i] : i;
+    float x = 0.f, y = 0.f, z = 0.f;
+    if (live) load_point(src, q, x, y, z);
+    const int cx = cell_of(x, map.res, map.inv_res, recip), cy = cell_of(y, map.res, map.inv_res, recip),
+              cz = cell_of(z, map.res, map.inv_res, recip);
+    const int ax = cx - R, ay = cy - R, az = cz - R;  // box origin
+    const int b0x = ax >> 2, b0y = ay >> 2, b0z = az >> 2;
+    const int srow = (((ax & 3) * 4 + (ay & 3)) * 4 + (az & 3)) * 8;
+
+    // phase 1: one probe per brick, all eight issued before any is used
+    int total = 0;
+#pragma unroll
+    for (int b = 0; b < 8; ++b) {
+        unsigned long long msk = 0ull, sel = 0ull;
+        uint32_t bas = 0u;
+        const unsigned long long want = s_masks[srow + b];
+        if (live && want) {
+            const int e = brick_find(bd.tab, bd.cap_mask, brick_key(b0x + (b >> 2), b0y + ((b >> 1) & 1), b0z + (b & 1)));
+            if (e >= 0) {
+                const uint4 v = __ldg(reinterpret_cast<const uint4*>(&bd.tab[e]));
+                msk = ((unsigned long long)v.y << 32) | v.x;
+                bas = v.z;
+                sel = msk & want;
+            }
+        }
+        bl->msk[b][tid] = msk;
+        bl->sel[b][tid] = sel;
+        bl->bas[b][tid] = bas;
+        total += __popcll(sel);
+    }
+
+    // phase 2: ONE loop over the lane's candidates of all bricks (trip count = max over the warp of `total`,
+    // not the sum over bricks of per-brick maxima); bodies are predicated so the warp stays converged
+    unsigned long long kk[K];
+#pragma unroll
+    for (int k = 0; k < K; ++k) kk[k] = ~0ull;
+    int nn = 0, b = -1;
+    unsigned long long m = 0ull, msk = 0ull;
+    uint32_t bas = 0u;
+    int ox = 0, oy = 0, oz = 0;
+    while (__any_sync(0xffffffffu, total > 0)) {
+        const bool act = total > 0;
+        while (act && m == 0ull) {  // next brick with candidates (at most 8 steps over the whole walk)
+            ++b;
+            m = bl->sel[b][tid];
+            msk = bl->msk[b][tid];
+            bas = bl->bas[b][tid];
+            ox = 4 * (b >> 2) - (ax & 3); oy = 4 * ((b >> 1) & 1) - (ay & 3); oz = 4 * (b & 1) - (az & 3);
+        }
+        --total;
+        const int bit = act ? __ffsll((long long)m) - 1 : 0;
+        m &= m - 1ull;  // 0 stays 0
+        const uint32_t rank = bas + (uint32_t)__popcll(msk & ((1ull << bit) - 1ull));
+        float4 rc = make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
+        if (act) rc = __ldg(&bd.rec[rank]);
+        const int lin = ((ox + (bit >> 4)) * W + (oy + ((bit >> 2) & 3))) * W + (oz + (bit & 3));
+        const uint32_t sid = s_sid[lin & 127];
+        const float d2 = dist2_rn(rc.x, rc.y, rc.z, x, y, z);
+        // valid: index != -1 (-2 = hazard H13, still a candidate) and not d2 > max (neural_points.py:499)
+        const bool ok = act && __float_as_int(rc.w) != -1 && !(d2 > map.max_d2);
+        nn += ok ? 1 : 0;
+        const unsigned long long key = ok ? ((unsigned long long)__float_as_uint(d2) << 32) | (sid << kRankBits) | rank : ~0ull;
+        topk_insert64(key, kk);
+    }
+    int32_t r[K];
+#pragma unroll
+    for (int k = 0; k < K; ++k) r[k] = kk[k] == ~0ull ? -1 : (int32_t)((uint32_t)kk[k] & ((1u << kRankBits) - 1u));
+    if (live && (!RESOLVE || p.grad_x)) {
+        int32_t* o = ws + i * kWs;
+#pragma unroll
+        for (int k = 0; k < K; ++k) o[k] = r[k];
+        o[K] = nn;
+    }
+    if (RESOLVE) {
+        QueryLane L;
+        resolve_ranks<false, true, true>(p, r, nn, q, live, x, y, z, L);
+        if (i - (tid & 31) < n) stage_store(p, i, tid & 31, L);
+    }
+}
+
 // Un-fused API form (model/neural_points.py:574-632): writes the [n,K,F+3] feature tensor, no MLP.
 __global__ void __launch_bounds__(kBlock) k_query_feature(const DecodeParams p) {
     const int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -396,16 +434,7 @@ __global__ void __launch_bounds__(kBlock) k_resolve(const DecodeParams p) {
     QueryLane L;
     resolve_query<false, true, true>(p, p.ws + i * kWs, i, q, live, x, y, z, L);
     if (i - lane >= p.n) return;  // whole warp past the end
-    StageBlock& sb = p.stage[i >> 5];
-#pragma unroll
-    for (int k = 0; k < K; ++k) {
-        sb.idx[k][lane] = L.kidx[k];
-        sb.w[k][lane] = L.w[k];
-        sb.v[k][0][lane] = L.vx[k];
-        sb.v[k][1][lane] = L.vy[k];
-        sb.v[k][2][lane] = L.vz[k];
-    }
-    sb.nn[lane] = L.nn;
+    stage_store(p, i, lane, L);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -471,12 +500,20 @@ __global__ void __launch_bounds__(kBlock, GRAD ? 3 : 4) k_decode_mma(const Decod
         __syncwarp();  // the previous iteration's epilogue reads of st are done
 
         // ---- lane = (g,t): software-pipelined over the 12 m-tiles ----
+        // two-stage pipeline: the neighbour indices are loaded two m-tiles ahead, the rows they address one m-tile
+        // ahead, so that neither load waits on the other inside the loop (ncu r1o: long-scoreboard was the top stall)
         float nraw[6];
         bool nany;
+        int nla, nlb;
+        auto fetch_idx = [&](int mt) {
+            const int qa = 16 * (mt & 1) + g;
+            nla = __ldg(&sb.idx[mt >> 1][qa]);
+            nlb = __ldg(&sb.idx[mt >> 1][qa + 8]);
+        };
         auto fetch = [&](int mt) {
             const int k = mt >> 1, half = mt & 1;
             const int qa = 16 * half + g, qb = qa + 8;
-            const int la = __ldg(&sb.idx[k][qa]), lb = __ldg(&sb.idx[k][qb]);
+            const int la = nla, lb = nlb;
 #pragma unroll
             for (int i = 0; i < 6; ++i) nraw[i] = 0.f;
             nany = __any_sync(0xffffffffu, (la >= 0) | (lb >= 0));
@@ -492,7 +529,9 @@ __global__ void __launch_bounds__(kBlock, GRAD ? 3 : 4) k_decode_mma(const Decod
             nraw[4] = t < 3 ? __ldg(&sb.v[k][t < 3 ? t : 0][qa]) : 1.f;
             nraw[5] = t < 3 ? __ldg(&sb.v[k][t < 3 ? t : 0][qb]) : 1.f;
         };
+        fetch_idx(0);
         fetch(0);
+        fetch_idx(1);
 #pragma unroll 1
         for (int mt = 0; mt < kMTiles; ++mt) {
             const int k = mt >> 1, half = mt & 1;
@@ -506,6 +545,7 @@ __global__ void __launch_bounds__(kBlock, GRAD ? 3 : 4) k_decode_mma(const Decod
             const bool any = nany;
 #endif
             if (mt + 1 < kMTiles) fetch(mt + 1);
+            if (mt + 2 < kMTiles) fetch_idx(mt + 2);
             uint32_t bits = 0;
             float sA = 0.f, sB = 0.f, c2[4] = {0.f, 0.f, 0.f, 0.f};
             if (any) {  // warp-uniform: tiles without a single valid neighbour carry weight 0 everywhere
@@ -702,7 +742,6 @@ static int run_query(const pinq_query_args* a, int mode, float* feat_out, const 
         if (rc) return rc;
         perm = a->perm;
     }
-    ktime_mark(PINQ_KT_SEARCH, st);
     const bool brick = a->map.brick_tab != nullptr;
     BrickDev bd;
     if (brick) {
@@ -715,16 +754,7 @@ static int run_query(const pinq_query_args* a, int mode, float* feat_out, const 
         bd.cap_mask = a->map.brick_cap - 1;
         bd.rec = reinterpret_cast<const float4*>(a->map.brick_rec4);
         bd.radius = a->map.stencil_radius;
-        unsigned long long* smasks = reinterpret_cast<unsigned long long*>(
-            reinterpret_cast<unsigned char*>(a->workspace) + ws_off_masks(n));
-        k_stencil_masks<<<1, 256, 0, st>>>(map.stencil_dx, map.kn, bd.radius, smasks);
-        const size_t smem = sizeof(BrickLane) + kStencilMasks * 8 + 128;
-        k_search_brick<<<grid_for(n, kBlock), kBlock, smem, st>>>(map, bd, src, n, recip, perm, smasks, ws);
-    } else {
-        k_search<<<grid_for(n, kBlock), kBlock, map.kn * sizeof(uint32_t), st>>>(map, src, n, recip, perm, ws);
     }
-    rc = check_launch("k_search");
-    if (rc) return rc;
 
     DecodeParams p;
     p.rec = brick ? bd.rec : map.rec; p.max_d2 = map.max_d2; p.dec = a->dec; p.src = src; p.n = n;
@@ -742,13 +772,32 @@ static int run_query(const pinq_query_args* a, int mode, float* feat_out, const 
     p.relu_mask = reinterpret_cast<uint32_t*>(a->relu_mask);
     p.stage = reinterpret_cast<StageBlock*>(a->stage ? a->stage
                                                      : reinterpret_cast<unsigned char*>(a->workspace) + ws_off_stage(n));
+
+    ktime_mark(PINQ_KT_SEARCH, st);
+    const bool resolve_in_search = brick && mode != 1;
+    if (brick) {
+        unsigned long long* smasks = reinterpret_cast<unsigned long long*>(
+            reinterpret_cast<unsigned char*>(a->workspace) + ws_off_masks(n));
+        k_stencil_masks<<<1, 256, 0, st>>>(map.stencil_dx, map.kn, bd.radius, smasks);
+        const size_t smem = sizeof(BrickLane) + kStencilMasks * 8 + 128;
+        if (resolve_in_search)
+            k_search_brick<true><<<grid_for(n, kBlock), kBlock, smem, st>>>(map, bd, src, n, recip, perm, smasks, ws, p);
+        else
+            k_search_brick<false><<<grid_for(n, kBlock), kBlock, smem, st>>>(map, bd, src, n, recip, perm, smasks, ws, p);
+    } else {
+        k_search<<<grid_for(n, kBlock), kBlock, map.kn * sizeof(uint32_t), st>>>(map, src, n, recip, perm, ws);
+    }
+    rc = check_launch("k_search");
+    if (rc) return rc;
     ktime_mark(PINQ_KT_RESOLVE, st);
     if (mode == 1) {
         k_query_feature<<<grid_for(n, kBlock), kBlock, 0, st>>>(p);
     } else {
-        k_resolve<<<grid_for(n, kBlock), kBlock, 0, st>>>(p);
-        rc = check_launch("k_resolve");
-        if (rc) return rc;
+        if (!resolve_in_search) {
+            k_resolve<<<grid_for(n, kBlock), kBlock, 0, st>>>(p);
+            rc = check_launch("k_resolve");
+            if (rc) return rc;
+        }
         ktime_mark(PINQ_KT_DECODE, st);
         // persistent-ish grid: the decoder fragments are built once per CTA and amortised over its blocks
         const unsigned nb = grid_for(n, kBlock);

@@ -32,8 +32,11 @@ __device__ __forceinline__ void red_add_v2(float* addr, float a, float b) {
     asm volatile("red.global.add.v2.f32 [%0], {%1, %2};" ::"l"(addr), "f"(a), "f"(b) : "memory");
 }
 
-struct BwdStage {
+template <bool DEC>
+struct BwdStage {  // per-warp copy of what phase B reads row-wise (shared-memory latency instead of L1/L2 latency)
+    int32_t idx[K][32];
     float ab[K][32];  // a_k = g w_k scale of row (k, query); 0 for invalid rows
+    float v[DEC ? K : 1][3][32];
 };
 
 constexpr int kGCols = IN + 1;  // 11 inputs + the bias column
@@ -44,7 +47,7 @@ template <bool DEC, bool FEAT>
 __global__ void __launch_bounds__(kBlock, 4) k_bwd_mma(const BwdParams p) {
     extern __shared__ __align__(16) unsigned char s_raw[];
     DecFrags* fr = reinterpret_cast<DecFrags*>(s_raw);
-    BwdStage* stages = reinterpret_cast<BwdStage*>(s_raw + sizeof(DecFrags));
+    BwdStage<DEC>* stages = reinterpret_cast<BwdStage<DEC>*>(s_raw + sizeof(DecFrags));
     __shared__ float s_G[DEC ? H * kGCols : 1];
     __shared__ float s_db2;
     build_dec_frags(p.dec, fr, false, FEAT, false);
@@ -54,7 +57,7 @@ __global__ void __launch_bounds__(kBlock, 4) k_bwd_mma(const BwdParams p) {
     }
     __syncthreads();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane >> 2, t = lane & 3;
-    BwdStage& st = stages[warp];
+    BwdStage<DEC>& st = stages[warp];
     const float scale = p.dec.sdf_scale;
     const int64_t nblocks = (p.n + kBlock - 1) / kBlock;
 
@@ -72,7 +75,7 @@ __global__ void __launch_bounds__(kBlock, 4) k_bwd_mma(const BwdParams p) {
         const bool live = i < p.n;
         const int64_t q = (live && p.perm) ? (int64_t)p.perm[i] : i;
         const StageBlock& sb = p.stage[q0 >> 5];
-        // ---- phase A: lane = query ----
+        // ---- phase A: lane = query (coalesced, independent loads) ----
         __syncwarp();
         {
             const float gq = live ? p.grad_sdf[q] : 0.f;
@@ -80,20 +83,45 @@ __global__ void __launch_bounds__(kBlock, 4) k_bwd_mma(const BwdParams p) {
             for (int k = 0; k < K; ++k) {
                 const int32_t li = __ldg(&sb.idx[k][lane]);
                 const float a = (live && li >= 0) ? gq * __ldg(&sb.w[k][lane]) * scale : 0.f;
+                st.idx[k][lane] = li;
                 st.ab[k][lane] = a;
-                if (DEC) db2 += a;
+                if (DEC) {
+                    db2 += a;
+#pragma unroll
+                    for (int c = 0; c < 3; ++c) st.v[k][c][lane] = __ldg(&sb.v[k][c][lane]);
+                }
             }
         }
         __syncwarp();
 
-        // ---- phase B: lane = (g, t) ----
+        // ---- phase B: lane = (g, t); the mask bits and the gathered feature column of the next m-tile are in
+        // flight while this one is multiplied ----
+        uint32_t nbits;
+        float nf[DEC ? 4 : 1];
+        auto fetch = [&](int mt) {
+            nbits = __ldg(&p.relu_mask[((q0 >> 5) * kMTiles + mt) * 32 + lane]);
+            if (DEC) {
+#pragma unroll
+                for (int r4 = 0; r4 < 4; ++r4) {
+                    const int lr = st.idx[mt >> 1][16 * (mt & 1) + 2 * t + (r4 & 1) + 8 * (r4 >> 1)];
+                    nf[r4] = lr >= 0 ? __ldg(p.features + (int64_t)lr * F + g) : 0.f;
+                }
+            }
+        };
+        fetch(0);
 #pragma unroll 1
         for (int mt = 0; mt < kMTiles; ++mt) {
             const int k = mt >> 1, half = mt & 1;
             const int qa = 16 * half + g, qb = qa + 8;
-            const int la = __ldg(&sb.idx[k][qa]), lb = __ldg(&sb.idx[k][qb]);
+            const int la = st.idx[k][qa], lb = st.idx[k][qb];
+            const uint32_t bits = nbits;
+            float fcol[DEC ? 4 : 1];
+            if (DEC) {
+#pragma unroll
+                for (int r4 = 0; r4 < 4; ++r4) fcol[r4] = nf[r4];
+            }
+            if (mt + 1 < kMTiles) fetch(mt + 1);
             if (!__any_sync(0xffffffffu, (la >= 0) | (lb >= 0))) continue;  // warp-uniform
-            const uint32_t bits = __ldg(&p.relu_mask[((q0 >> 5) * kMTiles + mt) * 32 + lane]);
             uint32_t am[4][4];
             mask_frags(bits, am);
             if (FEAT) {
@@ -130,11 +158,10 @@ __global__ void __launch_bounds__(kBlock, 4) k_bwd_mma(const BwdParams p) {
 #pragma unroll
                 for (int r4 = 0; r4 < 4; ++r4) {
                     const int qr = 16 * half + 2 * t + (r4 & 1) + 8 * (r4 >> 1);
-                    const int lr = __ldg(&sb.idx[k][qr]);
                     const float ar = st.ab[k][qr];
-                    const float f = lr >= 0 ? ar * __ldg(p.features + (int64_t)lr * F + g) : 0.f;
+                    const float f = ar * fcol[r4];
                     // columns 8..10 = x - p_k from the stage, column 11 = the bias input 1
-                    const float v = g < 3 ? ar * __ldg(&sb.v[k][g < 3 ? g : 0][qr]) : (g == 3 ? ar : 0.f);
+                    const float v = g < 3 ? ar * st.v[k][g < 3 ? g : 0][qr] : (g == 3 ? ar : 0.f);
                     bf16_split3(f, xf[r4][0], xf[r4][1], xf[r4][2]);
                     bf16_split3(v, xv[r4][0], xv[r4][1], xv[r4][2]);
                 }
@@ -210,16 +237,18 @@ extern "C" int pinq_query_fused_bwd(const pinq_bwd_args* a, void* stream) {
     p.grad_W1 = a->grad_W1; p.grad_b1 = a->grad_b1; p.grad_W2 = a->grad_W2; p.grad_b2 = a->grad_b2;
     cudaStream_t st = as_stream(stream);
     const unsigned nb = grid_for(a->n, kBlock);
-    const size_t sm = sizeof(DecFrags) + (kBlock / 32) * sizeof(BwdStage);
+    const size_t sm_dec = sizeof(DecFrags) + (kBlock / 32) * sizeof(BwdStage<true>);
+    const size_t sm_feat = sizeof(DecFrags) + (kBlock / 32) * sizeof(BwdStage<false>);
+    const size_t sm = dec ? sm_dec : sm_feat;
     // one wave of resident CTAs striding over the blocks (every CTA ends in 833 global atomics when dec)
     static int occ_a = 0, occ_b = 0, occ_c = 0, sms = 0;
     if (!sms) {
         int dev = 0;
         cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_a, k_bwd_mma<true, true>, kBlock, sm);
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_b, k_bwd_mma<true, false>, kBlock, sm);
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_c, k_bwd_mma<false, true>, kBlock, sm);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_a, k_bwd_mma<true, true>, kBlock, sm_dec);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_b, k_bwd_mma<true, false>, kBlock, sm_dec);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_c, k_bwd_mma<false, true>, kBlock, sm_feat);
     }
     const int occ = dec ? (feat ? occ_a : occ_b) : occ_c;
     const unsigned cap = (unsigned)(sms * (occ > 0 ? occ : 1));
