@@ -37,9 +37,9 @@ UNIT = "queries/s"
 
 # kernels of libpinq launched by one step (fused forward + backward of a binned training-mode batch):
 # k_bin_count, k_bin_tile_sums, k_bin_tile_scan, k_bin_tile_apply, k_bin_scatter, k_stencil_masks, k_search_brick,
-# k_resolve, k_decode_mma, k_bwd_mma (the certainty scatter is fused into k_resolve unless the caller asks for the
-# queried certainty).  profiles/*_launches.csv is the ncu list of the same command.
-LAUNCHES_PER_STEP = 10
+# k_decode_mma, k_bwd_mma (the resolve step and the certainty scatter run in the tail of k_search_brick unless the
+# caller asks for the queried certainty).  profiles/*_launches.csv is the ncu list of the same command.
+LAUNCHES_PER_STEP = 9
 KERNEL_NAMES = {"bin": "k_bin_* (5 kernels)", "search": "k_search_brick", "resolve": "k_resolve",
                 "decode": "k_decode_mma", "scatter": "k_certainty_scatter", "bwd": "k_bwd_mma"}
 
@@ -345,15 +345,17 @@ def main():
                 if k and buf[j] >= 0:
                     acc[k].append(float(buf[j]))
     lib.pinq_kernel_timing(0)
-    kms = {k: float(np.mean(v)) for k, v in acc.items() if v}
+    kms = {k: float(np.mean(v)) for k, v in acc.items() if v and float(np.mean(v)) > 0.01}  # empty phases: event gaps
     ms_f = sum(v for k, v in kms.items() if k != "bwd")
     ms_b = kms.get("bwd", 0.0)
     hbm, peak_kind = peaks()
     # algorithmic bytes per query of each kernel (DESIGN.md "kernels"; SURVEY.md 8(d) for the whole path)
     kbytes = {
         "bin": 12 + 4 + 4 + 4,                 # xyz in, key out; key in, perm out (histogram stays in L2)
-        "search": 4 + 12 + 20 * vbar + 28,     # perm, xyz, 16 B record + 4 B brick share per occupied stencil voxel, K ranks + count
-        "resolve": 4 + 12 + 28 + K * 16 + 124 + 4,   # perm, xyz, ranks, K records, stage block out, nn_count out
+        # perm, xyz, 16 B record + 4 B brick share per occupied stencil voxel; resolve tail: stage block out, nn_count,
+        # training side effects (certainty add 4 + ts max 8 per neighbour)
+        "search": 4 + 12 + 20 * vbar + 124 + 4 + K * 12,
+        "resolve": 4 + 12 + 28 + K * 16 + 124 + 4,   # (slot-probing path only) perm, xyz, ranks, K records, stage out, nn_count
         "decode": 124 + K * 32 + 48 + 4 + 4,   # stage in, K feature rows, relu bits out, perm, sdf out
         "scatter": K * (4 + 4 + 4 + 8),        # idx, w in; certainty and ts atomics
         "bwd": 4 + 4 + 124 + 48 + K * 32 + K * 32,  # perm, dL/dsdf, stage, relu bits, K feature rows (decoder grads), K gradient rows

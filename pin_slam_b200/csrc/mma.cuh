@@ -49,6 +49,18 @@ __device__ __forceinline__ void bf16_split3(float x, __nv_bfloat16& b1, __nv_bfl
     const float r2 = r1 - __bfloat162float(b2);
     b3 = __float2bfloat16_rn(r2);
 }
+// Hot-loop variant for a PAIR of values: pieces by truncation (x & 0xffff0000 is a bf16; the remainders are exact), so
+// each piece of the pair is one PRMT of the two high halves: a = p[0].lo + p[1].lo + p[2].lo + O(2^-24 |a|), b likewise
+// in the high halves.  2 LOP3 + 2 FADD per value + 3 PRMT per pair instead of ~10 instructions per value (F2F based).
+__device__ __forceinline__ void bf16_split3_pair(float a, float b, uint32_t (&p)[3]) {
+    p[0] = __byte_perm(__float_as_uint(a), __float_as_uint(b), 0x7632);
+    const float a1 = a - __uint_as_float(__float_as_uint(a) & 0xffff0000u);
+    const float b1 = b - __uint_as_float(__float_as_uint(b) & 0xffff0000u);
+    p[1] = __byte_perm(__float_as_uint(a1), __float_as_uint(b1), 0x7632);
+    const float a2 = a1 - __uint_as_float(__float_as_uint(a1) & 0xffff0000u);
+    const float b2 = b1 - __uint_as_float(__float_as_uint(b1) & 0xffff0000u);
+    p[2] = __byte_perm(__float_as_uint(a2), __float_as_uint(b2), 0x7632);
+}
 __device__ __forceinline__ uint32_t pack_bf16(__nv_bfloat16 lo, __nv_bfloat16 hi) {
     return (uint32_t)__bfloat16_as_ushort(lo) | ((uint32_t)__bfloat16_as_ushort(hi) << 16);
 }
@@ -130,17 +142,16 @@ __device__ __forceinline__ void build_dec_frags(const pinq_decoder_view& d, DecF
     }
 }
 
-// relu'(pre) of one 16-row m-tile as bf16 A fragments (4 k-steps of 16 hidden units), from the bit mask
-// bit (4 nt + c) <-> accumulator acc[nt][c]
+// relu'(pre) of one 16-row m-tile as bf16 A fragments (4 k-steps of 16 hidden units), from the bit mask.
+// Bit layout chosen for this expansion: accumulator acc[nt][c] <-> bit 2 nt + (c >> 1) + 16 (c & 1), i.e. the two
+// elements of one fragment register sit 16 bits apart and one shift + and + multiply by bf16(1) expands them.
+__device__ __forceinline__ constexpr int mask_bit(int nt, int c) { return 2 * nt + (c >> 1) + 16 * (c & 1); }
 __device__ __forceinline__ void mask_frags(uint32_t bits, uint32_t (&a)[4][4]) {
 #pragma unroll
     for (int p = 0; p < 4; ++p) {
 #pragma unroll
-        for (int r = 0; r < 4; ++r) {
-            const int nt = 2 * p + (r >> 1), c = 2 * (r & 1);  // r: 0 (g, lo n-tile) 1 (g+8, lo) 2 (g, hi) 3 (g+8, hi)
-            const uint32_t lo = (bits >> (4 * nt + c)) & 1u, hi = (bits >> (4 * nt + c + 1)) & 1u;
-            a[p][r] = (lo ? kBf16One : 0u) | (hi ? (kBf16One << 16) : 0u);
-        }
+        for (int r = 0; r < 4; ++r)  // r: 0 (g, lo n-tile) 1 (g+8, lo) 2 (g, hi) 3 (g+8, hi)
+            a[p][r] = ((bits >> (4 * p + r)) & 0x00010001u) * kBf16One;
     }
 }
 

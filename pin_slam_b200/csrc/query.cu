@@ -274,22 +274,27 @@ __global__ void k_stencil_masks(const int32_t* __restrict__ stencil_dx, int kn, 
     }
 }
 
-// sorted insertion of a 64-bit key (d^2 bits : stencil position : rank) into the ascending top-K
+// sorted insertion of a 64-bit key (d^2 bits : stencil position : rank) into the ascending top-K: K compares,
+// each shared by two neighbouring slots
 __device__ __forceinline__ void topk_insert64(unsigned long long key, unsigned long long (&kk)[K]) {
+    bool lt[K];
 #pragma unroll
-    for (int k = K - 1; k > 0; --k) {
-        // after the step slot k holds the k-th smallest of {old slots, key}
-        const unsigned long long lo = kk[k - 1], cur = kk[k];
-        kk[k] = key < lo ? lo : (key < cur ? key : cur);
-    }
-    kk[0] = key < kk[0] ? key : kk[0];
+    for (int k = 0; k < K; ++k) lt[k] = key < kk[k];
+#pragma unroll
+    for (int k = K - 1; k > 0; --k) kk[k] = lt[k - 1] ? kk[k - 1] : (lt[k] ? key : kk[k]);
+    kk[0] = lt[0] ? key : kk[0];
 }
 
-struct BrickLane {  // per-lane walk state of one brick, staged in shared memory ([brick][thread], conflict-free)
-    unsigned long long msk[8][kBlock];
-    unsigned long long sel[8][kBlock];
-    uint32_t bas[8][kBlock];
+// Per-lane walk list staged in shared memory ([entry][thread], conflict-free).  An entry is one non-empty HALF brick
+// (x-slab of 2 x 4 x 4 voxels = 32 bits, so the walk is all 32-bit integer work); a (2R+1)^3 stencil with R <= 2
+// touches at most 3 x 2 x 2 of them.
+constexpr int kWalkEntries = 12;
+struct BrickLane {
+    uint32_t sel[kWalkEntries][kBlock];  // occupied stencil members still to visit
+    uint32_t msk[kWalkEntries][kBlock];  // occupancy of the half brick
+    uint32_t pk[kWalkEntries][kBlock];   // rank of its first record | (64 + linear stencil offset of its voxel 0) << 24
 };
+constexpr size_t kBrickSmem = sizeof(BrickLane) + kStencilMasks * 8 + 128 + 32;
 
 // RESOLVE: the walk ends with the lane's K winners in registers and their records hot in L1, so the resolve step
 // (stage block, per-query outputs, training side effects -- what k_resolve does after the slot-probing search)
@@ -303,9 +308,11 @@ __global__ void __launch_bounds__(kBlock) k_search_brick(MapDev map, BrickDev bd
     BrickLane* bl = reinterpret_cast<BrickLane*>(s_brick_raw);
     unsigned long long* s_masks = reinterpret_cast<unsigned long long*>(s_brick_raw + sizeof(BrickLane));
     uint8_t* s_sid = reinterpret_cast<uint8_t*>(s_masks + kStencilMasks);  // stencil position of offset (dx,dy,dz)
+    uint8_t* s_bitoff = s_sid + 128;  // linear stencil offset of voxel `bit` of a half brick relative to its voxel 0
     const int R = bd.radius, W = 2 * R + 1, tid = threadIdx.x;
     for (int c = tid; c < kStencilMasks; c += blockDim.x) s_masks[c] = stencil_masks[c];
     for (int c = tid; c < 128; c += blockDim.x) s_sid[c] = 0xFF;
+    for (int c = tid; c < 32; c += blockDim.x) s_bitoff[c] = (uint8_t)(((c >> 4) * W + ((c >> 2) & 3)) * W + (c & 3));
     __syncthreads();
     for (int c = tid; c < map.kn; c += blockDim.x) {
         const int dx = map.stencil_dx[3 * c], dy = map.stencil_dx[3 * c + 1], dz = map.stencil_dx[3 * c + 2];
@@ -324,59 +331,82 @@ __global__ void __launch_bounds__(kBlock) k_search_brick(MapDev map, BrickDev bd
     const int b0x = ax >> 2, b0y = ay >> 2, b0z = az >> 2;
     const int srow = (((ax & 3) * 4 + (ay & 3)) * 4 + (az & 3)) * 8;
 
-    // phase 1: one probe per brick, all eight issued before any is used
-    int total = 0;
+    // phase 1: one probe per brick, all eight issued before any is used; non-empty halves appended to the walk list
+    int total = 0, cnt = 0;
+    unsigned long long pm[8];
+    uint32_t pb[8];
 #pragma unroll
     for (int b = 0; b < 8; ++b) {
-        unsigned long long msk = 0ull, sel = 0ull;
-        uint32_t bas = 0u;
-        const unsigned long long want = s_masks[srow + b];
-        if (live && want) {
+        pm[b] = 0ull;
+        pb[b] = 0u;
+        if (live && s_masks[srow + b]) {
             const int e = brick_find(bd.tab, bd.cap_mask, brick_key(b0x + (b >> 2), b0y + ((b >> 1) & 1), b0z + (b & 1)));
             if (e >= 0) {
                 const uint4 v = __ldg(reinterpret_cast<const uint4*>(&bd.tab[e]));
-                msk = ((unsigned long long)v.y << 32) | v.x;
-                bas = v.z;
-                sel = msk & want;
+                pm[b] = ((unsigned long long)v.y << 32) | v.x;
+                pb[b] = v.z;
             }
         }
-        bl->msk[b][tid] = msk;
-        bl->sel[b][tid] = sel;
-        bl->bas[b][tid] = bas;
-        total += __popcll(sel);
+    }
+#pragma unroll
+    for (int b = 0; b < 8; ++b) {
+        const unsigned long long sel = pm[b] & s_masks[srow + b];
+        // stencil offset of the brick's voxel 0 from the box origin, linearised like s_sid
+        const int lin0 = ((4 * (b >> 2) - (ax & 3)) * W + (4 * ((b >> 1) & 1) - (ay & 3))) * W + (4 * (b & 1) - (az & 3));
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const uint32_t sel32 = (uint32_t)(sel >> (32 * h));
+            if (sel32) {
+                const uint32_t base = pb[b] + (h ? (uint32_t)__popc((uint32_t)pm[b]) : 0u);
+                bl->sel[cnt][tid] = sel32;
+                bl->msk[cnt][tid] = (uint32_t)(pm[b] >> (32 * h));
+                bl->pk[cnt][tid] = base | ((uint32_t)(lin0 + h * 2 * W * W + 64) << kRankBits);
+                ++cnt;
+                total += __popc(sel32);
+            }
+        }
     }
 
-    // phase 2: ONE loop over the lane's candidates of all bricks (trip count = max over the warp of `total`,
-    // not the sum over bricks of per-brick maxima); bodies are predicated so the warp stays converged
+    // phase 2: ONE loop over the lane's candidates of all its half bricks (trip count = max over the warp of `total`,
+    // bodies predicated so the warp stays converged), software-pipelined: the record of the next candidate is in
+    // flight while the current one is ranked
     unsigned long long kk[K];
 #pragma unroll
     for (int k = 0; k < K; ++k) kk[k] = ~0ull;
-    int nn = 0, b = -1;
-    unsigned long long m = 0ull, msk = 0ull;
-    uint32_t bas = 0u;
-    int ox = 0, oy = 0, oz = 0;
-    while (__any_sync(0xffffffffu, total > 0)) {
-        const bool act = total > 0;
-        while (act && m == 0ull) {  // next brick with candidates (at most 8 steps over the whole walk)
-            ++b;
-            m = bl->sel[b][tid];
-            msk = bl->msk[b][tid];
-            bas = bl->bas[b][tid];
-            ox = 4 * (b >> 2) - (ax & 3); oy = 4 * ((b >> 1) & 1) - (ay & 3); oz = 4 * (b & 1) - (az & 3);
+    int nn = 0, e = -1, lin0 = 0;
+    uint32_t m = 0u, msk = 0u, bas = 0u;
+    bool nact;
+    float4 nrc;
+    uint32_t nlow;  // stencil position << 24 | record rank of the candidate in flight
+    auto advance = [&]() {
+        nact = total > 0;
+        if (nact && m == 0u) {  // next half brick of the list
+            ++e;
+            m = bl->sel[e][tid];
+            msk = bl->msk[e][tid];
+            const uint32_t pk = bl->pk[e][tid];
+            bas = pk & ((1u << kRankBits) - 1u);
+            lin0 = (int)(pk >> kRankBits) - 64;
         }
         --total;
-        const int bit = act ? __ffsll((long long)m) - 1 : 0;
-        m &= m - 1ull;  // 0 stays 0
-        const uint32_t rank = bas + (uint32_t)__popcll(msk & ((1ull << bit) - 1ull));
-        float4 rc = make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
-        if (act) rc = __ldg(&bd.rec[rank]);
-        const int lin = ((ox + (bit >> 4)) * W + (oy + ((bit >> 2) & 3))) * W + (oz + (bit & 3));
-        const uint32_t sid = s_sid[lin & 127];
+        const int bit = (__ffs((int)m) - 1) & 31;
+        m &= m - 1u;  // 0 stays 0
+        const uint32_t rank = bas + (uint32_t)__popc(msk & ((1u << bit) - 1u));
+        nrc = make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
+        if (nact) nrc = __ldg(&bd.rec[rank]);
+        nlow = ((uint32_t)s_sid[(lin0 + s_bitoff[bit]) & 127] << kRankBits) | rank;
+    };
+    advance();
+    while (__any_sync(0xffffffffu, nact)) {
+        const bool act = nact;
+        const float4 rc = nrc;
+        const uint32_t low = nlow;
+        advance();
         const float d2 = dist2_rn(rc.x, rc.y, rc.z, x, y, z);
         // valid: index != -1 (-2 = hazard H13, still a candidate) and not d2 > max (neural_points.py:499)
         const bool ok = act && __float_as_int(rc.w) != -1 && !(d2 > map.max_d2);
         nn += ok ? 1 : 0;
-        const unsigned long long key = ok ? ((unsigned long long)__float_as_uint(d2) << 32) | (sid << kRankBits) | rank : ~0ull;
+        const unsigned long long key = ok ? ((unsigned long long)__float_as_uint(d2) << 32) | low : ~0ull;
         topk_insert64(key, kk);
     }
     int32_t r[K];
@@ -479,8 +509,9 @@ __global__ void __launch_bounds__(kBlock, GRAD ? 3 : 4) k_decode_mma(const Decod
     for (int nt = 0; nt < 8; ++nt) {
         const float4 wa = fr->w1a[nt][lane];
         const float4 wb = fr->w1b[nt][lane];
-        breg[nt][0] = __float_as_uint(wa.x); breg[nt][1] = __float_as_uint(wa.y); breg[nt][2] = __float_as_uint(wa.z);
-        breg[nt][3] = __float_as_uint(wa.w); breg[nt][4] = __float_as_uint(wb.x); breg[nt][5] = __float_as_uint(wb.y);
+        // pairs as the k-steps consume them: (hi B[t], hi B[t+4]) (lo B[t], lo B[t+4]) (hi B[8+t], lo B[8+t])
+        breg[nt][0] = __float_as_uint(wa.x); breg[nt][1] = __float_as_uint(wa.y); breg[nt][2] = __float_as_uint(wa.w);
+        breg[nt][3] = __float_as_uint(wb.x); breg[nt][4] = __float_as_uint(wa.z); breg[nt][5] = __float_as_uint(wb.y);
     }
 
     for (int64_t blk = blockIdx.x; blk < nblocks; blk += gridDim.x) {
@@ -552,19 +583,24 @@ __global__ void __launch_bounds__(kBlock, GRAD ? 3 : 4) k_decode_mma(const Decod
                 uint32_t ah[6], al[6];
 #pragma unroll
                 for (int i = 0; i < 6; ++i) tf32_split_trunc(raw[i], ah[i], al[i]);
+                // The three products of 3xTF32 in 5 k-steps with four DISJOINT A quads (a value shared by two quads
+                // makes the register allocator rebuild the aligned tuples per n-tile: 60 MOVs per m-tile in SASS):
+                //   q0 = lo(cols t, t+4)   x hi B          q1 = hi(cols t, t+4) x lo B, then x hi B
+                //   q2 = lo | hi (col 8+t) x (hi B | lo B)  q3 = hi(col 8+t), 0 x (hi B | -)
+                const uint32_t q2a = al[4], q2b = al[5], q2c = ah[4], q2d = ah[5];
+                uint32_t q3a = ah[4], q3b = ah[5];
+                asm volatile("" : "+r"(q3a), "+r"(q3b));  // distinct registers for the second use of hi(col 8+t)
                 float acc[8][4];
 #pragma unroll
                 for (int nt = 0; nt < 8; ++nt) {
                     acc[nt][0] = acc[nt][1] = acc[nt][2] = acc[nt][3] = 0.f;
-                    const uint32_t bh0 = breg[nt][0], bh1 = breg[nt][1], ch = breg[nt][2], bl0 = breg[nt][3];
-                    const uint32_t bl1 = breg[nt][4], cl = breg[nt][5];
-                    // the three products of 3xTF32 concatenated along K: [lo | hi | hi] x [hi ; lo ; hi] = 36 real
-                    // columns in 5 k-steps (small terms first)
-                    mma_tf32(acc[nt], al[0], al[1], al[2], al[3], bh0, bh1);
-                    mma_tf32(acc[nt], al[4], al[5], ah[0], ah[1], ch, bl0);
-                    mma_tf32(acc[nt], ah[2], ah[3], ah[4], ah[5], bl1, cl);
-                    mma_tf32(acc[nt], ah[0], ah[1], ah[2], ah[3], bh0, bh1);
-                    mma_tf32(acc[nt], ah[4], ah[5], 0u, 0u, ch, 0u);
+                    const uint32_t h0 = breg[nt][0], h1 = breg[nt][1], l0 = breg[nt][2], l1 = breg[nt][3];
+                    const uint32_t h2 = breg[nt][4], l2 = breg[nt][5];
+                    mma_tf32(acc[nt], al[0], al[1], al[2], al[3], h0, h1);  // small terms first
+                    mma_tf32(acc[nt], ah[0], ah[1], ah[2], ah[3], l0, l1);
+                    mma_tf32(acc[nt], q2a, q2b, q2c, q2d, h2, l2);
+                    mma_tf32(acc[nt], ah[0], ah[1], ah[2], ah[3], h0, h1);
+                    mma_tf32(acc[nt], q3a, q3b, 0u, 0u, h2, l2);
                 }
                 uint32_t bitsA = 0u, bitsB = 0u;  // two chains: rows g and g + 8
 #pragma unroll
@@ -577,11 +613,11 @@ __global__ void __launch_bounds__(kBlock, GRAD ? 3 : 4) k_decode_mma(const Decod
                     sB = fmaf(h2, w2.x, sB);
                     sB = fmaf(h3, w2.y, sB);
                     // relu'(pre) = [h > 0] = min(bits(h), 1) for h >= 0: one IMNMX + one IMAD per element,
-                    // bit (4 nt + c) <-> acc[nt][c]
-                    bitsA = umin1(h0) * (1u << (4 * nt + 0)) + bitsA;
-                    bitsA = umin1(h1) * (1u << (4 * nt + 1)) + bitsA;
-                    bitsB = umin1(h2) * (1u << (4 * nt + 2)) + bitsB;
-                    bitsB = umin1(h3) * (1u << (4 * nt + 3)) + bitsB;
+                    // bit positions of mma.cuh's mask_bit()
+                    bitsA = umin1(h0) * (1u << mask_bit(nt, 0)) + bitsA;
+                    bitsA = umin1(h1) * (1u << mask_bit(nt, 1)) + bitsA;
+                    bitsB = umin1(h2) * (1u << mask_bit(nt, 2)) + bitsB;
+                    bitsB = umin1(h3) * (1u << mask_bit(nt, 3)) + bitsB;
                 }
                 bits = bitsA | bitsB;
                 sA += __shfl_xor_sync(0xffffffffu, sA, 1);
@@ -779,7 +815,7 @@ static int run_query(const pinq_query_args* a, int mode, float* feat_out, const 
         unsigned long long* smasks = reinterpret_cast<unsigned long long*>(
             reinterpret_cast<unsigned char*>(a->workspace) + ws_off_masks(n));
         k_stencil_masks<<<1, 256, 0, st>>>(map.stencil_dx, map.kn, bd.radius, smasks);
-        const size_t smem = sizeof(BrickLane) + kStencilMasks * 8 + 128;
+        const size_t smem = kBrickSmem;
         if (resolve_in_search)
             k_search_brick<true><<<grid_for(n, kBlock), kBlock, smem, st>>>(map, bd, src, n, recip, perm, smasks, ws, p);
         else

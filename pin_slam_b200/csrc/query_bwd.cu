@@ -154,26 +154,27 @@ __global__ void __launch_bounds__(kBlock, 4) k_bwd_mma(const BwdParams p) {
                     at[pp][3] = movmatrix_trans(am[pp][3]);  // (j = 16p + 8 + g ; rows 2t+8, 2t+9)
                 }
                 // B = X (row x input column): rows 2t, 2t+1, 2t+8, 2t+9 of this m-tile, column g (and 8 + g)
-                __nv_bfloat16 xf[4][3], xv[4][3];
+                float xf[4], xv[4];
 #pragma unroll
                 for (int r4 = 0; r4 < 4; ++r4) {
                     const int qr = 16 * half + 2 * t + (r4 & 1) + 8 * (r4 >> 1);
                     const float ar = st.ab[k][qr];
-                    const float f = ar * fcol[r4];
+                    xf[r4] = ar * fcol[r4];
                     // columns 8..10 = x - p_k from the stage, column 11 = the bias input 1
-                    const float v = g < 3 ? ar * st.v[k][g < 3 ? g : 0][qr] : (g == 3 ? ar : 0.f);
-                    bf16_split3(f, xf[r4][0], xf[r4][1], xf[r4][2]);
-                    bf16_split3(v, xv[r4][0], xv[r4][1], xv[r4][2]);
+                    xv[r4] = g < 3 ? ar * st.v[k][g < 3 ? g : 0][qr] : (g == 3 ? ar : 0.f);
                 }
+                uint32_t pf[2][3], pv[2][3];  // B fragments {rows 2t, 2t+1} {rows 2t+8, 2t+9} of the three bf16 pieces
+                bf16_split3_pair(xf[0], xf[1], pf[0]);
+                bf16_split3_pair(xf[2], xf[3], pf[1]);
+                bf16_split3_pair(xv[0], xv[1], pv[0]);
+                bf16_split3_pair(xv[2], xv[3], pv[1]);
 #pragma unroll
                 for (int jt = 0; jt < 4; ++jt) {
                     float tf[4] = {0.f, 0.f, 0.f, 0.f}, tv[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
                     for (int s = 2; s >= 0; --s) {
-                        mma_bf16(tf, at[jt][0], at[jt][1], at[jt][2], at[jt][3], pack_bf16(xf[0][s], xf[1][s]),
-                                 pack_bf16(xf[2][s], xf[3][s]));
-                        mma_bf16(tv, at[jt][0], at[jt][1], at[jt][2], at[jt][3], pack_bf16(xv[0][s], xv[1][s]),
-                                 pack_bf16(xv[2][s], xv[3][s]));
+                        mma_bf16(tf, at[jt][0], at[jt][1], at[jt][2], at[jt][3], pf[0][s], pf[1][s]);
+                        mma_bf16(tv, at[jt][0], at[jt][1], at[jt][2], at[jt][3], pv[0][s], pv[1][s]);
                     }
                     // accumulate outside the tensor core (round-to-nearest fp32 adds over the long row reduction)
 #pragma unroll
