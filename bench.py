@@ -375,12 +375,36 @@ def main():
     if not args.no_e2e:
         qh, th = q_host.pin_memory(), ts_host.pin_memory()
         out_h = torch.empty(n, dtype=torch.float32).pin_memory()
+        # The batch crosses PCIe in chunks on a copy stream, double-buffered against the fused forward + backward of
+        # the previous chunk (gradients accumulate over the chunks as over one batch); results go back per chunk.
+        nchunk = 4 if n % 4 == 0 and n >= 4 * 65536 else 1
+        cn = n // nchunk
+        copy_stream = torch.cuda.Stream()
+        xb = [torch.empty((cn, 3), dtype=torch.float32, device=dev) for _ in range(2)]
+        tb = [torch.empty(cn, dtype=torch.int64, device=dev) for _ in range(2)]
+        copied = [torch.cuda.Event() for _ in range(2)]
+        consumed = [torch.cuda.Event() for _ in range(2)]
+        ones_c = ones[:cn]
 
         def e2e_step():
-            x = qh.to(dev, non_blocking=True)
-            tt = th.to(dev, non_blocking=True)
-            s_ = step(x, tt)
-            out_h.copy_(s_.detach(), non_blocking=True)
+            zero_grads()
+            main = torch.cuda.current_stream()
+            for c in range(nchunk):
+                bi = c % 2
+                with torch.cuda.stream(copy_stream):
+                    copy_stream.wait_event(consumed[bi])  # the chunk that used this buffer is done
+                    xb[bi].copy_(qh[c * cn:(c + 1) * cn], non_blocking=True)
+                    tb[bi].copy_(th[c * cn:(c + 1) * cn], non_blocking=True)
+                    copied[bi].record(copy_stream)
+                main.wait_event(copied[bi])
+                out = npts.query_sdf(xb[bi], dec, tb[bi], True, True)
+                out["sdf"].backward(ones_c)
+                out_h[c * cn:(c + 1) * cn].copy_(out["sdf"].detach(), non_blocking=True)
+                consumed[bi].record(main)
+            if world > 1:
+                flat = torch.cat([p.grad.reshape(-1) for p in params[1:]])
+                dist.all_reduce(npts.local_geo_features.grad)
+                dist.all_reduce(flat)
 
         for _ in range(3):
             e2e_step()
