@@ -142,17 +142,23 @@ __device__ __forceinline__ void build_dec_frags(const pinq_decoder_view& d, DecF
     }
 }
 
-// relu'(pre) of one 16-row m-tile as bf16 A fragments (4 k-steps of 16 hidden units), from the bit mask.
-// Bit layout chosen for this expansion: accumulator acc[nt][c] <-> bit 2 nt + (c >> 1) + 16 (c & 1), i.e. the two
-// elements of one fragment register sit 16 bits apart and one shift + and + multiply by bf16(1) expands them.
-__device__ __forceinline__ constexpr int mask_bit(int nt, int c) { return 2 * nt + (c >> 1) + 16 * (c & 1); }
-__device__ __forceinline__ void mask_frags(uint32_t bits, uint32_t (&a)[4][4]) {
+// relu'(pre) bits of one (query, neighbour) row = two words (the saved mask is uint2[32-query block][K][query]):
+// hidden unit 16 p + 8 h + 2 t + e  <->  bit 8 (p & 1) + 4 h + t + 16 e of word p >> 1, i.e. the two elements of one
+// bf16 A-fragment register sit 16 bits apart and shift + and + multiply by bf16(1) expands them.
+// Fragments of one 16-row m-tile (4 k-steps of 16 hidden units) for lane (g, t) from the words of rows g and g + 8:
+__device__ __forceinline__ void mask_frags_rows(uint2 ra, uint2 rb, int t, uint32_t (&a)[4][4]) {
 #pragma unroll
     for (int p = 0; p < 4; ++p) {
+        const uint32_t wa = (p >> 1) ? ra.y : ra.x, wb = (p >> 1) ? rb.y : rb.x;
 #pragma unroll
-        for (int r = 0; r < 4; ++r)  // r: 0 (g, lo n-tile) 1 (g+8, lo) 2 (g, hi) 3 (g+8, hi)
-            a[p][r] = ((bits >> (4 * p + r)) & 0x00010001u) * kBf16One;
+        for (int h = 0; h < 2; ++h) {
+            const int sh = 8 * (p & 1) + 4 * h + t;
+            a[p][2 * h] = ((wa >> sh) & 0x00010001u) * kBf16One;      // row g,     hidden 16 p + 8 h + 2 t (+1)
+            a[p][2 * h + 1] = ((wb >> sh) & 0x00010001u) * kBf16One;  // row g + 8
+        }
     }
 }
+// position (before the shift by t) of accumulator acc[nt][c] of the mma.sync decode in its row's word nt >> 2
+__device__ __forceinline__ constexpr int mask_row_bit0(int nt, int c) { return 4 * (nt & 3) + 16 * (c & 1); }
 
 }  // namespace pinq

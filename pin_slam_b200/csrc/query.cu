@@ -11,6 +11,8 @@
 #ifndef PINQ_EXP
 #define PINQ_EXP 0  // timing experiments (scripts/gpu_exp.sh); 0 = the product
 #endif
+#include <stdlib.h>
+
 #include "brick.cuh"
 #include "mma.cuh"
 
@@ -577,7 +579,7 @@ __global__ void __launch_bounds__(kBlock, GRAD ? 3 : 4) k_decode_mma(const Decod
 #endif
             if (mt + 1 < kMTiles) fetch(mt + 1);
             if (mt + 2 < kMTiles) fetch_idx(mt + 2);
-            uint32_t bits = 0;
+            uint32_t mA0 = 0u, mA1 = 0u, mB0 = 0u, mB1 = 0u;  // relu' words of rows qa and qb (this lane's share)
             float sA = 0.f, sB = 0.f, c2[4] = {0.f, 0.f, 0.f, 0.f};
             if (any) {  // warp-uniform: tiles without a single valid neighbour carry weight 0 everywhere
                 uint32_t ah[6], al[6];
@@ -602,7 +604,6 @@ __global__ void __launch_bounds__(kBlock, GRAD ? 3 : 4) k_decode_mma(const Decod
                     mma_tf32(acc[nt], ah[0], ah[1], ah[2], ah[3], h0, h1);
                     mma_tf32(acc[nt], q3a, q3b, 0u, 0u, h2, l2);
                 }
-                uint32_t bitsA = 0u, bitsB = 0u;  // two chains: rows g and g + 8
 #pragma unroll
                 for (int nt = 0; nt < 8; ++nt) {
                     const float2 w2 = fr->w2[4 * nt + t];
@@ -612,21 +613,32 @@ __global__ void __launch_bounds__(kBlock, GRAD ? 3 : 4) k_decode_mma(const Decod
                     sA = fmaf(h1, w2.y, sA);
                     sB = fmaf(h2, w2.x, sB);
                     sB = fmaf(h3, w2.y, sB);
-                    // relu'(pre) = [h > 0] = min(bits(h), 1) for h >= 0: one IMNMX + one IMAD per element,
-                    // bit positions of mma.cuh's mask_bit()
-                    bitsA = umin1(h0) * (1u << mask_bit(nt, 0)) + bitsA;
-                    bitsA = umin1(h1) * (1u << mask_bit(nt, 1)) + bitsA;
-                    bitsB = umin1(h2) * (1u << mask_bit(nt, 2)) + bitsB;
-                    bitsB = umin1(h3) * (1u << mask_bit(nt, 3)) + bitsB;
+                    // relu'(pre) = [h > 0] = min(bits(h), 1) for h >= 0: one IMNMX + one IMAD per element, at the
+                    // t = 0 positions of mma.cuh's row layout (shifted by t below)
+                    uint32_t& wa = nt < 4 ? mA0 : mA1;
+                    uint32_t& wb = nt < 4 ? mB0 : mB1;
+                    wa = umin1(h0) * (1u << mask_row_bit0(nt, 0)) + wa;
+                    wa = umin1(h1) * (1u << mask_row_bit0(nt, 1)) + wa;
+                    wb = umin1(h2) * (1u << mask_row_bit0(nt, 2)) + wb;
+                    wb = umin1(h3) * (1u << mask_row_bit0(nt, 3)) + wb;
                 }
-                bits = bitsA | bitsB;
                 sA += __shfl_xor_sync(0xffffffffu, sA, 1);
                 sB += __shfl_xor_sync(0xffffffffu, sB, 1);
                 sA += __shfl_xor_sync(0xffffffffu, sA, 2);
                 sB += __shfl_xor_sync(0xffffffffu, sB, 2);
+                if (GRAD || p.relu_mask) {  // the four lanes of a quad hold disjoint bits of the same two rows
+                    mA0 <<= t; mA1 <<= t; mB0 <<= t; mB1 <<= t;
+#pragma unroll
+                    for (int o = 1; o <= 2; o <<= 1) {
+                        mA0 |= __shfl_xor_sync(0xffffffffu, mA0, o);
+                        mA1 |= __shfl_xor_sync(0xffffffffu, mA1, o);
+                        mB0 |= __shfl_xor_sync(0xffffffffu, mB0, o);
+                        mB1 |= __shfl_xor_sync(0xffffffffu, mB1, o);
+                    }
+                }
                 if (GRAD) {  // d s_k / d v_k = sum_j relu'(pre_j) W2[j] W1[j][8..10]
                     uint32_t am[4][4];
-                    mask_frags(bits, am);
+                    mask_frags_rows(make_uint2(mA0, mA1), make_uint2(mB0, mB1), t, am);
 #pragma unroll
                     for (int s = 2; s >= 0; --s)
 #pragma unroll
@@ -646,7 +658,11 @@ __global__ void __launch_bounds__(kBlock, GRAD ? 3 : 4) k_decode_mma(const Decod
                 if (t == 0) { ga[0] = c2[0]; ga[1] = c2[1]; gb[0] = c2[2]; gb[1] = c2[3]; }
                 if (t == 1) { ga[2] = c2[0]; gb[2] = c2[2]; }
             }
-            if (p.relu_mask) p.relu_mask[((q0 >> 5) * kMTiles + mt) * 32 + lane] = bits;
+            if (p.relu_mask && t < 2) {
+                uint2* m2 = reinterpret_cast<uint2*>(p.relu_mask) + ((q0 >> 5) * K + k) * 32;
+                if (t == 0) m2[qa] = make_uint2(mA0, mA1);
+                else m2[qb] = make_uint2(mB0, mB1);
+            }
         }
         __syncwarp();
 
@@ -701,6 +717,9 @@ __global__ void __launch_bounds__(kBlock, GRAD ? 3 : 4) k_decode_mma(const Decod
         }
     }
 }
+
+#include "decode_tc.cuh"
+
 
 // second pass of the exact training path: scatter after every query has read its certainties
 __global__ void k_certainty_scatter(const StageBlock* __restrict__ stage, const int64_t* __restrict__ query_ts,
@@ -856,12 +875,30 @@ static int run_query(const pinq_query_args* a, int mode, float* feat_out, const 
             cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_mesh, k_decode_mma<false, true>, kBlock, sm_plain);
             cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_grad, k_decode_mma<true, false>, kBlock, sm_grad);
         }
-        const int occ = mode == 2 ? occ_mesh : (a->grad_x ? occ_grad : occ_plain);
-        const unsigned cap = (unsigned)(sms * (occ > 0 ? occ : 1));
-        const unsigned g = nb < cap ? nb : cap;
-        if (mode == 2) k_decode_mma<false, true><<<g, kBlock, sm_plain, st>>>(p);
-        else if (a->grad_x) k_decode_mma<true, false><<<g, kBlock, sm_grad, st>>>(p);
-        else k_decode_mma<false, false><<<g, kBlock, sm_plain, st>>>(p);
+        // plain and mesher flavours: tcgen05 / TMEM kernel (decode_tc.cuh); PINQ_DECODE=mma keeps the mma.sync one
+        static int use_tc = -1;
+        if (use_tc < 0) {
+            const char* e = getenv("PINQ_DECODE");
+            use_tc = !(e && e[0] == 'm');
+            cudaFuncSetAttribute(k_decode_tc<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc::kSmemRequest);
+            cudaFuncSetAttribute(k_decode_tc<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc::kSmemRequest);
+            cudaFuncSetAttribute(k_decode_tc<false>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+            cudaFuncSetAttribute(k_decode_tc<true>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+        }
+        if (use_tc && !a->grad_x) {
+            const unsigned nb128 = grid_for(n, tc::kRows);
+            const unsigned cap128 = (unsigned)sms * 4u;  // 4 CTAs x 128 TMEM columns per SM
+            const unsigned g128 = nb128 < cap128 ? nb128 : cap128;
+            if (mode == 2) k_decode_tc<true><<<g128, tc::kRows, tc::kSmemRequest, st>>>(p);
+            else k_decode_tc<false><<<g128, tc::kRows, tc::kSmemRequest, st>>>(p);
+        } else {
+            const int occ = mode == 2 ? occ_mesh : (a->grad_x ? occ_grad : occ_plain);
+            const unsigned cap = (unsigned)(sms * (occ > 0 ? occ : 1));
+            const unsigned g = nb < cap ? nb : cap;
+            if (mode == 2) k_decode_mma<false, true><<<g, kBlock, sm_plain, st>>>(p);
+            else if (a->grad_x) k_decode_mma<true, false><<<g, kBlock, sm_grad, st>>>(p);
+            else k_decode_mma<false, false><<<g, kBlock, sm_plain, st>>>(p);
+        }
     }
     rc = check_launch("k_decode");
     if (rc) return rc;

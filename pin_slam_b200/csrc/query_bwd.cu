@@ -96,10 +96,12 @@ __global__ void __launch_bounds__(kBlock, 4) k_bwd_mma(const BwdParams p) {
 
         // ---- phase B: lane = (g, t); the mask bits and the gathered feature column of the next m-tile are in
         // flight while this one is multiplied ----
-        uint32_t nbits;
+        uint2 nra, nrb;  // relu' words of rows qa, qb of the next m-tile
         float nf[DEC ? 4 : 1];
         auto fetch = [&](int mt) {
-            nbits = __ldg(&p.relu_mask[((q0 >> 5) * kMTiles + mt) * 32 + lane]);
+            const uint2* m2 = reinterpret_cast<const uint2*>(p.relu_mask) + ((q0 >> 5) * K + (mt >> 1)) * 32 + 16 * (mt & 1) + g;
+            nra = __ldg(m2);
+            nrb = __ldg(m2 + 8);
             if (DEC) {
 #pragma unroll
                 for (int r4 = 0; r4 < 4; ++r4) {
@@ -114,7 +116,7 @@ __global__ void __launch_bounds__(kBlock, 4) k_bwd_mma(const BwdParams p) {
             const int k = mt >> 1, half = mt & 1;
             const int qa = 16 * half + g, qb = qa + 8;
             const int la = st.idx[k][qa], lb = st.idx[k][qb];
-            const uint32_t bits = nbits;
+            const uint2 ra = nra, rb = nrb;
             float fcol[DEC ? 4 : 1];
             if (DEC) {
 #pragma unroll
@@ -123,7 +125,7 @@ __global__ void __launch_bounds__(kBlock, 4) k_bwd_mma(const BwdParams p) {
             if (mt + 1 < kMTiles) fetch(mt + 1);
             if (!__any_sync(0xffffffffu, (la >= 0) | (lb >= 0))) continue;  // warp-uniform
             uint32_t am[4][4];
-            mask_frags(bits, am);
+            mask_frags_rows(ra, rb, t, am);
             if (FEAT) {
                 float c2[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
