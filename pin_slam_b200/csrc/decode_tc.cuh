@@ -85,18 +85,21 @@ __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.a
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 
-__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
     asm volatile(
-        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
         : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
-          "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),
-          "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
-          "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+          "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
         : "r"(taddr) : "memory");
 }
-__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+// wait for the outstanding tcgen05.ld; the registers are operands so that no use of them is scheduled above the wait
+__device__ __forceinline__ void tmem_ld_wait(uint32_t (&v)[16]) {
+    asm volatile("tcgen05.wait::ld.sync.aligned;"
+                 : "+r"(v[0]), "+r"(v[1]), "+r"(v[2]), "+r"(v[3]), "+r"(v[4]), "+r"(v[5]), "+r"(v[6]), "+r"(v[7]), "+r"(v[8]),
+                   "+r"(v[9]), "+r"(v[10]), "+r"(v[11]), "+r"(v[12]), "+r"(v[13]), "+r"(v[14]), "+r"(v[15])
+                 :: "memory");
+}
 
 }  // namespace tc
 
@@ -158,26 +161,36 @@ __global__ void __launch_bounds__(tc::kRows) k_decode_tc(const DecodeParams p) {
         mbar_wait(smem_u32(&S.bar[buf]), phase[buf]);
         phase[buf] ^= 1u;
         tc_fence_after();
-        uint32_t v0[32], v1[32];
-        tmem_ld32(tmem_row + (uint32_t)(buf * H), v0);
-        tmem_ld32(tmem_row + (uint32_t)(buf * H + 32), v1);
-        tmem_ld_wait();
-        tc_fence_before();  // the accumulator buffer may be overwritten after the next block-wide barrier
+        // 16 columns at a time, the next chunk in flight while this one is reduced (32 live registers instead of 64)
+        uint32_t va[16], vb[16];
+        const uint32_t t0 = tmem_row + (uint32_t)(buf * H);
         float s0 = 0.f, s1 = 0.f;
         uint32_t neg0 = 0u, neg1 = 0u;
+        auto reduce16 = [&](const uint32_t (&v)[16], int c0, float& s, uint32_t& neg) {
 #pragma unroll
-        for (int c = 0; c < 32; c += 4) {
-            const float4 wa = *reinterpret_cast<const float4*>(&S.w2[c]);
-            const float4 wb = *reinterpret_cast<const float4*>(&S.w2[32 + c]);
-            const float wav[4] = {wa.x, wa.y, wa.z, wa.w}, wbv[4] = {wb.x, wb.y, wb.z, wb.w};
+            for (int c = 0; c < 16; c += 4) {
+                const float4 w4 = *reinterpret_cast<const float4*>(&S.w2[c0 + c]);
+                const float wv[4] = {w4.x, w4.y, w4.z, w4.w};
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
-                s0 = fmaf(fmaxf(__uint_as_float(v0[c + u]), 0.f), wav[u], s0);
-                s1 = fmaf(fmaxf(__uint_as_float(v1[c + u]), 0.f), wbv[u], s1);
-                neg0 = __funnelshift_l(v0[c + u], neg0, 1);  // sign bits: 1 <-> relu' = 0
-                neg1 = __funnelshift_l(v1[c + u], neg1, 1);
+                for (int u = 0; u < 4; ++u) {
+                    s = fmaf(fmaxf(__uint_as_float(v[c + u]), 0.f), wv[u], s);
+                    neg = __funnelshift_l(v[c + u], neg, 1);  // sign bits: 1 <-> relu' = 0
+                }
             }
-        }
+        };
+        tmem_ld16(t0, va);
+        tmem_ld_wait(va);
+        tmem_ld16(t0 + 16, vb);
+        reduce16(va, 0, s0, neg0);
+        tmem_ld_wait(vb);
+        tmem_ld16(t0 + 32, va);
+        reduce16(vb, 16, s1, neg0);
+        tmem_ld_wait(va);
+        tmem_ld16(t0 + 48, vb);
+        reduce16(va, 32, s0, neg1);
+        tmem_ld_wait(vb);
+        tc_fence_before();  // the accumulator buffer may be overwritten after the next block-wide barrier
+        reduce16(vb, 48, s1, neg1);
         if (mask2 && ewarp) mask2[((ei >> 5) * K + k) * 32 + lane] = make_uint2(~neg0, ~neg1);
         const float s = ((s0 + s1) + b2) * scale;  // decoder.py:80-81
         sk[k] = s;
@@ -208,27 +221,48 @@ __global__ void __launch_bounds__(tc::kRows) k_decode_tc(const DecodeParams p) {
         }
     };
 
+    // Software pipeline of the gathers: the neighbour indices of a block are loaded one block ahead (coalesced), the
+    // feature row and x - p_k of a tile one tile ahead, so staging never waits on a dependent load.
+    int cidx[K], nidx[K];
+    float4 pfa, pfb, phv;  // inputs of the next tile to stage
+    auto load_idx = [&](int64_t bi, int (&idx)[K]) {
+        const bool wl = (bi - lane) < p.n;
+        const StageBlock& sb = p.stage[wl ? (bi >> 5) : 0];
+#pragma unroll
+        for (int k = 0; k < K; ++k) idx[k] = wl ? __ldg(&sb.idx[k][lane]) : -1;
+    };
+    auto load_tile = [&](int64_t bi, int k, int li) {
+        pfa = make_float4(0.f, 0.f, 0.f, 0.f);
+        pfb = pfa;
+        phv = make_float4(0.f, 0.f, 0.f, 1.f);  // inputs 8..10 = x - p_k, input 11 = 1 (bias column)
+        if (li >= 0) {
+            const StageBlock& sb = p.stage[bi >> 5];
+            const float4* fr = reinterpret_cast<const float4*>(p.features + (int64_t)li * F);
+            pfa = __ldg(fr);
+            pfb = __ldg(fr + 1);
+            phv.x = __ldg(&sb.v[k][0][lane]);
+            phv.y = __ldg(&sb.v[k][1][lane]);
+            phv.z = __ldg(&sb.v[k][2][lane]);
+        }
+    };
     int64_t pend_i = -1;  // processing position (of this thread) of the block whose last tile is still in flight
     bool pend_warp = false;
+    if ((int64_t)blockIdx.x < nblocks) {
+        load_idx((int64_t)blockIdx.x * kRows + tid, cidx);
+        load_tile((int64_t)blockIdx.x * kRows + tid, 0, cidx[0]);
+    }
     for (int64_t blk = blockIdx.x; blk < nblocks; blk += gridDim.x) {
         const int64_t i = blk * kRows + tid;
         const bool wlive = (i - lane) < p.n;  // this warp has a stage block
-        const StageBlock& sb = p.stage[wlive ? (i >> 5) : 0];
+        const int64_t ni = i + (int64_t)gridDim.x * kRows;
+        const bool has_next = blk + gridDim.x < nblocks;
+#pragma unroll
+        for (int k = 0; k < K; ++k) nidx[k] = -1;
 #pragma unroll
         for (int k = 0; k < K; ++k) {
             const int buf = k & 1;  // K is even: the tile parity is the same in every block
             // ---- stage tile (blk, k): thread = row ----
-            const int li = wlive ? __ldg(&sb.idx[k][lane]) : -1;
-            float4 fa = make_float4(0.f, 0.f, 0.f, 0.f), fb = fa;
-            float4 hv = make_float4(0.f, 0.f, 0.f, 1.f);  // inputs 8..10 = x - p_k, input 11 = 1 (bias column)
-            if (li >= 0) {
-                const float4* fr = reinterpret_cast<const float4*>(p.features + (int64_t)li * F);
-                fa = __ldg(fr);
-                fb = __ldg(fr + 1);
-                hv.x = __ldg(&sb.v[k][0][lane]);
-                hv.y = __ldg(&sb.v[k][1][lane]);
-                hv.z = __ldg(&sb.v[k][2][lane]);
-            }
+            const float4 fa = pfa, fb = pfb, hv = phv;
             auto lo_of = [](float x) { return x - __uint_as_float(__float_as_uint(x) & 0xffffe000u); };
             unsigned char* arow = S.a[buf] + tid * 16;
             *reinterpret_cast<float4*>(arow + 0 * kChunkABytes) = make_float4(lo_of(fa.x), lo_of(fa.y), lo_of(fa.z), lo_of(fa.w));
@@ -252,7 +286,10 @@ __global__ void __launch_bounds__(tc::kRows) k_decode_tc(const DecodeParams p) {
                 umma_tf32(d, adesc + 3 * ca, bdesc + 4 * cb, 1u);  // hi(v,1) | 0  x  hi W ; -
                 umma_commit(smem_u32(&S.bar[buf]));
             }
-            // ---- epilogue of the previous tile while these MMAs run ----
+            // ---- loads of the next tile, then the epilogue of the previous one while the MMAs run ----
+            if (k == 1 && has_next) load_idx(ni, nidx);
+            if (k + 1 < K) load_tile(i, k + 1, cidx[k + 1 < K ? k + 1 : 0]);
+            else if (has_next) load_tile(ni, 0, nidx[0]);
             if (k > 0) {
                 epilogue(k - 1, i, wlive);
             } else if (pend_i >= 0) {
@@ -262,6 +299,8 @@ __global__ void __launch_bounds__(tc::kRows) k_decode_tc(const DecodeParams p) {
         }
         pend_i = i;
         pend_warp = wlive;
+#pragma unroll
+        for (int k = 0; k < K; ++k) cidx[k] = nidx[k];
     }
     if (pend_i >= 0) {
         epilogue(K - 1, pend_i, pend_warp);
