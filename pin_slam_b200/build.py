@@ -15,7 +15,7 @@ CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libpinq.so")
 STAMP = os.path.join(HERE, ".libpinq.stamp")
 SOURCES = ["table.cu", "index.cu", "sort.cu", "brick.cu", "query.cu", "query_bwd.cu", "gn.cu"]
-HEADERS = [os.path.join(CSRC, "common.cuh"), os.path.join(CSRC, "query_common.cuh"), os.path.join(CSRC, "mma.cuh"), os.path.join(CSRC, "brick.cuh"), os.path.join(CSRC, "decode_tc.cuh"),
+HEADERS = [os.path.join(CSRC, "common.cuh"), os.path.join(CSRC, "query_common.cuh"), os.path.join(CSRC, "mma.cuh"), os.path.join(CSRC, "brick.cuh"), os.path.join(CSRC, "decode_tc.cuh"), os.path.join(CSRC, "tc.cuh"), os.path.join(CSRC, "bwd_tc.cuh"),
            os.path.join(ROOT, "include", "pinq.h")]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",

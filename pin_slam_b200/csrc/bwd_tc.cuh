@@ -1,0 +1,306 @@
+// bwd_tc.cuh -- backward of the fused query on tcgen05 / TMEM (included by query_bwd.cu inside namespace pinq).
+//
+// Same algebra as k_bwd_mma (query_bwd.cu header), other mapping: tile k = neighbour k of a block of 128 queries, so
+// THREAD = QUERY = row.  Per tile the thread expands its 64 relu' bits into one bf16 row of the MASK tile and writes
+// a_k [f_k, v_k, 1] (3 bf16 pieces, truncation split) into the X tile; both tiles are stored [8-element chunk][row] x 16
+// bytes, which is the UMMA canonical no-swizzle layout K-major for (row x hidden) AND MN-major for its transpose:
+//   mask x V    D1[128 rows x 32]   = MASK (A, K-major)  x V3 (B, K-major; 3 pieces x 8 feature columns)     4 MMAs K=16
+//   G^T         D2[128 x 64 hidden] += X^T (A, MN-major) x MASK (B, MN-major), reduction over the 128 rows    8 MMAs K=16
+// X^T has 40 rows (3 pieces x 12 inputs + pad); the instruction runs with M = 128 (same cost as M = 64, known TMEM
+// layout row = lane) and simply reads the shared memory behind the X tile for rows 40..127, whose results are never read.
+// D1 -> thread-local epilogue: dL/df_k = a_k (sum of the 3 pieces) -> red.global.add.v4.f32 x 2 into grad_features[idx_k].
+// D2 is flushed into fp32 shared-memory sums once per block of 6 tiles (768 rows), so the long reduction over rows is
+// done with round-to-nearest adds outside the tensor core as in k_bwd_mma.
+#pragma once
+#include "tc.cuh"
+
+namespace tcb {
+
+constexpr int kRows = 128;
+constexpr int kXCols = 40;                  // 3 pieces x 12 inputs (+4 zero)
+constexpr uint32_t kChunk = kRows * 16;     // 2048 bytes: one 8-element chunk of all 128 rows
+constexpr int kMaskChunks = H / 8;          // 8
+constexpr int kXChunks = kXCols / 8;        // 5
+constexpr int kVN = 32;                     // 3 pieces x 8 feature columns (+8 zero)
+constexpr uint32_t kTmemCols = 128;         // D1 at column 0 (32), D2 at column 64 (64)
+constexpr size_t kSmemRequest = 48 * 1024;  // at most 4 CTAs (4 x 128 TMEM columns) per SM
+
+struct Smem {
+    alignas(128) unsigned char x[kXChunks * kChunk];        // read as 16 chunks (M = 128): must be followed by >= 22 KB
+    alignas(128) unsigned char mask[kMaskChunks * kChunk];
+    alignas(128) unsigned char v3[kMaskChunks * kVN * 16];  // [hidden chunk][n] x 16 bytes
+    float gacc[H][kXCols];                                  // flushed G^T sums, [mask column][piece * 12 + input]
+    alignas(8) unsigned long long bar;
+    uint32_t tmem_base;
+    float db2;
+};
+static_assert(sizeof(Smem) <= kSmemRequest, "bwd_tc shared memory");
+static_assert(offsetof(Smem, x) + 16 * kChunk <= sizeof(Smem), "the M = 128 window of X^T must stay inside the allocation");
+
+// column of the MASK tile <-> hidden unit: pair u = col >> 1 comes from bit (u & 15) (+16 for the odd column) of word
+// u >> 4 of the row layout (mma.cuh: hidden 16 p + 8 h + 2 t + e <-> bit 8 (p & 1) + 4 h + t + 16 e of word p >> 1)
+__host__ __device__ constexpr int hidden_of_maskcol(int col) {
+    const int u = col >> 1, e = col & 1, w = u >> 4, s = u & 15;
+    return 16 * (2 * w + (s >> 3)) + 8 * ((s >> 2) & 1) + 2 * (s & 3) + e;
+}
+
+// D = f32, A = B = bf16
+constexpr uint32_t kIdescBase = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(kRows >> 4) << 24);
+constexpr uint32_t kIdescMV = kIdescBase | ((uint32_t)(kVN >> 3) << 17);                           // K-major x K-major, N = 32
+constexpr uint32_t kIdescGT = kIdescBase | (1u << 15) | (1u << 16) | ((uint32_t)(H >> 3) << 17);   // MN-major x MN-major, N = 64
+
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        :: "r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
+    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" :: "l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+__device__ __forceinline__ uint32_t hi16_pair(float a, float b) {  // {bf16 trunc(a), bf16 trunc(b)}
+    return __byte_perm(__float_as_uint(a), __float_as_uint(b), 0x7632);
+}
+__device__ __forceinline__ float drop_hi16(float x) { return x - __uint_as_float(__float_as_uint(x) & 0xffff0000u); }
+
+}  // namespace tcb
+
+template <bool DEC, bool FEAT>
+__global__ void __launch_bounds__(tcb::kRows) k_bwd_tc(const BwdParams p) {
+    using namespace tc;
+    using namespace tcb;
+    extern __shared__ __align__(128) unsigned char s_tcb_raw[];
+    Smem& S = *reinterpret_cast<Smem*>(s_tcb_raw);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+
+    // ---- once per CTA ----
+    if (FEAT) {  // V3[hidden chunk][n = piece * 8 + feature column]: 8 hidden units (mask-column order) x bf16
+        for (int e = tid; e < kMaskChunks * kVN; e += kRows) {
+            const int kc = e / kVN, n = e % kVN, s = n >> 3, c = n & 7;
+            uint32_t w[4];
+#pragma unroll
+            for (int pr = 0; pr < 4; ++pr) {
+                __nv_bfloat16 b[2][3];
+#pragma unroll
+                for (int e2 = 0; e2 < 2; ++e2) {
+                    const int j = hidden_of_maskcol(8 * kc + 2 * pr + e2);
+                    const float v = n < 24 ? __ldg(&p.dec.W2[j]) * __ldg(&p.dec.W1[j * IN + c]) : 0.f;
+                    bf16_split3(v, b[e2][0], b[e2][1], b[e2][2]);
+                }
+                w[pr] = pack_bf16(b[0][s < 3 ? s : 0], b[1][s < 3 ? s : 0]);
+            }
+            *reinterpret_cast<uint4*>(S.v3 + e * 16) = make_uint4(w[0], w[1], w[2], w[3]);
+        }
+    }
+    if (DEC) {
+        for (int e = tid; e < H * kXCols; e += kRows) (&S.gacc[0][0])[e] = 0.f;
+        if (tid == 0) S.db2 = 0.f;
+    }
+    if (tid == 0) {
+        mbar_init(smem_u32(&S.bar), 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
+                     :: "r"(smem_u32(&S.tmem_base)), "r"(kTmemCols) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    fence_async_smem();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = S.tmem_base;
+    const uint32_t tmem_row = tmem + ((uint32_t)(32 * warp) << 16);
+    const uint32_t kD2 = 64;  // first TMEM column of the G^T accumulator
+    // K-major: LBO = next 8-element chunk along K, SBO = next 8 rows.  MN-major: LBO = next 8 rows (K), SBO = next chunk.
+    const uint64_t maskK = umma_desc(smem_u32(S.mask), kChunk, 128);
+    const uint64_t v3K = umma_desc(smem_u32(S.v3), kVN * 16, 128);
+    const uint64_t xMN = umma_desc(smem_u32(S.x), 128, kChunk);
+    const uint64_t maskMN = umma_desc(smem_u32(S.mask), 128, kChunk);
+    const float scale = p.dec.sdf_scale;
+    const int64_t nblocks = (p.n + kRows - 1) / kRows;
+    const uint2* mask2 = reinterpret_cast<const uint2*>(p.relu_mask);
+    uint32_t phase = 0u;
+    float db2 = 0.f;
+
+    // software pipeline: indices and dL/dsdf one block ahead, tile inputs one tile ahead
+    int cidx[K], nidx[K];
+    float cg = 0.f, ng = 0.f;
+    uint2 pm = make_uint2(0u, 0u);
+    float pw = 0.f;
+    float4 pfa = make_float4(0.f, 0.f, 0.f, 0.f), pfb = pfa, phv = make_float4(0.f, 0.f, 0.f, 1.f);
+    auto load_block = [&](int64_t bi, int (&idx)[K], float& g) {
+        const bool wl = (bi - lane) < p.n;
+        const StageBlock& sb = p.stage[wl ? (bi >> 5) : 0];
+#pragma unroll
+        for (int k = 0; k < K; ++k) idx[k] = wl ? __ldg(&sb.idx[k][lane]) : -1;
+        g = 0.f;
+        if (bi < p.n) g = p.grad_sdf[p.perm ? (int64_t)p.perm[bi] : bi];
+    };
+    auto load_tile = [&](int64_t bi, int k, int li) {
+        pm = make_uint2(0u, 0u);
+        pw = 0.f;
+        pfa = make_float4(0.f, 0.f, 0.f, 0.f);
+        pfb = pfa;
+        phv = make_float4(0.f, 0.f, 0.f, 1.f);
+        if (li >= 0) {
+            const StageBlock& sb = p.stage[bi >> 5];
+            pm = __ldg(&mask2[((bi >> 5) * K + k) * 32 + lane]);
+            pw = __ldg(&sb.w[k][lane]);
+            if (DEC) {
+                const float4* fr = reinterpret_cast<const float4*>(p.features + (int64_t)li * F);
+                pfa = __ldg(fr);
+                pfb = __ldg(fr + 1);
+                phv.x = __ldg(&sb.v[k][0][lane]);
+                phv.y = __ldg(&sb.v[k][1][lane]);
+                phv.z = __ldg(&sb.v[k][2][lane]);
+            }
+        }
+    };
+    if ((int64_t)blockIdx.x < nblocks) {
+        load_block((int64_t)blockIdx.x * kRows + tid, cidx, cg);
+        load_tile((int64_t)blockIdx.x * kRows + tid, 0, cidx[0]);
+    }
+    for (int64_t blk = blockIdx.x; blk < nblocks; blk += gridDim.x) {
+        const int64_t i = blk * kRows + tid;
+        const int64_t ni = i + (int64_t)gridDim.x * kRows;
+        const bool has_next = blk + gridDim.x < nblocks;
+#pragma unroll
+        for (int k = 0; k < K; ++k) nidx[k] = -1;
+        ng = 0.f;
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+            const int li = cidx[k];
+            const float a = li >= 0 ? cg * pw * scale : 0.f;  // rows without a neighbour carry no gradient
+            // ---- MASK tile: 64 bits -> 32 bf16 pairs -> 8 chunks of 16 bytes ----
+            {
+                const uint2 m = li >= 0 ? pm : make_uint2(0u, 0u);
+#pragma unroll
+                for (int hc = 0; hc < kMaskChunks; ++hc) {
+                    uint32_t r[4];
+#pragma unroll
+                    for (int u4 = 0; u4 < 4; ++u4) {
+                        const int u = 4 * hc + u4;
+                        r[u4] = (((u < 16 ? m.x : m.y) >> (u & 15)) & 0x00010001u) * kBf16One;
+                    }
+                    *reinterpret_cast<uint4*>(S.mask + hc * kChunk + tid * 16) = make_uint4(r[0], r[1], r[2], r[3]);
+                }
+            }
+            // ---- X tile: a_k [f_k, v_k, 1] in 3 bf16 pieces (truncation split), column = piece * 12 + input ----
+            if (DEC) {
+                db2 += a;
+                float ps[12] = {pfa.x, pfa.y, pfa.z, pfa.w, pfb.x, pfb.y, pfb.z, pfb.w, phv.x, phv.y, phv.z, phv.w};
+#pragma unroll
+                for (int c = 0; c < 12; ++c) ps[c] *= a;
+                uint32_t wds[20];
+#pragma unroll
+                for (int s = 0; s < 3; ++s) {
+#pragma unroll
+                    for (int ip = 0; ip < 6; ++ip) {
+                        wds[s * 6 + ip] = hi16_pair(ps[2 * ip], ps[2 * ip + 1]);
+                        if (s < 2) {
+                            ps[2 * ip] = drop_hi16(ps[2 * ip]);
+                            ps[2 * ip + 1] = drop_hi16(ps[2 * ip + 1]);
+                        }
+                    }
+                }
+                wds[18] = wds[19] = 0u;
+#pragma unroll
+                for (int c = 0; c < kXChunks; ++c)
+                    *reinterpret_cast<uint4*>(S.x + c * kChunk + tid * 16) =
+                        make_uint4(wds[4 * c], wds[4 * c + 1], wds[4 * c + 2], wds[4 * c + 3]);
+            }
+            fence_async_smem();
+            tc_fence_before();
+            __syncthreads();
+            if (tid == 0) {
+                tc_fence_after();
+                if (FEAT) {
+#pragma unroll
+                    for (int ks = 0; ks < 4; ++ks)  // 16 hidden units = 2 chunks per step
+                        umma_bf16(tmem, maskK + (uint64_t)ks * (2 * kChunk >> 4), v3K + (uint64_t)ks * (2 * kVN * 16 >> 4),
+                                  kIdescMV, ks > 0);
+                }
+                if (DEC) {
+#pragma unroll
+                    for (int ks = 0; ks < 8; ++ks)  // 16 rows = 256 bytes per step
+                        umma_bf16(tmem + kD2, xMN + (uint64_t)ks * (256 >> 4), maskMN + (uint64_t)ks * (256 >> 4), kIdescGT,
+                                  (k > 0) | (ks > 0));
+                }
+                umma_commit(smem_u32(&S.bar));
+            }
+            // ---- loads of the next tile while the MMAs run ----
+            if (k == 1 && has_next) load_block(ni, nidx, ng);
+            if (k + 1 < K) load_tile(i, k + 1, cidx[k + 1 < K ? k + 1 : 0]);
+            else if (has_next) load_tile(ni, 0, nidx[0]);
+            mbar_wait(smem_u32(&S.bar), phase);
+            phase ^= 1u;
+            tc_fence_after();
+            if (FEAT) {  // D1 row: columns piece * 8 + c
+                uint32_t d0[16], d1[16];
+                tmem_ld16(tmem_row, d0);
+                tmem_ld16(tmem_row + 16, d1);
+                tmem_ld_wait(d0);
+                tmem_ld_wait(d1);
+                if (li >= 0) {
+                    float o[8];
+#pragma unroll
+                    for (int c = 0; c < 8; ++c)
+                        o[c] = ((__uint_as_float(d1[c]) + __uint_as_float(d0[8 + c])) + __uint_as_float(d0[c])) * a;
+                    float* gf = p.grad_features + (int64_t)li * F;
+                    red_add_v4(gf, o[0], o[1], o[2], o[3]);
+                    red_add_v4(gf + 4, o[4], o[5], o[6], o[7]);
+                }
+            }
+            if (DEC && k == K - 1 && warp < 2) {  // flush G^T of this block: row (lane) m = piece * 12 + input
+#pragma unroll
+                for (int c4 = 0; c4 < 4; ++c4) {
+                    uint32_t v[16];
+                    tmem_ld16(tmem_row + kD2 + 16 * c4, v);
+                    tmem_ld_wait(v);
+                    if (tid < kXCols) {
+#pragma unroll
+                        for (int u = 0; u < 16; ++u) S.gacc[16 * c4 + u][tid] += __uint_as_float(v[u]);
+                    }
+                }
+            }
+            tc_fence_before();
+        }
+#pragma unroll
+        for (int k = 0; k < K; ++k) cidx[k] = nidx[k];
+        cg = ng;
+    }
+
+    if (DEC) {
+        db2 = warp_sum(db2);
+        if (lane == 0) atomicAdd(&S.db2, db2);
+    }
+    __syncthreads();
+    if (DEC) {  // G[j][i] = sum of the 3 pieces; then dW1 = W2 G, db1 = W2 G[:,11], dW2[j] = W1b[j] . G[j], db2
+        float* sG = reinterpret_cast<float*>(S.mask);  // [H][12], the tiles are idle now
+        for (int e = tid; e < H * 12; e += kRows) {
+            const int c = e / 12, i = e - 12 * c, j = hidden_of_maskcol(c);
+            sG[j * 12 + i] = (S.gacc[c][24 + i] + S.gacc[c][12 + i]) + S.gacc[c][i];
+        }
+        __syncthreads();
+        for (int e = tid; e < H * 12; e += kRows) {
+            const int j = e / 12, i = e - 12 * j;
+            const float v = __ldg(&p.dec.W2[j]) * sG[e];
+            if (i < IN) atomicAdd(&p.grad_W1[j * IN + i], v);
+            else atomicAdd(&p.grad_b1[j], v);
+        }
+        for (int j = tid; j < H; j += kRows) {
+            float acc = __ldg(&p.dec.b1[j]) * sG[j * 12 + IN];
+#pragma unroll
+            for (int i = 0; i < IN; ++i) acc = fmaf(__ldg(&p.dec.W1[j * IN + i]), sG[j * 12 + i], acc);
+            atomicAdd(&p.grad_W2[j], acc);
+        }
+        if (tid == 0) atomicAdd(p.grad_b2, S.db2);
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem), "r"(kTmemCols) : "memory");
+    }
+}

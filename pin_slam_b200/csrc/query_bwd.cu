@@ -12,6 +12,9 @@
 // Nothing of the hidden layer is recomputed: the backward needs the mask (48 B/query), the K indices and
 // weights, and -- only while the decoder is trainable -- the gathered inputs.  Both products have one EXACT
 // operand (the 0/1 mask), so a 3-way bf16 split of the other one keeps fp32 accuracy (csrc/mma.cuh).
+#include <stddef.h>
+#include <stdlib.h>
+
 #include "mma.cuh"
 
 namespace pinq {
@@ -218,6 +221,8 @@ __global__ void __launch_bounds__(kBlock, 4) k_bwd_mma(const BwdParams p) {
     }
 }
 
+#include "bwd_tc.cuh"
+
 }  // namespace pinq
 
 using namespace pinq;
@@ -253,13 +258,34 @@ extern "C" int pinq_query_fused_bwd(const pinq_bwd_args* a, void* stream) {
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_b, k_bwd_mma<true, false>, kBlock, sm_dec);
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_c, k_bwd_mma<false, true>, kBlock, sm_feat);
     }
-    const int occ = dec ? (feat ? occ_a : occ_b) : occ_c;
-    const unsigned cap = (unsigned)(sms * (occ > 0 ? occ : 1));
-    const unsigned g = nb < cap ? nb : cap;
+    // tcgen05 / TMEM kernel (bwd_tc.cuh); PINQ_BWD=mma keeps the mma.sync one
+    static int use_tc = -1;
+    if (use_tc < 0) {
+        const char* e = getenv("PINQ_BWD");
+        use_tc = !(e && e[0] == 'm');
+        cudaFuncSetAttribute(k_bwd_tc<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tcb::kSmemRequest);
+        cudaFuncSetAttribute(k_bwd_tc<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tcb::kSmemRequest);
+        cudaFuncSetAttribute(k_bwd_tc<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tcb::kSmemRequest);
+        cudaFuncSetAttribute(k_bwd_tc<true, true>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+        cudaFuncSetAttribute(k_bwd_tc<true, false>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+        cudaFuncSetAttribute(k_bwd_tc<false, true>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+    }
     ktime_mark(PINQ_KT_BWD, st);
-    if (dec && feat) k_bwd_mma<true, true><<<g, kBlock, sm, st>>>(p);
-    else if (dec) k_bwd_mma<true, false><<<g, kBlock, sm, st>>>(p);
-    else k_bwd_mma<false, true><<<g, kBlock, sm, st>>>(p);
+    if (use_tc) {
+        const unsigned nb128 = grid_for(a->n, tcb::kRows);
+        const unsigned cap128 = (unsigned)sms * 4u;  // 4 CTAs x 128 TMEM columns per SM
+        const unsigned g128 = nb128 < cap128 ? nb128 : cap128;
+        if (dec && feat) k_bwd_tc<true, true><<<g128, tcb::kRows, tcb::kSmemRequest, st>>>(p);
+        else if (dec) k_bwd_tc<true, false><<<g128, tcb::kRows, tcb::kSmemRequest, st>>>(p);
+        else k_bwd_tc<false, true><<<g128, tcb::kRows, tcb::kSmemRequest, st>>>(p);
+    } else {
+        const int occ = dec ? (feat ? occ_a : occ_b) : occ_c;
+        const unsigned cap = (unsigned)(sms * (occ > 0 ? occ : 1));
+        const unsigned g = nb < cap ? nb : cap;
+        if (dec && feat) k_bwd_mma<true, true><<<g, kBlock, sm, st>>>(p);
+        else if (dec) k_bwd_mma<true, false><<<g, kBlock, sm, st>>>(p);
+        else k_bwd_mma<false, true><<<g, kBlock, sm, st>>>(p);
+    }
     ktime_mark(PINQ_KT_BWD_END, st);
     return check_launch("pinq_query_fused_bwd");
 }
