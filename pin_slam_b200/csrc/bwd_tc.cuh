@@ -126,9 +126,10 @@ __global__ void __launch_bounds__(tcb::kRows) k_bwd_tc(const BwdParams p) {
     // software pipeline: indices and dL/dsdf one block ahead, tile inputs one tile ahead
     int cidx[K], nidx[K];
     float cg = 0.f, ng = 0.f;
-    uint2 pm = make_uint2(0u, 0u);
-    float pw = 0.f;
-    float4 pfa = make_float4(0.f, 0.f, 0.f, 0.f), pfb = pfa, phv = make_float4(0.f, 0.f, 0.f, 1.f);
+    // two register sets, tile t uses set t & 1 and is loaded while tile t - 2 is multiplied
+    uint2 pm[2];
+    float pw[2];
+    float4 pfa[2], pfb[2], phv[2];
     auto load_block = [&](int64_t bi, int (&idx)[K], float& g) {
         const bool wl = (bi - lane) < p.n;
         const StageBlock& sb = p.stage[wl ? (bi >> 5) : 0];
@@ -138,28 +139,30 @@ __global__ void __launch_bounds__(tcb::kRows) k_bwd_tc(const BwdParams p) {
         if (bi < p.n) g = p.grad_sdf[p.perm ? (int64_t)p.perm[bi] : bi];
     };
     auto load_tile = [&](int64_t bi, int k, int li) {
-        pm = make_uint2(0u, 0u);
-        pw = 0.f;
-        pfa = make_float4(0.f, 0.f, 0.f, 0.f);
-        pfb = pfa;
-        phv = make_float4(0.f, 0.f, 0.f, 1.f);
+        const int st = k & 1;
+        pm[st] = make_uint2(0u, 0u);
+        pw[st] = 0.f;
+        pfa[st] = make_float4(0.f, 0.f, 0.f, 0.f);
+        pfb[st] = pfa[st];
+        phv[st] = make_float4(0.f, 0.f, 0.f, 1.f);
         if (li >= 0) {
             const StageBlock& sb = p.stage[bi >> 5];
-            pm = __ldg(&mask2[((bi >> 5) * K + k) * 32 + lane]);
-            pw = __ldg(&sb.w[k][lane]);
+            pm[st] = __ldg(&mask2[((bi >> 5) * K + k) * 32 + lane]);
+            pw[st] = __ldg(&sb.w[k][lane]);
             if (DEC) {
                 const float4* fr = reinterpret_cast<const float4*>(p.features + (int64_t)li * F);
-                pfa = __ldg(fr);
-                pfb = __ldg(fr + 1);
-                phv.x = __ldg(&sb.v[k][0][lane]);
-                phv.y = __ldg(&sb.v[k][1][lane]);
-                phv.z = __ldg(&sb.v[k][2][lane]);
+                pfa[st] = __ldg(fr);
+                pfb[st] = __ldg(fr + 1);
+                phv[st].x = __ldg(&sb.v[k][0][lane]);
+                phv[st].y = __ldg(&sb.v[k][1][lane]);
+                phv[st].z = __ldg(&sb.v[k][2][lane]);
             }
         }
     };
     if ((int64_t)blockIdx.x < nblocks) {
         load_block((int64_t)blockIdx.x * kRows + tid, cidx, cg);
         load_tile((int64_t)blockIdx.x * kRows + tid, 0, cidx[0]);
+        load_tile((int64_t)blockIdx.x * kRows + tid, 1, cidx[1]);
     }
     for (int64_t blk = blockIdx.x; blk < nblocks; blk += gridDim.x) {
         const int64_t i = blk * kRows + tid;
@@ -171,10 +174,11 @@ __global__ void __launch_bounds__(tcb::kRows) k_bwd_tc(const BwdParams p) {
 #pragma unroll
         for (int k = 0; k < K; ++k) {
             const int li = cidx[k];
-            const float a = li >= 0 ? cg * pw * scale : 0.f;  // rows without a neighbour carry no gradient
+            const int st = k & 1;
+            const float a = li >= 0 ? cg * pw[st] * scale : 0.f;  // rows without a neighbour carry no gradient
             // ---- MASK tile: 64 bits -> 32 bf16 pairs -> 8 chunks of 16 bytes ----
             {
-                const uint2 m = li >= 0 ? pm : make_uint2(0u, 0u);
+                const uint2 m = li >= 0 ? pm[st] : make_uint2(0u, 0u);
 #pragma unroll
                 for (int hc = 0; hc < kMaskChunks; ++hc) {
                     uint32_t r[4];
@@ -189,7 +193,8 @@ __global__ void __launch_bounds__(tcb::kRows) k_bwd_tc(const BwdParams p) {
             // ---- X tile: a_k [f_k, v_k, 1] in 3 bf16 pieces (truncation split), column = piece * 12 + input ----
             if (DEC) {
                 db2 += a;
-                float ps[12] = {pfa.x, pfa.y, pfa.z, pfa.w, pfb.x, pfb.y, pfb.z, pfb.w, phv.x, phv.y, phv.z, phv.w};
+                float ps[12] = {pfa[st].x, pfa[st].y, pfa[st].z, pfa[st].w, pfb[st].x, pfb[st].y, pfb[st].z, pfb[st].w,
+                                phv[st].x, phv[st].y, phv[st].z, phv[st].w};
 #pragma unroll
                 for (int c = 0; c < 12; ++c) ps[c] *= a;
                 uint32_t wds[20];
@@ -229,10 +234,10 @@ __global__ void __launch_bounds__(tcb::kRows) k_bwd_tc(const BwdParams p) {
                 }
                 umma_commit(smem_u32(&S.bar));
             }
-            // ---- loads of the next tile while the MMAs run ----
+            // ---- loads of the tile after the next while the MMAs run ----
             if (k == 1 && has_next) load_block(ni, nidx, ng);
-            if (k + 1 < K) load_tile(i, k + 1, cidx[k + 1 < K ? k + 1 : 0]);
-            else if (has_next) load_tile(ni, 0, nidx[0]);
+            if (k + 2 < K) load_tile(i, k + 2, cidx[k + 2 < K ? k + 2 : 0]);
+            else if (has_next) load_tile(ni, k + 2 - K, nidx[k + 2 >= K ? k + 2 - K : 0]);
             mbar_wait(smem_u32(&S.bar), phase);
             phase ^= 1u;
             tc_fence_after();
