@@ -5,9 +5,9 @@
 // a_k [f_k, v_k, 1] (3 bf16 pieces, truncation split) into the X tile; both tiles are stored [8-element chunk][row] x 16
 // bytes, which is the UMMA canonical no-swizzle layout K-major for (row x hidden) AND MN-major for its transpose:
 //   mask x V    D1[128 rows x 32]   = MASK (A, K-major)  x V3 (B, K-major; 3 pieces x 8 feature columns)     4 MMAs K=16
-//   G^T         D2[128 x 64 hidden] += X^T (A, MN-major) x MASK (B, MN-major), reduction over the 128 rows    8 MMAs K=16
-// X^T has 40 rows (3 pieces x 12 inputs + pad); the instruction runs with M = 128 (same cost as M = 64, known TMEM
-// layout row = lane) and simply reads the shared memory behind the X tile for rows 40..127, whose results are never read.
+//   G           D2[64 hidden x 40] += MASK^T (A, MN-major) x X (B, MN-major), reduction over the 128 rows      8 MMAs K=16
+// (X has 40 columns: 3 pieces x 12 inputs + pad).  Shared-memory bandwidth is what bounds this kernel (ncu: L1TEX 67 %):
+// per tile 26 KB of tile writes + 46 KB of operand reads by the tensor core.
 // D1 -> thread-local epilogue: dL/df_k = a_k (sum of the 3 pieces) -> red.global.add.v4.f32 x 2 into grad_features[idx_k].
 // D2 is flushed into fp32 shared-memory sums once per block of 6 tiles (768 rows), so the long reduction over rows is
 // done with round-to-nearest adds outside the tensor core as in k_bwd_mma.
@@ -22,20 +22,19 @@ constexpr uint32_t kChunk = kRows * 16;     // 2048 bytes: one 8-element chunk o
 constexpr int kMaskChunks = H / 8;          // 8
 constexpr int kXChunks = kXCols / 8;        // 5
 constexpr int kVN = 32;                     // 3 pieces x 8 feature columns (+8 zero)
-constexpr uint32_t kTmemCols = 128;         // D1 at column 0 (32), D2 at column 64 (64)
-constexpr size_t kSmemRequest = 48 * 1024;  // at most 4 CTAs (4 x 128 TMEM columns) per SM
+constexpr uint32_t kTmemCols = 128;         // D1 buffers at columns 0 and 32, D2 at column 64 (64)
+constexpr size_t kSmemRequest = 72 * 1024;  // 3 CTAs per SM (3 x 128 TMEM columns)
 
-struct Smem {
-    alignas(128) unsigned char x[kXChunks * kChunk];        // read as 16 chunks (M = 128): must be followed by >= 22 KB
-    alignas(128) unsigned char mask[kMaskChunks * kChunk];
+struct Smem {  // the tiles are double-buffered: tile t + 1 is staged while the MMAs of tile t run
+    alignas(128) unsigned char x[2][kXChunks * kChunk];        // each read as 16 chunks (M = 128): followed by >= 22 KB
+    alignas(128) unsigned char mask[2][kMaskChunks * kChunk];
     alignas(128) unsigned char v3[kMaskChunks * kVN * 16];  // [hidden chunk][n] x 16 bytes
-    float gacc[H][kXCols];                                  // flushed G^T sums, [mask column][piece * 12 + input]
-    alignas(8) unsigned long long bar;
+    float gacc[kXCols][H];                                  // flushed G sums, [piece * 12 + input][mask column]
+    alignas(8) unsigned long long bar[2];
     uint32_t tmem_base;
     float db2;
 };
 static_assert(sizeof(Smem) <= kSmemRequest, "bwd_tc shared memory");
-static_assert(offsetof(Smem, x) + 16 * kChunk <= sizeof(Smem), "the M = 128 window of X^T must stay inside the allocation");
 
 // column of the MASK tile <-> hidden unit: pair u = col >> 1 comes from bit (u & 15) (+16 for the odd column) of word
 // u >> 4 of the row layout (mma.cuh: hidden 16 p + 8 h + 2 t + e <-> bit 8 (p & 1) + 4 h + t + 16 e of word p >> 1)
@@ -47,7 +46,9 @@ __host__ __device__ constexpr int hidden_of_maskcol(int col) {
 // D = f32, A = B = bf16
 constexpr uint32_t kIdescBase = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(kRows >> 4) << 24);
 constexpr uint32_t kIdescMV = kIdescBase | ((uint32_t)(kVN >> 3) << 17);                           // K-major x K-major, N = 32
-constexpr uint32_t kIdescGT = kIdescBase | (1u << 15) | (1u << 16) | ((uint32_t)(H >> 3) << 17);   // MN-major x MN-major, N = 64
+// decoder-gradient product: M = 64 hidden units, N = 40, both operands MN-major (= transposed views of the row-major tiles)
+constexpr uint32_t kIdescG = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(kXCols >> 3) << 17) |
+                             ((uint32_t)(H >> 4) << 24);
 
 __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
     asm volatile(
@@ -97,7 +98,8 @@ __global__ void __launch_bounds__(tcb::kRows) k_bwd_tc(const BwdParams p) {
         if (tid == 0) S.db2 = 0.f;
     }
     if (tid == 0) {
-        mbar_init(smem_u32(&S.bar), 1);
+        mbar_init(smem_u32(&S.bar[0]), 1);
+        mbar_init(smem_u32(&S.bar[1]), 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 0) {
@@ -113,14 +115,11 @@ __global__ void __launch_bounds__(tcb::kRows) k_bwd_tc(const BwdParams p) {
     const uint32_t tmem_row = tmem + ((uint32_t)(32 * warp) << 16);
     const uint32_t kD2 = 64;  // first TMEM column of the G^T accumulator
     // K-major: LBO = next 8-element chunk along K, SBO = next 8 rows.  MN-major: LBO = next 8 rows (K), SBO = next chunk.
-    const uint64_t maskK = umma_desc(smem_u32(S.mask), kChunk, 128);
     const uint64_t v3K = umma_desc(smem_u32(S.v3), kVN * 16, 128);
-    const uint64_t xMN = umma_desc(smem_u32(S.x), 128, kChunk);
-    const uint64_t maskMN = umma_desc(smem_u32(S.mask), 128, kChunk);
     const float scale = p.dec.sdf_scale;
     const int64_t nblocks = (p.n + kRows - 1) / kRows;
     const uint2* mask2 = reinterpret_cast<const uint2*>(p.relu_mask);
-    uint32_t phase = 0u;
+    uint32_t phase[2] = {0u, 0u};
     float db2 = 0.f;
 
     // software pipeline: indices and dL/dsdf one block ahead, tile inputs one tile ahead
@@ -164,6 +163,50 @@ __global__ void __launch_bounds__(tcb::kRows) k_bwd_tc(const BwdParams p) {
         load_tile((int64_t)blockIdx.x * kRows + tid, 0, cidx[0]);
         load_tile((int64_t)blockIdx.x * kRows + tid, 1, cidx[1]);
     }
+    // epilogue of the tile that ran in buffer `buf`: D1 row of this thread -> dL/df of neighbour `li`
+    float a_prev = 0.f;
+    int li_prev = -1;
+    auto epilogue = [&](int buf) {
+        mbar_wait(smem_u32(&S.bar[buf]), phase[buf]);
+        phase[buf] ^= 1u;
+        tc_fence_after();
+        if (FEAT) {  // columns piece * 8 + c
+            uint32_t d0[16], d1[16];
+            tmem_ld16(tmem_row + 32 * buf, d0);
+            tmem_ld16(tmem_row + 32 * buf + 16, d1);
+            tmem_ld_wait(d0);
+            tmem_ld_wait(d1);
+            if (li_prev >= 0) {
+                float o[8];
+#pragma unroll
+                for (int c = 0; c < 8; ++c)
+                    o[c] = ((__uint_as_float(d1[c]) + __uint_as_float(d0[8 + c])) + __uint_as_float(d0[c])) * a_prev;
+                float* gf = p.grad_features + (int64_t)li_prev * F;
+                red_add_v4(gf, o[0], o[1], o[2], o[3]);
+                red_add_v4(gf + 4, o[4], o[5], o[6], o[7]);
+            }
+        }
+        tc_fence_before();
+    };
+    // G of a finished block (all its MMAs waited for) -> fp32 sums.  M = 64 accumulator layout: hidden row m sits in
+    // TMEM lane (m % 16) + 32 (m / 16), i.e. lanes 0..15 of every warp (cute/atom/mma_traits_sm100.hpp, 1SM M_MMA == 64)
+    auto flush = [&]() {
+        if (DEC) {
+#pragma unroll
+            for (int c3 = 0; c3 < 3; ++c3) {
+                uint32_t v[16];
+                tmem_ld16(tmem_row + kD2 + 16 * c3, v);
+                tmem_ld_wait(v);
+                if (lane < 16) {
+#pragma unroll
+                    for (int u = 0; u < 16; ++u)
+                        if (16 * c3 + u < kXCols) S.gacc[16 * c3 + u][16 * warp + lane] += __uint_as_float(v[u]);
+                }
+            }
+            tc_fence_before();
+        }
+    };
+    bool pending = false;  // the last tile of the previous block is still in flight
     for (int64_t blk = blockIdx.x; blk < nblocks; blk += gridDim.x) {
         const int64_t i = blk * kRows + tid;
         const int64_t ni = i + (int64_t)gridDim.x * kRows;
@@ -174,7 +217,7 @@ __global__ void __launch_bounds__(tcb::kRows) k_bwd_tc(const BwdParams p) {
 #pragma unroll
         for (int k = 0; k < K; ++k) {
             const int li = cidx[k];
-            const int st = k & 1;
+            const int st = k & 1;  // register set, tile buffer, D1 buffer and barrier of this tile (K is even)
             const float a = li >= 0 ? cg * pw[st] * scale : 0.f;  // rows without a neighbour carry no gradient
             // ---- MASK tile: 64 bits -> 32 bf16 pairs -> 8 chunks of 16 bytes ----
             {
@@ -187,7 +230,7 @@ __global__ void __launch_bounds__(tcb::kRows) k_bwd_tc(const BwdParams p) {
                         const int u = 4 * hc + u4;
                         r[u4] = (((u < 16 ? m.x : m.y) >> (u & 15)) & 0x00010001u) * kBf16One;
                     }
-                    *reinterpret_cast<uint4*>(S.mask + hc * kChunk + tid * 16) = make_uint4(r[0], r[1], r[2], r[3]);
+                    *reinterpret_cast<uint4*>(S.mask[st] + hc * kChunk + tid * 16) = make_uint4(r[0], r[1], r[2], r[3]);
                 }
             }
             // ---- X tile: a_k [f_k, v_k, 1] in 3 bf16 pieces (truncation split), column = piece * 12 + input ----
@@ -212,68 +255,53 @@ __global__ void __launch_bounds__(tcb::kRows) k_bwd_tc(const BwdParams p) {
                 wds[18] = wds[19] = 0u;
 #pragma unroll
                 for (int c = 0; c < kXChunks; ++c)
-                    *reinterpret_cast<uint4*>(S.x + c * kChunk + tid * 16) =
+                    *reinterpret_cast<uint4*>(S.x[st] + c * kChunk + tid * 16) =
                         make_uint4(wds[4 * c], wds[4 * c + 1], wds[4 * c + 2], wds[4 * c + 3]);
+            }
+            if (k == 0 && pending) {  // drain the previous block before its G^T accumulator is overwritten
+                epilogue(1);
+                flush();
             }
             fence_async_smem();
             tc_fence_before();
             __syncthreads();
             if (tid == 0) {
                 tc_fence_after();
+                // K-major: LBO = next 8-element chunk along K, SBO = next 8 rows.  MN-major: LBO = next 8 rows, SBO = next chunk.
+                const uint32_t ma = smem_u32(S.mask[st]);
                 if (FEAT) {
+                    const uint64_t maskK = umma_desc(ma, kChunk, 128);
 #pragma unroll
                     for (int ks = 0; ks < 4; ++ks)  // 16 hidden units = 2 chunks per step
-                        umma_bf16(tmem, maskK + (uint64_t)ks * (2 * kChunk >> 4), v3K + (uint64_t)ks * (2 * kVN * 16 >> 4),
-                                  kIdescMV, ks > 0);
+                        umma_bf16(tmem + 32 * st, maskK + (uint64_t)ks * (2 * kChunk >> 4),
+                                  v3K + (uint64_t)ks * (2 * kVN * 16 >> 4), kIdescMV, ks > 0);
                 }
                 if (DEC) {
+                    const uint64_t xMN = umma_desc(smem_u32(S.x[st]), 128, kChunk);
+                    const uint64_t maskMN = umma_desc(ma, 128, kChunk);
 #pragma unroll
                     for (int ks = 0; ks < 8; ++ks)  // 16 rows = 256 bytes per step
-                        umma_bf16(tmem + kD2, xMN + (uint64_t)ks * (256 >> 4), maskMN + (uint64_t)ks * (256 >> 4), kIdescGT,
+                        umma_bf16(tmem + kD2, maskMN + (uint64_t)ks * (256 >> 4), xMN + (uint64_t)ks * (256 >> 4), kIdescG,
                                   (k > 0) | (ks > 0));
                 }
-                umma_commit(smem_u32(&S.bar));
+                umma_commit(smem_u32(&S.bar[st]));
             }
-            // ---- loads of the tile after the next while the MMAs run ----
+            // ---- loads of the tile after the next, then the epilogue of the previous tile while the MMAs run ----
             if (k == 1 && has_next) load_block(ni, nidx, ng);
             if (k + 2 < K) load_tile(i, k + 2, cidx[k + 2 < K ? k + 2 : 0]);
             else if (has_next) load_tile(ni, k + 2 - K, nidx[k + 2 >= K ? k + 2 - K : 0]);
-            mbar_wait(smem_u32(&S.bar), phase);
-            phase ^= 1u;
-            tc_fence_after();
-            if (FEAT) {  // D1 row: columns piece * 8 + c
-                uint32_t d0[16], d1[16];
-                tmem_ld16(tmem_row, d0);
-                tmem_ld16(tmem_row + 16, d1);
-                tmem_ld_wait(d0);
-                tmem_ld_wait(d1);
-                if (li >= 0) {
-                    float o[8];
-#pragma unroll
-                    for (int c = 0; c < 8; ++c)
-                        o[c] = ((__uint_as_float(d1[c]) + __uint_as_float(d0[8 + c])) + __uint_as_float(d0[c])) * a;
-                    float* gf = p.grad_features + (int64_t)li * F;
-                    red_add_v4(gf, o[0], o[1], o[2], o[3]);
-                    red_add_v4(gf + 4, o[4], o[5], o[6], o[7]);
-                }
-            }
-            if (DEC && k == K - 1 && warp < 2) {  // flush G^T of this block: row (lane) m = piece * 12 + input
-#pragma unroll
-                for (int c4 = 0; c4 < 4; ++c4) {
-                    uint32_t v[16];
-                    tmem_ld16(tmem_row + kD2 + 16 * c4, v);
-                    tmem_ld_wait(v);
-                    if (tid < kXCols) {
-#pragma unroll
-                        for (int u = 0; u < 16; ++u) S.gacc[16 * c4 + u][tid] += __uint_as_float(v[u]);
-                    }
-                }
-            }
-            tc_fence_before();
+            if (k > 0) epilogue(st ^ 1);
+            a_prev = a;
+            li_prev = li;
         }
+        pending = true;
 #pragma unroll
         for (int k = 0; k < K; ++k) cidx[k] = nidx[k];
         cg = ng;
+    }
+    if (pending) {
+        epilogue(1);
+        flush();
     }
 
     if (DEC) {
@@ -282,10 +310,10 @@ __global__ void __launch_bounds__(tcb::kRows) k_bwd_tc(const BwdParams p) {
     }
     __syncthreads();
     if (DEC) {  // G[j][i] = sum of the 3 pieces; then dW1 = W2 G, db1 = W2 G[:,11], dW2[j] = W1b[j] . G[j], db2
-        float* sG = reinterpret_cast<float*>(S.mask);  // [H][12], the tiles are idle now
+        float* sG = reinterpret_cast<float*>(S.mask[0]);  // [H][12], the tiles are idle now
         for (int e = tid; e < H * 12; e += kRows) {
             const int c = e / 12, i = e - 12 * c, j = hidden_of_maskcol(c);
-            sG[j * 12 + i] = (S.gacc[c][24 + i] + S.gacc[c][12 + i]) + S.gacc[c][i];
+            sG[j * 12 + i] = (S.gacc[24 + i][c] + S.gacc[12 + i][c]) + S.gacc[i][c];
         }
         __syncthreads();
         for (int e = tid; e < H * 12; e += kRows) {

@@ -273,7 +273,7 @@ extern "C" int pinq_query_fused_bwd(const pinq_bwd_args* a, void* stream) {
     ktime_mark(PINQ_KT_BWD, st);
     if (use_tc) {
         const unsigned nb128 = grid_for(a->n, tcb::kRows);
-        const unsigned cap128 = (unsigned)sms * 4u;  // 4 CTAs x 128 TMEM columns per SM
+        const unsigned cap128 = (unsigned)sms * 3u;  // 3 CTAs (72 KB of tiles, 128 TMEM columns each) per SM
         const unsigned g128 = nb128 < cap128 ? nb128 : cap128;
         if (dec && feat) k_bwd_tc<true, true><<<g128, tcb::kRows, tcb::kSmemRequest, st>>>(p);
         else if (dec) k_bwd_tc<true, false><<<g128, tcb::kRows, tcb::kSmemRequest, st>>>(p);
