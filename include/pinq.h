@@ -36,6 +36,7 @@ extern "C" {
 #define PINQ_F_ROTATE 4u       /* after_pgo=True: rotate x-p_k into the point frame (tools.py:316)     */
 #define PINQ_F_RECIP_DIV 8u    /* floor(x*(1/res)) instead of floor(x/res): CUDA-eager oracle (H1)     */
 #define PINQ_F_SKIP_EMPTY 16u  /* mesher: sdf = 0 where nn_count == 0 (utils/mesher.py:96-103)         */
+#define PINQ_F_MMA_SYNC 32u    /* decode / backward: the mma.sync kernels instead of the tcgen05 ones (A/B tests; also pinq_bwd_args.flags) */
 
 const char* pinq_last_error(void);
 int pinq_version(void);
@@ -45,12 +46,12 @@ int pinq_version(void);
  * kernels.  pinq_kernel_times() waits for them and returns, per phase i, the milliseconds between mark i and the
  * next recorded mark (-1 where a phase did not run).  Phases of one fused forward + backward: */
 #define PINQ_KT_BIN 0      /* spatial binning (memset + 5 kernels)          */
-#define PINQ_KT_SEARCH 1   /* stencil masks + K-nearest search              */
-#define PINQ_KT_RESOLVE 2  /* k_resolve                                     */
-#define PINQ_KT_DECODE 3   /* k_decode_mma                                  */
+#define PINQ_KT_SEARCH 1   /* stencil masks + K-nearest search (+ resolve)  */
+#define PINQ_KT_RESOLVE 2  /* k_resolve (slot-probing search only)          */
+#define PINQ_KT_DECODE 3   /* k_decode_tc / k_decode_mma                    */
 #define PINQ_KT_SCATTER 4  /* second-pass certainty scatter (training)      */
 #define PINQ_KT_FWD_END 5
-#define PINQ_KT_BWD 6      /* k_bwd_mma                                     */
+#define PINQ_KT_BWD 6      /* k_bwd_tc / k_bwd_mma                          */
 #define PINQ_KT_BWD_END 7
 #define PINQ_KT_MARKS 8
 void pinq_kernel_timing(int enable);

@@ -885,7 +885,7 @@ static int run_query(const pinq_query_args* a, int mode, float* feat_out, const 
             cudaFuncSetAttribute(k_decode_tc<false>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
             cudaFuncSetAttribute(k_decode_tc<true>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
         }
-        if (use_tc && !a->grad_x) {
+        if (use_tc && !a->grad_x && !(a->flags & PINQ_F_MMA_SYNC)) {
             const unsigned nb128 = grid_for(n, tc::kRows);
             const unsigned cap128 = (unsigned)sms * 4u;  // 4 CTAs x 128 TMEM columns per SM
             const unsigned g128 = nb128 < cap128 ? nb128 : cap128;

@@ -100,6 +100,7 @@ class NeuralPoints(nn.Module):
         self.bin_queries_min = 32768  # fused queries of at least this many points are binned by brick first
         # fused search through the brick index when it is provably equivalent (PINQ_BRICK=0: slot probing only)
         self.use_brick_index = os.environ.get("PINQ_BRICK", "1") != "0"
+        self.use_mma_sync = False  # A/B tests: the mma.sync decode / backward kernels instead of the tcgen05 ones
         self._brick_tab = self._brick_global = self._brick_local = self._brick_buf = self._brick_counters = None
         self._brick_host = self._brick_event = None
         self._brick_cap = 0
@@ -503,6 +504,8 @@ class NeuralPoints(nn.Module):
             flags |= P.F_TRAINING
         if self.after_pgo:
             flags |= P.F_ROTATE
+        if self.use_mma_sync:
+            flags |= P.F_MMA_SYNC
         feats = self.local_geo_features if query_locally else self.geo_features
         cert = self.local_point_certainties if query_locally else self.point_certainties
         quats = self.local_point_orientations if query_locally else self.point_orientations
@@ -651,7 +654,7 @@ class _FusedSDFFn(torch.autograd.Function):
         b = P.BwdArgs()
         b.dec = decoder.view()
         b.n = ctx.n
-        b.flags = 0
+        b.flags = P.F_MMA_SYNC if npts.use_mma_sync else 0
         b.k = int(npts.config.query_nn_k)
         b.feature_dim = int(npts.geo_feature_dim)
         b.features = P.ptr(feats.detach())

@@ -233,3 +233,63 @@ def test_brick_index_equals_slot_probing(maps):
     assert int(m._brick_counters[0].item()) == n_occ
     assert torch.equal(torch.sort(m._cand_global[:n_occ, 3].view(torch.int32)).values,
                        torch.sort(m._brick_global[:n_occ, 3].view(torch.int32)).values)
+
+
+@pytest.mark.parametrize("n", [1, 33, 127, 129, 6000])
+def test_tcgen05_kernels_match_mma_sync(maps, n):
+    """The tcgen05 / TMEM decode and backward (csrc/decode_tc.cuh, bwd_tc.cuh) against the mma.sync kernels on ragged
+    batch sizes (partial warps, partial 128-row tiles): same neighbours, sdf and every gradient to rounding."""
+    s, m, cfg, dec, d, _ = maps
+    q = make_queries(s.points, max(n, 8), seed=17)[:n].cuda()
+    ts = torch.full((n,), 1, dtype=torch.int64, device="cuda")
+    up = torch.linspace(-1.0, 1.0, n, device="cuda") if n > 1 else torch.ones(1, device="cuda")
+    cert0 = m.local_point_certainties.clone()
+    tsu0 = m.local_point_ts_update.clone()
+    res = {}
+    try:
+        for name, flag in (("tc", False), ("mma", True)):
+            m.use_mma_sync = flag
+            m.local_point_certainties = cert0.clone()
+            m.local_point_ts_update = tsu0.clone()
+            m.local_geo_features.grad = None
+            for p_ in dec.parameters():
+                p_.grad = None
+            out = m.query_sdf(q, dec, ts, True, True, want_std=True)
+            (out["sdf"] * up).sum().backward()
+            res[name] = dict(sdf=out["sdf"].detach().clone(), std=out["std"].clone(), nn=out["nn_count"].clone(),
+                             gf=m.local_geo_features.grad.clone(), gd=[p_.grad.clone() for p_ in dec.parameters()])
+    finally:
+        m.use_mma_sync = False
+        m.local_point_certainties, m.local_point_ts_update = cert0, tsu0
+    a, b = res["mma"], res["tc"]
+    assert torch.equal(a["nn"], b["nn"])
+    assert rel_err(b["sdf"], a["sdf"]) < 2e-6
+    assert rel_err(b["std"], a["std"]) < 1e-4
+    if float(a["gf"].abs().sum()) > 0:
+        assert rel_err(b["gf"], a["gf"]) < 1e-5
+    for x, y in zip(a["gd"], b["gd"]):
+        if float(x.abs().sum()) > 0:
+            assert rel_err(y, x) < 1e-5
+
+
+def test_kernel_timing_marks(maps):
+    """pinq_kernel_timing / pinq_kernel_times: CUDA-event time of each phase of the last fused forward + backward."""
+    import ctypes
+    from pin_slam_b200 import _pinq as P
+    s, m, cfg, dec, d, _ = maps
+    q = make_queries(s.points, 40000, seed=3).cuda()
+    lib = P.load()
+    cert0 = m.local_point_certainties.clone()
+    tsu0 = m.local_point_ts_update.clone()
+    lib.pinq_kernel_timing(1)
+    try:
+        out = m.query_sdf(q, dec, None, True, True)
+        out["sdf"].sum().backward()
+        torch.cuda.synchronize()
+        buf = (ctypes.c_float * 8)()
+        assert lib.pinq_kernel_times(buf, 8) == 7
+    finally:
+        lib.pinq_kernel_timing(0)
+        m.local_point_certainties, m.local_point_ts_update = cert0, tsu0
+    bin_, search, decode, bwd = buf[0], buf[1], buf[3], buf[6]
+    assert 0 < bin_ < 50 and 0 < search < 50 and 0 < decode < 50 and 0 < bwd < 50
