@@ -378,9 +378,12 @@ def main():
         out_h = torch.empty(n, dtype=torch.float32).pin_memory()
         # The batch crosses PCIe in chunks on a copy stream, double-buffered against the fused forward + backward of
         # the previous chunk (gradients accumulate over the chunks as over one batch); results go back per chunk.
-        nchunk = 4 if n % 4 == 0 and n >= 4 * 65536 else 1
+        nchunk = int(os.environ.get("PINQ_E2E_CHUNKS", "2"))  # per-chunk fixed costs (binning, launches) favour few chunks
+        if n % nchunk or n < nchunk * 65536:
+            nchunk = 1
         cn = n // nchunk
         copy_stream = torch.cuda.Stream()
+        back_stream = torch.cuda.Stream()  # results return on their own stream: D2H overlaps the next chunk's kernels
         xb = [torch.empty((cn, 3), dtype=torch.float32, device=dev) for _ in range(2)]
         tb = [torch.empty(cn, dtype=torch.int64, device=dev) for _ in range(2)]
         copied = [torch.cuda.Event() for _ in range(2)]
@@ -400,12 +403,17 @@ def main():
                 main.wait_event(copied[bi])
                 out = npts.query_sdf(xb[bi], dec, tb[bi], True, True)
                 out["sdf"].backward(ones_c)
-                out_h[c * cn:(c + 1) * cn].copy_(out["sdf"].detach(), non_blocking=True)
                 consumed[bi].record(main)
+                sdf_c = out["sdf"].detach()
+                back_stream.wait_event(consumed[bi])
+                with torch.cuda.stream(back_stream):
+                    out_h[c * cn:(c + 1) * cn].copy_(sdf_c, non_blocking=True)
+                sdf_c.record_stream(back_stream)
             if world > 1:
                 flat = torch.cat([p.grad.reshape(-1) for p in params[1:]])
                 dist.all_reduce(npts.local_geo_features.grad)
                 dist.all_reduce(flat)
+            main.wait_stream(back_stream)  # the step ends when its results are on the host
 
         for _ in range(3):
             e2e_step()
@@ -418,7 +426,7 @@ def main():
         te = torch.tensor([ev0.elapsed_time(ev1)], device=dev, dtype=torch.float64)
         if world > 1:
             dist.all_reduce(te, op=dist.ReduceOp.MAX)
-        e2e = {"value": world * n / (float(te.item()) / args.steps * 1e-3), "unit": UNIT,
+        e2e = {"value": world * n / (float(te.item()) / args.steps * 1e-3), "unit": UNIT, "chunks": nchunk,
                "h2d_bytes_per_step": n * 12 + n * 8, "d2h_bytes_per_step": n * 4}
 
     cpu_baseline = None
