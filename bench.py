@@ -415,7 +415,7 @@ def main():
                 dist.all_reduce(flat)
             main.wait_stream(back_stream)  # the step ends when its results are on the host
 
-        for _ in range(3):
+        for _ in range(max(5, args.warmup)):  # PCIe link and pinned pages warm
             e2e_step()
         barrier()
         ev0.record()

@@ -7,15 +7,17 @@
 // in the CUDA-core instruction stream (ncu on the mma.sync formulation: tensor pipe and issue both ~50 % busy, stalled on
 // each other's latencies at 16 warps/SM).
 //
-//   stage   thread = row: 32-byte feature row + (x - p_k) from the stage block -> 3xTF32 pieces -> six 16-byte chunks of
-//           the A tile in shared memory (UMMA canonical K-major layout without swizzle: chunk c of row r at c*2048 + r*16)
-//   mma     one thread: 5 x tcgen05.mma.kind::tf32 M=128 N=64 K=8 (small terms first), tcgen05.commit -> mbarrier
-//              [lo(f0..7)] x [hi W]   [hi(f0..7)] x [lo W]   [lo(v,1) | hi(v,1)] x [hi W ; lo W]
-//              [hi(f0..7)] x [hi W]   [hi(v,1) | 0] x [hi W ; -]
+//   stage   thread = row: 32-byte feature row + (x - p_k) from the stage block -> 3xTF32 pieces -> ONE tcgen05.st of the
+//           32 A columns of the thread's TMEM lane (the A operand never touches shared memory: ncu on the shared-memory
+//           version showed L1TEX 80 % busy with the tile writes, the tensor core's operand reads and the gathers)
+//   mma     one thread: 5 x tcgen05.mma.kind::tf32 M=128 N=64 K=8, A from TMEM, B from shared memory (small terms first)
+//              [lo(f0..7)] x [hi W]   [hi(f0..7)] x [lo W]   [lo(v,0) | hi(v,1)] x [hi W ; lo W]
+//              [hi(f0..7)] x [hi W]   [hi(v,1) | 0] x [hi W ; -]          then tcgen05.commit -> mbarrier
 //           `hi` is the raw fp32 word (the tensor core ignores the low 13 mantissa bits), lo = x - trunc(x) is exact
 //   epilog  tcgen05.ld 32x32b: 64 pre-activations of the thread's row; relu . W2 with W2 broadcast from shared memory;
 //           relu' bits collected from the SIGN of the pre-activation with one funnel shift per element
-// A tiles and accumulators are double-buffered: the MMAs of tile t run while the epilogue of tile t-1 executes.
+// 96 TMEM columns per CTA (64 accumulator + 32 A) -> 5 CTAs per SM; the other CTAs' work hides the MMA latency
+// (single-buffered tiles measured as fast as double-buffered ones at 4 CTAs).
 //
 // Deviation (documented in DESIGN.md): relu'(+0.0) is taken as 1 (torch: 0); reachable only when a hidden
 // pre-activation is exactly +0.0.
@@ -26,19 +28,18 @@
 namespace tc {
 
 constexpr int kRows = 128;                          // UMMA M = queries per CTA block = threads per CTA
-constexpr int kChunksA = 7;                         // [L0 L1 L2 H2 Z H0 H1], 16 bytes (4 tf32) per row each
-constexpr int kChunksB = 6;                         // [h0 h1 l0 l1 h2 l2] per hidden unit
-constexpr uint32_t kChunkABytes = kRows * 16;       // 2048: K-direction (leading) byte offset of A
+constexpr int kChunksB = 6;                         // [h0 h1 l0 l1 h2 l2] per hidden unit, 16 bytes (4 tf32) each
 constexpr uint32_t kChunkBBytes = H * 16;           // 1024: K-direction (leading) byte offset of B
-constexpr uint32_t kTmemCols = 2 * H;               // two accumulator buffers of 64 fp32 columns
-constexpr size_t kSmemRequest = 48 * 1024;          // > 227 KB / 5: at most 4 CTAs (4 x 128 = 512 TMEM columns) per SM
+constexpr uint32_t kTmemColsD = H;                  // accumulator: 64 fp32 columns
+constexpr uint32_t kTmemColsA = 32;                 // A operand: 4 k-steps of 8 tf32 columns
+constexpr unsigned kCtasPerSm = 5;                  // 5 x 96 TMEM columns <= 512
+constexpr size_t kSmemRequest = 40 * 1024;          // > 227 KB / 6: caps residency at 5 CTAs per SM
 
 struct Smem {
-    alignas(128) unsigned char a[2][kChunksA * kChunkABytes];
     alignas(128) unsigned char b[kChunksB * kChunkBBytes];
     alignas(16) float w2[H];  // W2 in accumulator-column order
-    alignas(8) unsigned long long bar[2];
-    uint32_t tmem_base;
+    alignas(8) unsigned long long bar;
+    uint32_t tmem_d, tmem_a;
 };
 static_assert(sizeof(Smem) <= kSmemRequest, "decode_tc shared memory");
 
@@ -60,6 +61,13 @@ __device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint6
         "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
         :: "r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(kIdesc), "r"(accumulate) : "memory");
 }
+__device__ __forceinline__ void umma_tf32_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t}"
+        :: "r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(kIdesc), "r"(accumulate) : "memory");
+}
+
 }  // namespace tc
 
 template <bool MESH>
@@ -69,7 +77,7 @@ __global__ void __launch_bounds__(tc::kRows) k_decode_tc(const DecodeParams p) {
     Smem& S = *reinterpret_cast<Smem*>(s_tc_raw);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
-    // ---- once per CTA: B operand and W2 in accumulator-column order, zero chunk, barriers, TMEM ----
+    // ---- once per CTA: B operand and W2 in accumulator-column order, barrier, TMEM (accumulator + A operand) ----
     for (int c = tid; c < H; c += kRows) {
         const int j = hidden_of_col(c);
         S.w2[c] = __ldg(&p.dec.W2[j]);
@@ -84,45 +92,43 @@ __global__ void __launch_bounds__(tc::kRows) k_decode_tc(const DecodeParams p) {
         brow[4 * (kChunkBBytes / 16)] = make_uint4(hi[8], hi[9], hi[10], hi[11]);
         brow[5 * (kChunkBBytes / 16)] = make_uint4(lo[8], lo[9], lo[10], lo[11]);
     }
-#pragma unroll
-    for (int b = 0; b < 2; ++b) *reinterpret_cast<uint4*>(S.a[b] + 4 * kChunkABytes + tid * 16) = make_uint4(0u, 0u, 0u, 0u);
     if (tid == 0) {
-        mbar_init(smem_u32(&S.bar[0]), 1);
-        mbar_init(smem_u32(&S.bar[1]), 1);
+        mbar_init(smem_u32(&S.bar), 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 0) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
-                     :: "r"(smem_u32(&S.tmem_base)), "r"(kTmemCols) : "memory");
+                     :: "r"(smem_u32(&S.tmem_d)), "r"(kTmemColsD) : "memory");
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
+                     :: "r"(smem_u32(&S.tmem_a)), "r"(kTmemColsA) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
     fence_async_smem();
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
-    const uint32_t tmem = S.tmem_base;
-    const uint32_t tmem_row = tmem + ((uint32_t)(32 * warp) << 16);  // this warp's 32 TMEM lanes
+    const uint32_t tmem_d = S.tmem_d, tmem_a = S.tmem_a;
+    const uint32_t lanes = (uint32_t)(32 * warp) << 16;  // this warp's 32 TMEM lanes
     const uint64_t bdesc = umma_desc(smem_u32(S.b), kChunkBBytes, 128);
     const float b2 = __ldg(p.dec.b2), scale = p.dec.sdf_scale;
     const int64_t nblocks = (p.n + kRows - 1) / kRows;
     uint2* mask2 = reinterpret_cast<uint2*>(p.relu_mask);
 
-    uint32_t phase[2] = {0u, 0u};
+    uint32_t phase = 0u;
     float sdf = 0.f, sk[K], wk[K];
 #pragma unroll
     for (int k = 0; k < K; ++k) sk[k] = wk[k] = 0.f;
 
-    // epilogue of tile k of the block whose row of this thread is processing position ei
+    // epilogue of tile k: the accumulator row of this thread (processing position ei)
     auto epilogue = [&](int k, int64_t ei, bool ewarp) {
-        const int buf = k & 1;
         const StageBlock& sb = p.stage[ewarp ? (ei >> 5) : 0];
         const float w = ewarp ? __ldg(&sb.w[k][lane]) : 0.f;
-        mbar_wait(smem_u32(&S.bar[buf]), phase[buf]);
-        phase[buf] ^= 1u;
+        mbar_wait(smem_u32(&S.bar), phase);
+        phase ^= 1u;
         tc_fence_after();
         // 16 columns at a time, the next chunk in flight while this one is reduced (32 live registers instead of 64)
         uint32_t va[16], vb[16];
-        const uint32_t t0 = tmem_row + (uint32_t)(buf * H);
+        const uint32_t t0 = tmem_d + lanes;
         float s0 = 0.f, s1 = 0.f;
         uint32_t neg0 = 0u, neg1 = 0u;
         auto reduce16 = [&](const uint32_t (&v)[16], int c0, float& s, uint32_t& neg) {
@@ -148,7 +154,7 @@ __global__ void __launch_bounds__(tc::kRows) k_decode_tc(const DecodeParams p) {
         tmem_ld16(t0 + 48, vb);
         reduce16(va, 32, s0, neg1);
         tmem_ld_wait(vb);
-        tc_fence_before();  // the accumulator buffer may be overwritten after the next block-wide barrier
+        tc_fence_before();  // the accumulator may be overwritten after the next block-wide barrier
         reduce16(vb, 48, s1, neg1);
         if (mask2 && ewarp) mask2[((ei >> 5) * K + k) * 32 + lane] = make_uint2(~neg0, ~neg1);
         const float s = ((s0 + s1) + b2) * scale;  // decoder.py:80-81
@@ -204,8 +210,6 @@ __global__ void __launch_bounds__(tc::kRows) k_decode_tc(const DecodeParams p) {
             phv.z = __ldg(&sb.v[k][2][lane]);
         }
     };
-    int64_t pend_i = -1;  // processing position (of this thread) of the block whose last tile is still in flight
-    bool pend_warp = false;
     if ((int64_t)blockIdx.x < nblocks) {
         load_idx((int64_t)blockIdx.x * kRows + tid, cidx);
         load_tile((int64_t)blockIdx.x * kRows + tid, 0, cidx[0]);
@@ -219,57 +223,53 @@ __global__ void __launch_bounds__(tc::kRows) k_decode_tc(const DecodeParams p) {
         for (int k = 0; k < K; ++k) nidx[k] = -1;
 #pragma unroll
         for (int k = 0; k < K; ++k) {
-            const int buf = k & 1;  // K is even: the tile parity is the same in every block
-            // ---- stage tile (blk, k): thread = row ----
-            const float4 fa = pfa, fb = pfb, hv = phv;
-            auto lo_of = [](float x) { return x - __uint_as_float(__float_as_uint(x) & 0xffffe000u); };
-            unsigned char* arow = S.a[buf] + tid * 16;
-            *reinterpret_cast<float4*>(arow + 0 * kChunkABytes) = make_float4(lo_of(fa.x), lo_of(fa.y), lo_of(fa.z), lo_of(fa.w));
-            *reinterpret_cast<float4*>(arow + 1 * kChunkABytes) = make_float4(lo_of(fb.x), lo_of(fb.y), lo_of(fb.z), lo_of(fb.w));
-            *reinterpret_cast<float4*>(arow + 2 * kChunkABytes) = make_float4(lo_of(hv.x), lo_of(hv.y), lo_of(hv.z), 0.f);
-            *reinterpret_cast<float4*>(arow + 3 * kChunkABytes) = hv;
-            *reinterpret_cast<float4*>(arow + 5 * kChunkABytes) = fa;
-            *reinterpret_cast<float4*>(arow + 6 * kChunkABytes) = fb;
-            fence_async_smem();  // generic-proxy writes -> visible to the tensor core's async proxy
+            // ---- stage tile (blk, k): thread = row = TMEM lane; one tcgen05.st of the 32 A columns
+            //      [lo f0..3 | lo f4..7 | lo v,0 | hi v,1 | hi v,1 | 0 | hi f0..3 | hi f4..7]
+            {
+                const float4 fa = pfa, fb = pfb, hv = phv;
+                auto lo_of = [](float x) { return __float_as_uint(x - __uint_as_float(__float_as_uint(x) & 0xffffe000u)); };
+                uint32_t r[32];
+                r[0] = lo_of(fa.x); r[1] = lo_of(fa.y); r[2] = lo_of(fa.z); r[3] = lo_of(fa.w);
+                r[4] = lo_of(fb.x); r[5] = lo_of(fb.y); r[6] = lo_of(fb.z); r[7] = lo_of(fb.w);
+                r[8] = lo_of(hv.x); r[9] = lo_of(hv.y); r[10] = lo_of(hv.z); r[11] = 0u;
+                r[12] = __float_as_uint(hv.x); r[13] = __float_as_uint(hv.y); r[14] = __float_as_uint(hv.z);
+                r[15] = __float_as_uint(hv.w);
+                r[16] = r[12]; r[17] = r[13]; r[18] = r[14]; r[19] = r[15];
+                r[20] = r[21] = r[22] = r[23] = 0u;
+                r[24] = __float_as_uint(fa.x); r[25] = __float_as_uint(fa.y); r[26] = __float_as_uint(fa.z);
+                r[27] = __float_as_uint(fa.w);
+                r[28] = __float_as_uint(fb.x); r[29] = __float_as_uint(fb.y); r[30] = __float_as_uint(fb.z);
+                r[31] = __float_as_uint(fb.w);
+                tmem_st32(tmem_a + lanes, r);
+                asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+            }
             tc_fence_before();
             __syncthreads();
             if (tid == 0) {
                 tc_fence_after();
-                const uint64_t adesc = umma_desc(smem_u32(S.a[buf]), kChunkABytes, 128);
-                const uint32_t d = tmem + (uint32_t)(buf * H);
-                constexpr uint64_t ca = kChunkABytes >> 4, cb = kChunkBBytes >> 4;  // descriptor units per chunk
-                umma_tf32(d, adesc + 0 * ca, bdesc + 0 * cb, 0u);  // lo(f) x hi W
-                umma_tf32(d, adesc + 5 * ca, bdesc + 2 * cb, 1u);  // hi(f) x lo W
-                umma_tf32(d, adesc + 2 * ca, bdesc + 4 * cb, 1u);  // lo(v,1) | hi(v,1)  x  hi W ; lo W
-                umma_tf32(d, adesc + 5 * ca, bdesc + 0 * cb, 1u);  // hi(f) x hi W
-                umma_tf32(d, adesc + 3 * ca, bdesc + 4 * cb, 1u);  // hi(v,1) | 0  x  hi W ; -
-                umma_commit(smem_u32(&S.bar[buf]));
+                constexpr uint64_t cb = kChunkBBytes >> 4;  // descriptor units per B chunk
+                umma_tf32_ts(tmem_d, tmem_a + 0, bdesc + 0 * cb, 0u);   // lo(f) x hi W
+                umma_tf32_ts(tmem_d, tmem_a + 24, bdesc + 2 * cb, 1u);  // hi(f) x lo W
+                umma_tf32_ts(tmem_d, tmem_a + 8, bdesc + 4 * cb, 1u);   // lo(v,0) | hi(v,1)  x  hi W ; lo W
+                umma_tf32_ts(tmem_d, tmem_a + 24, bdesc + 0 * cb, 1u);  // hi(f) x hi W
+                umma_tf32_ts(tmem_d, tmem_a + 16, bdesc + 4 * cb, 1u);  // hi(v,1) | 0  x  hi W ; -
+                umma_commit(smem_u32(&S.bar));
             }
-            // ---- loads of the next tile, then the epilogue of the previous one while the MMAs run ----
+            // ---- loads of the next tile while the MMAs run, then the epilogue of this one ----
             if (k == 1 && has_next) load_idx(ni, nidx);
             if (k + 1 < K) load_tile(i, k + 1, cidx[k + 1 < K ? k + 1 : 0]);
             else if (has_next) load_tile(ni, 0, nidx[0]);
-            if (k > 0) {
-                epilogue(k - 1, i, wlive);
-            } else if (pend_i >= 0) {
-                epilogue(K - 1, pend_i, pend_warp);
-                finalize(pend_i);
-            }
+            epilogue(k, i, wlive);
         }
-        pend_i = i;
-        pend_warp = wlive;
+        finalize(i);
 #pragma unroll
         for (int k = 0; k < K; ++k) cidx[k] = nidx[k];
-    }
-    if (pend_i >= 0) {
-        epilogue(K - 1, pend_i, pend_warp);
-        finalize(pend_i);
     }
     tc_fence_before();
     __syncthreads();
     if (warp == 0) {
         tc_fence_after();
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem), "r"(kTmemCols) : "memory");
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem_d), "r"(kTmemColsD) : "memory");
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem_a), "r"(kTmemColsA) : "memory");
     }
 }
-

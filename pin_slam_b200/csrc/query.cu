@@ -887,7 +887,7 @@ static int run_query(const pinq_query_args* a, int mode, float* feat_out, const 
         }
         if (use_tc && !a->grad_x && !(a->flags & PINQ_F_MMA_SYNC)) {
             const unsigned nb128 = grid_for(n, tc::kRows);
-            const unsigned cap128 = (unsigned)sms * 4u;  // 4 CTAs x 128 TMEM columns per SM
+            const unsigned cap128 = (unsigned)sms * tc::kCtasPerSm;  // TMEM columns per CTA bound the residency
             const unsigned g128 = nb128 < cap128 ? nb128 : cap128;
             if (mode == 2) k_decode_tc<true><<<g128, tc::kRows, tc::kSmemRequest, st>>>(p);
             else k_decode_tc<false><<<g128, tc::kRows, tc::kSmemRequest, st>>>(p);
