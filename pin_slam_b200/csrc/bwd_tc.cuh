@@ -153,9 +153,7 @@ __global__ void __launch_bounds__(tcb::kRows) k_bwd_tc(const BwdParams p) {
             pm[st] = __ldg(&mask2[((bi >> 5) * K + k) * 32 + lane]);
             pw[st] = __ldg(&sb.w[k][lane]);
             if (DEC) {
-                const float4* fr = reinterpret_cast<const float4*>(p.features + (int64_t)li * F);
-                pfa[st] = __ldg(fr);
-                pfb[st] = __ldg(fr + 1);
+                ldg_row8(p.features + (int64_t)li * F, pfa[st], pfb[st]);
                 phv[st].x = __ldg(&sb.v[k][0][lane]);
                 phv[st].y = __ldg(&sb.v[k][1][lane]);
                 phv[st].z = __ldg(&sb.v[k][2][lane]);

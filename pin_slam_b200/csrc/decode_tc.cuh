@@ -202,9 +202,7 @@ __global__ void __launch_bounds__(tc::kRows) k_decode_tc(const DecodeParams p) {
         phv = make_float4(0.f, 0.f, 0.f, 1.f);  // inputs 8..10 = x - p_k, input 11 = 1 (bias column)
         if (li >= 0) {
             const StageBlock& sb = p.stage[bi >> 5];
-            const float4* fr = reinterpret_cast<const float4*>(p.features + (int64_t)li * F);
-            pfa = __ldg(fr);
-            pfb = __ldg(fr + 1);
+            ldg_row8(p.features + (int64_t)li * F, pfa, pfb);
             phv.x = __ldg(&sb.v[k][0][lane]);
             phv.y = __ldg(&sb.v[k][1][lane]);
             phv.z = __ldg(&sb.v[k][2][lane]);
