@@ -6,9 +6,9 @@
 // 4 x 4 x 4 voxels) turns those gathers into L1 hits.  Only the PROCESSING ORDER changes: every kernel
 // reads its inputs and writes its per-query outputs through perm[], so results are those of the unsorted
 // batch.  The order inside a bin is whatever the atomics produce -- no output depends on it.
-//   k_bin_count   key[i] = brick key of query i, hist[key]++
+//   k_bin_count   key[i] = brick key of query i, arrival[i] = hist[key]++  (the atomic's return value)
 //   k_bin_tile_*  exclusive scan of the 2^21 counters (tile sums, scan of the sums, per-tile prefix)
-//   k_bin_scatter perm[cursor[key[i]]++] = i
+//   k_bin_scatter perm[base[key[i]] + arrival[i]] = i   (no second round of atomics)
 #include "query_common.cuh"
 
 namespace pinq {
@@ -25,13 +25,13 @@ __device__ __forceinline__ uint32_t brick_key21(int gx, int gy, int gz) {
 }
 
 __global__ void k_bin_count(const float* __restrict__ xyz, int64_t n, float res, float inv_res, bool recip,
-                            uint32_t* __restrict__ keys, uint32_t* __restrict__ hist) {
+                            uint32_t* __restrict__ keys, uint32_t* __restrict__ arrival, uint32_t* __restrict__ hist) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const uint32_t key = brick_key21(cell_of(xyz[3 * i], res, inv_res, recip), cell_of(xyz[3 * i + 1], res, inv_res, recip),
                                      cell_of(xyz[3 * i + 2], res, inv_res, recip));
     keys[i] = key;
-    atomicAdd(&hist[key], 1u);
+    arrival[i] = atomicAdd(&hist[key], 1u);
 }
 
 // block-wide exclusive scan of one value per thread (1024 threads); returns the exclusive prefix, total in *tot
@@ -84,25 +84,26 @@ __global__ void __launch_bounds__(kScanTile) k_bin_tile_apply(uint32_t* __restri
     hist[idx] = tiles[blockIdx.x] + ex;
 }
 
-__global__ void k_bin_scatter(const uint32_t* __restrict__ keys, int64_t n, uint32_t* __restrict__ cursor,
-                              int32_t* __restrict__ perm) {
+__global__ void k_bin_scatter(const uint32_t* __restrict__ keys, const uint32_t* __restrict__ arrival, int64_t n,
+                              const uint32_t* __restrict__ base, int32_t* __restrict__ perm) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    perm[atomicAdd(&cursor[keys[i]], 1u)] = (int32_t)i;
+    perm[__ldg(&base[keys[i]]) + arrival[i]] = (int32_t)i;
 }
 
-int64_t bin_scratch_bytes(int64_t n) { return (int64_t)(kBins + kScanTiles) * 4 + ((n * 4 + 15) / 16) * 16; }
+int64_t bin_scratch_bytes(int64_t n) { return (int64_t)(kBins + kScanTiles) * 4 + 2 * (((n * 4 + 15) / 16) * 16); }
 
 int launch_spatial_bin(const float* xyz, int64_t n, float res, bool recip, void* scratch, int32_t* perm, cudaStream_t st) {
     uint32_t* hist = reinterpret_cast<uint32_t*>(scratch);
     uint32_t* tiles = hist + kBins;
     uint32_t* keys = tiles + kScanTiles;
+    uint32_t* arrival = keys + ((n + 3) / 4) * 4;
     cudaMemsetAsync(hist, 0, (size_t)kBins * 4, st);
-    k_bin_count<<<grid_for(n, 256), 256, 0, st>>>(xyz, n, res, 1.0f / res, recip, keys, hist);
+    k_bin_count<<<grid_for(n, 256), 256, 0, st>>>(xyz, n, res, 1.0f / res, recip, keys, arrival, hist);
     k_bin_tile_sums<<<kScanTiles, kScanTile, 0, st>>>(hist, tiles);
     k_bin_tile_scan<<<1, kScanTile, 0, st>>>(tiles);
     k_bin_tile_apply<<<kScanTiles, kScanTile, 0, st>>>(hist, tiles);
-    k_bin_scatter<<<grid_for(n, 256), 256, 0, st>>>(keys, n, hist, perm);
+    k_bin_scatter<<<grid_for(n, 256), 256, 0, st>>>(keys, arrival, n, hist, perm);
     return check_launch("spatial binning");
 }
 
