@@ -162,7 +162,14 @@ typedef struct pinq_map_view {
     const float* brick_rec4;    /* [n_occupied][4] records in brick order (same flavour as rec4) */
     uint32_t brick_cap;         /* power of two                                               */
     int32_t stencil_radius;     /* max |dx| over the stencil (<= 2 for the brick path)        */
+    const uint64_t* stencil_masks; /* [512] from pinq_stencil_masks_build for this stencil, or NULL =
+                                   rebuilt inside every query launch (costs one small kernel)    */
 } pinq_map_view;
+
+/* Brick-voxel membership masks of a stencil (64 box phases x 8 bricks, one 64-bit word each): depends on
+ * stencil_dx only, so set_search_neighborhood() (neural_points.py:430-457) can build it once. */
+int pinq_stencil_masks_build(const int32_t* stencil_dx, int32_t kn, int32_t stencil_radius, uint64_t* out512,
+                             void* stream);
 
 /* model/neural_points.py:459-509 -- standalone API form: writes dist2[n,kn] f32 and idx[n,kn] i64
  * (global indices).  time_filtering reads ts_create / travel_dist exactly as the reference does. */
@@ -282,6 +289,66 @@ int pinq_mesher_grid_query(const pinq_query_args* args, const float* origin3_hos
 /* ---- fused Adam (utils/tools.py:89-116; torch.optim.Adam single-tensor semantics) -------- */
 int pinq_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, float lr,
                    float beta1, float beta2, float eps, int32_t step, void* stream);
+
+/* ---- fused mapping iterations (utils/mapper.py:425-593) -----------------------------------
+ * One call runs `iters` iterations of Mapper.mapping() on the device without returning to the host:
+ *   get_batch (mapper.py:323-361)  -> k_map_gather: pool rows of the pre-drawn indices, plus the
+ *                                     6 x ceil(bs/decimation) numerical-gradient points (mapper.py:683-733)
+ *                                     appended to the same query batch (query_ts = -1: no ts amax, H9)
+ *   sdf prediction (mapper.py:461-468)  -> pinq_query_fused_fwd over the bs + 6*ng points
+ *   bce + eikonal loss (mapper.py:515-547, loss.py:40-47) -> k_map_loss_grad: dL/dsdf in closed form
+ *   cur_loss.backward() (mapper.py:572) -> pinq_query_fused_bwd
+ *   opt.step() (mapper.py:573, tools.py:89-116) -> one multi-tensor Adam launch (also zeroes the grads)
+ * The optimizer is fresh per call (mapper.py:441): iteration `it` is Adam step it+1 and step 1 ignores
+ * what exp_avg / exp_avg_sq held before. */
+typedef struct pinq_adam_tensor {
+    float* param;
+    float* grad;               /* zero on entry; left zero on return                        */
+    float* exp_avg;            /* scratch, same size (contents ignored at step 1)           */
+    float* exp_avg_sq;
+    int64_t n;
+} pinq_adam_tensor;
+
+#define PINQ_EIK_ALL 0
+#define PINQ_EIK_SURFACE 1
+#define PINQ_EIK_FREESPACE 2
+
+typedef struct pinq_mapping_args {
+    pinq_query_args query;     /* xyz = batch_xyz, n = bs + 6*ng, query_ts = batch_ts, sdf, nn_count,
+                                  stage, relu_mask, workspace set; TRAINING | LOCAL flags          */
+    pinq_bwd_args bwd;         /* n as above, grad_sdf = grad_sdf below, grad_* = the adam grads   */
+    /* replay pool (mapper.py:59-66) */
+    const float* pool_xyz;     /* [P,3] global_coord_pool (or coord_pool after BA)                 */
+    const float* pool_label;   /* [P]                                                              */
+    const float* pool_weight;  /* [P]                                                              */
+    const int64_t* pool_ts;    /* [P]                                                              */
+    /* pre-drawn uniform indices, one row per iteration, in the order get_batch draws them */
+    const int64_t* draws_hist; /* [iters][bs - bs_new] in [0, P)                                   */
+    const int64_t* draws_new;  /* [iters][bs_new] in [0, new_count) or NULL when bs_new == 0       */
+    const int64_t* new_idx;    /* [new_count] pool rows of the newly observed samples              */
+    int32_t bs, bs_new;
+    int32_t decimation;        /* gradient_decimation; ng = ceil(bs / decimation); 0 = no eikonal  */
+    int32_t eik_mode;          /* PINQ_EIK_*  (ekional_add_to)                                     */
+    int32_t weighted;          /* loss_weight_on                                                   */
+    float eps_step;            /* voxel_size_m * num_grad_step_ratio                               */
+    float sigma;               /* logistic_gaussian_ratio * sigma_sigmoid_m                        */
+    float weight_e;
+    float surface_range;       /* surface_sample_range_m (eik_mode != ALL)                         */
+    /* per-iteration batch buffers */
+    float* batch_xyz;          /* [n,3]                                                            */
+    int64_t* batch_ts;         /* [n]                                                              */
+    float* batch_label;        /* [bs]                                                             */
+    float* batch_weight;       /* [bs]  |weight|                                                   */
+    float* grad_sdf;           /* [n]                                                              */
+    float* loss;               /* [iters][2] (bce, eikonal) or NULL; zero on entry                 */
+    int32_t* eik_count;        /* [iters] selected eikonal samples; zero on entry                  */
+    /* optimizer */
+    pinq_adam_tensor tensors[8];
+    int32_t tensor_count;
+    float lr, beta1, beta2, adam_eps, weight_decay;
+} pinq_mapping_args;
+
+int pinq_mapping_run(const pinq_mapping_args* args, int32_t iters, void* stream);
 
 #ifdef __cplusplus
 }

@@ -18,7 +18,7 @@ _vp, _i64, _i32, _u32, _u64, _f32 = C.c_void_p, C.c_int64, C.c_int32, C.c_uint32
 class MapView(C.Structure):
     _fields_ = [("occ", _vp), ("rec4", _vp), ("buffer_size", _u32), ("resolution", _f32), ("max_valid_dist2", _f32),
                 ("kn", _i32), ("stencil_dx", _vp), ("m", _i64), ("brick_tab", _vp), ("brick_rec4", _vp), ("brick_cap", _u32),
-                ("stencil_radius", _i32)]
+                ("stencil_radius", _i32), ("stencil_masks", _vp)]
 
 
 class DecoderView(C.Structure):
@@ -37,6 +37,23 @@ class BwdArgs(C.Structure):
     _fields_ = [("dec", DecoderView), ("n", _i64), ("flags", _u32), ("k", _i32), ("feature_dim", _i32),
                 ("features", _vp), ("stage", _vp), ("relu_mask", _vp), ("perm", _vp), ("grad_sdf", _vp), ("grad_features", _vp), ("grad_W1", _vp), ("grad_b1", _vp), ("grad_W2", _vp),
                 ("grad_b2", _vp)]
+
+
+class AdamTensor(C.Structure):
+    _fields_ = [("param", _vp), ("grad", _vp), ("exp_avg", _vp), ("exp_avg_sq", _vp), ("n", _i64)]
+
+
+EIK_ALL, EIK_SURFACE, EIK_FREESPACE = 0, 1, 2
+
+
+class MappingArgs(C.Structure):
+    _fields_ = [("query", QueryArgs), ("bwd", BwdArgs), ("pool_xyz", _vp), ("pool_label", _vp), ("pool_weight", _vp),
+                ("pool_ts", _vp), ("draws_hist", _vp), ("draws_new", _vp), ("new_idx", _vp), ("bs", _i32), ("bs_new", _i32),
+                ("decimation", _i32), ("eik_mode", _i32), ("weighted", _i32), ("eps_step", _f32), ("sigma", _f32),
+                ("weight_e", _f32), ("surface_range", _f32), ("batch_xyz", _vp), ("batch_ts", _vp), ("batch_label", _vp),
+                ("batch_weight", _vp), ("grad_sdf", _vp), ("loss", _vp), ("eik_count", _vp), ("tensors", AdamTensor * 8),
+                ("tensor_count", _i32), ("lr", _f32), ("beta1", _f32), ("beta2", _f32), ("adam_eps", _f32),
+                ("weight_decay", _f32)]
 
 
 # name -> (restype, argtypes); mirrors include/pinq.h one to one
@@ -77,6 +94,8 @@ SIGNATURES = {
     "pinq_mesher_grid_query": (C.c_int, [C.POINTER(QueryArgs), C.POINTER(_f32), C.POINTER(_i32), _f32, _i64, _i64,
                                          _i32, _vp, _vp, _vp]),
     "pinq_adam_step": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _f32, _f32, _f32, _f32, _i32, _vp]),
+    "pinq_stencil_masks_build": (C.c_int, [_vp, _i32, _i32, _vp, _vp]),
+    "pinq_mapping_run": (C.c_int, [C.POINTER(MappingArgs), _i32, _vp]),
 }
 
 _lib = None

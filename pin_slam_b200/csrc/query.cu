@@ -831,9 +831,13 @@ static int run_query(const pinq_query_args* a, int mode, float* feat_out, const 
     ktime_mark(PINQ_KT_SEARCH, st);
     const bool resolve_in_search = brick && mode != 1;
     if (brick) {
-        unsigned long long* smasks = reinterpret_cast<unsigned long long*>(
-            reinterpret_cast<unsigned char*>(a->workspace) + ws_off_masks(n));
-        k_stencil_masks<<<1, 256, 0, st>>>(map.stencil_dx, map.kn, bd.radius, smasks);
+        const unsigned long long* smasks = reinterpret_cast<const unsigned long long*>(a->map.stencil_masks);
+        if (!smasks) {
+            unsigned long long* built = reinterpret_cast<unsigned long long*>(
+                reinterpret_cast<unsigned char*>(a->workspace) + ws_off_masks(n));
+            k_stencil_masks<<<1, 256, 0, st>>>(map.stencil_dx, map.kn, bd.radius, built);
+            smasks = built;
+        }
         const size_t smem = kBrickSmem;
         if (resolve_in_search)
             k_search_brick<true><<<grid_for(n, kBlock), kBlock, smem, st>>>(map, bd, src, n, recip, perm, smasks, ws, p);
@@ -928,6 +932,14 @@ int64_t pinq_query_workspace_bytes(int64_t n) { return ws_off_stage(n > 0 ? n : 
 int64_t pinq_stage_bytes(int64_t n) { return stage_bytes(n); }
 
 int64_t pinq_relu_mask_words(int64_t n) { return ((n > 0 ? n : 1) + 31) / 32 * (int64_t)kMTiles * 32; }
+
+int pinq_stencil_masks_build(const int32_t* stencil_dx, int32_t kn, int32_t stencil_radius, uint64_t* out512, void* stream) {
+    PINQ_REQUIRE(stencil_dx && out512, "null pointer");
+    PINQ_REQUIRE(kn > 0 && kn <= PINQ_MAX_STENCIL && stencil_radius >= 0 && stencil_radius <= 2, "stencil radius 0..2 only");
+    k_stencil_masks<<<1, 256, 0, as_stream(stream)>>>(stencil_dx, kn, stencil_radius,
+                                                      reinterpret_cast<unsigned long long*>(out512));
+    return check_launch("pinq_stencil_masks_build");
+}
 
 int pinq_neighbor_search(const pinq_map_view* map, const float* xyz, int64_t n, uint32_t flags, const float* map_xyz,
                          const int64_t* ts_create, const float* travel_dist, int64_t cur_ts,

@@ -349,6 +349,7 @@ class NeuralPoints(nn.Module):
         self._stencil_radius = int(num_nei_cells)
         self.max_valid_dist2 = 3 * ((num_nei_cells + 1) * self.resolution) ** 2
         self._stencil_i32 = self.neighbor_dx.to(torch.int32).contiguous()
+        self._stencil_key = (int(num_nei_cells), float(search_alpha))
 
     # ---- packed views for the kernels ---------------------------------------------------------
     def _refresh_candidates(self):
@@ -457,7 +458,20 @@ class NeuralPoints(nn.Module):
                          float(self.max_valid_dist2), int(self.neighbor_K), P.ptr(self._stencil_i32),
                          int(self.neural_points.shape[0]), P.ptr(self._brick_tab) if use_brick else None,
                          P.ptr(brec) if use_brick else None, int(self._brick_cap) if use_brick else 0,
-                         int(self._stencil_radius) if use_brick else 0)
+                         int(self._stencil_radius) if use_brick else 0,
+                         P.ptr(self._stencil_masks()) if use_brick else None)
+
+    def _stencil_masks(self):
+        """Brick-voxel membership masks of the current stencil (pinq_stencil_masks_build), built once per
+        (num_nei_cells, search_alpha) -- process_frame switches between two stencils every frame."""
+        cache = self.__dict__.setdefault("_stencil_mask_cache", {})
+        key = self._stencil_key
+        if key not in cache:
+            out = torch.empty(512, dtype=torch.int64, device=self.device)
+            P.check(P.load().pinq_stencil_masks_build(P.ptr(self._stencil_i32), int(self.neighbor_K),
+                                                      int(self._stencil_radius), P.ptr(out), P.stream()))
+            cache[key] = (out, self._stencil_i32)
+        return cache[key][0]
 
     def _workspace(self, n: int):
         nbytes = int(P.load().pinq_query_workspace_bytes(n))
@@ -579,6 +593,7 @@ class NeuralPoints(nn.Module):
         self._brick_host = self._brick_event = None
         self._brick_pending = False
         self._ws = None
+        self._stencil_mask_cache = {}
         self._ts_keepalive = None
         self._local_idx = None
         self.local_neural_points = None

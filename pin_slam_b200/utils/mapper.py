@@ -63,6 +63,10 @@ class Mapper:
         self.cur_sample_count = 0
         self.pool_sample_count = 0
         self.timing = {}
+        self.fused_mapping = True   # False: run the iterations as separate autograd steps (A/B tests)
+        self.last_loss = None
+        self._fused_buf, self._fused_last = {}, None
+        self._draw_host, self._draw_event = {}, None
 
     # ------------------------------------------------------------------------------------------
     def dynamic_filter(self, points_torch, type_2_on: bool = False):
@@ -195,10 +199,21 @@ class Mapper:
 
     # ------------------------------------------------------------------------------------------
     def mapping(self, iter_count):
-        """reference: utils/mapper.py:425-593."""
-        cfg = self.config
+        """reference: utils/mapper.py:425-593.  The iterations run inside libpinq (`pinq_mapping_run`: batch gather,
+        fused query, closed-form loss gradient, backward kernel, multi-tensor Adam -- 8 launches per iteration and no
+        host work between them); configurations the fused loop does not cover take the autograd form of the same
+        kernels (`_mapping_autograd`)."""
         if self.train_less:
             iter_count = max(1, iter_count - 5)
+        if self.fused_mapping and self._fused_mapping_supported():
+            self._mapping_fused(iter_count)
+        else:
+            self._mapping_autograd(iter_count)
+        self.neural_points.assign_local_to_global()
+
+    def _mapping_autograd(self, iter_count):
+        """The reference's loop verbatim (get_batch -> loss -> backward -> Adam) over the fused autograd node."""
+        cfg = self.config
         neural_point_feat = list(self.neural_points.parameters())
         geo_mlp_param = list(self.geo_mlp.parameters())
         opt = setup_optimizer(cfg, neural_point_feat, geo_mlp_param, None, None)
@@ -209,7 +224,139 @@ class Mapper:
             cur_loss.backward(retain_graph=False)
             opt.step()
             self.total_iter += 1
-        self.neural_points.assign_local_to_global()
+
+    def _trainable_decoder(self):
+        """None if the decoder is frozen (H11), the four fused tensors if all train, False for a partial freeze."""
+        params = list(self.geo_mlp.parameters())
+        trainable = [p for p in params if p.requires_grad]
+        if not trainable:
+            return None
+        fused = self.geo_mlp.fused_params() if self.geo_mlp.fused_supported() else ()
+        if len(trainable) == len(params) == 4 and all(a is b for a, b in zip(params, fused)):
+            return fused
+        return False
+
+    def _fused_mapping_supported(self) -> bool:
+        cfg = self.config
+        return bool(cfg.opt_adam and cfg.main_loss_type == "bce" and not cfg.weighted_first and self.geo_mlp.fused_supported()
+                    and (not cfg.ekional_loss_on or cfg.weight_e <= 0 or cfg.numerical_grad)
+                    and cfg.ekional_add_to in ("all", "surface", "freespace") and self._trainable_decoder() is not False
+                    and self.neural_points.local_geo_features.requires_grad and self.pool_sample_count > 0
+                    and self.sdf_label_pool.shape[0] == self.pool_sample_count)
+
+    def _draw_batches(self, iters, bs_hist, bs_new, new_count):
+        """The uniform indices of all iterations, drawn in get_batch's order (history, then new samples, per
+        iteration) so a seeded generator yields the sequence the per-iteration form would."""
+        gen, dev = self.generator, self.device
+        if gen is None:
+            hist = torch.randint(0, self.pool_sample_count, (iters, bs_hist), device=dev)
+            new = torch.randint(0, new_count, (iters, bs_new), device=dev) if bs_new > 0 else None
+            return hist, new
+        on_cpu = gen.device.type == "cpu"
+        if on_cpu and self._draw_event is not None:
+            self._draw_event.synchronize()  # the previous frame's upload has left the pinned buffer
+        key = (iters, bs_hist, bs_new)
+        if on_cpu and self._draw_host.get("key") != key:
+            self._draw_host = {"key": key, "hist": torch.empty((iters, bs_hist), dtype=torch.int64).pin_memory(),
+                               "new": torch.empty((iters, max(bs_new, 1)), dtype=torch.int64).pin_memory()}
+        hist_rows, new_rows = [], []
+        for it in range(iters):
+            h = torch.randint(0, self.pool_sample_count, (bs_hist,), device=gen.device, generator=gen)
+            n = torch.randint(0, new_count, (bs_new,), device=gen.device, generator=gen) if bs_new > 0 else None
+            if on_cpu:
+                self._draw_host["hist"][it].copy_(h)
+                if n is not None:
+                    self._draw_host["new"][it].copy_(n)
+            else:
+                hist_rows.append(h)
+                new_rows.append(n)
+        if on_cpu:
+            hist = self._draw_host["hist"].to(dev, non_blocking=True)
+            new = self._draw_host["new"].to(dev, non_blocking=True) if bs_new > 0 else None
+            self._draw_event = torch.cuda.Event()
+            self._draw_event.record()
+            return hist, new
+        return torch.stack(hist_rows).to(dev), (torch.stack(new_rows).to(dev) if bs_new > 0 else None)
+
+    def _mapping_fused(self, iters):
+        cfg, npts, dev = self.config, self.neural_points, self.device
+        lib = P.load()
+        bs = int(cfg.bs)
+        bs_new = 0
+        stop_status = getattr(self.dataset, "stop_status", False)
+        if cfg.bs_new_sample > 0 and self.new_idx is not None and not self.lose_track and not stop_status:
+            bs_new = min(int(self.new_idx.shape[0]), int(cfg.bs_new_sample))  # get_batch, mapper.py:336-343
+        bs_hist = bs - bs_new
+        eik_on = bool(cfg.ekional_loss_on and cfg.weight_e > 0)
+        decim = int(cfg.gradient_decimation) if eik_on else 0
+        ng = (bs + decim - 1) // decim if decim > 0 else 0
+        n = bs + 6 * ng
+        hist, new = self._draw_batches(iters, bs_hist, bs_new, int(self.new_idx.shape[0]) if bs_new > 0 else 0)
+        pool = (self.coord_pool if self.ba_done_flag else self.global_coord_pool).contiguous()
+        buf = self._fused_buf
+        if buf.get("n") != n:
+            buf.clear()
+            buf.update(n=n, xyz=torch.empty((n, 3), dtype=torch.float32, device=dev),
+                       ts=torch.empty(n, dtype=torch.int64, device=dev),
+                       label=torch.empty(bs, dtype=torch.float32, device=dev),
+                       weight=torch.empty(bs, dtype=torch.float32, device=dev),
+                       sdf=torch.empty(n, dtype=torch.float32, device=dev),
+                       nn=torch.empty(n, dtype=torch.int32, device=dev),
+                       grad_sdf=torch.empty(n, dtype=torch.float32, device=dev),
+                       stage=torch.empty(int(lib.pinq_stage_bytes(n)), dtype=torch.uint8, device=dev),
+                       relu=torch.empty(int(lib.pinq_relu_mask_words(n)), dtype=torch.int32, device=dev),
+                       perm=torch.empty(n, dtype=torch.int32, device=dev) if n >= npts.bin_queries_min else None)
+        feats = npts.local_geo_features.data
+        decoder = self._trainable_decoder()
+        dec_n = sum(int(t.numel()) for t in decoder) if decoder else 0
+        # one zero-filled block: feature + decoder gradients, loss log, eikonal counters; Adam leaves the grads zero
+        zero = torch.zeros(feats.numel() + dec_n + 2 * iters + iters, dtype=torch.float32, device=dev)
+        moments = torch.empty(2 * (feats.numel() + dec_n), dtype=torch.float32, device=dev)
+        g_feats, off = zero[: feats.numel()], feats.numel()
+        a = npts._query_args(buf["xyz"], self.geo_mlp.view(), buf["ts"], True, True)
+        a.sdf, a.nn_count, a.stage, a.relu_mask, a.perm = (P.ptr(buf["sdf"]), P.ptr(buf["nn"]), P.ptr(buf["stage"]),
+                                                           P.ptr(buf["relu"]), P.ptr(buf["perm"]))
+        m = P.MappingArgs()
+        m.query = a
+        b = m.bwd
+        b.dec, b.n, b.flags, b.k, b.feature_dim = a.dec, n, (P.F_MMA_SYNC if npts.use_mma_sync else 0), a.k, a.feature_dim
+        b.features, b.stage, b.relu_mask, b.perm = a.features, a.stage, a.relu_mask, a.perm
+        b.grad_sdf, b.grad_features = P.ptr(buf["grad_sdf"]), P.ptr(g_feats)
+        tensors = [(feats, g_feats)]
+        if decoder:
+            grads = []
+            for t in decoder:
+                grads.append(zero[off: off + t.numel()])
+                off += t.numel()
+                tensors.append((t.data, grads[-1]))
+            b.grad_W1, b.grad_b1, b.grad_W2, b.grad_b2 = (P.ptr(g) for g in grads)
+        loss = zero[off: off + 2 * iters]
+        eik_count = zero[off + 2 * iters:].view(torch.int32)
+        mo = 0
+        for i, (p, g) in enumerate(tensors):
+            if not p.is_contiguous():
+                raise P.PinqError("fused mapping needs contiguous parameters")
+            cnt = p.numel()
+            m.tensors[i] = P.AdamTensor(P.ptr(p), P.ptr(g), P.ptr(moments[mo: mo + cnt]), P.ptr(moments[mo + cnt: mo + 2 * cnt]), cnt)
+            mo += 2 * cnt
+        m.tensor_count = len(tensors)
+        m.pool_xyz, m.pool_label, m.pool_weight, m.pool_ts = (P.ptr(pool), P.ptr(self.sdf_label_pool.contiguous()),
+                                                              P.ptr(self.weight_pool.contiguous()), P.ptr(self.time_pool.contiguous()))
+        m.draws_hist, m.draws_new = P.ptr(hist), P.ptr(new)
+        m.new_idx = P.ptr(self.new_idx.contiguous()) if bs_new > 0 else None
+        m.bs, m.bs_new, m.decimation = bs, bs_new, decim
+        m.eik_mode = {"all": P.EIK_ALL, "surface": P.EIK_SURFACE, "freespace": P.EIK_FREESPACE}[cfg.ekional_add_to]
+        m.weighted = int(bool(cfg.loss_weight_on))
+        m.eps_step = float(cfg.voxel_size_m * cfg.num_grad_step_ratio)
+        m.sigma, m.weight_e, m.surface_range = float(self.sdf_scale), float(cfg.weight_e), float(cfg.surface_sample_range_m)
+        m.batch_xyz, m.batch_ts, m.batch_label, m.batch_weight = (P.ptr(buf["xyz"]), P.ptr(buf["ts"]), P.ptr(buf["label"]),
+                                                                  P.ptr(buf["weight"]))
+        m.grad_sdf, m.loss, m.eik_count = P.ptr(buf["grad_sdf"]), P.ptr(loss), P.ptr(eik_count)
+        m.lr, m.beta1, m.beta2, m.adam_eps, m.weight_decay = float(cfg.lr), 0.9, 0.99, float(cfg.adam_eps), float(cfg.weight_decay)
+        P.check(lib.pinq_mapping_run(m, int(iters), P.stream()))
+        self.total_iter += iters
+        self.last_loss = loss.view(iters, 2)   # (bce, eikonal) per iteration, on the device
+        self._fused_last = {"moments": moments, "tensors": tensors}  # read by the parity tests
 
     def mapping_loss(self, coord, sdf_label, ts, weight):
         """One iteration's loss (reference: utils/mapper.py:461-547): BCE on the fused SDF prediction plus the

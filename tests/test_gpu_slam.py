@@ -152,6 +152,131 @@ def test_mesher_grid_matches_oracle(world):
     assert np.array_equal(mask_g.numpy().astype(bool), mask_ref.numpy())
 
 
+def _mapper_with_pool(world, pool_n=12000, seed=31):
+    from pin_slam_b200.utils.mapper import Mapper
+    s, m, cfg, dec, d = world
+    g = torch.Generator().manual_seed(seed)
+    mp = Mapper(cfg, None, m, dec, None, None)
+    coord = make_queries(s.points, pool_n, seed=seed).cuda()
+    mp.global_coord_pool = coord
+    mp.coord_pool = coord.clone()
+    mp.sdf_label_pool = (0.2 * torch.randn(pool_n, generator=g)).cuda()
+    w = torch.rand(pool_n, generator=g) + 0.5
+    w[::3] *= -1
+    mp.weight_pool = w.cuda()
+    mp.time_pool = torch.randint(0, 3, (pool_n,), generator=g).cuda()
+    mp.pool_sample_count = pool_n
+    mp.new_idx = torch.arange(pool_n - 900, pool_n, device="cuda")
+    return mp
+
+
+def _snapshot(m, dec):
+    return (m.local_geo_features.data.clone(), [p.data.clone() for p in dec.parameters()],
+            m.local_point_certainties.clone(), m.local_point_ts_update.clone())
+
+
+def _restore(m, dec, snap):
+    m.local_geo_features.data.copy_(snap[0])
+    for p, q in zip(dec.parameters(), snap[1]):
+        p.data.copy_(q)
+        p.grad = None
+    m.local_geo_features.grad = None
+    m.local_point_certainties, m.local_point_ts_update = snap[2].clone(), snap[3].clone()
+
+
+@pytest.mark.parametrize("eik_mode", ["all", "surface"])
+def test_fused_mapping_iteration_matches_autograd_step(world, eik_mode):
+    """pinq_mapping_run (gather + fused query + closed-form loss gradient + backward + multi-tensor Adam) against
+    the same iteration written as get_batch -> mapping_loss -> autograd -> torch.optim.Adam on identical draws
+    (reference: utils/mapper.py:323-361, 441-573)."""
+    from pin_slam_b200.utils.tools import setup_optimizer
+    s, m, cfg, dec, d = world
+    old = (cfg.bs, cfg.bs_new_sample, cfg.ekional_add_to)
+    cfg.bs, cfg.bs_new_sample, cfg.ekional_add_to = 2048, 256, eik_mode
+    snap = _snapshot(m, dec)
+    try:
+        mp = _mapper_with_pool(world)
+        mp.generator = torch.Generator().manual_seed(3)
+        coord, label, ts, _, _, _, weight = mp.get_batch(global_coord=True)
+        loss_ref, _ = mp.mapping_loss(coord, label, ts, weight)
+        opt = setup_optimizer(cfg, list(m.parameters()), list(dec.parameters()), None, None)
+        opt.zero_grad(set_to_none=True)
+        loss_ref.backward()
+        grads_ref = [m.local_geo_features.grad.clone()] + [p.grad.clone() for p in dec.fused_params()]
+        opt.step()
+        after_ref = [m.local_geo_features.data.clone()] + [p.data.clone() for p in dec.fused_params()]
+        cert_ref, ts_ref = m.local_point_certainties.clone(), m.local_point_ts_update.clone()
+        _restore(m, dec, snap)
+
+        mp.generator = torch.Generator().manual_seed(3)
+        assert mp._fused_mapping_supported()
+        mp._mapping_fused(1)
+        torch.cuda.synchronize()
+        loss = mp.last_loss[0, 0] + cfg.weight_e * mp.last_loss[0, 1]
+        assert abs(float(loss) - float(loss_ref)) < 2e-5 * abs(float(loss_ref)), (float(loss), float(loss_ref))
+        moments, tensors = mp._fused_last["moments"], mp._fused_last["tensors"]
+        off = 0
+        for (p, g), g_ref, p_ref in zip(tensors, grads_ref, after_ref):
+            cnt = p.numel()
+            g_fused = moments[off: off + cnt].view_as(g_ref) / (1.0 - 0.9)   # exp_avg after step 1 = (1 - beta1) g
+            off += 2 * cnt
+            assert rel_err(g_fused, g_ref) < 3e-5
+            assert float(g.abs().max()) == 0.0                               # zero_grad
+            # step 1 moves every touched element by lr * sign(g): only elements whose gradient is rounding noise may differ
+            bad = ((p - p_ref).abs() > 1e-6).float().mean()
+            assert float(bad) < 2e-3, float(bad)
+        assert rel_err(m.local_point_certainties, cert_ref) < 1e-5
+        assert torch.equal(m.local_point_ts_update, ts_ref)
+    finally:
+        cfg.bs, cfg.bs_new_sample, cfg.ekional_add_to = old
+        _restore(m, dec, snap)
+
+
+def test_fused_mapping_follows_autograd_loop(world):
+    """Five iterations: the device-side loop and the per-iteration autograd loop train to the same map."""
+    from pin_slam_b200.utils.tools import freeze_model, unfreeze_model
+    s, m, cfg, dec, d = world
+    old = (cfg.bs, cfg.bs_new_sample)
+    cfg.bs, cfg.bs_new_sample = 2048, 256
+    snap = _snapshot(m, dec)
+    probe = make_queries(s.points, 4000, seed=77).cuda()
+    try:
+        for frozen in (False, True):
+            if frozen:
+                freeze_model(dec)
+            out = []
+            for fused in (False, True):
+                mp = _mapper_with_pool(world)
+                mp.generator = torch.Generator().manual_seed(5)
+                mp.fused_mapping = fused
+                assert mp._fused_mapping_supported()
+                if fused:
+                    mp._mapping_fused(5)
+                else:
+                    mp._mapping_autograd(5)
+                with torch.no_grad():
+                    sdf = m.query_sdf(probe, dec, None, False, True)["sdf"].clone()
+                out.append((m.local_geo_features.data.clone(), [p.data.clone() for p in dec.parameters()], sdf))
+                assert mp.total_iter == 5
+                _restore(m, dec, snap)
+            (f0, d0, s0), (f1, d1, s1) = out
+            moved = (f0 - snap[0]).abs() > 0
+            assert float(moved.float().mean()) > 0.01
+            assert float(((f0 - f1).abs() > 1e-4)[moved].float().mean()) < 0.02
+            assert float((s0 - s1).abs().mean()) < 1e-4 * max(1.0, float(s0.abs().mean()))
+            for a, b, c in zip(d0, d1, snap[1]):
+                if frozen:
+                    assert torch.equal(a, c) and torch.equal(b, c)
+                else:
+                    assert float((a - b).abs().max()) < 1e-3
+            if frozen:
+                unfreeze_model(dec)
+    finally:
+        unfreeze_model(dec)
+        cfg.bs, cfg.bs_new_sample = old
+        _restore(m, dec, snap)
+
+
 def test_adam_step_matches_torch():
     from pin_slam_b200 import _pinq as P
     g = torch.Generator().manual_seed(3)
