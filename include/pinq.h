@@ -286,6 +286,21 @@ int pinq_mesher_grid_query(const pinq_query_args* args, const float* origin3_hos
                            float voxel, int64_t first, int64_t count, int32_t min_nn, float* sdf_out,
                            uint8_t* mask_out, void* stream);
 
+/* One Gauss-Newton iteration of Tracker.tracking (utils/tracker.py:91-107 + registration_step :277-452) as a
+ * single call: cur = T * source (utils/tools.py:386-399; skipped when h_T12 is NULL: query.xyz is read as is),
+ * fused query with gradient and std, the reduction above, and the copy of its 32 doubles to pinned host
+ * memory.  The caller synchronises the stream, then solves the 6x6 system on the host (tracker.py:468-520). */
+typedef struct pinq_tracking_args {
+    pinq_query_args query;     /* xyz = [n,3] buffer for the transformed points; sdf, grad_x, sdf_std, nn_count set */
+    const float* source_xyz;   /* [n,3] points in the sensor frame                                  */
+    const float* sdf_label;    /* [n] or NULL                                                       */
+    int32_t min_nn;
+    float min_grad_norm, max_grad_norm, max_sdf_std, gm_dist, gm_grad;
+    double* gn_out;            /* [32] device                                                       */
+    double* h_gn_out;          /* [32] pinned host                                                  */
+} pinq_tracking_args;
+int pinq_tracking_step(const pinq_tracking_args* args, const float* h_T12, void* stream);
+
 /* ---- fused Adam (utils/tools.py:89-116; torch.optim.Adam single-tensor semantics) -------- */
 int pinq_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, float lr,
                    float beta1, float beta2, float eps, int32_t step, void* stream);

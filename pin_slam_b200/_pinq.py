@@ -39,6 +39,12 @@ class BwdArgs(C.Structure):
                 ("grad_b2", _vp)]
 
 
+class TrackingArgs(C.Structure):
+    _fields_ = [("query", QueryArgs), ("source_xyz", _vp), ("sdf_label", _vp), ("min_nn", _i32), ("min_grad_norm", _f32),
+                ("max_grad_norm", _f32), ("max_sdf_std", _f32), ("gm_dist", _f32), ("gm_grad", _f32), ("gn_out", _vp),
+                ("h_gn_out", _vp)]
+
+
 class AdamTensor(C.Structure):
     _fields_ = [("param", _vp), ("grad", _vp), ("exp_avg", _vp), ("exp_avg_sq", _vp), ("n", _i64)]
 
@@ -95,6 +101,7 @@ SIGNATURES = {
                                          _i32, _vp, _vp, _vp]),
     "pinq_adam_step": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _f32, _f32, _f32, _f32, _i32, _vp]),
     "pinq_stencil_masks_build": (C.c_int, [_vp, _i32, _i32, _vp, _vp]),
+    "pinq_tracking_step": (C.c_int, [C.POINTER(TrackingArgs), C.POINTER(_f32), _vp]),
     "pinq_mapping_run": (C.c_int, [C.POINTER(MappingArgs), _i32, _vp]),
 }
 

@@ -15,6 +15,18 @@ __global__ void k_transform(const float* __restrict__ xyz, int64_t n, const floa
         out[3 * i + r] = fmaf(x, T12[4 * r], fmaf(y, T12[4 * r + 1], fmaf(z, T12[4 * r + 2], T12[4 * r + 3])));
 }
 
+struct Pose12 { float v[12]; };
+
+// same arithmetic with the pose passed by value: no host->device copy in front of every Gauss-Newton iteration
+__global__ void k_transform_pose(const float* __restrict__ xyz, int64_t n, Pose12 T, float* __restrict__ out) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float x = xyz[3 * i], y = xyz[3 * i + 1], z = xyz[3 * i + 2];
+#pragma unroll
+    for (int r = 0; r < 3; ++r)
+        out[3 * i + r] = fmaf(x, T.v[4 * r], fmaf(y, T.v[4 * r + 1], fmaf(z, T.v[4 * r + 2], T.v[4 * r + 3])));
+}
+
 constexpr int kGnVals = 30;  // 21 (upper H) + 6 (b) + sum w + sum |r| + count
 constexpr int kGnBlock = 256;
 
@@ -114,6 +126,30 @@ int pinq_gn_accumulate(const float* xyz, const float* sdf, const float* grad, co
                                                            min_grad_norm, max_grad_norm, max_sdf_std, gm_dist, gm_grad,
                                                            out32, valid_out);
     return check_launch("pinq_gn_accumulate");
+}
+
+int pinq_tracking_step(const pinq_tracking_args* a, const float* h_T12, void* stream) {
+    PINQ_REQUIRE(a && a->gn_out && a->h_gn_out, "null pointer");
+    const pinq_query_args& q = a->query;
+    PINQ_REQUIRE(q.xyz && q.sdf && q.grad_x && q.sdf_std && q.nn_count, "query outputs sdf / grad_x / sdf_std / nn_count needed");
+    PINQ_REQUIRE(!h_T12 || a->source_xyz, "source points needed with a pose");
+    cudaStream_t st = as_stream(stream);
+    const int64_t n = q.n;
+    int rc;
+    if (n > 0 && h_T12) {
+        Pose12 T;
+        for (int i = 0; i < 12; ++i) T.v[i] = h_T12[i];
+        k_transform_pose<<<grid_for(n, 256), 256, 0, st>>>(a->source_xyz, n, T, const_cast<float*>(q.xyz));
+        if ((rc = check_launch("k_transform_pose")) != PINQ_OK) return rc;
+    }
+    if ((rc = pinq_query_fused_fwd(&a->query, stream)) != PINQ_OK) return rc;
+    if (cudaMemsetAsync(a->gn_out, 0, 32 * sizeof(double), st) != cudaSuccess) return check_launch("pinq_tracking_step memset");
+    rc = pinq_gn_accumulate(q.xyz, q.sdf, q.grad_x, q.sdf_std, q.nn_count, a->sdf_label, n, a->min_nn, a->min_grad_norm,
+                            a->max_grad_norm, a->max_sdf_std, a->gm_dist, a->gm_grad, a->gn_out, nullptr, stream);
+    if (rc != PINQ_OK) return rc;
+    if (cudaMemcpyAsync(a->h_gn_out, a->gn_out, 32 * sizeof(double), cudaMemcpyDeviceToHost, st) != cudaSuccess)
+        return check_launch("pinq_tracking_step copy");
+    return PINQ_OK;
 }
 
 int pinq_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, float lr, float beta1,

@@ -311,7 +311,7 @@ class Mapper:
         dec_n = sum(int(t.numel()) for t in decoder) if decoder else 0
         # one zero-filled block: feature + decoder gradients, loss log, eikonal counters; Adam leaves the grads zero
         zero = torch.zeros(feats.numel() + dec_n + 2 * iters + iters, dtype=torch.float32, device=dev)
-        moments = torch.empty(2 * (feats.numel() + dec_n), dtype=torch.float32, device=dev)
+        moments = torch.empty(2 * (feats.numel() + dec_n) + 64, dtype=torch.float32, device=dev)
         g_feats, off = zero[: feats.numel()], feats.numel()
         a = npts._query_args(buf["xyz"], self.geo_mlp.view(), buf["ts"], True, True)
         a.sdf, a.nn_count, a.stage, a.relu_mask, a.perm = (P.ptr(buf["sdf"]), P.ptr(buf["nn"]), P.ptr(buf["stage"]),
@@ -337,8 +337,9 @@ class Mapper:
             if not p.is_contiguous():
                 raise P.PinqError("fused mapping needs contiguous parameters")
             cnt = p.numel()
-            m.tensors[i] = P.AdamTensor(P.ptr(p), P.ptr(g), P.ptr(moments[mo: mo + cnt]), P.ptr(moments[mo + cnt: mo + 2 * cnt]), cnt)
-            mo += 2 * cnt
+            pad = (cnt + 3) // 4 * 4   # keeps every moment slice 16-byte aligned (vectorised Adam)
+            m.tensors[i] = P.AdamTensor(P.ptr(p), P.ptr(g), P.ptr(moments[mo: mo + cnt]), P.ptr(moments[mo + pad: mo + pad + cnt]), cnt)
+            mo += 2 * pad
         m.tensor_count = len(tensors)
         m.pool_xyz, m.pool_label, m.pool_weight, m.pool_ts = (P.ptr(pool), P.ptr(self.sdf_label_pool.contiguous()),
                                                               P.ptr(self.weight_pool.contiguous()), P.ptr(self.time_pool.contiguous()))

@@ -1,14 +1,15 @@
 """Tracker -- point-to-implicit-model registration (reference: utils/tracker.py:19-520).
 
 Same constructor, `tracking()` signature, return tuple and validity control flow as the reference.
-Per Gauss-Newton iteration the device runs four launches -- transform (pinq_transform_points),
-search + decode (pinq_query_fused_fwd: sdf, d sdf/dx, std, nn_count in one pass, replacing
-query_feature -> Decoder.sdf -> get_gradient) and the fused mask/weights/normal-equation reduction
-(pinq_gn_accumulate) -- followed by ONE 256-byte device->host read; the 6x6 solve runs on the host in
-fp64 exactly as the reference does (tracker.py:491).  Colour / normal / semantic inputs are out of scope.
+Per Gauss-Newton iteration the host makes ONE call (pinq_tracking_step) that enqueues four launches --
+transform by the current pose (passed by value), search + decode (pinq_query_fused_fwd: sdf, d sdf/dx, std,
+nn_count in one pass, replacing query_feature -> Decoder.sdf -> get_gradient) and the fused
+mask/weights/normal-equation reduction (pinq_gn_accumulate) -- and ONE 256-byte device->host read into
+pinned memory; the 6x6 solve runs on the host in fp64 exactly as the reference does (tracker.py:491).  Colour / normal / semantic inputs are out of scope.
 """
 from __future__ import annotations
 
+import ctypes
 import math
 
 import numpy as np
@@ -30,6 +31,10 @@ class Tracker:
         self.sdf_scale = config.logistic_gaussian_ratio * config.sigma_sigmoid_m
         self._gn_out = torch.zeros(32, dtype=torch.float64, device=self.device)
         self._gn_host = torch.zeros(32, dtype=torch.float64).pin_memory()
+        self._gn_host_np = self._gn_host.numpy()
+        self._t12 = np.zeros((3, 4), dtype=np.float32)
+        self._t12_ptr = self._t12.ctypes.data_as(ctypes.POINTER(ctypes.c_float))
+        self._step_buf, self._label_keepalive = {}, None
         self.last_iterations = 0
 
     # ------------------------------------------------------------------------------------------
@@ -64,14 +69,12 @@ class Tracker:
         valid_point_count = 0
         eigenvalues = None
         cur_points = torch.empty_like(src)
-        lib = P.load()
+        step_args = self._tracking_args(cur_points, src, source_sdf, min_grad_norm, max_grad_norm, GM_dist, GM_grad)
         it = 0
         for i in range(iter_n):
             it = i + 1
-            T12 = torch.from_numpy(T[:3, :].astype(np.float32)).to(self.device, non_blocking=True)
-            P.check(lib.pinq_transform_points(P.ptr(src), source_point_count, P.ptr(T12), P.ptr(cur_points), P.stream()))
-            reg = self.registration_step(cur_points, None, source_sdf, None, cur_ts, min_grad_norm, max_grad_norm,
-                                         GM_dist, GM_grad, cfg.reg_lm_lambda, (vis_result and converged))
+            # one call per iteration: transform by T, fused query (sdf, gradient, std), normal-equation reduction
+            reg = self._gauss_newton_step(step_args, T, cfg.reg_lm_lambda, (vis_result and converged))
             delta_T, cov_mat, eigenvalues, _, valid_point_count, sdf_residual_cm, _ = reg
             T = delta_T @ T
             if (sdf_residual_cm - last_sdf_residual_cm) / last_sdf_residual_cm > max_increment_sdf_residual_ratio:
@@ -137,30 +140,57 @@ class Tracker:
                     certainty[head:tail] = out["certainty"]
         return sdf_pred, sdf_grad, None, None, None, mc_mask, certainty, sdf_std
 
-    def registration_step(self, points, normals, sdf_labels, colors, cur_ts, min_grad_norm, max_grad_norm, GM_dist=None,
-                          GM_grad=None, lm_lambda=0.0, vis_weight_pc=False):
-        """reference: utils/tracker.py:277-452 + implicit_reg :468-520.
-        -> (delta_T ndarray[4,4] f64, cov_mat, eigenvalues, None, valid_point_count, residual_cm, None)"""
-        cfg = self.config
-        lib = P.load()
-        n = points.shape[0]
-        with torch.no_grad():
-            out = self.neural_points.query_sdf(points, self.geo_decoder, None, False, True, want_grad=True, want_std=True)
-        max_sdf_std = cfg.surface_sample_range_m * cfg.max_sdf_std_ratio
-        self._gn_out.zero_()
-        P.check(lib.pinq_gn_accumulate(P.ptr(points), P.ptr(out["sdf"]), P.ptr(out["grad"]), P.ptr(out["std"]),
-                                       P.ptr(out["nn_count"]), P.ptr(sdf_labels) if sdf_labels is not None else None, n,
-                                       int(cfg.query_nn_k), float(min_grad_norm), float(max_grad_norm), float(max_sdf_std),
-                                       float(GM_dist or 0.0), float(GM_grad or 0.0), P.ptr(self._gn_out), None, P.stream()))
-        self._gn_host.copy_(self._gn_out, non_blocking=True)
+    def _tracking_args(self, xyz, source, sdf_labels, min_grad_norm, max_grad_norm, GM_dist, GM_grad):
+        """pinq_tracking_args for `xyz` [n,3] (the buffer the fused query reads); built once per tracking() call --
+        the map does not change between Gauss-Newton iterations."""
+        cfg, npts, dev = self.config, self.neural_points, self.device
+        n = xyz.shape[0]
+        if self._step_buf.get("n") != n:
+            self._step_buf = {"n": n, "sdf": torch.empty(n, dtype=torch.float32, device=dev),
+                              "grad": torch.empty((n, 3), dtype=torch.float32, device=dev),
+                              "std": torch.empty(n, dtype=torch.float32, device=dev),
+                              "nn": torch.empty(n, dtype=torch.int32, device=dev),
+                              "perm": torch.empty(n, dtype=torch.int32, device=dev) if n >= npts.bin_queries_min else None}
+        b = self._step_buf
+        a = npts._query_args(xyz, self.geo_decoder.view(), None, False, True)
+        a.sdf, a.grad_x, a.sdf_std, a.nn_count, a.perm = (P.ptr(b["sdf"]), P.ptr(b["grad"]), P.ptr(b["std"]), P.ptr(b["nn"]),
+                                                         P.ptr(b["perm"]))
+        t = P.TrackingArgs()
+        t.query = a
+        t.source_xyz = P.ptr(source)
+        self._label_keepalive = sdf_labels.detach().float().contiguous() if sdf_labels is not None else None
+        t.sdf_label = P.ptr(self._label_keepalive)
+        t.min_nn = int(cfg.query_nn_k)
+        t.min_grad_norm, t.max_grad_norm = float(min_grad_norm), float(max_grad_norm)
+        t.max_sdf_std = float(cfg.surface_sample_range_m * cfg.max_sdf_std_ratio)
+        t.gm_dist, t.gm_grad = float(GM_dist or 0.0), float(GM_grad or 0.0)
+        t.gn_out, t.h_gn_out = P.ptr(self._gn_out), self._gn_host.data_ptr()
+        return t
+
+    def _gauss_newton_step(self, step_args, T, lm_lambda, vis_weight_pc=False):
+        """Enqueue pinq_tracking_step (pose T applied to the source points; None: points as given), wait for the
+        32 doubles and solve on the host."""
+        t12 = None
+        if T is not None:
+            self._t12[:] = T[:3, :]  # float64 -> float32 as the reference's tensor cast (tracker.py:94)
+            t12 = self._t12_ptr
+        P.check(P.load().pinq_tracking_step(step_args, t12, P.stream()))
         torch.cuda.current_stream().synchronize()
-        g = self._gn_host.numpy()
+        g = self._gn_host_np
         valid_point_count = int(round(g[29]))
         if valid_point_count < 10:  # tracker.py:310-312
             return np.eye(4), None, None, None, valid_point_count, 0.0, 0.0
         residual_cm = g[28] / valid_point_count * 100.0
-        T, cov_mat, eig = solve_normal_equations(g, valid_point_count, lm_lambda, vis_weight_pc, vis_weight_pc)
-        return T, cov_mat, eig, None, valid_point_count, residual_cm, None
+        Td, cov_mat, eig = solve_normal_equations(g, valid_point_count, lm_lambda, vis_weight_pc, vis_weight_pc)
+        return Td, cov_mat, eig, None, valid_point_count, residual_cm, None
+
+    def registration_step(self, points, normals, sdf_labels, colors, cur_ts, min_grad_norm, max_grad_norm, GM_dist=None,
+                          GM_grad=None, lm_lambda=0.0, vis_weight_pc=False):
+        """reference: utils/tracker.py:277-452 + implicit_reg :468-520.
+        -> (delta_T ndarray[4,4] f64, cov_mat, eigenvalues, None, valid_point_count, residual_cm, None)"""
+        pts = points.detach().to(self.dtype).contiguous()
+        args = self._tracking_args(pts, None, sdf_labels, min_grad_norm, max_grad_norm, GM_dist, GM_grad)
+        return self._gauss_newton_step(args, None, lm_lambda, vis_weight_pc)
 
 
 def solve_normal_equations(g: np.ndarray, count: int, lm_lambda: float, require_cov=False, require_eigen=False):
