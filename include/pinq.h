@@ -36,6 +36,7 @@ extern "C" {
 #define PINQ_F_ROTATE 4u       /* after_pgo=True: rotate x-p_k into the point frame (tools.py:316)     */
 #define PINQ_F_RECIP_DIV 8u    /* floor(x*(1/res)) instead of floor(x/res): CUDA-eager oracle (H1)     */
 #define PINQ_F_SKIP_EMPTY 16u  /* mesher: sdf = 0 where nn_count == 0 (utils/mesher.py:96-103)         */
+#define PINQ_F_EXACT_KEYS 64u  /* brick search: every query through the 64-bit-key pass (the fast pass falls back to it on truncated-key ties; tests) */
 #define PINQ_F_MMA_SYNC 32u    /* decode / backward: the mma.sync kernels instead of the tcgen05 ones (A/B tests; also pinq_bwd_args.flags) */
 
 const char* pinq_last_error(void);

@@ -10,7 +10,7 @@ import torch
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIB_PATH = os.path.join(_HERE, "libpinq.so")
 
-F_LOCAL, F_TRAINING, F_ROTATE, F_RECIP_DIV, F_SKIP_EMPTY, F_MMA_SYNC = 1, 2, 4, 8, 16, 32
+F_LOCAL, F_TRAINING, F_ROTATE, F_RECIP_DIV, F_SKIP_EMPTY, F_MMA_SYNC, F_EXACT_KEYS = 1, 2, 4, 8, 16, 32, 64
 
 _vp, _i64, _i32, _u32, _u64, _f32 = C.c_void_p, C.c_int64, C.c_int32, C.c_uint32, C.c_uint64, C.c_float
 

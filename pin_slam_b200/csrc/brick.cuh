@@ -60,6 +60,7 @@ struct BrickDev {
     uint32_t cap_mask;
     const float4* rec;  // brick-ordered candidate records {x, y, z, bits(index)}
     int radius;         // stencil radius in voxels (<= 2)
+    bool exact_keys;    // PINQ_F_EXACT_KEYS
 };
 
 }  // namespace pinq

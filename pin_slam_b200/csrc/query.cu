@@ -291,6 +291,7 @@ __device__ __forceinline__ void topk_insert64(unsigned long long key, unsigned l
 // (x-slab of 2 x 4 x 4 voxels = 32 bits, so the walk is all 32-bit integer work); a (2R+1)^3 stencil with R <= 2
 // touches at most 3 x 2 x 2 of them.
 constexpr int kWalkEntries = 12;
+constexpr uint32_t kWalkIdMask = 0x1FFu;  // entry (4 bits) << 5 | voxel bit (5 bits): identity of a candidate within a lane's walk
 struct BrickLane {
     uint32_t sel[kWalkEntries][kBlock];  // occupied stencil members still to visit
     uint32_t msk[kWalkEntries][kBlock];  // occupancy of the half brick
@@ -371,24 +372,30 @@ __global__ void __launch_bounds__(kBlock) k_search_brick(MapDev map, BrickDev bd
 
     // phase 2: ONE loop over the lane's candidates of all its half bricks (trip count = max over the warp of `total`,
     // bodies predicated so the warp stays converged), software-pipelined: the record of the next candidate is in
-    // flight while the current one is ranked
-    unsigned long long kk[K];
+    // flight while the current one is ranked.
+    //
+    // Fast pass: 32-bit keys = top 23 bits of d^2 (sign-free fp32 order = unsigned order) | walk identity (entry << 5 | bit),
+    // sorted top-(K+1) by min/max pairs (2 instructions per slot instead of 7 for the 64-bit key).  A key with fewer d^2 bits
+    // orders two candidates correctly unless their truncated d^2 are EQUAL; if no two neighbours of the final sorted top-(K+1)
+    // share their 23 bits, every candidate outside it has a strictly larger d^2 than slot K-1 and the K winners and their
+    // order are those of the exact (d^2, stencil position) sort.  Otherwise (about 1 query in 10^4 on the bench map, exact
+    // ties included) the lane repeats the walk with the full 64-bit keys.
+    const int total0 = total;
+    uint32_t k7[K + 1];
 #pragma unroll
-    for (int k = 0; k < K; ++k) kk[k] = ~0ull;
-    int nn = 0, e = -1, lin0 = 0;
+    for (int k = 0; k <= K; ++k) k7[k] = ~0u;
+    int nn = 0, e = -1;
     uint32_t m = 0u, msk = 0u, bas = 0u;
     bool nact;
     float4 nrc;
-    uint32_t nlow;  // stencil position << 24 | record rank of the candidate in flight
-    auto advance = [&]() {
+    uint32_t nid;  // walk identity of the candidate in flight
+    auto advance32 = [&]() {
         nact = total > 0;
         if (nact && m == 0u) {  // next half brick of the list
             ++e;
             m = bl->sel[e][tid];
             msk = bl->msk[e][tid];
-            const uint32_t pk = bl->pk[e][tid];
-            bas = pk & ((1u << kRankBits) - 1u);
-            lin0 = (int)(pk >> kRankBits) - 64;
+            bas = bl->pk[e][tid] & ((1u << kRankBits) - 1u);
         }
         --total;
         const int bit = (__ffs((int)m) - 1) & 31;
@@ -396,24 +403,82 @@ __global__ void __launch_bounds__(kBlock) k_search_brick(MapDev map, BrickDev bd
         const uint32_t rank = bas + (uint32_t)__popc(msk & ((1u << bit) - 1u));
         nrc = make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
         if (nact) nrc = __ldg(&bd.rec[rank]);
-        nlow = ((uint32_t)s_sid[(lin0 + s_bitoff[bit]) & 127] << kRankBits) | rank;
+        nid = ((uint32_t)e << 5) | (uint32_t)bit;
     };
-    advance();
+    advance32();
     while (__any_sync(0xffffffffu, nact)) {
         const bool act = nact;
         const float4 rc = nrc;
-        const uint32_t low = nlow;
-        advance();
+        const uint32_t id = nid;
+        advance32();
         const float d2 = dist2_rn(rc.x, rc.y, rc.z, x, y, z);
         // valid: index != -1 (-2 = hazard H13, still a candidate) and not d2 > max (neural_points.py:499)
         const bool ok = act && __float_as_int(rc.w) != -1 && !(d2 > map.max_d2);
         nn += ok ? 1 : 0;
-        const unsigned long long key = ok ? ((unsigned long long)__float_as_uint(d2) << 32) | low : ~0ull;
-        topk_insert64(key, kk);
+        uint32_t key = ok ? ((__float_as_uint(d2) & ~kWalkIdMask) | id) : ~0u;
+#pragma unroll
+        for (int k = 0; k <= K; ++k) {  // ascending insertion: slot keeps the smaller, the larger moves on
+            const uint32_t lo = min(k7[k], key);
+            key = max(k7[k], key);
+            k7[k] = lo;
+        }
     }
+    bool tie = false;
+#pragma unroll
+    for (int k = 0; k < K; ++k) tie |= k7[k + 1] != ~0u && ((k7[k] ^ k7[k + 1]) <= kWalkIdMask);
+    tie |= bd.exact_keys;
     int32_t r[K];
 #pragma unroll
-    for (int k = 0; k < K; ++k) r[k] = kk[k] == ~0ull ? -1 : (int32_t)((uint32_t)kk[k] & ((1u << kRankBits) - 1u));
+    for (int k = 0; k < K; ++k) {
+        r[k] = -1;
+        if (k7[k] != ~0u) {
+            const uint32_t we = (k7[k] & kWalkIdMask) >> 5, wb = k7[k] & 31u;
+            r[k] = (int32_t)((bl->pk[we][tid] & ((1u << kRankBits) - 1u)) + (uint32_t)__popc(bl->msk[we][tid] & ((1u << wb) - 1u)));
+        }
+    }
+    if (__any_sync(0xffffffffu, tie)) {  // exact pass for the lanes with a truncated-key tie
+        unsigned long long kk[K];
+#pragma unroll
+        for (int k = 0; k < K; ++k) kk[k] = ~0ull;
+        total = tie ? total0 : 0;
+        e = -1;
+        m = 0u;
+        int lin0 = 0;
+        uint32_t nlow;  // stencil position << 24 | record rank of the candidate in flight
+        auto advance = [&]() {
+            nact = total > 0;
+            if (nact && m == 0u) {
+                ++e;
+                m = bl->sel[e][tid];
+                msk = bl->msk[e][tid];
+                const uint32_t pk = bl->pk[e][tid];
+                bas = pk & ((1u << kRankBits) - 1u);
+                lin0 = (int)(pk >> kRankBits) - 64;
+            }
+            --total;
+            const int bit = (__ffs((int)m) - 1) & 31;
+            m &= m - 1u;
+            const uint32_t rank = bas + (uint32_t)__popc(msk & ((1u << bit) - 1u));
+            nrc = make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
+            if (nact) nrc = __ldg(&bd.rec[rank]);
+            nlow = ((uint32_t)s_sid[(lin0 + s_bitoff[bit]) & 127] << kRankBits) | rank;
+        };
+        advance();
+        while (__any_sync(0xffffffffu, nact)) {
+            const bool act = nact;
+            const float4 rc = nrc;
+            const uint32_t low = nlow;
+            advance();
+            const float d2 = dist2_rn(rc.x, rc.y, rc.z, x, y, z);
+            const bool ok = act && __float_as_int(rc.w) != -1 && !(d2 > map.max_d2);
+            const unsigned long long key = ok ? ((unsigned long long)__float_as_uint(d2) << 32) | low : ~0ull;
+            topk_insert64(key, kk);
+        }
+        if (tie) {
+#pragma unroll
+            for (int k = 0; k < K; ++k) r[k] = kk[k] == ~0ull ? -1 : (int32_t)((uint32_t)kk[k] & ((1u << kRankBits) - 1u));
+        }
+    }
     if (live && (!RESOLVE || p.grad_x)) {
         int32_t* o = ws + i * kWs;
 #pragma unroll
@@ -809,6 +874,7 @@ static int run_query(const pinq_query_args* a, int mode, float* feat_out, const 
         bd.cap_mask = a->map.brick_cap - 1;
         bd.rec = reinterpret_cast<const float4*>(a->map.brick_rec4);
         bd.radius = a->map.stencil_radius;
+        bd.exact_keys = (a->flags & PINQ_F_EXACT_KEYS) != 0;
     }
 
     DecodeParams p;

@@ -100,6 +100,7 @@ class NeuralPoints(nn.Module):
         self.bin_queries_min = 32768  # fused queries of at least this many points are binned by brick first
         # fused search through the brick index when it is provably equivalent (PINQ_BRICK=0: slot probing only)
         self.use_brick_index = os.environ.get("PINQ_BRICK", "1") != "0"
+        self.exact_search_keys = False  # A/B tests: brick search with 64-bit keys for every query
         self.use_mma_sync = False  # A/B tests: the mma.sync decode / backward kernels instead of the tcgen05 ones
         self._brick_tab = self._brick_global = self._brick_local = self._brick_buf = self._brick_counters = None
         self._brick_host = self._brick_event = None
@@ -520,6 +521,8 @@ class NeuralPoints(nn.Module):
             flags |= P.F_ROTATE
         if self.use_mma_sync:
             flags |= P.F_MMA_SYNC
+        if self.exact_search_keys:
+            flags |= P.F_EXACT_KEYS
         feats = self.local_geo_features if query_locally else self.geo_features
         cert = self.local_point_certainties if query_locally else self.point_certainties
         quats = self.local_point_orientations if query_locally else self.point_orientations

@@ -235,6 +235,38 @@ def test_brick_index_equals_slot_probing(maps):
                        torch.sort(m._brick_global[:n_occ, 3].view(torch.int32)).values)
 
 
+def test_truncated_key_search_equals_exact_keys(maps):
+    """Brick search fast pass (32-bit keys: 23 bits of d^2 | walk identity, csrc/query.cu) against the 64-bit-key pass
+    forced for every query (PINQ_F_EXACT_KEYS): same K neighbours in the same order, also for queries built to tie
+    (midpoints of two neural points, copies of neural points, a query repeated many times)."""
+    s, m, _, dec, d, _ = maps
+    from pin_slam_b200 import _pinq as P
+    pts = s.points
+    g = torch.Generator().manual_seed(23)
+    i = torch.randint(0, pts.shape[0], (20000,), generator=g)
+    j = torch.randint(0, pts.shape[0], (20000,), generator=g)
+    near = (pts[i] - pts[j]).norm(dim=1) < 0.8
+    mid = ((pts[i] + pts[j]) * 0.5)[near]  # exact d^2 ties whenever the halving is exact
+    q = torch.cat([make_queries(s.points, 60000, seed=29), mid, pts[i[:5000]], pts[i[:1]].repeat(4000, 1)]).cuda()
+    res = {}
+    try:
+        for exact in (False, True):
+            m.exact_search_keys = exact
+            a = m._query_args(q, dec.view(), None, False, True)
+            knn = torch.empty((q.shape[0], 6), dtype=torch.int32, device="cuda")
+            sdf = torch.empty(q.shape[0], device="cuda")
+            a.knn_idx, a.sdf = P.ptr(knn), P.ptr(sdf)
+            P.check(P.load().pinq_query_fused_fwd(a, P.stream()))
+            torch.cuda.synchronize()
+            res[exact] = (knn, sdf)
+    finally:
+        m.exact_search_keys = False
+    assert torch.equal(res[False][0], res[True][0])
+    assert torch.equal(res[False][1], res[True][1])
+    _, _, _, _, knn_ref = O.query_feature(s, q.cpu(), None, False, True)
+    assert torch.equal(res[False][0].cpu().long(), knn_ref)
+
+
 @pytest.mark.parametrize("n", [1, 33, 127, 129, 6000])
 def test_tcgen05_kernels_match_mma_sync(maps, n):
     """The tcgen05 / TMEM decode and backward (csrc/decode_tc.cuh, bwd_tc.cuh) against the mma.sync kernels on ragged
