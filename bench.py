@@ -21,6 +21,7 @@ import ctypes
 import json
 import os
 import subprocess
+import threading
 import sys
 import time
 
@@ -116,20 +117,65 @@ def mean_nonempty_slots(npts, q, sample=100_000):
 
 
 class ClockSampler:
+    """SM clock and throttle reasons sampled DURING the timed region: an NVML thread polling every ~2 ms (the timed region
+    of the default run is tens of milliseconds, shorter than nvidia-smi's fastest loop), plus explicit `sample()` calls from
+    the timing loop so that at least one reading falls inside it; nvidia-smi -lms as the fallback when NVML is absent."""
     QUERY = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
              "clocks_event_reasons.sw_power_cap")
 
     def __init__(self, gpu_index):
-        self.proc = None
+        self.proc = self.nv = self.handle = self.thread = None
+        self.sm, self.mx, self.reasons = [], [], set()
+        self._stop = False
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(gpu_index), "--query-gpu=" + self.QUERY,
-                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
-                                         stderr=subprocess.DEVNULL, text=True)
+            import pynvml
+            pynvml.nvmlInit()
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = int(vis.split(",")[gpu_index]) if vis and all(t.strip().isdigit() for t in vis.split(",")) else gpu_index
+            self.handle = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self.nv = pynvml
+            self.mx.append(float(pynvml.nvmlDeviceGetMaxClockInfo(self.handle, pynvml.NVML_CLOCK_SM)))
+            self.thread = threading.Thread(target=self._loop, daemon=True)
+            self.thread.start()
         except Exception:
-            self.proc = None
+            self.nv = None
+            try:
+                self.proc = subprocess.Popen(["nvidia-smi", "-i", str(gpu_index), "--query-gpu=" + self.QUERY,
+                                              "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                             stderr=subprocess.DEVNULL, text=True)
+            except Exception:
+                self.proc = None
+
+    def sample(self):
+        nv = self.nv
+        if nv is None:
+            return
+        try:
+            self.sm.append(float(nv.nvmlDeviceGetClockInfo(self.handle, nv.NVML_CLOCK_SM)))
+            r = int(nv.nvmlDeviceGetCurrentClocksEventReasons(self.handle))
+            for name, bit in (("hw_slowdown", nv.nvmlClocksEventReasonHwSlowdown),
+                              ("hw_thermal_slowdown", nv.nvmlClocksEventReasonHwThermalSlowdown),
+                              ("sw_thermal_slowdown", nv.nvmlClocksEventReasonSwThermalSlowdown),
+                              ("sw_power_cap", nv.nvmlClocksEventReasonSwPowerCap)):
+                if r & int(bit):
+                    self.reasons.add(name)
+        except Exception:
+            pass
+
+    def _loop(self):
+        while not self._stop:
+            self.sample()
+            time.sleep(0.002)
 
     def stop(self):
+        if self.nv is not None:
+            self._stop = True
+            self.thread.join(timeout=2)
+            if not self.sm:
+                return None
+            return {"sm_mhz": float(np.median(self.sm)), "sm_max_mhz": float(max(self.mx)), "reasons": sorted(self.reasons),
+                    "samples": len(self.sm), "source": "nvml"}
         if self.proc is None:
             return None
         self.proc.terminate()
@@ -155,7 +201,7 @@ class ClockSampler:
         if not sm:
             return None
         return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons),
-                "samples": len(sm)}
+                "samples": len(sm), "source": "nvidia-smi"}
 
 
 # ------------------------------------------------------------------------------------------------
@@ -300,8 +346,10 @@ def main():
     sampler = ClockSampler(local_rank) if rank == 0 else None
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record()
-    for _ in range(args.steps):
+    for i in range(args.steps):
         step(q, ts)
+        if sampler and i == args.steps // 2:
+            sampler.sample()  # the host runs ahead of the device: this reading is taken with the queue full
     ev1.record()
     barrier()
     ms_total = ev0.elapsed_time(ev1)
