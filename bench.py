@@ -321,18 +321,43 @@ def main():
     ones = torch.ones(n, device=dev)
     params = [npts.local_geo_features] + list(dec.parameters())
 
+    # data-parallel exchange step: the feature-table and decoder gradients are summed over the ranks.
+    # Default: they accumulate straight into this rank's cudaIpc-shared peer block and ONE kernel per rank reduces them
+    # over NVLink (pinq_peer_exchange, csrc/peer.cu); PINQ_EXCHANGE=nccl selects the NCCL all-reduce A/B partner.
+    peer = carve = None
+    exchange = "none"
+    if world > 1:
+        exchange = os.environ.get("PINQ_EXCHANGE", "peer")
+        if exchange == "peer":
+            from pin_slam_b200.parallel import MappingPeer, PeerExchange
+            rows, fdim = npts.local_geo_features.shape
+            peer = PeerExchange(MappingPeer.capacity(rows, fdim, dec), dev, grid=int(os.environ.get("PINQ_PEER_GRID", "0")))
+            carve = MappingPeer(peer, rows, fdim, dec)
+            n_ex = carve.n_sum - (rows - 1)  # features + decoder (the certainty increments are not part of this step)
+            npts.feature_grad_sink, dec.grad_sink = carve.grad_features, tuple(carve.grad_decoder)
+            grad_block = peer.sum_region()[:n_ex]
+            torch.cuda.synchronize()
+            dist.barrier()
+
     def zero_grads():
+        if peer is not None:
+            grad_block.zero_()
         for p in params:
             p.grad = None
+
+    def exchange_grads():
+        if peer is not None:
+            peer.exchange(n_sum=n_ex, n_max=0)
+        elif world > 1:
+            flat = torch.cat([p.grad.reshape(-1) for p in params[1:]])
+            dist.all_reduce(npts.local_geo_features.grad)
+            dist.all_reduce(flat)
 
     def step(x, t):
         zero_grads()
         out = npts.query_sdf(x, dec, t, True, True)
         out["sdf"].backward(ones)
-        if world > 1:  # data-parallel exchange step: feature-table + decoder gradients
-            flat = torch.cat([p.grad.reshape(-1) for p in params[1:]])
-            dist.all_reduce(npts.local_geo_features.grad)
-            dist.all_reduce(flat)
+        exchange_grads()
         return out["sdf"]
 
     def barrier():
@@ -457,10 +482,7 @@ def main():
                 with torch.cuda.stream(back_stream):
                     out_h[c * cn:(c + 1) * cn].copy_(sdf_c, non_blocking=True)
                 sdf_c.record_stream(back_stream)
-            if world > 1:
-                flat = torch.cat([p.grad.reshape(-1) for p in params[1:]])
-                dist.all_reduce(npts.local_geo_features.grad)
-                dist.all_reduce(flat)
+            exchange_grads()
             main.wait_stream(back_stream)  # the step ends when its results are on the host
 
         for _ in range(max(5, args.warmup)):  # PCIe link and pinned pages warm
@@ -485,6 +507,7 @@ def main():
                         "sample": "%d queries of the same set, fwd+bwd, 3 steps after 1 warm-up, torch CPU fp32 "
                                   "restatement of the reference path" % min(args.cpu_sample, n)}
 
+    peer_err = peer.error() if peer is not None else 0
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
@@ -492,9 +515,18 @@ def main():
                 "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e,
                 "gpu_launches": LAUNCHES_PER_STEP * args.steps, "clocks": clocks}
         line["config"]["parallelism"] = "replicated map, queries sharded x%d%s" % (
-            world, ", NCCL all-reduce of feature+decoder grads" if world > 1 else "")
+            world, {"none": "", "nccl": ", NCCL all-reduce of feature+decoder grads",
+                    "peer": ", feature+decoder grads summed by one peer-memory kernel per rank over NVLink "
+                            "(pinq_peer_exchange)"}[exchange])
+        if peer is not None:
+            line["gpu_launches"] += args.steps
+            line["peer_exchange_error"] = peer_err
         print(json.dumps(line))
     if world > 1:
+        if peer is not None:
+            npts.feature_grad_sink = dec.grad_sink = None
+            dist.barrier()
+            peer.close()
         dist.destroy_process_group()
 
 

@@ -366,6 +366,48 @@ typedef struct pinq_mapping_args {
 
 int pinq_mapping_run(const pinq_mapping_args* args, int32_t iters, void* stream);
 
+/* ---- data-parallel exchange over NVLink peer memory ------------------------------------------
+ * Replaces what a data-parallel run has to do between `cur_loss.backward()` and `opt.step()` of Mapper.mapping
+ * (utils/mapper.py:572-573; optimizer: utils/tools.py:89-116): the sum of the feature-table and decoder gradients
+ * (and of the certainty increments, model/neural_points.py:637-642) and the max of local_point_ts_update (:643-645)
+ * over the ranks.  Every rank owns one "peer block" with the same layout -- [signal pad | payload] -- allocated by
+ * pinq_peer_alloc (cudaMalloc, so it can be exported), exported as a 64-byte cudaIpc handle, and mapped by the other
+ * ranks of the node (one process per GPU).  pinq_peer_exchange launches ONE kernel per rank:
+ *   barrier (flags in peer memory) -> this rank's 1/world slice: sum over all ranks' blocks (P2P loads)
+ *   [-> Adam on the slice, optimizer state held by the slice owner only] -> result stored into every rank's block
+ *   (P2P stores: summed gradients, or updated parameters + zeroed gradients) -> barrier.
+ * Ranks must call it in lock-step with the same epoch (1, 2, 3, ...).  A peer that does not arrive within timeout_ms
+ * sets the error word (pinq_peer_error_offset() bytes into the block, non-zero = failed) instead of hanging.
+ * These are the only entry points that allocate or that touch other devices. */
+#define PINQ_PEER_MAX 8
+#define PINQ_PEER_HANDLE_BYTES 64
+#define PINQ_PEER_MAX_GRID 256
+#define PINQ_PEER_PAD_BYTES 16384 /* flags [PINQ_PEER_MAX_GRID][8] uint32, error word, padding */
+int pinq_peer_alloc(int64_t bytes, void** d_out);          /* zero-filled; bytes >= PINQ_PEER_PAD_BYTES   */
+int pinq_peer_free(void* d_block);
+int pinq_peer_export(void* d_block, void* h_handle);       /* h_handle: PINQ_PEER_HANDLE_BYTES            */
+int pinq_peer_open(const void* h_handle, void** d_out);    /* in another process of the same node         */
+int pinq_peer_close(void* d_mapped);
+int64_t pinq_peer_error_offset(void);
+typedef struct pinq_peer_args {
+    int32_t rank, world;       /* world in {1, 2, 4, 8}                                                  */
+    void* block[PINQ_PEER_MAX]; /* block[r] = rank r's peer block as mapped in this process               */
+    int64_t sum_off, n_sum;    /* fp32 sum region: byte offset (16-byte aligned), element count (% 4)    */
+    int64_t max_off, n_max;    /* int64 max region: byte offset (16-byte aligned), element count (% 2)   */
+    uint32_t epoch;            /* call counter, identical on every rank, starting at 1                   */
+    int32_t grid;              /* CTAs (<= PINQ_PEER_MAX_GRID, identical on every rank); 0 = 128         */
+    float timeout_ms;          /* 0 = 5000                                                               */
+    /* fused optimizer (n_adam > 0): the first n_adam elements of the sum region are the gradients of the
+     * n_adam parameters at param_off of the same block; exp_avg / exp_avg_sq are LOCAL arrays of n_adam
+     * floats of which only this rank's slice is used; gradients come back zeroed. */
+    int64_t param_off, n_adam;
+    float* exp_avg;
+    float* exp_avg_sq;
+    float lr, beta1, beta2, adam_eps;
+    int32_t adam_step;         /* 1-based                                                                */
+} pinq_peer_args;
+int pinq_peer_exchange(const pinq_peer_args* args, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

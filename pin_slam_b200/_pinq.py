@@ -62,6 +62,16 @@ class MappingArgs(C.Structure):
                 ("weight_decay", _f32)]
 
 
+PEER_MAX, PEER_HANDLE_BYTES, PEER_PAD_BYTES, PEER_MAX_GRID = 8, 64, 16384, 256
+
+
+class PeerArgs(C.Structure):
+    _fields_ = [("rank", _i32), ("world", _i32), ("block", _vp * PEER_MAX), ("sum_off", _i64), ("n_sum", _i64),
+                ("max_off", _i64), ("n_max", _i64), ("epoch", _u32), ("grid", _i32), ("timeout_ms", _f32),
+                ("param_off", _i64), ("n_adam", _i64), ("exp_avg", _vp), ("exp_avg_sq", _vp), ("lr", _f32), ("beta1", _f32),
+                ("beta2", _f32), ("adam_eps", _f32), ("adam_step", _i32)]
+
+
 # name -> (restype, argtypes); mirrors include/pinq.h one to one
 SIGNATURES = {
     "pinq_last_error": (C.c_char_p, []),
@@ -103,6 +113,13 @@ SIGNATURES = {
     "pinq_stencil_masks_build": (C.c_int, [_vp, _i32, _i32, _vp, _vp]),
     "pinq_tracking_step": (C.c_int, [C.POINTER(TrackingArgs), C.POINTER(_f32), _vp]),
     "pinq_mapping_run": (C.c_int, [C.POINTER(MappingArgs), _i32, _vp]),
+    "pinq_peer_alloc": (C.c_int, [_i64, C.POINTER(_vp)]),
+    "pinq_peer_free": (C.c_int, [_vp]),
+    "pinq_peer_export": (C.c_int, [_vp, _vp]),
+    "pinq_peer_open": (C.c_int, [_vp, C.POINTER(_vp)]),
+    "pinq_peer_close": (C.c_int, [_vp]),
+    "pinq_peer_error_offset": (_i64, []),
+    "pinq_peer_exchange": (C.c_int, [C.POINTER(PeerArgs), _vp]),
 }
 
 _lib = None

@@ -681,13 +681,25 @@ class _FusedSDFFn(torch.autograd.Function):
         b.perm = P.ptr(perm)
         b.grad_sdf = P.ptr(g)
         g_feats = gW1 = gb1 = gW2 = gb2 = None
+        # gradient sinks (data-parallel runs, parallel.PeerExchange): the kernel accumulates straight into caller-owned
+        # buffers -- views of the rank's peer block -- and autograd sees no gradient for those inputs (p.grad stays None)
+        f_sink = getattr(npts, "feature_grad_sink", None)
+        d_sink = getattr(decoder, "grad_sink", None)
         if ctx.needs_input_grad[3]:
-            g_feats = torch.zeros_like(feats)
-            b.grad_features = P.ptr(g_feats)
+            if f_sink is not None:
+                if f_sink.shape != feats.shape or f_sink.dtype != torch.float32:
+                    raise P.PinqError("feature_grad_sink must be a float32 tensor shaped like local_geo_features")
+                b.grad_features = P.ptr(f_sink)
+            else:
+                g_feats = torch.zeros_like(feats)
+                b.grad_features = P.ptr(g_feats)
         if any(ctx.needs_input_grad[i] for i in (4, 5, 6, 7)):  # decoder not frozen (hazard H11)
             W1, b1, W2, b2 = decoder.fused_params()
-            gW1, gb1, gW2, gb2 = (torch.zeros_like(t) for t in (W1, b1, W2, b2))
-            b.grad_W1, b.grad_b1, b.grad_W2, b.grad_b2 = P.ptr(gW1), P.ptr(gb1), P.ptr(gW2), P.ptr(gb2)
+            if d_sink is not None:
+                b.grad_W1, b.grad_b1, b.grad_W2, b.grad_b2 = (P.ptr(t) for t in d_sink)
+            else:
+                gW1, gb1, gW2, gb2 = (torch.zeros_like(t) for t in (W1, b1, W2, b2))
+                b.grad_W1, b.grad_b1, b.grad_W2, b.grad_b2 = P.ptr(gW1), P.ptr(gb1), P.ptr(gW2), P.ptr(gb2)
         P.check(lib.pinq_query_fused_bwd(b, P.stream()))
         g_x = g.unsqueeze(-1) * dx if ctx.needs_input_grad[2] else None
         return (None, None, g_x, g_feats, gW1, gb1, gW2, gb2, None, None, None, None, None, None)

@@ -8,7 +8,10 @@ torch.distributed (NCCL over NVLink on the box, gloo in the CPU tests).
   after which every rank applies the identical Adam step (replicated optimiser, no parameter broadcast).
 * mesher grid: ranks evaluate disjoint linear ranges of the grid -- no collective (utils/mesher.py here).
 
-Nothing below touches CUDA directly, so the exchange logic is testable with gloo on CPU tensors.
+The NCCL form of the exchange (`exchange_gradients`) touches no CUDA API, so its logic is testable with gloo on CPU
+tensors.  On the GPU box the exchange is `PeerExchange`: gradients accumulate straight into a cudaIpc-shared "peer block"
+and ONE kernel per rank (`pinq_peer_exchange`, csrc/peer.cu) does barrier -> owner-sliced reduction over P2P loads
+[-> Adam] -> P2P stores -> barrier over NVLink/NVSwitch; NCCL stays as the A/B partner (`PINQ_EXCHANGE=nccl`).
 """
 from __future__ import annotations
 
@@ -68,7 +71,7 @@ def exchange_gradients(params, sum_buffers=(), max_buffers=(), group=None):
     return calls
 
 
-def dp_mapping_iteration(mapper, coord, sdf_label, ts, weight, opt, group=None):
+def dp_mapping_iteration(mapper, coord, sdf_label, ts, weight, opt, group=None, peer=None):
     """One data-parallel iteration of Mapper.mapping() (reference: utils/mapper.py:443-573) over a GLOBAL batch
     that every rank holds (indices are drawn with a shared seed): slice -> fused fwd/bwd -> exchange -> Adam.
     The per-rank loss is normalised by the GLOBAL counts so that the summed gradients equal the single-GPU
@@ -92,6 +95,29 @@ def dp_mapping_iteration(mapper, coord, sdf_label, ts, weight, opt, group=None):
             loss = loss + cfg.weight_e * ((g.norm(2, dim=-1) - 1.0) ** 2).sum() / n_dec_global
     params = [p for grp in opt.param_groups for p in grp["params"]]
     opt.zero_grad(set_to_none=True)
+    if peer is not None:  # gradients accumulate in the peer block; one kernel sums them over NVLink (csrc/peer.cu)
+        mp = MappingPeer(peer, npts.local_geo_features.shape[0], npts.local_geo_features.shape[1], mapper.geo_mlp)
+        mp.attach(npts, mapper.geo_mlp)
+        try:
+            loss.backward()
+        finally:
+            MappingPeer.detach(npts, mapper.geo_mlp)
+        mp.cert_delta.copy_(npts.local_point_certainties - cert_before)
+        mp.ts_update.copy_(npts.local_point_ts_update)
+        peer.exchange(n_sum=mp.n_sum, n_max=mp.n_max)
+        npts.local_point_certainties = cert_before + mp.cert_delta
+        npts.local_point_ts_update.copy_(mp.ts_update)
+        fused = list(mapper.geo_mlp.fused_params())
+        for p in params:
+            if p is npts.local_geo_features:
+                p.grad = mp.grad_features
+            else:
+                for t, g in zip(fused, mp.grad_decoder):
+                    if p is t:
+                        p.grad = g
+        opt.step()
+        opt.zero_grad(set_to_none=True)  # the views die with this iteration's carve
+        return loss.detach()
     loss.backward()
     for p in params:  # a rank whose slice never touched a parameter still has to join the collective
         if p.requires_grad and p.grad is None and p.numel() > 0:
@@ -101,3 +127,178 @@ def dp_mapping_iteration(mapper, coord, sdf_label, ts, weight, opt, group=None):
     npts.local_point_certainties = cert_before + delta
     opt.step()
     return loss.detach()
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# Peer-memory exchange (include/pinq.h "data-parallel exchange over NVLink peer memory")
+def _align(n: int, a: int) -> int:
+    return (n + a - 1) // a * a
+
+
+class _RawCuda:
+    """A bare device allocation seen through __cuda_array_interface__ (torch.as_tensor keeps this object alive)."""
+
+    def __init__(self, ptr: int, nbytes: int):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 2}
+
+
+class PeerLayout:
+    """Byte layout of a peer block: [pad | fp32 sum region | (fp32 parameter region) | int64 max region]."""
+
+    def __init__(self, n_sum: int, n_max: int = 0, n_param: int = 0):
+        from . import _pinq as P
+        self.n_sum, self.n_max, self.n_param = _align(n_sum, 4), _align(n_max, 2), _align(n_param, 4)
+        self.sum_off = P.PEER_PAD_BYTES
+        self.param_off = self.sum_off + 4 * self.n_sum
+        self.max_off = _align(self.param_off + 4 * self.n_param, 16)
+        self.nbytes = _align(self.max_off + 8 * self.n_max, 256)
+
+
+class PeerExchange:
+    """One peer block per rank, mapped into every rank of the node.
+
+    `ranks_on_this_device` > 1 builds that many blocks in ONE process on one GPU and runs their kernels on separate
+    streams: the single-GPU form used by the GPU tests (same kernel, same flags, same P2P code path minus the link)."""
+
+    def __init__(self, layout: PeerLayout, device, group=None, simulate_world: int = 0, grid: int = 0, timeout_ms: float = 0.0):
+        import ctypes as C
+        from . import _pinq as P
+        self.P, self.lib, self.layout, self.device = P, P.load(), layout, torch.device(device)
+        self.grid, self.timeout_ms, self.epoch = int(grid), float(timeout_ms), 0
+        self.simulated = simulate_world > 0
+        self._mapped, self._owned = [], []
+        with torch.cuda.device(self.device):
+            if self.simulated:
+                self.rank, self.world = 0, int(simulate_world)
+                self.blocks = []
+                for _ in range(self.world):
+                    ptr = C.c_void_p()
+                    P.check(self.lib.pinq_peer_alloc(layout.nbytes, C.byref(ptr)))
+                    self._owned.append(ptr.value)
+                    self.blocks.append(ptr.value)
+                self.streams = [torch.cuda.Stream(device=self.device) for _ in range(self.world)]
+            else:
+                self.rank, self.world = world_info(group)
+                ptr = C.c_void_p()
+                P.check(self.lib.pinq_peer_alloc(layout.nbytes, C.byref(ptr)))
+                self._owned.append(ptr.value)
+                handle = (C.c_ubyte * P.PEER_HANDLE_BYTES)()
+                P.check(self.lib.pinq_peer_export(ptr, handle))
+                handles = [None] * self.world
+                if self.world > 1:
+                    dist.all_gather_object(handles, bytes(handle), group=group)
+                self.blocks = []
+                for r in range(self.world):
+                    if r == self.rank:
+                        self.blocks.append(ptr.value)
+                        continue
+                    buf = (C.c_ubyte * P.PEER_HANDLE_BYTES).from_buffer_copy(handles[r])
+                    mapped = C.c_void_p()
+                    P.check(self.lib.pinq_peer_open(buf, C.byref(mapped)))
+                    self._mapped.append(mapped.value)
+                    self.blocks.append(mapped.value)
+        self._views = [torch.as_tensor(_RawCuda(b, layout.nbytes), device=self.device)
+                       for b in (self.blocks if self.simulated else [self.blocks[self.rank]])]
+
+    # -- typed views of a block's regions (this rank's block; `r` selects the block in the simulated form)
+    def _view(self, r=None):
+        return self._views[r if self.simulated else 0]
+
+    def sum_region(self, r=None):
+        L = self.layout
+        return self._view(r)[L.sum_off:L.sum_off + 4 * L.n_sum].view(torch.float32)
+
+    def param_region(self, r=None):
+        L = self.layout
+        return self._view(r)[L.param_off:L.param_off + 4 * L.n_param].view(torch.float32)
+
+    def max_region(self, r=None):
+        L = self.layout
+        return self._view(r)[L.max_off:L.max_off + 8 * L.n_max].view(torch.int64)
+
+    def _args(self, rank, adam):
+        P, L = self.P, self.layout
+        a = P.PeerArgs()
+        a.rank, a.world = rank, self.world
+        for r, b in enumerate(self.blocks):
+            a.block[r] = b
+        a.sum_off, a.n_sum, a.max_off, a.n_max = L.sum_off, self._n_sum, L.max_off, self._n_max
+        a.epoch, a.grid, a.timeout_ms = self.epoch, self.grid, self.timeout_ms
+        if adam is not None:
+            a.param_off, a.n_adam = L.param_off, L.n_param
+            a.exp_avg, a.exp_avg_sq = P.ptr(adam["exp_avg"][rank if self.simulated else 0]), P.ptr(adam["exp_avg_sq"][rank if self.simulated else 0])
+            a.lr, a.beta1, a.beta2, a.adam_eps, a.adam_step = adam["lr"], adam["beta1"], adam["beta2"], adam["eps"], adam["step"]
+        return a
+
+    def exchange(self, adam=None, n_sum=None, n_max=None):
+        """Sum / max the regions over the ranks (and, with `adam`, apply the optimizer step on the owned slice and
+        broadcast the parameters).  `n_sum` / `n_max` restrict the call to a prefix of the regions (identical on every
+        rank).  Asynchronous on the current stream; every rank calls it in lock-step."""
+        P = self.P
+        self.epoch += 1
+        self._n_sum = self.layout.n_sum if n_sum is None else _align(int(n_sum), 4)
+        self._n_max = self.layout.n_max if n_max is None else _align(int(n_max), 2)
+        if self._n_sum > self.layout.n_sum or self._n_max > self.layout.n_max:
+            raise P.PinqError("exchange larger than the peer block's regions")
+        if not self.simulated:
+            P.check(self.lib.pinq_peer_exchange(self._args(self.rank, adam), P.stream()))
+            return
+        cur = torch.cuda.current_stream(self.device)
+        for r, st in enumerate(self.streams):  # the "ranks" must be co-resident: small grids on separate streams
+            st.wait_stream(cur)
+            P.check(self.lib.pinq_peer_exchange(self._args(r, adam), st.cuda_stream))
+        for st in self.streams:
+            cur.wait_stream(st)
+
+    def error(self) -> int:
+        """Non-zero if a barrier timed out in any exchange so far (synchronises)."""
+        off = int(self.lib.pinq_peer_error_offset())
+        return int(max(int(v[off:off + 4].view(torch.int32).item()) & 0x7fffffff for v in self._views))
+
+    def close(self):
+        self._views = []
+        for m in self._mapped:
+            self.lib.pinq_peer_close(m)
+        for o in self._owned:
+            self.lib.pinq_peer_free(o)
+        self._mapped, self._owned = [], []
+
+
+class MappingPeer:
+    """Carves the sum / max regions of a PeerExchange for one data-parallel mapping iteration:
+    sum = [d loss / d local_geo_features (M+1)*F | dW1 | db1 | dW2 | db2 | pad | certainty increments M], max = [ts_update M]."""
+
+    def __init__(self, peer: PeerExchange, feature_rows: int, feature_dim: int, decoder, r=None):
+        self.peer = peer
+        sumr, maxr = peer.sum_region(r), peer.max_region(r)
+        self._sum = sumr
+        nf = feature_rows * feature_dim
+        self.grad_features = sumr[:nf].view(feature_rows, feature_dim)
+        off, self.grad_decoder = nf, []
+        for t in decoder.fused_params():
+            self.grad_decoder.append(sumr[off:off + t.numel()].view(t.shape))
+            off += t.numel()
+        off = _align(off, 4)
+        m = feature_rows - 1
+        self.cert_delta = sumr[off:off + m]
+        self.n_sum = off + m
+        self.ts_update = maxr[:m]
+        self.n_max = m
+        if self.n_sum > peer.layout.n_sum or m > peer.layout.n_max:
+            raise peer.P.PinqError("peer block too small for this local map")
+
+    @staticmethod
+    def capacity(feature_rows: int, feature_dim: int, decoder):
+        nd = sum(t.numel() for t in decoder.fused_params())
+        return PeerLayout(_align(feature_rows * feature_dim + nd, 4) + feature_rows, feature_rows)
+
+    def attach(self, npts, decoder):
+        """Zeroes the used prefix and points the fused backward's gradient sinks at it."""
+        self._sum[:self.n_sum].zero_()
+        npts.feature_grad_sink = self.grad_features
+        decoder.grad_sink = tuple(self.grad_decoder)
+
+    @staticmethod
+    def detach(npts, decoder):
+        npts.feature_grad_sink = None
+        decoder.grad_sink = None
