@@ -21,7 +21,6 @@ import ctypes
 import json
 import os
 import subprocess
-import threading
 import sys
 import time
 
@@ -116,66 +115,58 @@ def mean_nonempty_slots(npts, q, sample=100_000):
     return float((npts._table[h] >= 0).sum(1).float().mean())
 
 
+_CLOCK_CHILD = r"""
+import sys, time
+import pynvml as nv
+nv.nvmlInit()
+h = nv.nvmlDeviceGetHandleByIndex(int(sys.argv[1]))
+period = float(sys.argv[2])
+mx = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+bits = (("hw_slowdown", nv.nvmlClocksEventReasonHwSlowdown), ("hw_thermal_slowdown", nv.nvmlClocksEventReasonHwThermalSlowdown),
+        ("sw_thermal_slowdown", nv.nvmlClocksEventReasonSwThermalSlowdown), ("sw_power_cap", nv.nvmlClocksEventReasonSwPowerCap))
+print("ready", mx, flush=True)
+while True:
+    t = time.time()
+    sm = nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)
+    r = int(nv.nvmlDeviceGetCurrentClocksEventReasons(h))
+    print(t, sm, "|".join(n for n, b in bits if r & int(b)), flush=True)
+    time.sleep(period)
+"""
+
+
 class ClockSampler:
-    """SM clock and throttle reasons sampled DURING the timed region: an NVML thread polling every ~2 ms (the timed region
-    of the default run is tens of milliseconds, shorter than nvidia-smi's fastest loop), plus explicit `sample()` calls from
-    the timing loop so that at least one reading falls inside it; nvidia-smi -lms as the fallback when NVML is absent."""
-    QUERY = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
-             "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
-             "clocks_event_reasons.sw_power_cap")
+    """SM clock and throttle reasons sampled DURING the timed region by a separate process polling NVML every few ms
+    (time-stamped readings, filtered to the region afterwards).  A separate process because NVML calls made from the
+    benchmark's own process were measured to stall its kernel launches (an in-process polling thread cost 5 % at 2 ms and
+    whole milliseconds per step on a 2-GPU box); the timed region of the default run is tens of milliseconds, shorter than
+    nvidia-smi's fastest loop, hence NVML rather than `nvidia-smi -lms`."""
 
     def __init__(self, gpu_index):
-        self.proc = self.nv = self.handle = self.thread = None
-        self.sm, self.mx, self.reasons = [], [], set()
-        self._stop = False
+        self.proc, self.mx, self.t0, self.t1 = None, None, None, None
+        period = float(os.environ.get("PINQ_CLOCK_POLL_MS", "4")) * 1e-3
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        phys = int(vis.split(",")[gpu_index]) if vis and all(t.strip().isdigit() for t in vis.split(",")) else gpu_index
         try:
-            import pynvml
-            pynvml.nvmlInit()
-            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
-            phys = int(vis.split(",")[gpu_index]) if vis and all(t.strip().isdigit() for t in vis.split(",")) else gpu_index
-            self.handle = pynvml.nvmlDeviceGetHandleByIndex(phys)
-            self.nv = pynvml
-            self.mx.append(float(pynvml.nvmlDeviceGetMaxClockInfo(self.handle, pynvml.NVML_CLOCK_SM)))
-            self.thread = threading.Thread(target=self._loop, daemon=True)
-            self.thread.start()
+            env = dict(os.environ)
+            env.pop("CUDA_VISIBLE_DEVICES", None)
+            self.proc = subprocess.Popen([sys.executable, "-c", _CLOCK_CHILD, str(phys), str(period)], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True, env=env)
+            first = self.proc.stdout.readline().split()  # blocks until NVML is up: start-up stays outside the timed region
+            if len(first) != 2 or first[0] != "ready":
+                raise RuntimeError("clock sampler did not start")
+            self.mx = float(first[1])
         except Exception:
-            self.nv = None
-            try:
-                self.proc = subprocess.Popen(["nvidia-smi", "-i", str(gpu_index), "--query-gpu=" + self.QUERY,
-                                              "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
-                                             stderr=subprocess.DEVNULL, text=True)
-            except Exception:
-                self.proc = None
+            if self.proc is not None:
+                self.proc.kill()
+            self.proc = None
 
-    def sample(self):
-        nv = self.nv
-        if nv is None:
-            return
-        try:
-            self.sm.append(float(nv.nvmlDeviceGetClockInfo(self.handle, nv.NVML_CLOCK_SM)))
-            r = int(nv.nvmlDeviceGetCurrentClocksEventReasons(self.handle))
-            for name, bit in (("hw_slowdown", nv.nvmlClocksEventReasonHwSlowdown),
-                              ("hw_thermal_slowdown", nv.nvmlClocksEventReasonHwThermalSlowdown),
-                              ("sw_thermal_slowdown", nv.nvmlClocksEventReasonSwThermalSlowdown),
-                              ("sw_power_cap", nv.nvmlClocksEventReasonSwPowerCap)):
-                if r & int(bit):
-                    self.reasons.add(name)
-        except Exception:
-            pass
+    def begin(self):
+        self.t0 = time.time()
 
-    def _loop(self):
-        while not self._stop:
-            self.sample()
-            time.sleep(0.002)
+    def end(self):
+        self.t1 = time.time()
 
     def stop(self):
-        if self.nv is not None:
-            self._stop = True
-            self.thread.join(timeout=2)
-            if not self.sm:
-                return None
-            return {"sm_mhz": float(np.median(self.sm)), "sm_max_mhz": float(max(self.mx)), "reasons": sorted(self.reasons),
-                    "samples": len(self.sm), "source": "nvml"}
         if self.proc is None:
             return None
         self.proc.terminate()
@@ -184,24 +175,22 @@ class ClockSampler:
         except Exception:
             self.proc.kill()
             return None
-        sm, mx, reasons = [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for line in out.strip().splitlines():
-            f = [t.strip() for t in line.split(",")]
-            if len(f) < 9:
-                continue
+        sm, reasons = [], set()
+        for line in out.splitlines():
+            f = line.split()
             try:
-                sm.append(float(f[1]))
-                mx.append(float(f[2]))
-            except ValueError:
+                t, clk = float(f[0]), float(f[1])
+            except (ValueError, IndexError):
                 continue
-            for name, v in zip(names, f[5:9]):
-                if v.lower().startswith("active"):
-                    reasons.add(name)
+            if self.t0 is not None and self.t1 is not None and not (self.t0 <= t <= self.t1):
+                continue
+            sm.append(clk)
+            if len(f) > 2:
+                reasons.update(x for x in f[2].split("|") if x)
         if not sm:
             return None
-        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons),
-                "samples": len(sm), "source": "nvidia-smi"}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": self.mx, "reasons": sorted(reasons), "samples": len(sm),
+                "source": "nvml, separate process, readings inside the timed region"}
 
 
 # ------------------------------------------------------------------------------------------------
@@ -345,7 +334,11 @@ def main():
         for p in params:
             p.grad = None
 
+    skip_exchange = [False]
+
     def exchange_grads():
+        if skip_exchange[0]:
+            return
         if peer is not None:
             peer.exchange(n_sum=n_ex, n_max=0)
         elif world > 1:
@@ -367,16 +360,18 @@ def main():
 
     for _ in range(max(args.warmup, 3)):
         step(q, ts)
-    barrier()
-    sampler = ClockSampler(local_rank) if rank == 0 else None
+    sampler = ClockSampler(local_rank) if rank == 0 else None  # NVML start-up (tens of ms) stays outside the timed region
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    if sampler:
+        sampler.begin()
     ev0.record()
     for i in range(args.steps):
         step(q, ts)
-        if sampler and i == args.steps // 2:
-            sampler.sample()  # the host runs ahead of the device: this reading is taken with the queue full
     ev1.record()
     barrier()
+    if sampler:
+        sampler.end()
     ms_total = ev0.elapsed_time(ev1)
     clocks = sampler.stop() if sampler else None
     t = torch.tensor([ms_total], device=dev, dtype=torch.float64)
@@ -384,6 +379,40 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms_step = float(t.item()) / args.steps
     value = world * n / (ms_step * 1e-3)
+
+    # ---- diagnostics (N > 1): every rank's own time for the timed region, and the step without its exchange
+    rank_ms = no_exchange_ms = None
+    if world > 1:
+        allt = [torch.zeros(1, device=dev, dtype=torch.float64) for _ in range(world)]
+        dist.all_gather(allt, torch.tensor([ms_total / args.steps], device=dev, dtype=torch.float64))
+        rank_ms = [float(x.item()) for x in allt]
+        skip_exchange[0] = True
+        barrier()
+        ev0.record()
+        for _ in range(args.steps):
+            step(q, ts)
+        ev1.record()
+        barrier()
+        tn = torch.tensor([ev0.elapsed_time(ev1) / args.steps], device=dev, dtype=torch.float64)
+        dist.all_reduce(tn, op=dist.ReduceOp.MAX)
+        no_exchange_ms = float(tn.item())
+        skip_exchange[0] = False
+
+    # ---- the exchange step alone (N > 1): zeroed gradient block -> summed block, max over ranks
+    exchange_ms = None
+    if world > 1:
+        if peer is None:
+            step(q, ts)  # leaves p.grad populated for the NCCL form
+        barrier()
+        xe0, xe1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        xe0.record()
+        for _ in range(10):
+            exchange_grads()
+        xe1.record()
+        barrier()
+        tx = torch.tensor([xe0.elapsed_time(xe1) / 10], device=dev, dtype=torch.float64)
+        dist.all_reduce(tx, op=dist.ReduceOp.MAX)
+        exchange_ms = float(tx.item())
 
     # ---- per-kernel timing (CUDA events on the launching stream, recorded by the library between its kernels)
     K = 6
@@ -521,6 +550,10 @@ def main():
         if peer is not None:
             line["gpu_launches"] += args.steps
             line["peer_exchange_error"] = peer_err
+        if exchange_ms is not None:
+            line["exchange_ms"] = exchange_ms
+            line["ms_per_step_by_rank"] = rank_ms
+            line["ms_per_step_without_exchange"] = no_exchange_ms
         print(json.dumps(line))
     if world > 1:
         if peer is not None:

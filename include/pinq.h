@@ -395,7 +395,7 @@ typedef struct pinq_peer_args {
     int64_t sum_off, n_sum;    /* fp32 sum region: byte offset (16-byte aligned), element count (% 4)    */
     int64_t max_off, n_max;    /* int64 max region: byte offset (16-byte aligned), element count (% 2)   */
     uint32_t epoch;            /* call counter, identical on every rank, starting at 1                   */
-    int32_t grid;              /* CTAs (<= PINQ_PEER_MAX_GRID, identical on every rank); 0 = 128         */
+    int32_t grid;              /* CTAs (<= PINQ_PEER_MAX_GRID, identical on every rank); 0 = 148         */
     float timeout_ms;          /* 0 = 5000                                                               */
     /* fused optimizer (n_adam > 0): the first n_adam elements of the sum region are the gradients of the
      * n_adam parameters at param_off of the same block; exp_avg / exp_avg_sq are LOCAL arrays of n_adam

@@ -69,39 +69,52 @@ __global__ void __launch_bounds__(kPeerThreads) k_peer_exchange(PeerDev a) {
 
     const int64_t tid = (int64_t)blockIdx.x * kPeerThreads + threadIdx.x;
     const int64_t nthr = (int64_t)gridDim.x * kPeerThreads;
-    {   // fp32 sum region: this rank owns float4 [lo, hi)
+    {   // fp32 sum region: this rank owns float4 [lo, hi).  U elements per thread and trip, all W x U loads issued before the
+        // first add: the link wants megabytes in flight (latency ~2 us x 0.8 TB/s), not one 16-byte load per thread.
+        constexpr int U = W >= 8 ? 2 : (W == 4 ? 4 : 8);
         const int64_t lo = a.nsum4 * a.rank / W, hi = a.nsum4 * (a.rank + 1) / W;
-        for (int64_t i = lo + tid; i < hi; i += nthr) {
-            float4 v[W];
+        for (int64_t i0 = lo + tid; i0 < hi; i0 += nthr * U) {
+            float4 v[U][W];
 #pragma unroll
-            for (int p = 0; p < W; ++p) v[p] = __ldcg(reinterpret_cast<const float4*>(a.block[p]) + a.sum_off4 + i);
-            float4 s = v[0];  // fixed rank order: the sum does not depend on which rank owns the slice
+            for (int u = 0; u < U; ++u) {
+                const int64_t i = i0 + u * nthr;
+                if (i < hi) {
 #pragma unroll
-            for (int p = 1; p < W; ++p) { s.x += v[p].x; s.y += v[p].y; s.z += v[p].z; s.w += v[p].w; }
-            if (ADAM && i < a.nadam4) {
-                // torch.optim.Adam single-tensor arithmetic (k_adam, gn.cu) on the owned slice; state lives on the owner only
-                float4 m = reinterpret_cast<float4*>(a.exp_avg)[i], q = reinterpret_cast<float4*>(a.exp_avg_sq)[i];
-                float4 w = __ldcg(reinterpret_cast<const float4*>(a.block[a.rank]) + a.par_off4 + i);
-                const float g[4] = {s.x, s.y, s.z, s.w};
-                float* mm = &m.x; float* qq = &q.x; float* ww = &w.x;
-#pragma unroll
-                for (int c = 0; c < 4; ++c) {
-                    mm[c] = mm[c] + (g[c] - mm[c]) * (1.f - a.beta1);
-                    qq[c] = qq[c] * a.beta2 + (1.f - a.beta2) * g[c] * g[c];
-                    const float denom = sqrtf(qq[c]) / a.bc2_sqrt + a.eps;
-                    ww[c] = ww[c] - a.step_size * (mm[c] / denom);
+                    for (int p = 0; p < W; ++p) v[u][p] = __ldcg(reinterpret_cast<const float4*>(a.block[p]) + a.sum_off4 + i);
                 }
-                reinterpret_cast<float4*>(a.exp_avg)[i] = m;
-                reinterpret_cast<float4*>(a.exp_avg_sq)[i] = q;
-                const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+            }
 #pragma unroll
-                for (int p = 0; p < W; ++p) {
-                    __stcg(reinterpret_cast<float4*>(a.block[p]) + a.par_off4 + i, w);  // parameter broadcast
-                    __stcg(reinterpret_cast<float4*>(a.block[p]) + a.sum_off4 + i, z);  // zero_grad on every replica
+            for (int u = 0; u < U; ++u) {
+                const int64_t i = i0 + u * nthr;
+                if (i >= hi) break;
+                float4 s = v[u][0];  // fixed rank order: the sum does not depend on which rank owns the slice
+#pragma unroll
+                for (int p = 1; p < W; ++p) { s.x += v[u][p].x; s.y += v[u][p].y; s.z += v[u][p].z; s.w += v[u][p].w; }
+                if (ADAM && i < a.nadam4) {
+                    // torch.optim.Adam single-tensor arithmetic (k_adam, gn.cu) on the owned slice; state lives on the owner only
+                    float4 m = reinterpret_cast<float4*>(a.exp_avg)[i], q = reinterpret_cast<float4*>(a.exp_avg_sq)[i];
+                    float4 w = __ldcg(reinterpret_cast<const float4*>(a.block[a.rank]) + a.par_off4 + i);
+                    const float g[4] = {s.x, s.y, s.z, s.w};
+                    float* mm = &m.x; float* qq = &q.x; float* ww = &w.x;
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) {
+                        mm[c] = mm[c] + (g[c] - mm[c]) * (1.f - a.beta1);
+                        qq[c] = qq[c] * a.beta2 + (1.f - a.beta2) * g[c] * g[c];
+                        const float denom = sqrtf(qq[c]) / a.bc2_sqrt + a.eps;
+                        ww[c] = ww[c] - a.step_size * (mm[c] / denom);
+                    }
+                    reinterpret_cast<float4*>(a.exp_avg)[i] = m;
+                    reinterpret_cast<float4*>(a.exp_avg_sq)[i] = q;
+                    const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+                    for (int p = 0; p < W; ++p) {
+                        __stcg(reinterpret_cast<float4*>(a.block[p]) + a.par_off4 + i, w);  // parameter broadcast
+                        __stcg(reinterpret_cast<float4*>(a.block[p]) + a.sum_off4 + i, z);  // zero_grad on every replica
+                    }
+                } else {
+#pragma unroll
+                    for (int p = 0; p < W; ++p) __stcg(reinterpret_cast<float4*>(a.block[p]) + a.sum_off4 + i, s);
                 }
-            } else {
-#pragma unroll
-                for (int p = 0; p < W; ++p) __stcg(reinterpret_cast<float4*>(a.block[p]) + a.sum_off4 + i, s);
             }
         }
     }
@@ -199,7 +212,7 @@ int pinq_peer_exchange(const pinq_peer_args* a, void* stream) {
                      "adam region: a multiple of 4 leading elements of the sum region, parameters 16-byte aligned");
         PINQ_REQUIRE(a->exp_avg && a->exp_avg_sq && a->adam_step >= 1, "adam state");
     }
-    int grid = a->grid > 0 ? a->grid : 128;
+    int grid = a->grid > 0 ? a->grid : 148;  // one CTA per SM: all of them resident, which the flag barrier needs
     PINQ_REQUIRE(grid <= PINQ_PEER_MAX_GRID, "grid too large for the signal pad");
     PeerDev d{};
     for (int p = 0; p < a->world; ++p) d.block[p] = reinterpret_cast<float*>(a->block[p]);
