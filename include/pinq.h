@@ -362,6 +362,16 @@ typedef struct pinq_mapping_args {
     pinq_adam_tensor tensors[8];
     int32_t tensor_count;
     float lr, beta1, beta2, adam_eps, weight_decay;
+    /* data-parallel form (all zero / NULL = one device).  The batch above is this rank's contiguous slice
+     * [shard_first, shard_first + bs) of a GLOBAL batch of global_bs samples drawn with one shared seed: the losses are
+     * normalised by the global counts and the eikonal subset is the global batch's x[::decimation], so the sum of the
+     * ranks' gradients is the single-device gradient.  With `peer` (a HOST pointer, see pinq_peer_args below) the local
+     * Adam launch is replaced by pinq_peer_exchange with the fused optimizer: tensors[].param / .grad must then be the
+     * param / sum regions of this rank's peer block in one common order, epoch = peer->epoch + iteration, the
+     * caller zeroes peer->exp_avg / exp_avg_sq, and lr / betas / eps are taken from this struct. */
+    int32_t global_bs;
+    int32_t shard_first;
+    const struct pinq_peer_args* peer;
 } pinq_mapping_args;
 
 int pinq_mapping_run(const pinq_mapping_args* args, int32_t iters, void* stream);

@@ -51,17 +51,6 @@ class AdamTensor(C.Structure):
 
 EIK_ALL, EIK_SURFACE, EIK_FREESPACE = 0, 1, 2
 
-
-class MappingArgs(C.Structure):
-    _fields_ = [("query", QueryArgs), ("bwd", BwdArgs), ("pool_xyz", _vp), ("pool_label", _vp), ("pool_weight", _vp),
-                ("pool_ts", _vp), ("draws_hist", _vp), ("draws_new", _vp), ("new_idx", _vp), ("bs", _i32), ("bs_new", _i32),
-                ("decimation", _i32), ("eik_mode", _i32), ("weighted", _i32), ("eps_step", _f32), ("sigma", _f32),
-                ("weight_e", _f32), ("surface_range", _f32), ("batch_xyz", _vp), ("batch_ts", _vp), ("batch_label", _vp),
-                ("batch_weight", _vp), ("grad_sdf", _vp), ("loss", _vp), ("eik_count", _vp), ("tensors", AdamTensor * 8),
-                ("tensor_count", _i32), ("lr", _f32), ("beta1", _f32), ("beta2", _f32), ("adam_eps", _f32),
-                ("weight_decay", _f32)]
-
-
 PEER_MAX, PEER_HANDLE_BYTES, PEER_PAD_BYTES, PEER_MAX_GRID = 8, 64, 16384, 256
 
 
@@ -70,6 +59,16 @@ class PeerArgs(C.Structure):
                 ("max_off", _i64), ("n_max", _i64), ("epoch", _u32), ("grid", _i32), ("timeout_ms", _f32),
                 ("param_off", _i64), ("n_adam", _i64), ("exp_avg", _vp), ("exp_avg_sq", _vp), ("lr", _f32), ("beta1", _f32),
                 ("beta2", _f32), ("adam_eps", _f32), ("adam_step", _i32)]
+
+
+class MappingArgs(C.Structure):
+    _fields_ = [("query", QueryArgs), ("bwd", BwdArgs), ("pool_xyz", _vp), ("pool_label", _vp), ("pool_weight", _vp),
+                ("pool_ts", _vp), ("draws_hist", _vp), ("draws_new", _vp), ("new_idx", _vp), ("bs", _i32), ("bs_new", _i32),
+                ("decimation", _i32), ("eik_mode", _i32), ("weighted", _i32), ("eps_step", _f32), ("sigma", _f32),
+                ("weight_e", _f32), ("surface_range", _f32), ("batch_xyz", _vp), ("batch_ts", _vp), ("batch_label", _vp),
+                ("batch_weight", _vp), ("grad_sdf", _vp), ("loss", _vp), ("eik_count", _vp), ("tensors", AdamTensor * 8),
+                ("tensor_count", _i32), ("lr", _f32), ("beta1", _f32), ("beta2", _f32), ("adam_eps", _f32),
+                ("weight_decay", _f32), ("global_bs", _i32), ("shard_first", _i32), ("peer", C.POINTER(PeerArgs))]
 
 
 # name -> (restype, argtypes); mirrors include/pinq.h one to one

@@ -18,7 +18,7 @@ struct GatherParams {
     const int64_t* draws_hist;  // this iteration's row
     const int64_t* draws_new;
     const int64_t* new_idx;
-    int bs, bs_hist, ng, decim, eik_mode;
+    int bs, bs_hist, ng, decim, eik_mode, eik_start;
     float eps, surface_range;
     float* xyz;
     int64_t* ts;
@@ -33,7 +33,8 @@ __device__ __forceinline__ int64_t pool_row(const GatherParams& p, int i) {
 }
 
 // One thread per query of the iteration's batch: [0, bs) the training samples, then six groups of ng points
-// x[::decim] +/- eps along x, y, z in the order mapper.py:697 concatenates them.
+// x[::decim] +/- eps along x, y, z in the order mapper.py:697 concatenates them (data-parallel form: the members of the
+// GLOBAL batch's x[::decim] that fall into this rank's slice, i.e. local rows eik_start, eik_start + decim, ...).
 __global__ void k_map_gather(GatherParams p) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     const int n = p.bs + 6 * p.ng;
@@ -47,7 +48,7 @@ __global__ void k_map_gather(GatherParams p) {
         const float lab = p.pool_label[r];
         p.label[i] = lab;
         p.weight[i] = fabsf(p.pool_weight[r]);
-        if (p.eik_mode != PINQ_EIK_ALL && p.decim > 0 && i % p.decim == 0) {
+        if (p.eik_mode != PINQ_EIK_ALL && p.decim > 0 && i % p.decim == 0) {  // (single device only: eik_start == 0)
             const bool surface = fabsf(lab) < p.surface_range;
             if (surface == (p.eik_mode == PINQ_EIK_SURFACE)) atomicAdd(p.eik_count, 1);
         }
@@ -55,7 +56,7 @@ __global__ void k_map_gather(GatherParams p) {
     }
     const int e = i - p.bs;
     const int group = e / p.ng, j = e - group * p.ng;
-    const int64_t r = pool_row(p, j * p.decim);
+    const int64_t r = pool_row(p, p.eik_start + j * p.decim);
     float v[3] = {p.pool_xyz[3 * r + 0], p.pool_xyz[3 * r + 1], p.pool_xyz[3 * r + 2]};
     const int axis = group >> 1;
     v[axis] = (group & 1) ? __fsub_rn(v[axis], p.eps) : __fadd_rn(v[axis], p.eps);
@@ -69,7 +70,8 @@ struct LossParams {
     const float* sdf;     // [bs + 6 ng]
     const float* label;   // [bs]
     const float* weight;  // [bs]
-    int bs, ng, decim, eik_mode, weighted;
+    int bs, ng, decim, eik_mode, weighted, eik_start;
+    int norm_bs, norm_ng;  // the GLOBAL batch's sample / eikonal counts (data-parallel form; = bs, ng on one device)
     float sigma, weight_e, two_eps, surface_range;
     const int32_t* eik_count;
     float* grad_sdf;
@@ -87,15 +89,15 @@ __global__ void k_map_loss_grad(LossParams p) {
         const float z = p.sdf[i] / p.sigma;
         const float t = sigmoidf_(p.label[i] / p.sigma);
         const float w = p.weighted ? p.weight[i] : 1.f;
-        p.grad_sdf[i] = ((sigmoidf_(z) - t) * w) * (1.f / (float)p.bs) / p.sigma;
+        p.grad_sdf[i] = ((sigmoidf_(z) - t) * w) * (1.f / (float)p.norm_bs) / p.sigma;
         const float mz = fmaxf(-z, 0.f);
         l_bce = w * ((1.f - t) * z + mz + logf(expf(-mz) + expf(-z - mz)));
     } else if (i < p.bs + p.ng) {
         const int j = i - p.bs;
         bool selected = true;
-        int count = p.ng;
+        int count = p.norm_ng;
         if (p.eik_mode != PINQ_EIK_ALL) {
-            const bool surface = fabsf(p.label[j * p.decim]) < p.surface_range;
+            const bool surface = fabsf(p.label[p.eik_start + j * p.decim]) < p.surface_range;
             selected = surface == (p.eik_mode == PINQ_EIK_SURFACE);
             count = *p.eik_count;
         }
@@ -123,9 +125,9 @@ __global__ void k_map_loss_grad(LossParams p) {
         l_bce = warp_sum(l_bce);
         l_eik = warp_sum(l_eik);
         if ((threadIdx.x & 31) == 0) {
-            if (l_bce != 0.f) atomicAdd(&p.loss[0], l_bce / (float)p.bs);
+            if (l_bce != 0.f) atomicAdd(&p.loss[0], l_bce / (float)p.norm_bs);
             if (l_eik != 0.f) {
-                const int count = p.eik_mode == PINQ_EIK_ALL ? p.ng : *p.eik_count;
+                const int count = p.eik_mode == PINQ_EIK_ALL ? p.norm_ng : *p.eik_count;
                 atomicAdd(&p.loss[1], l_eik / (float)count);
             }
         }
@@ -211,9 +213,19 @@ extern "C" int pinq_mapping_run(const pinq_mapping_args* a, int32_t iters, void*
     PINQ_REQUIRE(a->tensor_count >= 1 && a->tensor_count <= 8, "1..8 optimizer tensors");
     PINQ_REQUIRE(a->eik_mode >= PINQ_EIK_ALL && a->eik_mode <= PINQ_EIK_FREESPACE, "bad eik_mode");
     const int decim = a->decimation;
-    const int ng = decim > 0 ? (a->bs + decim - 1) / decim : 0;
+    // data-parallel form: this rank holds samples [shard_first, shard_first + bs) of a global batch of global_bs samples
+    const int global_bs = a->global_bs > 0 ? a->global_bs : a->bs;
+    const bool sharded = a->global_bs > 0 || a->peer;
+    PINQ_REQUIRE(a->shard_first >= 0 && a->shard_first + a->bs <= global_bs, "shard outside the global batch");
+    if (sharded && (a->eik_mode != PINQ_EIK_ALL || a->weight_decay != 0.f)) {
+        set_error("pinq_mapping_run: the data-parallel form supports ekional_add_to = all and no weight decay");
+        return PINQ_ERR_UNSUPPORTED;
+    }
+    const int eik_start = decim > 0 ? (decim - a->shard_first % decim) % decim : 0;
+    const int ng = decim > 0 && eik_start < a->bs ? (a->bs - eik_start + decim - 1) / decim : 0;
+    const int global_ng = decim > 0 ? (global_bs + decim - 1) / decim : 0;
     const int64_t n = (int64_t)a->bs + 6 * (int64_t)ng;
-    PINQ_REQUIRE(a->query.n == n && a->bwd.n == n, "query / bwd n must be bs + 6 * ceil(bs / decimation)");
+    PINQ_REQUIRE(a->query.n == n && a->bwd.n == n, "query / bwd n must be bs + 6 * (eikonal samples of this shard)");
     PINQ_REQUIRE(a->query.xyz == a->batch_xyz && a->query.sdf && a->bwd.grad_sdf == a->grad_sdf, "batch buffers not wired");
     PINQ_REQUIRE(a->eik_mode == PINQ_EIK_ALL || a->eik_count, "eik_count needed for surface / freespace eikonal");
     cudaStream_t st = as_stream(stream);
@@ -236,13 +248,14 @@ extern "C" int pinq_mapping_run(const pinq_mapping_args* a, int32_t iters, void*
     GatherParams gp;
     gp.pool_xyz = a->pool_xyz; gp.pool_label = a->pool_label; gp.pool_weight = a->pool_weight; gp.pool_ts = a->pool_ts;
     gp.new_idx = a->new_idx;
-    gp.bs = a->bs; gp.bs_hist = a->bs - a->bs_new; gp.ng = ng; gp.decim = decim; gp.eik_mode = a->eik_mode;
+    gp.bs = a->bs; gp.bs_hist = a->bs - a->bs_new; gp.ng = ng; gp.decim = decim; gp.eik_mode = a->eik_mode; gp.eik_start = eik_start;
     gp.eps = a->eps_step; gp.surface_range = a->surface_range;
     gp.xyz = a->batch_xyz; gp.ts = a->batch_ts; gp.label = a->batch_label; gp.weight = a->batch_weight;
 
     LossParams lp;
     lp.sdf = a->query.sdf; lp.label = a->batch_label; lp.weight = a->batch_weight;
-    lp.bs = a->bs; lp.ng = ng; lp.decim = decim; lp.eik_mode = a->eik_mode; lp.weighted = a->weighted;
+    lp.bs = a->bs; lp.ng = ng; lp.decim = decim; lp.eik_mode = a->eik_mode; lp.weighted = a->weighted; lp.eik_start = eik_start;
+    lp.norm_bs = global_bs; lp.norm_ng = global_ng;
     lp.sigma = a->sigma; lp.weight_e = ng > 0 ? a->weight_e : 0.f;
     lp.two_eps = (float)(2.0 * (double)a->eps_step);
     lp.surface_range = a->surface_range;
@@ -265,6 +278,16 @@ extern "C" int pinq_mapping_run(const pinq_mapping_args* a, int32_t iters, void*
         rc = pinq_query_fused_bwd(&a->bwd, stream);
         if (rc != PINQ_OK) return rc;
         const int step = it + 1;
+        if (a->peer) {  // exchange + optimizer as ONE kernel over peer memory (csrc/peer.cu): sum of the ranks' gradient blocks,
+                        // Adam on the owned slice, parameters broadcast, gradients zeroed
+            pinq_peer_args pa = *a->peer;
+            pa.epoch = a->peer->epoch + (uint32_t)it;
+            pa.adam_step = step;
+            pa.lr = a->lr; pa.beta1 = a->beta1; pa.beta2 = a->beta2; pa.adam_eps = a->adam_eps;
+            rc = pinq_peer_exchange(&pa, stream);
+            if (rc != PINQ_OK) return rc;
+            continue;
+        }
         const double bc1 = 1.0 - pow((double)a->beta1, (double)step);
         const double bc2 = 1.0 - pow((double)a->beta2, (double)step);
         const float step_size = (float)((double)a->lr / bc1), bc2_sqrt = (float)sqrt(bc2);

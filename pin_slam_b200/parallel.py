@@ -71,16 +71,18 @@ def exchange_gradients(params, sum_buffers=(), max_buffers=(), group=None):
     return calls
 
 
-def dp_mapping_iteration(mapper, coord, sdf_label, ts, weight, opt, group=None, peer=None):
+def dp_mapping_iteration(mapper, coord, sdf_label, ts, weight, opt, group=None, peer=None, shard=None, keep_grads=None):
     """One data-parallel iteration of Mapper.mapping() (reference: utils/mapper.py:443-573) over a GLOBAL batch
     that every rank holds (indices are drawn with a shared seed): slice -> fused fwd/bwd -> exchange -> Adam.
     The per-rank loss is normalised by the GLOBAL counts so that the summed gradients equal the single-GPU
-    gradient of the mean losses."""
+    gradient of the mean losses.  `peer` (a PeerExchange) selects the peer-memory kernel for the exchange; `shard` =
+    (rank, world) overrides the slicing (shard=(0, 1): the un-sharded iteration, no exchange -- self-checks);
+    `keep_grads` (a list) receives clones of the exchanged feature and decoder gradients."""
     from .utils.loss import sdf_bce_loss
 
     cfg = mapper.config
     npts = mapper.neural_points
-    rank, world = world_info(group)
+    rank, world = shard if shard is not None else world_info(group)
     n = coord.shape[0]
     first, last = shard_range(n, rank, world)
     c, lab, t, w = coord[first:last], sdf_label[first:last], ts[first:last], torch.abs(weight[first:last]).detach()
@@ -108,6 +110,8 @@ def dp_mapping_iteration(mapper, coord, sdf_label, ts, weight, opt, group=None, 
         npts.local_point_certainties = cert_before + mp.cert_delta
         npts.local_point_ts_update.copy_(mp.ts_update)
         fused = list(mapper.geo_mlp.fused_params())
+        if keep_grads is not None:
+            keep_grads.extend([mp.grad_features.clone()] + [g.clone() for g in mp.grad_decoder])
         for p in params:
             if p is npts.local_geo_features:
                 p.grad = mp.grad_features
@@ -122,9 +126,13 @@ def dp_mapping_iteration(mapper, coord, sdf_label, ts, weight, opt, group=None, 
     for p in params:  # a rank whose slice never touched a parameter still has to join the collective
         if p.requires_grad and p.grad is None and p.numel() > 0:
             p.grad = torch.zeros_like(p)
-    delta = npts.local_point_certainties - cert_before
-    exchange_gradients(params, sum_buffers=[delta], max_buffers=[npts.local_point_ts_update], group=group)
-    npts.local_point_certainties = cert_before + delta
+    if world > 1:
+        delta = npts.local_point_certainties - cert_before
+        exchange_gradients(params, sum_buffers=[delta], max_buffers=[npts.local_point_ts_update], group=group)
+        npts.local_point_certainties = cert_before + delta
+    if keep_grads is not None:
+        fused = list(mapper.geo_mlp.fused_params())
+        keep_grads.extend([npts.local_geo_features.grad.clone()] + [t.grad.clone() for t in fused])
     opt.step()
     return loss.detach()
 
@@ -164,7 +172,7 @@ class PeerExchange:
         import ctypes as C
         from . import _pinq as P
         self.P, self.lib, self.layout, self.device = P, P.load(), layout, torch.device(device)
-        self.grid, self.timeout_ms, self.epoch = int(grid), float(timeout_ms), 0
+        self.grid, self.timeout_ms = int(grid), float(timeout_ms)
         self.simulated = simulate_world > 0
         self._mapped, self._owned = [], []
         with torch.cuda.device(self.device):
@@ -197,6 +205,7 @@ class PeerExchange:
                     P.check(self.lib.pinq_peer_open(buf, C.byref(mapped)))
                     self._mapped.append(mapped.value)
                     self.blocks.append(mapped.value)
+        self._epochs = [0] * (self.world if self.simulated else 1)
         self._views = [torch.as_tensor(_RawCuda(b, layout.nbytes), device=self.device)
                        for b in (self.blocks if self.simulated else [self.blocks[self.rank]])]
 
@@ -216,37 +225,54 @@ class PeerExchange:
         L = self.layout
         return self._view(r)[L.max_off:L.max_off + 8 * L.n_max].view(torch.int64)
 
-    def _args(self, rank, adam):
+    def next_epochs(self, rank: int, count: int = 1) -> int:
+        """First of `count` consecutive epochs for `rank`'s next calls (every rank draws the same sequence)."""
+        i = rank if self.simulated else 0
+        first = self._epochs[i] + 1
+        self._epochs[i] += count
+        return first
+
+    def make_args(self, rank, epoch, n_sum=None, n_max=None, sum_off_elems=0, adam=None):
+        """pinq_peer_args of one call: the sum region restricted to [sum_off_elems, sum_off_elems + n_sum), the max
+        region to its first n_max elements.  adam = dict(exp_avg, exp_avg_sq, n, lr, beta1, beta2, eps, step): fused
+        optimizer over the first adam['n'] elements (parameters: the head of the param region)."""
         P, L = self.P, self.layout
+        n_sum = L.n_sum - sum_off_elems if n_sum is None else _align(int(n_sum), 4)
+        n_max = L.n_max if n_max is None else _align(int(n_max), 2)
+        if sum_off_elems % 4 or sum_off_elems + n_sum > L.n_sum or n_max > L.n_max:
+            raise P.PinqError("exchange outside the peer block's regions")
         a = P.PeerArgs()
         a.rank, a.world = rank, self.world
         for r, b in enumerate(self.blocks):
             a.block[r] = b
-        a.sum_off, a.n_sum, a.max_off, a.n_max = L.sum_off, self._n_sum, L.max_off, self._n_max
-        a.epoch, a.grid, a.timeout_ms = self.epoch, self.grid, self.timeout_ms
+        a.sum_off, a.n_sum, a.max_off, a.n_max = L.sum_off + 4 * sum_off_elems, n_sum, L.max_off, n_max
+        a.epoch, a.grid, a.timeout_ms = epoch, self.grid, self.timeout_ms
         if adam is not None:
-            a.param_off, a.n_adam = L.param_off, L.n_param
-            a.exp_avg, a.exp_avg_sq = P.ptr(adam["exp_avg"][rank if self.simulated else 0]), P.ptr(adam["exp_avg_sq"][rank if self.simulated else 0])
+            adam = dict(adam)
+            adam.setdefault("n", L.n_param)
+            if sum_off_elems or _align(int(adam["n"]), 4) > min(n_sum, L.n_param):
+                raise P.PinqError("fused Adam works on the head of the sum / param regions")
+            a.param_off, a.n_adam = L.param_off, _align(int(adam["n"]), 4)
+            a.exp_avg, a.exp_avg_sq = P.ptr(adam["exp_avg"]), P.ptr(adam["exp_avg_sq"])
             a.lr, a.beta1, a.beta2, a.adam_eps, a.adam_step = adam["lr"], adam["beta1"], adam["beta2"], adam["eps"], adam["step"]
         return a
 
-    def exchange(self, adam=None, n_sum=None, n_max=None):
+    def exchange(self, adam=None, n_sum=None, n_max=None, sum_off_elems=0):
         """Sum / max the regions over the ranks (and, with `adam`, apply the optimizer step on the owned slice and
-        broadcast the parameters).  `n_sum` / `n_max` restrict the call to a prefix of the regions (identical on every
-        rank).  Asynchronous on the current stream; every rank calls it in lock-step."""
+        broadcast the parameters).  `n_sum` / `n_max` / `sum_off_elems` restrict the call to a part of the regions
+        (identical on every rank).  Asynchronous on the current stream; every rank calls it in lock-step.
+        Simulated form: `adam['exp_avg'] / ['exp_avg_sq']` are lists with one tensor per simulated rank."""
         P = self.P
-        self.epoch += 1
-        self._n_sum = self.layout.n_sum if n_sum is None else _align(int(n_sum), 4)
-        self._n_max = self.layout.n_max if n_max is None else _align(int(n_max), 2)
-        if self._n_sum > self.layout.n_sum or self._n_max > self.layout.n_max:
-            raise P.PinqError("exchange larger than the peer block's regions")
         if not self.simulated:
-            P.check(self.lib.pinq_peer_exchange(self._args(self.rank, adam), P.stream()))
+            a = self.make_args(self.rank, self.next_epochs(self.rank), n_sum, n_max, sum_off_elems, adam)
+            P.check(self.lib.pinq_peer_exchange(a, P.stream()))
             return
         cur = torch.cuda.current_stream(self.device)
         for r, st in enumerate(self.streams):  # the "ranks" must be co-resident: small grids on separate streams
             st.wait_stream(cur)
-            P.check(self.lib.pinq_peer_exchange(self._args(r, adam), st.cuda_stream))
+            ad = None if adam is None else dict(adam, exp_avg=adam["exp_avg"][r], exp_avg_sq=adam["exp_avg_sq"][r])
+            a = self.make_args(r, self.next_epochs(r), n_sum, n_max, sum_off_elems, ad)
+            P.check(self.lib.pinq_peer_exchange(a, st.cuda_stream))
         for st in self.streams:
             cur.wait_stream(st)
 
@@ -275,10 +301,12 @@ class MappingPeer:
         nf = feature_rows * feature_dim
         self.grad_features = sumr[:nf].view(feature_rows, feature_dim)
         off, self.grad_decoder = nf, []
-        for t in decoder.fused_params():
+        for t in (decoder.fused_params() if decoder is not None else ()):  # None: frozen decoder (H11), features only
             self.grad_decoder.append(sumr[off:off + t.numel()].view(t.shape))
             off += t.numel()
+        self.n_grad = off                      # feature + decoder gradients: the fused optimizer's element count
         off = _align(off, 4)
+        self.cert_off = off
         m = feature_rows - 1
         self.cert_delta = sumr[off:off + m]
         self.n_sum = off + m
@@ -288,9 +316,11 @@ class MappingPeer:
             raise peer.P.PinqError("peer block too small for this local map")
 
     @staticmethod
-    def capacity(feature_rows: int, feature_dim: int, decoder):
-        nd = sum(t.numel() for t in decoder.fused_params())
-        return PeerLayout(_align(feature_rows * feature_dim + nd, 4) + feature_rows, feature_rows)
+    def capacity(feature_rows: int, feature_dim: int, decoder, with_params: bool = False):
+        """Layout for local maps of up to `feature_rows` rows; `with_params`: also a parameter region (fused Adam)."""
+        nd = sum(t.numel() for t in decoder.fused_params()) if decoder is not None else 0
+        n_grad = _align(feature_rows * feature_dim + nd, 4)
+        return PeerLayout(n_grad + feature_rows + 8, feature_rows + 2, n_grad if with_params else 0)
 
     def attach(self, npts, decoder):
         """Zeroes the used prefix and points the fused backward's gradient sinks at it."""
@@ -302,3 +332,62 @@ class MappingPeer:
     def detach(npts, decoder):
         npts.feature_grad_sink = None
         decoder.grad_sink = None
+
+
+class DataParallelMapping:
+    """Data-parallel form of Mapper.mapping's device-side loop (`Mapper.dp = DataParallelMapping(peer)`): every rank draws
+    the same global batches (shared seed), trains on its slice, and `pinq_mapping_run` replaces its Adam launch by
+    `pinq_peer_exchange` with the fused optimizer -- per iteration ONE extra kernel sums the gradient blocks over NVLink,
+    steps the owned slice and broadcasts the parameters.  Certainty increments and ts_update, which no iteration reads,
+    are exchanged once after the last iteration.  `rank` is only given in the simulated single-GPU form."""
+
+    def __init__(self, peer: PeerExchange, rank=None):
+        self.peer = peer
+        self.rank = peer.rank if rank is None else int(rank)
+        self.world = peer.world
+        self._keep = None
+
+    def shard(self, n: int):
+        return shard_range(n, self.rank, self.world)
+
+    def begin(self, npts, decoder):
+        """Moves the trained parameters into this rank's peer block (param region) and carves the gradient block."""
+        peer = self.peer
+        r = self.rank if peer.simulated else None
+        rows, fdim = npts.local_geo_features.shape
+        carve = MappingPeer(peer, rows, fdim, decoder, r=r)
+        par = peer.param_region(r)
+        if _align(carve.n_grad, 4) > par.numel():
+            raise peer.P.PinqError("peer block has no parameter region of this size (MappingPeer.capacity(with_params=True))")
+        tensors = [npts.local_geo_features] + (list(decoder.fused_params()) if decoder is not None else [])
+        home, off = [], 0
+        for t in tensors:
+            cnt = t.numel()
+            view = par[off:off + cnt].view(t.shape)
+            view.copy_(t.data)
+            home.append(t.data)
+            t.data = view
+            off += cnt
+        carve._sum[:carve.n_sum].zero_()
+        return {"carve": carve, "grads": carve._sum, "tensors": tensors, "home": home,
+                "cert_before": npts.local_point_certainties.clone()}
+
+    def peer_args(self, iters: int, n_grad: int, exp_avg, exp_avg_sq):
+        adam = {"exp_avg": exp_avg, "exp_avg_sq": exp_avg_sq, "n": n_grad, "lr": 0.0, "beta1": 0.0, "beta2": 0.0, "eps": 0.0,
+                "step": 1}  # hyper-parameters and step are filled in per iteration by pinq_mapping_run
+        self._keep = self.peer.make_args(self.rank, self.peer.next_epochs(self.rank, iters), n_sum=_align(n_grad, 4), n_max=0,
+                                         adam=adam)
+        return self._keep
+
+    def end(self, npts, decoder, moved):
+        peer, carve = self.peer, moved["carve"]
+        m = carve.n_max
+        carve.cert_delta.copy_(npts.local_point_certainties - moved["cert_before"])
+        carve.ts_update.copy_(npts.local_point_ts_update)
+        a = peer.make_args(self.rank, peer.next_epochs(self.rank), n_sum=m, n_max=m, sum_off_elems=carve.cert_off)
+        peer.P.check(peer.lib.pinq_peer_exchange(a, peer.P.stream()))
+        npts.local_point_certainties = moved["cert_before"] + carve.cert_delta
+        npts.local_point_ts_update.copy_(carve.ts_update)
+        for t, h in zip(moved["tensors"], moved["home"]):  # parameters back into torch-owned memory
+            h.copy_(t.data)
+            t.data = h

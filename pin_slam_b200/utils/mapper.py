@@ -13,6 +13,8 @@ from __future__ import annotations
 
 import math
 
+import ctypes as C
+
 import torch
 
 from .. import _pinq as P
@@ -64,6 +66,7 @@ class Mapper:
         self.pool_sample_count = 0
         self.timing = {}
         self.fused_mapping = True   # False: run the iterations as separate autograd steps (A/B tests)
+        self.dp = None              # parallel.DataParallelMapping: shard every batch over the ranks
         self.last_loss = None
         self._fused_buf, self._fused_last = {}, None
         self._draw_host, self._draw_event = {}, None
@@ -281,6 +284,7 @@ class Mapper:
     def _mapping_fused(self, iters):
         cfg, npts, dev = self.config, self.neural_points, self.device
         lib = P.load()
+        dp = self.dp
         bs = int(cfg.bs)
         bs_new = 0
         stop_status = getattr(self.dataset, "stop_status", False)
@@ -289,14 +293,27 @@ class Mapper:
         bs_hist = bs - bs_new
         eik_on = bool(cfg.ekional_loss_on and cfg.weight_e > 0)
         decim = int(cfg.gradient_decimation) if eik_on else 0
-        ng = (bs + decim - 1) // decim if decim > 0 else 0
-        n = bs + 6 * ng
         hist, new = self._draw_batches(iters, bs_hist, bs_new, int(self.new_idx.shape[0]) if bs_new > 0 else 0)
+        global_bs, first = bs, 0
+        if dp is not None:
+            # data-parallel form: the draws above are the GLOBAL batch (shared seed: identical on every rank); this rank
+            # trains on the contiguous slice [first, last) of every row
+            first, last = dp.shard(bs)
+            hist = hist[:, min(first, bs_hist):min(last, bs_hist)].contiguous()
+            if bs_new > 0:
+                new = new[:, max(first, bs_hist) - bs_hist:max(last, bs_hist) - bs_hist].contiguous()
+            bs, bs_hist = last - first, hist.shape[1]
+            bs_new = bs - bs_hist
+            if bs_new == 0:
+                new = None
+        eik_start = (decim - first % decim) % decim if decim > 0 else 0
+        ng = (bs - eik_start + decim - 1) // decim if decim > 0 and eik_start < bs else 0
+        n = bs + 6 * ng
         pool = (self.coord_pool if self.ba_done_flag else self.global_coord_pool).contiguous()
         buf = self._fused_buf
-        if buf.get("n") != n:
+        if buf.get("n") != n or buf.get("bs") != bs:
             buf.clear()
-            buf.update(n=n, xyz=torch.empty((n, 3), dtype=torch.float32, device=dev),
+            buf.update(n=n, bs=bs, xyz=torch.empty((n, 3), dtype=torch.float32, device=dev),
                        ts=torch.empty(n, dtype=torch.int64, device=dev),
                        label=torch.empty(bs, dtype=torch.float32, device=dev),
                        weight=torch.empty(bs, dtype=torch.float32, device=dev),
@@ -306,13 +323,19 @@ class Mapper:
                        stage=torch.empty(int(lib.pinq_stage_bytes(n)), dtype=torch.uint8, device=dev),
                        relu=torch.empty(int(lib.pinq_relu_mask_words(n)), dtype=torch.int32, device=dev),
                        perm=torch.empty(n, dtype=torch.int32, device=dev) if n >= npts.bin_queries_min else None)
-        feats = npts.local_geo_features.data
         decoder = self._trainable_decoder()
         dec_n = sum(int(t.numel()) for t in decoder) if decoder else 0
-        # one zero-filled block: feature + decoder gradients, loss log, eikonal counters; Adam leaves the grads zero
-        zero = torch.zeros(feats.numel() + dec_n + 2 * iters + iters, dtype=torch.float32, device=dev)
-        moments = torch.empty(2 * (feats.numel() + dec_n) + 64, dtype=torch.float32, device=dev)
-        g_feats, off = zero[: feats.numel()], feats.numel()
+        nf = npts.local_geo_features.numel()
+        if dp is not None:
+            # parameters and gradients live in this rank's peer block for the duration of the call (csrc/peer.cu)
+            moved = dp.begin(npts, self.geo_mlp if decoder else None)
+        feats = npts.local_geo_features.data
+        # one zero-filled block: [feature + decoder gradients,] loss log, eikonal counters; Adam leaves the grads zero
+        n_own_grads = 0 if dp is not None else nf + dec_n
+        zero = torch.zeros(n_own_grads + 2 * iters + iters, dtype=torch.float32, device=dev)
+        moments = (torch.zeros if dp is not None else torch.empty)(2 * (nf + dec_n) + 64, dtype=torch.float32, device=dev)
+        grad_block = moved["grads"] if dp is not None else zero
+        g_feats, off = grad_block[:nf], nf
         a = npts._query_args(buf["xyz"], self.geo_mlp.view(), buf["ts"], True, True)
         a.sdf, a.nn_count, a.stage, a.relu_mask, a.perm = (P.ptr(buf["sdf"]), P.ptr(buf["nn"]), P.ptr(buf["stage"]),
                                                            P.ptr(buf["relu"]), P.ptr(buf["perm"]))
@@ -326,12 +349,12 @@ class Mapper:
         if decoder:
             grads = []
             for t in decoder:
-                grads.append(zero[off: off + t.numel()])
+                grads.append(grad_block[off: off + t.numel()])
                 off += t.numel()
                 tensors.append((t.data, grads[-1]))
             b.grad_W1, b.grad_b1, b.grad_W2, b.grad_b2 = (P.ptr(g) for g in grads)
-        loss = zero[off: off + 2 * iters]
-        eik_count = zero[off + 2 * iters:].view(torch.int32)
+        loss = zero[n_own_grads: n_own_grads + 2 * iters]
+        eik_count = zero[n_own_grads + 2 * iters:].view(torch.int32)
         mo = 0
         for i, (p, g) in enumerate(tensors):
             if not p.is_contiguous():
@@ -343,7 +366,7 @@ class Mapper:
         m.tensor_count = len(tensors)
         m.pool_xyz, m.pool_label, m.pool_weight, m.pool_ts = (P.ptr(pool), P.ptr(self.sdf_label_pool.contiguous()),
                                                               P.ptr(self.weight_pool.contiguous()), P.ptr(self.time_pool.contiguous()))
-        m.draws_hist, m.draws_new = P.ptr(hist), P.ptr(new)
+        m.draws_hist, m.draws_new = P.ptr(hist) if bs_hist > 0 else None, P.ptr(new) if bs_new > 0 else None
         m.new_idx = P.ptr(self.new_idx.contiguous()) if bs_new > 0 else None
         m.bs, m.bs_new, m.decimation = bs, bs_new, decim
         m.eik_mode = {"all": P.EIK_ALL, "surface": P.EIK_SURFACE, "freespace": P.EIK_FREESPACE}[cfg.ekional_add_to]
@@ -354,9 +377,16 @@ class Mapper:
                                                                   P.ptr(buf["weight"]))
         m.grad_sdf, m.loss, m.eik_count = P.ptr(buf["grad_sdf"]), P.ptr(loss), P.ptr(eik_count)
         m.lr, m.beta1, m.beta2, m.adam_eps, m.weight_decay = float(cfg.lr), 0.9, 0.99, float(cfg.adam_eps), float(cfg.weight_decay)
+        if dp is not None:
+            m.global_bs, m.shard_first = global_bs, first
+            exp_avg, exp_avg_sq = moments[:nf + dec_n], moments[(nf + dec_n + 3) // 4 * 4: (nf + dec_n + 3) // 4 * 4 + nf + dec_n]
+            pa = dp.peer_args(iters, n_grad=nf + dec_n, exp_avg=exp_avg, exp_avg_sq=exp_avg_sq)
+            m.peer = C.pointer(pa)
         P.check(lib.pinq_mapping_run(m, int(iters), P.stream()))
+        if dp is not None:
+            dp.end(npts, self.geo_mlp if decoder else None, moved)  # certainty / ts_update exchange, parameters back home
         self.total_iter += iters
-        self.last_loss = loss.view(iters, 2)   # (bce, eikonal) per iteration, on the device
+        self.last_loss = loss.view(iters, 2)   # (bce, eikonal) per iteration, on the device (data-parallel: this rank's part)
         self._fused_last = {"moments": moments, "tensors": tensors}  # read by the parity tests
 
     def mapping_loss(self, coord, sdf_label, ts, weight):

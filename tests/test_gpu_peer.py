@@ -96,9 +96,7 @@ def test_barrier_timeout_sets_the_error_word_instead_of_hanging():
     from pin_slam_b200.parallel import PeerExchange, PeerLayout
     peer = PeerExchange(PeerLayout(1024), "cuda:0", simulate_world=2, grid=4, timeout_ms=20.0)
     try:
-        peer.epoch = 1
-        peer._n_sum, peer._n_max = 1024, 0
-        P.check(peer.lib.pinq_peer_exchange(peer._args(0, None), P.stream()))
+        P.check(peer.lib.pinq_peer_exchange(peer.make_args(0, 1, 1024, 0), P.stream()))
         torch.cuda.synchronize()
         assert peer.error() != 0
     finally:
@@ -151,3 +149,80 @@ def test_two_shard_backward_plus_exchange_equals_unsharded_gradient():
         m.local_point_certainties, m.local_point_ts_update = cert0, ts0
         m.feature_grad_sink = None
         dec.grad_sink = None
+
+
+def _replica(frames, seed_pool=31, pool_n=12000):
+    """One rank's replica: map, decoder and a mapper with a replay pool -- identical on every call."""
+    from pin_slam_b200.utils.mapper import Mapper
+    s = build_oracle_map(frames)
+    m, cfg = build_cuda_map(frames)
+    randomize_features(s, m, std=0.3)
+    dec, _ = decoder_pair(cfg)
+    cfg.bs, cfg.bs_new_sample = 2048, 256
+    g = torch.Generator().manual_seed(seed_pool)
+    mp = Mapper(cfg, None, m, dec, None, None)
+    coord = make_queries(s.points, pool_n, seed=seed_pool).cuda()
+    mp.global_coord_pool, mp.coord_pool = coord, coord.clone()
+    mp.sdf_label_pool = (0.2 * torch.randn(pool_n, generator=g)).cuda()
+    w = torch.rand(pool_n, generator=g) + 0.5
+    w[::3] *= -1
+    mp.weight_pool = w.cuda()
+    mp.time_pool = torch.randint(0, 3, (pool_n,), generator=g).cuda()
+    mp.pool_sample_count = pool_n
+    mp.new_idx = torch.arange(pool_n - 900, pool_n, device="cuda")
+    return s, m, cfg, dec, mp
+
+
+@pytest.mark.parametrize("world,iters", [(2, 1), (2, 5), (4, 3)])
+def test_data_parallel_fused_mapping_matches_single_device(world, iters):
+    """pinq_mapping_run in its data-parallel form (sharded global batch, global loss normalisation, pinq_peer_exchange with
+    the fused Adam between backward and the next iteration; certainty / ts exchange at the end) on `world` simulated ranks
+    -- `world` replicas of the map on one GPU, one stream each -- against the single-device loop on the same draws."""
+    from pin_slam_b200.parallel import DataParallelMapping, MappingPeer, PeerExchange
+    frames = frames_of_points(3, 40000)
+    s, m_ref, cfg, dec_ref, mp_ref = _replica(frames)
+    probe = make_queries(s.points, 4000, seed=77).cuda()
+    start = m_ref.local_geo_features.data.clone()
+    mp_ref.generator = torch.Generator().manual_seed(5)
+    mp_ref._mapping_fused(iters)
+    torch.cuda.synchronize()
+    with torch.no_grad():
+        sdf_ref = m_ref.query_sdf(probe, dec_ref, None, False, True)["sdf"].clone()
+
+    reps = [_replica(frames) for _ in range(world)]
+    rows, fdim = reps[0][1].local_geo_features.shape
+    peer = PeerExchange(MappingPeer.capacity(rows, fdim, reps[0][3], with_params=True), "cuda:0", simulate_world=world,
+                        grid=8, timeout_ms=3000.0)
+    try:
+        torch.cuda.synchronize()
+        streams = [torch.cuda.Stream() for _ in range(world)]
+        for r, (_, m, _, dec, mp) in enumerate(reps):   # everything below is asynchronous: the "ranks" meet on the device
+            mp.generator = torch.Generator().manual_seed(5)
+            mp.dp = DataParallelMapping(peer, rank=r)
+            with torch.cuda.stream(streams[r]):
+                mp._mapping_fused(iters)
+        torch.cuda.synchronize()
+        assert peer.error() == 0
+        f_ref = m_ref.local_geo_features.data
+        moved = (f_ref - start).abs() > 0
+        assert float(moved.float().mean()) > 0.01
+        for r, (_, m, _, dec, mp) in enumerate(reps):
+            f = m.local_geo_features.data
+            assert torch.equal(f, reps[0][1].local_geo_features.data)          # replicas stay bit-identical
+            for a, b in zip(dec.parameters(), reps[0][3].parameters()):
+                assert torch.equal(a.data, b.data)
+            # Adam (eps 1e-15) moves an element by ~lr * sign(g) when g is rounding noise: compare like the autograd-loop test
+            assert float(((f - f_ref).abs() > 1e-4)[moved].float().mean()) < 0.02
+            for a, b in zip(dec.parameters(), dec_ref.parameters()):
+                assert float((a.data - b.data).abs().max()) < 1e-3
+            with torch.no_grad():
+                sdf = m.query_sdf(probe, dec, None, False, True)["sdf"]
+            assert float((sdf - sdf_ref).abs().mean()) < 1e-4 * max(1.0, float(sdf_ref.abs().mean()))
+            assert rel_err(m.local_point_certainties, m_ref.local_point_certainties) < 1e-5
+            assert torch.equal(m.local_point_ts_update, m_ref.local_point_ts_update)
+            assert f.data_ptr() != peer.param_region(r).data_ptr()             # parameters are back in torch-owned memory
+        # the logged losses are per-rank partial sums of the global means
+        loss_dp = sum(mp.last_loss for (_, _, _, _, mp) in reps)
+        assert rel_err(loss_dp, mp_ref.last_loss) < 1e-4
+    finally:
+        peer.close()
