@@ -1042,6 +1042,7 @@ int pinq_query_certainty(const pinq_map_view* map, const float* xyz, int64_t n, 
 
 int pinq_query_fused_fwd(const pinq_query_args* a, void* stream) {
     PINQ_REQUIRE(a != nullptr, "null args");
+    PINQ_REQUIRE(((uintptr_t)a->features & 31) == 0, "features must be 32-byte aligned (rows are gathered with 256-bit loads)");
     return run_query(a, 0, nullptr, nullptr, 0, nullptr, as_stream(stream));
 }
 

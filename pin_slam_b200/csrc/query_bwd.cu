@@ -233,6 +233,8 @@ extern "C" int pinq_query_fused_bwd(const pinq_bwd_args* a, void* stream) {
     if (rc) return rc;
     PINQ_REQUIRE(a->features && a->stage && a->grad_sdf && a->relu_mask,
                  "null input (the backward needs the stage and the relu mask saved by pinq_query_fused_fwd)");
+    PINQ_REQUIRE(((uintptr_t)a->features & 31) == 0 && ((uintptr_t)a->grad_features & 15) == 0,
+                 "features must be 32-byte aligned (256-bit row loads), grad_features 16-byte aligned (vector reductions)");
     const bool dec = a->grad_W1 != nullptr;
     PINQ_REQUIRE(!dec || (a->grad_b1 && a->grad_W2 && a->grad_b2), "decoder gradients: all four or none");
     const bool feat = a->grad_features != nullptr;

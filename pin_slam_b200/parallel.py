@@ -155,10 +155,12 @@ class PeerLayout:
 
     def __init__(self, n_sum: int, n_max: int = 0, n_param: int = 0):
         from . import _pinq as P
-        self.n_sum, self.n_max, self.n_param = _align(n_sum, 4), _align(n_max, 2), _align(n_param, 4)
+        # every region starts on a 256-byte boundary: the query kernels gather 32-byte feature rows with 256-bit loads
+        # straight out of the parameter region
+        self.n_sum, self.n_max, self.n_param = _align(n_sum, 64), _align(n_max, 32), _align(n_param, 64)
         self.sum_off = P.PEER_PAD_BYTES
         self.param_off = self.sum_off + 4 * self.n_sum
-        self.max_off = _align(self.param_off + 4 * self.n_param, 16)
+        self.max_off = self.param_off + 4 * self.n_param
         self.nbytes = _align(self.max_off + 8 * self.n_max, 256)
 
 

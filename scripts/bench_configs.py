@@ -136,15 +136,58 @@ def main():
             losses.append(dp_mapping_iteration(mapper, pool[idx], label[idx], tsp[idx], weight[idx], opt, peer=peer))
         e1.record()
         barrier()
-        ms = max_over_ranks(e0.elapsed_time(e1))
+        ms_autograd = max_over_ranks(e0.elapsed_time(e1))
         err = peer.error() if peer is not None else 0
+        if peer is not None:
+            dist.barrier()
+            peer.close()
+            peer = None
+        del draws
+        torch.cuda.empty_cache()
+
+        # the product form: Mapper.mapping's device-side loop (pinq_mapping_run), data-parallel through Mapper.dp
+        from pin_slam_b200.parallel import DataParallelMapping
+        cfg.bs, cfg.bs_new_sample = args.batch, 0
+        mapper.global_coord_pool, mapper.coord_pool = pool, pool
+        mapper.sdf_label_pool, mapper.weight_pool, mapper.time_pool = label, weight, tsp
+        mapper.pool_sample_count = args.pool
+        mapper.generator = torch.Generator(device=dev).manual_seed(11)  # the same Philox stream on every rank
+        if world > 1:
+            peer = PeerExchange(MappingPeer.capacity(rows, fdim, dec, with_params=True), dev)
+            torch.cuda.synchronize()
+            dist.barrier()
+            mapper.dp = DataParallelMapping(peer)
+        assert mapper._fused_mapping_supported()
+        for _ in range(2):
+            mapper._mapping_fused(args.iters)
+        barrier()
+        e0.record()
+        mapper._mapping_fused(args.iters)
+        e1.record()
+        barrier()
+        ms = max_over_ranks(e0.elapsed_time(e1))
+        err = max(err, peer.error() if peer is not None else 0)
+        last = mapper.last_loss.clone()
+        if world > 1:
+            dist.all_reduce(last)
+        same = torch.tensor([float(npts.local_geo_features.data.double().sum())], device=dev, dtype=torch.float64)
+        lo_hi = [same.clone(), same.clone()]
+        if world > 1:
+            dist.all_reduce(lo_hi[0], op=dist.ReduceOp.MIN)
+            dist.all_reduce(lo_hi[1], op=dist.ReduceOp.MAX)
         if rank == 0:
             n_eik = 6 * ((args.batch + cfg.gradient_decimation - 1) // cfg.gradient_decimation)
             print(json.dumps({"config": "batched mapping (BASELINE configs[3])", "n_gpus": world, "samples_per_iter": args.batch,
                               "queries_per_iter": args.batch + n_eik, "iters": args.iters, "pool": args.pool, "neural_points": m,
                               "ms_per_iter": ms / args.iters, "value": args.batch * args.iters / (ms * 1e-3), "unit": "samples/s",
-                              "exchange": exchange, "peer_exchange_error": err, "adam": "replicated torch.optim.Adam",
-                              "loss_first_last_rank0": [float(losses[0]), float(losses[-1])], "self_check": check}))
+                              "form": "device-side loop (pinq_mapping_run)" + (", pinq_peer_exchange with fused Adam per iteration" if world > 1 else ""),
+                              "exchange": "peer" if world > 1 else "none", "peer_exchange_error": err,
+                              "loss_bce_eik_first_last": [last[0].tolist(), last[-1].tolist()],
+                              "replicas_identical": bool(float(lo_hi[0]) == float(lo_hi[1])),
+                              "autograd_form": {"ms_per_iter": ms_autograd / args.iters, "exchange": exchange,
+                                                "adam": "replicated torch.optim.Adam",
+                                                "loss_first_last_rank0": [float(losses[0]), float(losses[-1])],
+                                                "self_check": check}}))
         if peer is not None:
             dist.barrier()
             peer.close()

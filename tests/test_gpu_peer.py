@@ -71,7 +71,7 @@ def test_fused_adam_matches_torch_adam(world):
         for r in range(world):
             peer.param_region(r).copy_(p0)
         for step in range(1, 4):
-            grads = [torch.randn(n_par + n_extra, device="cuda", generator=g) * 1e-3 for _ in range(world)]
+            grads = [torch.randn(peer.layout.n_sum, device="cuda", generator=g) * 1e-3 for _ in range(world)]
             for r in range(world):
                 peer.sum_region(r).copy_(grads[r])
             peer.exchange(adam=dict(state, step=step))
