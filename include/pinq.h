@@ -418,6 +418,31 @@ typedef struct pinq_peer_args {
 } pinq_peer_args;
 int pinq_peer_exchange(const pinq_peer_args* args, void* stream);
 
+/* ---- replay pool upkeep (utils/mapper.py:209-263) ------------------------------------------
+ * Per frame: append the new samples (mapper.py:209-222), keep the rows inside the window around the sensor
+ * (mapper.py:229-233), knock out random survivors above pool_capacity (:237-246), compact all five pool tensors
+ * (:248-263).  Three calls around pinq_compact_flags so that the caller owns all memory and draws the random
+ * numbers (the reference's torch.randint stream):
+ *   pinq_pool_flags    flags[i] = ||g_i - origin||^2 < radius2 over [old pool | new samples]
+ *   pinq_compact_flags survivors' row numbers, in order (boolean-mask indexing keeps order)
+ *   [pinq_pool_discard flags[kept_index[discarded[k]]] = 0, then compact again]
+ *   pinq_pool_move     survivor j <- its row of the old pool or of the new samples (timestamp = new_ts), written
+ *                      into `out` (must not alias the inputs); *d_kept_new += survivors among the new samples
+ *                      (= filter_mask[-cur_sample_count:].sum(), mapper.py:262).                                  */
+typedef struct pinq_pool_view {
+    float* coord;          /* [n,3] sensor-frame sample (coord_pool)          */
+    float* global_coord;   /* [n,3] world-frame sample (global_coord_pool)    */
+    float* sdf_label;      /* [n]                                              */
+    float* weight;         /* [n]                                              */
+    int64_t* ts;           /* [n] frame id (time_pool); unused for new samples */
+} pinq_pool_view;
+int pinq_pool_flags(const float* pool_global_xyz, int64_t n_pool, const float* new_global_xyz, int64_t n_new,
+                    const float* d_origin3, float radius2, uint8_t* flags, void* stream);
+int pinq_pool_discard(uint8_t* flags, const int32_t* kept_index, const int64_t* discarded, int64_t n_discard, void* stream);
+int pinq_pool_move(const pinq_pool_view* old_pool, int64_t n_pool, const pinq_pool_view* new_samples, int64_t n_new,
+                   int64_t new_ts, const int32_t* kept_index, const int32_t* d_count, const pinq_pool_view* out,
+                   int32_t* d_kept_new, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

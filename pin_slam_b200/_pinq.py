@@ -71,6 +71,10 @@ class MappingArgs(C.Structure):
                 ("weight_decay", _f32), ("global_bs", _i32), ("shard_first", _i32), ("peer", C.POINTER(PeerArgs))]
 
 
+class PoolView(C.Structure):
+    _fields_ = [("coord", _vp), ("global_coord", _vp), ("sdf_label", _vp), ("weight", _vp), ("ts", _vp)]
+
+
 # name -> (restype, argtypes); mirrors include/pinq.h one to one
 SIGNATURES = {
     "pinq_last_error": (C.c_char_p, []),
@@ -119,6 +123,9 @@ SIGNATURES = {
     "pinq_peer_close": (C.c_int, [_vp]),
     "pinq_peer_error_offset": (_i64, []),
     "pinq_peer_exchange": (C.c_int, [C.POINTER(PeerArgs), _vp]),
+    "pinq_pool_flags": (C.c_int, [_vp, _i64, _vp, _i64, _vp, _f32, _vp, _vp]),
+    "pinq_pool_discard": (C.c_int, [_vp, _vp, _vp, _i64, _vp]),
+    "pinq_pool_move": (C.c_int, [C.POINTER(PoolView), _i64, C.POINTER(PoolView), _i64, _i64, _vp, _vp, C.POINTER(PoolView), _vp, _vp]),
 }
 
 _lib = None

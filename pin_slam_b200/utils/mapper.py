@@ -66,6 +66,8 @@ class Mapper:
         self.pool_sample_count = 0
         self.timing = {}
         self.fused_mapping = True   # False: run the iterations as separate autograd steps (A/B tests)
+        self.fused_pool = True      # False: replay-pool upkeep with torch ops (A/B tests)
+        self._pool_store = [None, None]
         self.dp = None              # parallel.DataParallelMapping: shard every batch over the ranks
         self.last_loss = None
         self._fused_buf, self._fused_last = {}, None
@@ -124,10 +126,6 @@ class Mapper:
             self.neural_points.recreate_hash(None, None, True, True, frame_id)
         self.neural_points.update(update_points, frame_origin_torch, frame_orientation_torch, frame_id)
         T3 = get_time()
-        self.coord_pool = torch.cat((self.coord_pool, coord), 0)
-        self.weight_pool = torch.cat((self.weight_pool, weight), 0)
-        self.sdf_label_pool = torch.cat((self.sdf_label_pool, sdf_label), 0)
-        self.time_pool = torch.cat((self.time_pool, time_repeat), 0)
         if cfg.track_on and getattr(self.dataset, "odom_poses", None):
             import numpy as np
             self.used_poses = torch.tensor(np.array(self.dataset.odom_poses), device=self.device, dtype=torch.float64)
@@ -135,27 +133,11 @@ class Mapper:
             import numpy as np
             self.used_poses = torch.tensor(np.array(self.dataset.gt_poses), device=self.device, dtype=torch.float64)
         global_coord = transform_torch(coord.contiguous(), cur_pose_torch)
-        self.global_coord_pool = torch.cat((self.global_coord_pool, global_coord), 0)
-        T3_1 = get_time()
-        if (frame_id + 1) % cfg.pool_filter_freq == 0:  # mapper.py:229-263
-            rel = self.global_coord_pool - frame_origin_torch.to(self.global_coord_pool)
-            filter_mask = torch.sum(rel ** 2, dim=-1) < cfg.window_radius ** 2
-            true_indices = torch.nonzero(filter_mask).squeeze()
-            pool_sample_count = true_indices.shape[0]
-            if pool_sample_count > cfg.pool_capacity:
-                discard_count = pool_sample_count - cfg.pool_capacity
-                discarded = self._randint(pool_sample_count, (discard_count,))
-                filter_mask[true_indices[discarded]] = False
-            self.coord_pool = self.coord_pool[filter_mask]
-            self.global_coord_pool = self.global_coord_pool[filter_mask]
-            self.sdf_label_pool = self.sdf_label_pool[filter_mask]
-            self.weight_pool = self.weight_pool[filter_mask]
-            self.time_pool = self.time_pool[filter_mask]
-            self.cur_sample_count = int(filter_mask[-self.cur_sample_count:].sum().item())
-            self.pool_sample_count = int(filter_mask.sum().item())
+        T3_1 = T3
+        if self.fused_pool and (frame_id + 1) % cfg.pool_filter_freq == 0:
+            self._pool_update_fused(coord, global_coord, sdf_label, weight, int(frame_id), frame_origin_torch)
         else:
-            self.cur_sample_count = coord.shape[0]
-            self.pool_sample_count = self.coord_pool.shape[0]
+            T3_1 = self._pool_update_torch(coord, global_coord, sdf_label, weight, time_repeat, frame_id, frame_origin_torch)
         T3_2 = get_time()
         if cfg.bs_new_sample > 0:  # mapper.py:274-307: learn more where the map is new
             cur = self.global_coord_pool[-self.cur_sample_count:]
@@ -177,6 +159,94 @@ class Mapper:
         self.timing = {"dynamic_filter_ms": (T1 - T0) * 1e3, "sampling_ms": (T2 - T1) * 1e3,
                        "map_update_ms": (T3 - T2) * 1e3, "pool_ms": (T4 - T3) * 1e3,
                        "pool_transform_ms": (T3_1 - T3) * 1e3, "pool_filter_ms": (T3_2 - T3_1) * 1e3}
+
+    def _pool_update_torch(self, coord, global_coord, sdf_label, weight, time_repeat, frame_id, frame_origin_torch):
+        """Replay-pool upkeep with torch ops, the reference's formulation (utils/mapper.py:209-263): the parity partner
+        of `_pool_update_fused` and the path for frames on which the pool is not filtered."""
+        cfg = self.config
+        self.coord_pool = torch.cat((self.coord_pool, coord), 0)
+        self.weight_pool = torch.cat((self.weight_pool, weight), 0)
+        self.sdf_label_pool = torch.cat((self.sdf_label_pool, sdf_label), 0)
+        self.time_pool = torch.cat((self.time_pool, time_repeat), 0)
+        self.global_coord_pool = torch.cat((self.global_coord_pool, global_coord), 0)
+        T3_1 = get_time()
+        if (frame_id + 1) % cfg.pool_filter_freq == 0:  # mapper.py:229-263
+            rel = self.global_coord_pool - frame_origin_torch.to(self.global_coord_pool)
+            filter_mask = torch.sum(rel ** 2, dim=-1) < cfg.window_radius ** 2
+            true_indices = torch.nonzero(filter_mask).squeeze()
+            pool_sample_count = true_indices.shape[0]
+            if pool_sample_count > cfg.pool_capacity:
+                discard_count = pool_sample_count - cfg.pool_capacity
+                discarded = self._randint(pool_sample_count, (discard_count,))
+                filter_mask[true_indices[discarded]] = False
+            self.coord_pool = self.coord_pool[filter_mask]
+            self.global_coord_pool = self.global_coord_pool[filter_mask]
+            self.sdf_label_pool = self.sdf_label_pool[filter_mask]
+            self.weight_pool = self.weight_pool[filter_mask]
+            self.time_pool = self.time_pool[filter_mask]
+            self.cur_sample_count = int(filter_mask[-self.cur_sample_count:].sum().item())
+            self.pool_sample_count = int(filter_mask.sum().item())
+        else:
+            self.cur_sample_count = coord.shape[0]
+            self.pool_sample_count = self.coord_pool.shape[0]
+        return T3_1
+
+    def _pool_store_side(self, rows):
+        """The half of the ping-pong store the next pool is written to: not the one the pool tensors live in now."""
+        live = self.coord_pool.data_ptr() if self.coord_pool.numel() else 0
+        side = 0
+        if self._pool_store[0] is not None and live == self._pool_store[0]["coord"].data_ptr():
+            side = 1
+        st = self._pool_store[side]
+        if st is None or st["ts"].shape[0] < rows:
+            cap = max(int(rows * 1.5), 1 << 16)
+            dev = self.device
+            st = {"coord": torch.empty((cap, 3), dtype=torch.float32, device=dev),
+                  "global_coord": torch.empty((cap, 3), dtype=torch.float32, device=dev),
+                  "sdf_label": torch.empty(cap, dtype=torch.float32, device=dev),
+                  "weight": torch.empty(cap, dtype=torch.float32, device=dev),
+                  "ts": torch.empty(cap, dtype=torch.int64, device=dev)}
+            self._pool_store[side] = st
+        return st
+
+    def _pool_update_fused(self, coord, global_coord, sdf_label, weight, frame_id, frame_origin_torch):
+        """utils/mapper.py:209-263 on libpinq (csrc/pool.cu): window flags over [old pool | new samples] -> order-preserving
+        compaction [-> random discard above pool_capacity, same torch.randint draw as the reference] -> one move of the
+        survivors into the other half of a preallocated ping-pong store.  One host read-back (two counters) per frame."""
+        cfg, dev = self.config, self.device
+        lib = P.load()
+        n_old, n_new = int(self.sdf_label_pool.shape[0]), int(sdf_label.shape[0])
+        n_tot = n_old + n_new
+        if n_tot == 0:
+            self.cur_sample_count = self.pool_sample_count = 0
+            return
+        f32 = lambda t: t.contiguous().float()  # noqa: E731
+        old = P.PoolView(P.ptr(f32(self.coord_pool)), P.ptr(f32(self.global_coord_pool)), P.ptr(f32(self.sdf_label_pool)),
+                         P.ptr(f32(self.weight_pool)), P.ptr(self.time_pool.contiguous())) if n_old else P.PoolView()
+        c_new, g_new, l_new, w_new = f32(coord), f32(global_coord), f32(sdf_label), f32(weight)
+        new = P.PoolView(P.ptr(c_new), P.ptr(g_new), P.ptr(l_new), P.ptr(w_new), None) if n_new else P.PoolView()
+        origin = frame_origin_torch.to(device=dev, dtype=torch.float32).contiguous()
+        flags = torch.empty(n_tot, dtype=torch.uint8, device=dev)
+        kept = torch.empty(n_tot, dtype=torch.int32, device=dev)
+        counts = torch.zeros(2, dtype=torch.int32, device=dev)  # [survivors, survivors among the new samples]
+        scratch = torch.empty(int(lib.pinq_compact_scratch_bytes(n_tot)), dtype=torch.uint8, device=dev)
+        st = P.stream()
+        P.check(lib.pinq_pool_flags(old.global_coord, n_old, new.global_coord, n_new, P.ptr(origin),
+                                    float(cfg.window_radius ** 2), P.ptr(flags), st))
+        P.check(lib.pinq_compact_flags(P.ptr(flags), n_tot, P.ptr(kept), P.ptr(counts[0:1]), P.ptr(scratch), st))
+        if n_tot > cfg.pool_capacity:  # only then can the survivors exceed the capacity (mapper.py:237-246)
+            survivors = int(counts[0].item())
+            if survivors > cfg.pool_capacity:
+                discarded = self._randint(survivors, (survivors - int(cfg.pool_capacity),)).contiguous()
+                P.check(lib.pinq_pool_discard(P.ptr(flags), P.ptr(kept), P.ptr(discarded), discarded.shape[0], st))
+                P.check(lib.pinq_compact_flags(P.ptr(flags), n_tot, P.ptr(kept), P.ptr(counts[0:1]), P.ptr(scratch), st))
+        dst = self._pool_store_side(n_tot)
+        out = P.PoolView(P.ptr(dst["coord"]), P.ptr(dst["global_coord"]), P.ptr(dst["sdf_label"]), P.ptr(dst["weight"]), P.ptr(dst["ts"]))
+        P.check(lib.pinq_pool_move(old, n_old, new, n_new, frame_id, P.ptr(kept), P.ptr(counts[0:1]), out, P.ptr(counts[1:2]), st))
+        total, kept_new = (int(v) for v in counts.tolist())
+        self.coord_pool, self.global_coord_pool = dst["coord"][:total], dst["global_coord"][:total]
+        self.sdf_label_pool, self.weight_pool, self.time_pool = dst["sdf_label"][:total], dst["weight"][:total], dst["ts"][:total]
+        self.cur_sample_count, self.pool_sample_count = kept_new, total
 
     def get_batch(self, global_coord=False):
         """reference: utils/mapper.py:323-361."""

@@ -338,3 +338,60 @@ def test_short_slam_run_tracks_ground_truth_and_oracle():
     assert ate_oracle < 0.30, ate_oracle
     n_cuda, n_ref = res["neural_points"].count(), orc.s.points.shape[0]
     assert abs(n_cuda - n_ref) < 0.02 * n_ref, (n_cuda, n_ref)
+
+
+@pytest.mark.parametrize("capacity", [10**9, 9000])
+def test_fused_pool_update_matches_torch_formulation(world, capacity):
+    """Replay-pool upkeep (utils/mapper.py:209-263): csrc/pool.cu against the reference's torch formulation over three
+    consecutive frames -- append, window filter, random discard above pool_capacity (same seeded draws), compaction.
+    All five pool tensors and both counters bit-exact; the ping-pong store never aliases its input."""
+    from pin_slam_b200.utils.mapper import Mapper
+    s, m, cfg, dec, d = world
+    old = (cfg.pool_capacity, cfg.window_radius)
+    cfg.pool_capacity, cfg.window_radius = capacity, 60.0
+    try:
+        mappers = []
+        for fused in (False, True):
+            mp = Mapper(cfg, None, m, dec, None, None)
+            mp.fused_pool = fused
+            mp.generator = torch.Generator().manual_seed(9)
+            mappers.append(mp)
+        g = torch.Generator().manual_seed(2)
+        for frame_id in range(3):
+            n_new = [7000, 1, 6500][frame_id]
+            coord = ((torch.rand(n_new, 3, generator=g) - 0.5) * 90.0).cuda()
+            pose = torch.eye(4)
+            pose[:3, 3] = torch.tensor([5.0 * frame_id, 1.0, 0.0])
+            pose = pose.cuda()
+            from pin_slam_b200.utils.tools import transform_torch
+            gcoord = transform_torch(coord.contiguous(), pose)
+            label = (torch.randn(n_new, generator=g) * 0.2).cuda()
+            weight = (torch.rand(n_new, generator=g) - 0.3).cuda()
+            ts = torch.full((n_new,), frame_id, dtype=torch.long, device="cuda")
+            for mp in mappers:
+                mp.cur_sample_count = n_new
+                if mp.fused_pool:
+                    mp._pool_update_fused(coord, gcoord, label, weight, frame_id, pose[:3, 3])
+                else:
+                    mp._pool_update_torch(coord, gcoord, label, weight, ts, frame_id, pose[:3, 3])
+            a, b = mappers
+            assert (a.pool_sample_count, a.cur_sample_count) == (b.pool_sample_count, b.cur_sample_count)
+            assert 0 < a.pool_sample_count <= 14501 and a.coord_pool.shape[0] == a.pool_sample_count
+            if frame_id == 2 and capacity == 9000:  # the discard path ran (duplicate draws leave a few rows above capacity)
+                assert capacity <= a.pool_sample_count < capacity + 1000
+            for name in ("coord_pool", "global_coord_pool", "sdf_label_pool", "weight_pool", "time_pool"):
+                assert torch.equal(getattr(a, name), getattr(b, name)), (name, frame_id)
+    finally:
+        cfg.pool_capacity, cfg.window_radius = old
+
+
+def test_fused_pool_update_empty_cases(world):
+    from pin_slam_b200.utils.mapper import Mapper
+    s, m, cfg, dec, d = world
+    mp = Mapper(cfg, None, m, dec, None, None)
+    e3, e1 = torch.empty((0, 3), device="cuda"), torch.empty(0, device="cuda")
+    mp._pool_update_fused(e3, e3, e1, e1, 0, torch.zeros(3, device="cuda"))
+    assert mp.pool_sample_count == 0 and mp.cur_sample_count == 0
+    far = torch.full((50, 3), 1.0e4, device="cuda")   # everything outside the window: the pool becomes empty
+    mp._pool_update_fused(far, far, torch.zeros(50, device="cuda"), torch.ones(50, device="cuda"), 1, torch.zeros(3, device="cuda"))
+    assert mp.pool_sample_count == 0 and mp.coord_pool.shape == (0, 3) and mp.time_pool.dtype == torch.int64
