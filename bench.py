@@ -66,6 +66,8 @@ def parse():
     ap.add_argument("--cpu-sample", type=int, default=200_000, help="queries per CPU-baseline step")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--slam-frames", type=int, default=30, help="N=1 only: frames of the synthetic 64-beam SLAM run reported "
+                    "under 'slam' (BASELINE configs[1]; 0 = skip)")
     return ap.parse_args()
 
 
@@ -263,6 +265,37 @@ def run_reference(args):
         "e2e": {"value": qps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line))
+
+
+def _scan_job(job):
+    from pin_slam_b200 import synth
+    pose, noise_seed = job
+    return synth.lidar_scan(synth.StreetScene(42), pose, synth.lidar_directions(64, 1875), np.random.default_rng(noise_seed))
+
+
+def slam_leg(n_frames):
+    """BASELINE.json's second metric, SLAM frames/s (configs[1]): the full per-frame loop -- preprocess, tracking, map update,
+    replay pool, 15 mapping iterations (600 on the first frame) -- on synthetic 64-beam scans (120 000 rays each, SURVEY.md
+    8(d)), run_kitti parameters.  Scans are ray-cast on the host cores beforehand (not timed); times are the reference's own
+    per-stage columns (pin_slam.py:343) taken with a device synchronize on both sides of every stage."""
+    import multiprocessing as mp
+
+    from pin_slam_b200 import synth
+    from pin_slam_b200.slam import absolute_trajectory_error, run_slam
+    from pin_slam_b200.utils.config import kitti_config
+
+    gt = synth.trajectory(n_frames)
+    with mp.get_context("spawn").Pool(min(os.cpu_count() or 1, 16)) as pool:
+        frames = pool.map(_scan_job, [(gt[i], 1000 + i) for i in range(n_frames)])
+    cfg = kitti_config("cuda")
+    cfg.deskew, cfg.correction_deg, cfg.silence = False, 0.0, True  # DESIGN.md section 6: harness deviations
+    res = run_slam(cfg, frames, None, generator=torch.Generator().manual_seed(7))
+    tt = res["time_table"]
+    return {"frames": n_frames, "rays_per_scan": 120000, "frames_per_s": float((n_frames - 1) / tt[1:].sum()),
+            "first_frame_s": float(tt[0].sum()),
+            "ms_per_frame": {k: float(tt[1:, i].mean() * 1e3) for i, k in enumerate(("preprocess", "tracking", "map_update", "mapping"))},
+            "ate_vs_ground_truth_m": float(absolute_trajectory_error(res["poses"], gt, align=False)),
+            "note": "frames/s excludes the first frame (600 warm-up iterations)"}
 
 
 def workload_config(args, npts, vbar):
@@ -537,12 +570,20 @@ def main():
                                   "restatement of the reference path" % min(args.cpu_sample, n)}
 
     peer_err = peer.error() if peer is not None else 0
+    slam = None
+    if rank == 0 and world == 1 and args.slam_frames > 1:
+        try:
+            slam = slam_leg(args.slam_frames)
+        except Exception as e:  # the headline line must not depend on this leg
+            slam = {"error": repr(e)[:200]}
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(args, npts, vbar),
                 "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e,
                 "gpu_launches": LAUNCHES_PER_STEP * args.steps, "clocks": clocks}
+        if slam is not None:
+            line["slam"] = slam
         line["config"]["parallelism"] = "replicated map, queries sharded x%d%s" % (
             world, {"none": "", "nccl": ", NCCL all-reduce of feature+decoder grads",
                     "peer": ", feature+decoder grads summed by one peer-memory kernel per rank over NVLink "

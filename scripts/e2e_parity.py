@@ -27,8 +27,15 @@ def make_cfg(device, args):
     return cfg
 
 
+def _scan(job):
+    from pin_slam_b200 import synth
+    seed, pose, beams, azimuth, noise_seed = job
+    return synth.lidar_scan(synth.StreetScene(seed), pose, synth.lidar_directions(beams, azimuth), np.random.default_rng(noise_seed))
+
+
 def main():
     ap = argparse.ArgumentParser()
+    ap.add_argument("--workers", type=int, default=1, help="> 1: generate the scans in parallel with per-frame noise seeds")
     ap.add_argument("--frames", type=int, default=100)
     ap.add_argument("--oracle-frames", type=int, default=0)
     ap.add_argument("--beams", type=int, default=64)
@@ -44,7 +51,12 @@ def main():
     dirs = synth.lidar_directions(args.beams, args.azimuth)
     rng = np.random.default_rng(0)
     t0 = time.time()
-    frames = [synth.lidar_scan(scene, gt[i], dirs, rng) for i in range(args.frames)]
+    if args.workers > 1:  # per-frame noise streams, scans ray-cast on all host cores (4 min -> seconds on the GPU box)
+        import multiprocessing as mp
+        with mp.get_context("fork").Pool(args.workers) as pool:
+            frames = pool.map(_scan, [(42, gt[i], args.beams, args.azimuth, 1000 + i) for i in range(args.frames)])
+    else:
+        frames = [synth.lidar_scan(scene, gt[i], dirs, rng) for i in range(args.frames)]
     gen_s = time.time() - t0
     res = run_slam(make_cfg("cuda", args), frames, None, generator=torch.Generator().manual_seed(7))
     tt = res["time_table"]
