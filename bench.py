@@ -289,11 +289,16 @@ def slam_leg(n_frames):
         frames = pool.map(_scan_job, [(gt[i], 1000 + i) for i in range(n_frames)])
     cfg = kitti_config("cuda")
     cfg.deskew, cfg.correction_deg, cfg.silence = False, 0.0, True  # harness deviations
-    res = run_slam(cfg, frames, None, generator=torch.Generator().manual_seed(7))
+    stages = []
+    res = run_slam(cfg, frames, None, generator=torch.Generator().manual_seed(7),
+                   on_frame=lambda fid, dataset, npts, mapper: stages.append(dict(mapper.timing)))
     tt = res["time_table"]
     return {"frames": n_frames, "rays_per_scan": 120000, "frames_per_s": float((n_frames - 1) / tt[1:].sum()),
             "first_frame_s": float(tt[0].sum()),
             "ms_per_frame": {k: float(tt[1:, i].mean() * 1e3) for i, k in enumerate(("preprocess", "tracking", "map_update", "mapping"))},
+            "map_update_stages_ms": {k: float(np.mean([t[k] for t in stages[1:] if k in t])) for k in (stages[-1] if stages else {})},
+            "median_ms_per_frame": float(np.median(tt[1:].sum(1)) * 1e3),
+            "per_frame_ms": [round(float(v) * 1e3, 1) for v in tt.sum(1)],
             "ate_vs_ground_truth_m": float(absolute_trajectory_error(res["poses"], gt, align=False)),
             "note": "frames/s excludes the first frame (600 warm-up iterations)"}
 

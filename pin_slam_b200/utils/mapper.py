@@ -68,6 +68,7 @@ class Mapper:
         self.fused_mapping = True   # False: run the iterations as separate autograd steps (A/B tests)
         self.fused_pool = True      # False: replay-pool upkeep with torch ops (A/B tests)
         self._pool_store = [None, None]
+        self._pool_ws = None
         self.dp = None              # parallel.DataParallelMapping: shard every batch over the ranks
         self.last_loss = None
         self._fused_buf, self._fused_last = {}, None
@@ -199,7 +200,7 @@ class Mapper:
             side = 1
         st = self._pool_store[side]
         if st is None or st["ts"].shape[0] < rows:
-            cap = max(int(rows * 1.5), 1 << 16)
+            cap = max(2 * int(rows), 1 << 22 if rows > (1 << 16) else 1 << 16)  # few re-allocations: cudaMalloc stalls a frame
             dev = self.device
             st = {"coord": torch.empty((cap, 3), dtype=torch.float32, device=dev),
                   "global_coord": torch.empty((cap, 3), dtype=torch.float32, device=dev),
@@ -226,10 +227,14 @@ class Mapper:
         c_new, g_new, l_new, w_new = f32(coord), f32(global_coord), f32(sdf_label), f32(weight)
         new = P.PoolView(P.ptr(c_new), P.ptr(g_new), P.ptr(l_new), P.ptr(w_new), None) if n_new else P.PoolView()
         origin = frame_origin_torch.to(device=dev, dtype=torch.float32).contiguous()
-        flags = torch.empty(n_tot, dtype=torch.uint8, device=dev)
-        kept = torch.empty(n_tot, dtype=torch.int32, device=dev)
+        ws = self._pool_ws
+        if ws is None or ws["rows"] < n_tot:  # work buffers persist across frames and grow geometrically
+            rows = max(2 * n_tot, 1 << 16)
+            ws = self._pool_ws = {"rows": rows, "flags": torch.empty(rows, dtype=torch.uint8, device=dev),
+                                  "kept": torch.empty(rows, dtype=torch.int32, device=dev),
+                                  "scratch": torch.empty(int(lib.pinq_compact_scratch_bytes(rows)), dtype=torch.uint8, device=dev)}
+        flags, kept, scratch = ws["flags"], ws["kept"], ws["scratch"]
         counts = torch.zeros(2, dtype=torch.int32, device=dev)  # [survivors, survivors among the new samples]
-        scratch = torch.empty(int(lib.pinq_compact_scratch_bytes(n_tot)), dtype=torch.uint8, device=dev)
         st = P.stream()
         P.check(lib.pinq_pool_flags(old.global_coord, n_old, new.global_coord, n_new, P.ptr(origin),
                                     float(cfg.window_radius ** 2), P.ptr(flags), st))

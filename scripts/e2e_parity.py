@@ -70,6 +70,7 @@ def main():
            "mean_ms": {"preprocess": float(tt[1:, 0].mean() * 1e3), "tracking": float(tt[1:, 1].mean() * 1e3),
                        "map_prep": float(tt[1:, 2].mean() * 1e3), "training": float(tt[1:, 3].mean() * 1e3)},
            "first_frame_s": float(tt[0].sum()), "tracking_iters_mean": float(np.mean(res["tracking_iters"])),
+           "tracking_iters": [int(v) for v in res["tracking_iters"]],
            "neural_points": int(res["neural_points"].count()), "local_points": int(res["neural_points"].local_count()),
            "pool_samples": int(res["mapper"].pool_sample_count)}
     if args.oracle_frames > 0:
@@ -94,6 +95,7 @@ def main():
                          "frames_per_s_excl_first": float((n - 1) / times[1:].sum()) if n > 1 else None,
                          "first_frame_s": float(times[0].sum()),
                          "tracking_iters_mean": float(np.mean(orc.tracking_iters)) if orc.tracking_iters else None,
+                         "tracking_iters": [int(v) for v in orc.tracking_iters],
                          "neural_points": int(orc.s.points.shape[0])}
     line = json.dumps(out)
     print(line)

@@ -10,7 +10,7 @@ python -c "import __graft_entry__ as g; g.build(); g.smoke()" > "$OUT/smoke.log"
 timeout 1500 python -m pytest tests -x -q -m gpu > "$OUT/pytest_gpu.log" 2>&1; echo "pytest rc=$?"; tail -3 "$OUT/pytest_gpu.log"
 timeout 600 python bench.py --steps 10 --warmup 3 > "$OUT/bench.json" 2> "$OUT/bench.err"; echo "bench rc=$?"; cat "$OUT/bench.json"
 timeout 600 python bench.py --impl reference --steps 3 --warmup 1 > "$OUT/bench_reference.json" 2> "$OUT/bench_reference.err"; echo "ref rc=$?"; cat "$OUT/bench_reference.json"
-SMALL="bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-e2e"
+SMALL="bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-e2e --slam-frames 0"
 timeout 600 python $SMALL > "$OUT/plain.log" 2>&1 &&
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file "$OUT/launches.csv" python $SMALL > "$OUT/ncu_launches.log" 2>&1
 echo "launches rc=$?"
