@@ -66,6 +66,8 @@ def parse():
     ap.add_argument("--cpu-sample", type=int, default=200_000, help="queries per CPU-baseline step")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--slam-seeded", action="store_true", help="SLAM leg: a seeded CPU generator for the sampler and the batch draws "
+                    "(reproducible, slower) instead of torch's device RNG (what the reference uses)")
     ap.add_argument("--slam-frames", type=int, default=30, help="N=1 only: frames of the synthetic 64-beam SLAM run reported "
                     "under 'slam' (BASELINE configs[1]; 0 = skip)")
     return ap.parse_args()
@@ -273,7 +275,7 @@ def _scan_job(job):
     return synth.lidar_scan(synth.StreetScene(42), pose, synth.lidar_directions(64, 1875), np.random.default_rng(noise_seed))
 
 
-def slam_leg(n_frames):
+def slam_leg(n_frames, device_rng=True):
     """BASELINE.json's second metric, SLAM frames/s (configs[1]): the full per-frame loop -- preprocess, tracking, map update,
     replay pool, 15 mapping iterations (600 on the first frame) -- on synthetic 64-beam scans (120 000 rays each, SURVEY.md
     8(d)), run_kitti parameters.  Scans are ray-cast on the host cores beforehand (not timed); times are the reference's own
@@ -290,10 +292,10 @@ def slam_leg(n_frames):
     cfg = kitti_config("cuda")
     cfg.deskew, cfg.correction_deg, cfg.silence = False, 0.0, True  # harness deviations
     stages = []
-    res = run_slam(cfg, frames, None, generator=torch.Generator().manual_seed(7),
+    res = run_slam(cfg, frames, None, generator=None if device_rng else torch.Generator().manual_seed(7),
                    on_frame=lambda fid, dataset, npts, mapper: stages.append(dict(mapper.timing)))
     tt = res["time_table"]
-    return {"frames": n_frames, "rays_per_scan": 120000, "frames_per_s": float((n_frames - 1) / tt[1:].sum()),
+    return {"frames": n_frames, "rays_per_scan": 120000, "rng": "device" if device_rng else "seeded cpu generator", "frames_per_s": float((n_frames - 1) / tt[1:].sum()),
             "first_frame_s": float(tt[0].sum()),
             "ms_per_frame": {k: float(tt[1:, i].mean() * 1e3) for i, k in enumerate(("preprocess", "tracking", "map_update", "mapping"))},
             "map_update_stages_ms": {k: float(np.mean([t[k] for t in stages[1:] if k in t])) for k in (stages[-1] if stages else {})},
@@ -578,7 +580,7 @@ def main():
     slam = None
     if rank == 0 and world == 1 and args.slam_frames > 1:
         try:
-            slam = slam_leg(args.slam_frames)
+            slam = slam_leg(args.slam_frames, not args.slam_seeded)
         except Exception as e:  # the headline line must not depend on this leg
             slam = {"error": repr(e)[:200]}
     if rank == 0:

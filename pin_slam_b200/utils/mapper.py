@@ -214,8 +214,10 @@ class Mapper:
         """utils/mapper.py:209-263 on libpinq (csrc/pool.cu): window flags over [old pool | new samples] -> order-preserving
         compaction [-> random discard above pool_capacity, same torch.randint draw as the reference] -> one move of the
         survivors into the other half of a preallocated ping-pong store.  One host read-back (two counters) per frame."""
+        import time as _time
         cfg, dev = self.config, self.device
         lib = P.load()
+        t_begin = _time.perf_counter()
         n_old, n_new = int(self.sdf_label_pool.shape[0]), int(sdf_label.shape[0])
         n_tot = n_old + n_new
         if n_tot == 0:
@@ -245,10 +247,16 @@ class Mapper:
                 discarded = self._randint(survivors, (survivors - int(cfg.pool_capacity),)).contiguous()
                 P.check(lib.pinq_pool_discard(P.ptr(flags), P.ptr(kept), P.ptr(discarded), discarded.shape[0], st))
                 P.check(lib.pinq_compact_flags(P.ptr(flags), n_tot, P.ptr(kept), P.ptr(counts[0:1]), P.ptr(scratch), st))
+        t_enq = _time.perf_counter()
         dst = self._pool_store_side(n_tot)
+        t_store = _time.perf_counter()
         out = P.PoolView(P.ptr(dst["coord"]), P.ptr(dst["global_coord"]), P.ptr(dst["sdf_label"]), P.ptr(dst["weight"]), P.ptr(dst["ts"]))
         P.check(lib.pinq_pool_move(old, n_old, new, n_new, frame_id, P.ptr(kept), P.ptr(counts[0:1]), out, P.ptr(counts[1:2]), st))
+        t_move = _time.perf_counter()
         total, kept_new = (int(v) for v in counts.tolist())
+        t_read = _time.perf_counter()
+        self.pool_timing = {"flags_compact_enqueue_ms": (t_enq - t_begin) * 1e3, "store_ms": (t_store - t_enq) * 1e3,
+                            "move_enqueue_ms": (t_move - t_store) * 1e3, "readback_ms": (t_read - t_move) * 1e3, "rows": n_tot}
         self.coord_pool, self.global_coord_pool = dst["coord"][:total], dst["global_coord"][:total]
         self.sdf_label_pool, self.weight_pool, self.time_pool = dst["sdf_label"][:total], dst["weight"][:total], dst["ts"][:total]
         self.cur_sample_count, self.pool_sample_count = kept_new, total
