@@ -230,6 +230,8 @@ typedef struct pinq_query_args {
                                   knn_d2 / relu_mask are then stored in PROCESSING order; pass the same
                                   perm to pinq_query_fused_bwd.  Ignored by pinq_query_feature and the mesher. */
     void* workspace;           /* pinq_query_workspace_bytes(n) bytes: search -> decode hand-off      */
+    const int32_t* skip;       /* NULL, or a device flag: when non-zero at launch time the search / resolve /
+                                  decode kernels of this call return at once (pinq_tracking_run)         */
 } pinq_query_args;
 
 int64_t pinq_query_workspace_bytes(int64_t n);
@@ -301,6 +303,26 @@ typedef struct pinq_tracking_args {
     double* h_gn_out;          /* [32] pinned host                                                  */
 } pinq_tracking_args;
 int pinq_tracking_step(const pinq_tracking_args* args, const float* h_T12, void* stream);
+
+/* A chunk of Gauss-Newton iterations of Tracker.tracking (utils/tracker.py:91-141) WITHOUT returning to the host in
+ * between: per iteration  cur = T * source  ->  fused query  ->  normal-equation reduction  ->  one-thread solve
+ * (implicit_reg, tracker.py:468-520: LM damping, 6x6 solve, expmap, T = dT @ T in fp64) + the loop's bookkeeping
+ * (residual growth, valid-point ratio, convergence thresholds, `converged` one iteration ahead of the break).
+ * Once the loop's break condition holds, the remaining launches of the chunk return at once (pinq_query_args.skip).
+ * The caller enqueues chunks until state says done (one stream synchronise per chunk instead of per iteration).
+ * state: PINQ_TRACK_STATE_DOUBLES doubles -- [0..15] T row-major, [16] last_sdf_residual_cm, [17] sdf_residual_cm;
+ * doubles 24..31 hold int32 flags: [0] done, [1] valid_flag, [2] converged, [3] iterations run, [4] valid_point_count,
+ * [5] failure reason (1 residual grew beyond max_increment_ratio, 2 too few valid points). */
+#define PINQ_TRACK_STATE_DOUBLES 32
+typedef struct pinq_tracking_loop {
+    double* state;             /* device                                                              */
+    const double* h_state_in;  /* pinned host; non-NULL: uploaded before the chunk (first chunk)       */
+    double* h_state;           /* pinned host; written after the chunk                                 */
+    int32_t first_iter, iters, iter_n;
+    int32_t min_valid_points;
+    float lm_lambda, term_thre_deg, term_thre_m, min_valid_ratio, max_increment_ratio;
+} pinq_tracking_loop;
+int pinq_tracking_run(const pinq_tracking_args* args, const pinq_tracking_loop* loop, void* stream);
 
 /* ---- fused Adam (utils/tools.py:89-116; torch.optim.Adam single-tensor semantics) -------- */
 int pinq_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, float lr,

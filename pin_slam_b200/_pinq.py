@@ -30,7 +30,7 @@ class QueryArgs(C.Structure):
     _fields_ = [("map", MapView), ("dec", DecoderView), ("xyz", _vp), ("n", _i64), ("flags", _u32), ("k", _i32),
                 ("feature_dim", _i32), ("features", _vp), ("point_xyz", _vp), ("certainties", _vp), ("quats", _vp), ("ts_update", _vp),
                 ("query_ts", _vp), ("sdf", _vp), ("grad_x", _vp), ("sdf_std", _vp), ("nn_count", _vp),
-                ("certainty", _vp), ("knn_idx", _vp), ("knn_w", _vp), ("knn_d2", _vp), ("stage", _vp), ("relu_mask", _vp), ("perm", _vp), ("workspace", _vp)]
+                ("certainty", _vp), ("knn_idx", _vp), ("knn_w", _vp), ("knn_d2", _vp), ("stage", _vp), ("relu_mask", _vp), ("perm", _vp), ("workspace", _vp), ("skip", _vp)]
 
 
 class BwdArgs(C.Structure):
@@ -43,6 +43,15 @@ class TrackingArgs(C.Structure):
     _fields_ = [("query", QueryArgs), ("source_xyz", _vp), ("sdf_label", _vp), ("min_nn", _i32), ("min_grad_norm", _f32),
                 ("max_grad_norm", _f32), ("max_sdf_std", _f32), ("gm_dist", _f32), ("gm_grad", _f32), ("gn_out", _vp),
                 ("h_gn_out", _vp)]
+
+
+class TrackingLoop(C.Structure):
+    _fields_ = [("state", _vp), ("h_state_in", _vp), ("h_state", _vp), ("first_iter", _i32), ("iters", _i32), ("iter_n", _i32),
+                ("min_valid_points", _i32), ("lm_lambda", _f32), ("term_thre_deg", _f32), ("term_thre_m", _f32),
+                ("min_valid_ratio", _f32), ("max_increment_ratio", _f32)]
+
+
+TRACK_STATE_DOUBLES = 32
 
 
 class AdamTensor(C.Structure):
@@ -116,6 +125,7 @@ SIGNATURES = {
     "pinq_stencil_masks_build": (C.c_int, [_vp, _i32, _i32, _vp, _vp]),
     "pinq_tracking_step": (C.c_int, [C.POINTER(TrackingArgs), C.POINTER(_f32), _vp]),
     "pinq_mapping_run": (C.c_int, [C.POINTER(MappingArgs), _i32, _vp]),
+    "pinq_tracking_run": (C.c_int, [C.POINTER(TrackingArgs), C.POINTER(TrackingLoop), _vp]),
     "pinq_peer_alloc": (C.c_int, [_i64, C.POINTER(_vp)]),
     "pinq_peer_free": (C.c_int, [_vp]),
     "pinq_peer_export": (C.c_int, [_vp, _vp]),

@@ -73,6 +73,7 @@ __device__ __forceinline__ void umma_tf32_ts(uint32_t tmem_d, uint32_t tmem_a, u
 template <bool MESH>
 __global__ void __launch_bounds__(tc::kRows) k_decode_tc(const DecodeParams p) {
     using namespace tc;
+    if (p.skip && *p.skip) return;
     extern __shared__ __align__(128) unsigned char s_tc_raw[];
     Smem& S = *reinterpret_cast<Smem*>(s_tc_raw);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;

@@ -87,6 +87,103 @@ __global__ void __launch_bounds__(kGnBlock) k_gn_accumulate(
     }
 }
 
+// ---- device-side Gauss-Newton loop (Tracker.tracking, utils/tracker.py:91-141) -------------------------------------
+// state = 32 doubles: [0..15] pose T (row-major 4x4), [16] last_sdf_residual_cm, [17] sdf_residual_cm, [18..23] spare,
+// then 16 int32 in the place of doubles 24..31: [0] done, [1] valid_flag, [2] converged, [3] iterations run,
+// [4] valid_point_count, [5] failure reason (1 = residual grew, 2 = too few valid points).
+constexpr int kTsLast = 16, kTsRes = 17, kTsInts = 24;
+enum { kTiDone = 0, kTiValid = 1, kTiConv = 2, kTiIters = 3, kTiCount = 4, kTiReason = 5 };
+
+__device__ __forceinline__ int32_t* track_ints(double* state) { return reinterpret_cast<int32_t*>(state + kTsInts); }
+
+// cur = T * source with the pose cast to fp32 as the reference does (tracker.py:94, tools.py:386-399)
+__global__ void k_track_transform(const float* __restrict__ xyz, int64_t n, const double* __restrict__ state,
+                                  float* __restrict__ out) {
+    if (reinterpret_cast<const int32_t*>(state + kTsInts)[kTiDone]) return;
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float x = xyz[3 * i], y = xyz[3 * i + 1], z = xyz[3 * i + 2];
+#pragma unroll
+    for (int r = 0; r < 3; ++r)
+        out[3 * i + r] = fmaf(x, (float)state[4 * r], fmaf(y, (float)state[4 * r + 1], fmaf(z, (float)state[4 * r + 2], (float)state[4 * r + 3])));
+}
+
+struct TrackLoop {
+    int iter, iter_n, min_valid_points;
+    double lm_lambda, term_deg, term_m, min_valid_ratio, max_increment_ratio, source_count;
+};
+
+// implicit_reg (tracker.py:468-520) + the loop body's bookkeeping (:108-141), one thread, fp64
+__global__ void k_track_solve(const double* __restrict__ g, double* __restrict__ state, TrackLoop L) {
+    if (threadIdx.x != 0) return;
+    int32_t* fl = track_ints(state);
+    if (fl[kTiDone]) return;
+    fl[kTiIters] = L.iter + 1;
+    const int count = (int)llrint(g[29]);
+    fl[kTiCount] = count;
+    double dT[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1};
+    double residual = 0.0;
+    if (count >= 10) {  // tracker.py:310-312 otherwise: identity increment, residual 0
+        residual = g[28] / count * 100.0;
+        const double norm = 2.0 * g[27] / count;  // w /= 2 mean(w), tracker.py:394
+        double H[6][7];
+        int k = 0;
+        for (int r = 0; r < 6; ++r)
+            for (int c = r; c < 6; ++c, ++k) H[r][c] = H[c][r] = g[k] / norm;
+        for (int r = 0; r < 6; ++r) {
+            H[r][6] = -g[21 + r] / norm;
+            H[r][r] += L.lm_lambda * H[r][r];   // H + lambda diag(H), tracker.py:489
+        }
+        for (int c = 0; c < 6; ++c) {           // t = H^-1 b by elimination with partial pivoting
+            int piv = c;
+            for (int r = c + 1; r < 6; ++r)
+                if (fabs(H[r][c]) > fabs(H[piv][c])) piv = r;
+            if (piv != c)
+                for (int j = 0; j < 7; ++j) { const double tmp = H[c][j]; H[c][j] = H[piv][j]; H[piv][j] = tmp; }
+            for (int r = c + 1; r < 6; ++r) {
+                const double f = H[r][c] / H[c][c];
+                for (int j = c; j < 7; ++j) H[r][j] -= f * H[c][j];
+            }
+        }
+        double t[6];
+        for (int r = 5; r >= 0; --r) {
+            double v = H[r][6];
+            for (int j = r + 1; j < 6; ++j) v -= H[r][j] * t[j];
+            t[r] = v / H[r][r];
+        }
+        // expmap (tracker.py:580-589): a zero rotation yields NaNs there as here
+        const double angle = sqrt(t[0] * t[0] + t[1] * t[1] + t[2] * t[2]);
+        const double ax = t[0] / angle, ay = t[1] / angle, az = t[2] / angle;
+        const double S[9] = {0, -az, ay, az, 0, -ax, -ay, ax, 0};
+        const double sn = sin(angle), cs = 1.0 - cos(angle);
+        for (int r = 0; r < 3; ++r)
+            for (int c = 0; c < 3; ++c) {
+                double ss = 0.0;
+                for (int j = 0; j < 3; ++j) ss += S[3 * r + j] * S[3 * j + c];
+                dT[4 * r + c] = (r == c ? 1.0 : 0.0) + S[3 * r + c] * sn + ss * cs;
+            }
+        dT[3] = t[3]; dT[7] = t[4]; dT[11] = t[5];
+    }
+    double Tn[16];
+    for (int r = 0; r < 4; ++r)
+        for (int c = 0; c < 4; ++c) {
+            double v = 0.0;
+            for (int j = 0; j < 4; ++j) v += dT[4 * r + j] * state[4 * j + c];
+            Tn[4 * r + c] = v;
+        }
+    for (int i = 0; i < 16; ++i) state[i] = Tn[i];
+    state[kTsRes] = residual;
+    const double last = state[kTsLast];
+    if ((residual - last) / last > L.max_increment_ratio) { fl[kTiValid] = 0; fl[kTiReason] = 1; }
+    else state[kTsLast] = residual;
+    if (count < L.min_valid_points || (double)count / L.source_count < L.min_valid_ratio) { fl[kTiValid] = 0; fl[kTiReason] = 2; }
+    if (!fl[kTiValid] || fl[kTiConv] || L.iter == L.iter_n - 1) { fl[kTiDone] = 1; return; }
+    const double rot_deg = acos((dT[0] + dT[5] + dT[10] - 1.0) / 2.0) * (180.0 / 3.14159265358979323846);
+    const double tran = sqrt(dT[3] * dT[3] + dT[7] * dT[7] + dT[11] * dT[11]);
+    // `and` binds tighter than `or` (tracker.py:135); a NaN angle compares false
+    if ((fabs(rot_deg) < L.term_deg && tran < L.term_m) || L.iter == L.iter_n - 2) fl[kTiConv] = 1;
+}
+
 __global__ void k_adam(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
                        int64_t n, float beta1, float beta2, float eps, float step_size, float bc2_sqrt) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -149,6 +246,42 @@ int pinq_tracking_step(const pinq_tracking_args* a, const float* h_T12, void* st
     if (rc != PINQ_OK) return rc;
     if (cudaMemcpyAsync(a->h_gn_out, a->gn_out, 32 * sizeof(double), cudaMemcpyDeviceToHost, st) != cudaSuccess)
         return check_launch("pinq_tracking_step copy");
+    return PINQ_OK;
+}
+
+int pinq_tracking_run(const pinq_tracking_args* a, const pinq_tracking_loop* L, void* stream) {
+    PINQ_REQUIRE(a && L && a->gn_out && L->state && L->h_state, "null pointer");
+    const pinq_query_args& q0 = a->query;
+    PINQ_REQUIRE(q0.xyz && q0.sdf && q0.grad_x && q0.sdf_std && q0.nn_count && a->source_xyz, "query buffers / source points needed");
+    PINQ_REQUIRE(L->iters >= 0 && L->first_iter >= 0 && L->first_iter + L->iters <= L->iter_n, "chunk outside [0, iter_n)");
+    cudaStream_t st = as_stream(stream);
+    const int64_t n = q0.n;
+    if (L->h_state_in &&
+        cudaMemcpyAsync(L->state, L->h_state_in, PINQ_TRACK_STATE_DOUBLES * sizeof(double), cudaMemcpyHostToDevice, st) != cudaSuccess)
+        return check_launch("pinq_tracking_run upload");
+    pinq_query_args q = q0;
+    q.skip = reinterpret_cast<const int32_t*>(L->state + kTsInts) + kTiDone;
+    TrackLoop tl;
+    tl.iter_n = L->iter_n; tl.min_valid_points = L->min_valid_points;
+    tl.lm_lambda = L->lm_lambda; tl.term_deg = L->term_thre_deg; tl.term_m = L->term_thre_m;
+    tl.min_valid_ratio = L->min_valid_ratio; tl.max_increment_ratio = L->max_increment_ratio; tl.source_count = (double)n;
+    int rc;
+    for (int j = 0; j < L->iters; ++j) {
+        if (n > 0) {
+            k_track_transform<<<grid_for(n, 256), 256, 0, st>>>(a->source_xyz, n, L->state, const_cast<float*>(q.xyz));
+            if ((rc = check_launch("k_track_transform")) != PINQ_OK) return rc;
+        }
+        if ((rc = pinq_query_fused_fwd(&q, stream)) != PINQ_OK) return rc;
+        if (cudaMemsetAsync(a->gn_out, 0, 32 * sizeof(double), st) != cudaSuccess) return check_launch("pinq_tracking_run memset");
+        rc = pinq_gn_accumulate(q.xyz, q.sdf, q.grad_x, q.sdf_std, q.nn_count, a->sdf_label, n, a->min_nn, a->min_grad_norm,
+                                a->max_grad_norm, a->max_sdf_std, a->gm_dist, a->gm_grad, a->gn_out, nullptr, stream);
+        if (rc != PINQ_OK) return rc;
+        tl.iter = L->first_iter + j;
+        k_track_solve<<<1, 32, 0, st>>>(a->gn_out, L->state, tl);
+        if ((rc = check_launch("k_track_solve")) != PINQ_OK) return rc;
+    }
+    if (cudaMemcpyAsync(L->h_state, L->state, PINQ_TRACK_STATE_DOUBLES * sizeof(double), cudaMemcpyDeviceToHost, st) != cudaSuccess)
+        return check_launch("pinq_tracking_run copy");
     return PINQ_OK;
 }
 

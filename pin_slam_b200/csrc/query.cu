@@ -85,7 +85,9 @@ __global__ void k_query_certainty(MapDev map, const float* __restrict__ xyz, int
 constexpr int kWs = K + 1;
 
 __global__ void __launch_bounds__(kBlock) k_search(MapDev map, PointSrc src, int64_t n, bool recip,
-                                                   const int32_t* __restrict__ perm, int32_t* __restrict__ ws) {
+                                                   const int32_t* __restrict__ perm, int32_t* __restrict__ ws,
+                                                   const int32_t* __restrict__ skip) {
+    if (skip && *skip) return;
     extern __shared__ uint32_t s_off_s[];
     load_stencil(map, s_off_s);
     __syncthreads();
@@ -129,6 +131,7 @@ struct DecodeParams {
     float* feat_out;      // un-fused query_feature: [n,K,IN]
     int min_nn;           // mesher
     uint8_t* mask_out;
+    const int32_t* skip;  // device flag: non-zero = this launch is a no-op (device-side Gauss-Newton loop, gn.cu)
 };
 
 // Per-query part shared by the fused decode and the un-fused query_feature: resolve the K record ranks
@@ -307,6 +310,7 @@ __global__ void __launch_bounds__(kBlock) k_search_brick(MapDev map, BrickDev bd
                                                          const int32_t* __restrict__ perm,
                                                          const unsigned long long* __restrict__ stencil_masks,
                                                          int32_t* __restrict__ ws, const DecodeParams p) {
+    if (p.skip && *p.skip) return;
     extern __shared__ __align__(16) unsigned char s_brick_raw[];
     BrickLane* bl = reinterpret_cast<BrickLane*>(s_brick_raw);
     unsigned long long* s_masks = reinterpret_cast<unsigned long long*>(s_brick_raw + sizeof(BrickLane));
@@ -522,6 +526,7 @@ __global__ void __launch_bounds__(kBlock) k_query_feature(const DecodeParams p) 
 // (few registers, many resident warps) so that its dependent gathers are hidden by occupancy instead of
 // stalling the tensor-core kernel (ncu r1l: that part ran at IPC 0.2 inside the decode).
 __global__ void __launch_bounds__(kBlock) k_resolve(const DecodeParams p) {
+    if (p.skip && *p.skip) return;
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;  // processing position
     const int lane = threadIdx.x & 31;
     const bool live = i < p.n;
@@ -560,6 +565,7 @@ __device__ __forceinline__ uint32_t umin1(float h) {
 
 template <bool GRAD, bool MESH>
 __global__ void __launch_bounds__(kBlock, GRAD ? 3 : 4) k_decode_mma(const DecodeParams p) {
+    if (p.skip && *p.skip) return;
     extern __shared__ __align__(16) unsigned char s_raw[];
     DecFrags* fr = reinterpret_cast<DecFrags*>(s_raw);
     WarpStage<GRAD>* stages = reinterpret_cast<WarpStage<GRAD>*>(s_raw + dec_frag_bytes(GRAD));
@@ -889,7 +895,7 @@ static int run_query(const pinq_query_args* a, int mode, float* feat_out, const 
     p.ts_update = reinterpret_cast<long long*>(a->ts_update); p.query_ts = a->query_ts;
     p.sdf = a->sdf; p.grad_x = a->grad_x; p.sdf_std = a->sdf_std; p.nn_count = a->nn_count;
     p.certainty = a->certainty; p.knn_idx = a->knn_idx; p.knn_w = a->knn_w; p.knn_d2 = a->knn_d2;
-    p.feat_out = feat_out; p.min_nn = min_nn; p.mask_out = mask_out;
+    p.feat_out = feat_out; p.min_nn = min_nn; p.mask_out = mask_out; p.skip = a->skip;
     p.relu_mask = reinterpret_cast<uint32_t*>(a->relu_mask);
     p.stage = reinterpret_cast<StageBlock*>(a->stage ? a->stage
                                                      : reinterpret_cast<unsigned char*>(a->workspace) + ws_off_stage(n));
@@ -910,7 +916,7 @@ static int run_query(const pinq_query_args* a, int mode, float* feat_out, const 
         else
             k_search_brick<false><<<grid_for(n, kBlock), kBlock, smem, st>>>(map, bd, src, n, recip, perm, smasks, ws, p);
     } else {
-        k_search<<<grid_for(n, kBlock), kBlock, map.kn * sizeof(uint32_t), st>>>(map, src, n, recip, perm, ws);
+        k_search<<<grid_for(n, kBlock), kBlock, map.kn * sizeof(uint32_t), st>>>(map, src, n, recip, perm, ws, a->skip);
     }
     rc = check_launch("k_search");
     if (rc) return rc;

@@ -36,6 +36,14 @@ class Tracker:
         self._t12_ptr = self._t12.ctypes.data_as(ctypes.POINTER(ctypes.c_float))
         self._step_buf, self._label_keepalive = {}, None
         self.last_iterations = 0
+        # device-side Gauss-Newton loop (pinq_tracking_run): pose + bookkeeping live in 32 doubles on the device
+        self.device_loop = True      # False: one host round trip per iteration (A/B tests; always used with vis_result)
+        self.loop_chunk = 8          # iterations enqueued per stream synchronise
+        self._ts_dev = torch.zeros(P.TRACK_STATE_DOUBLES, dtype=torch.float64, device=self.device)
+        self._ts_in = torch.zeros(P.TRACK_STATE_DOUBLES, dtype=torch.float64).pin_memory()
+        self._ts_out = torch.zeros(P.TRACK_STATE_DOUBLES, dtype=torch.float64).pin_memory()
+        self._ts_in_np, self._ts_out_np = self._ts_in.numpy(), self._ts_out.numpy()
+        self._ts_in_flags, self._ts_out_flags = self._ts_in_np[24:].view(np.int32), self._ts_out_np[24:].view(np.int32)
 
     # ------------------------------------------------------------------------------------------
     def tracking(self, source_points, init_pose=None, source_colors=None, source_normals=None, source_semantics=None,
@@ -71,6 +79,36 @@ class Tracker:
         cur_points = torch.empty_like(src)
         step_args = self._tracking_args(cur_points, src, source_sdf, min_grad_norm, max_grad_norm, GM_dist, GM_grad)
         it = 0
+        if self.device_loop and not vis_result:
+            # chunks of iterations run on the device without a host round trip (csrc/gn.cu: k_track_transform, fused query,
+            # k_gn_accumulate, k_track_solve); the loop's break conditions are evaluated there
+            st_in, fl_in = self._ts_in_np, self._ts_in_flags
+            st_in[:] = 0.0
+            st_in[:16] = T.reshape(-1)
+            st_in[16] = last_sdf_residual_cm
+            fl_in[1] = 1  # valid_flag
+            loop = P.TrackingLoop()
+            loop.state, loop.h_state = P.ptr(self._ts_dev), self._ts_out.data_ptr()
+            loop.iter_n, loop.min_valid_points = int(iter_n), int(min_valid_points)
+            loop.lm_lambda, loop.term_thre_deg, loop.term_thre_m = float(cfg.reg_lm_lambda), float(cfg.reg_term_thre_deg), float(cfg.reg_term_thre_m)
+            loop.min_valid_ratio, loop.max_increment_ratio = float(min_valid_ratio), float(max_increment_sdf_residual_ratio)
+            lib, stream = P.load(), torch.cuda.current_stream()
+            first = 0
+            while first < iter_n:
+                loop.first_iter, loop.iters = first, min(int(self.loop_chunk), iter_n - first)
+                loop.h_state_in = self._ts_in.data_ptr() if first == 0 else None
+                P.check(lib.pinq_tracking_run(step_args, loop, stream.cuda_stream))
+                stream.synchronize()
+                first += loop.iters
+                if self._ts_out_flags[0]:
+                    break
+            fl = self._ts_out_flags
+            T = self._ts_out_np[:16].reshape(4, 4).copy()
+            it, valid_point_count, sdf_residual_cm = int(fl[3]), int(fl[4]), float(self._ts_out_np[17])
+            valid_flag = bool(fl[1])
+            if not valid_flag and not self.silence:
+                print("(Warning) registration failed: " + ("wrong optimization" if fl[5] == 1 else "not enough valid points"))
+            iter_n = 0  # the host loop below is skipped
         for i in range(iter_n):
             it = i + 1
             # one call per iteration: transform by T, fused query (sdf, gradient, std), normal-equation reduction

@@ -57,7 +57,7 @@ def test_ctypes_structs_match_the_header_layout(tmp_path):
     import subprocess
     from pin_slam_b200 import _pinq as P
     pairs = {"pinq_map_view": P.MapView, "pinq_decoder_view": P.DecoderView, "pinq_query_args": P.QueryArgs,
-             "pinq_bwd_args": P.BwdArgs, "pinq_tracking_args": P.TrackingArgs, "pinq_adam_tensor": P.AdamTensor,
+             "pinq_bwd_args": P.BwdArgs, "pinq_tracking_args": P.TrackingArgs, "pinq_tracking_loop": P.TrackingLoop, "pinq_adam_tensor": P.AdamTensor,
              "pinq_mapping_args": P.MappingArgs, "pinq_peer_args": P.PeerArgs, "pinq_pool_view": P.PoolView}
     header = open(os.path.join(ROOT, "include", "pinq.h")).read()
     declared = set(re.findall(r"typedef struct (pinq_[a-z_]+)", header))

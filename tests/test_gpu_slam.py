@@ -395,3 +395,43 @@ def test_fused_pool_update_empty_cases(world):
     far = torch.full((50, 3), 1.0e4, device="cuda")   # everything outside the window: the pool becomes empty
     mp._pool_update_fused(far, far, torch.zeros(50, device="cuda"), torch.ones(50, device="cuda"), 1, torch.zeros(3, device="cuda"))
     assert mp.pool_sample_count == 0 and mp.coord_pool.shape == (0, 3) and mp.time_pool.dtype == torch.int64
+
+
+@pytest.mark.parametrize("iter_n,chunk", [(3, 8), (20, 8), (20, 3), (50, 64)])
+def test_device_side_gauss_newton_loop_matches_host_loop(world, iter_n, chunk):
+    """pinq_tracking_run (pose, 6x6 solve and the loop's break conditions on the device, `chunk` iterations per host
+    round trip) against the per-iteration host loop over the same kernels: same iteration count, flags and pose."""
+    from pin_slam_b200.utils.tracker import Tracker
+    s, m, cfg, dec, d = world
+    pts = _source_points(s, 3000, seed=12).cuda()
+    init = torch.eye(4, dtype=torch.float64)
+    init[:3, 3] = torch.tensor([0.02, -0.01, 0.005], dtype=torch.float64)
+    old = (cfg.reg_min_grad_norm, cfg.reg_max_grad_norm, cfg.max_sdf_std_ratio, cfg.reg_iter_n)
+    cfg.reg_min_grad_norm, cfg.reg_max_grad_norm, cfg.max_sdf_std_ratio, cfg.reg_iter_n = 0.0, 1e3, 1e3, iter_n
+    try:
+        out = []
+        for device_loop in (False, True):
+            trk = Tracker(cfg, m, dec, None, None)
+            trk.device_loop, trk.loop_chunk = device_loop, chunk
+            T, _, _, valid = trk.tracking(pts, init.cuda())
+            out.append((T.cpu().numpy(), valid, trk.last_iterations))
+    finally:
+        cfg.reg_min_grad_norm, cfg.reg_max_grad_norm, cfg.max_sdf_std_ratio, cfg.reg_iter_n = old
+    (T0, v0, it0), (T1, v1, it1) = out
+    assert (v0, it0) == (v1, it1), out
+    assert np.allclose(T0, T1, rtol=0, atol=1e-9)
+
+
+def test_device_side_loop_flags_too_few_valid_points(world):
+    from pin_slam_b200.utils.tracker import Tracker
+    s, m, cfg, dec, d = world
+    far = (torch.rand(500, 3) * 5.0 + 1.0e3).cuda()  # nothing of the map is near: valid_point_count = 0
+    init = torch.eye(4, dtype=torch.float64).cuda()
+    res = []
+    for device_loop in (False, True):
+        trk = Tracker(cfg, m, dec, None, None)
+        trk.device_loop = device_loop
+        T, _, _, valid = trk.tracking(far, init)
+        res.append((valid, trk.last_iterations, T.cpu().numpy()))
+    assert res[0][0] is False and res[1][0] is False and res[0][1] == res[1][1] == 1
+    assert np.array_equal(res[0][2], res[1][2])  # invalid: the initial guess is returned (tracker.py:170-172)
