@@ -465,6 +465,16 @@ int pinq_pool_move(const pinq_pool_view* old_pool, int64_t n_pool, const pinq_po
                    int64_t new_ts, const int32_t* kept_index, const int32_t* d_count, const pinq_pool_view* out,
                    int32_t* d_kept_new, void* stream);
 
+/* utils/data_sampler.py:20-192 -- DataSampler.sample: per ray the measured point, n_surf gaussian samples around it,
+ * n_front uniform samples in the free space in front and n_behind behind, with projective SDF labels (-displacement)
+ * and weights (distance weighting :127-128, behind drop-off :131-135, negative sign = free space), written in ray-wise
+ * order (:169-175).  The random numbers are the caller's (torch.randn / torch.rand, the reference's RNG stream):
+ * r_surf[rep * n + ray] ~ N(0,1), r_front / r_behind ~ U(0,1). */
+int pinq_ray_samples(const float* xyz, int64_t n, const float* r_surf, const float* r_front, const float* r_behind,
+                     int32_t n_surf, int32_t n_front, int32_t n_behind, float surface_range, float free_begin_ratio,
+                     float free_end_dist, float max_range, float dist_weight_scale, int32_t dist_weight_on,
+                     int32_t behind_dropoff_on, float* out_xyz, float* out_label, float* out_weight, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

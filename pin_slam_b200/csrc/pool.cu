@@ -103,3 +103,82 @@ int pinq_pool_move(const pinq_pool_view* old_pool, int64_t n_pool, const pinq_po
 }
 
 }  // extern "C"
+
+// ---- DataSampler.sample (reference: utils/data_sampler.py:20-192) as one kernel ---------------------------------------
+namespace pinq {
+
+struct RaySampleParams {
+    const float* xyz;       // [n,3] sensor-frame points
+    const float* r_surf;    // [n_surf * n] N(0,1)   (element rep * n + ray, the order the reference's repeat() pairs them)
+    const float* r_front;   // [n_front * n] U(0,1)
+    const float* r_behind;  // [n_behind * n] U(0,1)
+    int64_t n;
+    int n_surf, n_front, n_behind;
+    float range, begin_ratio, end_dist, sigma_ratio, max_range, dist_weight_scale;
+    int dist_weight_on, behind_dropoff_on;
+    float* out_xyz;         // [n * n_all, 3] ray-wise: sample s of ray i at row i * n_all + s
+    float* out_label;
+    float* out_weight;
+};
+
+__global__ void k_ray_samples(RaySampleParams p) {
+    const int n_all = 1 + p.n_surf + p.n_front + p.n_behind;
+    const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= p.n * n_all) return;
+    const int64_t i = j / n_all;
+    const int s = (int)(j - i * n_all);
+    const float x = p.xyz[3 * i], y = p.xyz[3 * i + 1], z = p.xyz[3 * i + 2];
+    const float d = sqrtf(__fadd_rn(__fadd_rn(__fmul_rn(x, x), __fmul_rn(y, y)), __fmul_rn(z, z)));
+    float disp = 0.f, ratio = 1.f;
+    if (s >= 1 && s <= p.n_surf) {                      // gaussian around the surface (data_sampler.py:46-55)
+        disp = __fmul_rn(p.r_surf[(int64_t)(s - 1) * p.n + i], p.range);
+        ratio = __fadd_rn(__fdiv_rn(disp, d), 1.f);
+    } else if (s > p.n_surf && s <= p.n_surf + p.n_front) {  // free space in front (:76-83)
+        const float fmax = __fsub_rn(1.f, __fdiv_rn(__fmul_rn(p.sigma_ratio, p.range), d));
+        const float r = p.r_front[(int64_t)(s - 1 - p.n_surf) * p.n + i];
+        ratio = __fadd_rn(__fmul_rn(r, __fsub_rn(fmax, p.begin_ratio)), p.begin_ratio);
+        disp = __fmul_rn(__fsub_rn(ratio, 1.f), d);
+    } else if (s > p.n_surf + p.n_front) {              // free space behind (:90-97)
+        const float bmax = __fadd_rn(__fdiv_rn(p.end_dist, d), 1.f);
+        const float bmin = __fadd_rn(1.f, __fdiv_rn(__fmul_rn(p.sigma_ratio, p.range), d));
+        const float r = p.r_behind[(int64_t)(s - 1 - p.n_surf - p.n_front) * p.n + i];
+        ratio = __fadd_rn(__fmul_rn(r, __fsub_rn(bmax, bmin)), bmin);
+        disp = __fmul_rn(__fsub_rn(ratio, 1.f), d);
+    }
+    p.out_xyz[3 * j] = __fmul_rn(x, ratio);
+    p.out_xyz[3 * j + 1] = __fmul_rn(y, ratio);
+    p.out_xyz[3 * j + 2] = __fmul_rn(z, ratio);
+    float w = 1.f;
+    if (p.dist_weight_on && s <= p.n_surf)              // :127-128
+        w = __fsub_rn(__fadd_rn(1.f, __fmul_rn(p.dist_weight_scale, 0.5f)), __fmul_rn(__fdiv_rn(d, p.max_range), p.dist_weight_scale));
+    if (p.behind_dropoff_on) {                          // :131-135
+        const float dmin = __fmul_rn(0.2f, p.end_dist), dmax = p.end_dist;
+        const float c = fminf(fmaxf(__fdiv_rn(__fsub_rn(dmax, disp), __fsub_rn(dmax, dmin)), 0.f), 1.f);
+        w = __fmul_rn(w, __fadd_rn(__fmul_rn(c, 0.8f), 0.2f));
+    }
+    if (s > p.n_surf) w = -w;                           // the sign flags free-space samples
+    p.out_label[j] = -disp;
+    p.out_weight[j] = w;
+}
+
+}  // namespace pinq
+
+extern "C" int pinq_ray_samples(const float* xyz, int64_t n, const float* r_surf, const float* r_front, const float* r_behind,
+                                int32_t n_surf, int32_t n_front, int32_t n_behind, float surface_range, float free_begin_ratio,
+                                float free_end_dist, float max_range, float dist_weight_scale, int32_t dist_weight_on,
+                                int32_t behind_dropoff_on, float* out_xyz, float* out_label, float* out_weight, void* stream) {
+    PINQ_REQUIRE(n >= 0 && n_surf >= 0 && n_front >= 0 && n_behind >= 0, "negative size");
+    if (n == 0) return PINQ_OK;
+    PINQ_REQUIRE(xyz && out_xyz && out_label && out_weight, "null pointer");
+    PINQ_REQUIRE((n_surf == 0 || r_surf) && (n_front == 0 || r_front) && (n_behind == 0 || r_behind), "null random numbers");
+    pinq::RaySampleParams p;
+    p.xyz = xyz; p.r_surf = r_surf; p.r_front = r_front; p.r_behind = r_behind; p.n = n;
+    p.n_surf = n_surf; p.n_front = n_front; p.n_behind = n_behind;
+    p.range = surface_range; p.begin_ratio = free_begin_ratio; p.end_dist = free_end_dist; p.sigma_ratio = 2.0f;
+    p.max_range = max_range; p.dist_weight_scale = dist_weight_scale;
+    p.dist_weight_on = dist_weight_on; p.behind_dropoff_on = behind_dropoff_on;
+    p.out_xyz = out_xyz; p.out_label = out_label; p.out_weight = out_weight;
+    const int64_t total = n * (1 + n_surf + n_front + n_behind);
+    pinq::k_ray_samples<<<pinq::grid_for(total, 256), 256, 0, pinq::as_stream(stream)>>>(p);
+    return pinq::check_launch("pinq_ray_samples");
+}

@@ -1,19 +1,48 @@
 """DataSampler -- 1 + surface_n + front_n + behind_n samples along every LiDAR ray with projective SDF
-labels and weights (reference: utils/data_sampler.py:20-192).  Pure element-wise work (the authors
-measure 0.5 ms, data_sampler.py:187-190), out of scope as a kernel; restated
-with torch ops so that the harness does not depend on the reference tree.  A torch.Generator may be
-passed so that the CUDA path and the CPU oracle can be fed identical samples."""
+labels and weights (reference: utils/data_sampler.py:20-192).  On CUDA tensors the ~40 element-wise
+torch ops of the reference are one kernel (`pinq_ray_samples`, csrc/pool.cu) fed with the same three random tensors the
+reference draws, in the same order; `sample_torch` is that formulation restated with torch ops (parity partner, and the
+form the CPU oracle is fed from).  A torch.Generator may be passed so that the CUDA path and the CPU oracle can be fed
+identical samples."""
 from __future__ import annotations
 
 import torch
+
+from .. import _pinq as P
 
 
 class DataSampler:
     def __init__(self, config):
         self.config = config
         self.dev = config.device
+        self.fused = True  # False: the torch-op formulation on every device (A/B tests)
 
     def sample(self, points_torch, normal_torch=None, sem_label_torch=None, color_torch=None, generator=None):
+        if not (self.fused and points_torch.is_cuda):
+            return self.sample_torch(points_torch, normal_torch, sem_label_torch, color_torch, generator)
+        cfg = self.config
+        dev = points_torch.device
+        rng_dev = generator.device if generator is not None else dev
+        pts_in = points_torch.detach().float().contiguous()
+        n = pts_in.shape[0]
+        n_surf, n_front, n_behind = int(cfg.surface_sample_n), int(cfg.free_front_n), int(cfg.free_behind_n)
+        n_all = 1 + n_surf + n_front + n_behind
+        # the reference's draws, in its order: randn(n * n_surf), rand(n * n_front), rand(n * n_behind)
+        r1 = torch.randn(n * n_surf, 1, device=rng_dev, generator=generator).to(dev)
+        r2 = torch.rand(n * n_front, 1, device=rng_dev, generator=generator).to(dev)
+        r3 = torch.rand(n * n_behind, 1, device=rng_dev, generator=generator).to(dev)
+        pts = torch.empty((n * n_all, 3), dtype=torch.float32, device=dev)
+        label = torch.empty(n * n_all, dtype=torch.float32, device=dev)
+        weight = torch.empty(n * n_all, dtype=torch.float32, device=dev)
+        P.check(P.load().pinq_ray_samples(P.ptr(pts_in), n, P.ptr(r1) if n_surf else None, P.ptr(r2) if n_front else None,
+                                          P.ptr(r3) if n_behind else None, n_surf, n_front, n_behind,
+                                          float(cfg.surface_sample_range_m), float(cfg.free_sample_begin_ratio),
+                                          float(cfg.free_sample_end_dist_m), float(cfg.max_range), float(cfg.dist_weight_scale),
+                                          int(bool(cfg.dist_weight_on)), int(bool(cfg.behind_dropoff_on)),
+                                          P.ptr(pts), P.ptr(label), P.ptr(weight), P.stream()))
+        return pts, label, None, None, None, weight
+
+    def sample_torch(self, points_torch, normal_torch=None, sem_label_torch=None, color_torch=None, generator=None):
         cfg = self.config
         dev = points_torch.device
         rng_dev = generator.device if generator is not None else dev

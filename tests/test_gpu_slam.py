@@ -435,3 +435,26 @@ def test_device_side_loop_flags_too_few_valid_points(world):
         res.append((valid, trk.last_iterations, T.cpu().numpy()))
     assert res[0][0] is False and res[1][0] is False and res[0][1] == res[1][1] == 1
     assert np.array_equal(res[0][2], res[1][2])  # invalid: the initial guess is returned (tracker.py:170-172)
+
+
+@pytest.mark.parametrize("n", [1, 37, 5000])
+def test_fused_ray_sampler_matches_torch_formulation(world, n):
+    """DataSampler.sample (utils/data_sampler.py:20-192): pinq_ray_samples against the torch-op formulation fed with the
+    same seeded random draws -- sample positions, projective SDF labels, weights (sign = free space), ray-wise order."""
+    from pin_slam_b200.utils.data_sampler import DataSampler
+    s, m, cfg, dec, d = world
+    g = torch.Generator().manual_seed(4)
+    pts = ((torch.rand(n, 3, generator=g) - 0.5) * 60.0 + 1.5).cuda()
+    outs = []
+    for fused in (False, True):
+        ds = DataSampler(cfg)
+        ds.fused = fused
+        outs.append(ds.sample(pts, None, None, None, generator=torch.Generator().manual_seed(8)))
+    (c0, l0, _, _, _, w0), (c1, l1, _, _, _, w1) = outs
+    n_all = 1 + cfg.surface_sample_n + cfg.free_front_n + cfg.free_behind_n
+    assert c1.shape == (n * n_all, 3) and l1.shape == w1.shape == (n * n_all,)
+    assert torch.allclose(c0, c1, rtol=2e-6, atol=2e-6)
+    assert torch.allclose(l0, l1, rtol=1e-5, atol=2e-6)
+    assert torch.allclose(w0, w1, rtol=2e-6, atol=2e-6)
+    assert torch.equal(torch.sign(w0), torch.sign(w1))
+    assert torch.equal(c1[::n_all], pts) and float(l1[::n_all].abs().max()) == 0.0   # sample 0 of every ray is the measurement
