@@ -5,8 +5,10 @@ Same constructor, attributes (`lose_track`, `static_mask`, `used_poses`, the `*_
 query kernels for the 16 384 pool samples and for the 6 x ceil(bs/10) numerical-gradient samples
 (training mode, hazard H9), the BCE + eikonal loss on [N] tensors in PyTorch, the hand-derived backward
 kernel (feature scatter-add + decoder gradients, skipped per flag when the decoder is frozen, H11) and
-the Adam step.  `process_frame()` keeps the replay pool with torch ops ("next" row) and
-uses the libpinq kernels for the map update and the new-sample certainty query.
+the Adam step -- all of it inside `pinq_mapping_run` (one device-side loop per frame; data-parallel through `Mapper.dp`).
+`process_frame()` keeps the replay pool with the kernels of csrc/pool.cu (`_pool_update_torch` is the
+reference's torch formulation, kept as parity partner) and uses the libpinq kernels for the ray sampler, the map update and
+the new-sample certainty query.
 Bundle adjustment (pypose), semantics, colour and the Open3D helpers are out of scope.
 """
 from __future__ import annotations
