@@ -520,7 +520,7 @@ def main():
         out_h = torch.empty(n, dtype=torch.float32).pin_memory()
         # The batch crosses PCIe in chunks on a copy stream, double-buffered against the fused forward + backward of
         # the previous chunk (gradients accumulate over the chunks as over one batch); results go back per chunk.
-        nchunk = int(os.environ.get("PINQ_E2E_CHUNKS", "2"))  # per-chunk fixed costs (binning, launches) favour few chunks
+        nchunk = int(os.environ.get("PINQ_E2E_CHUNKS", "1"))  # per-chunk fixed costs (binning, launches) favour few chunks
         if n % nchunk or n < nchunk * 65536:
             nchunk = 1
         cn = n // nchunk
@@ -531,12 +531,14 @@ def main():
         copied = [torch.cuda.Event() for _ in range(2)]
         consumed = [torch.cuda.Event() for _ in range(2)]
         ones_c = ones[:cn]
+        chunk_no = [0]
 
         def e2e_step():
             zero_grads()
             main = torch.cuda.current_stream()
             for c in range(nchunk):
-                bi = c % 2
+                bi = chunk_no[0] % 2  # buffers alternate across step boundaries too: the next step's first copy overlaps this step's kernels
+                chunk_no[0] += 1
                 with torch.cuda.stream(copy_stream):
                     copy_stream.wait_event(consumed[bi])  # the chunk that used this buffer is done
                     xb[bi].copy_(qh[c * cn:(c + 1) * cn], non_blocking=True)
@@ -552,20 +554,27 @@ def main():
                     out_h[c * cn:(c + 1) * cn].copy_(sdf_c, non_blocking=True)
                 sdf_c.record_stream(back_stream)
             exchange_grads()
-            main.wait_stream(back_stream)  # the step ends when its results are on the host
+            if not pipelined:
+                main.wait_stream(back_stream)  # the step ends when its results are on the host
 
+        # steps are pipelined like a prefetching data loader: the next step's kernels do not wait for this step's results to
+        # reach the host (they return on their own stream); the timed region ends when the LAST result is on the host.
+        # PINQ_E2E_PIPELINE=0: every step waits for its own results before the next one starts.
+        pipelined = os.environ.get("PINQ_E2E_PIPELINE", "1") != "0"
         for _ in range(max(5, args.warmup)):  # PCIe link and pinned pages warm
             e2e_step()
+        torch.cuda.current_stream().wait_stream(back_stream)
         barrier()
         ev0.record()
         for _ in range(args.steps):
             e2e_step()
+        torch.cuda.current_stream().wait_stream(back_stream)
         ev1.record()
         barrier()
         te = torch.tensor([ev0.elapsed_time(ev1)], device=dev, dtype=torch.float64)
         if world > 1:
             dist.all_reduce(te, op=dist.ReduceOp.MAX)
-        e2e = {"value": world * n / (float(te.item()) / args.steps * 1e-3), "unit": UNIT, "chunks": nchunk,
+        e2e = {"value": world * n / (float(te.item()) / args.steps * 1e-3), "unit": UNIT, "chunks": nchunk, "steps_pipelined": pipelined,
                "h2d_bytes_per_step": n * 12 + n * 8, "d2h_bytes_per_step": n * 4}
 
     cpu_baseline = None
