@@ -152,5 +152,98 @@ def main():
     print("wrote", path, os.path.getsize(path) // 1024, "KiB;", npts.count(), "neural points,", npts.local_count(), "local")
 
 
+def pose_corrections(n_frames=3):
+    """Per-frame SE(3) corrections as a pose-graph optimisation would hand to adjust_map (small rotations + shifts)."""
+    T = torch.eye(4).repeat(n_frames, 1, 1)
+    for i, (az, ax, t) in enumerate(((0.02, -0.01, (0.05, -0.02, 0.01)), (-0.03, 0.015, (-0.04, 0.03, 0.0)),
+                                     (0.05, 0.02, (0.02, 0.06, -0.02)))[:n_frames]):
+        cz, sz, cx, sx = np.cos(az), np.sin(az), np.cos(ax), np.sin(ax)
+        Rz = torch.tensor([[cz, -sz, 0.0], [sz, cz, 0.0], [0.0, 0.0, 1.0]])
+        Rx = torch.tensor([[1.0, 0.0, 0.0], [0.0, cx, -sx], [0.0, sx, cx]])
+        T[i, :3, :3] = (Rz @ Rx).float()
+        T[i, :3, 3] = torch.tensor(t)
+    return T
+
+
+def main_pgo():
+    """Second fixture: the map-maintenance calls around a loop closure and the after_pgo branch of the
+    query (model/neural_points.py:597-607) -- adjust_map, recreate_hash (both flavours), prune_map, query_feature + decoder
+    + gradients with rotated neighbour offsets."""
+    torch.set_num_threads(1)
+    ns = ref_shim.load()
+    cfg = ref_shim.kitti_config("cpu")
+    cfg.buffer_size = 2_000_003
+    torch.manual_seed(42)
+    dec = ns.Decoder(cfg, 64, 1, 1)
+    npts = ns.NeuralPoints(cfg)
+    npts.travel_dist = torch.tensor([0.0, 3.0, 6.0])
+    frames = []
+    for ts in range(3):
+        p = synth.surface_points(9000, 40.0, seed=200 + ts)
+        p[:, 0] += 3.0 * ts
+        frames.append(p)
+        npts.update(torch.from_numpy(p), torch.tensor([3.0 * ts, 0.0, 0.0]), torch.eye(3), ts)
+    g = torch.Generator().manual_seed(2)
+    feats = torch.randn(npts.geo_features.shape, generator=g) * 0.2
+    feats[-1] = 0
+    cert = torch.rand(npts.point_certainties.shape, generator=g) * 30
+    npts.geo_features, npts.point_certainties = feats.clone(), cert.clone()
+    out = {"frames0": frames[0], "frames1": frames[1], "frames2": frames[2], "buffer_size": np.int64(cfg.buffer_size),
+           "features": feats.numpy(), "certainties": cert.numpy(),
+           "W1": dec.layers[0].weight.detach().numpy(), "b1": dec.layers[0].bias.detach().numpy(),
+           "W2": dec.lout.weight.detach().numpy(), "b2": dec.lout.bias.detach().numpy(), "sdf_scale": np.float64(dec.sdf_scale)}
+    # ---- adjust_map (model/neural_points.py:355-370)
+    pose_diff = pose_corrections(3)
+    out["pose_diff"] = pose_diff.numpy()
+    npts.adjust_map(pose_diff)
+    out["adj_points"], out["adj_quats"] = npts.neural_points.numpy().copy(), npts.point_orientations.numpy().copy()
+    # ---- recreate_hash, kept_points flavour, then the local map (model/neural_points.py:372-428)
+    sensor = torch.tensor([6.0, 0.0, 0.0])
+    npts.recreate_hash(sensor, torch.eye(3), True, True, 2)
+    out["rh_table"] = npts.buffer_pt_index.numpy().astype(np.int32)
+    out["rh_global2local"] = npts.global2local.numpy().astype(np.int32)
+    # ---- after_pgo query: tracking flavour (inference) with gradient, then a training-flavour backward
+    q = torch.from_numpy(synth.microbench_queries(npts.neural_points.numpy(), 400, seed=5))
+    out["queries"] = q.numpy()
+    qq = q.clone().requires_grad_(True)
+    fv, _, w, nn, qc = npts.query_feature(qq, training_mode=False, query_locally=True)
+    pred = dec.sdf(fv)
+    sdf = torch.sum(pred * w, dim=1).squeeze(1)
+    grad = ns.tools.get_gradient(qq, sdf)
+    out["fv"], out["w"], out["nn"] = fv.detach().numpy(), w.detach().numpy(), nn.numpy().astype(np.int32)
+    out["sdf"], out["grad"], out["qc"] = sdf.detach().numpy(), grad.detach().numpy(), qc.numpy()
+    up = torch.randn(q.shape[0], generator=g)
+    ts = torch.randint(0, 3, (q.shape[0],), generator=g)
+    for p_ in list(dec.parameters()) + [npts.local_geo_features]:
+        p_.grad = None
+    fv, _, w, _, _ = npts.query_feature(q, ts)
+    (torch.sum(dec.sdf(fv) * w, dim=1).squeeze(1) * up).sum().backward()
+    out["bwd_up"], out["bwd_ts"] = up.numpy(), ts.numpy()
+    out["bwd_gfeat"] = npts.local_geo_features.grad.numpy()
+    out["bwd_gW1"], out["bwd_gb1"] = dec.layers[0].weight.grad.numpy(), dec.layers[0].bias.grad.numpy()
+    out["bwd_gW2"], out["bwd_gb2"] = dec.lout.weight.grad.numpy(), dec.lout.bias.grad.numpy()
+    npts.assign_local_to_global()
+    out["after_query_certainties"] = npts.point_certainties.numpy().copy()
+    out["after_query_ts_update"] = npts.point_ts_update.numpy().copy()
+    # ---- prune_map (model/neural_points.py:328-353): frames 0/1 become inactive 500 m later
+    npts.travel_dist = torch.tensor([0.0, 3.0, 500.0])
+    npts.cur_ts = 2
+    out["prune_travel_dist"] = npts.travel_dist.numpy()
+    out["prune_thre"] = np.float64(15.0)
+    pruned = npts.prune_map(15.0)
+    out["pruned"] = np.int64(pruned)
+    out["prune_points"], out["prune_features"] = npts.neural_points.numpy().copy(), npts.geo_features.numpy().copy()
+    out["prune_ts_create"], out["prune_certainties"] = npts.point_ts_create.numpy().copy(), npts.point_certainties.numpy().copy()
+    # ---- recreate_hash, compacting flavour keyed on certainty (kept_points=False, with_ts=False)
+    npts.recreate_hash(None, None, False, False, 2)
+    out["rh2_table"] = npts.buffer_pt_index.numpy().astype(np.int32)
+    out["rh2_points"], out["rh2_features"] = npts.neural_points.numpy().copy(), npts.geo_features.numpy().copy()
+    path = os.path.join(OUT, "ref_kitti_pgo.npz")
+    np.savez_compressed(path, **out)
+    print("wrote", path, os.path.getsize(path) // 1024, "KiB;", npts.count(), "neural points after prune + compaction")
+
+
 if __name__ == "__main__":
-    main()
+    if "--pgo-only" not in sys.argv:
+        main()
+    main_pgo()

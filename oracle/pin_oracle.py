@@ -268,6 +268,47 @@ def recreate_hash(s: MapState, sensor_position, kept_points: bool = True, with_t
         reset_local_map(s, sensor_position, cur_ts)
 
 
+def prune_map(s: MapState, prune_certainty_thre: float) -> bool:
+    """model/neural_points.py:328-353 -- drop inactive (travel distance since the last update beyond the window) and
+    uncertain neural points when there are more than 100 of them; the caller re-creates hash and local map."""
+    diff = torch.abs(s.travel_dist[s.cur_ts] - s.travel_dist[s.ts_update])
+    prune = (diff > s.diff_travel_dist_local) & (s.certainty < prune_certainty_thre)
+    if int(prune.sum()) <= 100:
+        return False
+    s.points, s.quats = s.points[~prune], s.quats[~prune]
+    s.ts_create, s.ts_update, s.certainty = s.ts_create[~prune], s.ts_update[~prune], s.certainty[~prune]
+    s.feats = s.feats[~torch.cat((prune, torch.tensor([False])))]
+    return True
+
+
+def rotmat_to_quat(R: torch.Tensor) -> torch.Tensor:
+    """utils/tools.py:326-334 -- (w, x, y, z); valid for rotations with 1 + trace > 0."""
+    qw = torch.sqrt(1.0 + R[:, 0, 0] + R[:, 1, 1] + R[:, 2, 2]) / 2.0
+    qx = (R[:, 2, 1] - R[:, 1, 2]) / (4.0 * qw)
+    qy = (R[:, 0, 2] - R[:, 2, 0]) / (4.0 * qw)
+    qz = (R[:, 1, 0] - R[:, 0, 1]) / (4.0 * qw)
+    return torch.stack((qw, qx, qy, qz), dim=1)
+
+
+def quat_multiply(q1: torch.Tensor, q2: torch.Tensor) -> torch.Tensor:
+    """utils/tools.py:356-369 -- q1 (x) q2."""
+    w1, x1, y1, z1 = torch.unbind(q1, dim=1)
+    w2, x2, y2, z2 = torch.unbind(q2, dim=1)
+    return torch.stack((w1 * w2 - x1 * x2 - y1 * y2 - z1 * z2, w1 * x2 + x1 * w2 + y1 * z2 - z1 * y2,
+                        w1 * y2 - x1 * z2 + y1 * w2 + z1 * x2, w1 * z2 + x1 * y2 - y1 * x2 + z1 * w2), dim=1)
+
+
+def adjust_map(s: MapState, pose_diff: torch.Tensor) -> None:
+    """model/neural_points.py:355-370 -- after pose-graph optimisation every neural point is moved by the pose correction
+    of the frame that created it (utils/tools.py:401-407 transform_batch_torch) and its orientation is rotated; from
+    then on queries rotate x - p_k into the point's frame (after_pgo)."""
+    s.after_pgo = True
+    used = ((s.ts_create + s.ts_update) / 2).long() if s.p.use_mid_ts else s.ts_create
+    T = pose_diff[used]
+    s.points = (torch.matmul(T[:, :3, :3].to(s.points), s.points.unsqueeze(-1)) + T[:, :3, 3:].to(s.points)).squeeze(-1)
+    s.quats = quat_multiply(rotmat_to_quat(pose_diff[:, :3, :3])[used], s.quats)
+
+
 # --------------------------------------------------------------------------------------
 # neighbour search + feature query
 # --------------------------------------------------------------------------------------

@@ -97,6 +97,11 @@ def load_golden():
     return {k: v for k, v in np.load(GOLDEN).items()}
 
 
+def load_golden_pgo():
+    """Second fixture (oracle/make_golden.py main_pgo): map maintenance around a loop closure + the after_pgo query."""
+    return {k: v for k, v in np.load(os.path.join(ROOT, "tests", "golden", "ref_kitti_pgo.npz")).items()}
+
+
 def golden_oracle_world(G):
     """Replay the fixture's inputs through the oracle: (state, decoder)."""
     p = O.MapParams(buffer_size=int(G["buffer_size"]))
