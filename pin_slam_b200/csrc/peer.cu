@@ -105,12 +105,9 @@ __global__ void __launch_bounds__(kPeerThreads) k_peer_exchange(PeerDev a) {
                     }
                     reinterpret_cast<float4*>(a.exp_avg)[i] = m;
                     reinterpret_cast<float4*>(a.exp_avg_sq)[i] = q;
-                    const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
-                    for (int p = 0; p < W; ++p) {
+                    for (int p = 0; p < W; ++p)
                         __stcg(reinterpret_cast<float4*>(a.block[p]) + a.par_off4 + i, w);  // parameter broadcast
-                        __stcg(reinterpret_cast<float4*>(a.block[p]) + a.sum_off4 + i, z);  // zero_grad on every replica
-                    }
                 } else {
 #pragma unroll
                     for (int p = 0; p < W; ++p) __stcg(reinterpret_cast<float4*>(a.block[p]) + a.sum_off4 + i, s);
@@ -133,6 +130,13 @@ __global__ void __launch_bounds__(kPeerThreads) k_peer_exchange(PeerDev a) {
         }
     }
     peer_barrier(a, a.phase + 1);  // every slice has landed in this rank's block
+    if (ADAM) {
+        // zero_grad: every rank clears its OWN gradient block once all owners have read it (local stores at HBM speed
+        // instead of W - 1 remote zero streams over the links)
+        float4* g = reinterpret_cast<float4*>(a.block[a.rank]) + a.sum_off4;
+        const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int64_t i = tid; i < a.nadam4; i += nthr) __stcg(g + i, z);
+    }
 }
 
 template <int W>
