@@ -37,11 +37,12 @@ UNIT = "queries/s"
 
 # kernels of libpinq launched by one step (fused forward + backward of a binned training-mode batch):
 # k_bin_count, k_bin_tile_sums, k_bin_tile_scan, k_bin_tile_apply, k_bin_scatter, k_stencil_masks, k_search_brick,
-# k_decode_mma, k_bwd_mma (the resolve step and the certainty scatter run in the tail of k_search_brick unless the
-# caller asks for the queried certainty).  profiles/*_launches.csv is the ncu list of the same command.
-LAUNCHES_PER_STEP = 9
+# k_decode_tc, k_bwd_tc (the resolve step and the certainty scatter run in the tail of k_search_brick unless the
+# caller asks for the queried certainty; through NeuralPoints k_stencil_masks runs once per stencil, not per step:
+# 8 launches per step, as in profiles/r2n_launches.csv, the ncu list of the same command).
+LAUNCHES_PER_STEP = 8
 KERNEL_NAMES = {"bin": "k_bin_* (5 kernels)", "search": "k_search_brick", "resolve": "k_resolve",
-                "decode": "k_decode_mma", "scatter": "k_certainty_scatter", "bwd": "k_bwd_mma"}
+                "decode": "k_decode_tc", "scatter": "k_certainty_scatter", "bwd": "k_bwd_tc"}
 
 
 def ncu_traffic():

@@ -174,7 +174,10 @@ class PeerExchange:
         import ctypes as C
         from . import _pinq as P
         self.P, self.lib, self.layout, self.device = P, P.load(), layout, torch.device(device)
-        self.grid, self.timeout_ms = int(grid), float(timeout_ms)
+        import os
+        self.grid = int(grid)
+        # a rank that does not arrive within this bound makes the kernel give up and set the block's error word
+        self.timeout_ms = float(timeout_ms) if timeout_ms else float(os.environ.get("PINQ_PEER_TIMEOUT_MS", "0"))
         self.simulated = simulate_world > 0
         self._mapped, self._owned = [], []
         with torch.cuda.device(self.device):
@@ -390,6 +393,12 @@ class DataParallelMapping:
         peer.P.check(peer.lib.pinq_peer_exchange(a, peer.P.stream()))
         npts.local_point_certainties = moved["cert_before"] + carve.cert_delta
         npts.local_point_ts_update.copy_(carve.ts_update)
-        for t, h in zip(moved["tensors"], moved["home"]):  # parameters back into torch-owned memory
-            h.copy_(t.data)
-            t.data = h
+        self.abort(moved)
+
+    @staticmethod
+    def abort(moved):
+        """Parameters (with whatever values they hold now) back into the torch-owned memory they came from."""
+        for t, h in zip(moved["tensors"], moved["home"]):
+            if t.data.data_ptr() != h.data_ptr():
+                h.copy_(t.data)
+                t.data = h

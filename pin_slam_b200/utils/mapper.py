@@ -467,7 +467,12 @@ class Mapper:
             exp_avg, exp_avg_sq = moments[:nf + dec_n], moments[(nf + dec_n + 3) // 4 * 4: (nf + dec_n + 3) // 4 * 4 + nf + dec_n]
             pa = dp.peer_args(iters, n_grad=nf + dec_n, exp_avg=exp_avg, exp_avg_sq=exp_avg_sq)
             m.peer = C.pointer(pa)
-        P.check(lib.pinq_mapping_run(m, int(iters), P.stream()))
+        try:
+            P.check(lib.pinq_mapping_run(m, int(iters), P.stream()))
+        except Exception:
+            if dp is not None:
+                dp.abort(moved)  # parameters back into torch-owned memory before the error travels up
+            raise
         if dp is not None:
             dp.end(npts, self.geo_mlp if decoder else None, moved)  # certainty / ts_update exchange, parameters back home
         self.total_iter += iters

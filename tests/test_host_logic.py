@@ -93,3 +93,47 @@ def test_oracle_tracking_converges_on_analytic_plane():
     H, b, _ = O.gauss_newton_system(pts, torch.tensor([[0.0, 0.0, 1.0]]).repeat(500, 1), pts[:, 2], torch.ones(500, 1), 0.0)
     t = torch.linalg.pinv(H.double()) @ b.double()  # planar field: rank 3
     assert abs(float(t[5]) + 0.05) < 1e-5  # moves the points down by 5 cm
+
+
+def test_peer_layout_and_mapping_carve_arithmetic():
+    """Peer-block layout (pin_slam_b200/parallel.py): regions on 256-byte boundaries behind the signal pad, capacity covers
+    the carve of one data-parallel mapping iteration (no CUDA needed for the arithmetic)."""
+    from pin_slam_b200 import _pinq as P
+    from pin_slam_b200.parallel import MappingPeer, PeerLayout, _align
+
+    class Dec:
+        def fused_params(self):
+            import torch
+            return [torch.empty(64, 11), torch.empty(64), torch.empty(1, 64), torch.empty(1)]
+
+    for rows in (2, 1001, 34176, 2184854):
+        L = MappingPeer.capacity(rows, 8, Dec(), with_params=True)
+        assert L.sum_off == P.PEER_PAD_BYTES and L.sum_off % 256 == 0 and L.param_off % 256 == 0 and L.max_off % 256 == 0
+        assert L.param_off == L.sum_off + 4 * L.n_sum and L.max_off == L.param_off + 4 * L.n_param
+        assert L.nbytes >= L.max_off + 8 * L.n_max and L.nbytes % 256 == 0
+        n_grad = rows * 8 + 833
+        cert_off = _align(n_grad, 4)
+        assert L.n_param >= _align(n_grad, 4)                      # fused Adam: parameters fit the parameter region
+        assert cert_off + _align(rows - 1, 4) <= L.n_sum           # certainty increments behind the gradients
+        assert _align(rows - 1, 2) <= L.n_max                      # ts_update
+    assert PeerLayout(4, 2, 0).n_param == 0
+    assert P.PEER_PAD_BYTES >= P.PEER_MAX_GRID * 8 * 4 + 4         # flags [grid][8] + error word
+
+
+def test_data_parallel_draw_slices_tile_the_global_batch():
+    """The slices Mapper._mapping_fused cuts out of the global draws: history and new-sample parts of every rank tile the
+    global row, and the ranks' eikonal subsets are exactly the global batch's x[::decimation]."""
+    from pin_slam_b200.parallel import shard_range
+    for bs, bs_new, world, decim in ((2048, 256, 2, 10), (2048, 256, 4, 10), (16384, 2000, 8, 10), (1000, 0, 8, 7), (64, 64, 4, 10)):
+        bs_hist = bs - bs_new
+        hist_cover, new_cover, eik = [], [], []
+        for r in range(world):
+            first, last = shard_range(bs, r, world)
+            hist_cover += list(range(min(first, bs_hist), min(last, bs_hist)))
+            new_cover += list(range(max(first, bs_hist) - bs_hist, max(last, bs_hist) - bs_hist))
+            start = (decim - first % decim) % decim
+            n_local = last - first
+            ng = (n_local - start + decim - 1) // decim if start < n_local else 0
+            eik += [first + start + j * decim for j in range(ng)]
+        assert hist_cover == list(range(bs_hist)) and new_cover == list(range(bs_new))
+        assert eik == list(range(0, bs, decim))
