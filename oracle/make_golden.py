@@ -8,6 +8,7 @@ The reference publishes no golden vectors; these files pin
 (oracle/pin_oracle.py) -- and through it the CUDA path -- to the reference's own outputs on the GPU box,
 where /root/reference does not exist.
 """
+import importlib
 import os
 import sys
 
@@ -243,7 +244,70 @@ def main_pgo():
     print("wrote", path, os.path.getsize(path) // 1024, "KiB;", npts.count(), "neural points after prune + compaction")
 
 
+def main_frames():
+    """Third fixture: the per-frame data path of the mapper -- DataSampler.sample on a seeded RNG and three
+    Mapper.process_frame calls (sampling, map update, replay-pool append + window filter, new-sample certainty query) of the
+    unmodified reference.  The sampler's per-frame outputs are recorded by wrapping the bound method (instrumentation only)."""
+    import types
+    torch.set_num_threads(1)
+    ns = ref_shim.load()
+    cfg = ref_shim.kitti_config("cpu")
+    cfg.buffer_size = 2_000_003
+    cfg.window_radius = 14.0     # small enough that the moving sensor drops old samples from the pool
+    cfg.silence = True
+    cfg.pgo_on = False           # no pose graph in this repo's harness (DESIGN.md section 6): poses = odometry
+    out = {"buffer_size": np.int64(cfg.buffer_size), "window_radius": np.float64(cfg.window_radius)}
+    # ---- DataSampler.sample (utils/data_sampler.py:20-192) on torch.manual_seed(5)
+    sampler = importlib.import_module("utils.data_sampler").DataSampler(cfg)
+    pts = torch.from_numpy(synth.surface_points(300, 40.0, seed=300))
+    torch.manual_seed(5)
+    coord, label, _, _, _, weight = sampler.sample(pts, None, None, None)
+    out["s_points"], out["s_coord"], out["s_label"], out["s_weight"] = pts.numpy(), coord.numpy(), label.numpy(), weight.numpy()
+    # ---- three frames through Mapper.process_frame (utils/mapper.py:110-321)
+    torch.manual_seed(42)
+    dec = ns.Decoder(cfg, 64, 1, 1)
+    npts = ns.NeuralPoints(cfg)
+    npts.travel_dist = torch.tensor([0.0, 3.0, 6.0])
+    dataset = types.SimpleNamespace(odom_poses=[np.eye(4)], gt_pose_provided=False, stop_status=False)
+    mp = ns.Mapper(cfg, dataset, npts, dec, None, None)
+    rec = []
+    inner = mp.sampler.sample
+
+    def recording_sample(*a, **k):
+        r = inner(*a, **k)
+        rec.append((r[0].clone(), r[1].clone(), r[5].clone()))
+        return r
+    mp.sampler.sample = recording_sample
+    for f in range(3):
+        p = synth.surface_points(2500, 40.0, seed=310 + f)
+        pose = torch.eye(4, dtype=torch.float64)
+        pose[0, 3] = 3.0 * f
+        pose[1, 3] = 0.5 * f
+        local = (torch.from_numpy(p).double() - pose[:3, 3]).float()   # sensor-frame scan (identity rotation)
+        torch.manual_seed(100 + f)
+        mp.process_frame(local, None, pose, f, False)
+        dataset.odom_poses.append(pose.numpy())
+        out["f%d_scan" % f], out["f%d_pose" % f] = local.numpy(), pose.numpy()
+        out["f%d_coord" % f], out["f%d_label" % f], out["f%d_weight" % f] = (t.numpy() for t in rec[f])
+        out["f%d_pool_coord" % f] = mp.coord_pool.numpy().copy()
+        out["f%d_pool_global" % f] = mp.global_coord_pool.numpy().copy()
+        out["f%d_pool_label" % f] = mp.sdf_label_pool.numpy().copy()
+        out["f%d_pool_weight" % f] = mp.weight_pool.numpy().copy()
+        out["f%d_pool_ts" % f] = mp.time_pool.numpy().copy()
+        out["f%d_counts" % f] = np.array([mp.cur_sample_count, mp.pool_sample_count], dtype=np.int64)
+        out["f%d_new_idx" % f] = mp.new_idx.numpy().copy()
+        out["f%d_map_points" % f] = npts.neural_points.numpy().copy()
+    path = os.path.join(OUT, "ref_kitti_frames.npz")
+    np.savez_compressed(path, **out)
+    print("wrote", path, os.path.getsize(path) // 1024, "KiB; pool", mp.pool_sample_count, "of", sum(r[0].shape[0] for r in rec), "samples kept")
+
+
 if __name__ == "__main__":
-    if "--pgo-only" not in sys.argv:
+    only = [a for a in sys.argv[1:] if a.startswith("--only=")]
+    which = only[0].split("=")[1].split(",") if only else ["small", "pgo", "frames"]
+    if "small" in which:
         main()
-    main_pgo()
+    if "pgo" in which:
+        main_pgo()
+    if "frames" in which:
+        main_frames()

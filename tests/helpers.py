@@ -97,6 +97,11 @@ def load_golden():
     return {k: v for k, v in np.load(GOLDEN).items()}
 
 
+def load_golden_frames():
+    """Third fixture (oracle/make_golden.py main_frames): DataSampler.sample and three Mapper.process_frame calls."""
+    return {k: v for k, v in np.load(os.path.join(ROOT, "tests", "golden", "ref_kitti_frames.npz")).items()}
+
+
 def load_golden_pgo():
     """Second fixture (oracle/make_golden.py main_pgo): map maintenance around a loop closure + the after_pgo query."""
     return {k: v for k, v in np.load(os.path.join(ROOT, "tests", "golden", "ref_kitti_pgo.npz")).items()}
