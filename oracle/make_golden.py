@@ -109,6 +109,20 @@ def main():
                                                              0.0, 1e3, cfg.reg_GM_dist_m, cfg.reg_GM_grad, cfg.reg_lm_lambda)
     out["reg_src"], out["reg_T"] = src.numpy(), Tr.numpy()
     out["reg_valid"], out["reg_res_cm"] = np.int64(valid_pts.shape[0]), np.float64(res_cm)
+    # ---- the whole Gauss-Newton loop, Tracker.tracking (utils/tracker.py:39-174): 3 iterations from a perturbed pose with
+    # relaxed validity gates (random features: rough field), then once with run_kitti's own gates
+    init = torch.eye(4, dtype=torch.float64)
+    init[:3, 3] = torch.tensor([0.02, -0.01, 0.005], dtype=torch.float64)
+    keep = (cfg.reg_iter_n, cfg.reg_min_grad_norm, cfg.reg_max_grad_norm, cfg.max_sdf_std_ratio)
+    cfg.reg_iter_n, cfg.reg_min_grad_norm, cfg.reg_max_grad_norm, cfg.max_sdf_std_ratio = 3, 0.0, 1e3, 1e3
+    T1, _, _, v1 = trk.tracking(src.clone(), init.clone())
+    cfg.reg_min_grad_norm, cfg.reg_max_grad_norm, cfg.max_sdf_std_ratio = keep[1:]
+    T2, _, _, v2 = trk.tracking(src.clone(), init.clone())
+    cfg.reg_iter_n = keep[0]
+    out["trk_init"] = init.numpy()
+    out["trk_T_relaxed"], out["trk_valid_relaxed"] = T1.numpy(), np.int64(bool(v1))
+    out["trk_T_default"], out["trk_valid_default"] = T2.numpy(), np.int64(bool(v2))
+    print("tracking valid (relaxed, default):", bool(v1), bool(v2))
     # ---- mapping loss + gradients (utils/mapper.py:461-573), training-mode side effects included
     mp = ns.Mapper(cfg, None, npts, dec, None, None)
     n = 1024
@@ -297,6 +311,18 @@ def main_frames():
         out["f%d_counts" % f] = np.array([mp.cur_sample_count, mp.pool_sample_count], dtype=np.int64)
         out["f%d_new_idx" % f] = mp.new_idx.numpy().copy()
         out["f%d_map_points" % f] = npts.neural_points.numpy().copy()
+    # ---- Mapper.mapping (utils/mapper.py:425-593): four iterations incl. get_batch's draws and the Adam steps
+    cfg.bs, cfg.bs_new_sample = 2048, 256
+    mp.train_less = False
+    out["map_bs"], out["map_bs_new"], out["map_iters"], out["map_seed"] = np.int64(2048), np.int64(256), np.int64(4), np.int64(77)
+    out["map_features_before"] = npts.geo_features.detach().numpy().copy()
+    torch.manual_seed(77)
+    mp.mapping(4)
+    out["map_features_after"] = npts.geo_features.detach().numpy().copy()
+    out["map_certainties_after"] = npts.point_certainties.numpy().copy()
+    out["map_ts_update_after"] = npts.point_ts_update.numpy().copy()
+    for k, t in zip(("W1", "b1", "W2", "b2"), (dec.layers[0].weight, dec.layers[0].bias, dec.lout.weight, dec.lout.bias)):
+        out["map_%s_after" % k] = t.detach().numpy().copy()
     path = os.path.join(OUT, "ref_kitti_frames.npz")
     np.savez_compressed(path, **out)
     print("wrote", path, os.path.getsize(path) // 1024, "KiB; pool", mp.pool_sample_count, "of", sum(r[0].shape[0] for r in rec), "samples kept")

@@ -132,3 +132,27 @@ def test_h13_out_of_radius_candidates(world):
     finally:
         m.local_map_radius = old
         m.reset_local_map(torch.tensor([6.0, 0.0, 0.0]).cuda(), torch.eye(3).cuda(), 2)
+
+
+@pytest.mark.parametrize("device_loop", [True, False])
+def test_tracking_loop(world, device_loop):
+    """Tracker.tracking against the reference's own loop output (utils/tracker.py:39-174): three Gauss-Newton iterations on
+    the device-side loop (pinq_tracking_run) and on the per-iteration host loop; then run_kitti's validity gates on the same
+    rough field -> invalid, the initial guess comes back."""
+    from pin_slam_b200.utils.tracker import Tracker
+    G, m, dec, cfg = world
+    src, init = T(G["reg_src"]).cuda(), T(G["trk_init"]).cuda()
+    old = (cfg.reg_iter_n, cfg.reg_min_grad_norm, cfg.reg_max_grad_norm, cfg.max_sdf_std_ratio)
+    try:
+        cfg.reg_iter_n, cfg.reg_min_grad_norm, cfg.reg_max_grad_norm, cfg.max_sdf_std_ratio = 3, 0.0, 1e3, 1e3
+        trk = Tracker(cfg, m, dec, None, None)
+        trk.device_loop = device_loop
+        Tr, _, _, valid = trk.tracking(src, init)
+        assert valid == bool(G["trk_valid_relaxed"]) and trk.last_iterations == 3
+        assert np.allclose(Tr.cpu().numpy(), G["trk_T_relaxed"], rtol=1e-3, atol=2e-4)
+        cfg.reg_min_grad_norm, cfg.reg_max_grad_norm, cfg.max_sdf_std_ratio = old[1:]
+        Td, _, _, valid_d = trk.tracking(src, init)
+        assert valid_d == bool(G["trk_valid_default"])
+        assert np.array_equal(Td.cpu().numpy(), G["trk_T_default"])
+    finally:
+        cfg.reg_iter_n, cfg.reg_min_grad_norm, cfg.reg_max_grad_norm, cfg.max_sdf_std_ratio = old

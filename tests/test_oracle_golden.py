@@ -129,3 +129,19 @@ def test_h13_out_of_radius_candidates_map_to_local_row_1(world):
     out = O.query_sdf(s2, d, q, None, False, True, want_grad=True)
     assert rel_err(out["sdf"], T(G["h13_sdf"])) < 1e-6
     assert rel_err(out["grad"], T(G["h13_grad"])) < 1e-6
+
+
+def test_tracking_loop(world):
+    """Tracker.tracking of the reference (utils/tracker.py:39-174): three Gauss-Newton iterations with relaxed validity gates
+    (valid), and run_kitti's own gates on the same rough field (too few valid points: the initial guess comes back)."""
+    G, s, d = world
+    init = T(G["trk_init"])
+    Tr, valid, it, _ = O.tracking(s, d, T(G["reg_src"]), init, iter_n=3, min_grad_norm=0.0, max_grad_norm=1e3,
+                                  GM_dist=0.2, GM_grad=0.1, lm_lambda=1e-4, max_sdf_std=1e3 * 0.25)
+    assert valid == bool(G["trk_valid_relaxed"]) and valid and it == 3
+    assert np.allclose(Tr.numpy(), G["trk_T_relaxed"], rtol=1e-5, atol=1e-7)
+    assert np.abs(G["trk_T_relaxed"] - G["trk_init"]).max() > 1e-3      # the loop moved the pose
+    Td, valid_d, _, _ = O.tracking(s, d, T(G["reg_src"]), init, iter_n=3, min_grad_norm=0.5, max_grad_norm=2.0,
+                                   GM_dist=0.2, GM_grad=0.1, lm_lambda=1e-4, max_sdf_std=0.25 * 1.0)
+    assert valid_d == bool(G["trk_valid_default"]) and not valid_d
+    assert np.array_equal(Td.numpy(), G["trk_T_default"]) and np.array_equal(G["trk_T_default"], G["trk_init"])

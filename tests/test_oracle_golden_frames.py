@@ -77,3 +77,29 @@ def test_pool_update_torch_formulation_matches_the_reference():
         assert torch.equal(mp.coord_pool, T(G["f%d_pool_coord" % f])) and torch.equal(mp.time_pool, T(G["f%d_pool_ts" % f]))
         assert torch.equal(mp.sdf_label_pool, T(G["f%d_pool_label" % f])) and torch.equal(mp.weight_pool, T(G["f%d_pool_weight" % f]))
         assert float((mp.global_coord_pool - T(G["f%d_pool_global" % f])).abs().max()) < 1e-5
+
+
+def test_oracle_mapping_iterations_match_the_reference():
+    """Mapper.mapping(4) of the reference after the three frames (get_batch's draws on torch.manual_seed(77), BCE + eikonal
+    loss, Adam, write-back).  Adam with eps 1e-15 turns rounding noise of a near-zero gradient into +-lr steps, so the
+    comparison is: where the reference moved a feature, the oracle lands within 1e-4 for all but a few per cent."""
+    from oracle.slam_oracle import OracleSLAM
+    G = load_golden_frames()
+    cfg = _cfg(G)
+    slam = OracleSLAM(cfg, _Replay(G), torch.Generator().manual_seed(0))
+    slam.s.travel_dist = torch.tensor([0.0, 3.0, 6.0])
+    for f in range(3):
+        slam.process_frame(T(G["f%d_scan" % f]), G["f%d_pose" % f], f)
+    assert torch.equal(slam.s.feats, T(G["map_features_before"]))
+    cfg.bs, cfg.bs_new_sample = int(G["map_bs"]), int(G["map_bs_new"])
+    slam.gen = torch.Generator().manual_seed(int(G["map_seed"]))
+    slam.mapping(int(G["map_iters"]))
+    ref, before = T(G["map_features_after"]), T(G["map_features_before"])
+    moved = (ref - before).abs() > 0
+    assert float(moved.float().mean()) > 0.01
+    assert torch.equal((slam.s.feats - before).abs() > 0, moved)                      # the same rows were trained
+    assert float(((slam.s.feats - ref).abs() > 1e-4)[moved].float().mean()) < 0.03
+    for k, t in zip(("W1", "b1", "W2", "b2"), slam.d.tensors()):
+        assert float((t.detach() - T(G["map_%s_after" % k])).abs().max()) < 2e-3, k
+    assert float((slam.s.certainty - T(G["map_certainties_after"])).abs().max()) < 1e-3
+    assert torch.equal(slam.s.ts_update, T(G["map_ts_update_after"]))
