@@ -161,6 +161,19 @@ def main():
     out["h13_fv"], out["h13_w"], out["h13_nn"] = fv.detach().numpy(), w.detach().numpy(), nn.numpy().astype(np.int32)
     out["h13_sdf"], out["h13_grad"], out["h13_qc"] = sdf.detach().numpy(), grad.detach().numpy(), qc.numpy()
     out["h13_local_count"] = np.int64(npts.local_count())
+    # ---- Mesher.get_query_from_bbx + query_points (utils/mesher.py:138-180, 41-136): dense grid over a sub-volume,
+    # global query (no time filter), mask = nn_count >= mesh_min_nn
+    import types
+    mesher = importlib.import_module("utils.mesher").Mesher(cfg, npts, dec, None, None)
+    lo, hi = np.array([2.0, -4.0, -2.0]), np.array([9.1, 3.3, 1.05])
+    bbx = types.SimpleNamespace(get_min_bound=lambda: lo.copy(), get_max_bound=lambda: hi.copy())
+    coord, num_xyz, origin = mesher.get_query_from_bbx(bbx, 0.2, 1, 0)
+    sdf_pred, _, _, mc_mask = mesher.query_points(coord, 4096, True, False, False, True, False, 8)
+    out["mesh_lo"], out["mesh_hi"], out["mesh_voxel"], out["mesh_min_nn"] = lo, hi, np.float64(0.2), np.int64(8)
+    out["mesh_num_xyz"], out["mesh_origin"] = np.asarray(num_xyz, dtype=np.int64), np.asarray(origin, dtype=np.float64)
+    out["mesh_coord_first_last"] = np.stack((coord[0].numpy(), coord[-1].numpy()))
+    out["mesh_sdf"], out["mesh_mask"] = np.asarray(sdf_pred, dtype=np.float32), np.asarray(mc_mask).astype(np.uint8)
+    print("mesher grid", num_xyz, "inside fraction", float(np.mean(out["mesh_mask"])))
     os.makedirs(OUT, exist_ok=True)
     path = os.path.join(OUT, "ref_kitti_small.npz")
     np.savez_compressed(path, **out)

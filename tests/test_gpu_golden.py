@@ -156,3 +156,24 @@ def test_tracking_loop(world, device_loop):
         assert np.array_equal(Td.cpu().numpy(), G["trk_T_default"])
     finally:
         cfg.reg_iter_n, cfg.reg_min_grad_norm, cfg.reg_max_grad_norm, cfg.max_sdf_std_ratio = old
+
+
+@pytest.mark.parametrize("world_size", [1, 3])
+def test_mesher_grid(world, world_size):
+    """Mesher against the reference's own grid query (utils/mesher.py:41-180): the API form (materialised coordinates) and
+    the sharded in-kernel form (pinq_mesher_grid_query; concatenated rank ranges == the reference's full grid)."""
+    from pin_slam_b200.utils.mesher import Mesher
+    G, m, dec, cfg = world
+    mesher = Mesher(cfg, m, dec, None, None)
+    lo, hi, voxel, min_nn = G["mesh_lo"], G["mesh_hi"], float(G["mesh_voxel"]), int(G["mesh_min_nn"])
+    coord, num, origin = mesher.get_query_from_bbx((lo, hi), voxel, 1, 0)
+    assert [int(v) for v in num] == G["mesh_num_xyz"].tolist() and np.array_equal(origin, G["mesh_origin"])
+    assert torch.equal(torch.stack((coord[0], coord[-1])).cpu(), T(G["mesh_coord_first_last"]))
+    sdf, _, _, mask = mesher.query_points(coord, 4096, True, False, False, True, False, min_nn)
+    assert np.array_equal(mask.astype(np.uint8), G["mesh_mask"])
+    assert rel_err(torch.from_numpy(sdf), T(G["mesh_sdf"])) < 1e-5
+    parts = [mesher.query_grid(lo, hi, voxel, pad_voxel=1, mask_min_nn_count=min_nn, rank=r, world=world_size) for r in range(world_size)]
+    sdf_g = torch.cat([p[0] for p in parts]).cpu()
+    mask_g = torch.cat([p[1] for p in parts]).cpu()
+    assert torch.equal(mask_g, T(G["mesh_mask"]))
+    assert rel_err(sdf_g, T(G["mesh_sdf"])) < 1e-5

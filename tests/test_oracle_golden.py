@@ -145,3 +145,16 @@ def test_tracking_loop(world):
                                    GM_dist=0.2, GM_grad=0.1, lm_lambda=1e-4, max_sdf_std=0.25 * 1.0)
     assert valid_d == bool(G["trk_valid_default"]) and not valid_d
     assert np.array_equal(Td.numpy(), G["trk_T_default"]) and np.array_equal(G["trk_T_default"], G["trk_init"])
+
+
+def test_mesher_grid(world):
+    """Mesher.get_query_from_bbx + query_points of the reference (utils/mesher.py:138-180, 41-136): grid geometry, z-fastest
+    order, forward-only global query, mask = nn_count >= min_nn."""
+    G, s, d = world
+    coord, num, origin = O.grid_coords(G["mesh_lo"], G["mesh_hi"], float(G["mesh_voxel"]), 1, 0)
+    assert num.tolist() == G["mesh_num_xyz"].tolist() and np.array_equal(origin, G["mesh_origin"])
+    assert torch.equal(torch.stack((coord[0], coord[-1])), T(G["mesh_coord_first_last"]))
+    sdf, mask = O.mesher_query(s, d, coord, int(G["mesh_min_nn"]), False)
+    assert torch.equal(mask, T(G["mesh_mask"]).bool())
+    assert 0.2 < float(mask.float().mean()) < 0.9
+    assert rel_err(sdf, T(G["mesh_sdf"])) < 1e-6
