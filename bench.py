@@ -65,6 +65,7 @@ def parse():
     ap.add_argument("--surface-points", type=int, default=9_000_000, help="raw surface samples -> ~1 M neural points")
     ap.add_argument("--side", type=float, default=350.0)
     ap.add_argument("--cpu-sample", type=int, default=200_000, help="queries per CPU-baseline step")
+    ap.add_argument("--eager-sample", type=int, default=1 << 20, help="queries per step of the reference CUDA-eager comparator")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--slam-seeded", action="store_true", help="SLAM leg: a seeded CPU generator for the sampler and the batch draws "
@@ -199,73 +200,84 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------------------------
-def oracle_state_from(npts, dec):
-    """CPU oracle state holding the same map as the CUDA path (only the cpu_baseline / reference legs use it)."""
-    from oracle import pin_oracle as O
+def reference_legs(args, npts, dec, q_host, ts_host):
+    """Comparator legs of the GPU arm (N = 1, rank 0), both running the UNMODIFIED reference (oracle/_ref through
+    oracle/ref_shim.py) on the very map the CUDA path just used: (1) cpu_baseline -- its CPU path on the host cores on a
+    bounded sample; (2) reference_cuda_eager -- the same code with device = cuda on this B200 (stock PyTorch eager), the
+    comparator a user of the reference would run."""
+    from oracle import ref_bench, ref_shim
 
-    p = O.MapParams(local_map_radius=float(npts.local_map_radius))
-    s = O.MapState(p=p)
-    s.table = npts.buffer_pt_index.cpu()
-    s.points = npts.neural_points.cpu()
-    s.quats = npts.point_orientations.cpu()
-    s.feats = npts.geo_features.cpu()
-    s.ts_create = npts.point_ts_create.cpu()
-    s.ts_update = npts.point_ts_update.cpu()
-    s.certainty = npts.point_certainties.cpu()
-    s.travel_dist = npts.travel_dist.cpu()
-    O.set_search_neighborhood(s, p.num_nei_cells, p.search_alpha)
-    O.reset_local_map(s, torch.zeros(3), 0)
-    d = O.DecoderParams(*[t.detach().cpu().clone() for t in dec.fused_params()], sdf_scale=dec.sdf_scale)
-    return O, s, d
-
-
-def cpu_step(O, s, d, x, ts):
-    """fwd + bwd of the reference's PyTorch path (restated) on the host cores."""
-    s.l_feats = s.l_feats.detach().requires_grad_(True)
-    dp = O.DecoderParams(*[t.detach().requires_grad_(True) for t in d.tensors()], sdf_scale=d.sdf_scale)
-    out = O.query_sdf(s, dp, x, ts, True, True)
-    out["sdf"].backward(torch.ones_like(out["sdf"]))
-    return out["sdf"]
-
-
-def time_cpu(O, s, d, q_cpu, ts_cpu, sample, steps, warmup):
-    torch.set_num_threads(os.cpu_count() or 1)
-    x, ts = q_cpu[:sample].contiguous(), ts_cpu[:sample].contiguous()
-    for _ in range(warmup):
-        cpu_step(O, s, d, x, ts)
-    t0 = time.perf_counter()
-    for _ in range(steps):
-        cpu_step(O, s, d, x, ts)
-    dt = (time.perf_counter() - t0) / max(steps, 1)
-    return sample / dt, dt
+    if not ref_shim.available():
+        return None, {"unavailable": "oracle/_ref not staged"}
+    state = {"buffer_pt_index": npts.buffer_pt_index, "travel_dist": npts.travel_dist}
+    for k in ("neural_points", "point_orientations", "geo_features", "point_ts_create", "point_ts_update", "point_certainties"):
+        state[k] = getattr(npts, k)
+    state["W1"], state["b1"], state["W2"], state["b2"] = [t.detach() for t in dec.fused_params()]
+    state = {k: v.detach().clone() for k, v in state.items()}
+    sample = min(args.cpu_sample, q_host.shape[0])
+    cpu = eager = None
+    try:
+        _, rn, rd = ref_bench.reference_map_from_state(state, "cpu")
+        qps, dt = ref_bench.time_reference(rn, rd, q_host[:sample].contiguous(), ts_host[:sample].contiguous(), 3, 1, "cpu")
+        cpu = {"value": qps, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "reference",
+               "sample": "%d queries of the same set, fwd+bwd, 3 steps after 1 warm-up: unmodified reference "
+                         "query_feature -> Decoder.sdf -> sum w s -> backward() on torch CPU fp32, same map" % sample}
+        del rn, rd
+    except Exception as e:
+        cpu = {"error": repr(e)[:300]}
+    try:
+        dev = str(npts.neural_points.device)
+        _, rn, rd = ref_bench.reference_map_from_state(state, dev)
+        ne = min(args.eager_sample, q_host.shape[0])
+        xe, te = q_host[:ne].to(dev), ts_host[:ne].to(dev)
+        qps, dt = ref_bench.time_reference(rn, rd, xe, te, 5, 2, dev)
+        eager = {"queries_per_s": qps, "ms_per_step": dt * 1e3, "queries_per_step": ne,
+                 "what": "unmodified reference query_feature -> Decoder.sdf -> sum w s -> backward(), device=cuda (PyTorch eager) "
+                         "on the same B200 and the same map, 5 steps after 2 warm-ups, host-synchronised wall clock"}
+        del rn, rd, xe, te
+        torch.cuda.empty_cache()
+    except Exception as e:
+        eager = {"error": repr(e)[:300]}
+    return cpu, eager
 
 
 def run_reference(args):
-    """--impl reference: the reference's own CPU implementation of the path (oracle restatement; the Python
-    reference tree does not travel to the GPU box) on all host threads, bounded sample of the same workload."""
+    """--impl reference: the UNMODIFIED reference (oracle/_ref = byte-for-byte copy of /root/reference staged by
+    oracle/make_ref.py, imported through oracle/ref_shim.py) on the host cores with all threads: the map is built by the
+    reference's own NeuralPoints.update, each step is query_feature -> Decoder.sdf -> sum_k w_k s_k -> backward() on a
+    bounded sample of the GPU arm's query set.  This process never imports pin_slam_b200._pinq (no libpinq.so)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    dev = "cuda" if torch.cuda.is_available() else None
-    if dev is None:
-        print(json.dumps({"impl": "reference", "unavailable": "map construction needs the CUDA path (no GPU visible)"}))
-        return
-    from pin_slam_b200 import synth
+    from oracle import ref_bench, ref_shim
+    from pin_slam_b200 import synth  # numpy-only generators shared with the GPU arm
 
-    cfg, npts, dec = build_map(args, dev)
-    q = torch.from_numpy(synth.microbench_queries(npts.neural_points.cpu().numpy(), max(args.cpu_sample, 1), seed=1))
-    ts = torch.zeros(q.shape[0], dtype=torch.int64)
-    O, s, d = oracle_state_from(npts, dec)
-    qps, dt = time_cpu(O, s, d, q, ts, args.cpu_sample, args.steps, args.warmup)
+    if not ref_shim.available():
+        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref not staged (run python oracle/make_ref.py in the build container)"}))
+        return
+    torch.set_num_threads(os.cpu_count() or 1)
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    raw = synth.surface_points(args.surface_points, args.side, seed=0)
+    cfg, npts, dec = ref_bench.build_reference_map(raw, "cpu")
+    del raw
+    m = int(npts.neural_points.shape[0])
+    q = torch.from_numpy(synth.microbench_queries(npts.neural_points.numpy(), args.queries, seed=1))  # rank 0's query set
+    vbar = ref_bench.mean_nonempty_slots(npts, q)
+    sample = min(args.cpu_sample, args.queries)
+    x, ts = q[:sample].contiguous(), torch.zeros(sample, dtype=torch.int64)
+    qps, dt = ref_bench.time_reference(npts, dec, x, ts, args.steps, args.warmup, "cpu")
     cores = torch.get_num_threads()
     line = {
         "impl": "reference", "metric": METRIC, "value": qps, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": workload_config(args, npts, None),
-        "cpu_baseline": {"value": qps, "unit": UNIT, "cores": cores, "kind": "port",
-                         "sample": "%d queries/step of the same query set, fwd+bwd, torch CPU fp32" % args.cpu_sample},
+        "config": workload_config(args, m, vbar, world),
+        "cpu_baseline": {"value": qps, "unit": UNIT, "cores": cores, "kind": "reference",
+                         "sample": "%d queries/step (the first of the GPU arm's %d), unmodified reference "
+                                   "NeuralPoints.query_feature -> Decoder.sdf -> sum w s -> backward(), torch CPU fp32, "
+                                   "map built by the reference's own update()" % (sample, args.queries)},
         "e2e": {"value": qps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "reference_root": os.path.relpath(ref_shim.REFERENCE_ROOT, ROOT) if ref_shim.REFERENCE_ROOT.startswith(ROOT) else ref_shim.REFERENCE_ROOT,
     }
     print(json.dumps(line))
 
@@ -306,15 +318,16 @@ def slam_leg(n_frames, device_rng=True):
             "note": "frames/s excludes the first frame (600 warm-up iterations)"}
 
 
-def workload_config(args, npts, vbar):
-    c = {"workload": "isolated SDF query microbench (BASELINE configs[2]): fwd+bwd, K=6, Kn=81, F=8, local+time filter, "
-                     "training mode, feature+decoder grads",
-         "neural_points": int(npts.count()), "queries_per_gpu": int(args.queries), "voxel_size_m": 0.4,
-         "buffer_size": int(npts.buffer_size), "l2_policy": "inputs larger than L2 (200 MB slot table + 48 MB queries "
-                                                           "+ 32 MB features per step)"}
-    if vbar is not None:
-        c["mean_nonempty_slots"] = round(vbar, 2)
-    return c
+def workload_config(args, m, vbar, world):
+    """The `config` object -- identical on both arms (the reference arm rebuilds the same map and query set on the host)."""
+    return {"workload": "isolated SDF query microbench (BASELINE configs[2]): fwd+bwd, K=6, Kn=81, F=8, local+time filter, "
+                        "training mode, feature+decoder grads",
+            "neural_points": int(m), "queries_per_gpu": int(args.queries), "voxel_size_m": 0.4,
+            "buffer_size": 50000000, "map_side_m": float(args.side), "surface_samples": int(args.surface_points),
+            "l2_policy": "inputs larger than L2 (200 MB slot table + 48 MB queries + 32 MB features per step)",
+            "mean_nonempty_slots": round(vbar, 2),
+            "reference_arm_queries_per_step": int(min(args.cpu_sample, args.queries)),
+            "parallelism": "replicated map, queries sharded x%d" % world}
 
 
 # ------------------------------------------------------------------------------------------------
@@ -493,26 +506,36 @@ def main():
     ms_f = sum(v for k, v in kms.items() if k != "bwd")
     ms_b = kms.get("bwd", 0.0)
     hbm, peak_kind = peaks()
-    # algorithmic bytes per query of each kernel (DESIGN.md "kernels"; SURVEY.md 8(d) for the whole path)
-    kbytes = {
-        "bin": 12 + 4 + 4 + 4,                 # xyz in, key out; key in, perm out (histogram stays in L2)
-        # perm, xyz, 16 B record + 4 B brick share per occupied stencil voxel; resolve tail: stage block out, nn_count,
-        # training side effects (certainty add 4 + ts max 8 per neighbour)
-        "search": 4 + 12 + 20 * vbar + 124 + 4 + K * 12,
-        "resolve": 4 + 12 + 28 + K * 16 + 124 + 4,   # (slot-probing path only) perm, xyz, ranks, K records, stage out, nn_count
-        "decode": 124 + K * 32 + 48 + 4 + 4,   # stage in, K feature rows, relu bits out, perm, sdf out
-        "scatter": K * (4 + 4 + 4 + 8),        # idx, w in; certainty and ts atomics
-        "bwd": 4 + 4 + 124 + 48 + K * 32 + K * 32,  # perm, dL/dsdf, stage, relu bits, K feature rows (decoder grads), K gradient rows
-    }
-    dom = max(kms, key=kms.get)
-    ach = n * kbytes[dom] / (kms[dom] * 1e-3) / 1e9
-    bytes_step = sum(kbytes[k] for k in kms)
-    roofline = {"bound": "hbm", "kernel": KERNEL_NAMES[dom], "achieved": ach, "peak": hbm,
-                "peak_kind": peak_kind + " (burst copy)", "unit": "GB/s", "frac": ach / hbm,
-                "traffic": ncu_traffic().get(dom), "bytes_per_query": kbytes[dom],
-                "kernel_ms": kms, "kernel_bytes_per_query": {k: kbytes[k] for k in kms},
+    # algorithmic bytes per query of the WHOLE path, each datum counted once with compact types:
+    # B_q(fwd+bwd) = 788 + 20 V-bar.  roofline.frac is reproducible from `value`, config.mean_nonempty_slots and
+    # MEASURED_PEAKS.json alone: frac = (value / n_gpus) * B_q / (hbm_gbs * 1e9).
+    bq = 788.0 + 20.0 * round(vbar, 2)
+    ach = (value / world) * bq / 1e9
+    # per kernel: measured time (CUDA events recorded by the library between its kernels on the launching stream), the
+    # DRAM bytes ncu measured for one launch of the same command (profiles/ncu_traffic.json, `ncu --set full`), and the
+    # unit that limits it according to that capture (profiles/*_ncu_full_summary.csv) -- none of them is DRAM-bound.
+    traffic = ncu_traffic()
+    limiter = {"bin": "launch latency (small kernels) + histogram atomics", "search": "instruction issue (integer walk + top-K), L1TEX",
+               "decode": "instruction issue (CUDA-core epilogue of the tcgen05 product)", "bwd": "shared-memory bandwidth (tile writes + UMMA operand reads)",
+               "resolve": "L2 gathers", "scatter": "L2 atomics"}
+    kernels = {}
+    for k, ms in kms.items():
+        e = {"kernel": KERNEL_NAMES[k], "ms": ms, "share_of_step": ms / (ms_f + ms_b), "limiter": limiter.get(k)}
+        if traffic.get(k):
+            e["ncu_dram_bytes_per_launch"] = traffic[k]
+            e["ncu_dram_bytes_queries"] = traffic.get("queries_per_launch", 4194304)
+            e["dram_gbs_at_measured_ms"] = traffic[k] * (n / e["ncu_dram_bytes_queries"]) / (ms * 1e-3) / 1e9
+            e["dram_frac_of_peak"] = e["dram_gbs_at_measured_ms"] / hbm
+        kernels[k] = e
+    tr = [traffic.get(k) for k in kms if traffic.get(k)]
+    roofline = {"bound": "hbm", "achieved": ach, "peak": hbm, "peak_kind": peak_kind + " (burst copy)", "unit": "GB/s",
+                "frac": ach / hbm, "traffic": float(sum(tr)) if tr else None,
+                "bytes_per_query": bq, "formula": "SURVEY 8(d): (788 + 20 * mean_nonempty_slots) B/query * queries/s per GPU / hbm_gbs",
+                "dominant_kernel": KERNEL_NAMES[max(kms, key=kms.get)], "kernels": kernels,
                 "ms_fwd_kernels": ms_f, "ms_bwd_kernel": ms_b,
-                "step_frac_of_hbm": n * bytes_step / ((ms_f + ms_b) * 1e-3) / 1e9 / hbm}
+                "note": "`traffic` = dram bytes read+written per step summed over the kernels (ncu capture of the same command); "
+                        "it is BELOW the algorithmic bytes because binned queries share candidate records and feature rows in L1/L2: "
+                        "the step is issue / shared-memory bound, not DRAM bound"}
 
     # ---- end to end through the public API with HOST buffers ---------------------------------------------
     e2e = None
@@ -578,13 +601,9 @@ def main():
         e2e = {"value": world * n / (float(te.item()) / args.steps * 1e-3), "unit": UNIT, "chunks": nchunk, "steps_pipelined": pipelined,
                "h2d_bytes_per_step": n * 12 + n * 8, "d2h_bytes_per_step": n * 4}
 
-    cpu_baseline = None
+    cpu_baseline = cuda_eager = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        O, s, d = oracle_state_from(npts, dec)
-        qps, dt = time_cpu(O, s, d, q_host, ts_host, min(args.cpu_sample, n), 3, 1)
-        cpu_baseline = {"value": qps, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
-                        "sample": "%d queries of the same set, fwd+bwd, 3 steps after 1 warm-up, torch CPU fp32 "
-                                  "restatement of the reference path" % min(args.cpu_sample, n)}
+        cpu_baseline, cuda_eager = reference_legs(args, npts, dec, q_host, ts_host)
 
     peer_err = peer.error() if peer is not None else 0
     slam = None
@@ -596,15 +615,16 @@ def main():
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
-                "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(args, npts, vbar),
+                "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(args, npts.count(), vbar, world),
                 "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e,
                 "gpu_launches": LAUNCHES_PER_STEP * args.steps, "clocks": clocks}
         if slam is not None:
             line["slam"] = slam
-        line["config"]["parallelism"] = "replicated map, queries sharded x%d%s" % (
-            world, {"none": "", "nccl": ", NCCL all-reduce of feature+decoder grads",
-                    "peer": ", feature+decoder grads summed by one peer-memory kernel per rank over NVLink "
-                            "(pinq_peer_exchange)"}[exchange])
+        if cuda_eager is not None:
+            line["reference_cuda_eager"] = cuda_eager
+        line["exchange"] = {"none": "none", "nccl": "NCCL all-reduce of feature+decoder grads",
+                            "peer": "feature+decoder grads summed by one peer-memory kernel per rank over NVLink "
+                                    "(pinq_peer_exchange)"}[exchange]
         if peer is not None:
             line["gpu_launches"] += args.steps
             line["peer_exchange_error"] = peer_err

@@ -408,8 +408,9 @@ int pinq_mapping_run(const pinq_mapping_args* args, int32_t iters, void* stream)
  *   barrier (flags in peer memory) -> this rank's 1/world slice: sum over all ranks' blocks (P2P loads)
  *   [-> Adam on the slice, optimizer state held by the slice owner only] -> result stored into every rank's block
  *   (P2P stores: summed gradients, or updated parameters + zeroed gradients) -> barrier.
- * Ranks must call it in lock-step with the same epoch (1, 2, 3, ...).  A peer that does not arrive within timeout_ms
- * sets the error word (pinq_peer_error_offset() bytes into the block, non-zero = failed) instead of hanging.
+ * Ranks must call it in lock-step with the same epoch (1, 2, 3, ...).  The flag barrier pairs CTA b of every rank, so
+ * all CTAs of the grid must be resident at once: set `cooperative` (launch-time guarantee).  A peer that does not arrive
+ * within timeout_ms sets the error word (pinq_peer_error_offset() bytes into the block, non-zero = failed) instead of hanging.
  * These are the only entry points that allocate or that touch other devices. */
 #define PINQ_PEER_MAX 8
 #define PINQ_PEER_HANDLE_BYTES 64
@@ -437,6 +438,10 @@ typedef struct pinq_peer_args {
     float* exp_avg_sq;
     float lr, beta1, beta2, adam_eps;
     int32_t adam_step;         /* 1-based                                                                */
+    int32_t cooperative;       /* non-zero: cudaLaunchCooperativeKernel -- all `grid` CTAs are guaranteed co-resident
+                                * (needed as soon as anything else may share the device, e.g. the next step's search
+                                * on another stream); 0: plain launch, the caller vouches for co-residency (several
+                                * simulated ranks in ONE process must use 0: their kernels wait for each other)     */
 } pinq_peer_args;
 int pinq_peer_exchange(const pinq_peer_args* args, void* stream);
 

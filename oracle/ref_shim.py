@@ -7,9 +7,11 @@ the build container so that its own classes can be executed on CPU to
   * generate the golden vectors committed under ``tests/golden/``
     (``oracle/make_golden.py``).
 
-``/root/reference`` does not exist on the GPU box, so nothing in ``-m gpu``
-tests, ``smoke()`` or ``bench.py`` may import this module; ``available()``
-lets CPU tests skip when the tree is absent.
+``/root/reference`` does not exist on the GPU box; there the shim falls back to
+``oracle/_ref/`` -- the byte-for-byte staged copy written by ``oracle/make_ref.py``
+(git-ignored, travels with the tree) -- which is what ``bench.py --impl reference``
+and the bench's CUDA-eager comparator time.  Nothing under ``pin_slam_b200/``
+imports this module; ``available()`` lets tests skip when no tree is present.
 
 What is stubbed: the reference does top-of-file imports
 of packages that are not installed here (open3d, matplotlib, roma, natsort,
@@ -27,7 +29,18 @@ import sys
 import time
 import types
 
-REFERENCE_ROOT = os.environ.get("PINQ_REFERENCE_ROOT", "/root/reference")
+def _find_root():
+    """$PINQ_REFERENCE_ROOT, else the read-only reference of the build container, else the byte-for-byte staged copy
+    oracle/_ref/ (oracle/make_ref.py; git-ignored, travels to the GPU box like libpinq.so)."""
+    env = os.environ.get("PINQ_REFERENCE_ROOT")
+    if env:
+        return env
+    if os.path.isdir("/root/reference/model"):
+        return "/root/reference"
+    return os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref")
+
+
+REFERENCE_ROOT = _find_root()
 
 _STUBBED = [
     "open3d", "matplotlib", "matplotlib.cm", "matplotlib.pyplot", "roma", "natsort",
@@ -107,7 +120,7 @@ def _patch_get_time():
     if torch.cuda.is_available():
         return
     for modname in ("utils.tools", "model.neural_points", "utils.tracker", "utils.mapper",
-                    "utils.data_sampler"):
+                    "utils.data_sampler", "utils.loop_detector", "dataset.slam_dataset", "pin_slam"):
         mod = sys.modules.get(modname)
         if mod is not None and hasattr(mod, "get_time"):
             mod.get_time = time.time

@@ -132,17 +132,34 @@ __global__ void __launch_bounds__(kPeerThreads) k_peer_exchange(PeerDev a) {
     peer_barrier(a, a.phase + 1);  // every slice has landed in this rank's block
     if (ADAM) {
         // zero_grad: every rank clears its OWN gradient block once all owners have read it (local stores at HBM speed
-        // instead of W - 1 remote zero streams over the links)
+        // instead of W - 1 remote zero streams over the links).  peer_barrier only orders CTA b of this rank after CTA b
+        // of the owners, so thread (b, t) may clear exactly the elements that thread (b, t) of owner p loaded:
+        // lo_p + tid + j * nthr.  (Clearing with i = tid + j * nthr raced with slower CTAs of the owner -- ADVICE r1.)
         float4* g = reinterpret_cast<float4*>(a.block[a.rank]) + a.sum_off4;
         const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
-        for (int64_t i = tid; i < a.nadam4; i += nthr) __stcg(g + i, z);
+#pragma unroll
+        for (int p = 0; p < W; ++p) {
+            const int64_t lo = a.nsum4 * p / W, hi0 = a.nsum4 * (p + 1) / W;
+            const int64_t hi = hi0 < a.nadam4 ? hi0 : a.nadam4;
+            for (int64_t i = lo + tid; i < hi; i += nthr) __stcg(g + i, z);
+        }
     }
 }
 
+// Cooperative launch: the flag barrier needs every CTA of the grid resident at the same time on every rank.  A plain
+// launch only has that by luck when another kernel shares the device (e.g. the next step's search on another stream);
+// cudaLaunchCooperativeKernel makes it a launch-time guarantee (or a launch error) instead of a barrier timeout.
 template <int W>
-static void launch_peer(const PeerDev& d, bool adam, int grid, cudaStream_t st) {
-    if (adam) k_peer_exchange<W, true><<<grid, kPeerThreads, 0, st>>>(d);
-    else k_peer_exchange<W, false><<<grid, kPeerThreads, 0, st>>>(d);
+static cudaError_t launch_peer(PeerDev& d, bool adam, bool cooperative, int grid, cudaStream_t st) {
+    if (!cooperative) {  // several simulated ranks in one process: their kernels wait for each other, the caller vouches
+        if (adam) k_peer_exchange<W, true><<<grid, kPeerThreads, 0, st>>>(d);
+        else k_peer_exchange<W, false><<<grid, kPeerThreads, 0, st>>>(d);
+        return cudaGetLastError();
+    }
+    void* args[] = {&d};
+    const void* fn = adam ? reinterpret_cast<const void*>(&k_peer_exchange<W, true>)
+                          : reinterpret_cast<const void*>(&k_peer_exchange<W, false>);
+    return cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(kPeerThreads), args, 0, st);
 }
 
 }  // namespace pinq
@@ -216,7 +233,7 @@ int pinq_peer_exchange(const pinq_peer_args* a, void* stream) {
                      "adam region: a multiple of 4 leading elements of the sum region, parameters 16-byte aligned");
         PINQ_REQUIRE(a->exp_avg && a->exp_avg_sq && a->adam_step >= 1, "adam state");
     }
-    int grid = a->grid > 0 ? a->grid : 148;  // one CTA per SM: all of them resident, which the flag barrier needs
+    int grid = a->grid > 0 ? a->grid : 148;  // one CTA per SM, launched cooperatively: co-residency is guaranteed
     PINQ_REQUIRE(grid <= PINQ_PEER_MAX_GRID, "grid too large for the signal pad");
     PeerDev d{};
     for (int p = 0; p < a->world; ++p) d.block[p] = reinterpret_cast<float*>(a->block[p]);
@@ -243,11 +260,17 @@ int pinq_peer_exchange(const pinq_peer_args* a, void* stream) {
     const double ms = a->timeout_ms > 0 ? a->timeout_ms : 5000.0;
     d.timeout_cycles = (long long)(ms * 1.9e6);  // SM clock ~1.9 GHz; a bound, not a measurement
     cudaStream_t st = as_stream(stream);
+    cudaError_t le;
     switch (a->world) {
-        case 1: launch_peer<1>(d, adam, grid, st); break;
-        case 2: launch_peer<2>(d, adam, grid, st); break;
-        case 4: launch_peer<4>(d, adam, grid, st); break;
-        default: launch_peer<8>(d, adam, grid, st); break;
+        case 1: le = launch_peer<1>(d, adam, a->cooperative != 0, grid, st); break;
+        case 2: le = launch_peer<2>(d, adam, a->cooperative != 0, grid, st); break;
+        case 4: le = launch_peer<4>(d, adam, a->cooperative != 0, grid, st); break;
+        default: le = launch_peer<8>(d, adam, a->cooperative != 0, grid, st); break;
+    }
+    if (le != cudaSuccess) {
+        set_error("pinq_peer_exchange: %slaunch of %d CTAs failed: %s", a->cooperative ? "cooperative " : "", grid, cudaGetErrorString(le));
+        cudaGetLastError();
+        return PINQ_ERR_CUDA;
     }
     return check_launch("pinq_peer_exchange");
 }

@@ -252,6 +252,7 @@ class PeerExchange:
             a.block[r] = b
         a.sum_off, a.n_sum, a.max_off, a.n_max = L.sum_off + 4 * sum_off_elems, n_sum, L.max_off, n_max
         a.epoch, a.grid, a.timeout_ms = epoch, self.grid, self.timeout_ms
+        a.cooperative = 0 if self.simulated else 1  # simulated ranks share one device and wait for each other
         if adam is not None:
             adam = dict(adam)
             adam.setdefault("n", L.n_param)
@@ -394,6 +395,14 @@ class DataParallelMapping:
         npts.local_point_certainties = moved["cert_before"] + carve.cert_delta
         npts.local_point_ts_update.copy_(carve.ts_update)
         self.abort(moved)
+        # a rank that never arrived at a barrier leaves partial sums / parameters behind: fail loudly (the parameters are
+        # back in torch-owned memory, so the caller can still inspect or checkpoint them)
+        # (simulated ranks of the tests are launched back to back from one host thread and meet on the device: no host
+        # synchronisation may sit between them, the test reads the error word itself)
+        err = 0 if peer.simulated else peer.error()
+        if err:
+            raise peer.P.PinqError("pinq_peer_exchange: barrier timeout in epoch %d of this mapping call -- a rank was late or "
+                                   "dead; the trained parameters of this call are not the data-parallel result" % (err >> 1))
 
     @staticmethod
     def abort(moved):
