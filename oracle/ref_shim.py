@@ -83,6 +83,38 @@ class _StubModule(types.ModuleType):
         return _Anything(self.__name__ + "." + item)
 
 
+# ---- real (not permissive) stand-ins for two third-party helpers the per-frame driver actually computes with ----------
+def _rotmat_slerp(R0, R1, steps):
+    """roma.rotmat_slerp (roma 1.4/1.5, `roma/utils.py`; un-vendored dependency of utils/tools.py:560): spherical linear
+    interpolation R(t) = R0 exp(t log(R0^T R1)) for every t in `steps` (extrapolates for t outside [0,1]; shortest arc).
+    roma goes through unit quaternions and a rotation vector; this is the same map written with Rodrigues' formula."""
+    import torch
+    Rrel = R0.transpose(-1, -2) @ R1
+    cos = ((Rrel[0, 0] + Rrel[1, 1] + Rrel[2, 2]) - 1.0) * 0.5
+    cos = torch.clamp(cos, -1.0, 1.0)
+    theta = torch.acos(cos)
+    w = torch.stack([Rrel[2, 1] - Rrel[1, 2], Rrel[0, 2] - Rrel[2, 0], Rrel[1, 0] - Rrel[0, 1]])
+    n = torch.linalg.norm(w)
+    axis = w / n if float(n) > 1e-12 else torch.tensor([1.0, 0.0, 0.0], dtype=R1.dtype, device=R1.device)
+    if float(n) <= 1e-12:
+        theta = torch.zeros((), dtype=R1.dtype, device=R1.device)
+    ang = steps.reshape(-1) * theta                                   # [N]
+    Kx = torch.zeros(3, 3, dtype=R1.dtype, device=R1.device)
+    Kx[0, 1], Kx[0, 2], Kx[1, 0], Kx[1, 2], Kx[2, 0], Kx[2, 1] = -axis[2], axis[1], axis[2], -axis[0], -axis[1], axis[0]
+    eye = torch.eye(3, dtype=R1.dtype, device=R1.device)
+    R = eye[None] + torch.sin(ang)[:, None, None] * Kx[None] + (1.0 - torch.cos(ang))[:, None, None] * (Kx @ Kx)[None]
+    return (R0[None] @ R).reshape(steps.shape + (3, 3))
+
+
+def _natsorted(seq, key=None, reverse=False, alg=None):
+    import re
+
+    def nat(s):
+        s = key(s) if key is not None else s
+        return [int(t) if t.isdigit() else t.lower() for t in re.split(r"(\d+)", str(s))]
+    return sorted(seq, key=nat, reverse=reverse)
+
+
 def available() -> bool:
     return os.path.isdir(os.path.join(REFERENCE_ROOT, "model"))
 
@@ -109,6 +141,10 @@ def install():
         if "." in name:
             parent, child = name.rsplit(".", 1)
             setattr(sys.modules[parent], child, mod)
+        if name == "roma":
+            mod.rotmat_slerp = _rotmat_slerp
+        if name == "natsort":
+            mod.natsorted = _natsorted
     if REFERENCE_ROOT not in sys.path:
         sys.path.insert(0, REFERENCE_ROOT)
     _installed = True

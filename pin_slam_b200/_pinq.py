@@ -9,6 +9,8 @@ import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIB_PATH = os.path.join(_HERE, "libpinq.so")
+if os.environ.get("PINQ_LIB"):  # kernel experiments only (scripts/variants.py): another build of the same sources
+    _LIB_PATH = os.environ["PINQ_LIB"]
 
 F_LOCAL, F_TRAINING, F_ROTATE, F_RECIP_DIV, F_SKIP_EMPTY, F_MMA_SYNC, F_EXACT_KEYS = 1, 2, 4, 8, 16, 32, 64
 
@@ -155,6 +157,15 @@ def load():
         raise RuntimeError(
             "libpinq.so is missing (%s): build it with `python -m pin_slam_b200.build` "
             "(there is no CPU or PyTorch fallback for the neural-point query path)" % _LIB_PATH)
+    # a library built from other sources than the ones in the tree must not be used silently (the digest of the .cu /
+    # .cuh / pinq.h files and the nvcc flags is written next to the .so by build.py; both are git-ignored build artefacts)
+    if os.environ.get("PINQ_SKIP_STAMP_CHECK") != "1" and not os.environ.get("PINQ_LIB"):
+        from . import build as _build
+        if not _build.is_current():
+            try:
+                _build.build()
+            except Exception as e:
+                raise RuntimeError("libpinq.so is stale (sources changed since it was built) and rebuilding failed: %s" % e)
     lib = C.CDLL(_LIB_PATH, mode=C.RTLD_GLOBAL)
     for name, (res, args) in SIGNATURES.items():
         fn = getattr(lib, name)

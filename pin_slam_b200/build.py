@@ -41,14 +41,20 @@ def nvcc_path() -> str:
     return "nvcc"
 
 
+def is_current() -> bool:
+    """libpinq.so exists and was built from exactly the sources / flags in the tree."""
+    if not (os.path.exists(LIB) and os.path.exists(STAMP)):
+        return False
+    with open(STAMP) as f:
+        return f.read().strip() == _digest()
+
+
 def build(force: bool = False, verbose: bool = False) -> str:
     digest = _digest()
-    if not force and os.path.exists(LIB) and os.path.exists(STAMP):
-        with open(STAMP) as f:
-            if f.read().strip() == digest:
-                return LIB
+    if not force and is_current():
+        return LIB
     cmd = [nvcc_path()] + NVCC_FLAGS + ["-I" + os.path.join(ROOT, "include"), "-I" + CSRC]
-    cmd += os.environ.get("PINQ_NVCC_EXTRA", "").split()  # timing experiments only (e.g. -DPINQ_EXP=1)
+    cmd += os.environ.get("PINQ_NVCC_EXTRA", "").split()  # kernel experiments only (scripts/variants.py)
     if verbose:
         cmd += ["-Xptxas", "-v"]
     cmd += [os.path.join(CSRC, s) for s in SOURCES] + ["-o", LIB]

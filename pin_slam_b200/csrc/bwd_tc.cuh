@@ -14,10 +14,6 @@
 #pragma once
 #include "tc.cuh"
 
-#ifndef PINQ_EXP
-#define PINQ_EXP 0  // timing experiments (scripts/gpu_exp.sh); 0 = the product
-#endif
-
 namespace tcb {
 
 constexpr int kRows = 128;
@@ -184,12 +180,8 @@ __global__ void __launch_bounds__(tcb::kRows) k_bwd_tc(const BwdParams p) {
                 for (int c = 0; c < 8; ++c)
                     o[c] = ((__uint_as_float(d1[c]) + __uint_as_float(d0[8 + c])) + __uint_as_float(d0[c])) * a_prev;
                 float* gf = p.grad_features + (int64_t)li_prev * F;
-#if PINQ_EXP != 21
                 red_add_v4(gf, o[0], o[1], o[2], o[3]);
                 red_add_v4(gf + 4, o[4], o[5], o[6], o[7]);
-#else
-                if (o[0] + o[1] + o[2] + o[3] + o[4] + o[5] + o[6] + o[7] == 12345.f) gf[0] = 0.f;
-#endif
             }
         }
         tc_fence_before();
@@ -217,6 +209,12 @@ __global__ void __launch_bounds__(tcb::kRows) k_bwd_tc(const BwdParams p) {
         const int64_t i = blk * kRows + tid;
         const int64_t ni = i + (int64_t)gridDim.x * kRows;
         const bool has_next = blk + gridDim.x < nblocks;
+        if (tid == 0 && blk + 2 * (int64_t)gridDim.x < nblocks) {  // stage blocks + relu' masks of the block after the next -> L2
+            const int64_t sb0 = (blk + 2 * (int64_t)gridDim.x) * (kRows / 32), nsb = (p.n + 31) / 32;
+            const int64_t cnt = nsb - sb0 < kRows / 32 ? nsb - sb0 : kRows / 32;
+            l2_prefetch(&p.stage[sb0], (uint32_t)(cnt * sizeof(StageBlock)));
+            l2_prefetch(&mask2[sb0 * K * 32], (uint32_t)(cnt * K * 32 * sizeof(uint2)));
+        }
 #pragma unroll
         for (int k = 0; k < K; ++k) nidx[k] = -1;
         ng = 0.f;
@@ -240,7 +238,7 @@ __global__ void __launch_bounds__(tcb::kRows) k_bwd_tc(const BwdParams p) {
                 }
             }
             // ---- X tile: a_k [f_k, v_k, 1] in 3 bf16 pieces (truncation split), column = piece * 12 + input ----
-            if (DEC && PINQ_EXP != 23) {
+            if (DEC) {
                 db2 += a;
                 float ps[12] = {pfa[st].x, pfa[st].y, pfa[st].z, pfa[st].w, pfb[st].x, pfb[st].y, pfb[st].z, pfb[st].w,
                                 phv[st].x, phv[st].y, phv[st].z, phv[st].w};
@@ -275,14 +273,14 @@ __global__ void __launch_bounds__(tcb::kRows) k_bwd_tc(const BwdParams p) {
                 tc_fence_after();
                 // K-major: LBO = next 8-element chunk along K, SBO = next 8 rows.  MN-major: LBO = next 8 rows, SBO = next chunk.
                 const uint32_t ma = smem_u32(S.mask[st]);
-                if (FEAT && PINQ_EXP != 24) {
+                if (FEAT) {
                     const uint64_t maskK = umma_desc(ma, kChunk, 128);
 #pragma unroll
                     for (int ks = 0; ks < 4; ++ks)  // 16 hidden units = 2 chunks per step
                         umma_bf16(tmem + 32 * st, maskK + (uint64_t)ks * (2 * kChunk >> 4),
                                   v3K + (uint64_t)ks * (2 * kVN * 16 >> 4), kIdescMV, ks > 0);
                 }
-                if (DEC && PINQ_EXP != 22 && PINQ_EXP != 23) {
+                if (DEC) {
                     const uint64_t xMN = umma_desc(smem_u32(S.x[st]), 128, kChunk);
                     const uint64_t maskMN = umma_desc(ma, 128, kChunk);
 #pragma unroll

@@ -218,6 +218,11 @@ __global__ void __launch_bounds__(tc::kRows) k_decode_tc(const DecodeParams p) {
         const bool wlive = (i - lane) < p.n;  // this warp has a stage block
         const int64_t ni = i + (int64_t)gridDim.x * kRows;
         const bool has_next = blk + gridDim.x < nblocks;
+        if (tid == 0 && blk + 2 * (int64_t)gridDim.x < nblocks) {  // stage blocks of the block after the next -> L2
+            const int64_t sb0 = (blk + 2 * (int64_t)gridDim.x) * (kRows / 32), nsb = (p.n + 31) / 32;
+            const int64_t cnt = nsb - sb0 < kRows / 32 ? nsb - sb0 : kRows / 32;
+            l2_prefetch(&p.stage[sb0], (uint32_t)(cnt * sizeof(StageBlock)));
+        }
 #pragma unroll
         for (int k = 0; k < K; ++k) nidx[k] = -1;
 #pragma unroll

@@ -8,9 +8,6 @@
 //              FP32-FMA bound; the decoder lives in shared memory, activations in registers.
 // Reference: model/neural_points.py:459-674, model/decoder.py:66-88, utils/tracker.py:245-253,
 //            utils/mapper.py:466-468, utils/mesher.py:93-180.
-#ifndef PINQ_EXP
-#define PINQ_EXP 0  // timing experiments (scripts/gpu_exp.sh); 0 = the product
-#endif
 #include <stdlib.h>
 
 #include "brick.cuh"
@@ -209,12 +206,8 @@ __device__ __forceinline__ void resolve_ranks(const DecodeParams& p, const int32
 #pragma unroll
         for (int k = 0; k < K; ++k) {
             if (L.kidx[k] >= 0) {
-#if PINQ_EXP != 4
                 atomicAdd(&p.certainties[L.kidx[k]], L.w[k]);
-#endif
-#if PINQ_EXP != 4 && PINQ_EXP != 5
                 if (p.query_ts && p.ts_update) atomicMax(&p.ts_update[L.kidx[k]], ts);
-#endif
             }
         }
     }
@@ -643,11 +636,7 @@ __global__ void __launch_bounds__(kBlock, GRAD ? 3 : 4) k_decode_mma(const Decod
             float raw[6];
 #pragma unroll
             for (int i = 0; i < 6; ++i) raw[i] = nraw[i];
-#if PINQ_EXP == 6
-            const bool any = false;
-#else
             const bool any = nany;
-#endif
             if (mt + 1 < kMTiles) fetch(mt + 1);
             if (mt + 2 < kMTiles) fetch_idx(mt + 2);
             uint32_t mA0 = 0u, mA1 = 0u, mB0 = 0u, mB1 = 0u;  // relu' words of rows qa and qb (this lane's share)

@@ -48,7 +48,8 @@ def run_slam(config, frames=None, gt_poses=None, max_frames=None, seed=None, gen
         neural_points.travel_dist = torch.tensor(np.array(dataset.travel_dist), device=config.device, dtype=config.dtype)
         T3 = get_time()
         if not mapper.lose_track and not dataset.stop_status:
-            mapper.process_frame(dataset.cur_point_cloud_torch, None, dataset.cur_pose_torch, used_frame_id, False)
+            mapper.process_frame(dataset.cur_point_cloud_torch, None, dataset.cur_pose_torch, used_frame_id,
+                                 config.dynamic_filter_on and used_frame_id > 0)  # pin_slam.py:235-236
         else:
             neural_points.reset_local_map(dataset.cur_pose_torch[:3, 3], None, used_frame_id)
             mapper.static_mask = None

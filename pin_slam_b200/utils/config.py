@@ -53,6 +53,8 @@ class Config:
         self.color_on = False
         self.color_channel = 0
         self.dynamic_filter_on = False
+        self.dynamic_certainty_thre = 4.0   # config.py:231
+        self.dynamic_sdf_ratio_thre = 1.5   # config.py:232
         # neural points (config.py:88-127)
         self.weighted_first = True
         self.layer_norm_on = False
@@ -204,6 +206,7 @@ class Config:
             else:
                 self.vox_down_m = p.get("vox_down_m", self.max_range * 1e-3)
             self.estimate_normal = p.get("estimate_normal", False)
+            self.dynamic_filter_on = p.get("dynamic_filter_on", False)
             self.adaptive_range_on = p.get("adaptive_range_on", False)
         sm = args.get("sampler", None)
         if sm is not None:

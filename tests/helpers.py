@@ -83,6 +83,46 @@ def decoder_pair(cfg, seed=42):
     return dec, d
 
 
+def oracle_state_from(npts, dec):
+    """CPU oracle state holding the same map (and decoder) as a CUDA NeuralPoints / Decoder pair."""
+    p = O.MapParams(local_map_radius=float(npts.local_map_radius))
+    s = O.MapState(p=p)
+    s.table = npts.buffer_pt_index.cpu()
+    s.points = npts.neural_points.cpu()
+    s.quats = npts.point_orientations.cpu()
+    s.feats = npts.geo_features.cpu()
+    s.ts_create = npts.point_ts_create.cpu()
+    s.ts_update = npts.point_ts_update.cpu()
+    s.certainty = npts.point_certainties.cpu()
+    s.travel_dist = npts.travel_dist.cpu()
+    O.set_search_neighborhood(s, p.num_nei_cells, p.search_alpha)
+    O.reset_local_map(s, torch.zeros(3), 0)
+    d = O.DecoderParams(*[t.detach().cpu().clone() for t in dec.fused_params()], sdf_scale=dec.sdf_scale)
+    return O, s, d
+
+
+def to_double(obj):
+    """Shallow copy of an oracle MapState / DecoderParams with every float32 tensor promoted to float64 (the exact-arithmetic
+    arbiter of the noise-floor checks; run it under torch.set_default_dtype(torch.float64))."""
+    import copy
+    out = copy.copy(obj)
+    for k, v in vars(obj).items():
+        if torch.is_tensor(v) and v.dtype == torch.float32:
+            setattr(out, k, v.double())
+    return out
+
+
+def row_outliers(got, ref, tol=1e-5):
+    """Rows of `got` [R,F] further than tol (relative to the row's norm, floored by the median norm of the touched rows)
+    from `ref` -> (bool mask [R], relative error of everything else)."""
+    got, ref = got.detach().double().cpu(), ref.detach().double().cpu()
+    rn = ref.norm(dim=1)
+    floor = rn[rn > 0].median() if bool((rn > 0).any()) else torch.tensor(1.0, dtype=torch.float64)
+    bad = (got - ref).norm(dim=1) > tol * torch.maximum(rn, floor)
+    rest = float((got - ref)[~bad].norm()) / max(float(ref[~bad].norm()), 1e-30)
+    return bad, rest
+
+
 def rel_err(a, b, floor=1e-6):
     a = a.detach().double().cpu()
     b = b.detach().double().cpu()

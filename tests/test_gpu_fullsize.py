@@ -7,7 +7,7 @@ import argparse
 import pytest
 import torch
 
-from helpers import rel_err
+from helpers import oracle_state_from, rel_err, row_outliers, to_double
 
 pytestmark = pytest.mark.gpu
 N = 4 * 1024 * 1024
@@ -81,11 +81,106 @@ def test_full_size_backward_is_linear_in_the_upstream_gradient(big):
 
 
 def test_full_size_outputs_match_the_oracle_on_a_sample(big):
-    import bench
     cfg, npts, dec, q = big
     sdf, nn = _infer(npts, dec, q)
-    O, s, d = bench.oracle_state_from(npts, dec)
+    O, s, d = oracle_state_from(npts, dec)
     pick = torch.randperm(N, generator=torch.Generator().manual_seed(0))[:20000]
     ref = O.query_sdf(s, d, q[pick.cuda()].cpu(), None, False, True)
     assert torch.equal(nn[pick.cuda()].cpu().long(), ref["nn"])
     assert rel_err(sdf[pick.cuda()], ref["sdf"]) < 1e-5
+
+
+def test_full_size_backward_matches_the_oracle_on_a_sample(big):
+    """fwd + bwd of the bench step (training mode, local + time filter) on 200 000 queries of the bench batch against the
+    bench map: feature-gradient rows and all four decoder gradients vs the CPU oracle's autograd at 1e-5 (north_star),
+    training-mode side effects (certainty scatter 1e-5, ts amax exact).  The full 4 Mi-query backward is tied to this
+    by linearity: the gradient of the whole batch restricted to upstream weights that are zero outside the sample must
+    equal the gradient of the sample alone."""
+    cfg, npts, dec, q = big
+    n_s = 200_000
+    pick = torch.randperm(N, generator=torch.Generator().manual_seed(1))[:n_s].cuda()
+    xs = q[pick].contiguous()
+    ts = torch.zeros(n_s, dtype=torch.int64, device="cuda")
+    up = torch.linspace(0.5, 1.5, n_s, device="cuda")
+    cert0, tsu0 = npts.local_point_certainties.clone(), npts.local_point_ts_update.clone()
+    try:
+        npts.local_geo_features.grad = None
+        for p in dec.parameters():
+            p.grad = None
+        out = npts.query_sdf(xs, dec, ts, True, True)
+        (out["sdf"] * up).sum().backward()
+        g_feat = npts.local_geo_features.grad.clone()
+        g_dec = [p.grad.clone() for p in dec.fused_params()]
+        cert_after = npts.local_point_certainties.clone()
+        # the same rows through the full-size launch (binned order, other CTA / tile assignment of every query)
+        npts.local_point_certainties, npts.local_point_ts_update = cert0.clone(), tsu0.clone()
+        npts.local_geo_features.grad = None
+        for p in dec.parameters():
+            p.grad = None
+        up_full = torch.zeros(N, device="cuda")
+        up_full[pick] = up
+        out_f = npts.query_sdf(q, dec, torch.zeros(N, dtype=torch.int64, device="cuda"), True, True)
+        (out_f["sdf"] * up_full).sum().backward()
+        g_feat_full = npts.local_geo_features.grad.clone()
+        g_dec_full = [p.grad.clone() for p in dec.fused_params()]
+        assert torch.equal(out_f["sdf"][pick], out["sdf"])
+    finally:
+        npts.local_point_certainties, npts.local_point_ts_update = cert0, tsu0
+        npts.local_geo_features.grad = None
+        for p in dec.parameters():
+            p.grad = None
+    O, s, d = oracle_state_from(npts, dec)
+
+    def oracle_grads(s_, d_):
+        s_.l_feats = s_.l_feats.detach().requires_grad_(True)
+        dp = O.DecoderParams(*[t.detach().clone().requires_grad_(True) for t in d_.tensors()], sdf_scale=d_.sdf_scale)
+        dt = s_.l_feats.dtype
+        r = O.query_sdf(s_, dp, xs.cpu().to(dt), ts.cpu(), True, True)
+        (r["sdf"] * up.cpu().to(dt)).sum().backward()
+        return r, s_.l_feats.grad, [t.grad for t in dp.tensors()], s_.l_certainty
+
+    ref, gf_ref, gd_ref, cert_ref = oracle_grads(s, d)
+    assert torch.equal(out["nn_count"].cpu().long(), ref["nn"])
+    assert rel_err(out["sdf"], ref["sdf"]) < 1e-5
+    # decoder gradients (sums over all 1.2 M rows) and the two launches of the CUDA path against each other
+    errs = {}
+    for name, a, a_full, b in zip(("W1", "b1", "W2", "b2"), g_dec, g_dec_full, gd_ref):
+        errs[name] = rel_err(a, b.reshape(a.shape))
+        errs[name + "_full"] = rel_err(a_full, b.reshape(a.shape))
+    errs["feat_full_vs_sample_launch"] = rel_err(g_feat_full, g_feat)
+    # Feature-gradient rows.  relu'(pre) of a hidden unit whose pre-activation is within rounding of 0 is decided by the
+    # summation order of the 11-term dot product, so ANY two fp32 implementations disagree on a handful of the 77 M
+    # (row, unit) pairs of this sample -- each such unit changes one row by W2_j W1_j a_k.  The control: the oracle in
+    # float64 (exact arbiter) against the fp32 oracle shows the same kind of isolated rows.  Parity = every other row
+    # within 1e-5, and no more isolated rows than the fp32-vs-fp64 control shows (+ a small allowance).
+    bad, rest = row_outliers(g_feat, gf_ref)
+    bad_f, rest_f = row_outliers(g_feat_full, gf_ref)
+    torch.set_default_dtype(torch.float64)
+    try:
+        _, gf64, gd64, _ = oracle_grads(to_double(s), to_double(d))
+    finally:
+        torch.set_default_dtype(torch.float32)
+    bad_ctl, rest_ctl = row_outliers(gf_ref, gf64)
+    bad_c64, rest_c64 = row_outliers(g_feat, gf64)
+    touched = int((gf_ref.abs().sum(1) > 0).sum())
+    report = {"rows_touched": touched, "cuda_vs_oracle32": {"outlier_rows": int(bad.sum()), "rel_err_other_rows": rest,
+                                                            "rel_err_all_rows": rel_err(g_feat, gf_ref)},
+              "cuda_full_launch_vs_oracle32": {"outlier_rows": int(bad_f.sum()), "rel_err_other_rows": rest_f},
+              "control_oracle32_vs_oracle64": {"outlier_rows": int(bad_ctl.sum()), "rel_err_other_rows": rest_ctl,
+                                               "rel_err_all_rows": rel_err(gf_ref, gf64)},
+              "cuda_vs_oracle64": {"outlier_rows": int(bad_c64.sum()), "rel_err_other_rows": rest_c64,
+                                   "rel_err_all_rows": rel_err(g_feat, gf64)},
+              "decoder": errs}
+    print("full-size backward vs oracle:", report)
+    import json
+    import os
+    os.makedirs("gpurun_out", exist_ok=True)
+    with open("gpurun_out/fullsize_backward_parity.json", "w") as f:
+        json.dump(report, f, indent=1)
+    assert max(errs.values()) < 1e-5, errs
+    assert rest < 1e-5 and rest_f < 1e-5, report
+    assert int(bad.sum()) <= 3 * int(bad_ctl.sum()) + 8 and int(bad_f.sum()) <= 3 * int(bad_ctl.sum()) + 8, report
+    assert rel_err(g_feat, gf_ref) < 2e-4, report  # (bounds what the isolated rows may carry)
+    rows_differ = ((g_feat.abs().sum(1) > 0).cpu() != (gf_ref.abs().sum(1) > 0)).sum()
+    assert int(rows_differ) <= 2, int(rows_differ)  # (a row whose gradient underflows to 0 on one side only)
+    assert rel_err(cert_after, cert_ref) < 1e-5

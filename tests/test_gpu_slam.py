@@ -102,9 +102,9 @@ def test_mapping_loss_and_gradients(world):
     try:
         assert rel_err(pred, pred_ref) < 1e-5
         assert abs(float(loss) - float(loss_ref)) < 1e-5 * abs(float(loss_ref))
-        assert rel_err(m.local_geo_features.grad, s2.l_feats.grad) < 2e-5
-        assert rel_err(dec.layers[0].weight.grad, dp.W1.grad) < 2e-5
-        assert rel_err(dec.lout.weight.grad, dp.W2.grad) < 2e-5
+        assert rel_err(m.local_geo_features.grad, s2.l_feats.grad) < 1e-5
+        assert rel_err(dec.layers[0].weight.grad, dp.W1.grad) < 1e-5
+        assert rel_err(dec.lout.weight.grad, dp.W2.grad) < 1e-5
         assert rel_err(m.local_point_certainties, s2.l_certainty) < 1e-5
         assert torch.equal(m.local_point_ts_update.cpu(), s2.l_ts_update)
     finally:
