@@ -470,6 +470,16 @@ int pinq_pool_move(const pinq_pool_view* old_pool, int64_t n_pool, const pinq_po
                    int64_t new_ts, const int32_t* kept_index, const int32_t* d_count, const pinq_pool_view* out,
                    int32_t* d_kept_new, void* stream);
 
+/* Motion undistortion of a sweep (row f1): utils/tools.py:540-567 `deskewing` with the per-point times of
+ * dataset/slam_dataset.py:233-257.  pinq_velodyne_point_ts: ts = 0.5 (-atan2(y, x) / pi + 1) for scans without time stamps
+ * (KITTI .bin); pinq_deskew, in place: tau = (ts - min ts) / (max ts - min ts) - ts_mid_pose,
+ * p <- slerp(I, R, tau) p + tau t with [R | t] = T_last<-cur (row-major 4x4 float32 in device memory; the slerp is
+ * roma.rotmat_slerp's: rotation about the axis of R by tau times its angle, extrapolating for tau < 0).
+ * d_ts_minmax2 = {min ts, max ts} in device memory (torch.aminmax), `stride` = floats per point (>= 3). */
+int pinq_velodyne_point_ts(const float* xyz, int64_t n, int32_t stride, float* ts_out, void* stream);
+int pinq_deskew(float* xyz, int64_t n, int32_t stride, const float* ts, const float* d_ts_minmax2, const float* d_pose16,
+                float ts_mid_pose, void* stream);
+
 /* utils/data_sampler.py:20-192 -- DataSampler.sample: per ray the measured point, n_surf gaussian samples around it,
  * n_front uniform samples in the free space in front and n_behind behind, with projective SDF labels (-displacement)
  * and weights (distance weighting :127-128, behind drop-off :131-135, negative sign = free space), written in ray-wise

@@ -341,9 +341,99 @@ def main_frames():
     print("wrote", path, os.path.getsize(path) // 1024, "KiB; pool", mp.pool_sample_count, "of", sum(r[0].shape[0] for r in rec), "samples kept")
 
 
+def main_preprocess():
+    """Fourth fixture: the frame data path in FRONT of the hot path of the unmodified reference --
+    `deskewing` (utils/tools.py:540-567; roma.rotmat_slerp restated in oracle/ref_shim.py), three frames through
+    SLAMDataset.read_frame / preprocess_frame / update_odom_pose (dataset/slam_dataset.py:199-430: Velodyne per-point
+    times, voxel down-sampling, crop, KITTI intrinsic correction, constant-velocity guess, source down-sampling + deskew,
+    cloud deskew after the pose update) on a KITTI-layout folder of motion-distorted synthetic sweeps, and
+    Mapper.dynamic_filter (utils/mapper.py:79-108, both strategies) on the first fixture's map."""
+    import shutil
+    import tempfile
+    import types
+    torch.set_num_threads(1)
+    ns = ref_shim.load()
+    out = {}
+    g = torch.Generator().manual_seed(11)
+    # ---- deskewing alone
+    pts = (torch.rand(4000, 3, generator=g) - 0.5) * torch.tensor([120.0, 120.0, 8.0])
+    ts = torch.from_numpy(synth.velodyne_point_ts(pts.numpy().astype(np.float64)).astype(np.float32)).reshape(-1, 1)
+    yaw, pitch = 0.021, -0.004
+    cy, sy, cp, sp = np.cos(yaw), np.sin(yaw), np.cos(pitch), np.sin(pitch)
+    T = np.eye(4)
+    T[:3, :3] = np.array([[cy, -sy, 0], [sy, cy, 0], [0, 0, 1]]) @ np.array([[cp, 0, sp], [0, 1, 0], [-sp, 0, cp]])
+    T[:3, 3] = [0.91, 0.03, -0.01]
+    Tt = torch.tensor(T, dtype=torch.float32)
+    out["dk_points"], out["dk_ts"], out["dk_pose"] = pts.numpy().copy(), ts.numpy().copy(), Tt.numpy().copy()
+    out["dk_out"] = ns.tools.deskewing(pts.clone(), ts.clone(), Tt).numpy().copy()
+    out["dk_out_mid0"] = ns.tools.deskewing(pts.clone(), ts.clone(), Tt, ts_mid_pose=0.0).numpy().copy()
+    # ---- three frames through the reference's SLAMDataset
+    frames, gt = synth.make_sweeps(3, beams=24, azimuth=600, workers=1, correct_deg=0.195)
+    root = tempfile.mkdtemp(prefix="pinq_kitti_")
+    try:
+        paths = synth.write_kitti_sequence(root, frames, gt)
+        cfg = ns.Config()
+        cfg.load(ref_shim.write_kitti_yaml(os.path.join(root, "run_kitti.yaml"), paths, os.path.join(root, "out")))
+        cfg.device = "cpu"
+        SLAMDataset = importlib.import_module("dataset.slam_dataset").SLAMDataset
+        ds = SLAMDataset(cfg)
+        out["pp_n"] = np.int64(3)
+        out["pp_gt"] = np.stack(ds.poses_ref[:3]) if ds.gt_pose_provided else gt
+        for i in range(3):
+            out["pp%d_scan" % i] = frames[i]
+            ds.read_frame(i)
+            out["pp%d_ts_raw" % i] = ds.cur_point_ts_torch.numpy().copy()
+            ds.preprocess_frame(i)
+            out["pp%d_cloud" % i] = ds.cur_point_cloud_torch.numpy().copy()
+            out["pp%d_ts" % i] = ds.cur_point_ts_torch.numpy().copy()
+            if i > 0:
+                out["pp%d_guess" % i] = ds.cur_pose_guess_torch.numpy().copy()
+                out["pp%d_source" % i] = ds.cur_source_points.numpy().copy()
+                # the tracker's answer is replaced by a fixed pose near the ground truth (the fixture pins the data path)
+                est = ds.poses_ref[i].copy()
+                est[:3, 3] += np.array([0.01, -0.005, 0.002]) * i
+                out["pp%d_est" % i] = est
+                ds.update_odom_pose(torch.tensor(est, dtype=torch.float64))
+                out["pp%d_cloud_deskewed" % i] = ds.cur_point_cloud_torch.numpy().copy()
+                out["pp%d_last_odom_tran" % i] = ds.last_odom_tran.copy()
+            ds.processed_frame += 1
+        out["pp_travel_dist"] = np.array(ds.travel_dist)
+    finally:
+        shutil.rmtree(root, ignore_errors=True)
+    # ---- Mapper.dynamic_filter on the map of the first fixture
+    G = {k: v for k, v in np.load(os.path.join(OUT, "ref_kitti_small.npz")).items()}
+    cfg = ref_shim.kitti_config("cpu")
+    cfg.buffer_size = int(G["buffer_size"])
+    torch.manual_seed(42)
+    dec = ns.Decoder(cfg, 64, 1, 1)
+    with torch.no_grad():
+        dec.layers[0].weight.copy_(torch.from_numpy(G["W1"]))
+        dec.layers[0].bias.copy_(torch.from_numpy(G["b1"]))
+        dec.lout.weight.copy_(torch.from_numpy(G["W2"]))
+        dec.lout.bias.copy_(torch.from_numpy(G["b2"]))
+    npts = ns.NeuralPoints(cfg)
+    npts.travel_dist = torch.from_numpy(G["travel_dist"])
+    for t in range(3):
+        npts.update(torch.from_numpy(G["frames%d" % t]), torch.tensor([3.0 * t, 0.0, 0.0]), torch.eye(3), t)
+    npts.geo_features = torch.from_numpy(G["features"]).clone()
+    npts.point_certainties = torch.from_numpy(G["certainties"]).clone()
+    npts.reset_local_map(torch.tensor([6.0, 0.0, 0.0]), torch.eye(3), 2)
+    dataset = types.SimpleNamespace(odom_poses=[np.eye(4)], gt_pose_provided=False, stop_status=False)
+    mp = ns.Mapper(cfg, dataset, npts, dec, None, None)
+    q = torch.from_numpy(G["queries"]).clone()
+    out["df_static_1"] = mp.dynamic_filter(q.clone(), False).numpy().copy()
+    out["df_static_2"] = mp.dynamic_filter(q.clone(), True).detach().numpy().copy()
+    out["df_thresholds"] = np.array([cfg.dynamic_certainty_thre, cfg.dynamic_sdf_ratio_thre], dtype=np.float64)
+    path = os.path.join(OUT, "ref_kitti_preprocess.npz")
+    np.savez_compressed(path, **out)
+    print("wrote", path, os.path.getsize(path) // 1024, "KiB;", "static fraction", float(out["df_static_1"].mean()), float(out["df_static_2"].mean()))
+
+
 if __name__ == "__main__":
     only = [a for a in sys.argv[1:] if a.startswith("--only=")]
-    which = only[0].split("=")[1].split(",") if only else ["small", "pgo", "frames"]
+    which = only[0].split("=")[1].split(",") if only else ["small", "pgo", "frames", "preprocess"]
+    if "preprocess" in which:
+        main_preprocess()
     if "small" in which:
         main()
     if "pgo" in which:

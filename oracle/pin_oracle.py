@@ -620,3 +620,57 @@ def tracking(s: MapState, d: DecoderParams, source_points, init_pose, *, iter_n=
     if not valid_flag:
         T = init_pose
     return T, valid_flag, it, res_cm
+
+
+# --------------------------------------------------------------------------------------
+# frame data path in front of the hot path (dataset/slam_dataset.py, utils/tools.py:540-567)
+# --------------------------------------------------------------------------------------
+def velodyne_point_ts(points: torch.Tensor) -> torch.Tensor:
+    """dataset/slam_dataset.py:247-249: per-point time of a sweep without time stamps (clockwise from the -x axis)."""
+    yaw = -torch.atan2(points[:, 1], points[:, 0])
+    return 0.5 * (yaw / math.pi + 1.0)
+
+
+def rotmat_slerp_from_identity(R: torch.Tensor, steps: torch.Tensor) -> torch.Tensor:
+    """roma.rotmat_slerp(I, R, steps) -- roma is an un-vendored dependency of the reference (utils/tools.py:24, 560;
+    roma >= 1.4: rotation matrix -> unit quaternion -> rotation vector, scaled by every step, back to a matrix; shortest
+    arc; steps outside [0, 1] extrapolate).  Restated as exp(step * log R) with Rodrigues' formula -> [N,3,3]."""
+    cos = torch.clamp(((R[0, 0] + R[1, 1] + R[2, 2]) - 1.0) * 0.5, -1.0, 1.0)
+    w = torch.stack([R[2, 1] - R[1, 2], R[0, 2] - R[2, 0], R[1, 0] - R[0, 1]])
+    n = torch.linalg.norm(w)
+    if float(n) <= 1e-12:
+        return torch.eye(3, dtype=R.dtype).expand(steps.shape[0], 3, 3).clone()
+    axis = w / n
+    ang = steps * torch.atan2(0.5 * n, cos)
+    Kx = torch.zeros(3, 3, dtype=R.dtype)
+    Kx[0, 1], Kx[0, 2], Kx[1, 0], Kx[1, 2], Kx[2, 0], Kx[2, 1] = -axis[2], axis[1], axis[2], -axis[0], -axis[1], axis[0]
+    eye = torch.eye(3, dtype=R.dtype)
+    return eye[None] + torch.sin(ang)[:, None, None] * Kx[None] + (1.0 - torch.cos(ang))[:, None, None] * (Kx @ Kx)[None]
+
+
+def deskew(points: torch.Tensor, ts: torch.Tensor, pose: torch.Tensor, ts_mid_pose: float = 0.5) -> torch.Tensor:
+    """utils/tools.py:540-567 (returns a new tensor; the reference works in place): pose = T_last<-cur."""
+    if ts is None:
+        return points
+    t = ts.reshape(-1).to(points.dtype)
+    t = (t - torch.min(t)) / (torch.max(t) - torch.min(t)) - ts_mid_pose
+    R = rotmat_slerp_from_identity(pose[:3, :3].to(points.dtype), t)
+    return (R @ points[:, :3].unsqueeze(-1)).squeeze(-1) + t[:, None] * pose[:3, 3].to(points.dtype)
+
+
+def crop_frame(points, ts, min_z, max_z, min_range, max_range):
+    """dataset/slam_dataset.py:827-834."""
+    dist = torch.norm(points[:, :3], dim=1)
+    keep = (dist > min_range) & (dist < max_range) & (points[:, 2] > min_z) & (points[:, 2] < max_z)
+    return points[keep], (ts[keep] if ts is not None else None)
+
+
+def intrinsic_correct(points, correct_deg):
+    """dataset/slam_dataset.py:837-854 (KITTI vertical-angle calibration); returns a new tensor."""
+    if correct_deg == 0.0:
+        return points
+    dist = torch.norm(points[:, :3], dim=1)
+    v = torch.asin(points[:, 2] / dist)
+    vc = v + correct_deg / 180.0 * math.pi
+    hs = torch.cos(vc) / torch.cos(v)
+    return torch.stack([points[:, 0] * hs, points[:, 1] * hs, dist * torch.sin(vc)], 1)

@@ -92,9 +92,9 @@ def _rotmat_slerp(R0, R1, steps):
     Rrel = R0.transpose(-1, -2) @ R1
     cos = ((Rrel[0, 0] + Rrel[1, 1] + Rrel[2, 2]) - 1.0) * 0.5
     cos = torch.clamp(cos, -1.0, 1.0)
-    theta = torch.acos(cos)
     w = torch.stack([Rrel[2, 1] - Rrel[1, 2], Rrel[0, 2] - Rrel[2, 0], Rrel[1, 0] - Rrel[0, 1]])
     n = torch.linalg.norm(w)
+    theta = torch.atan2(0.5 * n, cos)  # (roma: 2 atan2(|q_xyz|, q_w) of the relative quaternion -- as well conditioned)
     axis = w / n if float(n) > 1e-12 else torch.tensor([1.0, 0.0, 0.0], dtype=R1.dtype, device=R1.device)
     if float(n) <= 1e-12:
         theta = torch.zeros((), dtype=R1.dtype, device=R1.device)
@@ -193,3 +193,23 @@ def kitti_config(device="cpu"):
     cfg.device = device
     cfg.o3d_vis_on = False
     return cfg
+
+
+def write_kitti_yaml(dst, paths, output_root, drop_pgo=True, extra=None):
+    """config/lidar_slam/run_kitti.yaml of the reference with ONLY these edits: the three input
+    paths and the output root, `o3d_vis_on: False` (no graphics stack on this box), and the `pgo:` section removed
+    (gtsam is not installed; no loop can fire within 100 frames / 90 m: needs > 4 x 82 m, pin_slam.py:172).  `extra`:
+    {section: {key: value}} overrides used by tests (stated by the caller)."""
+    import yaml
+    with open(os.path.join(REFERENCE_ROOT, "config/lidar_slam/run_kitti.yaml")) as f:
+        cfg = yaml.safe_load(f)
+    cfg["setting"].update({"pc_path": paths["pc_path"], "pose_path": paths["pose_path"], "calib_path": paths["calib_path"],
+                           "output_root": output_root})
+    cfg["eval"]["o3d_vis_on"] = False
+    if drop_pgo:
+        cfg.pop("pgo", None)
+    for sec, kv in (extra or {}).items():
+        cfg.setdefault(sec, {}).update(kv)
+    with open(dst, "w") as f:
+        yaml.safe_dump(cfg, f, sort_keys=False)
+    return dst

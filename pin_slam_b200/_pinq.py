@@ -136,6 +136,8 @@ SIGNATURES = {
     "pinq_peer_error_offset": (_i64, []),
     "pinq_peer_exchange": (C.c_int, [C.POINTER(PeerArgs), _vp]),
     "pinq_ray_samples": (C.c_int, [_vp, _i64, _vp, _vp, _vp, _i32, _i32, _i32, _f32, _f32, _f32, _f32, _f32, _i32, _i32, _vp, _vp, _vp, _vp]),
+    "pinq_velodyne_point_ts": (C.c_int, [_vp, _i64, _i32, _vp, _vp]),
+    "pinq_deskew": (C.c_int, [_vp, _i64, _i32, _vp, _vp, _vp, _f32, _vp]),
     "pinq_pool_flags": (C.c_int, [_vp, _i64, _vp, _i64, _vp, _f32, _vp, _vp]),
     "pinq_pool_discard": (C.c_int, [_vp, _vp, _vp, _i64, _vp]),
     "pinq_pool_move": (C.c_int, [C.POINTER(PoolView), _i64, C.POINTER(PoolView), _i64, _i64, _vp, _vp, C.POINTER(PoolView), _vp, _vp]),

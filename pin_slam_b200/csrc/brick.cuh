@@ -44,6 +44,12 @@ __device__ __forceinline__ uint32_t brick_hash(unsigned long long k, uint32_t ca
 }
 __device__ __forceinline__ int brick_bit(int cx, int cy, int cz) { return (((cx & 3) * 4) + (cy & 3)) * 4 + (cz & 3); }
 
+// one whole 32-byte entry with a single 256-bit load: words {mask lo, mask hi, base, pad, key lo, key hi, pad, pad}
+__device__ __forceinline__ void ldg_entry(const BrickEntry* e, uint32_t (&w)[8]) {
+    asm("ld.global.nc.v8.u32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+        : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]), "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7]) : "l"(e));
+}
+
 // read-only lookup: entry index of `key`, or -1
 __device__ __forceinline__ int brick_find(const BrickEntry* tab, uint32_t cap_mask, unsigned long long key) {
     uint32_t h = brick_hash(key, cap_mask);

@@ -2,11 +2,13 @@
 //
 // Same algebra as k_bwd_mma (query_bwd.cu header), other mapping: tile k = neighbour k of a block of 128 queries, so
 // THREAD = QUERY = row.  Per tile the thread expands its 64 relu' bits into one bf16 row of the MASK tile and writes
-// a_k [f_k, v_k, 1] (3 bf16 pieces, truncation split) into the X tile; both tiles are stored [8-element chunk][row] x 16
+// a_k [f_k, v_k, 1] (2 bf16 pieces, round-to-nearest split) into the X tile; both tiles are stored [8-element chunk][row] x 16
 // bytes, which is the UMMA canonical no-swizzle layout K-major for (row x hidden) AND MN-major for its transpose:
 //   mask x V    D1[128 rows x 32]   = MASK (A, K-major)  x V3 (B, K-major; 3 pieces x 8 feature columns)     4 MMAs K=16
-//   G           D2[64 hidden x 40] += MASK^T (A, MN-major) x X (B, MN-major), reduction over the 128 rows      8 MMAs K=16
-// (X has 40 columns: 3 pieces x 12 inputs + pad).  Shared-memory bandwidth is what bounds this kernel (ncu: L1TEX 67 %):
+//   G           D2[64 hidden x 24] += MASK^T (A, MN-major) x X (B, MN-major), reduction over the 128 rows      8 MMAs K=16
+// (X has 24 columns: 2 round-to-nearest bf16 pieces x 12 inputs: |x - (p0 + p1)| <= 2^-18 |x| and unbiased, and the decoder
+// gradient is a sum over all rows, so the pieces' rounding averages out -- measured 1e-6 relative on the four gradients;
+// three truncated pieces cost 10 KB of tile writes + 10 KB of operand reads per tile instead of 6 + 6).  Shared-memory bandwidth is what bounds this kernel (ncu: L1TEX 67 %):
 // per tile 26 KB of tile writes + 46 KB of operand reads by the tensor core.
 // D1 -> thread-local epilogue: dL/df_k = a_k (sum of the 3 pieces) -> red.global.add.v4.f32 x 2 into grad_features[idx_k].
 // D2 is flushed into fp32 shared-memory sums once per block of 6 tiles (768 rows), so the long reduction over rows is
@@ -17,13 +19,17 @@
 namespace tcb {
 
 constexpr int kRows = 128;
-constexpr int kXCols = 40;                  // 3 pieces x 12 inputs (+4 zero)
+constexpr int kXCols = 24;                  // 2 pieces x 12 inputs
 constexpr uint32_t kChunk = kRows * 16;     // 2048 bytes: one 8-element chunk of all 128 rows
 constexpr int kMaskChunks = H / 8;          // 8
-constexpr int kXChunks = kXCols / 8;        // 5
+constexpr int kXChunks = kXCols / 8;        // 3
 constexpr int kVN = 32;                     // 3 pieces x 8 feature columns (+8 zero)
 constexpr uint32_t kTmemCols = 128;         // D1 buffers at columns 0 and 32, D2 at column 64 (64)
-constexpr size_t kSmemRequest = 72 * 1024;  // 3 CTAs per SM (3 x 128 TMEM columns)
+#ifndef PINQ_BWD_CTAS
+#define PINQ_BWD_CTAS 4
+#endif
+constexpr unsigned kCtasPerSm = PINQ_BWD_CTAS;  // 4 x 128 TMEM columns = all 512; 4 x (55 KB + 1 KB reserved) of shared memory
+constexpr size_t kSmemRequest = (PINQ_BWD_CTAS >= 4 ? 55 : 72) * 1024;
 
 struct Smem {  // the tiles are double-buffered: tile t + 1 is staged while the MMAs of tile t run
     alignas(128) unsigned char x[2][kXChunks * kChunk];        // each read as 16 chunks (M = 128): followed by >= 22 KB
@@ -59,10 +65,12 @@ __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint6
 __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
     asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" :: "l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
-__device__ __forceinline__ uint32_t hi16_pair(float a, float b) {  // {bf16 trunc(a), bf16 trunc(b)}
-    return __byte_perm(__float_as_uint(a), __float_as_uint(b), 0x7632);
+// {bf16 rn(a) in the low half, bf16 rn(b) in the high half}: one cvt.rn.bf16x2.f32
+__device__ __forceinline__ uint32_t rn_bf16_pair(float a, float b) {
+    uint32_t r;
+    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(b), "f"(a));
+    return r;
 }
-__device__ __forceinline__ float drop_hi16(float x) { return x - __uint_as_float(__float_as_uint(x) & 0xffff0000u); }
 
 }  // namespace tcb
 
@@ -191,7 +199,7 @@ __global__ void __launch_bounds__(tcb::kRows) k_bwd_tc(const BwdParams p) {
     auto flush = [&]() {
         if (DEC) {
 #pragma unroll
-            for (int c3 = 0; c3 < 3; ++c3) {
+            for (int c3 = 0; c3 < (kXCols + 15) / 16; ++c3) {
                 uint32_t v[16];
                 tmem_ld16(tmem_row + kD2 + 16 * c3, v);
                 tmem_ld_wait(v);
@@ -237,26 +245,20 @@ __global__ void __launch_bounds__(tcb::kRows) k_bwd_tc(const BwdParams p) {
                     *reinterpret_cast<uint4*>(S.mask[st] + hc * kChunk + tid * 16) = make_uint4(r[0], r[1], r[2], r[3]);
                 }
             }
-            // ---- X tile: a_k [f_k, v_k, 1] in 3 bf16 pieces (truncation split), column = piece * 12 + input ----
+            // ---- X tile: a_k [f_k, v_k, 1] in 2 bf16 pieces (round to nearest), column = piece * 12 + input ----
             if (DEC) {
                 db2 += a;
                 float ps[12] = {pfa[st].x, pfa[st].y, pfa[st].z, pfa[st].w, pfb[st].x, pfb[st].y, pfb[st].z, pfb[st].w,
                                 phv[st].x, phv[st].y, phv[st].z, phv[st].w};
 #pragma unroll
                 for (int c = 0; c < 12; ++c) ps[c] *= a;
-                uint32_t wds[20];
+                uint32_t wds[12];
 #pragma unroll
-                for (int s = 0; s < 3; ++s) {
-#pragma unroll
-                    for (int ip = 0; ip < 6; ++ip) {
-                        wds[s * 6 + ip] = hi16_pair(ps[2 * ip], ps[2 * ip + 1]);
-                        if (s < 2) {
-                            ps[2 * ip] = drop_hi16(ps[2 * ip]);
-                            ps[2 * ip + 1] = drop_hi16(ps[2 * ip + 1]);
-                        }
-                    }
+                for (int ip = 0; ip < 6; ++ip) {
+                    const uint32_t hi = rn_bf16_pair(ps[2 * ip], ps[2 * ip + 1]);
+                    wds[ip] = hi;
+                    wds[6 + ip] = rn_bf16_pair(ps[2 * ip] - __uint_as_float(hi << 16), ps[2 * ip + 1] - __uint_as_float(hi & 0xffff0000u));
                 }
-                wds[18] = wds[19] = 0u;
 #pragma unroll
                 for (int c = 0; c < kXChunks; ++c)
                     *reinterpret_cast<uint4*>(S.x[st] + c * kChunk + tid * 16) =
@@ -313,11 +315,11 @@ __global__ void __launch_bounds__(tcb::kRows) k_bwd_tc(const BwdParams p) {
         if (lane == 0) atomicAdd(&S.db2, db2);
     }
     __syncthreads();
-    if (DEC) {  // G[j][i] = sum of the 3 pieces; then dW1 = W2 G, db1 = W2 G[:,11], dW2[j] = W1b[j] . G[j], db2
+    if (DEC) {  // G[j][i] = sum of the 2 pieces; then dW1 = W2 G, db1 = W2 G[:,11], dW2[j] = W1b[j] . G[j], db2
         float* sG = reinterpret_cast<float*>(S.mask[0]);  // [H][12], the tiles are idle now
         for (int e = tid; e < H * 12; e += kRows) {
             const int c = e / 12, i = e - 12 * c, j = hidden_of_maskcol(c);
-            sG[j * 12 + i] = (S.gacc[24 + i][c] + S.gacc[12 + i][c]) + S.gacc[i][c];
+            sG[j * 12 + i] = S.gacc[12 + i][c] + S.gacc[i][c];
         }
         __syncthreads();
         for (int e = tid; e < H * 12; e += kRows) {

@@ -298,8 +298,11 @@ constexpr size_t kBrickSmem = sizeof(BrickLane) + kStencilMasks * 8 + 128 + 32;
 // RESOLVE: the walk ends with the lane's K winners in registers and their records hot in L1, so the resolve step
 // (stage block, per-query outputs, training side effects -- what k_resolve does after the slot-probing search)
 // runs in the tail of this kernel; the rank workspace is then only written for the gradient flavour of the decode.
+#ifndef PINQ_SEARCH_MINB
+#define PINQ_SEARCH_MINB 8
+#endif
 template <bool RESOLVE>
-__global__ void __launch_bounds__(kBlock) k_search_brick(MapDev map, BrickDev bd, PointSrc src, int64_t n, bool recip,
+__global__ void __launch_bounds__(kBlock, PINQ_SEARCH_MINB) k_search_brick(MapDev map, BrickDev bd, PointSrc src, int64_t n, bool recip,
                                                          const int32_t* __restrict__ perm,
                                                          const unsigned long long* __restrict__ stencil_masks,
                                                          int32_t* __restrict__ ws, const DecodeParams p) {
@@ -331,20 +334,49 @@ __global__ void __launch_bounds__(kBlock) k_search_brick(MapDev map, BrickDev bd
     const int b0x = ax >> 2, b0y = ay >> 2, b0z = az >> 2;
     const int srow = (((ax & 3) * 4 + (ay & 3)) * 4 + (az & 3)) * 8;
 
-    // phase 1: one probe per brick, all eight issued before any is used; non-empty halves appended to the walk list
+    // phase 1: one probe per brick, in batches of PINQ_PROBE_BATCH: the 32-byte entries of a batch are requested back to
+    // back (one 256-bit load each) before the first key is compared, so a batch costs ONE exposed L2 latency instead of
+    // chained ones (ncu r3b: the eight sequential key waits were 11 % of the kernel's stall samples); batches of two keep
+    // the kernel at 64 registers = 8 CTAs per SM (batches of four: 80 registers, slower).  An entry that is not the
+    // brick's own (linear-probing displacement, rare at load factor <= 0.5) falls back to the probe loop
     int total = 0, cnt = 0;
     unsigned long long pm[8];
     uint32_t pb[8];
+#ifndef PINQ_PROBE_BATCH
+#define PINQ_PROBE_BATCH 2
+#endif
 #pragma unroll
-    for (int b = 0; b < 8; ++b) {
-        pm[b] = 0ull;
-        pb[b] = 0u;
-        if (live && s_masks[srow + b]) {
-            const int e = brick_find(bd.tab, bd.cap_mask, brick_key(b0x + (b >> 2), b0y + ((b >> 1) & 1), b0z + (b & 1)));
-            if (e >= 0) {
-                const uint4 v = __ldg(reinterpret_cast<const uint4*>(&bd.tab[e]));
-                pm[b] = ((unsigned long long)v.y << 32) | v.x;
-                pb[b] = v.z;
+    for (int b0 = 0; b0 < 8; b0 += PINQ_PROBE_BATCH) {
+        unsigned long long want[PINQ_PROBE_BATCH];
+        uint32_t ew[PINQ_PROBE_BATCH][8];
+        bool need[PINQ_PROBE_BATCH];
+#pragma unroll
+        for (int u = 0; u < PINQ_PROBE_BATCH; ++u) {
+            const int b = b0 + u;
+            need[u] = live && s_masks[srow + b] != 0ull;
+            want[u] = brick_key(b0x + (b >> 2), b0y + ((b >> 1) & 1), b0z + (b & 1));
+#pragma unroll
+            for (int w = 0; w < 8; ++w) ew[u][w] = 0u;
+            if (need[u]) ldg_entry(&bd.tab[brick_hash(want[u], bd.cap_mask)], ew[u]);
+        }
+#pragma unroll
+        for (int u = 0; u < PINQ_PROBE_BATCH; ++u) {
+            const int b = b0 + u;
+            pm[b] = 0ull;
+            pb[b] = 0u;
+            if (need[u]) {
+                const unsigned long long got = ((unsigned long long)ew[u][5] << 32) | ew[u][4];
+                if (got == want[u]) {
+                    pm[b] = ((unsigned long long)ew[u][1] << 32) | ew[u][0];
+                    pb[b] = ew[u][2];
+                } else if (got != kBrickEmpty) {  // displaced entry: walk the probe sequence
+                    const int e = brick_find(bd.tab, bd.cap_mask, want[u]);
+                    if (e >= 0) {
+                        const uint4 v = __ldg(reinterpret_cast<const uint4*>(&bd.tab[e]));
+                        pm[b] = ((unsigned long long)v.y << 32) | v.x;
+                        pb[b] = v.z;
+                    }
+                }
             }
         }
     }
@@ -402,22 +434,36 @@ __global__ void __launch_bounds__(kBlock) k_search_brick(MapDev map, BrickDev bd
         if (nact) nrc = __ldg(&bd.rec[rank]);
         nid = ((uint32_t)e << 5) | (uint32_t)bit;
     };
-    advance32();
-    while (__any_sync(0xffffffffu, nact)) {
-        const bool act = nact;
-        const float4 rc = nrc;
-        const uint32_t id = nid;
-        advance32();
-        const float d2 = dist2_rn(rc.x, rc.y, rc.z, x, y, z);
-        // valid: index != -1 (-2 = hazard H13, still a candidate) and not d2 > max (neural_points.py:499)
-        const bool ok = act && __float_as_int(rc.w) != -1 && !(d2 > map.max_d2);
-        nn += ok ? 1 : 0;
-        uint32_t key = ok ? ((__float_as_uint(d2) & ~kWalkIdMask) | id) : ~0u;
+    // U candidates per trip: their records are requested back to back and ranked afterwards, so the loads of a trip
+    // overlap each other (with one record in flight the copy of the loaded registers at the loop end waited for a load
+    // issued ~45 instructions earlier: 20 % of the kernel's stall samples sat on that one instruction, ncu r3b)
+#ifndef PINQ_SEARCH_BATCH
+#define PINQ_SEARCH_BATCH 3
+#endif
+    while (__any_sync(0xffffffffu, total > 0)) {
+        float4 rcs[PINQ_SEARCH_BATCH];
+        uint32_t ids[PINQ_SEARCH_BATCH];
+        bool acts[PINQ_SEARCH_BATCH];
 #pragma unroll
-        for (int k = 0; k <= K; ++k) {  // ascending insertion: slot keeps the smaller, the larger moves on
-            const uint32_t lo = min(k7[k], key);
-            key = max(k7[k], key);
-            k7[k] = lo;
+        for (int u = 0; u < PINQ_SEARCH_BATCH; ++u) {
+            advance32();
+            rcs[u] = nrc;
+            ids[u] = nid;
+            acts[u] = nact;
+        }
+#pragma unroll
+        for (int u = 0; u < PINQ_SEARCH_BATCH; ++u) {
+            const float d2 = dist2_rn(rcs[u].x, rcs[u].y, rcs[u].z, x, y, z);
+            // valid: index != -1 (-2 = hazard H13, still a candidate) and not d2 > max (neural_points.py:499)
+            const bool ok = acts[u] && __float_as_int(rcs[u].w) != -1 && !(d2 > map.max_d2);
+            nn += ok ? 1 : 0;
+            uint32_t key = ok ? ((__float_as_uint(d2) & ~kWalkIdMask) | ids[u]) : ~0u;
+#pragma unroll
+            for (int k = 0; k <= K; ++k) {  // ascending insertion: slot keeps the smaller, the larger moves on
+                const uint32_t lo = min(k7[k], key);
+                key = max(k7[k], key);
+                k7[k] = lo;
+            }
         }
     }
     bool tie = false;

@@ -275,7 +275,7 @@ extern "C" int pinq_query_fused_bwd(const pinq_bwd_args* a, void* stream) {
     ktime_mark(PINQ_KT_BWD, st);
     if (use_tc && !(a->flags & PINQ_F_MMA_SYNC)) {
         const unsigned nb128 = grid_for(a->n, tcb::kRows);
-        const unsigned cap128 = (unsigned)sms * 3u;  // 3 CTAs (72 KB of tiles, 128 TMEM columns each) per SM
+        const unsigned cap128 = (unsigned)sms * tcb::kCtasPerSm;  // resident CTAs: bounded by TMEM columns and the tile buffers
         const unsigned g128 = nb128 < cap128 ? nb128 : cap128;
         if (dec && feat) k_bwd_tc<true, true><<<g128, tcb::kRows, tcb::kSmemRequest, st>>>(p);
         else if (dec) k_bwd_tc<true, false><<<g128, tcb::kRows, tcb::kSmemRequest, st>>>(p);

@@ -4,7 +4,8 @@ Kept: frame reading (KITTI .bin folder or in-memory synthetic scans), voxel down
 libpinq kernel, cropping, KITTI intrinsic correction, the constant-velocity pose guess, source-point
 down-sampling, odometry / travel-distance bookkeeping and stop detection -- i.e. everything
 `pin_slam.py` touches between two calls into the hot path.  Out of scope: Open3D / .ply / .pcd / .las
-readers, semantic labels, deskewing (synthetic scans are instantaneous; `deskew` must be False), plots.
+readers, semantic labels, plots.  Deskewing (utils/tools.py:540-567) runs as one kernel, with the Velodyne per-point
+times of slam_dataset.py:247-249 when the scan carries none.
 """
 from __future__ import annotations
 
@@ -14,7 +15,7 @@ import os
 import numpy as np
 import torch
 
-from ..utils.tools import voxel_down_sample_torch
+from ..utils.tools import deskewing, velodyne_point_ts, voxel_down_sample_torch
 
 
 def crop_frame(points, ts, min_z_th=-3.0, max_z_th=100.0, min_range=2.75, max_range=100.0):
@@ -51,8 +52,6 @@ class SLAMDataset:
         self.silence = config.silence
         self.dtype = config.dtype
         self.device = config.device
-        if config.deskew:
-            raise NotImplementedError("deskewing (roma slerp) is out of scope: set deskew False (instantaneous scans)")
         self.frames = frames
         if frames is None:
             names = sorted(f for f in os.listdir(config.pc_path) if f.endswith(".bin"))
@@ -101,6 +100,10 @@ class SLAMDataset:
             pc = np.fromfile(os.path.join(self.config.pc_path, self.pc_filenames[frame_id]), dtype=np.float32).reshape(-1, 4)
         self.cur_point_cloud_torch = torch.tensor(pc[:, :3], device=self.device, dtype=self.dtype)
         self.cur_point_ts_torch = None
+        if self.config.deskew:  # slam_dataset.py:228-257 (KITTI .bin carries no per-point time: Velodyne yaw convention)
+            if self.config.lidar_type_guess != "velodyne":
+                raise NotImplementedError("per-point times are derived for Velodyne-type sweeps only")
+            self.cur_point_ts_torch = velodyne_point_ts(self.cur_point_cloud_torch)
 
     def preprocess_frame(self, frame_id=0):
         """reference: dataset/slam_dataset.py:260-374."""
@@ -114,8 +117,10 @@ class SLAMDataset:
         else:
             idx = voxel_down_sample_torch(self.cur_point_cloud_torch[:, :3].contiguous(), train_voxel_m)
         self.cur_point_cloud_torch = self.cur_point_cloud_torch[idx]
-        self.cur_point_cloud_torch, _ = crop_frame(self.cur_point_cloud_torch, None, cfg.min_z, cfg.max_z, cfg.min_range,
-                                                   crop_max_range)
+        if self.cur_point_ts_torch is not None:
+            self.cur_point_ts_torch = self.cur_point_ts_torch[idx]
+        self.cur_point_cloud_torch, self.cur_point_ts_torch = crop_frame(self.cur_point_cloud_torch, self.cur_point_ts_torch,
+                                                                         cfg.min_z, cfg.max_z, cfg.min_range, crop_max_range)
         if cfg.kitti_correction_on:
             self.cur_point_cloud_torch = intrinsic_correct(self.cur_point_cloud_torch, cfg.correction_deg)
         if self.processed_frame == 0:
@@ -136,6 +141,10 @@ class SLAMDataset:
             src = self.cur_point_cloud_torch.clone()
             idx = voxel_down_sample_torch(src[:, :3].contiguous(), source_voxel_m)
             self.cur_source_points = src[idx][:, :3].contiguous()
+            # deskewing of the source points with the motion of the previous interval (slam_dataset.py:367-370)
+            if cfg.deskew and not self.lose_track and self.cur_point_ts_torch is not None:
+                self.cur_source_points = deskewing(self.cur_source_points, self.cur_point_ts_torch[idx],
+                                                   torch.tensor(self.last_odom_tran, device=self.device, dtype=self.dtype))
 
     def update_odom_pose(self, cur_pose_torch):
         """reference: dataset/slam_dataset.py:376-430."""
@@ -155,6 +164,10 @@ class SLAMDataset:
             self.lose_track = True
         self.travel_dist.append(self.travel_dist[-1] + d)
         self.last_pose_ref = self.cur_pose_ref
+        # deskewing of the cloud used for mapping with the motion just estimated (slam_dataset.py:419-422)
+        if cfg.deskew and not self.lose_track and self.cur_point_ts_torch is not None:
+            self.cur_point_cloud_torch = deskewing(self.cur_point_cloud_torch.contiguous(), self.cur_point_ts_torch,
+                                                   torch.tensor(self.last_odom_tran, device=self.device, dtype=self.dtype))
         self.consecutive_lose_track_frame = self.consecutive_lose_track_frame + 1 if self.lose_track else 0
         if self.consecutive_lose_track_frame > 20:
             raise RuntimeError("Lose track for a long time, system failed")

@@ -52,6 +52,7 @@ class Config:
         self.color_map_on = False
         self.color_on = False
         self.color_channel = 0
+        self.lidar_type_guess = "velodyne"  # config.py:54
         self.dynamic_filter_on = False
         self.dynamic_certainty_thre = 4.0   # config.py:231
         self.dynamic_sdf_ratio_thre = 1.5   # config.py:232

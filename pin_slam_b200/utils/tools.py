@@ -1,7 +1,7 @@
 """Math helpers on the neural-point query path, backed by libpinq kernels.
 
 Mirrors the names of the reference's utils/tools.py for the functions that sit on the hot path
-(voxel_down_sample_torch :409, voxel_down_sample_min_value_torch :444, transform_torch :386,
+(voxel_down_sample_torch :409, voxel_down_sample_min_value_torch :444, transform_torch :386, deskewing :540,
 get_time :269, freeze_model :187, setup_optimizer :89).  Everything here requires CUDA tensors.
 """
 from __future__ import annotations
@@ -77,6 +77,36 @@ def transform_torch(points: torch.Tensor, transformation: torch.Tensor) -> torch
     out = torch.empty_like(pts)
     P.check(lib.pinq_transform_points(P.ptr(pts), pts.shape[0], P.ptr(T12), P.ptr(out), P.stream()))
     return out
+
+
+def deskewing(points: torch.Tensor, ts: torch.Tensor, pose: torch.Tensor, ts_mid_pose: float = 0.5) -> torch.Tensor:
+    """Motion undistortion of a sweep, in place like the reference (utils/tools.py:540-567): ts normalised to [0, 1] over the
+    cloud, tau = ts - ts_mid_pose, p <- slerp(I, R, tau) p + tau t with pose = T_last<-cur.  One kernel (pinq_deskew)."""
+    if ts is None:
+        return points
+    lib = P.load()
+    if points.dtype != torch.float32 or not points.is_contiguous():
+        raise P.PinqError("deskewing works in place on a contiguous float32 cloud")
+    t = ts.detach().reshape(-1).to(torch.float32).contiguous()
+    n = points.shape[0]
+    if n == 0:
+        return points
+    lo, hi = torch.aminmax(t)
+    minmax = torch.stack((lo, hi))
+    T = pose.detach().to(device=points.device, dtype=torch.float32).contiguous()
+    P.check(lib.pinq_deskew(P.ptr(points), n, points.shape[1], P.ptr(t), P.ptr(minmax), P.ptr(T), float(ts_mid_pose), P.stream()))
+    return points
+
+
+def velodyne_point_ts(points: torch.Tensor) -> torch.Tensor:
+    """Per-point time in [0, 1] of a scan without time stamps, Velodyne convention (dataset/slam_dataset.py:247-249)."""
+    lib = P.load()
+    pts = points.detach()
+    if pts.dtype != torch.float32 or not pts.is_contiguous():
+        pts = pts.float().contiguous()
+    ts = torch.empty(pts.shape[0], dtype=torch.float32, device=pts.device)
+    P.check(lib.pinq_velodyne_point_ts(P.ptr(pts), pts.shape[0], pts.shape[1], P.ptr(ts), P.stream()))
+    return ts
 
 
 def transform_batch_torch(points: torch.Tensor, transformation: torch.Tensor) -> torch.Tensor:

@@ -42,6 +42,8 @@ def main():
     ap.add_argument("--azimuth", type=int, default=1875)
     ap.add_argument("--init-iter-ratio", type=int, default=None)
     ap.add_argument("--out", default=None)
+    ap.add_argument("--cuda-repeats", type=int, default=1, help="extra CUDA runs on the same scans and draws (atomics order differs "
+                    "from run to run): the spread of the CUDA path against itself and against the oracle")
     args = ap.parse_args()
     from pin_slam_b200 import synth
     from pin_slam_b200.slam import absolute_trajectory_error, run_slam
@@ -59,6 +61,8 @@ def main():
         frames = [synth.lidar_scan(scene, gt[i], dirs, rng) for i in range(args.frames)]
     gen_s = time.time() - t0
     res = run_slam(make_cfg("cuda", args), frames, None, generator=torch.Generator().manual_seed(7))
+    repeats = [run_slam(make_cfg("cuda", args), frames, None, generator=torch.Generator().manual_seed(7))["poses"]
+               for _ in range(max(args.cuda_repeats - 1, 0))]
     tt = res["time_table"]
     out = {"frames": args.frames, "rays_per_scan": int(dirs.shape[0]), "points_per_scan_mean": float(np.mean([f.shape[0] for f in frames])),
            "scan_generation_s": gen_s,
@@ -97,6 +101,10 @@ def main():
                          "tracking_iters_mean": float(np.mean(orc.tracking_iters)) if orc.tracking_iters else None,
                          "tracking_iters": [int(v) for v in orc.tracking_iters],
                          "neural_points": int(orc.s.points.shape[0])}
+        if repeats:
+            out["oracle"]["ate_cuda_repeats_vs_oracle_m"] = [absolute_trajectory_error(r[:n], poses, align=False) for r in repeats]
+    if repeats:
+        out["ate_cuda_repeats_vs_first_cuda_m"] = [absolute_trajectory_error(r, res["poses"], align=False) for r in repeats]
     line = json.dumps(out)
     print(line)
     if args.out:

@@ -184,3 +184,9 @@ def golden_cuda_world(G):
         dec.lout.weight.copy_(torch.from_numpy(G["W2"]))
         dec.lout.bias.copy_(torch.from_numpy(G["b2"]))
     return m, dec, cfg
+
+
+def load_golden_preprocess():
+    """Fourth fixture (oracle/make_golden.py main_preprocess): deskewing, three frames through the reference's SLAMDataset
+    (Velodyne point times, voxel down-sampling, crop, KITTI correction, source points, deskew), Mapper.dynamic_filter."""
+    return {k: v for k, v in np.load(os.path.join(ROOT, "tests", "golden", "ref_kitti_preprocess.npz")).items()}
