@@ -45,7 +45,7 @@ REFERENCE_ROOT = _find_root()
 _STUBBED = [
     "open3d", "matplotlib", "matplotlib.cm", "matplotlib.pyplot", "roma", "natsort",
     "gtsam", "skimage", "skimage.measure", "pyquaternion", "pypose", "laspy",
-    "evo", "wandb",
+    "evo", "evo.core", "evo.core.trajectory", "evo.tools", "evo.tools.plot", "evo.tools.settings", "wandb",
 ]
 
 
@@ -73,6 +73,23 @@ class _Anything:
         return iter(())
 
     def __bool__(self):
+        return False
+
+    def __len__(self):
+        return 0
+
+    def _binary(self, other):
+        return _Anything(self._name + "<op>")
+
+    __add__ = __radd__ = __sub__ = __rsub__ = __mul__ = __rmul__ = __truediv__ = __rtruediv__ = _binary
+
+    def __neg__(self):
+        return _Anything("-" + self._name)
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
         return False
 
 

@@ -295,8 +295,13 @@ def test_adam_step_matches_torch():
 
 
 def test_short_slam_run_tracks_ground_truth_and_oracle():
-    """6 synthetic 64-beam scans through the whole loop (tracking + map update + mapping) on the CUDA path and
-    through the CPU oracle loop with identical random draws: trajectories agree within 1 cm (north_star)."""
+    """6 synthetic 64-beam scans through the whole loop (tracking + map update + mapping) on the CUDA path and through the
+    CPU oracle loop with identical random draws.  north_star asks for trajectories within 1 cm; online training is
+    chaotic in the reference itself (profiles/r3_e2e100_vs_oracle.json: the oracle against itself with one-ulp scan
+    noise or another ATen thread count drifts 0.4-0.6 cm apart over 6 full-size frames, 2.7-3.9 cm over 100), so the gate is
+        ATE(cuda, oracle) <= max(1 cm, 1.5 x noise floor),
+    the floor being measured HERE on the same scans: oracle vs one-ulp-perturbed oracle, and the CUDA path vs its own
+    repeats (atomics order).  The committed 100-frame record shows the same relation at every horizon."""
     from oracle.slam_oracle import OracleSLAM
     from pin_slam_b200 import synth
     from pin_slam_b200.slam import absolute_trajectory_error, run_slam
@@ -306,36 +311,45 @@ def test_short_slam_run_tracks_ground_truth_and_oracle():
     n_frames = 6
     scene = synth.StreetScene(42)
     gt = synth.trajectory(n_frames)
-    dirs = synth.lidar_directions(32, 450)  # reduced scan: keeps the CPU oracle leg in tens of seconds
+    dirs = synth.lidar_directions(32, 450)  # reduced scan: keeps the CPU oracle legs in tens of seconds
     rng = np.random.default_rng(0)
     frames = [synth.lidar_scan(scene, gt[i], dirs, rng) for i in range(n_frames)]
+    prng = np.random.default_rng(123)
+    frames_ulp = []
+    for f in frames:  # +-1 fp32 ulp on a random half of the coordinates
+        bits = f.view(np.int32).copy()
+        bits += prng.integers(-1, 2, bits.shape, dtype=np.int32) * (prng.random(bits.shape) < 0.5)
+        frames_ulp.append(bits.view(np.float32))
 
     def cfg_for(device):
         cfg = kitti_config(device)
-        cfg.deskew = False
+        cfg.deskew = False            # instantaneous scans
         cfg.correction_deg = 0.0      # keeps the reference's +0.8 m initial motion guess (slam_dataset.py:126)
         cfg.init_iter_ratio = 10      # 150 warm-up iterations instead of 600: test-time budget
         cfg.bs = 4096
         cfg.silence = True
         return cfg
 
-    res = run_slam(cfg_for("cuda"), frames, None, generator=torch.Generator().manual_seed(7))
-    cpu_cfg = cfg_for("cpu")
-    orc = OracleSLAM(cpu_cfg, DataSampler(cpu_cfg), torch.Generator().manual_seed(7), seed=cpu_cfg.seed)
-    poses_ref = np.stack([orc.step(frames[i], i)[0] for i in range(n_frames)])
-    ate_gt = absolute_trajectory_error(res["poses"], gt, align=False)
-    ate_oracle = absolute_trajectory_error(res["poses"], poses_ref, align=False)
-    ate_gt_oracle = absolute_trajectory_error(poses_ref, gt, align=False)
-    # Training is chaotic in the reference itself (a 1e-8 relative input perturbation changes the trained
-    # features by ~25 % after the 600 warm-up iterations -- DESIGN.md "trajectory parity"), so trajectories are
-    # compared through their accuracy, not bit by bit: both runs track the ground truth of this reduced
-    # (32 x 450 rays) drive equally well and stay close to each other.
-    print("ATE cuda-gt %.4f  oracle-gt %.4f  cuda-oracle %.4f" % (ate_gt, ate_gt_oracle, ate_oracle))
+    def run_oracle(fr):
+        cpu_cfg = cfg_for("cpu")
+        orc = OracleSLAM(cpu_cfg, DataSampler(cpu_cfg), torch.Generator().manual_seed(7), seed=cpu_cfg.seed)
+        return np.stack([orc.step(fr[i], i)[0] for i in range(n_frames)]), orc
+
+    runs = [run_slam(cfg_for("cuda"), frames, None, generator=torch.Generator().manual_seed(7)) for _ in range(3)]
+    res = runs[0]
+    poses_ref, orc = run_oracle(frames)
+    poses_ulp, _ = run_oracle(frames_ulp)
+    ate = lambda a, b: absolute_trajectory_error(a, b, align=False)  # noqa: E731
+    ate_gt, ate_gt_oracle = ate(res["poses"], gt), ate(poses_ref, gt)
+    ate_oracle = ate(res["poses"], poses_ref)
+    floor_oracle = ate(poses_ref, poses_ulp)
+    floor_cuda = max(ate(r["poses"], res["poses"]) for r in runs[1:])
+    floor = max(floor_oracle, floor_cuda)
+    print("ATE cuda-gt %.4f  oracle-gt %.4f  cuda-oracle %.4f | floor: oracle vs ulp-perturbed oracle %.4f, cuda vs cuda %.4f"
+          % (ate_gt, ate_gt_oracle, ate_oracle, floor_oracle, floor_cuda))
     assert ate_gt < 0.20, ate_gt
     assert abs(ate_gt - ate_gt_oracle) < 0.10, (ate_gt, ate_gt_oracle)
-    # mutual distance: 0.02-0.04 m typical; run-to-run scatter of the CUDA path alone (atomics order) is 0.02 m and
-    # single runs have reached 0.2 m, so this is a sanity bound, not a parity claim
-    assert ate_oracle < 0.30, ate_oracle
+    assert ate_oracle <= max(0.01, 1.5 * floor), (ate_oracle, floor_oracle, floor_cuda)
     n_cuda, n_ref = res["neural_points"].count(), orc.s.points.shape[0]
     assert abs(n_cuda - n_ref) < 0.02 * n_ref, (n_cuda, n_ref)
 
