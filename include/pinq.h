@@ -470,6 +470,29 @@ int pinq_pool_move(const pinq_pool_view* old_pool, int64_t n_pool, const pinq_po
                    int64_t new_ts, const int32_t* kept_index, const int32_t* d_count, const pinq_pool_view* out,
                    int32_t* d_kept_new, void* stream);
 
+/* ---- iso-surface extraction over the mesher's dense grid -----------------------------------
+ * Replaces utils/mesher.py:310-337 `mc_mesh` (skimage.measure.marching_cubes(sdf, level, allow_degenerate=False,
+ * mask=mask) on the host).  Grid = what pinq_mesher_grid_query writes: x-major, z fastest, dims = {nx, ny, nz}.
+ * A cell is processed when all eight of its corners are masked in (mask may be NULL = everything).  Two calls so that
+ * the caller owns all memory:
+ *   pinq_mc_count  classifies cells and owned edges, scans -> d_counts2 = {vertices, triangles} (device int32[2])
+ *   pinq_mc_emit   verts_out float32 [V,3] = origin + (grid position) * voxel, faces_out int32 [T,3] (+ vertex_base:
+ *                  lets several slabs share one vertex array).  `dims3_host` describes the slab handed in, `x_first` the
+ *                  index of its first x layer in the whole grid and `origin3_host` the WHOLE grid's origin: coordinates
+ *                  are computed from global grid indices, so the vertices on the layer two slabs (or two ranks) share
+ *                  are bit-identical on both sides.  Deterministic order: vertices by owner grid point then
+ *                  axis, triangles by cell; every vertex is emitted once (indexed mesh, no duplicate removal needed
+ *                  inside a slab).  Zero-area triangles are NOT removed here (`allow_degenerate=False` is a filter
+ *                  on the output, done by the caller).
+ * `scratch`: pinq_mc_scratch_bytes(nx * ny * nz) bytes, shared by the two calls.  pinq_mc_tables copies the
+ * 256-case table the kernels use (edge ids, 16 per case, -1 padded; triangles per case) for inspection / tests. */
+int64_t pinq_mc_scratch_bytes(int64_t n_points);
+int pinq_mc_tables(int8_t* tri_out_256x16, uint8_t* ntri_out_256);
+int pinq_mc_count(const float* sdf, const uint8_t* mask, const int32_t* dims3_host, float level, void* scratch,
+                  int32_t* d_counts2, void* stream);
+int pinq_mc_emit(const float* sdf, const int32_t* dims3_host, int32_t x_first, float level, const float* origin3_host,
+                 float voxel, const void* scratch, int32_t vertex_base, float* verts_out, int32_t* faces_out, void* stream);
+
 /* Motion undistortion of a sweep (row f1): utils/tools.py:540-567 `deskewing` with the per-point times of
  * dataset/slam_dataset.py:233-257.  pinq_velodyne_point_ts: ts = 0.5 (-atan2(y, x) / pi + 1) for scans without time stamps
  * (KITTI .bin); pinq_deskew, in place: tau = (ts - min ts) / (max ts - min ts) - ts_mid_pose,

@@ -136,6 +136,10 @@ SIGNATURES = {
     "pinq_peer_error_offset": (_i64, []),
     "pinq_peer_exchange": (C.c_int, [C.POINTER(PeerArgs), _vp]),
     "pinq_ray_samples": (C.c_int, [_vp, _i64, _vp, _vp, _vp, _i32, _i32, _i32, _f32, _f32, _f32, _f32, _f32, _i32, _i32, _vp, _vp, _vp, _vp]),
+    "pinq_mc_scratch_bytes": (_i64, [_i64]),
+    "pinq_mc_tables": (C.c_int, [_vp, _vp]),
+    "pinq_mc_count": (C.c_int, [_vp, _vp, C.POINTER(_i32), _f32, _vp, _vp, _vp]),
+    "pinq_mc_emit": (C.c_int, [_vp, C.POINTER(_i32), _i32, _f32, C.POINTER(_f32), _f32, _vp, _i32, _vp, _vp, _vp]),
     "pinq_velodyne_point_ts": (C.c_int, [_vp, _i64, _i32, _vp, _vp]),
     "pinq_deskew": (C.c_int, [_vp, _i64, _i32, _vp, _vp, _vp, _f32, _vp]),
     "pinq_pool_flags": (C.c_int, [_vp, _i64, _vp, _i64, _vp, _f32, _vp, _vp]),

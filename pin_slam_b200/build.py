@@ -14,7 +14,7 @@ ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libpinq.so")
 STAMP = os.path.join(HERE, ".libpinq.stamp")
-SOURCES = ["table.cu", "index.cu", "sort.cu", "brick.cu", "query.cu", "query_bwd.cu", "gn.cu", "mapping.cu", "peer.cu", "pool.cu", "frame.cu"]
+SOURCES = ["table.cu", "index.cu", "sort.cu", "brick.cu", "query.cu", "query_bwd.cu", "gn.cu", "mapping.cu", "peer.cu", "pool.cu", "frame.cu", "mc.cu"]
 HEADERS = [os.path.join(CSRC, "common.cuh"), os.path.join(CSRC, "query_common.cuh"), os.path.join(CSRC, "mma.cuh"), os.path.join(CSRC, "brick.cuh"), os.path.join(CSRC, "decode_tc.cuh"), os.path.join(CSRC, "tc.cuh"), os.path.join(CSRC, "bwd_tc.cuh"),
            os.path.join(ROOT, "include", "pinq.h")]
 NVCC_FLAGS = [

@@ -92,7 +92,17 @@ def main():
     argv0 = sys.argv
     sys.argv = ["pin_slam.py", yaml_path]
     cwd = os.getcwd()
-    os.chdir(ROOT)  # setup_experiment runs `git rev-parse HEAD` (utils/tools.py:73)
+    # setup_experiment runs `git rev-parse HEAD` in the working directory (utils/tools.py:73): use this repository, or --
+    # on the GPU box, whose snapshot has no .git -- a scratch repository with one empty commit
+    import subprocess
+    work = ROOT
+    if subprocess.run(["git", "rev-parse", "HEAD"], cwd=ROOT, capture_output=True).returncode != 0:
+        work = os.path.join(root, "gitwork")
+        os.makedirs(work, exist_ok=True)
+        subprocess.run(["git", "init", "-q"], cwd=work, check=True)
+        subprocess.run(["git", "-c", "user.name=pinq", "-c", "user.email=pinq@localhost", "commit", "-q", "--allow-empty", "-m", "scratch"],
+                       cwd=work, check=True)
+    os.chdir(work)
     t1 = time.time()
     try:
         pin_slam.run_pin_slam()
