@@ -68,6 +68,9 @@ def parse():
     ap.add_argument("--eager-sample", type=int, default=1 << 20, help="queries per step of the reference CUDA-eager comparator")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-extra-legs", action="store_true", help="skip flavours / sweep / configs[3] mapping / configs[4] mesher")
+    ap.add_argument("--driver-frames", type=int, default=100, help="N=1 only: frames of the run through the reference's unchanged "
+                    "pin_slam.py (drop-in and reference CUDA-eager); 0 = skip")
     ap.add_argument("--slam-seeded", action="store_true", help="SLAM leg: a seeded CPU generator for the sampler and the batch draws "
                     "(reproducible, slower) instead of torch's device RNG (what the reference uses)")
     ap.add_argument("--slam-frames", type=int, default=30, help="N=1 only: frames of the synthetic 64-beam SLAM run reported "
@@ -328,6 +331,234 @@ def workload_config(args, m, vbar, world):
             "mean_nonempty_slots": round(vbar, 2),
             "reference_arm_queries_per_step": int(min(args.cpu_sample, args.queries)),
             "parallelism": "replicated map, queries sharded x%d" % world}
+
+
+# ------------------------------------------------------------------------------------------------
+# Extra legs carried inside the same JSON line: other flavours of the path, the configuration
+# sweep of BASELINE configs[2], configs[3] (batched mapping, strong scaling) and configs[4] (mesher grid + marching cubes).
+def _max_over_ranks(ms, dev, world):
+    import torch.distributed as dist
+    t = torch.tensor([ms], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def flavour_legs(npts, dec, q, vbar, hbm):
+    """Tracking flavour (fwd + d sdf/dx + std, inference mode; SURVEY 8(d): 577 + 20 V-bar B/query) at the bench batch and in
+    the latency regime of a Gauss-Newton iteration (15 000 source points); mesher flavour (forward only, global map, no time
+    filter, coordinates generated in-kernel; 533 + 12 V-bar B/point with V-bar measured on the grid points)."""
+    from pin_slam_b200.utils.mesher import Mesher
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    out = {}
+
+    def timed(fn, reps, warm=3):
+        for _ in range(warm):
+            fn()
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(reps):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / reps
+
+    with torch.no_grad():
+        n = q.shape[0]
+        ms = timed(lambda: npts.query_sdf(q, dec, None, False, True, want_grad=True, want_std=True), 10)
+        bq = 577.0 + 20.0 * round(vbar, 2)
+        out["tracking"] = {"queries_per_s": n / (ms * 1e-3), "ms": ms, "queries": n, "bytes_per_query": bq,
+                           "frac": n / (ms * 1e-3) * bq / (hbm * 1e9), "outputs": "sdf, d sdf/dx, std, nn_count"}
+        q15 = q[:15000].contiguous()
+        ms15 = timed(lambda: npts.query_sdf(q15, dec, None, False, True, want_grad=True, want_std=True), 200, 20)
+        out["tracking"]["latency_regime"] = {"queries": 15000, "us_per_call": ms15 * 1e3, "queries_per_s": 15000 / (ms15 * 1e-3),
+                                             "what": "one Gauss-Newton iteration's query (host launch path included)"}
+        mesher = Mesher(npts.config, npts, dec, None, None)
+        pts = npts.neural_points
+        lo = pts.min(0).values.cpu().numpy()
+        hi = lo + np.array([64.0, 64.0, pts.max(0).values.cpu().numpy()[2] - lo[2]])
+        hi[:2] = np.minimum(hi[:2] + 100.0, pts.max(0).values.cpu().numpy()[:2])   # a 164 m x 164 m tile of the map at 0.1 m
+        dims, origin = mesher.grid_from_bounds(lo, hi, 0.1)
+        total = int(np.prod(dims))
+        for _ in range(2):
+            e0.record()
+            sdf, mask, _, _, _ = mesher.query_grid(lo, hi, 0.1, mask_min_nn_count=npts.config.mesh_min_nn)
+            e1.record()
+            torch.cuda.synchronize()
+            msg = e0.elapsed_time(e1)
+        # V-bar of the grid points (global table, no time filter)
+        g = torch.randint(0, total, (100_000,), device=q.device)
+        iz, r = g % int(dims[2]), g // int(dims[2])
+        iy, ix = r % int(dims[1]), r // int(dims[1])
+        gp = torch.stack((ix, iy, iz), 1).float() * 0.1 + torch.tensor(origin, dtype=torch.float32, device=q.device)
+        vg = mean_nonempty_slots(npts, gp)
+        bm = 533.0 + 12.0 * vg
+        out["mesher"] = {"points_per_s": total / (msg * 1e-3), "ms": msg, "grid_points": total, "grid_dims": [int(v) for v in dims],
+                         "mean_nonempty_slots": vg, "bytes_per_point": bm, "frac": total / (msg * 1e-3) * bm / (hbm * 1e9),
+                         "masked_in_fraction": float((mask != 0).float().mean())}
+        del sdf, mask
+    return out
+
+
+def sweep_legs(args, hbm):
+    """BASELINE configs[2] spans 1-10 M queries against 0.5-5 M neural points: the same step at the small and the large end."""
+    from pin_slam_b200 import synth
+    out = []
+    for name, n, surf, side in (("1M x 0.5M", 1_000_000, 3_000_000, 200.0), ("10M x 5M", 10_000_000, 30_000_000, 640.0)):
+        try:
+            cfg, npts, dec = build_map(argparse.Namespace(surface_points=surf, side=side), "cuda")
+            q = torch.from_numpy(synth.microbench_queries(npts.neural_points.cpu().numpy(), n, seed=1)).cuda()
+            ts = torch.zeros(n, dtype=torch.int64, device="cuda")
+            ones = torch.ones(n, device="cuda")
+            vbar = mean_nonempty_slots(npts, q)
+            params = [npts.local_geo_features] + list(dec.parameters())
+
+            def step():
+                for p in params:
+                    p.grad = None
+                o = npts.query_sdf(q, dec, ts, True, True)
+                o["sdf"].backward(ones)
+            for _ in range(3):
+                step()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            torch.cuda.synchronize()
+            e0.record()
+            for _ in range(10):
+                step()
+            e1.record()
+            torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1) / 10
+            bq = 788.0 + 20.0 * round(vbar, 2)
+            out.append({"config": name, "queries": n, "neural_points": int(npts.count()), "map_side_m": side, "mean_nonempty_slots": round(vbar, 2),
+                        "ms_per_step": ms, "value": n / (ms * 1e-3), "unit": UNIT, "bytes_per_query": bq,
+                        "frac": n / (ms * 1e-3) * bq / (hbm * 1e9), "brick_index": bool(npts._brick_safe() and npts.use_brick_index)})
+            del npts, dec, q, ts, ones, params
+            torch.cuda.empty_cache()
+        except Exception as e:  # the headline must not depend on this leg
+            out.append({"config": name, "error": repr(e)[:200]})
+    return out
+
+
+def mapping_leg(dev, world, rank, iters=15, batch=1 << 20, pool_n=8_000_000):
+    """BASELINE configs[3]: batched mapping, 2^20 samples per iteration drawn with one shared seed, every rank trains on its
+    slice, pinq_peer_exchange with the fused Adam per iteration (strong scaling: the global batch is fixed)."""
+    import torch.distributed as dist
+    from pin_slam_b200 import synth
+    from pin_slam_b200.parallel import DataParallelMapping, MappingPeer, PeerExchange
+    from pin_slam_b200.utils.mapper import Mapper
+    cfg, npts, dec = build_map(argparse.Namespace(surface_points=12_000_000, side=400.0), dev)
+    g = torch.Generator().manual_seed(3)
+    pool = torch.from_numpy(synth.microbench_queries(npts.neural_points.cpu().numpy(), pool_n, seed=5)).to(dev)
+    label = (torch.randn(pool_n, generator=g) * 0.1).to(dev)
+    weight = torch.ones(pool_n, device=dev)
+    tsp = torch.zeros(pool_n, dtype=torch.int64, device=dev)
+    mapper = Mapper(cfg, None, npts, dec, None, None)
+    cfg.bs, cfg.bs_new_sample = batch, 0
+    mapper.global_coord_pool, mapper.coord_pool = pool, pool
+    mapper.sdf_label_pool, mapper.weight_pool, mapper.time_pool = label, weight, tsp
+    mapper.pool_sample_count = pool_n
+    mapper.generator = torch.Generator(device=dev).manual_seed(11)  # the same Philox stream on every rank
+    peer = None
+    rows, fdim = npts.local_geo_features.shape
+    if world > 1:
+        peer = PeerExchange(MappingPeer.capacity(rows, fdim, dec, with_params=True), dev)
+        torch.cuda.synchronize()
+        dist.barrier()
+        mapper.dp = DataParallelMapping(peer)
+    for _ in range(2):
+        mapper._mapping_fused(iters)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0.record()
+    mapper._mapping_fused(iters)
+    e1.record()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    ms = _max_over_ranks(e0.elapsed_time(e1), dev, world)
+    n_eik = 6 * ((batch + cfg.gradient_decimation - 1) // cfg.gradient_decimation)
+    res = {"samples_per_iter": batch, "queries_per_iter": batch + n_eik, "iters": iters, "neural_points": int(npts.count()),
+           "ms_per_iter": ms / iters, "samples_per_s": batch * iters / (ms * 1e-3), "scaling": "strong",
+           "form": "device-side loop (pinq_mapping_run)" + (", pinq_peer_exchange with fused Adam per iteration" if world > 1 else "")}
+    if peer is not None:
+        dist.barrier()
+        peer.close()
+    del mapper, pool, label, weight, tsp
+    torch.cuda.empty_cache()
+    return res, (cfg, npts, dec)
+
+
+def mesher_leg(world_map, dev, world, rank, voxel=0.1):
+    """BASELINE configs[4]: 0.1 m grid over the 400 m map, x-slabs per rank, no collective: the dense query alone
+    (grid points/s, time to the full grid) and query + marching cubes (triangles/s)."""
+    import torch.distributed as dist
+    from pin_slam_b200.utils.mesher import Mesher
+    cfg, npts, dec = world_map
+    mesher = Mesher(cfg, npts, dec, None, None)
+    pts = npts.neural_points
+    lo, hi = pts.min(0).values.cpu().numpy(), pts.max(0).values.cpu().numpy()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    res = {}
+    for rep in range(2):  # first pass warms the allocator
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        e0.record()
+        sdf, mask, first, dims, origin = mesher.query_grid(lo, hi, voxel, mask_min_nn_count=cfg.mesh_min_nn, rank=rank, world=world)
+        e1.record()
+        torch.cuda.synchronize()
+        ms_q = _max_over_ranks(e0.elapsed_time(e1), dev, world)
+        del sdf, mask
+    total = int(np.prod(dims))
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0.record()
+    v, f, _, _ = mesher.recon_grid_mesh(lo, hi, voxel, cfg.mesh_min_nn, rank=rank, world=world)
+    e1.record()
+    torch.cuda.synchronize()
+    ms_m = _max_over_ranks(e0.elapsed_time(e1), dev, world)
+    tri = torch.tensor([float(f.shape[0]), float(v.shape[0])], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(tri)
+    res = {"voxel_m": voxel, "grid_dims": [int(x) for x in dims], "grid_points": total, "neural_points": int(npts.count()),
+           "seconds_to_full_grid": ms_q * 1e-3, "grid_points_per_s": total / (ms_q * 1e-3),
+           "seconds_query_plus_marching_cubes": ms_m * 1e-3, "triangles": int(tri[0].item()), "vertices": int(tri[1].item()),
+           "triangles_per_s": float(tri[0].item()) / (ms_m * 1e-3), "collective": "none (x-slabs per rank, one shared layer)"}
+    return res
+
+
+def slam_driver_leg(frames):
+    """BASELINE configs[1] through the reference's UNCHANGED pin_slam.py with pin_slam_b200.dropin (deskew and KITTI correction
+    on, run_kitti.yaml), and the same driver without the drop-in on the same GPU (reference CUDA-eager) -- separate processes."""
+    import tempfile
+    out = {}
+    data = tempfile.mkdtemp(prefix="pinq_kitti_bench_")
+    try:
+        for key, extra in (("dropin", ["--mode", "dropin"]), ("reference_cuda_eager", ["--mode", "reference", "--device", "cuda"])):
+            dst = os.path.join(data, key + ".json")
+            cmd = [sys.executable, os.path.join(ROOT, "scripts", "run_reference_driver.py"), "--frames", str(frames), "--data-dir", data,
+                   "--out", dst] + extra
+            p = subprocess.run(cmd, capture_output=True, text=True, timeout=900)
+            if p.returncode == 0 and os.path.exists(dst):
+                with open(dst) as f:
+                    out[key] = json.load(f)
+            else:
+                out[key] = {"error": (p.stderr or p.stdout)[-400:]}
+        if "poses" in out.get("dropin", {}) and "poses" in out.get("reference_cuda_eager", {}):
+            a = np.array(out["dropin"]["poses"])[:, [3, 7, 11]]
+            b = np.array(out["reference_cuda_eager"]["poses"])[:, [3, 7, 11]]
+            out["ate_dropin_vs_reference_cuda_eager_m"] = float(np.sqrt(((a - b) ** 2).sum(1).mean()))
+        for k in ("dropin", "reference_cuda_eager"):
+            out.get(k, {}).pop("poses", None)
+        if out.get("dropin", {}).get("frames_per_s") and out.get("reference_cuda_eager", {}).get("frames_per_s"):
+            out["speedup_vs_reference_cuda_eager"] = out["dropin"]["frames_per_s"] / out["reference_cuda_eager"]["frames_per_s"]
+    finally:
+        import shutil
+        shutil.rmtree(data, ignore_errors=True)
+    return out
 
 
 # ------------------------------------------------------------------------------------------------
@@ -606,20 +837,53 @@ def main():
         cpu_baseline, cuda_eager = reference_legs(args, npts, dec, q_host, ts_host)
 
     peer_err = peer.error() if peer is not None else 0
-    slam = None
+    config_line = workload_config(args, npts.count(), vbar, world)
+    slam = flav = sweep = mapping = mesher_res = None
+    if rank == 0 and world == 1 and not args.no_extra_legs:
+        try:
+            flav = flavour_legs(npts, dec, q, vbar, hbm)
+        except Exception as e:  # the headline line must not depend on these legs
+            flav = {"error": repr(e)[:300]}
+    if world > 1 and peer is not None:  # the microbench's peer block is not needed any more: free it before the other legs
+        npts.feature_grad_sink = dec.grad_sink = None
+        dist.barrier()
+        peer.close()
+        peer = grad_block = carve = None
+    del q, ts, ones, stage, relu_mask, perm, gf, sdf, nnc
+    npts = dec = None
+    torch.cuda.empty_cache()
+    if not args.no_extra_legs:
+        try:
+            mapping, world_map = mapping_leg(dev, world, rank)
+            mesher_res = mesher_leg(world_map, dev, world, rank)
+            del world_map
+            torch.cuda.empty_cache()
+        except Exception as e:
+            mapping = mapping or {"error": repr(e)[:300]}
+            mesher_res = mesher_res or {"error": repr(e)[:300]}
+    if rank == 0 and world == 1 and not args.no_extra_legs:
+        sweep = sweep_legs(args, hbm)
     if rank == 0 and world == 1 and args.slam_frames > 1:
         try:
             slam = slam_leg(args.slam_frames, not args.slam_seeded)
-        except Exception as e:  # the headline line must not depend on this leg
+        except Exception as e:
             slam = {"error": repr(e)[:200]}
+        if args.driver_frames > 1:
+            try:
+                slam["reference_driver"] = slam_driver_leg(args.driver_frames)
+            except Exception as e:
+                slam["reference_driver"] = {"error": repr(e)[:300]}
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
-                "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(args, npts.count(), vbar, world),
+                "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": config_line,
                 "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e,
                 "gpu_launches": LAUNCHES_PER_STEP * args.steps, "clocks": clocks}
         if slam is not None:
             line["slam"] = slam
+        for key, val in (("flavours", flav), ("mapping", mapping), ("mesher", mesher_res), ("sweep", sweep)):
+            if val is not None:
+                line[key] = val
         if cuda_eager is not None:
             line["reference_cuda_eager"] = cuda_eager
         line["exchange"] = {"none": "none", "nccl": "NCCL all-reduce of feature+decoder grads",
@@ -634,10 +898,6 @@ def main():
             line["ms_per_step_without_exchange"] = no_exchange_ms
         print(json.dumps(line))
     if world > 1:
-        if peer is not None:
-            npts.feature_grad_sink = dec.grad_sink = None
-            dist.barrier()
-            peer.close()
         dist.destroy_process_group()
 
 

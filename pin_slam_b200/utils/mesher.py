@@ -156,7 +156,7 @@ class Mesher:
         return verts.cpu().numpy().astype(np.float64), faces.cpu().numpy()
 
     def recon_grid_mesh(self, min_bound, max_bound, voxel_size, mask_min_nn_count: int = None, query_locally: bool = False,
-                        rank: int = 0, world: int = 1, max_points: int = 1 << 28):
+                        rank: int = 0, world: int = 1, max_points: int = 1 << 28, level: float = 0.0):
         """Dense query + marching cubes of the slab of x-layers this rank owns (no collective: the slabs overlap by one layer of
         grid points, so every cell belongs to exactly one rank and boundary vertices are bit-identical on both sides).  Slabs
         larger than `max_points` grid points are walked in x-chunks.  -> (verts [V,3] f32, faces [T,3] i64, dims, origin)."""
@@ -186,7 +186,7 @@ class Mesher:
                 a.workspace = P.ptr(npts._workspace(c))
                 P.check(lib.pinq_mesher_grid_query(a, origin32, dims32, float(voxel_size), c0 * layer + off, c, int(mask_min_nn_count),
                                                    sdf[off:].data_ptr(), mask[off:].data_ptr(), P.stream()))
-            v, f = self.extract_mesh(sdf, mask, (c1 - c0 + 1, ny, nz), origin, voxel_size, vertex_base=vbase, x_first=c0)
+            v, f = self.extract_mesh(sdf, mask, (c1 - c0 + 1, ny, nz), origin, voxel_size, level=level, vertex_base=vbase, x_first=c0)
             all_v.append(v)
             all_f.append(f)
             vbase += v.shape[0]

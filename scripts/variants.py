@@ -40,7 +40,7 @@ def run(extra):
         if path:
             env["PINQ_LIB"] = path
         cmd = [sys.executable, os.path.join(ROOT, "bench.py"), "--steps", "10", "--warmup", "3", "--no-e2e", "--no-cpu-baseline",
-               "--slam-frames", "0"] + extra
+               "--slam-frames", "0", "--no-extra-legs"] + extra
         p = subprocess.run(cmd, env=env, capture_output=True, text=True)
         try:
             line = json.loads(p.stdout.strip().splitlines()[-1])

@@ -50,12 +50,15 @@ def test_mesh_of_the_reference_pinned_grid_and_its_shards():
     lo, hi, voxel, min_nn = G["mesh_lo"], G["mesh_hi"], float(G["mesh_voxel"]), int(G["mesh_min_nn"])
     sdf, mask, first, dims, origin = mesher.query_grid(lo, hi, voxel, pad_voxel=1, mask_min_nn_count=min_nn)
     dims = [int(v) for v in dims]
-    v, f = mesher.extract_mesh(sdf, mask, dims, origin, voxel)
-    v_ref, f_ref = M.marching_cubes(sdf.cpu().numpy().reshape(dims), mask.cpu().numpy().reshape(dims) != 0, 0.0, voxel, origin)
+    # the fixture's map carries random features: its SDF is negative everywhere, so the iso level is the median of the
+    # reference's own masked values (any level exercises the same code; 0.0 is what the mesher uses on a trained map)
+    level = float(np.float32(np.median(G["mesh_sdf"][G["mesh_mask"] != 0])))
+    v, f = mesher.extract_mesh(sdf, mask, dims, origin, voxel, level=level)
+    v_ref, f_ref = M.marching_cubes(sdf.cpu().numpy().reshape(dims), mask.cpu().numpy().reshape(dims) != 0, level, voxel, origin)
     assert len(f_ref) > 500 and np.array_equal(f.cpu().numpy(), f_ref)
     assert np.abs(v.cpu().numpy() - v_ref).max() < 1e-6
     # the reference's own grid (fixture) gives the same triangle count up to cells whose SDF differs in the last bits
-    v_g, f_g = M.marching_cubes(G["mesh_sdf"].reshape(dims).astype(np.float32), G["mesh_mask"].reshape(dims) != 0, 0.0, voxel, origin)
+    v_g, f_g = M.marching_cubes(G["mesh_sdf"].reshape(dims).astype(np.float32), G["mesh_mask"].reshape(dims) != 0, level, voxel, origin)
     assert abs(len(f_g) - len(f_ref)) <= 0.01 * len(f_ref)
     cnt = Counter(map(tuple, np.concatenate([f_ref[:, [0, 1]], f_ref[:, [1, 2]], f_ref[:, [2, 0]]])))
     assert all(k == 1 for k in cnt.values())
@@ -77,17 +80,17 @@ def test_mesh_of_the_reference_pinned_grid_and_its_shards():
     assert n_open > 0                                                        # the mask does cut this surface
     # ---- 3 ranks, no collective
     # (recon_grid_mesh pads like the reference's get_query_from_bbx default: no padding -> compare against its own whole grid)
-    whole_v, whole_f, d0, o0 = mesher.recon_grid_mesh(lo, hi, voxel, min_nn, rank=0, world=1)
+    whole_v, whole_f, d0, o0 = mesher.recon_grid_mesh(lo, hi, voxel, min_nn, rank=0, world=1, level=level)
     tris = lambda vv, ff: Counter(map(lambda t: tuple(map(tuple, t)), vv.cpu().numpy()[ff.cpu().numpy()].round(7).tolist()))  # noqa: E731
     want = tris(whole_v, whole_f)
     got = Counter()
     for r in range(3):
-        pv, pf, d1, o1 = mesher.recon_grid_mesh(lo, hi, voxel, min_nn, rank=r, world=3)
+        pv, pf, d1, o1 = mesher.recon_grid_mesh(lo, hi, voxel, min_nn, rank=r, world=3, level=level)
         assert list(d1) == list(d0)
         got += tris(pv, pf)
     assert got == want and sum(want.values()) == whole_f.shape[0] > 300
     # small chunks inside one rank walk the same slab
-    cv, cf, _, _ = mesher.recon_grid_mesh(lo, hi, voxel, min_nn, max_points=int(d0[1]) * int(d0[2]) * 5)
+    cv, cf, _, _ = mesher.recon_grid_mesh(lo, hi, voxel, min_nn, max_points=int(d0[1]) * int(d0[2]) * 5, level=level)
     assert tris(cv, cf) == want
 
 
