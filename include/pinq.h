@@ -232,6 +232,10 @@ typedef struct pinq_query_args {
     void* workspace;           /* pinq_query_workspace_bytes(n) bytes: search -> decode hand-off      */
     const int32_t* skip;       /* NULL, or a device flag: when non-zero at launch time the search / resolve /
                                   decode kernels of this call return at once (pinq_tracking_run)         */
+    void* decode_wait_event;   /* NULL, or a cudaEvent_t the DECODE waits for (cudaStreamWaitEvent on `stream`):
+                                  binning and the neighbour search read only query points and map geometry, so a
+                                  data-parallel caller lets them run under the previous step's gradient exchange /
+                                  optimizer (which the decode, reading features and decoder, must follow)   */
 } pinq_query_args;
 
 int64_t pinq_query_workspace_bytes(int64_t n);

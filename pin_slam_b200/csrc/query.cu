@@ -964,6 +964,7 @@ static int run_query(const pinq_query_args* a, int mode, float* feat_out, const 
             rc = check_launch("k_resolve");
             if (rc) return rc;
         }
+        if (a->decode_wait_event) cudaStreamWaitEvent(st, reinterpret_cast<cudaEvent_t>(a->decode_wait_event), 0);
         ktime_mark(PINQ_KT_DECODE, st);
         // persistent-ish grid: the decoder fragments are built once per CTA and amortised over its blocks
         const unsigned nb = grid_for(n, kBlock);
@@ -991,17 +992,27 @@ static int run_query(const pinq_query_args* a, int mode, float* feat_out, const 
         if (use_tc < 0) {
             const char* e = getenv("PINQ_DECODE");
             use_tc = !(e && e[0] == 'm');
-            cudaFuncSetAttribute(k_decode_tc<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc::kSmemRequest);
-            cudaFuncSetAttribute(k_decode_tc<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc::kSmemRequest);
-            cudaFuncSetAttribute(k_decode_tc<false>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
-            cudaFuncSetAttribute(k_decode_tc<true>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+            cudaFuncSetAttribute(k_decode_tc<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc::kSmemRequest);
+            cudaFuncSetAttribute(k_decode_tc<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc::kSmemRequest);
+            cudaFuncSetAttribute(k_decode_tc<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc::kSmemRequest);
+            cudaFuncSetAttribute(k_decode_tc<false, false>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+            cudaFuncSetAttribute(k_decode_tc<true, false>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+            cudaFuncSetAttribute(k_decode_tc<false, true>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
         }
-        if (use_tc && !a->grad_x && !(a->flags & PINQ_F_MMA_SYNC)) {
+        if (use_tc && !(a->grad_x && mode == 2) && !(a->flags & PINQ_F_MMA_SYNC)) {
             const unsigned nb128 = grid_for(n, tc::kRows);
-            const unsigned cap128 = (unsigned)sms * tc::kCtasPerSm;  // TMEM columns per CTA bound the residency
+            static int occ_tc_grad = 0;  // the gradient flavour holds more registers: fewer resident CTAs
+            if (!occ_tc_grad) {
+                cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_tc_grad, k_decode_tc<false, true>, tc::kRows, tc::kSmemRequest);
+                if (occ_tc_grad < 1) occ_tc_grad = 1;
+                if (occ_tc_grad > (int)tc::kCtasPerSm) occ_tc_grad = (int)tc::kCtasPerSm;
+            }
+            const unsigned per_sm = (a->grad_x && mode != 2) ? (unsigned)occ_tc_grad : tc::kCtasPerSm;
+            const unsigned cap128 = (unsigned)sms * per_sm;  // TMEM columns (and registers) per CTA bound the residency
             const unsigned g128 = nb128 < cap128 ? nb128 : cap128;
-            if (mode == 2) k_decode_tc<true><<<g128, tc::kRows, tc::kSmemRequest, st>>>(p);
-            else k_decode_tc<false><<<g128, tc::kRows, tc::kSmemRequest, st>>>(p);
+            if (mode == 2) k_decode_tc<true, false><<<g128, tc::kRows, tc::kSmemRequest, st>>>(p);
+            else if (a->grad_x) k_decode_tc<false, true><<<g128, tc::kRows, tc::kSmemRequest, st>>>(p);
+            else k_decode_tc<false, false><<<g128, tc::kRows, tc::kSmemRequest, st>>>(p);
         } else {
             const int occ = mode == 2 ? occ_mesh : (a->grad_x ? occ_grad : occ_plain);
             const unsigned cap = (unsigned)(sms * (occ > 0 ? occ : 1));

@@ -101,6 +101,7 @@ class NeuralPoints(nn.Module):
         # fused search through the brick index when it is provably equivalent (PINQ_BRICK=0: slot probing only)
         self.use_brick_index = os.environ.get("PINQ_BRICK", "1") != "0"
         self.exact_search_keys = False  # A/B tests: brick search with 64-bit keys for every query
+        self.decode_wait_event = None  # torch.cuda.Event the fused query's decode waits for (see pinq_query_args)
         self.use_mma_sync = False  # A/B tests: the mma.sync decode / backward kernels instead of the tcgen05 ones
         self._brick_tab = self._brick_global = self._brick_local = self._brick_buf = self._brick_counters = None
         self._brick_host = self._brick_event = None
@@ -546,6 +547,9 @@ class NeuralPoints(nn.Module):
             self._ts_keepalive = query_ts.to(torch.int64).contiguous()
             a.query_ts = P.ptr(self._ts_keepalive)
         a.workspace = P.ptr(self._workspace(x.shape[0]))
+        ev = getattr(self, "decode_wait_event", None)
+        if ev is not None:  # data-parallel callers: the decode follows this (recorded) event, binning + search do not
+            a.decode_wait_event = ev.cuda_event
         return a
 
     def query_feature(self, query_points: torch.Tensor, query_ts: torch.Tensor = None, training_mode: bool = True,
