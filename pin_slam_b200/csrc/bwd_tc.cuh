@@ -2,13 +2,16 @@
 //
 // Same algebra as k_bwd_mma (query_bwd.cu header), other mapping: tile k = neighbour k of a block of 128 queries, so
 // THREAD = QUERY = row.  Per tile the thread expands its 64 relu' bits into one bf16 row of the MASK tile and writes
-// a_k [f_k, v_k, 1] (2 bf16 pieces, round-to-nearest split) into the X tile; both tiles are stored [8-element chunk][row] x 16
+// a_k [f_k, v_k, 1] (2 fp16 pieces, round-to-nearest split, block-scaled) into the X tile; both tiles are stored [8-element chunk][row] x 16
 // bytes, which is the UMMA canonical no-swizzle layout K-major for (row x hidden) AND MN-major for its transpose:
 //   mask x V    D1[128 rows x 32]   = MASK (A, K-major)  x V3 (B, K-major; 3 pieces x 8 feature columns)     4 MMAs K=16
 //   G           D2[64 hidden x 24] += MASK^T (A, MN-major) x X (B, MN-major), reduction over the 128 rows      8 MMAs K=16
-// (X has 24 columns: 2 round-to-nearest bf16 pieces x 12 inputs: |x - (p0 + p1)| <= 2^-18 |x| and unbiased, and the decoder
-// gradient is a sum over all rows, so the pieces' rounding averages out -- measured 1e-6 relative on the four gradients;
-// three truncated pieces cost 10 KB of tile writes + 10 KB of operand reads per tile instead of 6 + 6).  Shared-memory bandwidth is what bounds this kernel (ncu: L1TEX 67 %):
+// Operand format: fp16 (11-bit significand), not bf16 (8).  MASK holds exact 0 / 1; X and V3 are split into round-to-nearest
+// fp16 pieces, each following piece pre-scaled by 2^11 (so that it stays in fp16's normal range) and re-scaled when the
+// products are combined: X = 2 pieces (|x - (p0 + 2^-11 p1)| <= 2^-22 |x|; 24 columns = 6 KB per tile instead of the 10 KB of
+// three bf16 pieces, which is what lets 4 CTAs share an SM), V3 = 3 pieces.  fp16's narrow exponent range is handled by a
+// power-of-two scale per block of 6 tiles: X is multiplied by 2^s with s chosen from the block's largest |dL/dsdf| so that the
+// largest entries sit near 2^7, and the flushed accumulator is multiplied by 2^-s -- exact.  Shared-memory bandwidth is what bounds this kernel (ncu: L1TEX 67 %):
 // per tile 26 KB of tile writes + 46 KB of operand reads by the tensor core.
 // D1 -> thread-local epilogue: dL/df_k = a_k (sum of the 3 pieces) -> red.global.add.v4.f32 x 2 into grad_features[idx_k].
 // D2 is flushed into fp32 shared-memory sums once per block of 6 tiles (768 rows), so the long reduction over rows is
@@ -39,6 +42,7 @@ struct Smem {  // the tiles are double-buffered: tile t + 1 is staged while the 
     alignas(8) unsigned long long bar[2];
     uint32_t tmem_base;
     float db2;
+    float wmax[2][kRows / 32];  // per-warp max |dL/dsdf| of a block, double-buffered by block parity
 };
 static_assert(sizeof(Smem) <= kSmemRequest, "bwd_tc shared memory");
 
@@ -49,11 +53,13 @@ __host__ __device__ constexpr int hidden_of_maskcol(int col) {
     return 16 * (2 * w + (s >> 3)) + 8 * ((s >> 2) & 1) + 2 * (s & 3) + e;
 }
 
-// D = f32, A = B = bf16
-constexpr uint32_t kIdescBase = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(kRows >> 4) << 24);
+// D = f32, A = B = f16 (format code 0; bf16 would be 1)
+constexpr uint32_t kIdescBase = (1u << 4) | (0u << 7) | (0u << 10) | ((uint32_t)(kRows >> 4) << 24);
+constexpr uint32_t kF16One = 0x3C00u;
+constexpr float kPieceUp = 2048.f, kPieceDown = 1.f / 2048.f;  // 2^11: scale of every following fp16 piece
 constexpr uint32_t kIdescMV = kIdescBase | ((uint32_t)(kVN >> 3) << 17);                           // K-major x K-major, N = 32
 // decoder-gradient product: M = 64 hidden units, N = 40, both operands MN-major (= transposed views of the row-major tiles)
-constexpr uint32_t kIdescG = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(kXCols >> 3) << 17) |
+constexpr uint32_t kIdescG = (1u << 4) | (0u << 7) | (0u << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(kXCols >> 3) << 17) |
                              ((uint32_t)(H >> 4) << 24);
 
 __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
@@ -65,11 +71,17 @@ __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint6
 __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
     asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" :: "l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
-// {bf16 rn(a) in the low half, bf16 rn(b) in the high half}: one cvt.rn.bf16x2.f32
-__device__ __forceinline__ uint32_t rn_bf16_pair(float a, float b) {
-    uint32_t r;
-    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(b), "f"(a));
-    return r;
+// {fp16 rn(a) in the low half, fp16 rn(b) in the high half} and the two residuals scaled by 2^11
+__device__ __forceinline__ uint32_t rn_f16_pair(float a, float b, float& ra, float& rb) {
+    const __half2 h = __floats2half2_rn(a, b);
+    const float2 f = __half22float2(h);
+    ra = (a - f.x) * kPieceUp;
+    rb = (b - f.y) * kPieceUp;
+    return *reinterpret_cast<const uint32_t*>(&h);
+}
+__device__ __forceinline__ uint32_t rn_f16_pair(float a, float b) {
+    const __half2 h = __floats2half2_rn(a, b);
+    return *reinterpret_cast<const uint32_t*>(&h);
 }
 
 }  // namespace tcb
@@ -89,14 +101,22 @@ __global__ void __launch_bounds__(tcb::kRows) k_bwd_tc(const BwdParams p) {
             uint32_t w[4];
 #pragma unroll
             for (int pr = 0; pr < 4; ++pr) {
-                __nv_bfloat16 b[2][3];
+                float v[2];
 #pragma unroll
                 for (int e2 = 0; e2 < 2; ++e2) {
                     const int j = hidden_of_maskcol(8 * kc + 2 * pr + e2);
-                    const float v = n < 24 ? __ldg(&p.dec.W2[j]) * __ldg(&p.dec.W1[j * IN + c]) : 0.f;
-                    bf16_split3(v, b[e2][0], b[e2][1], b[e2][2]);
+                    v[e2] = n < 24 ? __ldg(&p.dec.W2[j]) * __ldg(&p.dec.W1[j * IN + c]) : 0.f;
                 }
-                w[pr] = pack_bf16(b[0][s < 3 ? s : 0], b[1][s < 3 ? s : 0]);
+                uint32_t piece = 0u;  // piece s of v = h0 + 2^-11 h1 + 2^-22 h2
+#pragma unroll
+                for (int q = 0; q < 3; ++q) {
+                    float r0, r1;
+                    const uint32_t h = rn_f16_pair(v[0], v[1], r0, r1);
+                    if (q == s) piece = h;
+                    v[0] = r0;
+                    v[1] = r1;
+                }
+                w[pr] = piece;
             }
             *reinterpret_cast<uint4*>(S.v3 + e * 16) = make_uint4(w[0], w[1], w[2], w[3]);
         }
@@ -186,7 +206,8 @@ __global__ void __launch_bounds__(tcb::kRows) k_bwd_tc(const BwdParams p) {
                 float o[8];
 #pragma unroll
                 for (int c = 0; c < 8; ++c)
-                    o[c] = ((__uint_as_float(d1[c]) + __uint_as_float(d0[8 + c])) + __uint_as_float(d0[c])) * a_prev;
+                    o[c] = ((__uint_as_float(d1[c]) * (kPieceDown * kPieceDown) + __uint_as_float(d0[8 + c]) * kPieceDown) +
+                            __uint_as_float(d0[c])) * a_prev;
                 float* gf = p.grad_features + (int64_t)li_prev * F;
                 red_add_v4(gf, o[0], o[1], o[2], o[3]);
                 red_add_v4(gf + 4, o[4], o[5], o[6], o[7]);
@@ -196,7 +217,7 @@ __global__ void __launch_bounds__(tcb::kRows) k_bwd_tc(const BwdParams p) {
     };
     // G of a finished block (all its MMAs waited for) -> fp32 sums.  M = 64 accumulator layout: hidden row m sits in
     // TMEM lane (m % 16) + 32 (m / 16), i.e. lanes 0..15 of every warp (cute/atom/mma_traits_sm100.hpp, 1SM M_MMA == 64)
-    auto flush = [&]() {
+    auto flush = [&](float inv_scale) {
         if (DEC) {
 #pragma unroll
             for (int c3 = 0; c3 < (kXCols + 15) / 16; ++c3) {
@@ -206,14 +227,41 @@ __global__ void __launch_bounds__(tcb::kRows) k_bwd_tc(const BwdParams p) {
                 if (lane < 16) {
 #pragma unroll
                     for (int u = 0; u < 16; ++u)
-                        if (16 * c3 + u < kXCols) S.gacc[16 * c3 + u][16 * warp + lane] += __uint_as_float(v[u]);
+                        if (16 * c3 + u < kXCols) S.gacc[16 * c3 + u][16 * warp + lane] += __uint_as_float(v[u]) * inv_scale;
                 }
             }
             tc_fence_before();
         }
     };
+    // Power-of-two scale of a block's X tiles: 2^s with 2^s * scale * max_rows |dL/dsdf| in [2^7, 2^8) -- |w_k| <= 1 and the
+    // decoder inputs are O(1), so the fp16 pieces stay far below 65504 and far above the subnormal range for every row that
+    // matters to the sum.  Each warp publishes its max one block ahead (the value arrives with the block's index loads).
+    auto publish_max = [&](float g, int parity) {
+        float m = fabsf(g);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+        if (lane == 0) S.wmax[parity][warp] = m;
+    };
+    auto block_scale = [&](int parity, float& up, float& down) {
+        const float m = fmaxf(fmaxf(S.wmax[parity][0], S.wmax[parity][1]), fmaxf(S.wmax[parity][2], S.wmax[parity][3])) * fabsf(scale);
+        int e = (int)((__float_as_uint(m) >> 23) & 0xffu) - 127;  // floor(log2 m) for normal m
+        if (m == 0.f || e < -100) e = -100;
+        if (e > 100) e = 100;
+        up = __uint_as_float((uint32_t)(127 + 7 - e) << 23);
+        down = __uint_as_float((uint32_t)(127 - 7 + e) << 23);
+    };
+    float xscale = 1.f, xinv = 1.f, xinv_prev = 1.f;
+    int parity = 0;
+    if (DEC) {
+        publish_max(cg, 0);
+        __syncthreads();
+    }
     bool pending = false;  // the last tile of the previous block is still in flight
     for (int64_t blk = blockIdx.x; blk < nblocks; blk += gridDim.x) {
+        if (DEC) {
+            xinv_prev = xinv;
+            block_scale(parity, xscale, xinv);
+        }
         const int64_t i = blk * kRows + tid;
         const int64_t ni = i + (int64_t)gridDim.x * kRows;
         const bool has_next = blk + gridDim.x < nblocks;
@@ -240,24 +288,25 @@ __global__ void __launch_bounds__(tcb::kRows) k_bwd_tc(const BwdParams p) {
 #pragma unroll
                     for (int u4 = 0; u4 < 4; ++u4) {
                         const int u = 4 * hc + u4;
-                        r[u4] = (((u < 16 ? m.x : m.y) >> (u & 15)) & 0x00010001u) * kBf16One;
+                        r[u4] = (((u < 16 ? m.x : m.y) >> (u & 15)) & 0x00010001u) * kF16One;
                     }
                     *reinterpret_cast<uint4*>(S.mask[st] + hc * kChunk + tid * 16) = make_uint4(r[0], r[1], r[2], r[3]);
                 }
             }
-            // ---- X tile: a_k [f_k, v_k, 1] in 2 bf16 pieces (round to nearest), column = piece * 12 + input ----
+            // ---- X tile: 2^s a_k [f_k, v_k, 1] in 2 fp16 pieces (round to nearest), column = piece * 12 + input ----
             if (DEC) {
                 db2 += a;
+                const float as = a * xscale;
                 float ps[12] = {pfa[st].x, pfa[st].y, pfa[st].z, pfa[st].w, pfb[st].x, pfb[st].y, pfb[st].z, pfb[st].w,
                                 phv[st].x, phv[st].y, phv[st].z, phv[st].w};
 #pragma unroll
-                for (int c = 0; c < 12; ++c) ps[c] *= a;
+                for (int c = 0; c < 12; ++c) ps[c] *= as;
                 uint32_t wds[12];
 #pragma unroll
                 for (int ip = 0; ip < 6; ++ip) {
-                    const uint32_t hi = rn_bf16_pair(ps[2 * ip], ps[2 * ip + 1]);
-                    wds[ip] = hi;
-                    wds[6 + ip] = rn_bf16_pair(ps[2 * ip] - __uint_as_float(hi << 16), ps[2 * ip + 1] - __uint_as_float(hi & 0xffff0000u));
+                    float r0, r1;
+                    wds[ip] = rn_f16_pair(ps[2 * ip], ps[2 * ip + 1], r0, r1);
+                    wds[6 + ip] = rn_f16_pair(r0, r1);
                 }
 #pragma unroll
                 for (int c = 0; c < kXChunks; ++c)
@@ -266,7 +315,7 @@ __global__ void __launch_bounds__(tcb::kRows) k_bwd_tc(const BwdParams p) {
             }
             if (k == 0 && pending) {  // drain the previous block before its G^T accumulator is overwritten
                 epilogue(1);
-                flush();
+                flush(xinv_prev);
             }
             fence_async_smem();
             tc_fence_before();
@@ -294,6 +343,7 @@ __global__ void __launch_bounds__(tcb::kRows) k_bwd_tc(const BwdParams p) {
             }
             // ---- loads of the tile after the next, then the epilogue of the previous tile while the MMAs run ----
             if (k == 1 && has_next) load_block(ni, nidx, ng);
+            if (DEC && k == 3) publish_max(ng, parity ^ 1);  // read at the start of the next block, two barriers from here
             if (k + 2 < K) load_tile(i, k + 2, cidx[k + 2 < K ? k + 2 : 0]);
             else if (has_next) load_tile(ni, k + 2 - K, nidx[k + 2 >= K ? k + 2 - K : 0]);
             if (k > 0) epilogue(st ^ 1);
@@ -301,13 +351,14 @@ __global__ void __launch_bounds__(tcb::kRows) k_bwd_tc(const BwdParams p) {
             li_prev = li;
         }
         pending = true;
+        parity ^= 1;
 #pragma unroll
         for (int k = 0; k < K; ++k) cidx[k] = nidx[k];
         cg = ng;
     }
     if (pending) {
         epilogue(1);
-        flush();
+        flush(xinv);  // the last block's own scale
     }
 
     if (DEC) {
@@ -319,7 +370,7 @@ __global__ void __launch_bounds__(tcb::kRows) k_bwd_tc(const BwdParams p) {
         float* sG = reinterpret_cast<float*>(S.mask[0]);  // [H][12], the tiles are idle now
         for (int e = tid; e < H * 12; e += kRows) {
             const int c = e / 12, i = e - 12 * c, j = hidden_of_maskcol(c);
-            sG[j * 12 + i] = S.gacc[12 + i][c] + S.gacc[i][c];
+            sG[j * 12 + i] = S.gacc[12 + i][c] * kPieceDown + S.gacc[i][c];
         }
         __syncthreads();
         for (int e = tid; e < H * 12; e += kRows) {

@@ -37,8 +37,7 @@ constexpr size_t kSmemRequest = 40 * 1024;          // > 227 KB / 6: caps reside
 
 struct Smem {
     alignas(128) unsigned char b[kChunksB * kChunkBBytes];
-    alignas(16) float w2[H];   // W2 in accumulator-column order
-    alignas(16) float4 vv[H];  // gradient flavour: W2_j W1[j][8..10] (d s_k / d v_k = sum_j relu'(pre_j) vv_j), column order
+    alignas(16) float w2[H];  // W2 in accumulator-column order
     alignas(8) unsigned long long bar;
     uint32_t tmem_d, tmem_a;
 };
@@ -71,13 +70,7 @@ __device__ __forceinline__ void umma_tf32_ts(uint32_t tmem_d, uint32_t tmem_a, u
 
 }  // namespace tc
 
-// GRAD (tracking, utils/tracker.py:230-253 + utils/tools.py:174): d sdf/dx in the same pass.  d s_k / d v_k needs the relu' mask
-// times W2 W1[:, 8:11]: the epilogue already walks the 64 pre-activations of the row, so it adds 3 predicated FMAs per column
-// (FSET + 3 FFMA) instead of a second tensor-core product -- tracking batches are ~10^4 points (latency regime), and at 4 Mi
-// queries this is 0.8 ms against 1.45 ms of the mma.sync gradient kernel it replaces (profiles/r3f_bench.json).  The IDW part
-// of the gradient needs the un-normalised weights and the TRUE x - p_k (hazard H13): re-derived per query from the search's
-// rank workspace in finalize(), exactly like k_decode_mma<GRAD>.
-template <bool MESH, bool GRAD>
+template <bool MESH>
 __global__ void __launch_bounds__(tc::kRows) k_decode_tc(const DecodeParams p) {
     using namespace tc;
     if (p.skip && *p.skip) return;
@@ -89,11 +82,6 @@ __global__ void __launch_bounds__(tc::kRows) k_decode_tc(const DecodeParams p) {
     for (int c = tid; c < H; c += kRows) {
         const int j = hidden_of_col(c);
         S.w2[c] = __ldg(&p.dec.W2[j]);
-        if (GRAD) {
-            const float w2j = __ldg(&p.dec.W2[j]);
-            S.vv[c] = make_float4(w2j * __ldg(&p.dec.W1[j * IN + 8]), w2j * __ldg(&p.dec.W1[j * IN + 9]),
-                                  w2j * __ldg(&p.dec.W1[j * IN + 10]), 0.f);
-        }
         uint32_t hi[12], lo[12];
 #pragma unroll
         for (int i = 0; i < 12; ++i) tf32_split(l1_operand(p.dec, i, j), hi[i], lo[i]);
@@ -129,7 +117,6 @@ __global__ void __launch_bounds__(tc::kRows) k_decode_tc(const DecodeParams p) {
 
     uint32_t phase = 0u;
     float sdf = 0.f, sk[K], wk[K];
-    float gvx[GRAD ? K : 1], gvy[GRAD ? K : 1], gvz[GRAD ? K : 1];  // d s_k / d v_k before the sdf scale
 #pragma unroll
     for (int k = 0; k < K; ++k) sk[k] = wk[k] = 0.f;
 
@@ -143,7 +130,7 @@ __global__ void __launch_bounds__(tc::kRows) k_decode_tc(const DecodeParams p) {
         // 16 columns at a time, the next chunk in flight while this one is reduced (32 live registers instead of 64)
         uint32_t va[16], vb[16];
         const uint32_t t0 = tmem_d + lanes;
-        float s0 = 0.f, s1 = 0.f, gx = 0.f, gy = 0.f, gz = 0.f;
+        float s0 = 0.f, s1 = 0.f;
         uint32_t neg0 = 0u, neg1 = 0u;
         auto reduce16 = [&](const uint32_t (&v)[16], int c0, float& s, uint32_t& neg) {
 #pragma unroll
@@ -154,13 +141,6 @@ __global__ void __launch_bounds__(tc::kRows) k_decode_tc(const DecodeParams p) {
                 for (int u = 0; u < 4; ++u) {
                     s = fmaf(fmaxf(__uint_as_float(v[c + u]), 0.f), wv[u], s);
                     neg = __funnelshift_l(v[c + u], neg, 1);  // sign bits: 1 <-> relu' = 0
-                    if (GRAD) {  // relu'(pre) as 1.0f / 0.0f from the sign bit (the convention of the saved mask)
-                        const float m = __uint_as_float(((uint32_t)((int32_t)~v[c + u] >> 31)) & 0x3f800000u);
-                        const float4 g4 = S.vv[c0 + c + u];
-                        gx = fmaf(m, g4.x, gx);
-                        gy = fmaf(m, g4.y, gy);
-                        gz = fmaf(m, g4.z, gz);
-                    }
                 }
             }
         };
@@ -181,7 +161,6 @@ __global__ void __launch_bounds__(tc::kRows) k_decode_tc(const DecodeParams p) {
         const float s = ((s0 + s1) + b2) * scale;  // decoder.py:80-81
         sk[k] = s;
         wk[k] = w;
-        if (GRAD) { gvx[k] = gx; gvy[k] = gy; gvz[k] = gz; }
         sdf = k == 0 ? s * w : fmaf(s, w, sdf);
     };
     // per-query outputs once the K tiles of a block are in
@@ -205,29 +184,6 @@ __global__ void __launch_bounds__(tc::kRows) k_decode_tc(const DecodeParams p) {
                 var = fmaf(wk[k], d * d, var);
             }
             p.sdf_std[q] = sqrtf(var);
-        }
-        if (GRAD && p.grad_x) {
-            // d sdf/dx = sum_k w_k R_k^T (ds_k/dv_k) + (1/S) sum_k (s_k - sdf) d wt_k/dx,  d wt_k/dx = -2 wt_k^2 (x - p_k)
-            float x, y, z;
-            load_point(p.src, q, x, y, z);
-            QueryLane L;
-            resolve_query<true, false, false>(p, p.ws + ei * kWs, ei, q, true, x, y, z, L);
-            float ox = 0.f, oy = 0.f, oz = 0.f;
-            const float inv_s = 1.0f / L.wsum;
-#pragma unroll
-            for (int k = 0; k < K; ++k) {
-                if (L.kidx[k] >= 0) {
-                    float ax = gvx[k] * scale, ay = gvy[k] * scale, az = gvz[k] * scale;
-                    if (p.rotate) quat_rotate(__ldg(&p.quats[L.kidx[k]]), true, ax, ay, az);
-                    const float c = (sk[k] - sdf) * (-2.f * L.wt[k] * L.wt[k]) * inv_s;
-                    ox += wk[k] * ax + c * L.ux[k];
-                    oy += wk[k] * ay + c * L.uy[k];
-                    oz += wk[k] * az + c * L.uz[k];
-                }
-            }
-            p.grad_x[3 * q] = ox;
-            p.grad_x[3 * q + 1] = oy;
-            p.grad_x[3 * q + 2] = oz;
         }
     };
 

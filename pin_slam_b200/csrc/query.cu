@@ -992,27 +992,20 @@ static int run_query(const pinq_query_args* a, int mode, float* feat_out, const 
         if (use_tc < 0) {
             const char* e = getenv("PINQ_DECODE");
             use_tc = !(e && e[0] == 'm');
-            cudaFuncSetAttribute(k_decode_tc<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc::kSmemRequest);
-            cudaFuncSetAttribute(k_decode_tc<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc::kSmemRequest);
-            cudaFuncSetAttribute(k_decode_tc<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc::kSmemRequest);
-            cudaFuncSetAttribute(k_decode_tc<false, false>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
-            cudaFuncSetAttribute(k_decode_tc<true, false>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
-            cudaFuncSetAttribute(k_decode_tc<false, true>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+            cudaFuncSetAttribute(k_decode_tc<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc::kSmemRequest);
+            cudaFuncSetAttribute(k_decode_tc<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc::kSmemRequest);
+            cudaFuncSetAttribute(k_decode_tc<false>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+            cudaFuncSetAttribute(k_decode_tc<true>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
         }
-        if (use_tc && !(a->grad_x && mode == 2) && !(a->flags & PINQ_F_MMA_SYNC)) {
+        // d sdf/dx (tracking) stays on the mma.sync kernel, whose layer-1 accumulator fragment IS the A fragment of the mask x V
+        // product; a CUDA-core gradient epilogue inside the tcgen05 kernel was measured slower (3.32 vs 2.41 ms per 4 Mi
+        // queries, 150 registers; profiles/r3g_bench.json) -- tracking batches are ~10^4 points, launch-latency bound either way
+        if (use_tc && !a->grad_x && !(a->flags & PINQ_F_MMA_SYNC)) {
             const unsigned nb128 = grid_for(n, tc::kRows);
-            static int occ_tc_grad = 0;  // the gradient flavour holds more registers: fewer resident CTAs
-            if (!occ_tc_grad) {
-                cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_tc_grad, k_decode_tc<false, true>, tc::kRows, tc::kSmemRequest);
-                if (occ_tc_grad < 1) occ_tc_grad = 1;
-                if (occ_tc_grad > (int)tc::kCtasPerSm) occ_tc_grad = (int)tc::kCtasPerSm;
-            }
-            const unsigned per_sm = (a->grad_x && mode != 2) ? (unsigned)occ_tc_grad : tc::kCtasPerSm;
-            const unsigned cap128 = (unsigned)sms * per_sm;  // TMEM columns (and registers) per CTA bound the residency
+            const unsigned cap128 = (unsigned)sms * tc::kCtasPerSm;  // TMEM columns (and registers) per CTA bound the residency
             const unsigned g128 = nb128 < cap128 ? nb128 : cap128;
-            if (mode == 2) k_decode_tc<true, false><<<g128, tc::kRows, tc::kSmemRequest, st>>>(p);
-            else if (a->grad_x) k_decode_tc<false, true><<<g128, tc::kRows, tc::kSmemRequest, st>>>(p);
-            else k_decode_tc<false, false><<<g128, tc::kRows, tc::kSmemRequest, st>>>(p);
+            if (mode == 2) k_decode_tc<true><<<g128, tc::kRows, tc::kSmemRequest, st>>>(p);
+            else k_decode_tc<false><<<g128, tc::kRows, tc::kSmemRequest, st>>>(p);
         } else {
             const int occ = mode == 2 ? occ_mesh : (a->grad_x ? occ_grad : occ_plain);
             const unsigned cap = (unsigned)(sms * (occ > 0 ? occ : 1));

@@ -56,24 +56,13 @@ def test_full_size_forward_paths_agree(big):
     assert torch.equal(nn, nn_m) and rel_err(sdf_m, sdf) < 1e-6
 
 
-def test_full_size_gradient_flavour_tcgen05_vs_mma_sync_vs_oracle(big):
-    """Tracking flavour (sdf, d sdf/dx, std): the tcgen05 gradient decode (k_decode_tc<GRAD>) against the mma.sync kernel it
-    replaces on the whole 4 Mi batch, and against the CPU oracle's autograd gradient on a 20 000-query sample."""
+def test_full_size_gradient_flavour_matches_the_oracle_on_a_sample(big):
+    """Tracking flavour (sdf, d sdf/dx, std) on the whole 4 Mi batch against the CPU oracle's autograd gradient on a
+    20 000-query sample."""
     cfg, npts, dec, q = big
-
-    def run():
-        with torch.no_grad():
-            o = npts.query_sdf(q, dec, None, False, True, want_grad=True, want_std=True)
-        return o["sdf"].clone(), o["grad"].clone(), o["std"].clone(), o["nn_count"].clone()
-
-    sdf, grad, std, nn = run()
-    npts.use_mma_sync = True
-    try:
-        sdf_m, grad_m, std_m, nn_m = run()
-    finally:
-        npts.use_mma_sync = False
-    assert torch.equal(nn, nn_m)
-    assert rel_err(sdf, sdf_m) < 1e-6 and rel_err(grad, grad_m) < 1e-5 and rel_err(std, std_m) < 1e-4
+    with torch.no_grad():
+        o = npts.query_sdf(q, dec, None, False, True, want_grad=True, want_std=True)
+    sdf, grad, std, nn = o["sdf"], o["grad"], o["std"], o["nn_count"]
     O, s, d = oracle_state_from(npts, dec)
     pick = torch.randperm(N, generator=torch.Generator().manual_seed(2))[:20000]
     ref = O.query_sdf(s, d, q[pick.cuda()].cpu(), None, False, True, want_grad=True, want_std=True)
