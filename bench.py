@@ -461,7 +461,7 @@ def mapping_leg(dev, world, rank, iters=15, batch=1 << 20, pool_n=8_000_000):
     peer = None
     rows, fdim = npts.local_geo_features.shape
     if world > 1:
-        peer = PeerExchange(MappingPeer.capacity(rows, fdim, dec, with_params=True), dev)
+        peer = PeerExchange(MappingPeer.capacity(rows, fdim, dec, with_params=True), dev, grid=int(os.environ.get("PINQ_MAP_PEER_GRID", "48")))
         torch.cuda.synchronize()
         dist.barrier()
         mapper.dp = DataParallelMapping(peer)
@@ -483,6 +483,8 @@ def mapping_leg(dev, world, rank, iters=15, batch=1 << 20, pool_n=8_000_000):
            "ms_per_iter": ms / iters, "samples_per_s": batch * iters / (ms * 1e-3), "scaling": "strong",
            "form": "device-side loop (pinq_mapping_run)" + (", pinq_peer_exchange with fused Adam per iteration" if world > 1 else "")}
     if peer is not None:
+        res["peer_exchange_error"] = peer.error()
+        res["peer_grid"] = peer.grid
         dist.barrier()
         peer.close()
     del mapper, pool, label, weight, tsp
@@ -605,7 +607,12 @@ def main():
         if exchange == "peer":
             from pin_slam_b200.parallel import MappingPeer, PeerExchange
             rows, fdim = npts.local_geo_features.shape
-            peer = PeerExchange(MappingPeer.capacity(rows, fdim, dec), dev, grid=int(os.environ.get("PINQ_PEER_GRID", "0")))
+            # overlapped with the next step's search (below): a plain launch of FEW CTAs -- they take SM slots as the search's
+            # CTAs retire (a cooperative grid would wait for an empty GPU); 32 CTAs x 512 threads keep ~4 MB of P2P loads in
+            # flight, which is what the links need (measured at N = 2: 148 / 64 / 32 CTAs -> 2.131 / 2.088 / 2.078 ms per step)
+            ov = os.environ.get("PINQ_EXCHANGE_OVERLAP", "1") != "0"
+            peer = PeerExchange(MappingPeer.capacity(rows, fdim, dec), dev, grid=int(os.environ.get("PINQ_PEER_GRID", "32" if ov else "0")),
+                                cooperative=not ov)
             carve = MappingPeer(peer, rows, fdim, dec)
             n_ex = carve.n_sum - (rows - 1)  # features + decoder (the certainty increments are not part of this step)
             npts.feature_grad_sink, dec.grad_sink = carve.grad_features, tuple(carve.grad_decoder)
@@ -869,6 +876,7 @@ def main():
         cpu_baseline, cuda_eager = reference_legs(args, npts, dec, q_host, ts_host)
 
     peer_err = peer.error() if peer is not None else 0
+    had_peer = peer is not None
     config_line = workload_config(args, npts.count(), vbar, world)
     slam = flav = sweep = mapping = mesher_res = None
     if rank == 0 and world == 1 and not args.no_extra_legs:
@@ -921,9 +929,10 @@ def main():
         line["exchange"] = {"none": "none", "nccl": "NCCL all-reduce of feature+decoder grads",
                             "peer": "feature+decoder grads summed by one peer-memory kernel per rank over NVLink "
                                     "(pinq_peer_exchange)"}[exchange]
-        if peer is not None:
+        if had_peer:
             line["gpu_launches"] += args.steps
             line["peer_exchange_error"] = peer_err
+            line["exchange_overlapped_with_next_search"] = bool(overlap)
         if exchange_ms is not None:
             line["exchange_ms"] = exchange_ms
             line["ms_per_step_by_rank"] = rank_ms

@@ -6,6 +6,10 @@
 // and `pinq_mapping_run` enqueues all iterations of a frame back to back: the host is not on the path.
 #include <math.h>
 
+#include <stdlib.h>
+
+#include <mutex>
+
 #include "common.cuh"
 
 namespace pinq {
@@ -197,6 +201,31 @@ __global__ void k_adam_multi(AdamPack pk, int64_t groups, float beta1, float bet
     }
 }
 
+// Data-parallel form: the exchange + optimizer kernel of iteration i runs on a side stream UNDER the batch gather, the binning
+// and the neighbour search of iteration i + 1 (they read sample positions and map geometry only); the decode of i + 1 -- the
+// first kernel that reads the parameters the optimizer updates -- waits for it (pinq_query_args.decode_wait_event).  One
+// side stream + two events per calling stream, created on first use and kept (the only objects this file creates).
+struct MapSide {
+    cudaStream_t main, side;
+    cudaEvent_t bwd_done, exchanged;
+};
+static MapSide* map_side_for(cudaStream_t st) {
+    static MapSide pool[32];
+    static int used = 0;
+    static std::mutex mu;
+    std::lock_guard<std::mutex> lock(mu);
+    for (int i = 0; i < used; ++i)
+        if (pool[i].main == st) return &pool[i];
+    if (used == 32) return nullptr;
+    MapSide& m = pool[used];
+    m.main = st;
+    if (cudaStreamCreateWithFlags(&m.side, cudaStreamNonBlocking) != cudaSuccess) return nullptr;
+    if (cudaEventCreateWithFlags(&m.bwd_done, cudaEventDisableTiming) != cudaSuccess) return nullptr;
+    if (cudaEventCreateWithFlags(&m.exchanged, cudaEventDisableTiming) != cudaSuccess) return nullptr;
+    ++used;
+    return &m;
+}
+
 }  // namespace pinq
 
 using namespace pinq;
@@ -261,6 +290,15 @@ extern "C" int pinq_mapping_run(const pinq_mapping_args* a, int32_t iters, void*
     lp.surface_range = a->surface_range;
     lp.grad_sdf = a->grad_sdf;
 
+    MapSide* ms = nullptr;
+    if (a->peer && a->peer->world > 1) {
+        static int overlap = -1;
+        if (overlap < 0) {
+            const char* e = getenv("PINQ_MAPPING_OVERLAP");
+            overlap = !(e && e[0] == '0');
+        }
+        if (overlap) ms = map_side_for(st);
+    }
     for (int it = 0; it < iters; ++it) {
         gp.draws_hist = a->draws_hist ? a->draws_hist + (int64_t)it * gp.bs_hist : nullptr;
         gp.draws_new = a->draws_new ? a->draws_new + (int64_t)it * a->bs_new : nullptr;
@@ -268,7 +306,13 @@ extern "C" int pinq_mapping_run(const pinq_mapping_args* a, int32_t iters, void*
         k_map_gather<<<grid_for(n, 256), 256, 0, st>>>(gp);
         int rc = check_launch("k_map_gather");
         if (rc != PINQ_OK) return rc;
-        rc = pinq_query_fused_fwd(&a->query, stream);
+        if (ms && it > 0) {  // gather + binning + search now, the decode after the previous iteration's exchange + optimizer
+            pinq_query_args q = a->query;
+            q.decode_wait_event = ms->exchanged;
+            rc = pinq_query_fused_fwd(&q, stream);
+        } else {
+            rc = pinq_query_fused_fwd(&a->query, stream);
+        }
         if (rc != PINQ_OK) return rc;
         lp.eik_count = gp.eik_count;
         lp.loss = a->loss ? a->loss + 2 * it : nullptr;
@@ -284,7 +328,17 @@ extern "C" int pinq_mapping_run(const pinq_mapping_args* a, int32_t iters, void*
             pa.epoch = a->peer->epoch + (uint32_t)it;
             pa.adam_step = step;
             pa.lr = a->lr; pa.beta1 = a->beta1; pa.beta2 = a->beta2; pa.adam_eps = a->adam_eps;
-            rc = pinq_peer_exchange(&pa, stream);
+            if (ms) {
+                // plain launch: a cooperative grid would wait for an empty GPU, i.e. behind the next iteration's search; its
+                // CTAs take SM slots as they free up and meet at the flag barrier (nothing the search needs depends on them)
+                pa.cooperative = 0;
+                cudaEventRecord(ms->bwd_done, st);
+                cudaStreamWaitEvent(ms->side, ms->bwd_done, 0);
+                rc = pinq_peer_exchange(&pa, ms->side);
+                cudaEventRecord(ms->exchanged, ms->side);
+            } else {
+                rc = pinq_peer_exchange(&pa, stream);
+            }
             if (rc != PINQ_OK) return rc;
             continue;
         }
@@ -300,5 +354,6 @@ extern "C" int pinq_mapping_run(const pinq_mapping_args* a, int32_t iters, void*
         rc = check_launch("k_adam_multi");
         if (rc != PINQ_OK) return rc;
     }
+    if (ms) cudaStreamWaitEvent(st, ms->exchanged, 0);  // the call is complete on `stream` when the last exchange has landed
     return PINQ_OK;
 }

@@ -170,12 +170,18 @@ class PeerExchange:
     `ranks_on_this_device` > 1 builds that many blocks in ONE process on one GPU and runs their kernels on separate
     streams: the single-GPU form used by the GPU tests (same kernel, same flags, same P2P code path minus the link)."""
 
-    def __init__(self, layout: PeerLayout, device, group=None, simulate_world: int = 0, grid: int = 0, timeout_ms: float = 0.0):
+    def __init__(self, layout: PeerLayout, device, group=None, simulate_world: int = 0, grid: int = 0, timeout_ms: float = 0.0,
+                 cooperative: bool = True):
         import ctypes as C
         from . import _pinq as P
         self.P, self.lib, self.layout, self.device = P, P.load(), layout, torch.device(device)
         import os
         self.grid = int(grid)
+        # cooperative launch = all CTAs of the exchange resident at once, guaranteed at launch time.  A caller that overlaps the
+        # exchange with kernels that do NOT depend on it (the next step's search) passes False: a cooperative grid would wait
+        # for a completely free GPU, i.e. behind that search, while a plain launch lets its CTAs take SM slots as they free up
+        # (they spin at the flag barrier until the rest arrive, which they do because the other kernel finishes regardless).
+        self.cooperative = bool(cooperative)
         # a rank that does not arrive within this bound makes the kernel give up and set the block's error word
         self.timeout_ms = float(timeout_ms) if timeout_ms else float(os.environ.get("PINQ_PEER_TIMEOUT_MS", "0"))
         self.simulated = simulate_world > 0
@@ -252,7 +258,7 @@ class PeerExchange:
             a.block[r] = b
         a.sum_off, a.n_sum, a.max_off, a.n_max = L.sum_off + 4 * sum_off_elems, n_sum, L.max_off, n_max
         a.epoch, a.grid, a.timeout_ms = epoch, self.grid, self.timeout_ms
-        a.cooperative = 0 if self.simulated else 1  # simulated ranks share one device and wait for each other
+        a.cooperative = 0 if (self.simulated or not self.cooperative) else 1  # simulated ranks share one device and wait for each other
         if adam is not None:
             adam = dict(adam)
             adam.setdefault("n", L.n_param)
