@@ -100,6 +100,9 @@ class NeuralPoints(nn.Module):
         self.bin_queries_min = 32768  # fused queries of at least this many points are binned by brick first
         # fused search through the brick index when it is provably equivalent (PINQ_BRICK=0: slot probing only)
         self.use_brick_index = os.environ.get("PINQ_BRICK", "1") != "0"
+        # the brick search packs a record rank into 24 key bits (csrc/query.cu kRankBits): maps of 2^24 = 16.7 M points or more
+        # fall back to the slot-probing search (same results, tested by forcing the limit down)
+        self.brick_max_points = 1 << 24
         self.exact_search_keys = False  # A/B tests: brick search with 64-bit keys for every query
         self.decode_wait_event = None  # torch.cuda.Event the fused query's decode waits for (see pinq_query_args)
         self.use_mma_sync = False  # A/B tests: the mma.sync decode / backward kernels instead of the tcgen05 ones
@@ -413,7 +416,7 @@ class NeuralPoints(nn.Module):
 
     def _build_bricks(self, m: int, have_local: bool, st):
         self._brick_tab = self._brick_global = self._brick_local = None
-        if not self.use_brick_index or m == 0 or m >= (1 << 24) or not self._brick_safe():
+        if not self.use_brick_index or m == 0 or m >= self.brick_max_points or not self._brick_safe():
             return
         lib = P.load()
         self.check_index_invariants(block=False)

@@ -235,6 +235,32 @@ def test_brick_index_equals_slot_probing(maps):
                        torch.sort(m._brick_global[:n_occ, 3].view(torch.int32)).values)
 
 
+def test_brick_rank_limit_falls_back_to_slot_probing(maps):
+    """Maps with 2^24 points or more do not fit the brick search's 24-bit record rank: NeuralPoints then serves the same queries
+    through the slot-probing search.  The limit is forced down to exercise that switch on a small map: no brick view is built,
+    results are bit-identical to the brick path, and the view comes back when the limit is restored."""
+    s, m, cfg, dec, d, _ = maps
+    q = make_queries(s.points, 20000, seed=9).cuda()
+    with torch.no_grad():
+        ref = m.query_sdf(q, dec, None, False, True, want_grad=True, want_std=True)
+    assert bool(m._map_view(True).brick_tab)
+    old = m.brick_max_points
+    m.brick_max_points = 1000            # < the map's point count
+    m._cand_dirty = True
+    try:
+        with torch.no_grad():
+            out = m.query_sdf(q, dec, None, False, True, want_grad=True, want_std=True)
+        assert not bool(m._map_view(True).brick_tab)
+        for key in ("sdf", "nn_count", "grad", "std"):
+            assert torch.equal(out[key], ref[key]), key
+    finally:
+        m.brick_max_points = old
+        m._cand_dirty = True
+    with torch.no_grad():
+        m.query_sdf(q[:100], dec, None, False, True)
+    assert bool(m._map_view(True).brick_tab)
+
+
 def test_truncated_key_search_equals_exact_keys(maps):
     """Brick search fast pass (32-bit keys: 23 bits of d^2 | walk identity, csrc/query.cu) against the 64-bit-key pass
     forced for every query (PINQ_F_EXACT_KEYS): same K neighbours in the same order, also for queries built to tie
