@@ -91,6 +91,18 @@ int64_t pinq_compact_scratch_bytes(int64_t n);
 int pinq_compact_flags(const uint8_t* flags, int64_t n, int32_t* out_index, int32_t* d_count, void* scratch,
                        void* stream);
 
+/* Allocation-free variant of pinq_compact_flags.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  Same inputs, outputs and results as pinq_compact_flags, but the scan's tile sums live in a static device
+ * array inside the library (64 KB per GPU, held from library load until exit) instead of caller scratch; the call issues
+ * no cudaMalloc / cudaFree / allocating library routine.  Limit: n <= PINQ_COMPACT_STATIC_MAX_N flags; larger n returns
+ * PINQ_ERR_BAD_ARG with a message naming the limit.  The array is shared by every call on the device and keeps the last
+ * call's contents (nothing needs clearing: each call overwrites what it reads): calls on one stream are ordered, calls
+ * that overlap on the GPU (several streams or host threads) RACE -- serialise them or use pinq_compact_flags.  The
+ * first call on a device resolves the array's address (cudaGetSymbolAddress): make it once outside graph capture. */
+#define PINQ_COMPACT_STATIC_MAX_N (16ll * 1024 * 1024)
+int pinq_compact_flags_static(const uint8_t* flags, int64_t n, int32_t* out_index, int32_t* d_count, void* stream);
+
 /* utils/tools.py:409-442 (mode 0, closest to voxel centre) and :444-477 (mode 1, min `value`).
  * Three steps so that the caller owns all memory:
  *   1. pinq_vds_prepare : per-point quirky linear key (scalar V, hazard H5) + quantised score;

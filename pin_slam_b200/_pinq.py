@@ -62,6 +62,8 @@ class AdamTensor(C.Structure):
 
 EIK_ALL, EIK_SURFACE, EIK_FREESPACE = 0, 1, 2
 
+COMPACT_STATIC_MAX_N = 16 * 1024 * 1024  # PINQ_COMPACT_STATIC_MAX_N
+
 PEER_MAX, PEER_HANDLE_BYTES, PEER_PAD_BYTES, PEER_MAX_GRID = 8, 64, 16384, 256
 
 
@@ -97,6 +99,7 @@ SIGNATURES = {
     "pinq_update_mask": (C.c_int, [_vp, _vp, _i64, _vp, _vp, _i64, _vp, _i64, _f32, _f32, _vp, _vp]),
     "pinq_compact_scratch_bytes": (_i64, [_i64]),
     "pinq_compact_flags": (C.c_int, [_vp, _i64, _vp, _vp, _vp, _vp]),
+    "pinq_compact_flags_static": (C.c_int, [_vp, _i64, _vp, _vp, _vp]),
     "pinq_vds_prepare": (C.c_int, [_vp, _i64, _f32, _vp, C.c_int, _vp, _vp, _vp, _vp]),
     "pinq_vds_select": (C.c_int, [_vp, _vp, _i64, _vp, _vp, _u64, _vp]),
     "pinq_vds_emit": (C.c_int, [_vp, _vp, _u64, _i64, _vp, _vp, _vp, _vp]),

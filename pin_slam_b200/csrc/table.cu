@@ -4,6 +4,8 @@
 #include <stdarg.h>
 #include <string.h>
 
+#include <mutex>
+
 #include "common.cuh"
 
 namespace pinq {
@@ -312,6 +314,34 @@ __global__ void k_local_mask(const float* __restrict__ xyz, const int64_t* __res
 
 }  // namespace pinq
 
+// built-in scratch of pinq_compact_flags_static: one int32 tile sum per 1024 flags, + 1 (file scope, see the entry point)
+static __device__ __align__(256) int32_t g_compact_static_tiles[PINQ_COMPACT_STATIC_MAX_N / 1024 + 1];
+
+// device address of g_compact_static_tiles on the CURRENT device (resolved once per device; NULL + error text on failure)
+static int32_t* compact_static_scratch() {
+    static int32_t* addr[64] = {nullptr};
+    static std::mutex mu;
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess || dev < 0 || dev >= 64) {
+        pinq::set_error("pinq_compact_flags_static: cudaGetDevice failed or device index %d out of range: %s", dev,
+                        cudaGetErrorString(e));
+        return nullptr;
+    }
+    std::lock_guard<std::mutex> lock(mu);
+    if (!addr[dev]) {
+        void* p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_compact_static_tiles);
+        if (e != cudaSuccess || !p) {
+            pinq::set_error("pinq_compact_flags_static: cudaGetSymbolAddress failed on device %d: %s", dev, cudaGetErrorString(e));
+            cudaGetLastError();
+            return nullptr;
+        }
+        addr[dev] = reinterpret_cast<int32_t*>(p);
+    }
+    return addr[dev];
+}
+
 using namespace pinq;
 
 extern "C" {
@@ -399,6 +429,35 @@ int pinq_compact_flags(const uint8_t* flags, int64_t n, int32_t* out_index, int3
     k_tile_scan<<<1, 1024, 0, st>>>(tiles, ntiles, d_count);
     k_tile_emit<<<(unsigned)ntiles, kScanTile, 0, st>>>(flags, n, tiles, out_index);
     return check_launch("pinq_compact_flags");
+}
+
+// ---- allocation-free variant of pinq_compact_flags (no counterpart in the reference; added
+// for callers that cannot allocate: CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).
+// The tile sums live in a file-scope device array instead of caller scratch.  In HOST code the array's name is only a
+// stand-in, not a device address: compact_static_scratch() asks the runtime for the address, once per device with that
+// device current, and the kernels are given that pointer.  Every GPU that loads the library holds the 64 KB until exit.
+// Nothing has to start at zero: k_tile_count overwrites every element a call reads.  All calls share the array, so
+// calls that overlap on the GPU (other streams, other host threads) race; calls on one stream are ordered.
+int pinq_compact_flags_static(const uint8_t* flags, int64_t n, int32_t* out_index, int32_t* d_count, void* stream) {
+    PINQ_REQUIRE(n >= 0, "bad n");
+    if (n > PINQ_COMPACT_STATIC_MAX_N) {
+        set_error("pinq_compact_flags_static: n = %lld exceeds the built-in scratch (PINQ_COMPACT_STATIC_MAX_N = %lld flags); "
+                  "use pinq_compact_flags with caller scratch", (long long)n, (long long)PINQ_COMPACT_STATIC_MAX_N);
+        return PINQ_ERR_BAD_ARG;
+    }
+    PINQ_REQUIRE(d_count && (n == 0 || (flags && out_index)), "null pointer");
+    cudaStream_t st = as_stream(stream);
+    if (n == 0) {
+        cudaMemsetAsync(d_count, 0, sizeof(int32_t), st);
+        return check_launch("pinq_compact_flags_static");
+    }
+    int32_t* tiles = compact_static_scratch();
+    if (!tiles) return PINQ_ERR_CUDA;  // (error text set by compact_static_scratch)
+    const int64_t ntiles = (n + kScanTile - 1) / kScanTile;
+    k_tile_count<<<(unsigned)ntiles, kScanTile, 0, st>>>(flags, n, tiles);
+    k_tile_scan<<<1, 1024, 0, st>>>(tiles, ntiles, d_count);
+    k_tile_emit<<<(unsigned)ntiles, kScanTile, 0, st>>>(flags, n, tiles, out_index);
+    return check_launch("pinq_compact_flags_static");
 }
 
 int pinq_vds_prepare(const float* xyz, int64_t n, float voxel, const float* value, int mode, float* d_scratch8,
