@@ -194,6 +194,20 @@ class Mapper:
             self.pool_sample_count = self.coord_pool.shape[0]
         return T3_1
 
+    def _pool_rows_target(self, rows, n_new=0):
+        """Rows to allocate for a pool buffer that must hold `rows` now.  The pool never exceeds pool_capacity after the
+        discard (utils/mapper.py:237-246), so [old pool | new samples] is bounded by pool_capacity + one frame of samples:
+        allocate that ONCE (run_kitti: 2e7 rows x 40 B = 0.9 GB per half of the ping-pong store) instead of doubling --
+        every doubling (cudaMalloc + the free of the old half) stalled a frame by 6-33 ms (profiles/r4a_driver100.json: 8 such
+        frames in 100).  Capacities too large to reserve up front (> 6e7 rows) keep the geometric growth."""
+        cap_cfg = int(self.config.pool_capacity)
+        self._pool_frame_rows = max(getattr(self, "_pool_frame_rows", 0), int(n_new))
+        if cap_cfg <= 60_000_000:
+            bound = cap_cfg + max(2 * self._pool_frame_rows, 1 << 21)
+            if rows <= bound:
+                return bound
+        return max(2 * int(rows), 1 << 22 if rows > (1 << 16) else 1 << 16)
+
     def _pool_store_side(self, rows):
         """The half of the ping-pong store the next pool is written to: not the one the pool tensors live in now."""
         live = self.coord_pool.data_ptr() if self.coord_pool.numel() else 0
@@ -202,7 +216,7 @@ class Mapper:
             side = 1
         st = self._pool_store[side]
         if st is None or st["ts"].shape[0] < rows:
-            cap = max(2 * int(rows), 1 << 22 if rows > (1 << 16) else 1 << 16)  # few re-allocations: cudaMalloc stalls a frame
+            cap = self._pool_rows_target(rows)
             dev = self.device
             st = {"coord": torch.empty((cap, 3), dtype=torch.float32, device=dev),
                   "global_coord": torch.empty((cap, 3), dtype=torch.float32, device=dev),
@@ -232,8 +246,8 @@ class Mapper:
         new = P.PoolView(P.ptr(c_new), P.ptr(g_new), P.ptr(l_new), P.ptr(w_new), None) if n_new else P.PoolView()
         origin = frame_origin_torch.to(device=dev, dtype=torch.float32).contiguous()
         ws = self._pool_ws
-        if ws is None or ws["rows"] < n_tot:  # work buffers persist across frames and grow geometrically
-            rows = max(2 * n_tot, 1 << 16)
+        if ws is None or ws["rows"] < n_tot:  # work buffers persist across frames: sized once for the steady state
+            rows = self._pool_rows_target(n_tot, n_new)
             ws = self._pool_ws = {"rows": rows, "flags": torch.empty(rows, dtype=torch.uint8, device=dev),
                                   "kept": torch.empty(rows, dtype=torch.int32, device=dev),
                                   "scratch": torch.empty(int(lib.pinq_compact_scratch_bytes(rows)), dtype=torch.uint8, device=dev)}

@@ -127,6 +127,7 @@ def main():
            "ms_per_frame": {k: float(tt[1:, i].mean() * 1e3) for i, k in enumerate(("preprocess", "tracking", "map_prep", "training"))} if n > 1 else None,
            "median_ms_per_frame": float(np.median(tt[1:, :4].sum(1)) * 1e3) if n > 1 else None,
            "preprocess_ms_by_frame": [round(float(v) * 1e3, 2) for v in tt[:, 0]][:40],
+           "stage_ms_by_frame": [[round(float(v) * 1e3, 2) for v in row[:4]] for row in tt],
            "wall_s_whole_run": wall, "scan_generation_s": gen_s,
            "ate_vs_ground_truth_m": float(ate_trans), "ate_rot_deg": float(ate_rot),
            "libpinq_loaded": sorted(set(os.path.basename(p) for p in native)),
