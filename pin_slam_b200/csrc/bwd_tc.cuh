@@ -342,7 +342,7 @@ __global__ void __launch_bounds__(tcb::kRows) k_bwd_tc(const BwdParams p) {
                 umma_commit(smem_u32(&S.bar[st]));
             }
             // ---- loads of the tile after the next, then the epilogue of the previous tile while the MMAs run ----
-            if (k == 1 && has_next) load_block(ni, nidx, ng);
+            if (k == 0 && has_next) load_block(ni, nidx, ng);
             if (DEC && k == 3) publish_max(ng, parity ^ 1);  // read at the start of the next block, two barriers from here
             if (k + 2 < K) load_tile(i, k + 2, cidx[k + 2 < K ? k + 2 : 0]);
             else if (has_next) load_tile(ni, k + 2 - K, nidx[k + 2 >= K ? k + 2 - K : 0]);

@@ -293,7 +293,7 @@ struct BrickLane {
     uint32_t msk[kWalkEntries][kBlock];  // occupancy of the half brick
     uint32_t pk[kWalkEntries][kBlock];   // rank of its first record | (64 + linear stencil offset of its voxel 0) << 24
 };
-constexpr size_t kBrickSmem = sizeof(BrickLane) + kStencilMasks * 8 + 128 + 32;
+constexpr size_t kBrickSmem = sizeof(BrickLane) + kStencilMasks * 8 + 128 + 32 + 64;
 
 // RESOLVE: the walk ends with the lane's K winners in registers and their records hot in L1, so the resolve step
 // (stage block, per-query outputs, training side effects -- what k_resolve does after the slot-probing search)
@@ -309,11 +309,26 @@ __global__ void __launch_bounds__(kBlock, PINQ_SEARCH_MINB) k_search_brick(MapDe
     if (p.skip && *p.skip) return;
     extern __shared__ __align__(16) unsigned char s_brick_raw[];
     BrickLane* bl = reinterpret_cast<BrickLane*>(s_brick_raw);
-    unsigned long long* s_masks = reinterpret_cast<unsigned long long*>(s_brick_raw + sizeof(BrickLane));
-    uint8_t* s_sid = reinterpret_cast<uint8_t*>(s_masks + kStencilMasks);  // stencil position of offset (dx,dy,dz)
+    // stencil masks staged as 32-bit HALF-brick masks, [2 b + h][s] with s = box origin inside its brick (0..63): a lane reads
+    // word s of a row, so lanes with different origins hit different banks (the [s][b] 64-bit rows of the global table put
+    // every lane on one of two bank groups: ncu r4a counted 17 wavefronts per LDS.64, 64 % of the kernel's shared wavefronts)
+    uint32_t* s_hm = reinterpret_cast<uint32_t*>(s_brick_raw + sizeof(BrickLane));
+    uint8_t* s_sid = reinterpret_cast<uint8_t*>(s_hm + 2 * kStencilMasks);  // stencil position of offset (dx,dy,dz)
     uint8_t* s_bitoff = s_sid + 128;  // linear stencil offset of voxel `bit` of a half brick relative to its voxel 0
+    uint8_t* s_need = s_bitoff + 32;  // per origin s: bit b = brick b holds stencil members
     const int R = bd.radius, W = 2 * R + 1, tid = threadIdx.x;
-    for (int c = tid; c < kStencilMasks; c += blockDim.x) s_masks[c] = stencil_masks[c];
+    for (int c = tid; c < kStencilMasks; c += blockDim.x) {  // c = b * 64 + s: consecutive lanes write consecutive words
+        const int b = c >> 6, so = c & 63;
+        const unsigned long long m = stencil_masks[so * 8 + b];
+        s_hm[(2 * b) * 64 + so] = (uint32_t)m;
+        s_hm[(2 * b + 1) * 64 + so] = (uint32_t)(m >> 32);
+    }
+    for (int c = tid; c < 64; c += blockDim.x) {
+        uint32_t nb = 0u;
+#pragma unroll
+        for (int b = 0; b < 8; ++b) nb |= (stencil_masks[c * 8 + b] != 0ull ? 1u : 0u) << b;
+        s_need[c] = (uint8_t)nb;
+    }
     for (int c = tid; c < 128; c += blockDim.x) s_sid[c] = 0xFF;
     for (int c = tid; c < 32; c += blockDim.x) s_bitoff[c] = (uint8_t)(((c >> 4) * W + ((c >> 2) & 3)) * W + (c & 3));
     __syncthreads();
@@ -332,7 +347,7 @@ __global__ void __launch_bounds__(kBlock, PINQ_SEARCH_MINB) k_search_brick(MapDe
               cz = cell_of(z, map.res, map.inv_res, recip);
     const int ax = cx - R, ay = cy - R, az = cz - R;  // box origin
     const int b0x = ax >> 2, b0y = ay >> 2, b0z = az >> 2;
-    const int srow = (((ax & 3) * 4 + (ay & 3)) * 4 + (az & 3)) * 8;
+    const int so = ((ax & 3) * 4 + (ay & 3)) * 4 + (az & 3);  // box origin inside brick b0
 
     // phase 1: one probe per brick, in batches of PINQ_PROBE_BATCH: the 32-byte entries of a batch are requested back to
     // back (one 256-bit load each) before the first key is compared, so a batch costs ONE exposed L2 latency instead of
@@ -340,12 +355,18 @@ __global__ void __launch_bounds__(kBlock, PINQ_SEARCH_MINB) k_search_brick(MapDe
     // the kernel at 64 registers = 8 CTAs per SM (batches of four: 80 registers, slower).  An entry that is not the
     // brick's own (linear-probing displacement, rare at load factor <= 0.5) falls back to the probe loop
     int total = 0, cnt = 0;
-    unsigned long long pm[8];
-    uint32_t pb[8];
+    const uint32_t needbits = live ? (uint32_t)s_need[so] : 0u;
 #ifndef PINQ_PROBE_BATCH
 #define PINQ_PROBE_BATCH 2
 #endif
-#pragma unroll
+#ifndef PINQ_PROBE_UNROLL
+#define PINQ_PROBE_UNROLL 1
+#endif
+    // A brick's entry goes straight into the walk list (no per-brick register arrays: the loop over the batches is a real
+    // loop, which keeps both the register count and the code size of this phase down)
+#define PINQ_PRAGMA_(x) _Pragma(#x)
+#define PINQ_UNROLL_(n) PINQ_PRAGMA_(unroll n)
+    PINQ_UNROLL_(PINQ_PROBE_UNROLL)
     for (int b0 = 0; b0 < 8; b0 += PINQ_PROBE_BATCH) {
         unsigned long long want[PINQ_PROBE_BATCH];
         uint32_t ew[PINQ_PROBE_BATCH][8];
@@ -353,7 +374,7 @@ __global__ void __launch_bounds__(kBlock, PINQ_SEARCH_MINB) k_search_brick(MapDe
 #pragma unroll
         for (int u = 0; u < PINQ_PROBE_BATCH; ++u) {
             const int b = b0 + u;
-            need[u] = live && s_masks[srow + b] != 0ull;
+            need[u] = (needbits >> b) & 1u;
             want[u] = brick_key(b0x + (b >> 2), b0y + ((b >> 1) & 1), b0z + (b & 1));
 #pragma unroll
             for (int w = 0; w < 8; ++w) ew[u][w] = 0u;
@@ -362,39 +383,36 @@ __global__ void __launch_bounds__(kBlock, PINQ_SEARCH_MINB) k_search_brick(MapDe
 #pragma unroll
         for (int u = 0; u < PINQ_PROBE_BATCH; ++u) {
             const int b = b0 + u;
-            pm[b] = 0ull;
-            pb[b] = 0u;
+            unsigned long long pmb = 0ull;
+            uint32_t pbb = 0u;
             if (need[u]) {
                 const unsigned long long got = ((unsigned long long)ew[u][5] << 32) | ew[u][4];
                 if (got == want[u]) {
-                    pm[b] = ((unsigned long long)ew[u][1] << 32) | ew[u][0];
-                    pb[b] = ew[u][2];
+                    pmb = ((unsigned long long)ew[u][1] << 32) | ew[u][0];
+                    pbb = ew[u][2];
                 } else if (got != kBrickEmpty) {  // displaced entry: walk the probe sequence
                     const int e = brick_find(bd.tab, bd.cap_mask, want[u]);
                     if (e >= 0) {
                         const uint4 v = __ldg(reinterpret_cast<const uint4*>(&bd.tab[e]));
-                        pm[b] = ((unsigned long long)v.y << 32) | v.x;
-                        pb[b] = v.z;
+                        pmb = ((unsigned long long)v.y << 32) | v.x;
+                        pbb = v.z;
                     }
                 }
             }
-        }
-    }
+            // stencil offset of the brick's voxel 0 from the box origin, linearised like s_sid
+            const int lin0 = ((4 * (b >> 2) - (ax & 3)) * W + (4 * ((b >> 1) & 1) - (ay & 3))) * W + (4 * (b & 1) - (az & 3));
 #pragma unroll
-    for (int b = 0; b < 8; ++b) {
-        const unsigned long long sel = pm[b] & s_masks[srow + b];
-        // stencil offset of the brick's voxel 0 from the box origin, linearised like s_sid
-        const int lin0 = ((4 * (b >> 2) - (ax & 3)) * W + (4 * ((b >> 1) & 1) - (ay & 3))) * W + (4 * (b & 1) - (az & 3));
-#pragma unroll
-        for (int h = 0; h < 2; ++h) {
-            const uint32_t sel32 = (uint32_t)(sel >> (32 * h));
-            if (sel32) {
-                const uint32_t base = pb[b] + (h ? (uint32_t)__popc((uint32_t)pm[b]) : 0u);
-                bl->sel[cnt][tid] = sel32;
-                bl->msk[cnt][tid] = (uint32_t)(pm[b] >> (32 * h));
-                bl->pk[cnt][tid] = base | ((uint32_t)(lin0 + h * 2 * W * W + 64) << kRankBits);
-                ++cnt;
-                total += __popc(sel32);
+            for (int h = 0; h < 2; ++h) {
+                const uint32_t occ32 = (uint32_t)(pmb >> (32 * h));
+                const uint32_t sel32 = occ32 & s_hm[(2 * b + h) * 64 + so];
+                if (sel32) {
+                    const uint32_t base = pbb + (h ? (uint32_t)__popc((uint32_t)pmb) : 0u);
+                    bl->sel[cnt][tid] = sel32;
+                    bl->msk[cnt][tid] = occ32;
+                    bl->pk[cnt][tid] = base | ((uint32_t)(lin0 + h * 2 * W * W + 64) << kRankBits);
+                    ++cnt;
+                    total += __popc(sel32);
+                }
             }
         }
     }
@@ -458,12 +476,23 @@ __global__ void __launch_bounds__(kBlock, PINQ_SEARCH_MINB) k_search_brick(MapDe
             const bool ok = acts[u] && __float_as_int(rcs[u].w) != -1 && !(d2 > map.max_d2);
             nn += ok ? 1 : 0;
             uint32_t key = ok ? ((__float_as_uint(d2) & ~kWalkIdMask) | ids[u]) : ~0u;
+#ifndef PINQ_SEARCH_SERIAL_INSERT
+            // ascending insertion, every slot from the OLD list: new[k] = min(old[k], max(old[k-1], key)) -- the same 2
+            // instructions per slot as a bubble pass, but no slot waits for its neighbour (dependency depth 2 instead of 2 K)
+            uint32_t nk[K + 1];
+            nk[0] = min(k7[0], key);
+#pragma unroll
+            for (int k = 1; k <= K; ++k) nk[k] = min(k7[k], max(k7[k - 1], key));
+#pragma unroll
+            for (int k = 0; k <= K; ++k) k7[k] = nk[k];
+#else
 #pragma unroll
             for (int k = 0; k <= K; ++k) {  // ascending insertion: slot keeps the smaller, the larger moves on
                 const uint32_t lo = min(k7[k], key);
                 key = max(k7[k], key);
                 k7[k] = lo;
             }
+#endif
         }
     }
     bool tie = false;
