@@ -78,6 +78,31 @@ def parse():
     return ap.parse_args()
 
 
+def bind_to_gpu_numa_node(local_rank):
+    """Pin this rank's host threads (and with them the first-touch placement of its pinned buffers) to the NUMA node its GPU
+    hangs off: without it cudaHostAlloc'ed pages land on whichever node the thread happened to run on and half the ranks of a
+    two-socket box pull their batches across the socket interconnect.  Returns what was done for the JSON line."""
+    try:
+        pr = torch.cuda.get_device_properties(local_rank)
+        bdf = "%04x:%02x:%02x.0" % (pr.pci_domain_id, pr.pci_bus_id, pr.pci_device_id)
+        with open("/sys/bus/pci/devices/%s/numa_node" % bdf) as f:
+            node = int(f.read().strip())
+        if node < 0:
+            return {"numa_node": node, "bound": False}
+        with open("/sys/devices/system/node/node%d/cpulist" % node) as f:
+            cpus = set()
+            for part in f.read().strip().split(","):
+                a, _, b = part.partition("-")
+                cpus.update(range(int(a), int(b or a) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return {"numa_node": node, "bound": False}
+        os.sched_setaffinity(0, cpus)
+        return {"numa_node": node, "bound": True, "cpus": len(cpus)}
+    except Exception as e:  # no sysfs / no permission: leave the scheduler alone
+        return {"bound": False, "why": str(e)[:80]}
+
+
 def peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -580,6 +605,7 @@ def main():
         raise SystemExit("bench.py needs a CUDA device: the neural-point query path has no CPU fallback")
     torch.cuda.set_device(local_rank)
     dev = "cuda:%d" % local_rank
+    host_binding = bind_to_gpu_numa_node(local_rank) if os.environ.get("PINQ_NUMA_BIND", "1") != "0" else {"bound": False}
     if world > 1:
         os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")  # keep stdout for the one JSON line
         dist.init_process_group("nccl", device_id=torch.device(dev))
@@ -857,6 +883,21 @@ def main():
         pipelined = os.environ.get("PINQ_E2E_PIPELINE", "1") != "0"
         for _ in range(max(5, args.warmup)):  # PCIe link and pinned pages warm
             e2e_step()
+        # the copies alone, all ranks at once: the host-side ceiling of this leg (bytes of one step over the slowest rank's time)
+        torch.cuda.current_stream().wait_stream(back_stream)
+        barrier()
+        ce0, ce1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ce0.record()
+        for _ in range(5):
+            xb[0].copy_(qh[:cn], non_blocking=True)
+            tb32[0].copy_(th[:cn], non_blocking=True)
+            out_h[:cn].copy_(sdf[:cn], non_blocking=True)
+        ce1.record()
+        barrier()
+        tc = torch.tensor([ce0.elapsed_time(ce1) / 5], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(tc, op=dist.ReduceOp.MAX)
+        copy_ms = float(tc.item()) * nchunk
         torch.cuda.current_stream().wait_stream(back_stream)
         barrier()
         ev0.record()
@@ -869,7 +910,9 @@ def main():
         if world > 1:
             dist.all_reduce(te, op=dist.ReduceOp.MAX)
         e2e = {"value": world * n / (float(te.item()) / args.steps * 1e-3), "unit": UNIT, "chunks": nchunk, "steps_pipelined": pipelined,
-               "h2d_bytes_per_step": n * 12 + n * 4, "d2h_bytes_per_step": n * 4}
+               "h2d_bytes_per_step": n * 12 + n * 4, "d2h_bytes_per_step": n * 4,
+               "copies_alone_ms_per_step": copy_ms, "copies_alone_gbs_per_gpu": (n * 20) / (copy_ms * 1e-3) / 1e9,
+               "host_binding": host_binding}
 
     cpu_baseline = cuda_eager = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
