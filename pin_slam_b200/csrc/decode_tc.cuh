@@ -33,7 +33,11 @@ constexpr uint32_t kChunkBBytes = H * 16;           // 1024: K-direction (leadin
 constexpr uint32_t kTmemColsD = H;                  // accumulator: 64 fp32 columns
 constexpr uint32_t kTmemColsA = 32;                 // A operand: 4 k-steps of 8 tf32 columns
 constexpr unsigned kCtasPerSm = 5;                  // 5 x 96 TMEM columns <= 512
-constexpr size_t kSmemRequest = 40 * 1024;          // > 227 KB / 6: caps residency at 5 CTAs per SM
+// Residency is capped at 5 CTAs per SM (TMEM columns) through shared memory: 5 x (19 + 1 KB) fill the 100 KB carve-out exactly
+// and a sixth CTA does not fit.  The rest of the 256 KB stays L1 for the feature-row gathers (a 40 KB request under a 100 %
+// carve-out did the same capping but left 28 KB of L1: decode 0.417 -> 0.407 ms).
+constexpr size_t kSmemRequest = 19 * 1024;
+constexpr int kCarveoutPct = 44;                    // of 227 KB -> the 100 KB configuration
 
 struct Smem {
     alignas(128) unsigned char b[kChunksB * kChunkBBytes];

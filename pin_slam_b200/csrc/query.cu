@@ -289,10 +289,12 @@ __device__ __forceinline__ void topk_insert64(unsigned long long key, unsigned l
 constexpr int kWalkEntries = 12;
 constexpr uint32_t kWalkIdMask = 0x1FFu;  // entry (4 bits) << 5 | voxel bit (5 bits): identity of a candidate within a lane's walk
 struct BrickLane {
-    uint32_t sel[kWalkEntries][kBlock];  // occupied stencil members still to visit
     uint32_t msk[kWalkEntries][kBlock];  // occupancy of the half brick
-    uint32_t pk[kWalkEntries][kBlock];   // rank of its first record | (64 + linear stencil offset of its voxel 0) << 24
+    uint32_t pk[kWalkEntries][kBlock];   // rank of its first record | (2 * brick + half) << 24
 };
+// (the stencil members still to visit are NOT stored: `msk & half-brick stencil mask` is recomputed when the walk reaches the
+// entry -- two words per entry instead of three keep the kernel's shared memory at 17 KB per CTA, i.e. 90 instead of 56 KB of
+// L1 for the candidate records next to 8 resident CTAs)
 constexpr size_t kBrickSmem = sizeof(BrickLane) + kStencilMasks * 8 + 128 + 32 + 64;
 
 // RESOLVE: the walk ends with the lane's K winners in registers and their records hot in L1, so the resolve step
@@ -399,17 +401,14 @@ __global__ void __launch_bounds__(kBlock, PINQ_SEARCH_MINB) k_search_brick(MapDe
                     }
                 }
             }
-            // stencil offset of the brick's voxel 0 from the box origin, linearised like s_sid
-            const int lin0 = ((4 * (b >> 2) - (ax & 3)) * W + (4 * ((b >> 1) & 1) - (ay & 3))) * W + (4 * (b & 1) - (az & 3));
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
                 const uint32_t occ32 = (uint32_t)(pmb >> (32 * h));
                 const uint32_t sel32 = occ32 & s_hm[(2 * b + h) * 64 + so];
                 if (sel32) {
                     const uint32_t base = pbb + (h ? (uint32_t)__popc((uint32_t)pmb) : 0u);
-                    bl->sel[cnt][tid] = sel32;
                     bl->msk[cnt][tid] = occ32;
-                    bl->pk[cnt][tid] = base | ((uint32_t)(lin0 + h * 2 * W * W + 64) << kRankBits);
+                    bl->pk[cnt][tid] = base | ((uint32_t)(2 * b + h) << kRankBits);
                     ++cnt;
                     total += __popc(sel32);
                 }
@@ -440,9 +439,10 @@ __global__ void __launch_bounds__(kBlock, PINQ_SEARCH_MINB) k_search_brick(MapDe
         nact = total > 0;
         if (nact && m == 0u) {  // next half brick of the list
             ++e;
-            m = bl->sel[e][tid];
             msk = bl->msk[e][tid];
-            bas = bl->pk[e][tid] & ((1u << kRankBits) - 1u);
+            const uint32_t pk = bl->pk[e][tid];
+            bas = pk & ((1u << kRankBits) - 1u);
+            m = msk & s_hm[(pk >> kRankBits) * 64 + so];
         }
         --total;
         const int bit = (__ffs((int)m) - 1) & 31;
@@ -521,11 +521,14 @@ __global__ void __launch_bounds__(kBlock, PINQ_SEARCH_MINB) k_search_brick(MapDe
             nact = total > 0;
             if (nact && m == 0u) {
                 ++e;
-                m = bl->sel[e][tid];
                 msk = bl->msk[e][tid];
                 const uint32_t pk = bl->pk[e][tid];
+                m = msk & s_hm[(pk >> kRankBits) * 64 + so];
                 bas = pk & ((1u << kRankBits) - 1u);
-                lin0 = (int)(pk >> kRankBits) - 64;
+                // stencil offset of the half brick's voxel 0 from the box origin, linearised like s_sid
+                const int bh = (int)(pk >> kRankBits), b = bh >> 1;
+                lin0 = ((4 * (b >> 2) - (ax & 3)) * W + (4 * ((b >> 1) & 1) - (ay & 3))) * W + (4 * (b & 1) - (az & 3)) +
+                       (bh & 1) * 2 * W * W;
             }
             --total;
             const int bit = (__ffs((int)m) - 1) & 31;
@@ -975,6 +978,15 @@ static int run_query(const pinq_query_args* a, int mode, float* feat_out, const 
             smasks = built;
         }
         const size_t smem = kBrickSmem;
+        static bool search_carve = false;
+        if (!search_carve) {
+            // shared memory for 8 CTAs and no more: what is left of the 256 KB stays L1 for the candidate records
+            const char* ce = getenv("PINQ_SEARCH_CARVEOUT");
+            const int carve = ce ? atoi(ce) : (int)((PINQ_SEARCH_MINB * (smem + 1024) * 100 + 232448 - 1) / 232448);
+            cudaFuncSetAttribute(k_search_brick<true>, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
+            cudaFuncSetAttribute(k_search_brick<false>, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
+            search_carve = true;
+        }
         if (resolve_in_search)
             k_search_brick<true><<<grid_for(n, kBlock), kBlock, smem, st>>>(map, bd, src, n, recip, perm, smasks, ws, p);
         else
@@ -1018,13 +1030,18 @@ static int run_query(const pinq_query_args* a, int mode, float* feat_out, const 
         }
         // plain and mesher flavours: tcgen05 / TMEM kernel (decode_tc.cuh); PINQ_DECODE=mma keeps the mma.sync one
         static int use_tc = -1;
+        static size_t dec_smem = tc::kSmemRequest;
         if (use_tc < 0) {
             const char* e = getenv("PINQ_DECODE");
             use_tc = !(e && e[0] == 'm');
-            cudaFuncSetAttribute(k_decode_tc<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc::kSmemRequest);
-            cudaFuncSetAttribute(k_decode_tc<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc::kSmemRequest);
-            cudaFuncSetAttribute(k_decode_tc<false>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
-            cudaFuncSetAttribute(k_decode_tc<true>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+            const char* se = getenv("PINQ_DEC_SMEM_KB");
+            const char* ce = getenv("PINQ_DEC_CARVEOUT");
+            dec_smem = se ? (size_t)atoi(se) * 1024 : tc::kSmemRequest;
+            const int carve = ce ? atoi(ce) : tc::kCarveoutPct;
+            cudaFuncSetAttribute(k_decode_tc<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dec_smem);
+            cudaFuncSetAttribute(k_decode_tc<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dec_smem);
+            cudaFuncSetAttribute(k_decode_tc<false>, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
+            cudaFuncSetAttribute(k_decode_tc<true>, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
         }
         // d sdf/dx (tracking) stays on the mma.sync kernel, whose layer-1 accumulator fragment IS the A fragment of the mask x V
         // product; a CUDA-core gradient epilogue inside the tcgen05 kernel was measured slower (3.32 vs 2.41 ms per 4 Mi
@@ -1033,8 +1050,8 @@ static int run_query(const pinq_query_args* a, int mode, float* feat_out, const 
             const unsigned nb128 = grid_for(n, tc::kRows);
             const unsigned cap128 = (unsigned)sms * tc::kCtasPerSm;  // TMEM columns (and registers) per CTA bound the residency
             const unsigned g128 = nb128 < cap128 ? nb128 : cap128;
-            if (mode == 2) k_decode_tc<true><<<g128, tc::kRows, tc::kSmemRequest, st>>>(p);
-            else k_decode_tc<false><<<g128, tc::kRows, tc::kSmemRequest, st>>>(p);
+            if (mode == 2) k_decode_tc<true><<<g128, tc::kRows, dec_smem, st>>>(p);
+            else k_decode_tc<false><<<g128, tc::kRows, dec_smem, st>>>(p);
         } else {
             const int occ = mode == 2 ? occ_mesh : (a->grad_x ? occ_grad : occ_plain);
             const unsigned cap = (unsigned)(sms * (occ > 0 ? occ : 1));
