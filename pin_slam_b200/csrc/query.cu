@@ -288,7 +288,13 @@ __device__ __forceinline__ void topk_insert64(unsigned long long key, unsigned l
 // touches at most 3 x 2 x 2 of them.
 constexpr int kWalkEntries = 12;
 constexpr uint32_t kWalkIdMask = 0x1FFu;  // entry (4 bits) << 5 | voxel bit (5 bits): identity of a candidate within a lane's walk
+#ifndef PINQ_WALK_SEL
+#define PINQ_WALK_SEL 0
+#endif
 struct BrickLane {
+#if PINQ_WALK_SEL
+    uint32_t sel[kWalkEntries][kBlock];
+#endif
     uint32_t msk[kWalkEntries][kBlock];  // occupancy of the half brick
     uint32_t pk[kWalkEntries][kBlock];   // rank of its first record | (2 * brick + half) << 24
 };
@@ -301,7 +307,7 @@ constexpr size_t kBrickSmem = sizeof(BrickLane) + kStencilMasks * 8 + 128 + 32 +
 // (stage block, per-query outputs, training side effects -- what k_resolve does after the slot-probing search)
 // runs in the tail of this kernel; the rank workspace is then only written for the gradient flavour of the decode.
 #ifndef PINQ_SEARCH_MINB
-#define PINQ_SEARCH_MINB 8
+#define PINQ_SEARCH_MINB 9
 #endif
 template <bool RESOLVE>
 __global__ void __launch_bounds__(kBlock, PINQ_SEARCH_MINB) k_search_brick(MapDev map, BrickDev bd, PointSrc src, int64_t n, bool recip,
@@ -407,6 +413,9 @@ __global__ void __launch_bounds__(kBlock, PINQ_SEARCH_MINB) k_search_brick(MapDe
                 const uint32_t sel32 = occ32 & s_hm[(2 * b + h) * 64 + so];
                 if (sel32) {
                     const uint32_t base = pbb + (h ? (uint32_t)__popc((uint32_t)pmb) : 0u);
+#if PINQ_WALK_SEL
+                    bl->sel[cnt][tid] = sel32;
+#endif
                     bl->msk[cnt][tid] = occ32;
                     bl->pk[cnt][tid] = base | ((uint32_t)(2 * b + h) << kRankBits);
                     ++cnt;
@@ -442,7 +451,11 @@ __global__ void __launch_bounds__(kBlock, PINQ_SEARCH_MINB) k_search_brick(MapDe
             msk = bl->msk[e][tid];
             const uint32_t pk = bl->pk[e][tid];
             bas = pk & ((1u << kRankBits) - 1u);
+#if PINQ_WALK_SEL
+            m = bl->sel[e][tid];
+#else
             m = msk & s_hm[(pk >> kRankBits) * 64 + so];
+#endif
         }
         --total;
         const int bit = (__ffs((int)m) - 1) & 31;
