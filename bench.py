@@ -808,8 +808,10 @@ def main():
     # DRAM bytes ncu measured for one launch of the same command (profiles/ncu_traffic.json, `ncu --set full`), and the
     # unit that limits it according to that capture (profiles/*_ncu_full_summary.csv) -- none of them is DRAM-bound.
     traffic = ncu_traffic()
-    limiter = {"bin": "launch latency (small kernels) + histogram atomics", "search": "instruction issue (integer walk + top-K), L1TEX",
-               "decode": "instruction issue (CUDA-core epilogue of the tcgen05 product)", "bwd": "shared-memory bandwidth (tile writes + UMMA operand reads)",
+    limiter = {"bin": "launch latency (small kernels) + histogram atomics",
+               "search": "instruction issue at 36 of 64 warps (integer walk + top-K; ALU pipe half rate), dependent loads",
+               "decode": "ALU pipe (relu + relu' bit of the CUDA-core epilogue of the tcgen05 product run on the half-rate pipe)",
+               "bwd": "shared-memory data pipe (int8 tile stores + UMMA operand reads), 16 warps per SM",
                "resolve": "L2 gathers", "scatter": "L2 atomics"}
     kernels = {}
     for k, ms in kms.items():
