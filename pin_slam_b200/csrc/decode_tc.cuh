@@ -41,7 +41,8 @@ constexpr int kCarveoutPct = 44;                    // of 227 KB -> the 100 KB c
 
 struct Smem {
     alignas(128) unsigned char b[kChunksB * kChunkBBytes];
-    alignas(16) float w2[H];  // W2 / 2 in accumulator-column order (the epilogue multiplies it by |x| + x = 2 relu(x))
+    alignas(16) float w2[H];  // W2 / 2 in accumulator-column order: relu(x) W2 = |x| W2/2 + x W2/2
+    alignas(16) float u[12];  // sum_j (W2_j / 2) [W1 | b1]_j: the linear half, sum_j x_j W2_j / 2 = in . u
     alignas(8) unsigned long long bar;
     uint32_t tmem_d, tmem_a;
 };
@@ -97,6 +98,11 @@ __global__ void __launch_bounds__(tc::kRows) k_decode_tc(const DecodeParams p) {
         brow[4 * (kChunkBBytes / 16)] = make_uint4(hi[8], hi[9], hi[10], hi[11]);
         brow[5 * (kChunkBBytes / 16)] = make_uint4(lo[8], lo[9], lo[10], lo[11]);
     }
+    if (tid < 12) {  // accumulated in double: u carries the linear half of every neighbour's sdf
+        double acc = 0.0;
+        for (int j = 0; j < H; ++j) acc += 0.5 * (double)__ldg(&p.dec.W2[j]) * (double)l1_operand(p.dec, tid, j);
+        S.u[tid] = (float)acc;
+    }
     if (tid == 0) {
         mbar_init(smem_u32(&S.bar), 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -125,7 +131,7 @@ __global__ void __launch_bounds__(tc::kRows) k_decode_tc(const DecodeParams p) {
     for (int k = 0; k < K; ++k) sk[k] = wk[k] = 0.f;
 
     // epilogue of tile k: the accumulator row of this thread (processing position ei)
-    auto epilogue = [&](int k, int64_t ei, bool ewarp) {
+    auto epilogue = [&](int k, int64_t ei, bool ewarp, float lin) {
         const StageBlock& sb = p.stage[ewarp ? (ei >> 5) : 0];
         const float w = ewarp ? __ldg(&sb.w[k][lane]) : 0.f;
         mbar_wait(smem_u32(&S.bar), phase);
@@ -134,7 +140,7 @@ __global__ void __launch_bounds__(tc::kRows) k_decode_tc(const DecodeParams p) {
         // 16 columns at a time, the next chunk in flight while this one is reduced (32 live registers instead of 64)
         uint32_t va[16], vb[16];
         const uint32_t t0 = tmem_d + lanes;
-        float s0 = 0.f, s1 = 0.f;
+        float s0 = lin, s1 = 0.f;
         uint32_t neg0 = 0u, neg1 = 0u;
         auto reduce16 = [&](const uint32_t (&v)[16], int c0, float& s, uint32_t& neg) {
 #pragma unroll
@@ -143,11 +149,11 @@ __global__ void __launch_bounds__(tc::kRows) k_decode_tc(const DecodeParams p) {
                 const float wv[4] = {w4.x, w4.y, w4.z, w4.w};
 #pragma unroll
                 for (int u = 0; u < 4; ++u) {
-                    // relu on the FMA pipe: |x| + x = 2 relu(x) exactly, times W2 / 2 -- the same product bit for bit as
-                    // max(x, 0) W2, but FADD + FFMA instead of FMNMX + FFMA: the max and the sign-bit funnel shift both
-                    // run on the half-rate ALU pipe, which bounded this epilogue (ncu r4a: pipe_alu 61 %, issue 63 %)
-                    const float x = __uint_as_float(v[c + u]);
-                    s = fmaf(fabsf(x) + x, wv[u], s);
+                    // relu(x) W2 = |x| W2/2 + x W2/2: the first half is ONE FFMA per element (|x| is an operand modifier), the
+                    // second is linear in the decoder inputs and was added once per tile (lin = in . u, 12 FFMAs).  The max
+                    // and the sign-bit funnel shift both run on the half-rate ALU pipe, which bounded this epilogue (ncu r4a:
+                    // pipe_alu 61 %, issue 63 %); now it is 2 instructions per element, one per pipe
+                    s = fmaf(fabsf(__uint_as_float(v[c + u])), wv[u], s);
                     neg = __funnelshift_l(v[c + u], neg, 1);  // sign bits: 1 <-> relu' = 0
                 }
             }
@@ -235,10 +241,23 @@ __global__ void __launch_bounds__(tc::kRows) k_decode_tc(const DecodeParams p) {
         for (int k = 0; k < K; ++k) nidx[k] = -1;
 #pragma unroll
         for (int k = 0; k < K; ++k) {
+            float lin = 0.f;  // linear half of this tile's sdf
             // ---- stage tile (blk, k): thread = row = TMEM lane; one tcgen05.st of the 32 A columns
             //      [lo f0..3 | lo f4..7 | lo v,0 | hi v,1 | hi v,1 | 0 | hi f0..3 | hi f4..7]
             {
                 const float4 fa = pfa, fb = pfb, hv = phv;
+                {
+                    // (re-read per tile through a volatile access: hoisted out of the loop the 12 values cost the registers
+                    // that keep 5 CTAs on an SM)
+                    const volatile float* su = S.u;
+                    const float4 u0 = make_float4(su[0], su[1], su[2], su[3]), u1 = make_float4(su[4], su[5], su[6], su[7]),
+                                 u2 = make_float4(su[8], su[9], su[10], su[11]);
+                    float l = hv.w * u2.w;
+                    l = fmaf(fa.x, u0.x, l); l = fmaf(fa.y, u0.y, l); l = fmaf(fa.z, u0.z, l); l = fmaf(fa.w, u0.w, l);
+                    l = fmaf(fb.x, u1.x, l); l = fmaf(fb.y, u1.y, l); l = fmaf(fb.z, u1.z, l); l = fmaf(fb.w, u1.w, l);
+                    l = fmaf(hv.x, u2.x, l); l = fmaf(hv.y, u2.y, l); l = fmaf(hv.z, u2.z, l);
+                    lin = l;
+                }
                 auto lo_of = [](float x) { return __float_as_uint(x - __uint_as_float(__float_as_uint(x) & 0xffffe000u)); };
                 uint32_t r[32];
                 r[0] = lo_of(fa.x); r[1] = lo_of(fa.y); r[2] = lo_of(fa.z); r[3] = lo_of(fa.w);
@@ -271,7 +290,7 @@ __global__ void __launch_bounds__(tc::kRows) k_decode_tc(const DecodeParams p) {
             if (k == 1 && has_next) load_idx(ni, nidx);
             if (k + 1 < K) load_tile(i, k + 1, cidx[k + 1 < K ? k + 1 : 0]);
             else if (has_next) load_tile(ni, 0, nidx[0]);
-            epilogue(k, i, wlive);
+            epilogue(k, i, wlive, lin);
         }
         finalize(i);
 #pragma unroll
