@@ -37,6 +37,7 @@ extern "C" {
 #define PINQ_F_RECIP_DIV 8u    /* floor(x*(1/res)) instead of floor(x/res): CUDA-eager oracle (H1)     */
 #define PINQ_F_SKIP_EMPTY 16u  /* mesher: sdf = 0 where nn_count == 0 (utils/mesher.py:96-103)         */
 #define PINQ_F_EXACT_KEYS 64u  /* brick search: every query through the 64-bit-key pass (the fast pass falls back to it on truncated-key ties; tests) */
+#define PINQ_F_STENCIL_IN_RANGE 128u /* brick search: the caller has verified that max over the stencil of sum_i ((|dx_i| + 1) res)^2 < max_valid_dist2, i.e. no candidate of a stencil cell can fail the distance test (model/neural_points.py:499): the test is skipped */
 #define PINQ_F_MMA_SYNC 32u    /* decode / backward: the mma.sync kernels instead of the tcgen05 ones (A/B tests; also pinq_bwd_args.flags) */
 
 const char* pinq_last_error(void);

@@ -12,7 +12,7 @@ _LIB_PATH = os.path.join(_HERE, "libpinq.so")
 if os.environ.get("PINQ_LIB"):  # kernel experiments only (scripts/variants.py): another build of the same sources
     _LIB_PATH = os.environ["PINQ_LIB"]
 
-F_LOCAL, F_TRAINING, F_ROTATE, F_RECIP_DIV, F_SKIP_EMPTY, F_MMA_SYNC, F_EXACT_KEYS = 1, 2, 4, 8, 16, 32, 64
+F_LOCAL, F_TRAINING, F_ROTATE, F_RECIP_DIV, F_SKIP_EMPTY, F_MMA_SYNC, F_EXACT_KEYS, F_STENCIL_IN_RANGE = 1, 2, 4, 8, 16, 32, 64, 128
 
 _vp, _i64, _i32, _u32, _u64, _f32 = C.c_void_p, C.c_int64, C.c_int32, C.c_uint32, C.c_uint64, C.c_float
 

@@ -309,7 +309,9 @@ constexpr size_t kBrickSmem = sizeof(BrickLane) + kStencilMasks * 8 + 128 + 32 +
 #ifndef PINQ_SEARCH_MINB
 #define PINQ_SEARCH_MINB 9
 #endif
-template <bool RESOLVE>
+// DTEST = false: the caller has proved that every stencil cell lies within max_valid_dist2 of every point of the query's own cell
+// (PINQ_F_STENCIL_IN_RANGE), so `d2 > max` never fires and the per-candidate comparison is compiled out.
+template <bool RESOLVE, bool DTEST>
 __global__ void __launch_bounds__(kBlock, PINQ_SEARCH_MINB) k_search_brick(MapDev map, BrickDev bd, PointSrc src, int64_t n, bool recip,
                                                          const int32_t* __restrict__ perm,
                                                          const unsigned long long* __restrict__ stencil_masks,
@@ -486,7 +488,7 @@ __global__ void __launch_bounds__(kBlock, PINQ_SEARCH_MINB) k_search_brick(MapDe
         for (int u = 0; u < PINQ_SEARCH_BATCH; ++u) {
             const float d2 = dist2_rn(rcs[u].x, rcs[u].y, rcs[u].z, x, y, z);
             // valid: index != -1 (-2 = hazard H13, still a candidate) and not d2 > max (neural_points.py:499)
-            const bool ok = acts[u] && __float_as_int(rcs[u].w) != -1 && !(d2 > map.max_d2);
+            const bool ok = acts[u] && __float_as_int(rcs[u].w) != -1 && (!DTEST || !(d2 > map.max_d2));
             nn += ok ? 1 : 0;
             uint32_t key = ok ? ((__float_as_uint(d2) & ~kWalkIdMask) | ids[u]) : ~0u;
 #ifndef PINQ_SEARCH_SERIAL_INSERT
@@ -558,7 +560,7 @@ __global__ void __launch_bounds__(kBlock, PINQ_SEARCH_MINB) k_search_brick(MapDe
             const uint32_t low = nlow;
             advance();
             const float d2 = dist2_rn(rc.x, rc.y, rc.z, x, y, z);
-            const bool ok = act && __float_as_int(rc.w) != -1 && !(d2 > map.max_d2);
+            const bool ok = act && __float_as_int(rc.w) != -1 && (!DTEST || !(d2 > map.max_d2));
             const unsigned long long key = ok ? ((unsigned long long)__float_as_uint(d2) << 32) | low : ~0ull;
             topk_insert64(key, kk);
         }
@@ -996,14 +998,21 @@ static int run_query(const pinq_query_args* a, int mode, float* feat_out, const 
             // shared memory for 8 CTAs and no more: what is left of the 256 KB stays L1 for the candidate records
             const char* ce = getenv("PINQ_SEARCH_CARVEOUT");
             const int carve = ce ? atoi(ce) : (int)((PINQ_SEARCH_MINB * (smem + 1024) * 100 + 232448 - 1) / 232448);
-            cudaFuncSetAttribute(k_search_brick<true>, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
-            cudaFuncSetAttribute(k_search_brick<false>, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
+            cudaFuncSetAttribute(k_search_brick<true, true>, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
+            cudaFuncSetAttribute(k_search_brick<false, true>, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
+            cudaFuncSetAttribute(k_search_brick<true, false>, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
+            cudaFuncSetAttribute(k_search_brick<false, false>, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
             search_carve = true;
         }
-        if (resolve_in_search)
-            k_search_brick<true><<<grid_for(n, kBlock), kBlock, smem, st>>>(map, bd, src, n, recip, perm, smasks, ws, p);
-        else
-            k_search_brick<false><<<grid_for(n, kBlock), kBlock, smem, st>>>(map, bd, src, n, recip, perm, smasks, ws, p);
+        const bool dtest = !(a->flags & PINQ_F_STENCIL_IN_RANGE);
+        const unsigned gsb = grid_for(n, kBlock);
+        if (resolve_in_search) {
+            if (dtest) k_search_brick<true, true><<<gsb, kBlock, smem, st>>>(map, bd, src, n, recip, perm, smasks, ws, p);
+            else k_search_brick<true, false><<<gsb, kBlock, smem, st>>>(map, bd, src, n, recip, perm, smasks, ws, p);
+        } else {
+            if (dtest) k_search_brick<false, true><<<gsb, kBlock, smem, st>>>(map, bd, src, n, recip, perm, smasks, ws, p);
+            else k_search_brick<false, false><<<gsb, kBlock, smem, st>>>(map, bd, src, n, recip, perm, smasks, ws, p);
+        }
     } else {
         k_search<<<grid_for(n, kBlock), kBlock, map.kn * sizeof(uint32_t), st>>>(map, src, n, recip, perm, ws, a->skip);
     }
@@ -1025,9 +1034,7 @@ static int run_query(const pinq_query_args* a, int mode, float* feat_out, const 
         const size_t sm_plain = dec_frag_bytes(false) + (kBlock / 32) * sizeof(WarpStage<false>);
         const size_t sm_grad = dec_frag_bytes(true) + (kBlock / 32) * sizeof(WarpStage<true>);
         static bool carve = false;
-        if (!carve) {  // let 6 CTAs of ~31 KB share an SM
-            cudaFuncSetAttribute(k_decode_mma<false, false>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
-            cudaFuncSetAttribute(k_decode_mma<false, true>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+        if (!carve) {
             cudaFuncSetAttribute(k_decode_mma<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_grad);
             carve = true;
         }
@@ -1040,6 +1047,11 @@ static int run_query(const pinq_query_args* a, int mode, float* feat_out, const 
             cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_plain, k_decode_mma<false, false>, kBlock, sm_plain);
             cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_mesh, k_decode_mma<false, true>, kBlock, sm_plain);
             cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_grad, k_decode_mma<true, false>, kBlock, sm_grad);
+            // shared memory for the resident CTAs and no more: the rest of the 256 KB stays L1 for the gathers
+            auto pct = [](int occ, size_t smem) { return (int)(((size_t)(occ > 0 ? occ : 1) * (smem + 1024) * 100 + 232448 - 1) / 232448); };
+            cudaFuncSetAttribute(k_decode_mma<false, false>, cudaFuncAttributePreferredSharedMemoryCarveout, pct(occ_plain, sm_plain));
+            cudaFuncSetAttribute(k_decode_mma<false, true>, cudaFuncAttributePreferredSharedMemoryCarveout, pct(occ_mesh, sm_plain));
+            cudaFuncSetAttribute(k_decode_mma<true, false>, cudaFuncAttributePreferredSharedMemoryCarveout, pct(occ_grad, sm_grad));
         }
         // plain and mesher flavours: tcgen05 / TMEM kernel (decode_tc.cuh); PINQ_DECODE=mma keeps the mma.sync one
         static int use_tc = -1;

@@ -104,6 +104,7 @@ class NeuralPoints(nn.Module):
         # fall back to the slot-probing search (same results, tested by forcing the limit down)
         self.brick_max_points = 1 << 24
         self.exact_search_keys = False  # A/B tests: brick search with 64-bit keys for every query
+        self.skip_in_range_test = True  # A/B tests: False keeps the per-candidate `d2 > max_valid_dist2` comparison
         self.decode_wait_event = None  # torch.cuda.Event the fused query's decode waits for (see pinq_query_args)
         self.use_mma_sync = False  # A/B tests: the mma.sync decode / backward kernels instead of the tcgen05 ones
         self._brick_tab = self._brick_global = self._brick_local = self._brick_buf = self._brick_counters = None
@@ -355,6 +356,12 @@ class NeuralPoints(nn.Module):
         self.max_valid_dist2 = 3 * ((num_nei_cells + 1) * self.resolution) ** 2
         self._stencil_i32 = self.neighbor_dx.to(torch.int32).contiguous()
         self._stencil_key = (int(num_nei_cells), float(search_alpha))
+        # A query and a neural point of stencil cell dx are at most (|dx_i| + 1) cells apart per axis.  If even that reach stays
+        # below max_valid_dist2 (run_kitti.yaml: 17 x 0.16 = 2.72 m^2 < 4.32 m^2), the reference's `dist2 > max_valid_dist2`
+        # rejection (:499) can never fire for a candidate found through the brick index and the kernel skips the comparison
+        # (PINQ_F_STENCIL_IN_RANGE).  0.1 % margin for the fp32 rounding of the cell assignment and of d^2.
+        reach2 = float(((self.neighbor_dx.abs() + 1) ** 2).sum(-1).max()) * float(self.resolution) ** 2
+        self._stencil_in_range = reach2 * 1.001 < float(self.max_valid_dist2)
 
     # ---- packed views for the kernels ---------------------------------------------------------
     def _refresh_candidates(self):
@@ -527,6 +534,8 @@ class NeuralPoints(nn.Module):
             flags |= P.F_MMA_SYNC
         if self.exact_search_keys:
             flags |= P.F_EXACT_KEYS
+        if getattr(self, "_stencil_in_range", False) and getattr(self, "skip_in_range_test", True):
+            flags |= P.F_STENCIL_IN_RANGE
         feats = self.local_geo_features if query_locally else self.geo_features
         cert = self.local_point_certainties if query_locally else self.point_certainties
         quats = self.local_point_orientations if query_locally else self.point_orientations

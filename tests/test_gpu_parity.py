@@ -261,6 +261,41 @@ def test_brick_rank_limit_falls_back_to_slot_probing(maps):
     assert bool(m._map_view(True).brick_tab)
 
 
+def test_skipped_distance_test_changes_nothing(maps):
+    """PINQ_F_STENCIL_IN_RANGE: with run_kitti.yaml's stencil no candidate of a stencil cell can be farther than
+    max_valid_dist2 (17 x 0.16 m^2 < 4.32 m^2), so the brick search compiles the `dist2 > max_valid_dist2` rejection
+    (model/neural_points.py:499) out.  Same neighbours, counts and sdf with the comparison kept -- incl. far queries whose
+    candidates sit in the outermost stencil cells -- and the oracle's neighbours."""
+    s, m, _, dec, d, _ = maps
+    from pin_slam_b200 import _pinq as P
+    assert m._stencil_in_range
+    pts = s.points
+    lo, hi = pts.min(0).values, pts.max(0).values
+    g = torch.Generator().manual_seed(31)
+    far = lo + (hi - lo) * torch.rand((30000, 3), generator=g)
+    q = torch.cat([make_queries(s.points, 60000, seed=37), far]).cuda()
+    res = {}
+    try:
+        for skip in (True, False):
+            m.skip_in_range_test = skip
+            a = m._query_args(q, dec.view(), None, False, True)
+            assert bool(a.flags & P.F_STENCIL_IN_RANGE) == skip
+            knn = torch.empty((q.shape[0], 6), dtype=torch.int32, device="cuda")
+            sdf = torch.empty(q.shape[0], device="cuda")
+            nn = torch.empty(q.shape[0], dtype=torch.int32, device="cuda")
+            a.knn_idx, a.sdf, a.nn_count = P.ptr(knn), P.ptr(sdf), P.ptr(nn)
+            P.check(P.load().pinq_query_fused_fwd(a, P.stream()))
+            torch.cuda.synchronize()
+            res[skip] = (knn, sdf, nn)
+    finally:
+        m.skip_in_range_test = True
+    for x, y in zip(res[True], res[False]):
+        assert torch.equal(x, y)
+    _, _, nn_ref, _, knn_ref = O.query_feature(s, q.cpu(), None, False, True)
+    assert torch.equal(res[True][0].cpu().long(), knn_ref)
+    assert torch.equal(res[True][2].cpu().long(), nn_ref.long())
+
+
 def test_truncated_key_search_equals_exact_keys(maps):
     """Brick search fast pass (32-bit keys: 23 bits of d^2 | walk identity, csrc/query.cu) against the 64-bit-key pass
     forced for every query (PINQ_F_EXACT_KEYS): same K neighbours in the same order, also for queries built to tie
