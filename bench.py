@@ -657,7 +657,8 @@ def main():
     # points and map geometry only); the decode of step i + 1 -- which in training reads the parameters the exchange's
     # optimizer would have updated -- waits for it (pinq_query_args.decode_wait_event), and so does everything after it.
     overlap = peer is not None and os.environ.get("PINQ_EXCHANGE_OVERLAP", "1") != "0"
-    side = torch.cuda.Stream() if overlap else None
+    # high priority: the exchange's few CTAs take the SM slots the search frees FIRST instead of queueing behind its 32 768 CTAs
+    side = torch.cuda.Stream(priority=int(os.environ.get("PINQ_EXCHANGE_PRIORITY", "-1"))) if overlap else None
     ev_bwd, ev_x = (torch.cuda.Event(), torch.cuda.Event()) if overlap else (None, None)
     if overlap:
         ev_x.record(torch.cuda.current_stream())

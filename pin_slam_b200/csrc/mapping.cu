@@ -219,7 +219,10 @@ static MapSide* map_side_for(cudaStream_t st) {
     if (used == 32) return nullptr;
     MapSide& m = pool[used];
     m.main = st;
-    if (cudaStreamCreateWithFlags(&m.side, cudaStreamNonBlocking) != cudaSuccess) return nullptr;
+    // highest priority: the exchange's few CTAs take the SM slots the next iteration's search frees first
+    int prio_lo = 0, prio_hi = 0;
+    cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);
+    if (cudaStreamCreateWithPriority(&m.side, cudaStreamNonBlocking, prio_hi) != cudaSuccess) return nullptr;
     if (cudaEventCreateWithFlags(&m.bwd_done, cudaEventDisableTiming) != cudaSuccess) return nullptr;
     if (cudaEventCreateWithFlags(&m.exchanged, cudaEventDisableTiming) != cudaSuccess) return nullptr;
     ++used;
