@@ -76,23 +76,6 @@ __device__ __forceinline__ void umma_i8(uint32_t tmem_d, uint64_t adesc, uint64_
 __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
     asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" :: "l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
-// the four balanced base-256 digits of I (|I| < 2^31 - 2^23), digit p in byte p: I = sum_p (int8)byte_p 256^p
-__device__ __forceinline__ uint32_t digits_of(int I) { return ((uint32_t)I + 0x00808080u) ^ 0x00808080u; }
-// sum_p D_p 256^p of four exact digit sums (|D_p| < 2^21), recombined in fp32
-__device__ __forceinline__ float undigit(uint32_t d0, uint32_t d1, uint32_t d2, uint32_t d3) {
-    const int lo = (int)d1 * 256 + (int)d0, hi = (int)d3 * 256 + (int)d2;
-    return fmaf((float)hi, 65536.f, (float)lo);
-}
-// 2^e as a float, e in [-126, 127]
-__device__ __forceinline__ float pow2i(int e) { return __uint_as_float((uint32_t)(127 + e) << 23); }
-// floor(log2 m) for a normal m > 0, clamped to +-100 (0 and subnormals -> -100)
-__device__ __forceinline__ int floor_log2(float m) {
-    int e = (int)((__float_as_uint(m) >> 23) & 0xffu) - 127;
-    if (m == 0.f || e < -100) e = -100;
-    if (e > 100) e = 100;
-    return e;
-}
-
 }  // namespace tcb
 
 template <bool DEC, bool FEAT>

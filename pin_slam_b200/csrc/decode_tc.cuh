@@ -33,6 +33,10 @@ constexpr uint32_t kChunkBBytes = H * 16;           // 1024: K-direction (leadin
 constexpr uint32_t kTmemColsD = H;                  // accumulator: 64 fp32 columns
 constexpr uint32_t kTmemColsA = 32;                 // A operand: 4 k-steps of 8 tf32 columns
 constexpr unsigned kCtasPerSm = 5;                  // 5 x 96 TMEM columns <= 512
+constexpr int kGradN = 16;                          // GRAD: mask x (W2 W1[:, 8:11]) in 4 digits -> 12 columns, padded to 16
+constexpr uint32_t kTmemColsG = 32;                 // GRAD: 16 columns of mask bytes (A operand) + 16 of s32 results
+constexpr unsigned kCtasPerSmGrad = 4;              // 4 x 128 TMEM columns
+constexpr size_t kSmemRequestGrad = 24 * 1024;      // 4 x (24 + 1) KB fill the same 100 KB configuration
 // Residency is capped at 5 CTAs per SM (TMEM columns) through shared memory: 5 x (19 + 1 KB) fill the 100 KB carve-out exactly
 // and a sixth CTA does not fit.  The rest of the 256 KB stays L1 for the feature-row gathers (a 40 KB request under a 100 %
 // carve-out did the same capping but left 28 KB of L1: decode 0.417 -> 0.407 ms).
@@ -43,8 +47,11 @@ struct Smem {
     alignas(128) unsigned char b[kChunksB * kChunkBBytes];
     alignas(16) float w2[H];  // W2 / 2 in accumulator-column order: relu(x) W2 = |x| W2/2 + x W2/2
     alignas(16) float u[12];  // sum_j (W2_j / 2) [W1 | b1]_j: the linear half, sum_j x_j W2_j / 2 = in . u
-    alignas(8) unsigned long long bar;
-    uint32_t tmem_d, tmem_a;
+    // GRAD: B operand of the mask product, [16 hidden (mask-bit order)][n = input * 4 + digit, 16] x 16 bytes of int8
+    alignas(128) unsigned char cq[(H / 16) * kGradN * 16];
+    float gscale[4];          // 2^-s of d s / d v_i
+    alignas(8) unsigned long long bar, bar2;
+    uint32_t tmem_d, tmem_a, tmem_g;
 };
 static_assert(sizeof(Smem) <= kSmemRequest, "decode_tc shared memory");
 
@@ -73,10 +80,28 @@ __device__ __forceinline__ void umma_tf32_ts(uint32_t tmem_d, uint32_t tmem_a, u
         :: "r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(kIdesc), "r"(accumulate) : "memory");
 }
 
+// mask product of the gradient flavour: D = s32, A = B = signed 8 bit, K-major, N = 16, M = 128; A from TMEM
+constexpr uint32_t kIdescG = (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(kGradN >> 3) << 17) | ((uint32_t)(kRows >> 4) << 24);
+__device__ __forceinline__ void umma_i8_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::i8 [%0], [%1], %2, %3, p;\n\t}"
+        :: "r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(kIdescG), "r"(accumulate) : "memory");
+}
+// K index kk of the mask product = bit kk of the row's 64 relu' bits (word kk >> 5, bit kk & 31) <-> accumulator column
+__host__ __device__ constexpr int col_of_maskbit(int kk) { return 32 * (kk >> 5) + 31 - (kk & 31); }
+
 }  // namespace tc
 
-template <bool MESH>
-__global__ void __launch_bounds__(tc::kRows) k_decode_tc(const DecodeParams p) {
+// GRAD (tracking, utils/tracker.py:230-253 + utils/tools.py:174): d sdf/dx in the same pass.  d s_k / d v_k = sum_j relu'_j W2_j
+// W1[j, 8:11] is a SECOND tensor-core product per tile: the row's 64 relu' bits, expanded to 0 / 1 bytes, go into 16 TMEM
+// columns as the A operand of a tcgen05.mma.kind::i8 against W2 W1[:, 8:11] in 32-bit fixed point (four digits per input,
+// tc.cuh), exact integer sums recombined in fp32.  It is issued together with the NEXT tile's layer-1 product (one barrier per
+// tile; one extra at the end of a block) and read one tile later.  The IDW part of the gradient needs the un-normalised
+// weights and the TRUE x - p_k (hazard H13): re-derived per query from the search's rank workspace in finalize(), exactly like
+// k_decode_mma<GRAD>.
+template <bool MESH, bool GRAD>
+__device__ __forceinline__ void decode_tc_body(const DecodeParams& p) {
     using namespace tc;
     if (p.skip && *p.skip) return;
     extern __shared__ __align__(128) unsigned char s_tc_raw[];
@@ -103,8 +128,34 @@ __global__ void __launch_bounds__(tc::kRows) k_decode_tc(const DecodeParams p) {
         for (int j = 0; j < H; ++j) acc += 0.5 * (double)__ldg(&p.dec.W2[j]) * (double)l1_operand(p.dec, tid, j);
         S.u[tid] = (float)acc;
     }
+    if (GRAD) {
+        if (tid < 3) {  // fixed-point scale of d s / d v_i: 2^(30 - e) with max_j |W2_j W1[j][8 + i]| < 2^e
+            float m = 0.f;
+            for (int j = 0; j < H; ++j) m = fmaxf(m, fabsf(__ldg(&p.dec.W2[j]) * __ldg(&p.dec.W1[j * IN + 8 + tid])));
+            int ec = floor_log2(m) + 1;
+            ec = ec < -90 ? -90 : ec;
+            S.gscale[tid] = pow2i(ec - 30);
+        }
+        __syncthreads();
+        for (int e = tid; e < (H / 16) * kGradN; e += kRows) {
+            const int kc = e / kGradN, n = e % kGradN, i = n >> 2, dg = n & 3;
+            uint32_t w[4] = {0u, 0u, 0u, 0u};
+            if (i < 3) {
+                const float q = 1.f / S.gscale[i];  // a power of two: exact
+#pragma unroll
+                for (int b = 0; b < 16; ++b) {
+                    const int j = hidden_of_col(col_of_maskbit(16 * kc + b));
+                    const float v = __ldg(&p.dec.W2[j]) * __ldg(&p.dec.W1[j * IN + 8 + i]);
+                    const uint32_t d = (digits_of(__float2int_rn(v * q)) >> (8 * dg)) & 0xffu;
+                    w[b >> 2] |= d << (8 * (b & 3));
+                }
+            }
+            *reinterpret_cast<uint4*>(S.cq + e * 16) = make_uint4(w[0], w[1], w[2], w[3]);
+        }
+    }
     if (tid == 0) {
         mbar_init(smem_u32(&S.bar), 1);
+        mbar_init(smem_u32(&S.bar2), 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 0) {
@@ -112,23 +163,40 @@ __global__ void __launch_bounds__(tc::kRows) k_decode_tc(const DecodeParams p) {
                      :: "r"(smem_u32(&S.tmem_d)), "r"(kTmemColsD) : "memory");
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
                      :: "r"(smem_u32(&S.tmem_a)), "r"(kTmemColsA) : "memory");
+        if (GRAD)
+            asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
+                         :: "r"(smem_u32(&S.tmem_g)), "r"(kTmemColsG) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
     fence_async_smem();
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
-    const uint32_t tmem_d = S.tmem_d, tmem_a = S.tmem_a;
+    const uint32_t tmem_d = S.tmem_d, tmem_a = S.tmem_a, tmem_g = GRAD ? S.tmem_g : 0u;
+    const uint64_t cdesc = umma_desc(smem_u32(S.cq), kGradN * 16, 128);  // K-major: next 16 hidden = 256 bytes, next 8 n = 128
     const uint32_t lanes = (uint32_t)(32 * warp) << 16;  // this warp's 32 TMEM lanes
     const uint64_t bdesc = umma_desc(smem_u32(S.b), kChunkBBytes, 128);
     const float b2 = __ldg(p.dec.b2), scale = p.dec.sdf_scale;
     const int64_t nblocks = (p.n + kRows - 1) / kRows;
     uint2* mask2 = reinterpret_cast<uint2*>(p.relu_mask);
 
-    uint32_t phase = 0u;
+    uint32_t phase = 0u, phase2 = 0u;
     float sdf = 0.f, sk[K], wk[K];
+    float gv[GRAD ? K : 1][3];  // d s_k / d v_k before the sdf scale
 #pragma unroll
     for (int k = 0; k < K; ++k) sk[k] = wk[k] = 0.f;
+    // result of the mask product issued for tile kp (one tile, or one barrier, earlier)
+    auto read_grad = [&](int kp) {
+        mbar_wait(smem_u32(&S.bar2), phase2);
+        phase2 ^= 1u;
+        tc_fence_after();
+        uint32_t d[16];
+        tmem_ld16(tmem_g + lanes + 16, d);
+        tmem_ld_wait(d);
+        tc_fence_before();
+#pragma unroll
+        for (int i = 0; i < 3; ++i) gv[GRAD ? kp : 0][i] = undigit(d[4 * i], d[4 * i + 1], d[4 * i + 2], d[4 * i + 3]) * S.gscale[i];
+    };
 
     // epilogue of tile k: the accumulator row of this thread (processing position ei)
     auto epilogue = [&](int k, int64_t ei, bool ewarp, float lin) {
@@ -172,6 +240,16 @@ __global__ void __launch_bounds__(tc::kRows) k_decode_tc(const DecodeParams p) {
         tc_fence_before();  // the accumulator may be overwritten after the next block-wide barrier
         reduce16(vb, 48, s1, neg1);
         if (mask2 && ewarp) mask2[((ei >> 5) * K + k) * 32 + lane] = make_uint2(~neg0, ~neg1);
+        if (GRAD) {
+            if (k > 0) read_grad(k - 1);  // ... which also frees the mask operand for this tile's bits
+            uint32_t mb[16];  // 64 relu' bits -> 64 bytes of 0 / 1 (4 bits -> 4 bytes by one multiply)
+#pragma unroll
+            for (int t4 = 0; t4 < 16; ++t4)
+                mb[t4] = ((((t4 < 8 ? ~neg0 : ~neg1) >> (4 * (t4 & 7))) & 0xfu) * 0x00204081u) & 0x01010101u;
+            tmem_st16(tmem_g + lanes, mb);
+            asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+            tc_fence_before();
+        }
         const float s = ((s0 + s1) + b2) * scale;  // decoder.py:80-81
         sk[k] = s;
         wk[k] = w;
@@ -198,6 +276,29 @@ __global__ void __launch_bounds__(tc::kRows) k_decode_tc(const DecodeParams p) {
                 var = fmaf(wk[k], d * d, var);
             }
             p.sdf_std[q] = sqrtf(var);
+        }
+        if (GRAD && p.grad_x) {
+            // d sdf/dx = sum_k w_k R_k^T (ds_k/dv_k) + (1/S) sum_k (s_k - sdf) d wt_k/dx,  d wt_k/dx = -2 wt_k^2 (x - p_k)
+            float x, y, z;
+            load_point(p.src, q, x, y, z);
+            QueryLane L;
+            resolve_query<true, false, false>(p, p.ws + ei * kWs, ei, q, true, x, y, z, L);
+            float ox = 0.f, oy = 0.f, oz = 0.f;
+            const float inv_s = 1.0f / L.wsum;
+#pragma unroll
+            for (int k = 0; k < K; ++k) {
+                if (L.kidx[k] >= 0) {
+                    float ax = gv[GRAD ? k : 0][0] * scale, ay = gv[GRAD ? k : 0][1] * scale, az = gv[GRAD ? k : 0][2] * scale;
+                    if (p.rotate) quat_rotate(__ldg(&p.quats[L.kidx[k]]), true, ax, ay, az);
+                    const float c = (sk[k] - sdf) * (-2.f * L.wt[k] * L.wt[k]) * inv_s;
+                    ox += wk[k] * ax + c * L.ux[k];
+                    oy += wk[k] * ay + c * L.uy[k];
+                    oz += wk[k] * az + c * L.uz[k];
+                }
+            }
+            p.grad_x[3 * q] = ox;
+            p.grad_x[3 * q + 1] = oy;
+            p.grad_x[3 * q + 2] = oz;
         }
     };
 
@@ -285,12 +386,27 @@ __global__ void __launch_bounds__(tc::kRows) k_decode_tc(const DecodeParams p) {
                 umma_tf32_ts(tmem_d, tmem_a + 24, bdesc + 0 * cb, 1u);  // hi(f) x hi W
                 umma_tf32_ts(tmem_d, tmem_a + 16, bdesc + 4 * cb, 1u);  // hi(v,1) | 0  x  hi W ; -
                 umma_commit(smem_u32(&S.bar));
+                if (GRAD && k > 0) {  // mask of tile k - 1 (staged by its epilogue) x W2 W1[:, 8:11]: 2 x K = 32
+                    umma_i8_ts(tmem_g + 16, tmem_g, cdesc, 0u);
+                    umma_i8_ts(tmem_g + 16, tmem_g + 8, cdesc + (2 * kGradN * 16 >> 4), 1u);
+                    umma_commit(smem_u32(&S.bar2));
+                }
             }
             // ---- loads of the next tile while the MMAs run, then the epilogue of this one ----
             if (k == 1 && has_next) load_idx(ni, nidx);
             if (k + 1 < K) load_tile(i, k + 1, cidx[k + 1 < K ? k + 1 : 0]);
             else if (has_next) load_tile(ni, 0, nidx[0]);
             epilogue(k, i, wlive, lin);
+        }
+        if (GRAD) {  // the last tile's mask product has no next tile to ride on
+            __syncthreads();
+            if (tid == 0) {
+                tc_fence_after();
+                umma_i8_ts(tmem_g + 16, tmem_g, cdesc, 0u);
+                umma_i8_ts(tmem_g + 16, tmem_g + 8, cdesc + (2 * kGradN * 16 >> 4), 1u);
+                umma_commit(smem_u32(&S.bar2));
+            }
+            read_grad(K - 1);
         }
         finalize(i);
 #pragma unroll
@@ -302,5 +418,15 @@ __global__ void __launch_bounds__(tc::kRows) k_decode_tc(const DecodeParams p) {
         tc_fence_after();
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem_d), "r"(kTmemColsD) : "memory");
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem_a), "r"(kTmemColsA) : "memory");
+        if (GRAD) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem_g), "r"(kTmemColsG) : "memory");
     }
+}
+
+// (two entry points: a min-blocks hint on the plain flavours makes ptxas spill at 96 registers where it needs 92 without one)
+template <bool MESH>
+__global__ void __launch_bounds__(tc::kRows) k_decode_tc(const DecodeParams p) {
+    decode_tc_body<MESH, false>(p);
+}
+__global__ void __launch_bounds__(tc::kRows, tc::kCtasPerSmGrad) k_decode_tc_grad(const DecodeParams p) {
+    decode_tc_body<false, true>(p);
 }

@@ -1053,29 +1053,33 @@ static int run_query(const pinq_query_args* a, int mode, float* feat_out, const 
             cudaFuncSetAttribute(k_decode_mma<false, true>, cudaFuncAttributePreferredSharedMemoryCarveout, pct(occ_mesh, sm_plain));
             cudaFuncSetAttribute(k_decode_mma<true, false>, cudaFuncAttributePreferredSharedMemoryCarveout, pct(occ_grad, sm_grad));
         }
-        // plain and mesher flavours: tcgen05 / TMEM kernel (decode_tc.cuh); PINQ_DECODE=mma keeps the mma.sync one
-        static int use_tc = -1;
+        // all flavours: tcgen05 / TMEM kernel (decode_tc.cuh); PINQ_DECODE=mma keeps the mma.sync ones, PINQ_DECODE_GRAD=mma only
+        // for the gradient flavour (A/B partner of k_decode_tc_grad)
+        static int use_tc = -1, use_tc_grad = 1;
         static size_t dec_smem = tc::kSmemRequest;
         if (use_tc < 0) {
             const char* e = getenv("PINQ_DECODE");
+            const char* eg = getenv("PINQ_DECODE_GRAD");
             use_tc = !(e && e[0] == 'm');
+            use_tc_grad = !(eg && eg[0] == 'm');
             const char* se = getenv("PINQ_DEC_SMEM_KB");
             const char* ce = getenv("PINQ_DEC_CARVEOUT");
             dec_smem = se ? (size_t)atoi(se) * 1024 : tc::kSmemRequest;
             const int carve = ce ? atoi(ce) : tc::kCarveoutPct;
             cudaFuncSetAttribute(k_decode_tc<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dec_smem);
             cudaFuncSetAttribute(k_decode_tc<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dec_smem);
+            cudaFuncSetAttribute(k_decode_tc_grad, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc::kSmemRequestGrad);
             cudaFuncSetAttribute(k_decode_tc<false>, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
             cudaFuncSetAttribute(k_decode_tc<true>, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
+            cudaFuncSetAttribute(k_decode_tc_grad, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
         }
-        // d sdf/dx (tracking) stays on the mma.sync kernel, whose layer-1 accumulator fragment IS the A fragment of the mask x V
-        // product; a CUDA-core gradient epilogue inside the tcgen05 kernel was measured slower (3.32 vs 2.41 ms per 4 Mi
-        // queries, 150 registers; profiles/r3g_bench.json) -- tracking batches are ~10^4 points, launch-latency bound either way
-        if (use_tc && !a->grad_x && !(a->flags & PINQ_F_MMA_SYNC)) {
+        if (use_tc && !(a->flags & PINQ_F_MMA_SYNC) && (!a->grad_x || (use_tc_grad && mode != 2))) {
             const unsigned nb128 = grid_for(n, tc::kRows);
-            const unsigned cap128 = (unsigned)sms * tc::kCtasPerSm;  // TMEM columns (and registers) per CTA bound the residency
+            // TMEM columns per CTA bound the residency (96 -> 5 CTAs; gradient flavour 128 -> 4)
+            const unsigned cap128 = (unsigned)sms * (a->grad_x ? tc::kCtasPerSmGrad : tc::kCtasPerSm);
             const unsigned g128 = nb128 < cap128 ? nb128 : cap128;
-            if (mode == 2) k_decode_tc<true><<<g128, tc::kRows, dec_smem, st>>>(p);
+            if (a->grad_x) k_decode_tc_grad<<<g128, tc::kRows, tc::kSmemRequestGrad, st>>>(p);
+            else if (mode == 2) k_decode_tc<true><<<g128, tc::kRows, dec_smem, st>>>(p);
             else k_decode_tc<false><<<g128, tc::kRows, dec_smem, st>>>(p);
         } else {
             const int occ = mode == 2 ? occ_mesh : (a->grad_x ? occ_grad : occ_plain);

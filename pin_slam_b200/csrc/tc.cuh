@@ -63,4 +63,32 @@ __device__ __forceinline__ void tmem_ld_wait(uint32_t (&v)[16]) {
                  :: "memory");
 }
 
+__device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t (&v)[16]) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
+        "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};"
+        :: "r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]), "r"(v[8]),
+           "r"(v[9]), "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15])
+        : "memory");
+}
+
+// ---- 32-bit fixed point in four balanced base-256 digits: the operand format of the tcgen05.mma.kind::i8 products ----
+// the four balanced base-256 digits of I (|I| < 2^31 - 2^23), digit p in byte p: I = sum_p (int8)byte_p 256^p
+__device__ __forceinline__ uint32_t digits_of(int I) { return ((uint32_t)I + 0x00808080u) ^ 0x00808080u; }
+// sum_p D_p 256^p of four exact digit sums (|D_p| < 2^21), recombined in fp32
+__device__ __forceinline__ float undigit(uint32_t d0, uint32_t d1, uint32_t d2, uint32_t d3) {
+    const int lo = (int)d1 * 256 + (int)d0, hi = (int)d3 * 256 + (int)d2;
+    return fmaf((float)hi, 65536.f, (float)lo);
+}
+// 2^e as a float, e in [-126, 127]
+__device__ __forceinline__ float pow2i(int e) { return __uint_as_float((uint32_t)(127 + e) << 23); }
+// floor(log2 m) for a normal m > 0, clamped to +-100 (0 and subnormals -> -100)
+__device__ __forceinline__ int floor_log2(float m) {
+    int e = (int)((__float_as_uint(m) >> 23) & 0xffu) - 127;
+    if (m == 0.f || e < -100) e = -100;
+    if (e > 100) e = 100;
+    return e;
+}
+
+
 }  // namespace tc

@@ -71,6 +71,17 @@ def test_full_size_gradient_flavour_matches_the_oracle_on_a_sample(big):
     # (a relu' bit that flips within rounding of 0 changes one query's gradient: bounded like the feature-gradient rows)
     bad, rest = row_outliers(grad[pick.cuda()], ref["grad"], tol=1e-4)
     assert int(bad.sum()) <= 4 and rest < 1e-5, (int(bad.sum()), rest)
+    # the tcgen05 gradient decode (k_decode_tc_grad: relu' bytes x W2 W1[:, 8:11] as a second, 8-bit integer UMMA) against the
+    # mma.sync kernel it replaced for tracking, on the whole batch
+    npts.use_mma_sync = True
+    try:
+        with torch.no_grad():
+            o2 = npts.query_sdf(q, dec, None, False, True, want_grad=True, want_std=True)
+    finally:
+        npts.use_mma_sync = False
+    assert torch.equal(o2["nn_count"], nn) and rel_err(o2["sdf"], sdf) < 1e-6 and rel_err(o2["std"], std) < 1e-4
+    bad2, rest2 = row_outliers(grad, o2["grad"], tol=1e-4)
+    assert int(bad2.sum()) <= N // 5000 and rest2 < 1e-5, (int(bad2.sum()), rest2)  # same rate as allowed against the oracle
 
 
 def test_full_size_backward_is_linear_in_the_upstream_gradient(big):
