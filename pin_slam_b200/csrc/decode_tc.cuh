@@ -35,8 +35,11 @@ constexpr uint32_t kTmemColsA = 32;                 // A operand: 4 k-steps of 8
 constexpr unsigned kCtasPerSm = 5;                  // 5 x 96 TMEM columns <= 512
 constexpr int kGradN = 16;                          // GRAD: mask x (W2 W1[:, 8:11]) in 4 digits -> 12 columns, padded to 16
 constexpr uint32_t kTmemColsG = 32;                 // GRAD: 16 columns of mask bytes (A operand) + 16 of s32 results
-constexpr unsigned kCtasPerSmGrad = 4;              // 4 x 128 TMEM columns
-constexpr size_t kSmemRequestGrad = 24 * 1024;      // 4 x (24 + 1) KB fill the same 100 KB configuration
+#ifndef PINQ_DEC_GRAD_CTAS
+#define PINQ_DEC_GRAD_CTAS 3
+#endif
+constexpr unsigned kCtasPerSmGrad = PINQ_DEC_GRAD_CTAS;  // 147 registers: 3 CTAs without spills beat 4 with (1.66 vs 1.75 ms per 4 Mi queries)
+constexpr size_t kSmemRequestGrad = (100 / PINQ_DEC_GRAD_CTAS - 1) * 1024;  // CTAS x (request + 1 KB) fill the same 100 KB configuration
 // Residency is capped at 5 CTAs per SM (TMEM columns) through shared memory: 5 x (19 + 1 KB) fill the 100 KB carve-out exactly
 // and a sixth CTA does not fit.  The rest of the 256 KB stays L1 for the feature-row gathers (a 40 KB request under a 100 %
 // carve-out did the same capping but left 28 KB of L1: decode 0.417 -> 0.407 ms).
