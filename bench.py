@@ -904,8 +904,10 @@ def main():
         torch.cuda.current_stream().wait_stream(back_stream)
         barrier()
         ev0.record()
+        t_host = time.perf_counter()
         for _ in range(args.steps):
             e2e_step()
+        t_host = (time.perf_counter() - t_host) / args.steps * 1e3  # host time to ENQUEUE a step (the GPU runs behind it)
         torch.cuda.current_stream().wait_stream(back_stream)
         ev1.record()
         barrier()
@@ -914,7 +916,7 @@ def main():
             dist.all_reduce(te, op=dist.ReduceOp.MAX)
         e2e = {"value": world * n / (float(te.item()) / args.steps * 1e-3), "unit": UNIT, "chunks": nchunk, "steps_pipelined": pipelined,
                "h2d_bytes_per_step": n * 12 + n * 4, "d2h_bytes_per_step": n * 4,
-               "copies_alone_ms_per_step": copy_ms, "copies_alone_gbs_per_gpu": (n * 20) / (copy_ms * 1e-3) / 1e9,
+               "host_enqueue_ms_per_step": t_host, "copies_alone_ms_per_step": copy_ms, "copies_alone_gbs_per_gpu": (n * 20) / (copy_ms * 1e-3) / 1e9,
                "host_binding": host_binding}
 
     cpu_baseline = cuda_eager = None

@@ -37,13 +37,12 @@ constexpr uint32_t kTmemCols = 128;         // D1 buffers at columns 0 and 32, D
 #define PINQ_BWD_CTAS 4
 #endif
 constexpr unsigned kCtasPerSm = PINQ_BWD_CTAS;  // 4 x 128 TMEM columns = all 512
-constexpr size_t kSmemRequest = 36 * 1024;
+constexpr size_t kSmemRequest = 31 * 1024;     // 4 x (31 + 1) KB fit the 132 KB configuration: 32 KB more L1 than the next one
 
 struct Smem {  // the tiles are double-buffered: tile t + 1 is staged while the MMAs of tile t run
     alignas(128) unsigned char x[2][kXChunks * kChunk];
     alignas(128) unsigned char mask[2][kMaskChunks * kChunk];
     alignas(128) unsigned char v4[kMaskChunks * kVN * 16];  // [hidden chunk][n] x 16 bytes
-    float gacc[12][H];                                      // flushed G sums, [input][mask column]
     float vscale[8];                                        // 2^-s of feature column c
     alignas(8) unsigned long long bar[2];
     uint32_t tmem_base;
@@ -113,7 +112,6 @@ __global__ void __launch_bounds__(tcb::kRows) k_bwd_tc(const BwdParams p) {
         }
     }
     if (DEC) {
-        for (int e = tid; e < H * 12; e += kRows) (&S.gacc[0][0])[e] = 0.f;
         if (tid == 0) S.db2 = 0.f;
     }
     if (tid == 0) {
@@ -212,6 +210,9 @@ __global__ void __launch_bounds__(tcb::kRows) k_bwd_tc(const BwdParams p) {
     };
     // G of a finished block (all its MMAs waited for) -> fp32 sums.  M = 64 accumulator layout: hidden row m sits in
     // TMEM lane (m % 16) + 32 (m / 16), i.e. lanes 0..15 of every warp (cute/atom/mma_traits_sm100.hpp, 1SM M_MMA == 64)
+    float gacc[12];  // flushed G sums of hidden row 16 warp + lane (lanes 0..15), one per decoder input
+#pragma unroll
+    for (int i = 0; i < 12; ++i) gacc[i] = 0.f;
     auto flush = [&](float inv_scale) {
         if (DEC) {
 #pragma unroll
@@ -219,12 +220,9 @@ __global__ void __launch_bounds__(tcb::kRows) k_bwd_tc(const BwdParams p) {
                 uint32_t v[16];
                 tmem_ld16(tmem_row + kD2 + 16 * c3, v);
                 tmem_ld_wait(v);
-                if (lane < 16) {
 #pragma unroll
-                    for (int u = 0; u < 4; ++u)
-                        S.gacc[4 * c3 + u][16 * warp + lane] +=
-                            undigit(v[4 * u], v[4 * u + 1], v[4 * u + 2], v[4 * u + 3]) * inv_scale;
-                }
+                for (int u = 0; u < 4; ++u)  // (meaningful in lanes 0..15: hidden row 16 warp + lane)
+                    gacc[4 * c3 + u] += undigit(v[4 * u], v[4 * u + 1], v[4 * u + 2], v[4 * u + 3]) * inv_scale;
             }
             tc_fence_before();
         }
@@ -353,9 +351,10 @@ __global__ void __launch_bounds__(tcb::kRows) k_bwd_tc(const BwdParams p) {
     __syncthreads();
     if (DEC) {  // G[j][i]; then dW1 = W2 G, db1 = W2 G[:,11], dW2[j] = W1b[j] . G[j], db2
         float* sG = reinterpret_cast<float*>(S.mask[0]);  // [H][12], the tiles are idle now
-        for (int e = tid; e < H * 12; e += kRows) {
-            const int c = e / 12, i = e - 12 * c, j = hidden_of_maskcol(c);
-            sG[j * 12 + i] = S.gacc[i][c];
+        if (lane < 16) {
+            const int j = hidden_of_maskcol(16 * warp + lane);
+#pragma unroll
+            for (int i = 0; i < 12; ++i) sG[j * 12 + i] = gacc[i];
         }
         __syncthreads();
         for (int e = tid; e < H * 12; e += kRows) {

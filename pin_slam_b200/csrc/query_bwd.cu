@@ -269,9 +269,9 @@ extern "C" int pinq_query_fused_bwd(const pinq_bwd_args* a, void* stream) {
         cudaFuncSetAttribute(k_bwd_tc<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tcb::kSmemRequest);
         cudaFuncSetAttribute(k_bwd_tc<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tcb::kSmemRequest);
         const char* ce = getenv("PINQ_BWD_CARVEOUT");
-        // 4 CTAs x (36 + 1 KB) of shared memory; the rest of the 256 KB stays L1 for the stage blocks, relu' masks and feature
+        // 4 CTAs x (31 + 1 KB) of shared memory; the rest of the 256 KB stays L1 for the stage blocks, relu' masks and feature
         // rows the tiles are built from (100 % carve-out: 0.594 ms, 66 %: 0.475 ms per 4 Mi queries)
-        const int carve = ce ? atoi(ce) : 66;
+        const int carve = ce ? atoi(ce) : (int)((tcb::kCtasPerSm * (tcb::kSmemRequest + 1024) * 100 + 232448 - 1) / 232448);
         cudaFuncSetAttribute(k_bwd_tc<true, true>, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
         cudaFuncSetAttribute(k_bwd_tc<true, false>, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
         cudaFuncSetAttribute(k_bwd_tc<false, true>, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
