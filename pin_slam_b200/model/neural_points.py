@@ -714,7 +714,13 @@ class _FusedSDFFn(torch.autograd.Function):
             if d_sink is not None:
                 b.grad_W1, b.grad_b1, b.grad_W2, b.grad_b2 = (P.ptr(t) for t in d_sink)
             else:
-                gW1, gb1, gW2, gb2 = (torch.zeros_like(t) for t in (W1, b1, W2, b2))
+                # one zero-filled buffer (one memset launch instead of four), the four gradients are views of it
+                sizes = [t.numel() for t in (W1, b1, W2, b2)]
+                offs = [0]
+                for sz in sizes:
+                    offs.append(offs[-1] + ((sz + 3) // 4) * 4)  # 16-byte aligned starts
+                flat = torch.zeros(offs[-1], dtype=W1.dtype, device=W1.device)
+                gW1, gb1, gW2, gb2 = (flat[o:o + sz].view(t.shape) for o, sz, t in zip(offs, sizes, (W1, b1, W2, b2)))
                 b.grad_W1, b.grad_b1, b.grad_W2, b.grad_b2 = P.ptr(gW1), P.ptr(gb1), P.ptr(gW2), P.ptr(gb2)
         P.check(lib.pinq_query_fused_bwd(b, P.stream()))
         g_x = g.unsqueeze(-1) * dx if ctx.needs_input_grad[2] else None
