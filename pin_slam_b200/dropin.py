@@ -4,10 +4,13 @@
 
 aliases the five hot-path modules the reference driver imports (pin_slam.py:13-25) --
 `model.neural_points`, `model.decoder`, `utils.tracker`, `utils.mapper`, `utils.mesher` -- to the mirrors in
-this package.  Everything else (`utils.config`, `utils.tools`, `dataset.*`, `utils.pgo`, ...) keeps coming
-from the reference tree on PYTHONPATH.
+this package, and rebinds four per-frame helpers inside the reference's own `utils.tools` (voxel down-sampling x 2,
+deskewing, transform_torch: what `dataset/slam_dataset.py` calls in `preprocess_frame`) to their kernel-backed mirrors.
+Everything else (`utils.config`, the rest of `utils.tools`, `dataset.*`, `utils.pgo`, ...) keeps coming from the
+reference tree on PYTHONPATH.
 """
 import importlib
+import os
 import sys
 
 HOT_PATH_MODULES = {
@@ -19,9 +22,49 @@ HOT_PATH_MODULES = {
 }
 
 
-def install():
+# functions of the reference's utils/tools.py that its own dataset code calls per frame (dataset/slam_dataset.py:260-374) and
+# that have a kernel-backed, golden-pinned mirror in pin_slam_b200/utils/tools.py
+TOOLS_FUNCTIONS = ("voxel_down_sample_torch", "voxel_down_sample_min_value_torch", "deskewing", "transform_torch")
+
+
+def _patch_reference_tools():
+    """Rebind the four per-frame helpers inside the reference's OWN `utils.tools` module (everything else in it stays the
+    reference's), so that `from utils.tools import ...` in dataset/slam_dataset.py picks the kernels up.  Each adapter keeps
+    the reference function for inputs the kernels do not take (CPU tensors, other dtypes)."""
+    try:
+        ref_tools = importlib.import_module("utils.tools")
+    except Exception:  # the reference tree is not on sys.path (or its own imports are missing): nothing to patch
+        return []
+    import torch
+    from pin_slam_b200.utils import tools as mine
+
+    def adapter(name):
+        ref_fn, my_fn = getattr(ref_tools, name), getattr(mine, name)
+
+        def call(points, *args, **kwargs):
+            if not (torch.is_tensor(points) and points.is_cuda and points.dtype == torch.float32 and points.dim() == 2
+                    and points.shape[0] > 0):
+                return ref_fn(points, *args, **kwargs)
+            if name == "deskewing":
+                if args and args[0] is None:
+                    return points
+                points = points.contiguous()  # in place on a contiguous cloud; the caller rebinds the result (slam_dataset.py:338, 362)
+            return my_fn(points, *args, **kwargs)
+
+        call.__name__, call.__doc__ = name, my_fn.__doc__
+        call.reference_function = ref_fn
+        return call
+
+    for name in TOOLS_FUNCTIONS:
+        if not hasattr(getattr(ref_tools, name), "reference_function"):
+            setattr(ref_tools, name, adapter(name))
+    return ["utils.tools." + n for n in TOOLS_FUNCTIONS]
+
+
+def install(patch_tools: bool = True):
     for ref_name, mine in HOT_PATH_MODULES.items():
         sys.modules[ref_name] = importlib.import_module(mine)
+    patched = _patch_reference_tools() if patch_tools and os.environ.get("PINQ_DROPIN_TOOLS", "1") != "0" else []
     # The mirrors never call cuBLAS; the reference's own preprocessing does (deskewing: a batched 3x3 matmul,
     # utils/tools.py:564).  Create the library handles now instead of inside the second frame's timed preprocessing
     # stage (measured: 115 ms in frame 1 of the unchanged driver).
@@ -30,4 +73,4 @@ def install():
         a = torch.eye(3, device="cuda").expand(4, 3, 3)
         torch.matmul(a, a)
         torch.cuda.synchronize()
-    return sorted(HOT_PATH_MODULES)
+    return sorted(HOT_PATH_MODULES) + patched
