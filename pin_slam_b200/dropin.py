@@ -72,5 +72,13 @@ def install(patch_tools: bool = True):
     if torch.cuda.is_available():
         a = torch.eye(3, device="cuda").expand(4, 3, 3)
         torch.matmul(a, a)
+        if patched:  # first use of a kernel loads its module: do that here, not inside the first frames' preprocessing stage
+            from pin_slam_b200.utils import tools as mine
+            pts = torch.rand((4096, 4), device="cuda")
+            ts = torch.rand((4096, 1), device="cuda")
+            mine.voxel_down_sample_torch(pts[:, :3], 0.05)
+            mine.voxel_down_sample_min_value_torch(pts[:, :3], 0.05, ts.squeeze(-1))
+            mine.deskewing(pts, ts, torch.eye(4, device="cuda", dtype=torch.float64))
+            mine.transform_torch(pts[:, :3], torch.eye(4, device="cuda", dtype=torch.float64))
         torch.cuda.synchronize()
     return sorted(HOT_PATH_MODULES) + patched
