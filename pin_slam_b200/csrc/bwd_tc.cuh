@@ -15,7 +15,8 @@
 // column; the tensor core's integer sums are EXACT and the digits are recombined in fp32 after the sum:
 //   V (= W2 W1, per feature column c): 2^s chosen per column from max_j |V_jc|  ->  |quantisation| <= 2^-31 max|V_c| per term
 //   X (= 2^s a_k [f_k, v_k, 1]):       2^s per block of 6 tiles from the block's largest |dL/dsdf| (the weights are <= 1 and
-//       the decoder inputs are assumed < 2^8 as before: the conversion saturates beyond) -> |quantisation| <= 2^-23 max|a| per
+//       the decoder inputs are assumed < 2^8, as the fp16 tiles assumed before: a larger input overflows the 32-bit fixed
+//       point and the gradients of that block are wrong) -> |quantisation| <= 2^-23 max|a| per
 //       element, against the 2^-24 |partial sum| an fp32 accumulation of the same rows commits per addition.
 // D1 -> thread-local epilogue: dL/df_k = a_k (digits recombined) 2^-s_c -> red.global.add.v4.f32 x 2 into grad_features[idx_k].
 // D2 is flushed into fp32 shared-memory sums once per block of 6 tiles (768 rows) with the block's 2^-s, so the long
@@ -228,7 +229,7 @@ __global__ void __launch_bounds__(tcb::kRows) k_bwd_tc(const BwdParams p) {
         }
     };
     // Power-of-two scale of a block's X tiles: 2^s with 2^s * scale * max_rows |dL/dsdf| in [2^21, 2^22) -- |w_k| <= 1 and the
-    // decoder inputs are below 2^8, so the fixed-point values stay below 2^30 (the conversion saturates otherwise).  Each warp
+    // decoder inputs are below 2^8, so the fixed-point values stay below 2^30.  Each warp
     // publishes its max one block ahead (the value arrives with the block's index loads).
     auto publish_max = [&](float g, int parity) {
         float m = fabsf(g);

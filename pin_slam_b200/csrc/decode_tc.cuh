@@ -14,10 +14,15 @@
 //              [lo(f0..7)] x [hi W]   [hi(f0..7)] x [lo W]   [lo(v,0) | hi(v,1)] x [hi W ; lo W]
 //              [hi(f0..7)] x [hi W]   [hi(v,1) | 0] x [hi W ; -]          then tcgen05.commit -> mbarrier
 //           `hi` is the raw fp32 word (the tensor core ignores the low 13 mantissa bits), lo = x - trunc(x) is exact
-//   epilog  tcgen05.ld 32x32b: 64 pre-activations of the thread's row; relu . W2 with W2 broadcast from shared memory;
-//           relu' bits collected from the SIGN of the pre-activation with one funnel shift per element
+//   epilog  tcgen05.ld 32x32b: 64 pre-activations x_j of the thread's row.  relu(x) W2 = |x| W2/2 + x W2/2: the first half is
+//           one FFMA per element (|x| as operand modifier, W2/2 broadcast from shared memory), the second is linear in the
+//           decoder inputs and added once per tile (in . u, u = sum_j W2_j/2 [W1 | b1]_j, 12 FFMAs at staging time); relu'
+//           bits collected from the SIGN of the pre-activation with one funnel shift per element -- 2 instructions per
+//           element, one on the FMA pipe and one on the (half-rate) ALU pipe
+//   grad    (k_decode_tc_grad, the tracker's flavour) the relu' bits, expanded to bytes in 16 more TMEM columns, are the A
+//           operand of a second product (tcgen05.mma.kind::i8) against W2 W1[:, 8:11] in 32-bit fixed point: d s_k / d v_k
 // 96 TMEM columns per CTA (64 accumulator + 32 A) -> 5 CTAs per SM; the other CTAs' work hides the MMA latency
-// (single-buffered tiles measured as fast as double-buffered ones at 4 CTAs).
+// (single-buffered tiles measured as fast as double-buffered ones at 4 CTAs).  Gradient flavour: 128 columns, 3 CTAs.
 //
 // Deviation (documented in DESIGN.md): relu'(+0.0) is taken as 1 (torch: 0); reachable only when a hidden
 // pre-activation is exactly +0.0.
