@@ -486,7 +486,8 @@ def mapping_leg(dev, world, rank, iters=15, batch=1 << 20, pool_n=8_000_000):
     peer = None
     rows, fdim = npts.local_geo_features.shape
     if world > 1:
-        peer = PeerExchange(MappingPeer.capacity(rows, fdim, dec, with_params=True), dev, grid=int(os.environ.get("PINQ_MAP_PEER_GRID", "48")))
+        peer = PeerExchange(MappingPeer.capacity(rows, fdim, dec, with_params=True), dev, grid=int(os.environ.get("PINQ_MAP_PEER_GRID", "48")),
+                            threads=int(os.environ.get("PINQ_MAP_PEER_THREADS", "0")))
         torch.cuda.synchronize()
         dist.barrier()
         mapper.dp = DataParallelMapping(peer)
@@ -638,7 +639,7 @@ def main():
             # flight, which is what the links need (measured at N = 2: 148 / 64 / 32 CTAs -> 2.131 / 2.088 / 2.078 ms per step)
             ov = os.environ.get("PINQ_EXCHANGE_OVERLAP", "1") != "0"
             peer = PeerExchange(MappingPeer.capacity(rows, fdim, dec), dev, grid=int(os.environ.get("PINQ_PEER_GRID", "32" if ov else "0")),
-                                cooperative=not ov)
+                                cooperative=not ov, threads=int(os.environ.get("PINQ_PEER_THREADS", "0")))
             carve = MappingPeer(peer, rows, fdim, dec)
             n_ex = carve.n_sum - (rows - 1)  # features + decoder (the certainty increments are not part of this step)
             npts.feature_grad_sink, dec.grad_sink = carve.grad_features, tuple(carve.grad_decoder)

@@ -459,6 +459,10 @@ typedef struct pinq_peer_args {
                                 * (needed as soon as anything else may share the device, e.g. the next step's search
                                 * on another stream); 0: plain launch, the caller vouches for co-residency (several
                                 * simulated ranks in ONE process must use 0: their kernels wait for each other)     */
+    int32_t threads;           /* threads per CTA, identical on every rank: 0 / 512 = stand-alone form; 128 = the form
+                                * for an exchange that runs UNDER another kernel (plain launch on a side stream): CTAs of
+                                * 128 threads x <= 56 registers fit into what ONE retiring CTA of the neighbour search
+                                * frees, a 512-thread CTA needs a completely drained SM                               */
 } pinq_peer_args;
 int pinq_peer_exchange(const pinq_peer_args* args, void* stream);
 

@@ -12,6 +12,7 @@
 //   [ signal pad: PINQ_PEER_PAD_BYTES ][ payload ... ]
 // pad: uint32 flag[PINQ_PEER_MAX_GRID][8] (flag[b][r] = last phase value rank r's CTA b signalled), then an error word.
 #include <math.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "common.cuh"
@@ -19,6 +20,11 @@
 namespace pinq {
 
 constexpr int kPeerThreads = 512;
+// default of PINQ_PEER_CARVEOUT; -1 = leave the driver's choice
+#ifndef PINQ_PEER_CARVEOUT_PCT
+#define PINQ_PEER_CARVEOUT_PCT -1
+#endif
+constexpr int kPeerCarveoutPct = PINQ_PEER_CARVEOUT_PCT;
 constexpr int kPadErrWord = PINQ_PEER_MAX_GRID * 8;  // uint32 index of the error word in the pad
 
 struct PeerDev {
@@ -63,33 +69,49 @@ __device__ __forceinline__ void peer_barrier(const PeerDev& a, uint32_t value) {
     __syncthreads();
 }
 
-template <int W, bool ADAM>
-__global__ void __launch_bounds__(kPeerThreads) k_peer_exchange(PeerDev a) {
+// T = threads per CTA.  512 (one CTA fills most of an SM's registers) is the stand-alone form.  128 with at most 56 registers
+// is the form that runs UNDER another kernel: one of its CTAs fits into exactly the registers ONE retiring CTA of the
+// neighbour search (128 threads x 56 registers, 9 per SM) leaves behind, so the exchange gets onto the SMs as soon as
+// the first search CTAs retire instead of waiting for an SM that has drained completely.
+template <int W, bool ADAM, int T>
+__global__ void __launch_bounds__(T, T == 128 ? 9 : 1) k_peer_exchange(PeerDev a) {
     peer_barrier(a, a.phase);  // every rank's backward has finished writing its gradient block
 
-    const int64_t tid = (int64_t)blockIdx.x * kPeerThreads + threadIdx.x;
-    const int64_t nthr = (int64_t)gridDim.x * kPeerThreads;
+    const int64_t tid = (int64_t)blockIdx.x * T + threadIdx.x;
+    const int64_t nthr = (int64_t)gridDim.x * T;
     {   // fp32 sum region: this rank owns float4 [lo, hi).  U elements per thread and trip, all W x U loads issued before the
         // first add: the link wants megabytes in flight (latency ~2 us x 0.8 TB/s), not one 16-byte load per thread.
-        constexpr int U = W >= 8 ? 2 : (W == 4 ? 4 : 8);
+        // (T = 128: four 16-byte loads in flight per thread -- 56 registers without spills; the grid is 4 x larger instead)
+        constexpr int U = T == 128 ? (W >= 4 ? 1 : 4 / W) : (W >= 8 ? 2 : (W == 4 ? 4 : 8));
+        constexpr int PC = (T == 128 && W > 4) ? 4 : W;  // ranks loaded per round
         const int64_t lo = a.nsum4 * a.rank / W, hi = a.nsum4 * (a.rank + 1) / W;
         for (int64_t i0 = lo + tid; i0 < hi; i0 += nthr * U) {
-            float4 v[U][W];
+            float4 acc[U];
 #pragma unroll
-            for (int u = 0; u < U; ++u) {
-                const int64_t i = i0 + u * nthr;
-                if (i < hi) {
+            for (int p0 = 0; p0 < W; p0 += PC) {
+                float4 v[U][PC];
 #pragma unroll
-                    for (int p = 0; p < W; ++p) v[u][p] = __ldcg(reinterpret_cast<const float4*>(a.block[p]) + a.sum_off4 + i);
+                for (int u = 0; u < U; ++u) {
+                    const int64_t i = i0 + u * nthr;
+                    if (i < hi) {
+#pragma unroll
+                        for (int p = 0; p < PC; ++p)
+                            v[u][p] = __ldcg(reinterpret_cast<const float4*>(a.block[p0 + p]) + a.sum_off4 + i);
+                    }
+                }
+#pragma unroll
+                for (int u = 0; u < U; ++u) {  // fixed rank order 0, 1, ..., W - 1: the sum does not depend on which rank owns the slice
+                    float4 s = p0 == 0 ? v[u][0] : acc[u];
+#pragma unroll
+                    for (int p = (p0 == 0 ? 1 : 0); p < PC; ++p) { s.x += v[u][p].x; s.y += v[u][p].y; s.z += v[u][p].z; s.w += v[u][p].w; }
+                    acc[u] = s;
                 }
             }
 #pragma unroll
             for (int u = 0; u < U; ++u) {
                 const int64_t i = i0 + u * nthr;
                 if (i >= hi) break;
-                float4 s = v[u][0];  // fixed rank order: the sum does not depend on which rank owns the slice
-#pragma unroll
-                for (int p = 1; p < W; ++p) { s.x += v[u][p].x; s.y += v[u][p].y; s.z += v[u][p].z; s.w += v[u][p].w; }
+                const float4 s = acc[u];
                 if (ADAM && i < a.nadam4) {
                     // torch.optim.Adam single-tensor arithmetic (k_adam, gn.cu) on the owned slice; state lives on the owner only
                     float4 m = reinterpret_cast<float4*>(a.exp_avg)[i], q = reinterpret_cast<float4*>(a.exp_avg_sq)[i];
@@ -149,17 +171,36 @@ __global__ void __launch_bounds__(kPeerThreads) k_peer_exchange(PeerDev a) {
 // Cooperative launch: the flag barrier needs every CTA of the grid resident at the same time on every rank.  A plain
 // launch only has that by luck when another kernel shares the device (e.g. the next step's search on another stream);
 // cudaLaunchCooperativeKernel makes it a launch-time guarantee (or a launch error) instead of a barrier timeout.
-template <int W>
-static cudaError_t launch_peer(PeerDev& d, bool adam, bool cooperative, int grid, cudaStream_t st) {
+template <int W, int T>
+static cudaError_t launch_peer_t(PeerDev& d, bool adam, bool cooperative, int grid, cudaStream_t st) {
+    static bool configured = false;
+    if (!configured) {  // PINQ_PEER_CARVEOUT: shared-memory carve-out (percent) the exchange asks for; -1 = the driver's choice
+        configured = true;
+        const char* ce = getenv("PINQ_PEER_CARVEOUT");
+        const int carve = ce ? atoi(ce) : kPeerCarveoutPct;
+        if (carve >= 0) {
+            cudaFuncSetAttribute(k_peer_exchange<W, true, T>, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
+            cudaFuncSetAttribute(k_peer_exchange<W, false, T>, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
+        }
+    }
     if (!cooperative) {  // several simulated ranks in one process: their kernels wait for each other, the caller vouches
-        if (adam) k_peer_exchange<W, true><<<grid, kPeerThreads, 0, st>>>(d);
-        else k_peer_exchange<W, false><<<grid, kPeerThreads, 0, st>>>(d);
+        if (adam) k_peer_exchange<W, true, T><<<grid, T, 0, st>>>(d);
+        else k_peer_exchange<W, false, T><<<grid, T, 0, st>>>(d);
         return cudaGetLastError();
     }
     void* args[] = {&d};
-    const void* fn = adam ? reinterpret_cast<const void*>(&k_peer_exchange<W, true>)
-                          : reinterpret_cast<const void*>(&k_peer_exchange<W, false>);
-    return cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(kPeerThreads), args, 0, st);
+    const void* fn = adam ? reinterpret_cast<const void*>(&k_peer_exchange<W, true, T>)
+                          : reinterpret_cast<const void*>(&k_peer_exchange<W, false, T>);
+    return cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(T), args, 0, st);
+}
+
+// Cooperative launch: the flag barrier needs every CTA of the grid resident at the same time on every rank.  A plain
+// launch only has that by luck when another kernel shares the device (e.g. the next step's search on another stream);
+// cudaLaunchCooperativeKernel makes it a launch-time guarantee (or a launch error) instead of a barrier timeout.
+template <int W>
+static cudaError_t launch_peer(PeerDev& d, bool adam, bool cooperative, int grid, int threads, cudaStream_t st) {
+    return threads == 128 ? launch_peer_t<W, 128>(d, adam, cooperative, grid, st)
+                          : launch_peer_t<W, kPeerThreads>(d, adam, cooperative, grid, st);
 }
 
 }  // namespace pinq
@@ -235,6 +276,7 @@ int pinq_peer_exchange(const pinq_peer_args* a, void* stream) {
     }
     int grid = a->grid > 0 ? a->grid : 148;  // one CTA per SM, launched cooperatively: co-residency is guaranteed
     PINQ_REQUIRE(grid <= PINQ_PEER_MAX_GRID, "grid too large for the signal pad");
+    PINQ_REQUIRE(a->threads == 0 || a->threads == 128 || a->threads == kPeerThreads, "threads: 0 (= 512), 128 or 512");
     PeerDev d{};
     for (int p = 0; p < a->world; ++p) d.block[p] = reinterpret_cast<float*>(a->block[p]);
     d.rank = a->rank;
@@ -262,10 +304,10 @@ int pinq_peer_exchange(const pinq_peer_args* a, void* stream) {
     cudaStream_t st = as_stream(stream);
     cudaError_t le;
     switch (a->world) {
-        case 1: le = launch_peer<1>(d, adam, a->cooperative != 0, grid, st); break;
-        case 2: le = launch_peer<2>(d, adam, a->cooperative != 0, grid, st); break;
-        case 4: le = launch_peer<4>(d, adam, a->cooperative != 0, grid, st); break;
-        default: le = launch_peer<8>(d, adam, a->cooperative != 0, grid, st); break;
+        case 1: le = launch_peer<1>(d, adam, a->cooperative != 0, grid, a->threads, st); break;
+        case 2: le = launch_peer<2>(d, adam, a->cooperative != 0, grid, a->threads, st); break;
+        case 4: le = launch_peer<4>(d, adam, a->cooperative != 0, grid, a->threads, st); break;
+        default: le = launch_peer<8>(d, adam, a->cooperative != 0, grid, a->threads, st); break;
     }
     if (le != cudaSuccess) {
         set_error("pinq_peer_exchange: %slaunch of %d CTAs failed: %s", a->cooperative ? "cooperative " : "", grid, cudaGetErrorString(le));

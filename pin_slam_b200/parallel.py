@@ -171,7 +171,7 @@ class PeerExchange:
     streams: the single-GPU form used by the GPU tests (same kernel, same flags, same P2P code path minus the link)."""
 
     def __init__(self, layout: PeerLayout, device, group=None, simulate_world: int = 0, grid: int = 0, timeout_ms: float = 0.0,
-                 cooperative: bool = True):
+                 cooperative: bool = True, threads: int = 0):
         import ctypes as C
         from . import _pinq as P
         self.P, self.lib, self.layout, self.device = P, P.load(), layout, torch.device(device)
@@ -182,6 +182,9 @@ class PeerExchange:
         # for a completely free GPU, i.e. behind that search, while a plain launch lets its CTAs take SM slots as they free up
         # (they spin at the flag barrier until the rest arrive, which they do because the other kernel finishes regardless).
         self.cooperative = bool(cooperative)
+        # threads per CTA (0 = 512).  An overlapped exchange wants 128: such a CTA fits into the registers one retiring CTA of the
+        # neighbour search frees, a 512-thread CTA (100-128 registers per thread) has to wait for an SM that drained completely
+        self.threads = int(threads)
         # a rank that does not arrive within this bound makes the kernel give up and set the block's error word
         self.timeout_ms = float(timeout_ms) if timeout_ms else float(os.environ.get("PINQ_PEER_TIMEOUT_MS", "0"))
         self.simulated = simulate_world > 0
@@ -257,7 +260,7 @@ class PeerExchange:
         for r, b in enumerate(self.blocks):
             a.block[r] = b
         a.sum_off, a.n_sum, a.max_off, a.n_max = L.sum_off + 4 * sum_off_elems, n_sum, L.max_off, n_max
-        a.epoch, a.grid, a.timeout_ms = epoch, self.grid, self.timeout_ms
+        a.epoch, a.grid, a.timeout_ms, a.threads = epoch, self.grid, self.timeout_ms, self.threads
         a.cooperative = 0 if (self.simulated or not self.cooperative) else 1  # simulated ranks share one device and wait for each other
         if adam is not None:
             adam = dict(adam)

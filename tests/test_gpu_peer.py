@@ -10,15 +10,17 @@ from helpers import build_cuda_map, decoder_pair, frames_of_points, make_queries
 pytestmark = pytest.mark.gpu
 
 
-def _peer(world, n_sum, n_max=0, n_param=0, grid=16):
+def _peer(world, n_sum, n_max=0, n_param=0, grid=16, threads=0):
     from pin_slam_b200.parallel import PeerExchange, PeerLayout
-    return PeerExchange(PeerLayout(n_sum, n_max, n_param), "cuda:0", simulate_world=world, grid=grid, timeout_ms=2000.0)
+    return PeerExchange(PeerLayout(n_sum, n_max, n_param), "cuda:0", simulate_world=world, grid=grid, timeout_ms=2000.0,
+                        threads=threads)
 
 
+@pytest.mark.parametrize("threads", [0, 128])  # 512-thread CTAs (stand-alone form) / 128-thread CTAs (overlapped form)
 @pytest.mark.parametrize("world", [1, 2, 4, 8])
 @pytest.mark.parametrize("n_sum,n_max", [(4, 2), (1000, 0), (262144 + 12, 4098), (3_000_000, 300_000)])
-def test_allreduce_sum_and_max_bit_exact(world, n_sum, n_max):
-    peer = _peer(world, n_sum, n_max, grid=8 if world == 8 else 16)
+def test_allreduce_sum_and_max_bit_exact(world, n_sum, n_max, threads):
+    peer = _peer(world, n_sum, n_max, grid=(8 if world == 8 else 16) * (4 if threads == 128 else 1), threads=threads)
     try:
         g = torch.Generator(device="cuda").manual_seed(world * 7 + n_sum)
         ins = [torch.randn(peer.layout.n_sum, device="cuda", generator=g) for _ in range(world)]
@@ -56,10 +58,11 @@ def test_prefix_exchange_leaves_the_rest_alone():
         peer.close()
 
 
+@pytest.mark.parametrize("threads", [0, 128])
 @pytest.mark.parametrize("world", [2, 4])
-def test_fused_adam_matches_torch_adam(world):
+def test_fused_adam_matches_torch_adam(world, threads):
     n_par, n_extra = 40000, 1000
-    peer = _peer(world, n_par + n_extra, 0, n_par)
+    peer = _peer(world, n_par + n_extra, 0, n_par, threads=threads)
     try:
         g = torch.Generator(device="cuda").manual_seed(11)
         p0 = torch.randn(n_par, device="cuda", generator=g)
