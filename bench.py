@@ -664,6 +664,8 @@ def main():
     if overlap:
         ev_x.record(torch.cuda.current_stream())
 
+    delay_cycles = int(os.environ.get("PINQ_EXCHANGE_DELAY_CYCLES", "0"))
+
     def exchange_grads():
         if skip_exchange[0]:
             return
@@ -684,6 +686,8 @@ def main():
             ev_bwd.record(main)
             with torch.cuda.stream(side):
                 side.wait_event(ev_bwd)
+                if delay_cycles:
+                    torch.cuda._sleep(delay_cycles)
                 peer.exchange(n_sum=n_ex, n_max=0)
                 grad_block.zero_()
                 ev_x.record(side)
@@ -746,6 +750,46 @@ def main():
         dist.all_reduce(tn, op=dist.ReduceOp.MAX)
         no_exchange_ms = float(tn.item())
         skip_exchange[0] = False
+
+    # ---- timeline of the overlapped step (PINQ_TRACE_OVERLAP=1): where the exchange sits under the next forward
+    overlap_trace = None
+    if overlap and os.environ.get("PINQ_TRACE_OVERLAP", "0") != "0":
+        main = torch.cuda.current_stream()
+        E = lambda: torch.cuda.Event(enable_timing=True)
+        rec = []
+        barrier()
+        for i in range(12):
+            e = {k: E() for k in ("q0", "q1", "b", "xs", "xe", "z")}
+            e["q0"].record(main)
+            npts.decode_wait_event = ev_x
+            out = npts.query_sdf(q, dec, ts, True, True)
+            npts.decode_wait_event = None
+            e["q1"].record(main)
+            out["sdf"].backward(ones)
+            e["b"].record(main)
+            ev_bwd.record(main)
+            with torch.cuda.stream(side):
+                side.wait_event(ev_bwd)
+                e["xs"].record(side)
+                peer.exchange(n_sum=n_ex, n_max=0)
+                e["xe"].record(side)
+                grad_block.zero_()
+                e["z"].record(side)
+                ev_x.record(side)
+            rec.append(e)
+        drain()
+        barrier()
+        med = lambda v: float(sorted(v)[len(v) // 2])
+        r = rec[2:]
+        overlap_trace = {
+            "forward_ms": med([e["q0"].elapsed_time(e["q1"]) for e in r]),
+            "backward_ms": med([e["q1"].elapsed_time(e["b"]) for e in r]),
+            "exchange_under_search_ms": med([e["xs"].elapsed_time(e["xe"]) for e in r]),
+            "zero_ms": med([e["xe"].elapsed_time(e["z"]) for e in r]),
+            "backward_end_to_exchange_start_ms": med([e["b"].elapsed_time(e["xs"]) for e in r]),
+            "exchange_end_to_next_forward_end_ms": med([rec[i]["z"].elapsed_time(rec[i + 1]["q1"]) for i in range(2, len(rec) - 1)]),
+            "step_ms": med([rec[i]["q0"].elapsed_time(rec[i + 1]["q0"]) for i in range(2, len(rec) - 1)]),
+        }
 
     # ---- the exchange step alone (N > 1): zeroed gradient block -> summed block, max over ranks
     exchange_ms = None
@@ -982,6 +1026,8 @@ def main():
             line["gpu_launches"] += args.steps
             line["peer_exchange_error"] = peer_err
             line["exchange_overlapped_with_next_search"] = bool(overlap)
+            if overlap_trace:
+                line["overlap_trace"] = overlap_trace
         if exchange_ms is not None:
             line["exchange_ms"] = exchange_ms
             line["ms_per_step_by_rank"] = rank_ms

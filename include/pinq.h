@@ -463,6 +463,12 @@ typedef struct pinq_peer_args {
                                 * for an exchange that runs UNDER another kernel (plain launch on a side stream): CTAs of
                                 * 128 threads x <= 56 registers fit into what ONE retiring CTA of the neighbour search
                                 * frees, a 512-thread CTA needs a completely drained SM                               */
+    void* mc_block;            /* NULL, or the NVLS multicast address of the peer blocks (one address that reaches the
+                                * block of EVERY rank through NVSwitch; the blocks must then be allocations bound to one
+                                * multicast object, e.g. torch.distributed._symmetric_memory): the fp32 sum region is
+                                * reduced with multimem.ld_reduce and broadcast with multimem.st -- 2 memory
+                                * instructions per 16 bytes of the owned slice instead of 2 x world; the sum is then the
+                                * switch's order, not rank order.  Flags and the int64 max region keep using block[] */
 } pinq_peer_args;
 int pinq_peer_exchange(const pinq_peer_args* args, void* stream);
 

@@ -71,7 +71,7 @@ class PeerArgs(C.Structure):
     _fields_ = [("rank", _i32), ("world", _i32), ("block", _vp * PEER_MAX), ("sum_off", _i64), ("n_sum", _i64),
                 ("max_off", _i64), ("n_max", _i64), ("epoch", _u32), ("grid", _i32), ("timeout_ms", _f32),
                 ("param_off", _i64), ("n_adam", _i64), ("exp_avg", _vp), ("exp_avg_sq", _vp), ("lr", _f32), ("beta1", _f32),
-                ("beta2", _f32), ("adam_eps", _f32), ("adam_step", _i32), ("cooperative", _i32), ("threads", _i32)]
+                ("beta2", _f32), ("adam_eps", _f32), ("adam_step", _i32), ("cooperative", _i32), ("threads", _i32), ("mc_block", _vp)]
 
 
 class MappingArgs(C.Structure):

@@ -29,6 +29,7 @@ constexpr int kPadErrWord = PINQ_PEER_MAX_GRID * 8;  // uint32 index of the erro
 
 struct PeerDev {
     float* block[PINQ_PEER_MAX];
+    float* mc;                 // NVLS multicast address of the same block (all ranks' copies at once), or nullptr
     int rank, world;
     int64_t sum_off4, nsum4;   // fp32 sum region, in float4 units from the block base
     int64_t max_off2, nmax2;   // int64 max region, in longlong2 units
@@ -69,6 +70,37 @@ __device__ __forceinline__ void peer_barrier(const PeerDev& a, uint32_t value) {
     __syncthreads();
 }
 
+// NVLS (NVSwitch multicast): ONE load returns the element summed over every rank's copy, reduced inside the switch, and ONE
+// store lands in every rank's copy -- 2 memory instructions per 16 bytes of the owned slice instead of 2 x world.
+__device__ __forceinline__ float4 multimem_ld_reduce_add(const float4* mc) {
+    float4 v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(mc) : "memory");
+    return v;
+}
+__device__ __forceinline__ void multimem_st(float4* mc, const float4 v) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};"
+                 :: "l"(mc), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+
+// torch.optim.Adam single-tensor arithmetic (k_adam, gn.cu) on float4 i of the owned slice; state lives on the owner only
+__device__ __forceinline__ float4 adam_update4(const PeerDev& a, int64_t i, const float4 s) {
+    float4 m = reinterpret_cast<float4*>(a.exp_avg)[i], q = reinterpret_cast<float4*>(a.exp_avg_sq)[i];
+    float4 w = __ldcg(reinterpret_cast<const float4*>(a.block[a.rank]) + a.par_off4 + i);
+    const float g[4] = {s.x, s.y, s.z, s.w};
+    float* mm = &m.x; float* qq = &q.x; float* ww = &w.x;
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+        mm[c] = mm[c] + (g[c] - mm[c]) * (1.f - a.beta1);
+        qq[c] = qq[c] * a.beta2 + (1.f - a.beta2) * g[c] * g[c];
+        const float denom = sqrtf(qq[c]) / a.bc2_sqrt + a.eps;
+        ww[c] = ww[c] - a.step_size * (mm[c] / denom);
+    }
+    reinterpret_cast<float4*>(a.exp_avg)[i] = m;
+    reinterpret_cast<float4*>(a.exp_avg_sq)[i] = q;
+    return w;
+}
+
 // T = threads per CTA.  512 (one CTA fills most of an SM's registers) is the stand-alone form.  128 with at most 56 registers
 // is the form that runs UNDER another kernel: one of its CTAs fits into exactly the registers ONE retiring CTA of the
 // neighbour search (128 threads x 56 registers, 9 per SM) leaves behind, so the exchange gets onto the SMs as soon as
@@ -85,6 +117,25 @@ __global__ void __launch_bounds__(T, T == 128 ? 9 : 1) k_peer_exchange(PeerDev a
         constexpr int U = T == 128 ? (W >= 4 ? 1 : 4 / W) : (W >= 8 ? 2 : (W == 4 ? 4 : 8));
         constexpr int PC = (T == 128 && W > 4) ? 4 : W;  // ranks loaded per round
         const int64_t lo = a.nsum4 * a.rank / W, hi = a.nsum4 * (a.rank + 1) / W;
+        if (a.mc) {  // NVLS form: same slices, same element -> thread mapping (the zero_grad below relies on it)
+            constexpr int UM = 4;
+            float4* mc = reinterpret_cast<float4*>(a.mc);
+            for (int64_t i0 = lo + tid; i0 < hi; i0 += nthr * UM) {
+                float4 v[UM];
+#pragma unroll
+                for (int u = 0; u < UM; ++u) {
+                    const int64_t i = i0 + u * nthr;
+                    if (i < hi) v[u] = multimem_ld_reduce_add(mc + a.sum_off4 + i);
+                }
+#pragma unroll
+                for (int u = 0; u < UM; ++u) {
+                    const int64_t i = i0 + u * nthr;
+                    if (i >= hi) break;
+                    if (ADAM && i < a.nadam4) multimem_st(mc + a.par_off4 + i, adam_update4(a, i, v[u]));
+                    else multimem_st(mc + a.sum_off4 + i, v[u]);
+                }
+            }
+        } else
         for (int64_t i0 = lo + tid; i0 < hi; i0 += nthr * U) {
             float4 acc[U];
 #pragma unroll
@@ -113,20 +164,7 @@ __global__ void __launch_bounds__(T, T == 128 ? 9 : 1) k_peer_exchange(PeerDev a
                 if (i >= hi) break;
                 const float4 s = acc[u];
                 if (ADAM && i < a.nadam4) {
-                    // torch.optim.Adam single-tensor arithmetic (k_adam, gn.cu) on the owned slice; state lives on the owner only
-                    float4 m = reinterpret_cast<float4*>(a.exp_avg)[i], q = reinterpret_cast<float4*>(a.exp_avg_sq)[i];
-                    float4 w = __ldcg(reinterpret_cast<const float4*>(a.block[a.rank]) + a.par_off4 + i);
-                    const float g[4] = {s.x, s.y, s.z, s.w};
-                    float* mm = &m.x; float* qq = &q.x; float* ww = &w.x;
-#pragma unroll
-                    for (int c = 0; c < 4; ++c) {
-                        mm[c] = mm[c] + (g[c] - mm[c]) * (1.f - a.beta1);
-                        qq[c] = qq[c] * a.beta2 + (1.f - a.beta2) * g[c] * g[c];
-                        const float denom = sqrtf(qq[c]) / a.bc2_sqrt + a.eps;
-                        ww[c] = ww[c] - a.step_size * (mm[c] / denom);
-                    }
-                    reinterpret_cast<float4*>(a.exp_avg)[i] = m;
-                    reinterpret_cast<float4*>(a.exp_avg_sq)[i] = q;
+                    const float4 w = adam_update4(a, i, s);
 #pragma unroll
                     for (int p = 0; p < W; ++p)
                         __stcg(reinterpret_cast<float4*>(a.block[p]) + a.par_off4 + i, w);  // parameter broadcast
@@ -279,6 +317,7 @@ int pinq_peer_exchange(const pinq_peer_args* a, void* stream) {
     PINQ_REQUIRE(a->threads == 0 || a->threads == 128 || a->threads == kPeerThreads, "threads: 0 (= 512), 128 or 512");
     PeerDev d{};
     for (int p = 0; p < a->world; ++p) d.block[p] = reinterpret_cast<float*>(a->block[p]);
+    d.mc = a->world > 1 ? reinterpret_cast<float*>(a->mc_block) : nullptr;
     d.rank = a->rank;
     d.world = a->world;
     d.sum_off4 = a->sum_off / 16;

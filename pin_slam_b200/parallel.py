@@ -171,7 +171,7 @@ class PeerExchange:
     streams: the single-GPU form used by the GPU tests (same kernel, same flags, same P2P code path minus the link)."""
 
     def __init__(self, layout: PeerLayout, device, group=None, simulate_world: int = 0, grid: int = 0, timeout_ms: float = 0.0,
-                 cooperative: bool = True, threads: int = 0):
+                 cooperative: bool = True, threads: int = 0, multicast=None):
         import ctypes as C
         from . import _pinq as P
         self.P, self.lib, self.layout, self.device = P, P.load(), layout, torch.device(device)
@@ -189,7 +189,26 @@ class PeerExchange:
         self.timeout_ms = float(timeout_ms) if timeout_ms else float(os.environ.get("PINQ_PEER_TIMEOUT_MS", "0"))
         self.simulated = simulate_world > 0
         self._mapped, self._owned = [], []
+        # NVLS: blocks allocated through torch's symmetric memory (cuMemCreate + one multicast object bound to every rank's
+        # block; torch does the handle exchange) instead of cudaMalloc + cudaIpc; multicast None = when the box offers it
+        # (PINQ_PEER_MULTICAST=0 / 1 overrides), False = never.  self.mc_block == 0 means the P2P form.
+        self.mc_block, self._symm = 0, None
+        if multicast is None:
+            multicast = os.environ.get("PINQ_PEER_MULTICAST", "auto")
+            multicast = None if multicast == "auto" else multicast not in ("0", "false", "False")
+        if not self.simulated and multicast is not False and world_info(group)[1] > 1:
+            self._symm = self._symmetric_block(layout.nbytes, group, required=multicast is True)
         with torch.cuda.device(self.device):
+            if self._symm is not None:
+                self.rank, self.world = world_info(group)
+                tensor, hdl = self._symm
+                self.blocks = [int(b) for b in hdl.buffer_ptrs]
+                self.mc_block = int(hdl.multicast_ptr)
+                if self.blocks[self.rank] != tensor.data_ptr():
+                    raise self.P.PinqError("symmetric memory: this rank's buffer is not the tensor it allocated")
+                self._epochs = [0]
+                self._views = [tensor]
+                return
             if self.simulated:
                 self.rank, self.world = 0, int(simulate_world)
                 self.blocks = []
@@ -222,6 +241,36 @@ class PeerExchange:
         self._epochs = [0] * (self.world if self.simulated else 1)
         self._views = [torch.as_tensor(_RawCuda(b, layout.nbytes), device=self.device)
                        for b in (self.blocks if self.simulated else [self.blocks[self.rank]])]
+
+    def _symmetric_block(self, nbytes: int, group, required: bool):
+        """(tensor, handle) of a zero-filled symmetric-memory block with an NVLS multicast address, or None when the box has
+        no multicast support (every rank takes the same branch: the support is a property of the node)."""
+        try:
+            import torch.distributed._symmetric_memory as symm
+            from torch._C._distributed_c10d import _SymmetricMemory as S
+            ok = bool(S.has_multicast_support(torch._C._autograd.DeviceType.CUDA, self.device.index or 0))
+        except Exception:  # noqa: BLE001 -- torch build without symmetric memory
+            ok = False
+        flag = torch.tensor([1 if ok else 0], device=self.device, dtype=torch.int32)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
+        if int(flag.item()) == 0:
+            if required:
+                raise self.P.PinqError("NVLS multicast requested but not supported on this node")
+            return None
+        with torch.cuda.device(self.device):
+            t = symm.empty(nbytes, dtype=torch.uint8, device=self.device)
+            t.zero_()
+            torch.cuda.synchronize(self.device)
+            hdl = symm.rendezvous(t, group if group is not None else dist.group.WORLD)
+        ok = 1 if int(hdl.multicast_ptr) != 0 else 0
+        flag = torch.tensor([ok], device=self.device, dtype=torch.int32)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
+        if int(flag.item()) == 0:
+            if required:
+                raise self.P.PinqError("symmetric memory rendezvous returned no multicast address")
+            return None
+        dist.barrier(group=group)
+        return t, hdl
 
     # -- typed views of a block's regions (this rank's block; `r` selects the block in the simulated form)
     def _view(self, r=None):
@@ -259,6 +308,7 @@ class PeerExchange:
         a.rank, a.world = rank, self.world
         for r, b in enumerate(self.blocks):
             a.block[r] = b
+        a.mc_block = self.mc_block or None
         a.sum_off, a.n_sum, a.max_off, a.n_max = L.sum_off + 4 * sum_off_elems, n_sum, L.max_off, n_max
         a.epoch, a.grid, a.timeout_ms, a.threads = epoch, self.grid, self.timeout_ms, self.threads
         a.cooperative = 0 if (self.simulated or not self.cooperative) else 1  # simulated ranks share one device and wait for each other
@@ -298,6 +348,7 @@ class PeerExchange:
 
     def close(self):
         self._views = []
+        self._symm = None
         for m in self._mapped:
             self.lib.pinq_peer_close(m)
         for o in self._owned:
