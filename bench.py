@@ -487,7 +487,8 @@ def mapping_leg(dev, world, rank, iters=15, batch=1 << 20, pool_n=8_000_000):
     rows, fdim = npts.local_geo_features.shape
     if world > 1:
         peer = PeerExchange(MappingPeer.capacity(rows, fdim, dec, with_params=True), dev, grid=int(os.environ.get("PINQ_MAP_PEER_GRID", "48")),
-                            threads=int(os.environ.get("PINQ_MAP_PEER_THREADS", "0")))
+                            threads=int(os.environ.get("PINQ_MAP_PEER_THREADS", "0")),
+                            multicast=os.environ.get("PINQ_MAP_PEER_MULTICAST", "0") == "1")  # NVLS form: not measured on this leg
         torch.cuda.synchronize()
         dist.barrier()
         mapper.dp = DataParallelMapping(peer)
@@ -970,6 +971,7 @@ def main():
 
     peer_err = peer.error() if peer is not None else 0
     had_peer = peer is not None
+    peer_form = None if peer is None else ("NVLS multimem.ld_reduce / multimem.st" if peer.mc_block else "P2P loads / stores")
     config_line = workload_config(args, npts.count(), vbar, world)
     slam = flav = sweep = mapping = mesher_res = None
     if rank == 0 and world == 1 and not args.no_extra_legs:
@@ -1026,6 +1028,7 @@ def main():
             line["gpu_launches"] += args.steps
             line["peer_exchange_error"] = peer_err
             line["exchange_overlapped_with_next_search"] = bool(overlap)
+            line["exchange_form"] = peer_form
             if overlap_trace:
                 line["overlap_trace"] = overlap_trace
         if exchange_ms is not None:
