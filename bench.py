@@ -665,8 +665,6 @@ def main():
     if overlap:
         ev_x.record(torch.cuda.current_stream())
 
-    delay_cycles = int(os.environ.get("PINQ_EXCHANGE_DELAY_CYCLES", "0"))
-
     def exchange_grads():
         if skip_exchange[0]:
             return
@@ -687,8 +685,6 @@ def main():
             ev_bwd.record(main)
             with torch.cuda.stream(side):
                 side.wait_event(ev_bwd)
-                if delay_cycles:
-                    torch.cuda._sleep(delay_cycles)
                 peer.exchange(n_sum=n_ex, n_max=0)
                 grad_block.zero_()
                 ev_x.record(side)
