@@ -249,6 +249,14 @@ typedef struct pinq_query_args {
                                   binning and the neighbour search read only query points and map geometry, so a
                                   data-parallel caller lets them run under the previous step's gradient exchange /
                                   optimizer (which the decode, reading features and decoder, must follow)   */
+    void* zero_fill;           /* NULL, or a device buffer of zero_fill_bytes (a multiple of 16, 16-byte aligned) that the
+                                  fused forward sets to zero on its way: the feature-gradient block the backward of this
+                                  query accumulates into (replaces the 53 MB memset of `torch.zeros_like(features)`
+                                  between forward and backward: one streaming 16-byte store per thread of the
+                                  neighbour search, which has the HBM bandwidth to spare).  Done by a plain memset
+                                  when the batch has fewer than zero_fill_bytes / 16 queries or takes the slot-probing
+                                  search.  Not touched when `skip` is set.  pinq_query_fused_fwd only.           */
+    int64_t zero_fill_bytes;
 } pinq_query_args;
 
 int64_t pinq_query_workspace_bytes(int64_t n);

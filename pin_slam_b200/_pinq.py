@@ -32,7 +32,8 @@ class QueryArgs(C.Structure):
     _fields_ = [("map", MapView), ("dec", DecoderView), ("xyz", _vp), ("n", _i64), ("flags", _u32), ("k", _i32),
                 ("feature_dim", _i32), ("features", _vp), ("point_xyz", _vp), ("certainties", _vp), ("quats", _vp), ("ts_update", _vp),
                 ("query_ts", _vp), ("sdf", _vp), ("grad_x", _vp), ("sdf_std", _vp), ("nn_count", _vp),
-                ("certainty", _vp), ("knn_idx", _vp), ("knn_w", _vp), ("knn_d2", _vp), ("stage", _vp), ("relu_mask", _vp), ("perm", _vp), ("workspace", _vp), ("skip", _vp), ("decode_wait_event", _vp)]
+                ("certainty", _vp), ("knn_idx", _vp), ("knn_w", _vp), ("knn_d2", _vp), ("stage", _vp), ("relu_mask", _vp), ("perm", _vp), ("workspace", _vp), ("skip", _vp), ("decode_wait_event", _vp),
+                ("zero_fill", _vp), ("zero_fill_bytes", _i64)]
 
 
 class BwdArgs(C.Structure):

@@ -129,6 +129,8 @@ struct DecodeParams {
     int min_nn;           // mesher
     uint8_t* mask_out;
     const int32_t* skip;  // device flag: non-zero = this launch is a no-op (device-side Gauss-Newton loop, gn.cu)
+    float4* zero_fill = nullptr;  // pinq_query_args.zero_fill: thread i of the brick search clears float4 i of it
+    int64_t zero_fill4 = 0;
 };
 
 // Per-query part shared by the fused decode and the un-fused query_feature: resolve the K record ranks
@@ -317,6 +319,10 @@ __global__ void __launch_bounds__(kBlock, PINQ_SEARCH_MINB) k_search_brick(MapDe
                                                          const unsigned long long* __restrict__ stencil_masks,
                                                          int32_t* __restrict__ ws, const DecodeParams p) {
     if (p.skip && *p.skip) return;
+    {   // pinq_query_args.zero_fill: the gradient block of the backward that follows, cleared with one streaming store per thread
+        const int64_t zi = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+        if (zi < p.zero_fill4) __stcs(p.zero_fill + zi, make_float4(0.f, 0.f, 0.f, 0.f));
+    }
     extern __shared__ __align__(16) unsigned char s_brick_raw[];
     BrickLane* bl = reinterpret_cast<BrickLane*>(s_brick_raw);
     // stencil masks staged as 32-bit HALF-brick masks, [2 b + h][s] with s = box origin inside its brick (0..63): a lane reads
@@ -932,7 +938,10 @@ static int run_query(const pinq_query_args* a, int mode, float* feat_out, const 
         return PINQ_ERR_BAD_ARG;
     }
     const int64_t n = grid_src ? a->n : a->n;
-    if (n == 0) return PINQ_OK;
+    if (n == 0) {
+        if (mode == 0 && a->zero_fill && a->zero_fill_bytes > 0) cudaMemsetAsync(a->zero_fill, 0, (size_t)a->zero_fill_bytes, st);
+        return PINQ_OK;
+    }
     const MapDev map = to_dev(a->map);
     PointSrc src;
     if (grid_src) src = *grid_src;
@@ -978,6 +987,18 @@ static int run_query(const pinq_query_args* a, int mode, float* feat_out, const 
     p.sdf = a->sdf; p.grad_x = a->grad_x; p.sdf_std = a->sdf_std; p.nn_count = a->nn_count;
     p.certainty = a->certainty; p.knn_idx = a->knn_idx; p.knn_w = a->knn_w; p.knn_d2 = a->knn_d2;
     p.feat_out = feat_out; p.min_nn = min_nn; p.mask_out = mask_out; p.skip = a->skip;
+    if (a->zero_fill && a->zero_fill_bytes > 0 && mode == 0) {
+        if ((a->zero_fill_bytes & 15) || (reinterpret_cast<uintptr_t>(a->zero_fill) & 15)) {
+            set_error("zero_fill: 16-byte aligned buffer, size a multiple of 16");
+            return PINQ_ERR_BAD_ARG;
+        }
+        if (brick && a->zero_fill_bytes / 16 <= (int64_t)grid_for(n, kBlock) * kBlock && !a->skip) {
+            p.zero_fill = reinterpret_cast<float4*>(a->zero_fill);
+            p.zero_fill4 = a->zero_fill_bytes / 16;
+        } else if (cudaMemsetAsync(a->zero_fill, 0, (size_t)a->zero_fill_bytes, st) != cudaSuccess) {
+            return check_launch("zero_fill memset");
+        }
+    }
     p.relu_mask = reinterpret_cast<uint32_t*>(a->relu_mask);
     p.stage = reinterpret_cast<StageBlock*>(a->stage ? a->stage
                                                      : reinterpret_cast<unsigned char*>(a->workspace) + ws_off_stage(n));

@@ -105,6 +105,7 @@ class NeuralPoints(nn.Module):
         self.brick_max_points = 1 << 24
         self.exact_search_keys = False  # A/B tests: brick search with 64-bit keys for every query
         self.skip_in_range_test = True  # A/B tests: False keeps the per-candidate `d2 > max_valid_dist2` comparison
+        self.zero_grad_in_search = True  # the fused forward clears the feature-gradient block of its backward (zero_fill)
         self.decode_wait_event = None  # torch.cuda.Event the fused query's decode waits for (see pinq_query_args)
         self.use_mma_sync = False  # A/B tests: the mma.sync decode / backward kernels instead of the tcgen05 ones
         self._brick_tab = self._brick_global = self._brick_local = self._brick_buf = self._brick_counters = None
@@ -667,7 +668,16 @@ class _FusedSDFFn(torch.autograd.Function):
         if want_certainty:
             cert = torch.empty(n, dtype=torch.float32, device=dev)
             a.certainty = P.ptr(cert)
+        g_feats = None
+        if (ctx.needs_input_grad[3] and npts.zero_grad_in_search and getattr(npts, "feature_grad_sink", None) is None
+                and feats.dtype == torch.float32 and feats.is_contiguous() and feats.numel() % 4 == 0
+                and 16 * n >= 4 * feats.numel()):
+            # the feature-gradient block of THIS query's backward, cleared by the neighbour search on its way
+            # (pinq_query_args.zero_fill) instead of a 53 MB memset between forward and backward
+            g_feats = torch.empty_like(feats)
+            a.zero_fill, a.zero_fill_bytes = P.ptr(g_feats), 4 * feats.numel()
         P.check(lib.pinq_query_fused_fwd(a, P.stream()))
+        ctx.g_feats = g_feats
         ctx.npts, ctx.decoder, ctx.query_locally = npts, decoder, query_locally
         ctx.after_pgo = npts.after_pgo
         if need_bwd:
@@ -707,7 +717,9 @@ class _FusedSDFFn(torch.autograd.Function):
                     raise P.PinqError("feature_grad_sink must be a float32 tensor shaped like local_geo_features")
                 b.grad_features = P.ptr(f_sink)
             else:
-                g_feats = torch.zeros_like(feats)
+                g_feats, ctx.g_feats = ctx.g_feats, None  # cleared by the forward's search; a second backward gets a fresh one
+                if g_feats is None:
+                    g_feats = torch.zeros_like(feats)
                 b.grad_features = P.ptr(g_feats)
         if any(ctx.needs_input_grad[i] for i in (4, 5, 6, 7)):  # decoder not frozen (hazard H11)
             W1, b1, W2, b2 = decoder.fused_params()

@@ -296,6 +296,59 @@ def test_skipped_distance_test_changes_nothing(maps):
     assert torch.equal(res[True][2].cpu().long(), nn_ref.long())
 
 
+def test_search_clears_the_gradient_block_of_its_backward(maps):
+    """pinq_query_args.zero_fill: the fused forward clears the feature-gradient block its backward accumulates into (one store
+    per thread of the neighbour search; a memset when the batch is smaller than the block or takes the slot-probing search).
+    The block is handed out by the allocator right after a poisoned tensor of the same size was freed: a store the search
+    skipped would show up as 1e3 in the gradient.  Same gradients as with the memset of `torch.zeros_like`, and the oracle's."""
+    s, m, _, dec, d, _ = maps
+    from pin_slam_b200 import _pinq as P
+    rows = m.local_geo_features.shape[0]
+    n = max(4 * rows, 50000)
+    q = make_queries(s.points, n, seed=43)
+    up = torch.randn(n, generator=torch.Generator().manual_seed(6))
+    # the C-ABI contract, both branches: search stores (n >= bytes / 16) and memset (n < bytes / 16)
+    for nq in (n, 1000):
+        buf = torch.full((rows, m.local_geo_features.shape[1]), 7.0, device="cuda")
+        a = m._query_args(q[:nq].cuda(), dec.view(), None, False, True)
+        sdf = torch.empty(nq, device="cuda")
+        nn = torch.empty(nq, dtype=torch.int32, device="cuda")
+        a.sdf, a.nn_count = P.ptr(sdf), P.ptr(nn)
+        a.zero_fill, a.zero_fill_bytes = P.ptr(buf), buf.numel() * 4
+        P.check(P.load().pinq_query_fused_fwd(a, P.stream()))
+        torch.cuda.synchronize()
+        assert torch.all(buf == 0), nq
+    a.zero_fill_bytes = 8
+    assert P.load().pinq_query_fused_fwd(a, P.stream()) == -1  # PINQ_ERR_BAD_ARG: size not a multiple of 16
+    # the autograd path
+    grads = {}
+    cert0, ts0 = m.local_point_certainties.clone(), m.local_point_ts_update.clone()
+    try:
+        for flag in (True, False):
+            m.zero_grad_in_search = flag
+            m.local_geo_features.grad = None
+            for p_ in dec.parameters():
+                p_.grad = None
+            junk = torch.full_like(m.local_geo_features, 1e3)
+            del junk
+            out = m.query_sdf(q.cuda(), dec, None, True, True)
+            (out["sdf"] * up.cuda()).sum().backward()
+            grads[flag] = m.local_geo_features.grad.clone()
+    finally:
+        m.zero_grad_in_search = True
+        m.local_point_certainties, m.local_point_ts_update = cert0, ts0
+    assert float(grads[True].abs().max()) < 100.0
+    assert rel_err(grads[True], grads[False]) < 1e-5
+    s2 = build_state_copy(s)
+    s2.l_feats.requires_grad_(True)
+    ref = O.query_sdf(s2, d, q[:20000], None, False, True)
+    m.local_geo_features.grad = None
+    out = m.query_sdf(q[:20000].cuda(), dec, None, False, True)   # 20 000 < 2 x rows or not: either branch must match the oracle
+    (out["sdf"] * up[:20000].cuda()).sum().backward()
+    (ref["sdf"] * up[:20000]).sum().backward()
+    assert rel_err(m.local_geo_features.grad, s2.l_feats.grad) < TOL
+
+
 def test_truncated_key_search_equals_exact_keys(maps):
     """Brick search fast pass (32-bit keys: 23 bits of d^2 | walk identity, csrc/query.cu) against the 64-bit-key pass
     forced for every query (PINQ_F_EXACT_KEYS): same K neighbours in the same order, also for queries built to tie
